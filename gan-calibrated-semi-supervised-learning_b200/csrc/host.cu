@@ -1,0 +1,76 @@
+// Host-side plumbing of the C-ABI: last-error string, launch checks, TMA tensor-map encoding through
+// the driver entry point (no link-time dependency on libcuda).
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "tmap.h"
+
+static thread_local char g_err[512] = "";
+
+void b2c_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int b2c_check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    b2c_set_error("%s: %s", what, cudaGetErrorString(e));
+    return B2C_ERR_CUDA;
+  }
+  return B2C_OK;
+}
+
+extern "C" const char* b2c_last_error(void) { return g_err; }
+extern "C" int b2c_abi_version(void) { return 1; }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// rank-R bf16 tensor map, 128-byte swizzle, zero OOB fill.  dims/box innermost first; strides in BYTES for dims 1..R-1.
+int b2c_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                       const uint32_t* box) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    b2c_set_error("cuTensorMapEncodeTiled driver entry point unavailable");
+    return B2C_ERR_DRIVER;
+  }
+  cuuint64_t gd[5], gs[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gd[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+    if (i > 0) gs[i - 1] = strides_bytes[i - 1];
+  }
+  if (((uintptr_t)base & 15) != 0) {
+    b2c_set_error("tensor map base not 16-byte aligned");
+    return B2C_ERR_ARG;
+  }
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    b2c_set_error("cuTensorMapEncodeTiled failed (%d): rank %d dims %llu %llu %llu box %u %u %u", (int)r, rank,
+                  (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
+                  (unsigned long long)(rank > 2 ? dims[2] : 0), box[0], rank > 1 ? box[1] : 0, rank > 2 ? box[2] : 0);
+    return B2C_ERR_DRIVER;
+  }
+  return B2C_OK;
+}

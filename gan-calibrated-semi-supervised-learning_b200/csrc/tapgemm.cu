@@ -1,0 +1,246 @@
+// tcgen05 implicit-GEMM convolutions for the cGAN step (sm_100a only).
+//
+// Every k4/s2/p1 convolution of the reference (cgan/models.py:57,72,113,236) and its data gradient is a sum of
+// "taps": one [128 pixels x 64 channels] activation box per (ky,kx) tap, times a [BN x 64] slice of packed weights.
+//   mode C4S2 : y[n,oy,ox,:]       = sum_{ky,kx} x[n,2oy+ky-1,2ox+kx-1,:] . Wc[:, (ky,kx,:)]        (16 taps)
+//               The NHWC input is viewed as a 5-D tensor (dj*C+c, j, di, i, n) with h=2i+di, w=2j+dj, so a tap is a
+//               plain TMA box; the conv's zero padding is TMA out-of-bounds fill (no padded copies, no im2col).
+//   mode T4S2 : y[n,2i+py,2j+px,:] = sum_{a,b}  x[n,i+py+a-1,j+px+b-1,:] . Wt[py,px][:, (a,b,:)]     (4 taps x 4 parities)
+//               = ConvTranspose2d(k4,s2,p1) and also the data gradient of C4S2.
+// Pipeline: warp 0 = TMA producer, warp 1 = single-thread tcgen05.mma issuer (accumulator in TMEM),
+// warps 2-5 = epilogue (tcgen05.ld -> +bias -> bf16 -> NHWC stores).  2 CTAs/SM overlap epilogue with mainloop.
+#include "common.cuh"
+#include "tmap.h"
+
+using namespace b2c;
+
+struct TapGemmParams {
+  int mode;  // 0 = C4S2, 1 = T4S2
+  int N, Ho, Wo, Cin, Cout;
+  int BW, BH, BI;           // pixel box, BW*BH*BI == 128
+  int tiles_x, tiles_y;     // tile grid over the tile space (C: output pixels; T: input-resolution pixels)
+  int kchunks;              // Cin / 64
+  __nv_bfloat16* y;
+  long long ldy;            // output pixel stride in elements
+  const float* bias;        // nullable, per output channel
+};
+
+template <int BN>
+struct TapGemmCfg {
+  static constexpr int STAGES = (BN == 128) ? 3 : 4;
+  static constexpr int A_BYTES = 128 * 128;
+  static constexpr int B_BYTES = BN * 128;
+  static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                      const __grid_constant__ CUtensorMap tmB, TapGemmParams p) {
+  using Cfg = TapGemmCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * Cfg::A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * Cfg::B_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile = blockIdx.x;
+  const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, tn = tile / (p.tiles_x * p.tiles_y);
+  const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
+  const int ncol0 = blockIdx.y * BN;
+  const int parity = blockIdx.z, py = parity >> 1, px = parity & 1;
+  const int ntaps = p.mode == 0 ? 16 : 4;
+  const int niters = ntaps * p.kchunks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<BN>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0, phase = 0;
+      for (int tap = 0; tap < ntaps; ++tap) {
+        for (int cc = 0; cc < p.kchunks; ++cc) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_expect_tx(&full[stage], Cfg::A_BYTES + Cfg::B_BYTES);
+          void* dA = sA + stage * Cfg::A_BYTES;
+          if (p.mode == 0) {
+            const int ky = tap >> 2, kx = tap & 3;
+            const int fy = (ky - 1) >> 1, di = (ky - 1) & 1, fx = (kx - 1) >> 1, dj = (kx - 1) & 1;
+            tma_load_5d(dA, &tmA, &full[stage], dj * p.Cin + cc * 64, x0 + fx, di, y0 + fy, n0);
+          } else {
+            const int a = tap >> 1, b = tap & 1;
+            tma_load_4d(dA, &tmA, &full[stage], cc * 64, x0 + px + b - 1, y0 + py + a - 1, n0);
+          }
+          tma_load_2d(sB + stage * Cfg::B_BYTES, &tmB, &full[stage], tap * p.Cin + cc * 64,
+                      parity * p.Cout + ncol0);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+      int stage = 0, phase = 0;
+      for (int it = 0; it < niters; ++it) {
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(sA + stage * Cfg::A_BYTES), b0 = smem_u32(sB + stage * Cfg::B_BYTES);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_bf16(tmem_base, umma_desc_sw128(a0 + k * 32, 16, 1024), umma_desc_sw128(b0 + k * 32, 16, 1024), idesc,
+                    (uint32_t)((it | k) != 0));
+        umma_commit(&empty[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    const int r = q * 32 + lane;
+    const int bw = r % p.BW, bh = (r / p.BW) % p.BH, bi = r / (p.BW * p.BH);
+    const int n = n0 + bi;
+    int oy = y0 + bh, ox = x0 + bw;
+    if (p.mode == 1) { oy = 2 * oy + py; ox = 2 * ox + px; }
+    const bool valid = n < p.N;
+    __nv_bfloat16* dst = p.y + (((long long)n * p.Ho + oy) * p.Wo + ox) * p.ldy + ncol0;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      uint32_t v0[16], v1[16];
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + c0;
+      tmem_ld16(taddr, v0);
+      tmem_ld16(taddr + 16, v1);
+      tmem_ld_wait();
+      if (valid) {
+        uint32_t o[16];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float a = __uint_as_float(v0[2 * j]), b = __uint_as_float(v0[2 * j + 1]);
+          float c = __uint_as_float(v1[2 * j]), d = __uint_as_float(v1[2 * j + 1]);
+          if (p.bias) {
+            a += __ldg(p.bias + ncol0 + c0 + 2 * j);
+            b += __ldg(p.bias + ncol0 + c0 + 2 * j + 1);
+            c += __ldg(p.bias + ncol0 + c0 + 16 + 2 * j);
+            d += __ldg(p.bias + ncol0 + c0 + 16 + 2 * j + 1);
+          }
+          o[j] = pack_bf16(a, b);
+          o[8 + j] = pack_bf16(c, d);
+        }
+        uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
+        d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+        d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
+        d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<BN>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+static bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+
+// Pixel box for a 128-row tile over a (TH x TW) tile space: widest row run first, then rows, then images.
+static int pick_box(int TH, int TW, int rows, int* BW, int* BH, int* BI) {
+  if (!is_pow2(TH) || !is_pow2(TW)) return 0;
+  *BW = TW < rows ? TW : rows;
+  int rem = rows / *BW;
+  *BH = TH < rem ? TH : rem;
+  *BI = rem / *BH;
+  return (*BW) * (*BH) * (*BI) == rows && *BI <= 256;
+}
+
+template <int BN>
+static int launch_tapgemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const TapGemmParams& p, dim3 grid,
+                          cudaStream_t st) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(tapgemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         TapGemmCfg<BN>::SMEM);
+    if (e != cudaSuccess) {
+      b2c_set_error("cudaFuncSetAttribute(tapgemm): %s", cudaGetErrorString(e));
+      return B2C_ERR_CUDA;
+    }
+    attr_done = true;
+  }
+  tapgemm_kernel<BN><<<grid, 192, TapGemmCfg<BN>::SMEM, st>>>(tmA, tmB, p);
+  return b2c_check_launch("tapgemm_kernel");
+}
+
+static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack, const float* bias, void* y,
+                       long long ldy, int N, int H, int W, int Cin, int Cout, void* stream) {
+  B2C_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "tapgemm: Cin=%d Cout=%d must be multiples of 64", Cin, Cout);
+  B2C_REQUIRE(ldy % 8 == 0 && ((uintptr_t)y & 15) == 0, "tapgemm: output must be 16-byte aligned (ldy=%lld)", ldy);
+  TapGemmParams p;
+  p.mode = mode; p.N = N; p.Cin = Cin; p.Cout = Cout; p.kchunks = Cin / 64;
+  p.y = (__nv_bfloat16*)y; p.ldy = ldy; p.bias = bias;
+  int TH, TW;
+  CUtensorMap tmA, tmB;
+  if (mode == 0) {
+    B2C_REQUIRE(ldx == Cin, "conv4s2: input must be dense NHWC (ldx=%lld, Cin=%d)", ldx, Cin);
+    B2C_REQUIRE(H % 2 == 0 && W % 2 == 0, "conv4s2: odd input size %dx%d", H, W);
+    p.Ho = H / 2; p.Wo = W / 2; TH = p.Ho; TW = p.Wo;
+  } else {
+    B2C_REQUIRE(ldx % 8 == 0, "convt4s2: ldx=%lld must be a multiple of 8", ldx);
+    p.Ho = 2 * H; p.Wo = 2 * W; TH = H; TW = W;
+  }
+  B2C_REQUIRE(pick_box(TH, TW, 128, &p.BW, &p.BH, &p.BI), "tapgemm: unsupported spatial size %dx%d (need powers of two)", TH, TW);
+  p.tiles_x = TW / p.BW; p.tiles_y = TH / p.BH;
+  const int tiles_n = (N + p.BI - 1) / p.BI;
+  int rc;
+  if (mode == 0) {
+    uint64_t dims[5] = {(uint64_t)2 * Cin, (uint64_t)W / 2, 2, (uint64_t)H / 2, (uint64_t)N};
+    uint64_t str[4] = {(uint64_t)4 * Cin, (uint64_t)2 * W * Cin, (uint64_t)4 * W * Cin, (uint64_t)2 * H * W * Cin};
+    uint32_t box[5] = {64, (uint32_t)p.BW, 1, (uint32_t)p.BH, (uint32_t)p.BI};
+    rc = b2c_make_tmap_bf16(&tmA, x, 5, dims, str, box);
+  } else {
+    uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint64_t str[3] = {(uint64_t)2 * ldx, (uint64_t)2 * W * ldx, (uint64_t)2 * H * W * ldx};
+    uint32_t box[4] = {64, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BI};
+    rc = b2c_make_tmap_bf16(&tmA, x, 4, dims, str, box);
+  }
+  if (rc) return rc;
+  const int BN = (Cout % 128 == 0) ? 128 : 64;
+  const int K = (mode == 0 ? 16 : 4) * Cin;
+  const int rows = (mode == 0 ? 1 : 4) * Cout;
+  {
+    uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
+    uint64_t str[1] = {(uint64_t)2 * K};
+    uint32_t box[2] = {64, (uint32_t)BN};
+    rc = b2c_make_tmap_bf16(&tmB, wpack, 2, dims, str, box);
+    if (rc) return rc;
+  }
+  dim3 grid(p.tiles_x * p.tiles_y * tiles_n, Cout / BN, mode == 0 ? 1 : 4);
+  if (BN == 128) return launch_tapgemm<128>(tmA, tmB, p, grid, (cudaStream_t)stream);
+  return launch_tapgemm<64>(tmA, tmB, p, grid, (cudaStream_t)stream);
+}
+
+extern "C" int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* bias, void* y,
+                                long long ldy, int N, int H, int W, int Cin, int Cout, void* stream) {
+  return run_tapgemm(0, x, ldx, wpack_c, bias, y, ldy, N, H, W, Cin, Cout, stream);
+}
+
+extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y,
+                                 long long ldy, int N, int H, int W, int Cin, int Cout, void* stream) {
+  return run_tapgemm(1, x, ldx, wpack_t, bias, y, ldy, N, H, W, Cin, Cout, stream);
+}
