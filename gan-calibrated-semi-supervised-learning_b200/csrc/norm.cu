@@ -1,0 +1,330 @@
+// InstanceNorm2d(affine=False, eps=1e-5) + LeakyReLU/ReLU + Dropout(0.5) fused bandwidth kernels, forward, backward and
+// backward-of-backward (cgan/models.py:59-62,73-77,114,241-242; the second-order path is what
+// compute_gradient_penalty, cgan/losses.py:213-220, pushes through D).  Formulas: SURVEY.md App. C.
+// Layout NHWC bf16 (pixel stride ld), statistics fp32.  Every pass is either a per-(n,c) plane reduction
+// (128-bit loads, shared-memory + global fp32 atomics) or an elementwise apply (128-bit loads/stores).
+#include "common.cuh"
+
+using namespace b2c;
+
+struct NormArgs {
+  const __nv_bfloat16* z; long long ldz;   // pre-norm conv output
+  const __nv_bfloat16* g; long long ldg;   // grad wrt the activation output
+  const float* gvec;                       // alternative: grad broadcast per (n,c) (pooled head), already / HW
+  const __nv_bfloat16* h; long long ldh;   // cotangent on g_z (double backward)
+  const uint8_t* mask;                     // dense dropout keep-mask [N*HW*C] or null
+  const float* zs;                         // [N][C][2] raw (sum z, sum z^2)
+  float* sums;                             // [N][C][NS] plane sums produced by reduce / consumed by apply
+  __nv_bfloat16* o0; long long ldo0;
+  __nv_bfloat16* o1; long long ldo1;
+  int N, HW, C;
+  float slope;
+};
+
+enum { M_FWD = 0, M_POOL = 1, M_BWD = 2, M_BWD2 = 3 };
+template <int MODE> struct NS { static constexpr int v = MODE == M_FWD ? 2 : MODE == M_POOL ? 1 : MODE == M_BWD ? 2 : 5; };
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
+  const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
+  float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y), c = unpack_bf16(u.z), d = unpack_bf16(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
+  *reinterpret_cast<uint4*>(p) = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+__device__ __forceinline__ void load_mask8(const uint8_t* m, long long idx, float (&k)[8]) {
+  if (!m) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) k[e] = 1.f;
+    return;
+  }
+  const uint2 u = __ldg(reinterpret_cast<const uint2*>(m + idx));
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    k[e] = ((u.x >> (8 * e)) & 0xff) ? 2.f : 0.f;
+    k[4 + e] = ((u.y >> (8 * e)) & 0xff) ? 2.f : 0.f;
+  }
+}
+// mean / rstd of 8 consecutive channels from the raw sums.
+__device__ __forceinline__ void load_stats8(const float* zs, int n, int C, int c0, int HW, float (&mean)[8], float (&rstd)[8]) {
+  const float inv = 1.f / (float)HW;
+  const float4* p = reinterpret_cast<const float4*>(zs + ((long long)n * C + c0) * 2);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float4 v = __ldg(p + j);
+    const float m0 = v.x * inv, m1 = v.z * inv;
+    mean[2 * j] = m0; mean[2 * j + 1] = m1;
+    rstd[2 * j] = rsqrtf(fmaxf(v.y * inv - m0 * m0, 0.f) + 1e-5f);
+    rstd[2 * j + 1] = rsqrtf(fmaxf(v.w * inv - m1 * m1, 0.f) + 1e-5f);
+  }
+}
+
+// Per-element quantities shared by reduce and apply.
+struct Elem { float xh[8], gn[8], hh[8], dact[8]; };
+
+template <int MODE>
+__device__ __forceinline__ void elem_load(const NormArgs& a, int n, long long pix, int c0, const float (&mean)[8],
+                                          const float (&rstd)[8], const float (&gv)[8], Elem& e) {
+  float z[8];
+  load8(a.z + pix * a.ldz + c0, z);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) e.xh[i] = (z[i] - mean[i]) * rstd[i];
+  if (MODE == M_BWD || MODE == M_BWD2) {
+    float k[8], g[8];
+    load_mask8(a.mask, pix * a.C + c0, k);
+    if (a.g) load8(a.g + pix * a.ldg + c0, g);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      e.dact[i] = (e.xh[i] > 0.f ? 1.f : a.slope) * k[i];
+      e.gn[i] = (a.g ? g[i] : gv[i]) * e.dact[i];
+    }
+  }
+  if (MODE == M_BWD2) load8(a.h + pix * a.ldh + c0, e.hh);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) plane_reduce_kernel(NormArgs a) {
+  constexpr int ns = NS<MODE>::v;
+  extern __shared__ float red[];  // [C][ns]
+  const int n = blockIdx.y, cvecs = a.C / 8, rows = 256 / cvecs;
+  const int cv = threadIdx.x % cvecs, prow = threadIdx.x / cvecs, c0 = cv * 8;
+  for (int i = threadIdx.x; i < a.C * ns; i += 256) red[i] = 0.f;
+  __syncthreads();
+  float mean[8], rstd[8], gv[8], acc[ns][8];
+#pragma unroll
+  for (int s = 0; s < ns; ++s)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[s][i] = 0.f;
+  if (MODE != M_FWD) load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
+  if ((MODE == M_BWD || MODE == M_BWD2) && !a.g) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) gv[i] = __ldg(a.gvec + (long long)n * a.C + c0 + i);
+  }
+  const int p_begin = (int)((long long)a.HW * blockIdx.x / gridDim.x), p_end = (int)((long long)a.HW * (blockIdx.x + 1) / gridDim.x);
+  for (int p = p_begin + prow; p < p_end; p += rows) {
+    const long long pix = (long long)n * a.HW + p;
+    if (MODE == M_FWD) {
+      float z[8];
+      load8(a.z + pix * a.ldz + c0, z);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { acc[0][i] += z[i]; acc[1][i] += z[i] * z[i]; }
+    } else {
+      Elem e;
+      elem_load<MODE>(a, n, pix, c0, mean, rstd, gv, e);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (MODE == M_POOL) acc[0][i] += e.xh[i] > 0.f ? e.xh[i] : e.xh[i] * a.slope;
+        if (MODE == M_BWD) { acc[0][i] += e.gn[i]; acc[1][i] += e.gn[i] * e.xh[i]; }
+        if (MODE == M_BWD2) {
+          acc[0][i] += e.hh[i]; acc[1][i] += e.hh[i] * e.xh[i]; acc[2][i] += e.gn[i];
+          acc[3][i] += e.gn[i] * e.xh[i]; acc[4 % ns][i] += e.hh[i] * e.gn[i];
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int s = 0; s < ns; ++s)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) atomicAdd(&red[(c0 + i) * ns + s], acc[s][i]);
+  __syncthreads();
+  for (int i = threadIdx.x; i < a.C * ns; i += 256) atomicAdd(a.sums + (long long)n * a.C * ns + i, red[i]);
+}
+
+// Elementwise applies.  One thread = 8 channels of one pixel.
+template <int MODE>
+__global__ void __launch_bounds__(256) plane_apply_kernel(NormArgs a) {
+  constexpr int ns = NS<MODE>::v;
+  const int cvecs = a.C / 8;
+  const long long total = (long long)a.N * a.HW * cvecs;
+  const float inv = 1.f / (float)a.HW;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int cv = (int)(i % cvecs), c0 = cv * 8;
+    const long long pix = i / cvecs;
+    const int n = (int)(pix / a.HW);
+    float mean[8], rstd[8], gv[8];
+    load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
+    if (MODE == M_FWD) {
+      float z[8], k[8], o[8];
+      load8(a.z + pix * a.ldz + c0, z);
+      load_mask8(a.mask, pix * a.C + c0, k);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float xh = (z[e] - mean[e]) * rstd[e];
+        o[e] = (xh > 0.f ? xh : xh * a.slope) * k[e];
+      }
+      store8(a.o0 + pix * a.ldo0 + c0, o);
+      if (a.o1) store8(a.o1 + pix * a.ldo1 + c0, o);
+    } else {
+      if (!a.g) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) gv[e] = __ldg(a.gvec + (long long)n * a.C + c0 + e);
+      }
+      Elem el;
+      elem_load<MODE>(a, n, pix, c0, mean, rstd, gv, el);
+      const float* s = a.sums + ((long long)n * a.C + c0) * ns;
+      if (MODE == M_BWD) {
+        float o[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = (el.gn[e] - s[e * ns] * inv - el.xh[e] * s[e * ns + 1] * inv) * rstd[e];
+        store8(a.o0 + pix * a.ldo0 + c0, o);
+      } else {  // M_BWD2: o0 = grad wrt g (the first-backward input), o1 = grad wrt z
+        float og[8], oz[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float mh = s[e * ns] * inv, ma = s[e * ns + 1] * inv, mg = s[e * ns + 2] * inv, mc = s[e * ns + 3] * inv,
+                      mhg = s[e * ns + 4 % ns] * inv;
+          const float q = mhg - mh * mg - ma * mc;
+          const float Ph = el.hh[e] - mh - el.xh[e] * ma, Pg = el.gn[e] - mg - el.xh[e] * mc;
+          og[e] = Ph * rstd[e] * el.dact[e];
+          oz[e] = -(q * el.xh[e] + mc * Ph + ma * Pg) * rstd[e] * rstd[e];
+        }
+        store8(a.o0 + pix * a.ldo0 + c0, og);
+        store8(a.o1 + pix * a.ldo1 + c0, oz);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+static int norm_check(const NormArgs& a, const char* who) {
+  B2C_REQUIRE(a.C >= 8 && a.C <= 2048 && (a.C & (a.C - 1)) == 0, "%s: C=%d must be a power of two in [8,2048]", who, a.C);
+  B2C_REQUIRE(a.ldz % 8 == 0, "%s: ldz=%lld must be a multiple of 8", who, a.ldz);
+  return B2C_OK;
+}
+static int reduce_splits(int N, int HW, int C) {
+  const int rows = 256 / (C / 8);
+  int s = 592 / (N > 0 ? N : 1);
+  const int cap = HW / (rows * 2);
+  if (s > cap) s = cap;
+  return s < 1 ? 1 : s;
+}
+template <int MODE>
+static int launch_reduce(const NormArgs& a, cudaStream_t st) {
+  constexpr int ns = NS<MODE>::v;
+  cudaError_t e = cudaMemsetAsync(a.sums, 0, sizeof(float) * (size_t)a.N * a.C * ns, st);
+  if (e != cudaSuccess) { b2c_set_error("norm memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+  dim3 grid(reduce_splits(a.N, a.HW, a.C), a.N);
+  plane_reduce_kernel<MODE><<<grid, 256, sizeof(float) * a.C * ns, st>>>(a);
+  return b2c_check_launch("plane_reduce");
+}
+template <int MODE>
+static int launch_apply(const NormArgs& a, cudaStream_t st) {
+  const long long total = (long long)a.N * a.HW * (a.C / 8);
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  plane_apply_kernel<MODE><<<(unsigned)blocks, 256, 0, st>>>(a);
+  return b2c_check_launch("plane_apply");
+}
+static NormArgs base_args(const void* z, long long ldz, const float* zs, int N, int HW, int C, float slope) {
+  NormArgs a = {};
+  a.z = (const __nv_bfloat16*)z; a.ldz = ldz; a.zs = zs; a.N = N; a.HW = HW; a.C = C; a.slope = slope;
+  return a;
+}
+
+// zs[N][C][2] <- (sum z, sum z^2) per plane.
+extern "C" int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream) {
+  NormArgs a = base_args(z, ldz, nullptr, N, HW, C, 0.f);
+  a.sums = zs;
+  if (int rc = norm_check(a, "in_stats")) return rc;
+  return launch_reduce<M_FWD>(a, (cudaStream_t)stream);
+}
+// o0 (and optionally o1) <- dropout(act(IN(z))).  mask: dense u8 keep-mask or null; kept values are scaled by 2.
+extern "C" int b2c_in_act_fwd(const void* z, long long ldz, const float* zs, const uint8_t* mask, float slope, void* o0,
+                              long long ldo0, void* o1, long long ldo1, int N, int HW, int C, void* stream) {
+  NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
+  a.mask = mask; a.o0 = (__nv_bfloat16*)o0; a.ldo0 = ldo0; a.o1 = (__nv_bfloat16*)o1; a.ldo1 = ldo1;
+  if (int rc = norm_check(a, "in_act_fwd")) return rc;
+  return launch_apply<M_FWD>(a, (cudaStream_t)stream);
+}
+// pooled_sums[N][C] <- sum over the plane of act(IN(z))   (global average pool numerator; models.py:118,139)
+extern "C" int b2c_in_act_pool_fwd(const void* z, long long ldz, const float* zs, float slope, float* pooled_sums, int N,
+                                   int HW, int C, void* stream) {
+  NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
+  a.sums = pooled_sums;
+  if (int rc = norm_check(a, "in_act_pool_fwd")) return rc;
+  return launch_reduce<M_POOL>(a, (cudaStream_t)stream);
+}
+// gz <- d/dz of dropout(act(IN(z))) given g (full tensor) or gvec (per-(n,c) broadcast).  ws: fp32 [N][C][2] scratch.
+extern "C" int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const void* z, long long ldz,
+                              const float* zs, const uint8_t* mask, float slope, float* ws, void* gz, long long ldgz,
+                              int N, int HW, int C, void* stream) {
+  NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
+  a.g = (const __nv_bfloat16*)g; a.ldg = ldg; a.gvec = gvec; a.mask = mask; a.sums = ws;
+  a.o0 = (__nv_bfloat16*)gz; a.ldo0 = ldgz;
+  if (int rc = norm_check(a, "in_act_bwd")) return rc;
+  B2C_REQUIRE((g != nullptr) != (gvec != nullptr), "in_act_bwd: exactly one of g / gvec");
+  if (int rc = launch_reduce<M_BWD>(a, (cudaStream_t)stream)) return rc;
+  return launch_apply<M_BWD>(a, (cudaStream_t)stream);
+}
+// Double backward of b2c_in_act_bwd: cotangent h on gz -> gg (wrt g) and gx (wrt z).  ws: fp32 [N][C][5] scratch.
+extern "C" int b2c_in_act_bwd2(const void* h, long long ldh, const void* g, long long ldg, const void* z, long long ldz,
+                               const float* zs, const uint8_t* mask, float slope, float* ws, void* gg, long long ldgg,
+                               void* gx, long long ldgx, int N, int HW, int C, void* stream) {
+  NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
+  a.g = (const __nv_bfloat16*)g; a.ldg = ldg; a.h = (const __nv_bfloat16*)h; a.ldh = ldh; a.mask = mask; a.sums = ws;
+  a.o0 = (__nv_bfloat16*)gg; a.ldo0 = ldgg; a.o1 = (__nv_bfloat16*)gx; a.ldo1 = ldgx;
+  if (int rc = norm_check(a, "in_act_bwd2")) return rc;
+  if (int rc = launch_reduce<M_BWD2>(a, (cudaStream_t)stream)) return rc;
+  return launch_apply<M_BWD2>(a, (cudaStream_t)stream);
+}
+
+// out = g * (a > 0 ? 1 : slope): backward of the LeakyReLU fused into the first-layer conv (sign(a) == sign(z)).
+__global__ void lrelu_bwd_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ a,
+                                 __nv_bfloat16* __restrict__ out, long long nvec, float slope) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+    float gv[8], av[8];
+    load8(g + i * 8, gv);
+    load8(a + i * 8, av);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) gv[e] *= av[e] > 0.f ? 1.f : slope;
+    store8(out + i * 8, gv);
+  }
+}
+extern "C" int b2c_lrelu_bwd(const void* g, const void* a, void* out, long long n, float slope, void* stream) {
+  B2C_REQUIRE(n % 8 == 0, "lrelu_bwd: n=%lld must be a multiple of 8", n);
+  long long blocks = (n / 8 + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  lrelu_bwd_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)a,
+                                                                       (__nv_bfloat16*)out, n / 8, slope);
+  return b2c_check_launch("lrelu_bwd");
+}
+
+// Strided NHWC channel-slice copy (skip-concat, models.py:82): dst[pix*ldd + c] = src[pix*lds + c], c < C.
+__global__ void copy_strided_kernel(const __nv_bfloat16* __restrict__ src, long long lds, __nv_bfloat16* __restrict__ dst,
+                                    long long ldd, long long npix, int cvecs) {
+  const long long total = npix * cvecs;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i / cvecs;
+    const int c0 = (int)(i % cvecs) * 8;
+    *reinterpret_cast<uint4*>(dst + pix * ldd + c0) = __ldg(reinterpret_cast<const uint4*>(src + pix * lds + c0));
+  }
+}
+extern "C" int b2c_copy_strided(const void* src, long long lds, void* dst, long long ldd, long long npix, int C, void* stream) {
+  B2C_REQUIRE(C % 8 == 0 && lds % 8 == 0 && ldd % 8 == 0, "copy_strided: C/lds/ldd must be multiples of 8");
+  long long blocks = (npix * (C / 8) + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  copy_strided_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)src, lds, (__nv_bfloat16*)dst, ldd, npix, C / 8);
+  return b2c_check_launch("copy_strided");
+}
+
+// Counter-based dropout keep-mask (p = 0.5): one hash per element index, keyed by (seed, offset).  u8 out.
+__device__ __forceinline__ uint32_t mix32(uint64_t x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+  return (uint32_t)x;
+}
+__global__ void dropout_mask_kernel(uint8_t* __restrict__ m, long long nvec, uint64_t seed, uint64_t offset) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+    const uint32_t r = mix32((seed * 0x9E3779B97F4A7C15ULL) ^ (offset + (uint64_t)i));
+    uint2 o;
+    o.x = (r & 1) | ((r >> 1 & 1) << 8) | ((r >> 2 & 1) << 16) | ((r >> 3 & 1) << 24);
+    o.y = (r >> 4 & 1) | ((r >> 5 & 1) << 8) | ((r >> 6 & 1) << 16) | ((r >> 7 & 1) << 24);
+    *reinterpret_cast<uint2*>(m + i * 8) = o;
+  }
+}
+extern "C" int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsigned long long offset, void* stream) {
+  B2C_REQUIRE(n % 8 == 0, "dropout_mask: n=%lld must be a multiple of 8", n);
+  long long blocks = (n / 8 + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  dropout_mask_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(mask, n / 8, seed, offset);
+  return b2c_check_launch("dropout_mask");
+}
