@@ -1,0 +1,113 @@
+"""ctypes binding of libb2c.so (C-ABI declared in include/b2c.h).
+
+There is NO fallback: if the library is missing or a call fails, an exception is raised.  Signatures are read
+from the header so the binding cannot drift from the ABI.  A test-only emulation backend can be installed with
+``set_backend`` (tests/emu_backend.py); the package itself never does that.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import re
+from pathlib import Path
+
+import torch
+
+_PKG = Path(__file__).resolve().parent
+_ROOT = _PKG.parent.parent
+HEADER = _ROOT / "include" / "b2c.h"
+LIBPATH = _PKG / "libb2c.so"
+
+_CTYPES = {"int": ctypes.c_int, "long long": ctypes.c_longlong, "float": ctypes.c_float,
+           "unsigned long long": ctypes.c_ulonglong}
+
+
+def parse_header(path: Path = HEADER):
+    """-> {name: (restype, [(ctype, is_pointer)])} for every b2c_* prototype."""
+    text = re.sub(r"/\*.*?\*/", "", path.read_text(), flags=re.S)
+    protos = {}
+    for m in re.finditer(r"(const char\*|int)\s+(b2c_\w+)\s*\(([^)]*)\)\s*;", text):
+        ret, name, args = m.group(1), m.group(2), m.group(3).strip()
+        sig = []
+        if args and args != "void":
+            for a in args.split(","):
+                a = a.strip()
+                if "*" in a:
+                    sig.append((ctypes.c_void_p, True))
+                else:
+                    ty = re.sub(r"\s+\w+$", "", a).replace("const ", "").strip()
+                    sig.append((_CTYPES[ty], False))
+        protos[name] = (ctypes.c_char_p if ret.startswith("const char") else ctypes.c_int, sig)
+    return protos
+
+
+class B2CError(RuntimeError):
+    pass
+
+
+class _Native:
+    def __init__(self):
+        if not LIBPATH.exists():
+            raise B2CError(f"{LIBPATH} not found: build it with __graft_entry__.build() "
+                           f"(csrc/build.sh); there is no CPU or library fallback")
+        self.lib = ctypes.CDLL(str(LIBPATH))
+        self.protos = parse_header()
+        self.fns = {}
+        for name, (ret, sig) in self.protos.items():
+            fn = getattr(self.lib, name)
+            fn.restype = ret
+            fn.argtypes = [t for t, _ in sig]
+            self.fns[name] = fn
+        self.launches = 0
+
+    def call(self, name, *args):
+        fn = self.fns[name]
+        conv = []
+        for a in args:
+            if isinstance(a, torch.Tensor):
+                if not a.is_cuda:
+                    raise B2CError(f"{name}: tensor argument is not on a CUDA device")
+                conv.append(a.data_ptr())
+            elif a is None:
+                conv.append(None)
+            else:
+                conv.append(a)
+        rc = fn(*conv, torch.cuda.current_stream().cuda_stream)
+        self.launches += 1
+        if rc != 0:
+            raise B2CError(f"{name} failed ({rc}): {self.lib.b2c_last_error().decode()}")
+
+
+_backend = None
+
+
+def backend():
+    global _backend
+    if _backend is None:
+        _backend = _Native()
+    return _backend
+
+
+def set_backend(b):
+    """TEST HOOK ONLY (tests/emu_backend.py installs a torch-CPU emulation to check host logic without a GPU)."""
+    global _backend
+    _backend = b
+
+
+def call(name, *args):
+    backend().call(name, *args)
+
+
+def launch_count() -> int:
+    return backend().launches
+
+
+_sm_count = None
+
+
+def sm_count() -> int:
+    global _sm_count
+    if _sm_count is None:
+        _sm_count = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count \
+            if torch.cuda.is_available() else 148
+    return _sm_count

@@ -78,7 +78,7 @@ extern "C" int b2c_multi_adam(float* const* p, float* const* g, float* const* m,
                               float eps, int step_index, void* stream) {
   TensorTable t;
   if (int rc = fill_table(t, p, g, m, v, n, count)) return rc;
-  const float bc1 = 1.f - powf(beta1, (float)step_index), bc2 = 1.f - powf(beta2, (float)step_index);
+  const float bc1 = (float)(1.0 - pow((double)beta1, (double)step_index)), bc2 = (float)(1.0 - pow((double)beta2, (double)step_index));
   multi_adam_kernel<<<dim3(128, count), 256, 0, (cudaStream_t)stream>>>(t, gnorm_sq, max_norm, lr, beta1, beta2, eps, bc1, bc2);
   return b2c_check_launch("multi_adam");
 }

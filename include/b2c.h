@@ -1,0 +1,94 @@
+/* b2c.h - C-ABI of libb2c.so: hand-written sm_100a kernels for the cGAN patch-calibrator train step.
+ *
+ * The reference (1213ray/GAN-Calibrated-Semi-Supervised-Learning) has no FFI of its own: its hot path is Python calling
+ * PyTorch ATen.  Each entry point below names the reference call site whose device work it replaces (paths relative
+ * to the reference root).  Conventions: plain device pointers and sizes, no ownership transfer, no allocation, every
+ * call enqueues on `stream` (a cudaStream_t) and returns 0 on success, else non-zero with b2c_last_error() set.
+ * Activations: NHWC bf16 with an explicit pixel stride `ld*` in elements; parameters, statistics, losses: fp32.
+ */
+#ifndef B2C_H
+#define B2C_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* b2c_last_error(void);
+int b2c_abi_version(void);
+
+/* ---- weight packing (+ spectral-norm 1/sigma; torch spectral_norm.py:111-112 via cgan/models.py:238) ---- */
+int b2c_pack_w_c(const float* w, const float* inv_sigma, void* out_bf16, int D0, int D1, void* stream);
+int b2c_pack_w_t(const float* w, const float* inv_sigma, void* out_bf16, int D0, int D1, void* stream);
+
+/* ---- tcgen05 implicit-GEMM convolutions ----
+ * conv4s2 : nn.Conv2d(k4,s2,p1) fprop (cgan/models.py:57,236) and ConvTranspose2d dgrad.   x dense (N,H,W,Cin).
+ * convt4s2: nn.ConvTranspose2d(k4,s2,p1) fprop (cgan/models.py:72,113) and Conv2d dgrad.   y is (N,2H,2W,Cout).
+ * wgrad4s2: weight gradient of both (autograd of the above; cgan/cgan_train_enhanced.py:330,366). */
+int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* bias, void* y, long long ldy,
+                     int N, int H, int W, int Cin, int Cout, void* stream);
+int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y, long long ldy,
+                      int N, int H, int W, int Cin, int Cout, void* stream);
+int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* large, long long ldl, float* ws, float* dw,
+                      int accumulate, int N, int Hs, int Ws, int Cs, int Cl, int sm_count, void* stream);
+
+/* ---- first layers, Cin = 3 / 6, NCHW fp32 in (cgan/models.py:103,245,257; interpolation cgan/losses.py:203-204) ---- */
+int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
+                    const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
+                    float slope, void* stream);
+int b2c_first_dgrad(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1, int N, int H, int W,
+                    void* stream);
+int b2c_first_wgrad(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
+                    const void* gz, float* dw, float* db, int N, int H, int W, void* stream);
+
+/* ---- PatchGAN head Conv2d(512,1,k4,s1,p1) (cgan/models.py:252) ---- */
+int b2c_head_fprop(const void* a, const float* w, float* out, int N, int h, int C, void* stream);
+int b2c_head_dgrad(const float* gy, const float* w, void* ga, int N, int h, int C, void* stream);
+int b2c_head_wgrad(const void* a, const float* gy, float* dw, int N, int h, int C, void* stream);
+
+/* ---- InstanceNorm2d + LeakyReLU/ReLU + Dropout(0.5) (cgan/models.py:59-62,73-77,114,241-242) ---- */
+int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream);
+int b2c_in_act_fwd(const void* z, long long ldz, const float* zs, const uint8_t* mask, float slope, void* o0,
+                   long long ldo0, void* o1, long long ldo1, int N, int HW, int C, void* stream);
+int b2c_in_act_pool_fwd(const void* z, long long ldz, const float* zs, float slope, float* pooled_sums, int N, int HW,
+                        int C, void* stream);
+int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const void* z, long long ldz, const float* zs,
+                   const uint8_t* mask, float slope, float* ws, void* gz, long long ldgz, int N, int HW, int C,
+                   void* stream);
+int b2c_in_act_bwd2(const void* h, long long ldh, const void* g, long long ldg, const void* z, long long ldz,
+                    const float* zs, const uint8_t* mask, float slope, float* ws, void* gg, long long ldgg, void* gx,
+                    long long ldgx, int N, int HW, int C, void* stream);
+int b2c_lrelu_bwd(const void* g, const void* a, void* out, long long n, float slope, void* stream);
+int b2c_copy_strided(const void* src, long long lds, void* dst, long long ldd, long long npix, int C, void* stream);
+int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsigned long long offset, void* stream);
+
+/* ---- spectral norm (torch spectral_norm.py:92-114) ---- */
+int b2c_sn_power_iter(const float* W, float* u, float* v, float* sig, float* ws, int R, int K, int train, void* stream);
+int b2c_sn_bwd(const float* dWe, const float* W, const float* u, const float* v, const float* sig, float* ws, float* dW,
+               int R, int K, int accumulate, void* stream);
+
+/* ---- losses (cgan/losses.py:19-73,99-183,223-231; cgan/cgan_train_enhanced.py:327-328,362) ---- */
+int b2c_apply_delta(const float* bbox, const float* delta, int training, float* out, const float* gout, float* gdelta,
+                    int B, void* stream);
+int b2c_eiou(const float* pred, const float* tgt, float eps, float* loss, const float* gscale, float* gpred,
+             float* iou_out, int B, void* stream);
+int b2c_rowsum(const float* x, long long n, int B, int square, float scale, float* out, void* stream);
+int b2c_gp_tail(const float* ss, float* gp, float* coef, int B, void* stream);
+int b2c_scale_rows(const float* x, const float* coef, const float* gscale, float* out, long long n, int B, void* stream);
+int b2c_fill_scaled(float* out, long long n, const float* gscale, float value, void* stream);
+
+/* ---- G head AvgPool -> Linear(64,4) -> Tanh -> *delta_scale (cgan/models.py:118-123,139-141) ---- */
+int b2c_pool_fc_fwd(const float* pooled_sums, const float* W, const float* bias, float scale, int HW, float* delta,
+                    float* tanh_out, int N, int C, void* stream);
+int b2c_pool_fc_bwd(const float* gdelta, const float* tanh_v, const float* pooled_sums, const float* W, float scale,
+                    int HW, float* dW, float* db, float* gvec, int N, int C, void* stream);
+
+/* ---- clip_grad_norm_(1.0) + Adam (cgan/cgan_train_enhanced.py:256-257,331-332,368-369) ---- */
+int b2c_multi_sumsq(float* const* g, const long long* n, int count, float* out, void* stream);
+int b2c_multi_adam(float* const* p, float* const* g, float* const* m, float* const* v, const long long* n, int count,
+                   const float* gnorm_sq, float max_norm, float lr, float beta1, float beta2, float eps, int step_index,
+                   void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,149 @@
+"""Per-kernel parity of libb2c.so (through the C-ABI) against torch CPU fp32 on the same bf16-rounded inputs.
+Tolerance: relative L2 <= 2e-2 for bf16 outputs (BASELINE.json north_star), <= 1e-4 for fp32-only kernels."""
+import ctypes
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def nhwc(x):  # NCHW fp32 cpu -> NHWC bf16 cuda
+    return x.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
+
+
+def nchw(y):  # NHWC cuda -> NCHW fp32 cpu
+    return y.float().cpu().permute(0, 3, 1, 2).contiguous()
+
+
+def q(x):  # bf16 rounding on cpu
+    return x.to(torch.bfloat16).float()
+
+
+@pytest.fixture(scope="module")
+def L():
+    from b200cgan import _lib
+    return _lib
+
+
+CONV_CASES = [(2, 16, 16, 64, 128), (3, 32, 32, 64, 64), (2, 8, 8, 256, 512), (1, 128, 128, 64, 128), (5, 4, 4, 128, 256),
+              (2, 256, 256, 64, 64)]
+
+
+@pytest.mark.parametrize("N,H,W,Cin,Cout", CONV_CASES)
+def test_conv4s2(L, N, H, W, Cin, Cout):
+    g = torch.Generator().manual_seed(1)
+    x = q(torch.randn(N, Cin, H, W, generator=g))
+    w = torch.randn(Cout, Cin, 4, 4, generator=g) * 0.05
+    b = torch.randn(Cout, generator=g)
+    wp = torch.empty(Cout, 16 * Cin, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_pack_w_c", w.cuda(), None, wp, Cout, Cin)
+    y = torch.empty(N, H // 2, W // 2, Cout, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, b.cuda(), y, Cout, N, H, W, Cin, Cout)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x, q(w), b, 2, 1)
+    assert rel(nchw(y), ref) < 1e-2
+
+
+@pytest.mark.parametrize("N,H,W,Cin,Cout", [(2, 8, 8, 128, 64), (3, 16, 16, 64, 128), (2, 4, 4, 512, 256),
+                                            (1, 64, 64, 128, 64), (2, 128, 128, 128, 64), (5, 2, 2, 64, 64)])
+def test_convt4s2(L, N, H, W, Cin, Cout):
+    g = torch.Generator().manual_seed(2)
+    x = q(torch.randn(N, Cin, H, W, generator=g))
+    w = torch.randn(Cin, Cout, 4, 4, generator=g) * 0.05
+    wp = torch.empty(4, Cout, 4 * Cin, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
+    y = torch.empty(N, 2 * H, 2 * W, Cout, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, N, H, W, Cin, Cout)
+    torch.cuda.synchronize()
+    ref = F.conv_transpose2d(x, q(w), None, 2, 1)
+    assert rel(nchw(y), ref) < 1e-2
+
+
+def test_conv_dgrad_is_convt(L):
+    """dgrad of Conv2d(k4,s2,p1) == convt4s2 with the conv weight packed in T-form."""
+    g = torch.Generator().manual_seed(3)
+    N, H, W, Cin, Cout = 2, 16, 16, 64, 128
+    gy = q(torch.randn(N, Cout, H // 2, W // 2, generator=g))
+    w = torch.randn(Cout, Cin, 4, 4, generator=g) * 0.05
+    wp = torch.empty(4, Cin, 4 * Cout, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_pack_w_t", w.cuda(), None, wp, Cout, Cin)
+    dx = torch.empty(N, H, W, Cin, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_convt4s2_bf16", nhwc(gy), Cout, wp, None, dx, Cin, N, H // 2, W // 2, Cout, Cin)
+    torch.cuda.synchronize()
+    ref = torch.nn.grad.conv2d_input((N, Cin, H, W), q(w), gy, 2, 1)
+    assert rel(nchw(dx), ref) < 1e-2
+
+
+@pytest.mark.parametrize("N,Hs,Ws,Cs,Cl", [(2, 8, 8, 128, 64), (3, 16, 16, 128, 128), (2, 4, 4, 512, 256),
+                                           (1, 64, 64, 128, 64), (5, 2, 2, 256, 128), (4, 32, 32, 256, 128)])
+def test_wgrad4s2(L, N, Hs, Ws, Cs, Cl):
+    g = torch.Generator().manual_seed(4)
+    small = q(torch.randn(N, Cs, Hs, Ws, generator=g))
+    large = q(torch.randn(N, Cl, 2 * Hs, 2 * Ws, generator=g))
+    ws = torch.empty(16, Cs, Cl, dtype=torch.float32, device="cuda")
+    dw = torch.empty(Cs, Cl, 4, 4, dtype=torch.float32, device="cuda")
+    L.call("b2c_wgrad4s2_bf16", nhwc(small), Cs, nhwc(large), Cl, ws, dw, 0, N, Hs, Ws, Cs, Cl, 148)
+    torch.cuda.synchronize()
+    ref = torch.nn.grad.conv2d_weight(large, (Cs, Cl, 4, 4), small, 2, 1)
+    assert rel(dw, ref) < 2e-3
+    L.call("b2c_wgrad4s2_bf16", nhwc(small), Cs, nhwc(large), Cl, ws, dw, 1, N, Hs, Ws, Cs, Cl, 148)
+    torch.cuda.synchronize()
+    assert rel(dw, 2 * ref) < 2e-3
+
+
+@pytest.mark.parametrize("cin", [3, 6])
+def test_first_layer(L, cin):
+    g = torch.Generator().manual_seed(5)
+    N, S = 3, 32
+    x = torch.randn(N, cin, S, S, generator=g)
+    xb = torch.randn(N, cin, S, S, generator=g)
+    alpha = torch.rand(N, generator=g)
+    w = torch.randn(64, cin, 4, 4, generator=g) * 0.1
+    b = torch.randn(64, generator=g) * 0.1
+    sig = torch.tensor([2.0, 0.5])
+    parts = lambda t: [t[:, :3].contiguous().cuda(), t[:, 3:].contiguous().cuda() if cin == 6 else None]
+    a0, a1 = parts(x)
+    b0, b1 = parts(xb)
+    y = torch.empty(N, S // 2, S // 2, 64, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_first_fprop", a0, a1, b0, b1 if cin == 6 else b0, alpha.cuda(), w.cuda(), sig.cuda()[1:], b.cuda(), y, N, S, S, 0.2)
+    al = alpha.view(N, 1, 1, 1)
+    xi = al * x + (1 - al) * xb
+    ref = F.leaky_relu(F.conv2d(xi, w * 0.5, b, 2, 1), 0.2)
+    assert rel(nchw(y), ref) < 5e-3
+    gz = q(torch.randn(N, 64, S // 2, S // 2, generator=g))
+    gx0 = torch.empty(N, 3, S, S, device="cuda")
+    gx1 = torch.empty(N, 3, S, S, device="cuda") if cin == 6 else None
+    L.call("b2c_first_dgrad", nhwc(gz), w.cuda(), sig.cuda()[1:], gx0, gx1, N, S, S)
+    refdx = torch.nn.grad.conv2d_input((N, cin, S, S), w * 0.5, gz, 2, 1)
+    got = torch.cat([gx0.cpu()] + ([gx1.cpu()] if cin == 6 else []), 1)
+    assert rel(got, refdx) < 1e-4
+    dw = torch.zeros(64, cin, 4, 4, device="cuda")
+    db = torch.zeros(64, device="cuda")
+    L.call("b2c_first_wgrad", a0, a1, b0, b1 if cin == 6 else b0, alpha.cuda(), nhwc(gz), dw, db, N, S, S)
+    refdw = torch.nn.grad.conv2d_weight(xi, (64, cin, 4, 4), gz, 2, 1)
+    assert rel(dw, refdw) < 1e-4
+    assert rel(db, gz.sum((0, 2, 3))) < 1e-4
+
+
+def test_head(L):
+    g = torch.Generator().manual_seed(6)
+    N, h, C = 3, 8, 512
+    a = q(torch.randn(N, C, h, h, generator=g))
+    w = torch.randn(1, C, 4, 4, generator=g) * 0.05
+    out = torch.empty(N, 1, h - 1, h - 1, device="cuda")
+    L.call("b2c_head_fprop", nhwc(a), w.cuda(), out, N, h, C)
+    assert rel(out, F.conv2d(a, w, None, 1, 1)) < 1e-4
+    gy = torch.randn(N, 1, h - 1, h - 1, generator=g)
+    ga = torch.empty(N, h, h, C, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_head_dgrad", gy.cuda(), w.cuda(), ga, N, h, C)
+    assert rel(nchw(ga), torch.nn.grad.conv2d_input((N, C, h, h), w, gy, 1, 1)) < 5e-3
+    dw = torch.zeros(1, C, 4, 4, device="cuda")
+    L.call("b2c_head_wgrad", nhwc(a), gy.cuda(), dw, N, h, C)
+    assert rel(dw, torch.nn.grad.conv2d_weight(a, (1, C, 4, 4), gy, 1, 1)) < 1e-4
