@@ -1,0 +1,130 @@
+"""Model-level parity on the GPU: the drop-in modules / train step (b200cgan, through libb2c.so) against the CPU oracle
+(oracle/cgan_oracle.py, pinned to the reference by tests/golden) on identical weights, inputs, dropout masks and GP
+alpha.  Tolerance (BASELINE.json north_star): relative L2 <= 2e-2 per output / gradient tensor in bf16."""
+import json
+from pathlib import Path
+
+import pytest
+import torch
+
+import cgan_oracle as O
+
+pytestmark = pytest.mark.gpu
+GOLD = Path(__file__).parent / "golden"
+TOL = 2e-2
+
+
+def rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def build(state):
+    from b200cgan.models import GeneratorUNet, Discriminator
+    G, D = GeneratorUNet(0.3), Discriminator(True)
+    G.load_state_dict(state["G"]); D.load_state_dict(state["D"])
+    return G.cuda(), D.cuda()
+
+
+def inject_masks(G, masks):
+    for site, m in zip(G.dropout_sites(), masks):
+        site.injected = None if m is None else m.permute(0, 2, 3, 1).contiguous().to(torch.uint8).cuda().reshape(-1)
+
+
+def cuda_batch(b):
+    return {k: v.cuda() for k, v in b.items()}
+
+
+@pytest.mark.parametrize("B,S", [(2, 64), (3, 128), (4, 32)])
+def test_generator_forward_backward(B, S):
+    st = O.init_state(42)
+    G, _ = build(st)
+    batch, masks, _ = O.make_batch(B, S, 0)
+    cb = cuda_batch(batch)
+    G.eval()
+    with torch.no_grad():
+        d_eval = G(cb["pred"])
+    ref_eval = O.g_forward(st["G"], batch["pred"], 0.3, train=False)
+    assert rel(d_eval, ref_eval) < TOL
+    G.train()
+    inject_masks(G, masks[0])
+    delta = G(cb["pred"])
+    leaves = {k: v.clone().requires_grad_(True) for k, v in st["G"].items()}
+    ref = O.g_forward(leaves, batch["pred"], 0.3, True, masks[0])
+    assert rel(delta, ref) < TOL
+    gd = torch.randn(B, 4, generator=torch.Generator().manual_seed(3))
+    delta.backward(gd.cuda())
+    ref.backward(gd)
+    for k, p in G.named_parameters():
+        assert rel(p.grad, leaves[k].grad) < 3e-2, k
+
+
+@pytest.mark.parametrize("B,S", [(2, 64), (3, 128), (4, 32)])
+def test_discriminator_forward_and_critic_grads(B, S):
+    st = O.init_state(42)
+    _, D = build(st)
+    batch, _, alphas = O.make_batch(B, S, 0)
+    cb = cuda_batch(batch)
+    D.train()
+    d_ref = {k: v.clone() for k, v in st["D"].items()}
+    with torch.no_grad():
+        out = D(cb["pred"], cb["gt"])
+        ref = O.d_forward(d_ref, batch["pred"], batch["gt"], True)
+    assert tuple(out.shape) == (B, 1, S // 16 - 1, S // 16 - 1)
+    assert rel(out, ref) < TOL
+    for idx in (0, 2, 5, 8):  # power iteration advanced identically
+        assert rel(D.model[idx].weight_u, d_ref[f"model.{idx}.weight_u"]) < 1e-4
+        assert rel(D.model[idx].weight_v, d_ref[f"model.{idx}.weight_v"]) < 1e-4
+    # one critic loss + grads with the same alpha
+    from b200cgan import losses, ops
+    real, fake = D(cb["pred"], cb["gt"]), D(cb["pred"], cb["refined"])
+    orig = torch.rand
+    torch.rand = lambda *a, **k: alphas[0].cuda()
+    try:
+        gp = losses.compute_gradient_penalty(D, (cb["pred"], cb["gt"]), (cb["pred"], cb["refined"]), "cuda")
+    finally:
+        torch.rand = orig
+    wd = ops.MapMean.apply(real) - ops.MapMean.apply(fake)
+    (-wd + gp).backward()
+    sc, grads = O.critic_grads(d_ref, batch["pred"], batch["gt"], batch["refined"], alphas[0], 1.0)
+    assert abs(float(gp) - sc["gp"]) <= TOL * abs(sc["gp"]) + 1e-4
+    assert abs(float(wd) - sc["wd"]) <= TOL * abs(sc["wd"]) + 2e-3
+    for k, p in D.named_parameters():
+        if k in O.D_BIAS_UNOBSERVABLE:
+            assert float(p.grad.abs().max()) == 0.0
+            continue
+        assert rel(p.grad, grads[k]) < 3e-2, k
+
+
+@pytest.mark.parametrize("name", ["step_B2_S64", "step_B4_S32"])
+def test_train_steps_vs_oracle_and_reference_golden(name):
+    from b200cgan.train_step import CGANTrainer
+    gold = json.loads((GOLD / f"{name}.json").read_text())
+    B, S = gold["B"], gold["S"]
+    st = O.init_state(42)
+    G, D = build(st)
+    tr = CGANTrainer(G, D, n_critic=gold["n_critic"], lambda_gp=gold["lambda_gp"])
+    for step, ref in enumerate(gold["steps"]):
+        batch, masks, alphas = O.make_batch(B, S, step)
+        cb = cuda_batch(batch)
+        calls = {"n": 0}
+        sites = G.dropout_sites()
+
+        def pre_hook(mod, inp):
+            inject_masks(G, masks[calls["n"]]); calls["n"] += 1
+        h = G.register_forward_pre_hook(pre_hook)
+        tr.alpha_source = lambda c: alphas[c].cuda()
+        out = tr.step(cb["pred"], cb["gt"], cb["refined"], cb["pred_box"], cb["delta_true"])
+        h.remove()
+        got = out.to_host()
+        oref = O.train_step(st, batch, masks, alphas, n_critic=gold["n_critic"], lambda_gp=gold["lambda_gp"])
+        for k in ("d_loss", "gp", "wd", "loss_G", "loss_iou", "loss_wgan", "g_gradnorm", "d_gradnorm_0", "d_gradnorm_1"):
+            tol = 3e-2 * abs(ref[k]) + 5e-3
+            assert abs(got[k] - ref[k]) <= tol, (step, k, got[k], ref[k])          # vs the reference's own numbers
+            assert abs(got[k] - oref[k]) <= tol, (step, k, got[k], oref[k])        # vs the oracle
+        assert rel(out.delta, torch.tensor(ref["delta"])) < 5e-2
+    for k, p in list(G.state_dict().items()) + list(D.state_dict().items()):
+        if k in O.D_BIAS_UNOBSERVABLE:
+            continue
+        r = st["G"][k] if k in st["G"] else st["D"][k]
+        assert rel(p, r) < 2e-2, k
