@@ -97,6 +97,30 @@ def new_adam_state(names, params):
             "v": {k: torch.zeros_like(params[k]) for k in names}}
 
 
+# ----------------------------------------------------------------------------- bf16 storage emulation
+# The B200 path stores tensor-core weights, conv outputs and activations in bf16 (fp32 accumulate).  Rounding a
+# pre-activation moves a few elements across the ReLU / LeakyReLU kink, and because the reference's losses see the
+# trunk only through InstanceNorm -> ReLU -> mean (a nearly scale/shift-invariant statistic), those few flips are a
+# 10-20 % relative-L2 change of G's weight gradients at random init - for ANY bf16 implementation.
+# `emulate_bf16()` applies the same forward roundings (straight-through in backward) so that gradient parity can be
+# checked against "the reference's arithmetic on bf16 storage"; the default (off) is the reference's fp32 arithmetic.
+_EMULATE = {"on": False}
+
+
+class emulate_bf16:
+    def __enter__(self):
+        self.prev = _EMULATE["on"]; _EMULATE["on"] = True
+
+    def __exit__(self, *a):
+        _EMULATE["on"] = self.prev
+
+
+def _r(t):
+    if not _EMULATE["on"]:
+        return t
+    return t + (t.to(torch.bfloat16).to(t.dtype) - t).detach()
+
+
 # ----------------------------------------------------------------------------- generator
 def _inorm(x):
     return F.instance_norm(x, eps=1e-5)
@@ -109,26 +133,28 @@ def g_forward(g, x, delta_scale: float = 0.3, train: bool = True,
     h = x
     mi = 0
     for name, _, _, norm, drop in G_DOWN:
-        h = F.conv2d(h, g[name + ".model.0.weight"], None, 2, 1)
+        w = g[name + ".model.0.weight"]
+        h = F.conv2d(h, _r(w) if norm else w, None, 2, 1)
         if norm:
-            h = _inorm(h)
+            h = _inorm(_r(h))
         h = F.leaky_relu(h, 0.2)
         if drop and train:
             h = h * masks[mi] * 2.0; mi += 1
+        h = _r(h)
         if taps is not None:
             taps[name] = h
         skips.append(h)
     d1, d2, d3, d4 = skips
     h = d4
     for (name, _, _, drop), skip in zip(G_UP, (d3, d2, d1)):
-        h = F.conv_transpose2d(h, g[name + ".model.0.weight"], None, 2, 1)
+        h = _r(F.conv_transpose2d(h, _r(g[name + ".model.0.weight"]), None, 2, 1))
         h = F.relu(_inorm(h))
         if drop and train:
             h = h * masks[mi] * 2.0; mi += 1
-        h = torch.cat((h, skip), 1)
+        h = torch.cat((_r(h), skip), 1)
         if taps is not None:
             taps[name] = h
-    h = F.relu(_inorm(F.conv_transpose2d(h, g["up4.0.weight"], None, 2, 1)))
+    h = F.relu(_inorm(_r(F.conv_transpose2d(h, _r(g["up4.0.weight"]), None, 2, 1))))
     if taps is not None:
         taps["up4"] = h
     pooled = h.mean(dim=(2, 3))
@@ -159,10 +185,10 @@ def d_forward(d, pred, other, train: bool = True, taps: Optional[dict] = None):
     h = torch.cat([pred, other], 1)
     for idx, _, _, norm in D_BLOCKS:
         w = sn_weight(d, idx, train) if sn else d[f"model.{idx}.weight"]
-        h = F.conv2d(h, w, d[f"model.{idx}.bias"], 2, 1)
+        h = F.conv2d(h, _r(w) if norm else w, d[f"model.{idx}.bias"], 2, 1)
         if norm:
-            h = _inorm(h)
-        h = F.leaky_relu(h, 0.2)
+            h = _inorm(_r(h))
+        h = _r(F.leaky_relu(h, 0.2))
         if taps is not None:
             taps[f"model.{idx}"] = h
     return F.conv2d(h, d["model.11.weight"], None, 1, 1)

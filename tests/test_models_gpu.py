@@ -49,14 +49,24 @@ def test_generator_forward_backward(B, S):
     G.train()
     inject_masks(G, masks[0])
     delta = G(cb["pred"])
-    leaves = {k: v.clone().requires_grad_(True) for k, v in st["G"].items()}
-    ref = O.g_forward(leaves, batch["pred"], 0.3, True, masks[0])
-    assert rel(delta, ref) < TOL
     gd = torch.randn(B, 4, generator=torch.Generator().manual_seed(3))
     delta.backward(gd.cuda())
+    # (1) the reference's fp32 arithmetic: outputs within 2e-2; weight gradients only loosely (bf16 storage flips
+    #     ReLU decisions next to a scale-invariant statistic: 10-20 % at random init for any bf16 implementation)
+    leaves = {k: v.clone().requires_grad_(True) for k, v in st["G"].items()}
+    ref = O.g_forward(leaves, batch["pred"], 0.3, True, masks[0])
     ref.backward(gd)
+    assert rel(delta, ref) < TOL
     for k, p in G.named_parameters():
-        assert rel(p.grad, leaves[k].grad) < 3e-2, k
+        assert rel(p.grad, leaves[k].grad) < (TOL if k.startswith("fc_delta") else 0.35), k
+    # (2) the reference's arithmetic on bf16 storage (same rounding points): every gradient within 2e-2
+    leaves = {k: v.clone().requires_grad_(True) for k, v in st["G"].items()}
+    with O.emulate_bf16():
+        ref = O.g_forward(leaves, batch["pred"], 0.3, True, masks[0])
+    ref.backward(gd)
+    assert rel(delta, ref) < TOL
+    for k, p in G.named_parameters():
+        assert rel(p.grad, leaves[k].grad) < TOL, (k, rel(p.grad, leaves[k].grad))
 
 
 @pytest.mark.parametrize("B,S", [(2, 64), (3, 128), (4, 32)])
@@ -86,14 +96,22 @@ def test_discriminator_forward_and_critic_grads(B, S):
         torch.rand = orig
     wd = ops.MapMean.apply(real) - ops.MapMean.apply(fake)
     (-wd + gp).backward()
+    d_ref2 = {k: v.clone() for k, v in d_ref.items()}
     sc, grads = O.critic_grads(d_ref, batch["pred"], batch["gt"], batch["refined"], alphas[0], 1.0)
+    with O.emulate_bf16():
+        sc2, grads2 = O.critic_grads(d_ref2, batch["pred"], batch["gt"], batch["refined"], alphas[0], 1.0)
     assert abs(float(gp) - sc["gp"]) <= TOL * abs(sc["gp"]) + 1e-4
     assert abs(float(wd) - sc["wd"]) <= TOL * abs(sc["wd"]) + 2e-3
+    errs = {}
     for k, p in D.named_parameters():
         if k in O.D_BIAS_UNOBSERVABLE:
             assert float(p.grad.abs().max()) == 0.0
             continue
-        assert rel(p.grad, grads[k]) < 3e-2, k
+        errs[k] = (rel(p.grad, grads[k]), rel(p.grad, grads2[k]))
+    print("D grad rel-L2 (vs fp32 oracle, vs bf16-storage oracle):", errs)
+    for k, (e32, e16) in errs.items():
+        assert e16 < 3e-2, (k, e32, e16)
+        assert e32 < 0.1, (k, e32, e16)
 
 
 @pytest.mark.parametrize("name", ["step_B2_S64", "step_B4_S32"])
