@@ -1,0 +1,319 @@
+#!/usr/bin/env python
+"""bench.py - cGAN G+D train-step throughput (patches/s) on B200, BASELINE.json configs[1] per GPU.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--img-size S] [--batch B]
+
+One "step" = the reference loop body (cgan/cgan_train_enhanced.py:297-369): n_critic=2 critic updates (two D
+forwards + gradient penalty with double backward + clip + Adam each) and one generator update, on B synthetic paired
+256x256 patches per GPU.  N>1: one rank per GPU (torchrun), batch sharded, gradient all-reduce over NCCL.
+
+The JSON line (rank 0) carries
+  value        patches/s with the step's inputs already resident in HBM (CUDA events, max over ranks)
+  e2e          the same step through the public API (b200cgan.train_step.CGANTrainer.step) from PINNED HOST buffers:
+               per-step H2D of the patches/boxes and D2H of the logged scalars inside the timed region
+  roofline     the dominant tensor-core kernel family: algorithmic FLOPs per launch / CUDA-event duration per launch,
+               measured live in the timed region, against MEASURED_PEAKS.json (sustained bf16 TFLOP/s)
+  cpu_baseline the CPU oracle (oracle/cgan_oracle.py, a port of the reference's torch-CPU fp32 path) on a bounded
+               sample of the workload, all host cores, rank 0 at N=1 only
+`--impl reference` times that CPU oracle alone (the reference is Python/PyTorch and /root/reference does not travel
+to the GPU box, so the restated port is the reference arm; oracle header explains how it is pinned).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT / "gan-calibrated-semi-supervised-learning_b200"))
+
+METRIC = "cgan_train_patches_per_s"
+UNIT = "patches/s"
+N_CRITIC, LAMBDA_GP = 2, 1.0
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--img-size", type=int, default=256)
+    ap.add_argument("--batch", type=int, default=64, help="patches per GPU")
+    ap.add_argument("--cpu-sample", type=int, default=4, help="patches per CPU-baseline step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------------------------- FLOP model
+def conv_flops_per_patch(S):
+    """(F_G, F_G1, F_D, F_D1): forward conv FLOPs per patch (MAC x 2), App. A of SURVEY.md."""
+    def conv(cin, cout, hout):
+        return 2.0 * hout * hout * cout * 16 * cin
+    fg1 = conv(3, 64, S // 2)
+    fg = fg1 + conv(64, 128, S // 4) + conv(128, 256, S // 8) + conv(256, 512, S // 16)
+    for cin, cout, hin in ((512, 256, S // 16), (512, 128, S // 8), (256, 64, S // 4), (128, 64, S // 2)):
+        fg += 2.0 * hin * hin * 16 * cin * cout
+    fd1 = conv(6, 64, S // 2)
+    fd = fd1 + conv(64, 128, S // 4) + conv(128, 256, S // 8) + conv(256, 512, S // 16)
+    fd += 2.0 * (S // 16 - 1) ** 2 * 512 * 16
+    return fg, fg1, fd, fd1
+
+
+def useful_flops_per_patch(S, c=N_CRITIC):
+    fg, fg1, fd, fd1 = conv_flops_per_patch(S)
+    return (c + 3) * fg - fg1 + (12 * c + 1) * fd - 3 * c * fd1
+
+
+GEMM_KERNELS = ("b2c_conv4s2_bf16", "b2c_convt4s2_bf16", "b2c_wgrad4s2_bf16")
+
+
+def gemm_flops(name, a):
+    """Algorithmic FLOPs of one launch from its scalar C-ABI arguments (include/b2c.h)."""
+    if name == "b2c_wgrad4s2_bf16":      # lds, ldl, accumulate, N, Hs, Ws, Cs, Cl, sm_count
+        _, _, _, N, Hs, Ws, Cs, Cl, _ = a
+        return 2.0 * N * Hs * Ws * Cs * 16 * Cl
+    _, _, N, H, W, Cin, Cout = a          # ldx, ldy, N, H, W, Cin, Cout
+    if name == "b2c_conv4s2_bf16":
+        return 2.0 * N * (H // 2) * (W // 2) * Cout * 16 * Cin
+    return 2.0 * N * H * W * Cout * 16 * Cin
+
+
+# --------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx = float(r[2])
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                if v == "Active":
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------- CPU oracle legs
+def cpu_oracle_run(S, sample, steps, warmup):
+    """Time `steps` train steps of the CPU oracle on `sample` patches, all host cores.  -> (patches/s, s/step, cores)."""
+    import torch
+    sys.path.insert(0, str(ROOT / "oracle"))
+    import cgan_oracle as O  # the checker / CPU baseline; never on the product path
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    st = O.init_state(42)
+    times = []
+    for i in range(warmup + steps):
+        batch, masks, alphas = O.make_batch(sample, S, i)
+        t0 = time.perf_counter()
+        O.train_step(st, batch, masks, alphas, n_critic=N_CRITIC, lambda_gp=LAMBDA_GP)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    total = sum(times)
+    return sample * steps / total, total / steps, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    S, sample = args.img_size, args.cpu_sample
+    v, spstep, cores = cpu_oracle_run(S, sample, args.steps, args.warmup)
+    desc = (f"{sample} synthetic {S}x{S} paired patches per step (of {args.batch}/GPU in the GPU workload), fp32, "
+            f"torch CPU with {cores} threads, {args.steps} steps after {args.warmup} warm-up")
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": spstep * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"cGAN G+D train step, n_critic={N_CRITIC}, {S}x{S} patches, CPU sample of "
+                                   f"{sample} patches/step", "img_size": S, "batch_per_gpu": args.batch},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------- the B200 arm
+def synth_host_batches(B, S, rank, count=2):
+    """Pinned host batches (SURVEY.md §8d distributions); `count` distinct batches are rotated over the steps."""
+    import torch
+    out = []
+    for i in range(count):
+        g = torch.Generator("cpu").manual_seed(1234 + 1000 * rank + i)
+        u = lambda *s: torch.rand(*s, generator=g)
+        b = {"pred": u(B, 3, S, S) * 2 - 1, "gt": u(B, 3, S, S) * 2 - 1, "refined": u(B, 3, S, S) * 2 - 1,
+             "pred_box": torch.cat([u(B, 2) * 0.6 + 0.2, u(B, 2) * 0.3 + 0.1], 1),
+             "delta_true": (torch.randn(B, 4, generator=g) * torch.tensor([0.17, 0.23, 0.32, 0.32])).clamp(-1.5, 1.5)}
+        out.append({k: v.pin_memory() for k, v in b.items()})
+    return out
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    from b200cgan import _lib, rng
+    from b200cgan.models import Discriminator, GeneratorUNet, weights_init_normal
+    from b200cgan.train_step import CGANTrainer
+
+    S, B, K, W = args.img_size, args.batch, args.steps, args.warmup
+    torch.manual_seed(42)
+    G, D = GeneratorUNet(0.3), Discriminator(True)
+    G.apply(weights_init_normal); D.apply(weights_init_normal)
+    G, D = G.to(dev), D.to(dev)
+    rng.manual_seed(42 + rank)
+    tr = CGANTrainer(G, D, n_critic=N_CRITIC, lambda_gp=LAMBDA_GP, world_size=world)
+    host = synth_host_batches(B, S, rank)
+    resident = [{k: v.to(dev) for k, v in b.items()} for b in host]
+    keys = ("pred", "gt", "refined", "pred_box", "delta_true")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    # ---- device-resident leg: `value` + live per-launch timing of the tensor-core kernels
+    for i in range(W):
+        tr.step(*[resident[i % 2][k] for k in keys])
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    timed = _lib.time_kernels(GEMM_KERNELS)
+    l0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        out = tr.step(*[resident[i % 2][k] for k in keys])
+    e1.record()
+    barrier()
+    ms_dev = max_over_ranks(e0.elapsed_time(e1))
+    launches = _lib.launch_count() - l0
+    clk = clocks.stop() if rank == 0 else None
+    _lib.time_kernels(None)
+    fam = {}
+    for name, recs in timed.items():
+        ms = sum(a.elapsed_time(b) for a, b, _ in recs)
+        fl = sum(gemm_flops(name, sc) for _, _, sc in recs)
+        fam[name] = {"launches_per_step": len(recs) / K, "ms_per_step": ms / K, "tflops": fl / ms / 1e9 if ms else 0.0,
+                     "flop_per_launch": fl / max(len(recs), 1), "ms_per_launch": ms / max(len(recs), 1)}
+    finite = all(bool(torch.isfinite(v).all()) for v in out.scalars.values())
+
+    # ---- end-to-end leg: pinned host -> device every step, scalars back to the host every step
+    h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+    stage = [{k: torch.empty_like(v, device=dev) for k, v in host[0].items()} for _ in range(2)]
+    for i in range(2):
+        for k in keys:
+            stage[i % 2][k].copy_(host[i % 2][k], non_blocking=True)
+        tr.step(*[stage[i % 2][k] for k in keys]).to_host()
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    d2h = 0
+    for i in range(K):
+        for k in keys:
+            stage[i % 2][k].copy_(host[i % 2][k], non_blocking=True)
+        sc = tr.step(*[stage[i % 2][k] for k in keys]).to_host()
+        d2h = 4 * len(sc)
+    f1.record()
+    barrier()
+    ms_e2e = max_over_ranks(f0.elapsed_time(f1))
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks = {}
+    pk = ROOT / "MEASURED_PEAKS.json"
+    if pk.exists():
+        peaks = json.loads(pk.read_text())
+    peak_tf, peak_src = peaks.get("bf16_tflops_sustained", 1400.0), ("measured" if peaks else "fallback")
+    dom = max(fam, key=lambda n: fam[n]["ms_per_step"])
+    total_ms = sum(f["ms_per_step"] for f in fam.values())
+    total_tf = sum(f["tflops"] * f["ms_per_step"] for f in fam.values()) / total_ms if total_ms else 0.0
+    roofline = {"bound": "tensor", "kernel": dom, "achieved": fam[dom]["tflops"], "peak": peak_tf, "unit": "TFLOP/s",
+                "frac": fam[dom]["tflops"] / peak_tf, "traffic": None, "peak_source": peak_src + " bf16_tflops_sustained",
+                "flop_per_launch": fam[dom]["flop_per_launch"], "ms_per_launch": fam[dom]["ms_per_launch"],
+                "share_of_step": fam[dom]["ms_per_step"] / (ms_dev / K),
+                "all_tensor_kernels": {"tflops": total_tf, "frac": total_tf / peak_tf,
+                                       "share_of_step": total_ms / (ms_dev / K)}}
+    value = world * B * K / (ms_dev / 1e3)
+    useful = useful_flops_per_patch(S)
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"BASELINE configs[1]: cGAN G+D train step (n_critic={N_CRITIC}, lambda_gp={LAMBDA_GP}, "
+                                   f"spectral norm, clip+Adam), bf16 storage / fp32 accumulate, batch {B} synthetic "
+                                   f"{S}x{S} paired patches per GPU", "img_size": S, "batch_per_gpu": B,
+                       "global_batch": B * world, "parallelism": f"dp{world}",
+                       "l2": "per-step working set (activation stash > 5 GB at B=64,S=256) far exceeds the 126 MB L2; "
+                             "two input batches alternate"},
+            "e2e": {"value": world * B * K / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K},
+            "gpu_launches": launches, "roofline": roofline, "kernels": fam, "clocks": clk,
+            "useful_conv_tflops": useful * B / (ms_dev / K) / 1e9, "finite": finite}
+    if world == 1 and not args.no_cpu_baseline:
+        v, spstep, cores = cpu_oracle_run(S, args.cpu_sample, 2, 1)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"{args.cpu_sample} patches {S}x{S} per step, 2 steps after 1 warm-up, fp32 "
+                                          f"torch CPU oracle ({spstep:.2f} s/step)"}
+    else:
+        line["cpu_baseline"] = None
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -59,6 +59,7 @@ class _Native:
             fn.argtypes = [t for t, _ in sig]
             self.fns[name] = fn
         self.launches = 0
+        self.timed = None  # bench hook: {kernel name: [(start_event, end_event, scalar args)]} (see time_kernels)
 
     def call(self, name, *args):
         fn = self.fns[name]
@@ -72,7 +73,15 @@ class _Native:
                 conv.append(None)
             else:
                 conv.append(a)
-        rc = fn(*conv, torch.cuda.current_stream().cuda_stream)
+        stream = torch.cuda.current_stream()
+        rec = self.timed.get(name) if self.timed is not None else None
+        if rec is not None:
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record(stream)
+        rc = fn(*conv, stream.cuda_stream)
+        if rec is not None:
+            ev1.record(stream)
+            rec.append((ev0, ev1, tuple(a for a in args if isinstance(a, (int, float)))))
         self.launches += 1
         if rc != 0:
             raise B2CError(f"{name} failed ({rc}): {self.lib.b2c_last_error().decode()}")
@@ -100,6 +109,14 @@ def call(name, *args):
 
 def launch_count() -> int:
     return backend().launches
+
+
+def time_kernels(names):
+    """Bench hook: bracket every later launch of the named kernels with CUDA events on the launching stream.
+    Returns the dict the (start, end, scalar-args) records are appended to; pass None to switch it off."""
+    b = backend()
+    b.timed = None if names is None else {n: [] for n in names}
+    return b.timed
 
 
 _sm_count = None
