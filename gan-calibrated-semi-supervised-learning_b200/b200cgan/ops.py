@@ -263,7 +263,8 @@ class FirstDgrad(torch.autograd.Function):
         ctx.save_for_backward(gzd)
         g0 = torch.empty(N, 3, 2 * Ho, 2 * Wo, dtype=torch.float32, device=gzd.device)
         g1 = torch.empty_like(g0) if has_a1 else None
-        _lib.call("b2c_first_dgrad", gzd, wctx.weight.detach(), wctx.inv_sigma, g0, g1, N, 2 * Ho, 2 * Wo)
+        ws = torch.empty(32 * 576, dtype=BF16, device=gzd.device)
+        _lib.call("b2c_first_dgrad", gzd, wctx.weight.detach(), wctx.inv_sigma, g0, g1, ws, N, 2 * Ho, 2 * Wo)
         if g1 is None:
             g1 = g0.new_zeros(())
             ctx.mark_non_differentiable(g1)

@@ -1,8 +1,17 @@
-// First-layer convolutions (Cin = 3 for G.down1, 6 for D.model.0; cgan/models.py:103,245,257).  K = 16*Cin is 48/96:
-// these layers are bandwidth-bound and read the caller's NCHW fp32 patches directly, so they run on
-// CUDA cores with the channel concat (models.py:257), the GP interpolation (losses.py:203-204), the spectral-norm
-// 1/sigma, bias and LeakyReLU(0.2) fused in.  Output / incoming gradients are NHWC bf16 like every other activation.
+// First-layer convolutions (Cin = 3 for G.down1, 6 for D.model.0; cgan/models.py:103,245,257) on tcgen05.
+//
+// K = 16*Cin is only 48/96, so these layers are HBM-bound: the job of the kernels is to stream the
+// caller's NCHW fp32 patches exactly once and keep the arithmetic off the CUDA cores.  Each thread owns one output
+// pixel of a 128-pixel tile: it gathers its 4x4xCin receptive field with coalesced 8-byte loads (+ warp shuffles for
+// the two halo columns), applies the optional GP interpolation x = alpha*a + (1-alpha)*b (cgan/losses.py:203-204) and
+// the channel concat (cgan/models.py:257), and writes one 256-byte im2col row k = tap*8 + c (bf16, channels padded
+// to 8) straight into the 128B-swizzled UMMA layout in shared memory.  That tile is
+//   fprop : the K-major  A operand of  y[128 pix x 64 co]  = A . W^T      (+bias, LeakyReLU, bf16 NHWC store)
+//   wgrad : the MN-major A operand of  dW[128 k  x 64 co] += A^T . gz     (gz tile by TMA; fp32 TMEM accumulation over
+//           all tiles of the CTA; one atomic flush per CTA; bias gradient = the all-ones im2col column k = 127)
+// dgrad (needed only under the gradient penalty) lives in tapgemm.cu (mode D1).
 #include "common.cuh"
+#include "tmap.h"
 
 using namespace b2c;
 
@@ -10,221 +19,347 @@ struct FirstIn {
   const float* a[2];   // up to two (N,3,H,W) fp32 tensors = channels 0-2 and 3-5
   const float* b[2];   // optional interpolation partners
   const float* alpha;  // optional (N) : x = alpha*a + (1-alpha)*b
-  int nparts;
 };
 
-__device__ __forceinline__ float first_in_load(const FirstIn& in, int n, int c, int h, int w, int H, int W) {
-  const int part = c >= 3 ? 1 : 0, cc = c - 3 * part;
-  const long long off = (((long long)n * 3 + cc) * H + h) * W + w;
-  float v = __ldg(in.a[part] + off);
-  if (in.alpha) {
-    const float al = __ldg(in.alpha + n);
-    v = al * v + (1.f - al) * __ldg(in.b[part] + off);
-  }
-  return v;
-}
+static constexpr int FT_THREADS = 128;
+static constexpr int FT_A_BYTES = 2 * 128 * 128;   // [2 k-blocks][128 rows][64 bf16]
+static constexpr int FT_B_BYTES = 128 * 128;       // fprop: [2 k-blocks][64 co][64 k] ; wgrad: [128 pix][64 co]
+static constexpr int FT_SMEM = FT_A_BYTES + FT_B_BYTES + 1024 + 64;
 
-// y[n,oy,ox,co] = act( s * sum x[n,c,2oy+ky-1,2ox+kx-1] w[co][c][ky][kx] + bias[co] ), 64 output channels.
+// Receptive field of one output pixel: v[c][ky] = (x[2ox], x[2ox+1]), l[c][ky] = x[2ox-1], r[c][ky] = x[2ox+2].
 template <int CIN>
-__global__ void __launch_bounds__(256) first_fprop_kernel(FirstIn in, const float* __restrict__ w,
-                                                          const float* __restrict__ inv_sigma,
-                                                          const float* __restrict__ bias, __nv_bfloat16* __restrict__ y,
-                                                          int N, int H, int W, float slope) {
-  constexpr int K = CIN * 16;
-  __shared__ float w_s[K][64];
-  const float s = inv_sigma ? *inv_sigma : 1.f;
-  for (int i = threadIdx.x; i < K * 64; i += 256) {
-    const int co = i / K, k = i % K;  // w is [co][k] contiguous in k
-    w_s[k][co] = w[i] * s;
+struct Field {
+  float2 v[CIN][4];
+  float l[CIN][4], r[CIN][4];
+};
+
+template <int CIN>
+__device__ __forceinline__ void gather_field(const FirstIn& in, long long pix, long long npix, int Ho, int Wo, int H,
+                                             int W, Field<CIN>& f) {
+  const int lane = threadIdx.x & 31;
+  const bool live = pix < npix;
+  int ox = 0, oy = 0, n = 0;
+  if (live) {
+    ox = (int)(pix % Wo);
+    oy = (int)((pix / Wo) % Ho);
+    n = (int)(pix / ((long long)Wo * Ho));
   }
-  __syncthreads();
-  const int Ho = H / 2, Wo = W / 2;
-  const long long npix = (long long)N * Ho * Wo;
-  const int cg = threadIdx.x >> 6;  // 4 groups of 16 output channels
-  for (long long pix = (long long)blockIdx.x * 64 + (threadIdx.x & 63); pix < npix; pix += (long long)gridDim.x * 64) {
-    const int ox = (int)(pix % Wo), oy = (int)((pix / Wo) % Ho), n = (int)(pix / ((long long)Wo * Ho));
-    float acc[16];
+  float al = 1.f;
+  if (in.alpha && live) al = __ldg(in.alpha + n);
 #pragma unroll
-    for (int j = 0; j < 16; ++j) acc[j] = bias ? __ldg(bias + cg * 16 + j) : 0.f;
+  for (int c = 0; c < CIN; ++c) {
+    const int part = c / 3, cc = c % 3;
+    const long long plane = ((long long)n * 3 + cc) * H;
 #pragma unroll
-    for (int c = 0; c < CIN; ++c) {
-#pragma unroll
-      for (int ky = 0; ky < 4; ++ky) {
-        const int iy = 2 * oy + ky - 1;
-#pragma unroll
-        for (int kx = 0; kx < 4; ++kx) {
-          const int ix = 2 * ox + kx - 1;
-          float xv = 0.f;
-          if (iy >= 0 && iy < H && ix >= 0 && ix < W) xv = first_in_load(in, n, c, iy, ix, H, W);
-          const float4* wr = reinterpret_cast<const float4*>(&w_s[c * 16 + ky * 4 + kx][cg * 16]);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float4 wv = wr[j];
-            acc[4 * j] += xv * wv.x; acc[4 * j + 1] += xv * wv.y; acc[4 * j + 2] += xv * wv.z; acc[4 * j + 3] += xv * wv.w;
-          }
+    for (int ky = 0; ky < 4; ++ky) {
+      const int iy = 2 * oy + ky - 1;
+      float2 t = make_float2(0.f, 0.f);
+      const bool row_ok = live && iy >= 0 && iy < H;
+      const long long off = (plane + iy) * W + 2 * ox;
+      if (row_ok) {
+        t = __ldg(reinterpret_cast<const float2*>(in.a[part] + off));
+        if (in.alpha) {
+          const float2 u = __ldg(reinterpret_cast<const float2*>(in.b[part] + off));
+          t.x = al * t.x + (1.f - al) * u.x;
+          t.y = al * t.y + (1.f - al) * u.y;
         }
       }
+      f.v[c][ky] = t;
+      // halo columns: neighbours in the warp hold them unless this lane sits at a warp or image-row edge
+      float lft = __shfl_up_sync(0xffffffffu, t.y, 1);
+      float rgt = __shfl_down_sync(0xffffffffu, t.x, 1);
+      if (ox == 0) lft = 0.f;
+      else if (lane == 0 && row_ok) {
+        lft = __ldg(in.a[part] + off - 1);
+        if (in.alpha) lft = al * lft + (1.f - al) * __ldg(in.b[part] + off - 1);
+      }
+      if (ox == Wo - 1) rgt = 0.f;
+      else if (lane == 31 && row_ok) {
+        rgt = __ldg(in.a[part] + off + 2);
+        if (in.alpha) rgt = al * rgt + (1.f - al) * __ldg(in.b[part] + off + 2);
+      }
+      f.l[c][ky] = row_ok ? lft : 0.f;
+      f.r[c][ky] = row_ok ? rgt : 0.f;
     }
-    uint32_t o[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float a = acc[2 * j], b = acc[2 * j + 1];
-      a = a > 0.f ? a : a * slope;
-      b = b > 0.f ? b : b * slope;
-      o[j] = pack_bf16(a, b);
-    }
-    uint4* d = reinterpret_cast<uint4*>(y + pix * 64 + cg * 16);
-    d[0] = make_uint4(o[0], o[1], o[2], o[3]);
-    d[1] = make_uint4(o[4], o[5], o[6], o[7]);
   }
 }
 
-// gx[n,c,h,w] = s * sum_{co,ky,kx} gz[n,oy,ox,co] w[co][c][ky][kx],  h = 2oy+ky-1, w = 2ox+kx-1.  fp32 NCHW out.
+// Write im2col row `row` (k = tap*8 + c) into the swizzled tile; `ones` puts 1.0 into the padding slot k = 127.
 template <int CIN>
-__global__ void __launch_bounds__(256) first_dgrad_kernel(const __nv_bfloat16* __restrict__ gz, const float* __restrict__ w,
-                                                          const float* __restrict__ inv_sigma, float* __restrict__ gx0,
-                                                          float* __restrict__ gx1, int N, int H, int W) {
-  constexpr int K = CIN * 16;
-  __shared__ float w_s[16][CIN][64];  // [tap][c][co]
-  const float s = inv_sigma ? *inv_sigma : 1.f;
-  for (int i = threadIdx.x; i < K * 64; i += 256) {
-    const int co = i / K, k = i % K, c = k / 16, tap = k % 16;
-    w_s[tap][c][co] = w[i] * s;
-  }
-  __syncthreads();
-  const int Ho = H / 2, Wo = W / 2;
-  const long long npix = (long long)N * H * W;
-  for (long long pix = (long long)blockIdx.x * 256 + threadIdx.x; pix < npix; pix += (long long)gridDim.x * 256) {
-    const int x = (int)(pix % W), yy = (int)((pix / W) % H), n = (int)(pix / ((long long)W * H));
-    float acc[CIN];
+__device__ __forceinline__ void store_field(uint8_t* sA, int row, const Field<CIN>& f, bool ones) {
+  uint8_t* base = sA + (row >> 3) * 1024 + (row & 7) * 128;
 #pragma unroll
-    for (int c = 0; c < CIN; ++c) acc[c] = 0.f;
+  for (int ky = 0; ky < 4; ++ky) {
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
-      const int ky = ((yy + 1) & 1) + 2 * (t >> 1), kx = ((x + 1) & 1) + 2 * (t & 1);
-      const int oy = (yy + 1 - ky) >> 1, ox = (x + 1 - kx) >> 1;
-      if (oy < 0 || oy >= Ho || ox < 0 || ox >= Wo) continue;
-      const uint4* g4 = reinterpret_cast<const uint4*>(gz + (((long long)n * Ho + oy) * Wo + ox) * 64);
+    for (int kx = 0; kx < 4; ++kx) {
+      float e[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        if (c < CIN) e[c] = kx == 0 ? f.l[c][ky] : kx == 1 ? f.v[c][ky].x : kx == 2 ? f.v[c][ky].y : f.r[c][ky];
+        else e[c] = 0.f;
+      }
       const int tap = ky * 4 + kx;
-#pragma unroll
-      for (int v = 0; v < 8; ++v) {
-        const uint4 u = __ldg(g4 + v);
-        const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float2 g = unpack_bf16(uu[e]);
-          const int co = v * 8 + e * 2;
-#pragma unroll
-          for (int c = 0; c < CIN; ++c) acc[c] += g.x * w_s[tap][c][co] + g.y * w_s[tap][c][co + 1];
-        }
-      }
-    }
-#pragma unroll
-    for (int c = 0; c < CIN; ++c) {
-      float* dst = c >= 3 ? gx1 : gx0;
-      dst[(((long long)n * 3 + (c % 3)) * H + yy) * W + x] = acc[c];
+      if (tap == 15 && ones) e[7] = 1.f;
+      const uint4 u = make_uint4(pack_bf16(e[0], e[1]), pack_bf16(e[2], e[3]), pack_bf16(e[4], e[5]), pack_bf16(e[6], e[7]));
+      *reinterpret_cast<uint4*>(base + (tap >> 3) * 16384 + (((tap & 7) ^ (row & 7)) << 4)) = u;
     }
   }
 }
 
-// dw[co][c][ky][kx] += sum_pix gz[pix,co] * x[n,c,2oy+ky-1,2ox+kx-1];  db[co] += sum_pix gz[pix,co].
-// Block: 256 threads = 64 co x 4 k-groups; pixels staged 32 at a time in shared memory; fp32 atomics at the end.
+// ------------------------------------------------------------------------------------------------ fprop
 template <int CIN>
-__global__ void __launch_bounds__(256) first_wgrad_kernel(FirstIn in, const __nv_bfloat16* __restrict__ gz,
-                                                          float* __restrict__ dw, float* __restrict__ db, int N, int H,
-                                                          int W, long long pix_per_block) {
-  constexpr int K = CIN * 16, KG = K / 4, P = 32;
-  __shared__ float x_s[P][K];
-  __shared__ float g_s[P][65];
+__global__ void __launch_bounds__(FT_THREADS) first_fprop_tc_kernel(FirstIn in, const float* __restrict__ w,
+                                                                    const float* __restrict__ inv_sigma,
+                                                                    const float* __restrict__ bias,
+                                                                    __nv_bfloat16* __restrict__ y, int N, int H, int W,
+                                                                    float slope) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + FT_A_BYTES;
+  uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sB + FT_B_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 1);
+  __shared__ float bias_s[64];
+
+  const int t = threadIdx.x, warp = t >> 5;
   const int Ho = H / 2, Wo = W / 2;
   const long long npix = (long long)N * Ho * Wo;
-  const long long p_begin = (long long)blockIdx.x * pix_per_block;
-  long long p_end = p_begin + pix_per_block;
-  if (p_end > npix) p_end = npix;
-  const int co = threadIdx.x & 63, kg = threadIdx.x >> 6;
-  float acc[KG];
-#pragma unroll
-  for (int j = 0; j < KG; ++j) acc[j] = 0.f;
-  float bacc = 0.f;
-  for (long long p0 = p_begin; p0 < p_end; p0 += P) {
-    const int np = (int)((p_end - p0) < P ? (p_end - p0) : P);
-    for (int i = threadIdx.x; i < P * K; i += 256) {
-      const int pp = i / K, k = i % K;
-      float v = 0.f;
-      if (pp < np) {
-        const long long pix = p0 + pp;
-        const int ox = (int)(pix % Wo), oy = (int)((pix / Wo) % Ho), n = (int)(pix / ((long long)Wo * Ho));
-        const int c = k / 16, ky = (k / 4) & 3, kx = k & 3;
-        const int iy = 2 * oy + ky - 1, ix = 2 * ox + kx - 1;
-        if (iy >= 0 && iy < H && ix >= 0 && ix < W) v = first_in_load(in, n, c, iy, ix, H, W);
-      }
-      x_s[pp][k] = v;
-    }
-    for (int i = threadIdx.x; i < P * 64; i += 256) {
-      const int pp = i >> 6, c = i & 63;
-      g_s[pp][c] = pp < np ? __bfloat162float(gz[(p0 + pp) * 64 + c]) : 0.f;
-    }
-    __syncthreads();
-#pragma unroll 4
-    for (int pp = 0; pp < P; ++pp) {
-      const float g = g_s[pp][co];
-      if (kg == 0) bacc += g;
-#pragma unroll
-      for (int j = 0; j < KG; ++j) acc[j] += g * x_s[pp][kg * KG + j];
-    }
-    __syncthreads();
+  const int ntiles = (int)((npix + 127) / 128);
+
+  if (t == 0) {
+    mbar_init(mma_bar, 1);
+    fence_barrier_init();
   }
+  if (warp == 1) tmem_alloc<64>(tmem_slot);
+  // weights: B[co][k = tap*8 + c] = w[co][c][tap] / sigma, K-major, two 64-wide k-blocks of [64 rows x 128 B]
+  {
+    const float s = inv_sigma ? __ldg(inv_sigma) : 1.f;
+    for (int i = t; i < 64 * 16; i += FT_THREADS) {
+      const int co = i >> 4, tap = i & 15;
+      float e[8];
 #pragma unroll
-  for (int j = 0; j < KG; ++j) atomicAdd(dw + (long long)co * K + kg * KG + j, acc[j]);
-  if (kg == 0 && db) atomicAdd(db + co, bacc);
+      for (int c = 0; c < 8; ++c) e[c] = c < CIN ? __ldg(w + ((long long)co * CIN + c) * 16 + tap) * s : 0.f;
+      const uint4 u = make_uint4(pack_bf16(e[0], e[1]), pack_bf16(e[2], e[3]), pack_bf16(e[4], e[5]), pack_bf16(e[6], e[7]));
+      *reinterpret_cast<uint4*>(sB + (tap >> 3) * 8192 + (co >> 3) * 1024 + (co & 7) * 128 + (((tap & 7) ^ (co & 7)) << 4)) = u;
+    }
+    if (t < 64) bias_s[t] = bias ? __ldg(bias + t) : 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 0);
+
+  Field<CIN> f;
+  int tile = blockIdx.x;
+  if (tile < ntiles) gather_field<CIN>(in, (long long)tile * 128 + t, npix, Ho, Wo, H, W, f);
+  uint32_t phase = 0;
+  for (; tile < ntiles; tile += gridDim.x) {
+    store_field<CIN>(sA, t, f, false);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    if (t == 0) {
+      tc_fence_after();
+      const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        umma_bf16(tmem_base, umma_desc_sw128(a0 + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
+                  umma_desc_sw128(b0 + (k >> 2) * 8192 + (k & 3) * 32, 16, 1024), idesc, (uint32_t)(k != 0));
+      umma_commit(mma_bar);
+    }
+    const long long pix = (long long)tile * 128 + t;
+    const int next = tile + gridDim.x;
+    if (next < ntiles) gather_field<CIN>(in, (long long)next * 128 + t, npix, Ho, Wo, H, W, f);  // overlaps the MMA
+    mbar_wait(mma_bar, phase);
+    phase ^= 1;
+    tc_fence_after();
+#pragma unroll
+    for (int c0 = 0; c0 < 64; c0 += 32) {
+      uint32_t v0[16], v1[16];
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + c0;
+      tmem_ld16(taddr, v0);
+      tmem_ld16(taddr + 16, v1);
+      tmem_ld_wait();
+      if (pix < npix) {
+        uint32_t o[16];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float a = __uint_as_float(v0[2 * j]) + bias_s[c0 + 2 * j], b = __uint_as_float(v0[2 * j + 1]) + bias_s[c0 + 2 * j + 1];
+          float c = __uint_as_float(v1[2 * j]) + bias_s[c0 + 16 + 2 * j], d = __uint_as_float(v1[2 * j + 1]) + bias_s[c0 + 17 + 2 * j];
+          a = a > 0.f ? a : a * slope; b = b > 0.f ? b : b * slope;
+          c = c > 0.f ? c : c * slope; d = d > 0.f ? d : d * slope;
+          o[j] = pack_bf16(a, b);
+          o[8 + j] = pack_bf16(c, d);
+        }
+        uint4* d4 = reinterpret_cast<uint4*>(y + pix * 64 + c0);
+        d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+        d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
+        d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<64>(tmem_base);
 }
 
+// ------------------------------------------------------------------------------------------------ wgrad
+// dw[co][c][ky][kx] += sum_pix gz[pix,co] * x[n,c,2oy+ky-1,2ox+kx-1];  db[co] += sum_pix gz[pix,co].
+template <int CIN>
+__global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, const __grid_constant__ CUtensorMap tmG,
+                                                                    float* __restrict__ dw, float* __restrict__ db,
+                                                                    int N, int H, int W) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + FT_A_BYTES;
+  uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sB + FT_B_BYTES);
+  uint64_t* tma_bar = mma_bar + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tma_bar + 1);
+
+  const int t = threadIdx.x, warp = t >> 5;
+  const int Ho = H / 2, Wo = W / 2;
+  const long long npix = (long long)N * Ho * Wo;
+  const int ntiles = (int)((npix + 127) / 128);
+
+  if (t == 0) {
+    tma_prefetch_desc(&tmG);
+    mbar_init(mma_bar, 1);
+    mbar_init(tma_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<64>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);
+
+  Field<CIN> f;
+  int tile = blockIdx.x;
+  if (tile < ntiles) gather_field<CIN>(in, (long long)tile * 128 + t, npix, Ho, Wo, H, W, f);
+  uint32_t it = 0;
+  for (; tile < ntiles; tile += gridDim.x, ++it) {
+    if (it > 0) mbar_wait(mma_bar, (it - 1) & 1);  // the previous tile's MMAs are done reading sA / sB
+    if (t == 0) {
+      mbar_expect_tx(tma_bar, FT_B_BYTES);
+      tma_load_2d(sB, &tmG, tma_bar, 0, tile * 128);  // rows past npix are zero-filled
+    }
+    store_field<CIN>(sA, t, f, (long long)tile * 128 + t < npix);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    if (t == 0) {
+      mbar_wait(tma_bar, it & 1);
+      tc_fence_after();
+      const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)  // 16 pixels of the reduction per MMA
+        umma_bf16(tmem_base, umma_desc_sw128(a0 + k * 2048, 16384, 1024), umma_desc_sw128(b0 + k * 2048, 16384, 1024),
+                  idesc, (uint32_t)((it | (uint32_t)k) != 0));
+      umma_commit(mma_bar);
+    }
+    const int next = tile + gridDim.x;
+    if (next < ntiles) gather_field<CIN>(in, (long long)next * 128 + t, npix, Ho, Wo, H, W, f);
+  }
+  if (it > 0) {
+    mbar_wait(mma_bar, (it - 1) & 1);
+    tc_fence_after();
+    const int tap = t >> 3, c = t & 7;
+#pragma unroll 1
+    for (int c0 = 0; c0 < 64; c0 += 16) {
+      uint32_t v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + c0, v);
+      tmem_ld_wait();
+      if (c < CIN) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) atomicAdd(dw + ((long long)(c0 + j) * CIN + c) * 16 + tap, __uint_as_float(v[j]));
+      } else if (t == 127 && db) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) atomicAdd(db + c0 + j, __uint_as_float(v[j]));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<64>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------ host side
 static FirstIn make_in(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha) {
   FirstIn in;
-  in.a[0] = a0; in.a[1] = a1; in.b[0] = b0; in.b[1] = b1; in.alpha = alpha; in.nparts = a1 ? 2 : 1;
+  in.a[0] = a0; in.a[1] = a1 ? a1 : a0; in.b[0] = b0; in.b[1] = b1 ? b1 : b0; in.alpha = alpha;
   return in;
+}
+
+template <typename K>
+static int first_attr(K kernel) {
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_SMEM);
+  if (e != cudaSuccess) {
+    b2c_set_error("cudaFuncSetAttribute(first layer): %s", cudaGetErrorString(e));
+    return B2C_ERR_CUDA;
+  }
+  return B2C_OK;
+}
+
+static int first_check(const float* a0, const float* b0, const float* alpha, int H, int W) {
+  B2C_REQUIRE(H % 2 == 0 && W % 2 == 0, "first layer: odd size %dx%d", H, W);
+  B2C_REQUIRE(((uintptr_t)a0 & 7) == 0, "first layer: input must be 8-byte aligned");
+  B2C_REQUIRE(!alpha || b0, "first layer: alpha given without interpolation partners");
+  return B2C_OK;
 }
 
 // a0/a1: (N,3,H,W) fp32 NCHW halves (a1 null => Cin=3).  b0/b1/alpha: optional interpolation (all or none).
 extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                                const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
                                float slope, void* stream) {
-  B2C_REQUIRE(H % 2 == 0 && W % 2 == 0, "first_fprop: odd size");
+  int rc = first_check(a0, b0, alpha, H, W);
+  if (rc) return rc;
+  static bool attr_done = false;
+  if (!attr_done) {
+    if ((rc = first_attr(first_fprop_tc_kernel<6>)) || (rc = first_attr(first_fprop_tc_kernel<3>))) return rc;
+    attr_done = true;
+  }
   FirstIn in = make_in(a0, a1, b0, b1, alpha);
   const long long npix = (long long)N * (H / 2) * (W / 2);
-  long long blocks = (npix + 63) / 64;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  long long blocks = (npix + 127) / 128;
+  if (blocks > 148 * 4) blocks = 148 * 4;
   if (a1)
-    first_fprop_kernel<6><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(in, w, inv_sigma, bias, (__nv_bfloat16*)y, N, H, W, slope);
+    first_fprop_tc_kernel<6><<<(unsigned)blocks, FT_THREADS, FT_SMEM, (cudaStream_t)stream>>>(
+        in, w, inv_sigma, bias, (__nv_bfloat16*)y, N, H, W, slope);
   else
-    first_fprop_kernel<3><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(in, w, inv_sigma, bias, (__nv_bfloat16*)y, N, H, W, slope);
+    first_fprop_tc_kernel<3><<<(unsigned)blocks, FT_THREADS, FT_SMEM, (cudaStream_t)stream>>>(
+        in, w, inv_sigma, bias, (__nv_bfloat16*)y, N, H, W, slope);
   return b2c_check_launch("first_fprop");
 }
 
-extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1, int N,
-                               int H, int W, void* stream) {
-  const long long npix = (long long)N * H * W;
-  long long blocks = (npix + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  if (gx1)
-    first_dgrad_kernel<6><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)gz, w, inv_sigma, gx0, gx1, N, H, W);
-  else
-    first_dgrad_kernel<3><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)gz, w, inv_sigma, gx0, gx1, N, H, W);
-  return b2c_check_launch("first_dgrad");
-}
-
-// dw: fp32 [64][Cin][4][4], db: fp32 [64] or null; both are ACCUMULATED into (caller zeroes).
+// dw: fp32 [64][Cin][4][4], db: fp32 [64] or null; both are ACCUMULATED into (caller zeroes).  gz: dense NHWC bf16.
 extern "C" int b2c_first_wgrad(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                                const void* gz, float* dw, float* db, int N, int H, int W, void* stream) {
+  int rc = first_check(a0, b0, alpha, H, W);
+  if (rc) return rc;
+  static bool attr_done = false;
+  if (!attr_done) {
+    if ((rc = first_attr(first_wgrad_tc_kernel<6>)) || (rc = first_attr(first_wgrad_tc_kernel<3>))) return rc;
+    attr_done = true;
+  }
   FirstIn in = make_in(a0, a1, b0, b1, alpha);
   const long long npix = (long long)N * (H / 2) * (W / 2);
-  long long blocks = 148 * 4;
-  long long ppb = (npix + blocks - 1) / blocks;
-  ppb = (ppb + 31) / 32 * 32;
-  blocks = (npix + ppb - 1) / ppb;
+  CUtensorMap tmG;
+  {
+    uint64_t dims[2] = {64, (uint64_t)npix};
+    uint64_t str[1] = {128};
+    uint32_t box[2] = {64, 128};
+    rc = b2c_make_tmap_bf16(&tmG, gz, 2, dims, str, box);
+    if (rc) return rc;
+  }
+  long long blocks = (npix + 127) / 128;
+  if (blocks > 148 * 4) blocks = 148 * 4;
   if (a1)
-    first_wgrad_kernel<6><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(in, (const __nv_bfloat16*)gz, dw, db, N, H, W, ppb);
+    first_wgrad_tc_kernel<6><<<(unsigned)blocks, FT_THREADS, FT_SMEM, (cudaStream_t)stream>>>(in, tmG, dw, db, N, H, W);
   else
-    first_wgrad_kernel<3><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(in, (const __nv_bfloat16*)gz, dw, db, N, H, W, ppb);
+    first_wgrad_tc_kernel<3><<<(unsigned)blocks, FT_THREADS, FT_SMEM, (cudaStream_t)stream>>>(in, tmG, dw, db, N, H, W);
   return b2c_check_launch("first_wgrad");
 }

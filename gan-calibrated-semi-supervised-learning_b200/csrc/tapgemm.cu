@@ -7,6 +7,10 @@
 //               plain TMA box; the conv's zero padding is TMA out-of-bounds fill (no padded copies, no im2col).
 //   mode T4S2 : y[n,2i+py,2j+px,:] = sum_{a,b}  x[n,i+py+a-1,j+px+b-1,:] . Wt[py,px][:, (a,b,:)]     (4 taps x 4 parities)
 //               = ConvTranspose2d(k4,s2,p1) and also the data gradient of C4S2.
+//   mode D1   : data gradient of the FIRST conv (Cin = 3/6, Cout = 64; cgan/models.py:103,245), needed only under the
+//               gradient penalty (cgan/losses.py:213-220).  One GEMM row per 2x2 block (i,j) of input pixels:
+//               gx[n,c,2i+di,2j+dj] = sum_{fy,fx,co} gz[n,i+fy,j+fx,co] . Wd[(di,dj,c)][(fy,fx,co)]   (9 taps, N = 32)
+//               with Wd holding w[co][c][di+1-2fy][dj+1-2fx] where that tap exists, else 0.  fp32 NCHW output.
 // Pipeline: warp 0 = TMA producer, warp 1 = single-thread tcgen05.mma issuer (accumulator in TMEM),
 // warps 2-5 = epilogue (tcgen05.ld -> +bias -> bf16 -> NHWC stores).  2 CTAs/SM overlap epilogue with mainloop.
 #include "common.cuh"
@@ -15,7 +19,7 @@
 using namespace b2c;
 
 struct TapGemmParams {
-  int mode;  // 0 = C4S2, 1 = T4S2
+  int mode;  // 0 = C4S2, 1 = T4S2, 2 = D1
   int N, Ho, Wo, Cin, Cout;
   int BW, BH, BI;           // pixel box, BW*BH*BI == 128
   int tiles_x, tiles_y;     // tile grid over the tile space (C: output pixels; T: input-resolution pixels)
@@ -23,11 +27,13 @@ struct TapGemmParams {
   __nv_bfloat16* y;
   long long ldy;            // output pixel stride in elements
   const float* bias;        // nullable, per output channel
+  float* gx0;               // mode D1: fp32 (N,3,2Ho,2Wo) outputs (gx1 null when Cin = 3)
+  float* gx1;
 };
 
 template <int BN>
 struct TapGemmCfg {
-  static constexpr int STAGES = (BN == 128) ? 3 : 4;
+  static constexpr int STAGES = (BN == 128) ? 3 : (BN == 32 ? 6 : 4);
   static constexpr int A_BYTES = 128 * 128;
   static constexpr int B_BYTES = BN * 128;
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;
@@ -53,7 +59,7 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
   const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
   const int ncol0 = blockIdx.y * BN;
   const int parity = blockIdx.z, py = parity >> 1, px = parity & 1;
-  const int ntaps = p.mode == 0 ? 16 : 4;
+  const int ntaps = p.mode == 0 ? 16 : (p.mode == 1 ? 4 : 9);
   const int niters = ntaps * p.kchunks;
 
   if (warp == 0 && lane == 0) {
@@ -84,9 +90,11 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
             const int ky = tap >> 2, kx = tap & 3;
             const int fy = (ky - 1) >> 1, di = (ky - 1) & 1, fx = (kx - 1) >> 1, dj = (kx - 1) & 1;
             tma_load_5d(dA, &tmA, &full[stage], dj * p.Cin + cc * 64, x0 + fx, di, y0 + fy, n0);
-          } else {
+          } else if (p.mode == 1) {
             const int a = tap >> 1, b = tap & 1;
             tma_load_4d(dA, &tmA, &full[stage], cc * 64, x0 + px + b - 1, y0 + py + a - 1, n0);
+          } else {
+            tma_load_4d(dA, &tmA, &full[stage], 0, x0 + tap % 3 - 1, y0 + tap / 3 - 1, n0);
           }
           tma_load_2d(sB + stage * Cfg::B_BYTES, &tmB, &full[stage], tap * p.Cin + cc * 64,
                       parity * p.Cout + ncol0);
@@ -122,6 +130,27 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
     __nv_bfloat16* dst = p.y + (((long long)n * p.Ho + oy) * p.Wo + ox) * p.ldy + ncol0;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
+    if (BN == 32) {  // mode D1: column = di*16 + dj*8 + c  ->  fp32 NCHW, one float2 (dj = 0,1) per (c, di)
+      uint32_t v0[16], v1[16];
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+      tmem_ld16(taddr, v0);
+      tmem_ld16(taddr + 16, v1);
+      tmem_ld_wait();
+      if (valid) {
+        const int H = 2 * p.Ho, W = 2 * p.Wo;
+        const int cin = p.gx1 ? 6 : 3;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          if (c < cin) {
+            float* plane = (c < 3 ? p.gx0 : p.gx1) + ((long long)n * 3 + (c % 3)) * H * W;
+            *reinterpret_cast<float2*>(plane + (long long)(2 * oy) * W + 2 * ox) =
+                make_float2(__uint_as_float(v0[c]), __uint_as_float(v0[8 + c]));
+            *reinterpret_cast<float2*>(plane + (long long)(2 * oy + 1) * W + 2 * ox) =
+                make_float2(__uint_as_float(v1[c]), __uint_as_float(v1[8 + c]));
+          }
+        }
+      }
+    } else
 #pragma unroll 1
     for (int c0 = 0; c0 < BN; c0 += 32) {
       uint32_t v0[16], v1[16];
@@ -193,7 +222,7 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
   B2C_REQUIRE(ldy % 8 == 0 && ((uintptr_t)y & 15) == 0, "tapgemm: output must be 16-byte aligned (ldy=%lld)", ldy);
   TapGemmParams p;
   p.mode = mode; p.N = N; p.Cin = Cin; p.Cout = Cout; p.kchunks = Cin / 64;
-  p.y = (__nv_bfloat16*)y; p.ldy = ldy; p.bias = bias;
+  p.y = (__nv_bfloat16*)y; p.ldy = ldy; p.bias = bias; p.gx0 = p.gx1 = nullptr;
   int TH, TW;
   CUtensorMap tmA, tmB;
   if (mode == 0) {
@@ -233,6 +262,55 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
   dim3 grid(p.tiles_x * p.tiles_y * tiles_n, Cout / BN, mode == 0 ? 1 : 4);
   if (BN == 128) return launch_tapgemm<128>(tmA, tmB, p, grid, (cudaStream_t)stream);
   return launch_tapgemm<64>(tmA, tmB, p, grid, (cudaStream_t)stream);
+}
+
+// Wd[(di*16 + dj*8 + c)][(tap9*64 + co)] for mode D1 (32 x 576 bf16), scaled by 1/sigma.
+__global__ void pack_w_d1_kernel(const float* __restrict__ w, const float* __restrict__ inv_sigma,
+                                 __nv_bfloat16* __restrict__ out, int cin) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 32 * 576) return;
+  const int row = i / 576, k = i % 576;
+  const int di = row >> 4, dj = (row >> 3) & 1, c = row & 7;
+  const int tap = k >> 6, co = k & 63;
+  const int fy = tap / 3 - 1, fx = tap % 3 - 1;
+  const int ky = di + 1 - 2 * fy, kx = dj + 1 - 2 * fx;
+  float v = 0.f;
+  if (c < cin && ky >= 0 && ky < 4 && kx >= 0 && kx < 4)
+    v = w[(((long long)co * cin + c) * 4 + ky) * 4 + kx] * (inv_sigma ? *inv_sigma : 1.f);
+  out[i] = __float2bfloat16(v);
+}
+
+// gz: dense (N,H/2,W/2,64) bf16; gx0/gx1: fp32 (N,3,H,W) (gx1 null => Cin = 3); ws: >= 36864 bytes, 16-byte aligned.
+extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1,
+                               void* ws, int N, int H, int W, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  B2C_REQUIRE(H % 2 == 0 && W % 2 == 0, "first_dgrad: odd size %dx%d", H, W);
+  B2C_REQUIRE(ws && ((uintptr_t)ws & 15) == 0, "first_dgrad: workspace missing or unaligned");
+  TapGemmParams p;
+  p.mode = 2; p.N = N; p.Cin = 64; p.Cout = 32; p.kchunks = 1;
+  p.y = nullptr; p.ldy = 0; p.bias = nullptr; p.gx0 = gx0; p.gx1 = gx1;
+  p.Ho = H / 2; p.Wo = W / 2;
+  B2C_REQUIRE(pick_box(p.Ho, p.Wo, 128, &p.BW, &p.BH, &p.BI), "first_dgrad: unsupported spatial size %dx%d", H, W);
+  p.tiles_x = p.Wo / p.BW; p.tiles_y = p.Ho / p.BH;
+  const int tiles_n = (N + p.BI - 1) / p.BI;
+  pack_w_d1_kernel<<<(32 * 576 + 255) / 256, 256, 0, st>>>(w, inv_sigma, (__nv_bfloat16*)ws, gx1 ? 6 : 3);
+  int rc = b2c_check_launch("pack_w_d1_kernel");
+  if (rc) return rc;
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[4] = {64, (uint64_t)p.Wo, (uint64_t)p.Ho, (uint64_t)N};
+    uint64_t str[3] = {128, (uint64_t)128 * p.Wo, (uint64_t)128 * p.Wo * p.Ho};
+    uint32_t box[4] = {64, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BI};
+    if ((rc = b2c_make_tmap_bf16(&tmA, gz, 4, dims, str, box))) return rc;
+  }
+  {
+    uint64_t dims[2] = {576, 32};
+    uint64_t str[1] = {2 * 576};
+    uint32_t box[2] = {64, 32};
+    if ((rc = b2c_make_tmap_bf16(&tmB, ws, 2, dims, str, box))) return rc;
+  }
+  dim3 grid(p.tiles_x * p.tiles_y * tiles_n, 1, 1);
+  return launch_tapgemm<32>(tmA, tmB, p, grid, st);
 }
 
 extern "C" int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* bias, void* y,

@@ -35,8 +35,8 @@ int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* large, long 
 int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                     const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
                     float slope, void* stream);
-int b2c_first_dgrad(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1, int N, int H, int W,
-                    void* stream);
+int b2c_first_dgrad(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1, void* ws, int N,
+                    int H, int W, void* stream); /* ws: >= 36864 bytes of scratch for the packed tap weights */
 int b2c_first_wgrad(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                     const void* gz, float* dw, float* db, int N, int H, int W, void* stream);
 

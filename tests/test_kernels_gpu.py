@@ -98,10 +98,11 @@ def test_wgrad4s2(L, N, Hs, Ws, Cs, Cl):
     assert rel(dw, 2 * ref) < 2e-3
 
 
-@pytest.mark.parametrize("cin", [3, 6])
-def test_first_layer(L, cin):
+@pytest.mark.parametrize("cin,N,S,interp", [(3, 3, 32, True), (6, 3, 32, True), (6, 2, 128, False), (3, 5, 64, False),
+                                             (6, 1, 256, True)])
+def test_first_layer(L, cin, N, S, interp):
+    """First-layer kernels (tcgen05, bf16 operands, fp32 accumulate) against torch on bf16-rounded x and w."""
     g = torch.Generator().manual_seed(5)
-    N, S = 3, 32
     x = torch.randn(N, cin, S, S, generator=g)
     xb = torch.randn(N, cin, S, S, generator=g)
     alpha = torch.rand(N, generator=g)
@@ -110,23 +111,25 @@ def test_first_layer(L, cin):
     sig = torch.tensor([2.0, 0.5])
     parts = lambda t: [t[:, :3].contiguous().cuda(), t[:, 3:].contiguous().cuda() if cin == 6 else None]
     a0, a1 = parts(x)
-    b0, b1 = parts(xb)
+    b0, b1 = parts(xb) if interp else (None, None)
+    al_d = alpha.cuda() if interp else None
     y = torch.empty(N, S // 2, S // 2, 64, dtype=torch.bfloat16, device="cuda")
-    L.call("b2c_first_fprop", a0, a1, b0, b1 if cin == 6 else b0, alpha.cuda(), w.cuda(), sig.cuda()[1:], b.cuda(), y, N, S, S, 0.2)
+    L.call("b2c_first_fprop", a0, a1, b0, b1, al_d, w.cuda(), sig.cuda()[1:], b.cuda(), y, N, S, S, 0.2)
     al = alpha.view(N, 1, 1, 1)
-    xi = al * x + (1 - al) * xb
-    ref = F.leaky_relu(F.conv2d(xi, w * 0.5, b, 2, 1), 0.2)
+    xi = q(al * x + (1 - al) * xb) if interp else q(x)
+    ref = F.leaky_relu(F.conv2d(xi, q(w * 0.5), b, 2, 1), 0.2)
     assert rel(nchw(y), ref) < 5e-3
     gz = q(torch.randn(N, 64, S // 2, S // 2, generator=g))
     gx0 = torch.empty(N, 3, S, S, device="cuda")
     gx1 = torch.empty(N, 3, S, S, device="cuda") if cin == 6 else None
-    L.call("b2c_first_dgrad", nhwc(gz), w.cuda(), sig.cuda()[1:], gx0, gx1, N, S, S)
-    refdx = torch.nn.grad.conv2d_input((N, cin, S, S), w * 0.5, gz, 2, 1)
+    ws = torch.empty(32 * 576, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_first_dgrad", nhwc(gz), w.cuda(), sig.cuda()[1:], gx0, gx1, ws, N, S, S)
+    refdx = torch.nn.grad.conv2d_input((N, cin, S, S), q(w * 0.5), gz, 2, 1)
     got = torch.cat([gx0.cpu()] + ([gx1.cpu()] if cin == 6 else []), 1)
     assert rel(got, refdx) < 1e-4
     dw = torch.zeros(64, cin, 4, 4, device="cuda")
     db = torch.zeros(64, device="cuda")
-    L.call("b2c_first_wgrad", a0, a1, b0, b1 if cin == 6 else b0, alpha.cuda(), nhwc(gz), dw, db, N, S, S)
+    L.call("b2c_first_wgrad", a0, a1, b0, b1, al_d, nhwc(gz), dw, db, N, S, S)
     refdw = torch.nn.grad.conv2d_weight(xi, (64, cin, 4, 4), gz, 2, 1)
     assert rel(dw, refdw) < 1e-4
     assert rel(db, gz.sum((0, 2, 3))) < 1e-4
