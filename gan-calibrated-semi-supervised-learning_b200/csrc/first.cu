@@ -24,7 +24,8 @@ struct FirstIn {
 static constexpr int FT_THREADS = 128;
 static constexpr int FT_A_BYTES = 2 * 128 * 128;   // [2 k-blocks][128 rows][64 bf16]
 static constexpr int FT_B_BYTES = 128 * 128;       // fprop: [2 k-blocks][64 co][64 k] ; wgrad: [128 pix][64 co]
-static constexpr int FT_SMEM = FT_A_BYTES + FT_B_BYTES + 1024 + 64;
+static constexpr int FT_SMEM = FT_A_BYTES + 2 * FT_B_BYTES + 1024 + 64;   // wgrad (double-buffered gz tile)
+static constexpr int FT_SMEM_FPROP = FT_A_BYTES + FT_B_BYTES + 1024 + 64;
 
 // Receptive field of one output pixel: v[c][ky] = (x[2ox], x[2ox+1]), l[c][ky] = x[2ox-1], r[c][ky] = x[2ox+2].
 template <int CIN>
@@ -33,7 +34,9 @@ struct Field {
   float l[CIN][4], r[CIN][4];
 };
 
-template <int CIN>
+// Two phases so that every global load of the field is in flight before the first dependent instruction: phase 1
+// issues the 4*CIN row loads (+ the predicated halo loads of the warp-edge lanes), phase 2 exchanges halo columns.
+template <int CIN, bool INTERP>
 __device__ __forceinline__ void gather_field(const FirstIn& in, long long pix, long long npix, int Ho, int Wo, int H,
                                              int W, Field<CIN>& f) {
   const int lane = threadIdx.x & 31;
@@ -44,8 +47,12 @@ __device__ __forceinline__ void gather_field(const FirstIn& in, long long pix, l
     oy = (int)((pix / Wo) % Ho);
     n = (int)(pix / ((long long)Wo * Ho));
   }
-  float al = 1.f;
-  if (in.alpha && live) al = __ldg(in.alpha + n);
+  constexpr bool interp = INTERP;
+  const float al = (interp && live) ? __ldg(in.alpha + n) : 1.f;
+  const float be = 1.f - al;
+  const bool want_l = lane == 0 && ox > 0, want_r = lane == 31 && ox < Wo - 1;
+  float2 u[CIN][4];
+  float lb[CIN][4], rb[CIN][4];
 #pragma unroll
   for (int c = 0; c < CIN; ++c) {
     const int part = c / 3, cc = c % 3;
@@ -53,33 +60,38 @@ __device__ __forceinline__ void gather_field(const FirstIn& in, long long pix, l
 #pragma unroll
     for (int ky = 0; ky < 4; ++ky) {
       const int iy = 2 * oy + ky - 1;
-      float2 t = make_float2(0.f, 0.f);
       const bool row_ok = live && iy >= 0 && iy < H;
-      const long long off = (plane + iy) * W + 2 * ox;
-      if (row_ok) {
-        t = __ldg(reinterpret_cast<const float2*>(in.a[part] + off));
-        if (in.alpha) {
-          const float2 u = __ldg(reinterpret_cast<const float2*>(in.b[part] + off));
-          t.x = al * t.x + (1.f - al) * u.x;
-          t.y = al * t.y + (1.f - al) * u.y;
-        }
+      const long long off = row_ok ? (plane + iy) * W + 2 * ox : 0;
+      const float* pa = in.a[part] + off;
+      f.v[c][ky] = row_ok ? __ldg(reinterpret_cast<const float2*>(pa)) : make_float2(0.f, 0.f);
+      f.l[c][ky] = (row_ok && want_l) ? __ldg(pa - 1) : 0.f;
+      f.r[c][ky] = (row_ok && want_r) ? __ldg(pa + 2) : 0.f;
+      if (interp) {
+        const float* pb = in.b[part] + off;
+        u[c][ky] = row_ok ? __ldg(reinterpret_cast<const float2*>(pb)) : make_float2(0.f, 0.f);
+        lb[c][ky] = (row_ok && want_l) ? __ldg(pb - 1) : 0.f;
+        rb[c][ky] = (row_ok && want_r) ? __ldg(pb + 2) : 0.f;
       }
-      f.v[c][ky] = t;
-      // halo columns: neighbours in the warp hold them unless this lane sits at a warp or image-row edge
-      float lft = __shfl_up_sync(0xffffffffu, t.y, 1);
-      float rgt = __shfl_down_sync(0xffffffffu, t.x, 1);
-      if (ox == 0) lft = 0.f;
-      else if (lane == 0 && row_ok) {
-        lft = __ldg(in.a[part] + off - 1);
-        if (in.alpha) lft = al * lft + (1.f - al) * __ldg(in.b[part] + off - 1);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < CIN; ++c) {
+#pragma unroll
+    for (int ky = 0; ky < 4; ++ky) {
+      float2 t = f.v[c][ky];
+      float le = f.l[c][ky], re = f.r[c][ky];
+      if (interp) {
+        t.x = al * t.x + be * u[c][ky].x;
+        t.y = al * t.y + be * u[c][ky].y;
+        le = al * le + be * lb[c][ky];
+        re = al * re + be * rb[c][ky];
+        f.v[c][ky] = t;
       }
-      if (ox == Wo - 1) rgt = 0.f;
-      else if (lane == 31 && row_ok) {
-        rgt = __ldg(in.a[part] + off + 2);
-        if (in.alpha) rgt = al * rgt + (1.f - al) * __ldg(in.b[part] + off + 2);
-      }
-      f.l[c][ky] = row_ok ? lft : 0.f;
-      f.r[c][ky] = row_ok ? rgt : 0.f;
+      // halo columns come from the neighbouring lanes (same image row) except at warp / image-row edges
+      const float lft = __shfl_up_sync(0xffffffffu, t.y, 1);
+      const float rgt = __shfl_down_sync(0xffffffffu, t.x, 1);
+      f.l[c][ky] = (lane == 0 || ox == 0) ? le : lft;
+      f.r[c][ky] = (lane == 31 || ox == Wo - 1) ? re : rgt;
     }
   }
 }
@@ -107,8 +119,8 @@ __device__ __forceinline__ void store_field(uint8_t* sA, int row, const Field<CI
 }
 
 // ------------------------------------------------------------------------------------------------ fprop
-template <int CIN>
-__global__ void __launch_bounds__(FT_THREADS) first_fprop_tc_kernel(FirstIn in, const float* __restrict__ w,
+template <int CIN, bool INTERP>
+__global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_kernel(FirstIn in, const float* __restrict__ w,
                                                                     const float* __restrict__ inv_sigma,
                                                                     const float* __restrict__ bias,
                                                                     __nv_bfloat16* __restrict__ y, int N, int H, int W,
@@ -152,7 +164,7 @@ __global__ void __launch_bounds__(FT_THREADS) first_fprop_tc_kernel(FirstIn in, 
 
   Field<CIN> f;
   int tile = blockIdx.x;
-  if (tile < ntiles) gather_field<CIN>(in, (long long)tile * 128 + t, npix, Ho, Wo, H, W, f);
+  if (tile < ntiles) gather_field<CIN, INTERP>(in, (long long)tile * 128 + t, npix, Ho, Wo, H, W, f);
   uint32_t phase = 0;
   for (; tile < ntiles; tile += gridDim.x) {
     store_field<CIN>(sA, t, f, false);
@@ -170,7 +182,7 @@ __global__ void __launch_bounds__(FT_THREADS) first_fprop_tc_kernel(FirstIn in, 
     }
     const long long pix = (long long)tile * 128 + t;
     const int next = tile + gridDim.x;
-    if (next < ntiles) gather_field<CIN>(in, (long long)next * 128 + t, npix, Ho, Wo, H, W, f);  // overlaps the MMA
+    if (next < ntiles) gather_field<CIN, INTERP>(in, (long long)next * 128 + t, npix, Ho, Wo, H, W, f);  // overlaps the MMA
     mbar_wait(mma_bar, phase);
     phase ^= 1;
     tc_fence_after();
@@ -207,28 +219,34 @@ __global__ void __launch_bounds__(FT_THREADS) first_fprop_tc_kernel(FirstIn in, 
 
 // ------------------------------------------------------------------------------------------------ wgrad
 // dw[co][c][ky][kx] += sum_pix gz[pix,co] * x[n,c,2oy+ky-1,2ox+kx-1];  db[co] += sum_pix gz[pix,co].
-template <int CIN>
+template <int CIN, bool INTERP>
 __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, const __grid_constant__ CUtensorMap tmG,
                                                                     float* __restrict__ dw, float* __restrict__ db,
                                                                     int N, int H, int W) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
-  uint8_t* sB = smem + FT_A_BYTES;
-  uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sB + FT_B_BYTES);
-  uint64_t* tma_bar = mma_bar + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tma_bar + 1);
+  uint8_t* sB = smem + FT_A_BYTES;                      // two gz tiles (double-buffered TMA destination)
+  uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sB + 2 * FT_B_BYTES);
+  uint64_t* tma_bar = mma_bar + 1;                      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tma_bar + 2);
 
   const int t = threadIdx.x, warp = t >> 5;
   const int Ho = H / 2, Wo = W / 2;
   const long long npix = (long long)N * Ho * Wo;
   const int ntiles = (int)((npix + 127) / 128);
 
+  int tile = blockIdx.x;
   if (t == 0) {
     tma_prefetch_desc(&tmG);
     mbar_init(mma_bar, 1);
-    mbar_init(tma_bar, 1);
+    mbar_init(&tma_bar[0], 1);
+    mbar_init(&tma_bar[1], 1);
     fence_barrier_init();
+    if (tile < ntiles) {
+      mbar_expect_tx(&tma_bar[0], FT_B_BYTES);
+      tma_load_2d(sB, &tmG, &tma_bar[0], 0, tile * 128);  // rows past npix are zero-filled
+    }
   }
   if (warp == 1) tmem_alloc<64>(tmem_slot);
   tc_fence_before();
@@ -238,38 +256,40 @@ __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, 
   constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);
 
   Field<CIN> f;
-  int tile = blockIdx.x;
-  if (tile < ntiles) gather_field<CIN>(in, (long long)tile * 128 + t, npix, Ho, Wo, H, W, f);
+  if (tile < ntiles) gather_field<CIN, INTERP>(in, (long long)tile * 128 + t, npix, Ho, Wo, H, W, f);
   uint32_t it = 0;
   for (; tile < ntiles; tile += gridDim.x, ++it) {
-    if (it > 0) mbar_wait(mma_bar, (it - 1) & 1);  // the previous tile's MMAs are done reading sA / sB
-    if (t == 0) {
-      mbar_expect_tx(tma_bar, FT_B_BYTES);
-      tma_load_2d(sB, &tmG, tma_bar, 0, tile * 128);  // rows past npix are zero-filled
+    if (it > 0) mbar_wait(mma_bar, (it - 1) & 1);  // the previous tile's MMAs are done reading sA and sB[(it-1)&1]
+    const int next = tile + gridDim.x;
+    if (t == 0 && next < ntiles) {
+      mbar_expect_tx(&tma_bar[(it + 1) & 1], FT_B_BYTES);
+      tma_load_2d(sB + ((it + 1) & 1) * FT_B_BYTES, &tmG, &tma_bar[(it + 1) & 1], 0, next * 128);
     }
     store_field<CIN>(sA, t, f, (long long)tile * 128 + t < npix);
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
     if (t == 0) {
-      mbar_wait(tma_bar, it & 1);
+      mbar_wait(&tma_bar[it & 1], (it >> 1) & 1);
       tc_fence_after();
-      const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+      const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB + (it & 1) * FT_B_BYTES);
 #pragma unroll
       for (int k = 0; k < 8; ++k)  // 16 pixels of the reduction per MMA
         umma_bf16(tmem_base, umma_desc_sw128(a0 + k * 2048, 16384, 1024), umma_desc_sw128(b0 + k * 2048, 16384, 1024),
                   idesc, (uint32_t)((it | (uint32_t)k) != 0));
       umma_commit(mma_bar);
     }
-    const int next = tile + gridDim.x;
-    if (next < ntiles) gather_field<CIN>(in, (long long)next * 128 + t, npix, Ho, Wo, H, W, f);
+    if (next < ntiles) gather_field<CIN, INTERP>(in, (long long)next * 128 + t, npix, Ho, Wo, H, W, f);
   }
   if (it > 0) {
     mbar_wait(mma_bar, (it - 1) & 1);
     tc_fence_after();
     const int tap = t >> 3, c = t & 7;
+    // CTAs finish together: rotate the column order per CTA so concurrent flushes hit different addresses
+    const int rot = (blockIdx.x * 16) & 63;
 #pragma unroll 1
-    for (int c0 = 0; c0 < 64; c0 += 16) {
+    for (int cc = 0; cc < 64; cc += 16) {
+      const int c0 = (cc + rot) & 63;
       uint32_t v[16];
       tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + c0, v);
       tmem_ld_wait();
@@ -311,28 +331,50 @@ static int first_check(const float* a0, const float* b0, const float* alpha, int
   return B2C_OK;
 }
 
+template <int CIN, bool INTERP>
+static int launch_first_fprop(const FirstIn& in, const float* w, const float* inv_sigma, const float* bias, void* y,
+                              int N, int H, int W, float slope, unsigned blocks, cudaStream_t st) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    int rc = first_attr(first_fprop_tc_kernel<CIN, INTERP>);
+    if (rc) return rc;
+    attr_done = true;
+  }
+  first_fprop_tc_kernel<CIN, INTERP><<<blocks, FT_THREADS, FT_SMEM_FPROP, st>>>(in, w, inv_sigma, bias, (__nv_bfloat16*)y, N,
+                                                                          H, W, slope);
+  return b2c_check_launch("first_fprop");
+}
+
+template <int CIN, bool INTERP>
+static int launch_first_wgrad(const FirstIn& in, const CUtensorMap& tmG, float* dw, float* db, int N, int H, int W,
+                              unsigned blocks, cudaStream_t st) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    int rc = first_attr(first_wgrad_tc_kernel<CIN, INTERP>);
+    if (rc) return rc;
+    attr_done = true;
+  }
+  first_wgrad_tc_kernel<CIN, INTERP><<<blocks, FT_THREADS, FT_SMEM, st>>>(in, tmG, dw, db, N, H, W);
+  return b2c_check_launch("first_wgrad");
+}
+
 // a0/a1: (N,3,H,W) fp32 NCHW halves (a1 null => Cin=3).  b0/b1/alpha: optional interpolation (all or none).
 extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                                const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
                                float slope, void* stream) {
   int rc = first_check(a0, b0, alpha, H, W);
   if (rc) return rc;
-  static bool attr_done = false;
-  if (!attr_done) {
-    if ((rc = first_attr(first_fprop_tc_kernel<6>)) || (rc = first_attr(first_fprop_tc_kernel<3>))) return rc;
-    attr_done = true;
-  }
   FirstIn in = make_in(a0, a1, b0, b1, alpha);
   const long long npix = (long long)N * (H / 2) * (W / 2);
   long long blocks = (npix + 127) / 128;
   if (blocks > 148 * 4) blocks = 148 * 4;
-  if (a1)
-    first_fprop_tc_kernel<6><<<(unsigned)blocks, FT_THREADS, FT_SMEM, (cudaStream_t)stream>>>(
-        in, w, inv_sigma, bias, (__nv_bfloat16*)y, N, H, W, slope);
-  else
-    first_fprop_tc_kernel<3><<<(unsigned)blocks, FT_THREADS, FT_SMEM, (cudaStream_t)stream>>>(
-        in, w, inv_sigma, bias, (__nv_bfloat16*)y, N, H, W, slope);
-  return b2c_check_launch("first_fprop");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (a1) {
+    if (alpha) return launch_first_fprop<6, true>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
+    return launch_first_fprop<6, false>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
+  }
+  if (alpha) return launch_first_fprop<3, true>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
+  return launch_first_fprop<3, false>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
 }
 
 // dw: fp32 [64][Cin][4][4], db: fp32 [64] or null; both are ACCUMULATED into (caller zeroes).  gz: dense NHWC bf16.
@@ -340,11 +382,6 @@ extern "C" int b2c_first_wgrad(const float* a0, const float* a1, const float* b0
                                const void* gz, float* dw, float* db, int N, int H, int W, void* stream) {
   int rc = first_check(a0, b0, alpha, H, W);
   if (rc) return rc;
-  static bool attr_done = false;
-  if (!attr_done) {
-    if ((rc = first_attr(first_wgrad_tc_kernel<6>)) || (rc = first_attr(first_wgrad_tc_kernel<3>))) return rc;
-    attr_done = true;
-  }
   FirstIn in = make_in(a0, a1, b0, b1, alpha);
   const long long npix = (long long)N * (H / 2) * (W / 2);
   CUtensorMap tmG;
@@ -357,9 +394,11 @@ extern "C" int b2c_first_wgrad(const float* a0, const float* a1, const float* b0
   }
   long long blocks = (npix + 127) / 128;
   if (blocks > 148 * 4) blocks = 148 * 4;
-  if (a1)
-    first_wgrad_tc_kernel<6><<<(unsigned)blocks, FT_THREADS, FT_SMEM, (cudaStream_t)stream>>>(in, tmG, dw, db, N, H, W);
-  else
-    first_wgrad_tc_kernel<3><<<(unsigned)blocks, FT_THREADS, FT_SMEM, (cudaStream_t)stream>>>(in, tmG, dw, db, N, H, W);
-  return b2c_check_launch("first_wgrad");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (a1) {
+    if (alpha) return launch_first_wgrad<6, true>(in, tmG, dw, db, N, H, W, (unsigned)blocks, st);
+    return launch_first_wgrad<6, false>(in, tmG, dw, db, N, H, W, (unsigned)blocks, st);
+  }
+  if (alpha) return launch_first_wgrad<3, true>(in, tmG, dw, db, N, H, W, (unsigned)blocks, st);
+  return launch_first_wgrad<3, false>(in, tmG, dw, db, N, H, W, (unsigned)blocks, st);
 }

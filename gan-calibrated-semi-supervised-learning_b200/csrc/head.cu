@@ -5,42 +5,67 @@
 
 using namespace b2c;
 
-// out[n,oy,ox] = sum_{ky,kx,c} a[n,oy+ky-1,ox+kx-1,c] * w[c][ky][kx]
+// Each input pixel is read ONCE: a warp owns a pixel, computes its 16 per-tap dot products
+// P[t] = a[n,iy,ix,:] . w[:,t] and scatters them to the (up to 16) score pixels they belong to,
+// out[n,iy-ky+1,ix-kx+1] += P[ky*4+kx].  `out` must be zeroed by the caller (the C entry point does it).
 __global__ void __launch_bounds__(256) head_fprop_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ w,
                                                          float* __restrict__ out, int N, int h, int C) {
-  extern __shared__ float w_s[];  // [16][C]
+  extern __shared__ float w_s[];  // [16 taps][C]
   for (int i = threadIdx.x; i < 16 * C; i += blockDim.x) {
     const int c = i / 16, t = i % 16;
     w_s[t * C + c] = w[i];
   }
   __syncthreads();
   const int ho = h - 1;
-  const long long npix = (long long)N * ho * ho;
+  const long long npix = (long long)N * h * h;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
   for (long long pix = (long long)blockIdx.x * wpb + warp; pix < npix; pix += (long long)gridDim.x * wpb) {
-    const int ox = (int)(pix % ho), oy = (int)((pix / ho) % ho), n = (int)(pix / ((long long)ho * ho));
-    float acc = 0.f;
+    const int ix = (int)(pix % h), iy = (int)((pix / h) % h), n = (int)(pix / ((long long)h * h));
+    float acc[16];
 #pragma unroll
-    for (int t = 0; t < 16; ++t) {
-      const int iy = oy + (t >> 2) - 1, ix = ox + (t & 3) - 1;
-      if (iy < 0 || iy >= h || ix < 0 || ix >= h) continue;
-      const __nv_bfloat16* row = a + (((long long)n * h + iy) * h + ix) * C;
-      for (int c = lane * 8; c < C; c += 256) {
-        const uint4 u = __ldg(reinterpret_cast<const uint4*>(row + c));
-        const float* ws = w_s + t * C + c;
-        const float2 f0 = unpack_bf16(u.x), f1 = unpack_bf16(u.y), f2 = unpack_bf16(u.z), f3 = unpack_bf16(u.w);
-        acc += f0.x * ws[0] + f0.y * ws[1] + f1.x * ws[2] + f1.y * ws[3] + f2.x * ws[4] + f2.y * ws[5] + f3.x * ws[6] +
-               f3.y * ws[7];
+    for (int t = 0; t < 16; ++t) acc[t] = 0.f;
+    const __nv_bfloat16* row = a + pix * C;
+    for (int c = lane * 8; c < C; c += 256) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(row + c));
+      const float2 f0 = unpack_bf16(u.x), f1 = unpack_bf16(u.y), f2 = unpack_bf16(u.z), f3 = unpack_bf16(u.w);
+#pragma unroll
+      for (int t = 0; t < 16; ++t) {
+        const float4 w0 = *reinterpret_cast<const float4*>(w_s + t * C + c);
+        const float4 w1 = *reinterpret_cast<const float4*>(w_s + t * C + c + 4);
+        acc[t] += f0.x * w0.x + f0.y * w0.y + f1.x * w0.z + f1.y * w0.w + f2.x * w1.x + f2.y * w1.y + f3.x * w1.z + f3.y * w1.w;
       }
     }
-    acc = warp_sum(acc);
-    if (lane == 0) out[pix] = acc;
+    // 16 values x 32 lanes -> lane t (< 16) ends up with the full sum of tap t (halving butterfly)
+#pragma unroll
+    for (int half = 8, off = 16; half >= 1; half >>= 1, off >>= 1) {
+      const bool upper = (lane & off) != 0;
+#pragma unroll
+      for (int j = 0; j < half; ++j) {
+        const float send = upper ? acc[j] : acc[j + half];
+        const float keep = upper ? acc[j + half] : acc[j];
+        acc[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+      }
+    }
+    float v = acc[0] + __shfl_xor_sync(0xffffffffu, acc[0], 1);
+    // after the butterfly lane L holds tap index built from its bits: bit4->+8, bit3->+4, bit2->+2, bit1->+1
+    const int t = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+    if ((lane & 1) == 0) {
+      const int oy = iy - (t >> 2) + 1, ox = ix - (t & 3) + 1;
+      if (oy >= 0 && oy < ho && ox >= 0 && ox < ho) atomicAdd(out + ((long long)n * ho + oy) * ho + ox, v);
+    }
   }
 }
 
-// ga[n,iy,ix,c] = sum_{ky,kx} gy[n,iy-ky+1,ix-kx+1] * w[c][ky][kx]
+// ga[n,iy,ix,c] = sum_{ky,kx} gy[n,iy-ky+1,ix-kx+1] * w[c][ky][kx].  64 threads x 8 channels per pixel; the weights
+// sit in shared memory as [tap][C] so a thread reads its 8 channels of a tap with two 16-byte loads.
 __global__ void __launch_bounds__(256) head_dgrad_kernel(const float* __restrict__ gy, const float* __restrict__ w,
                                                          __nv_bfloat16* __restrict__ ga, int N, int h, int C) {
+  extern __shared__ float w_s[];  // [16 taps][C]
+  for (int i = threadIdx.x; i < 16 * C; i += blockDim.x) {
+    const int c = i / 16, t = i % 16;
+    w_s[t * C + c] = w[i];
+  }
+  __syncthreads();
   const int ho = h - 1;
   const int cvecs = C / 8;
   const long long total = (long long)N * h * h * cvecs;
@@ -54,8 +79,10 @@ __global__ void __launch_bounds__(256) head_dgrad_kernel(const float* __restrict
       const int oy = iy - (t >> 2) + 1, ox = ix - (t & 3) + 1;
       if (oy < 0 || oy >= ho || ox < 0 || ox >= ho) continue;
       const float g = __ldg(gy + ((long long)n * ho + oy) * ho + ox);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += g * __ldg(w + (long long)(cv * 8 + e) * 16 + t);
+      const float4 w0 = *reinterpret_cast<const float4*>(w_s + t * C + cv * 8);
+      const float4 w1 = *reinterpret_cast<const float4*>(w_s + t * C + cv * 8 + 4);
+      acc[0] += g * w0.x; acc[1] += g * w0.y; acc[2] += g * w0.z; acc[3] += g * w0.w;
+      acc[4] += g * w1.x; acc[5] += g * w1.y; acc[6] += g * w1.z; acc[7] += g * w1.w;
     }
     uint4 o = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]), pack_bf16(acc[4], acc[5]),
                          pack_bf16(acc[6], acc[7]));
@@ -63,29 +90,52 @@ __global__ void __launch_bounds__(256) head_dgrad_kernel(const float* __restrict
   }
 }
 
-// dw[c][ky][kx] += sum_{n,oy,ox} gy[n,oy,ox] * a[n,oy+ky-1,ox+kx-1,c].  grid = (16 taps, image splits).
+// dw[c][ky][kx] += sum_{n,iy,ix} a[n,iy,ix,c] * gy[n,iy-ky+1,ix-kx+1].  Each input pixel is read once: a thread owns
+// two channels and keeps all 16 taps in registers over its block's pixel range (8 pixels per batch so that the loads
+// of a batch are in flight together); one atomic flush per block.  Requires C == 2 * blockDim.x.
 __global__ void __launch_bounds__(256) head_wgrad_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ gy,
                                                          float* __restrict__ dw, int N, int h, int C) {
-  const int t = blockIdx.x, ky = t >> 2, kx = t & 3;
+  constexpr int PB = 8;
   const int ho = h - 1;
-  const int n_begin = (int)((long long)N * blockIdx.y / gridDim.y), n_end = (int)((long long)N * (blockIdx.y + 1) / gridDim.y);
-  for (int c = threadIdx.x * 2; c < C; c += 512) {
-    float a0 = 0.f, a1 = 0.f;
-    for (int n = n_begin; n < n_end; ++n)
-      for (int oy = 0; oy < ho; ++oy) {
-        const int iy = oy + ky - 1;
-        if (iy < 0 || iy >= h) continue;
-        for (int ox = 0; ox < ho; ++ox) {
-          const int ix = ox + kx - 1;
-          if (ix < 0 || ix >= h) continue;
-          const float g = __ldg(gy + ((long long)n * ho + oy) * ho + ox);
-          const float2 f = unpack_bf16(__ldg(reinterpret_cast<const uint32_t*>(a + (((long long)n * h + iy) * h + ix) * C + c)));
-          a0 += g * f.x;
-          a1 += g * f.y;
-        }
+  const long long npix = (long long)N * h * h;
+  const long long p_begin = npix * blockIdx.x / gridDim.x, p_end = npix * (blockIdx.x + 1) / gridDim.x;
+  __shared__ float g_s[2][PB][16];
+  const int c = threadIdx.x * 2;
+  float acc0[16], acc1[16];
+#pragma unroll
+  for (int t = 0; t < 16; ++t) acc0[t] = acc1[t] = 0.f;
+  int buf = 0;
+  for (long long p0 = p_begin; p0 < p_end; p0 += PB, buf ^= 1) {
+    if (threadIdx.x < PB * 16) {
+      const long long pix = p0 + (threadIdx.x >> 4);
+      float g = 0.f;
+      if (pix < p_end) {
+        const int ix = (int)(pix % h), iy = (int)((pix / h) % h), n = (int)(pix / ((long long)h * h));
+        const int t = threadIdx.x & 15, oy = iy - (t >> 2) + 1, ox = ix - (t & 3) + 1;
+        if (oy >= 0 && oy < ho && ox >= 0 && ox < ho) g = __ldg(gy + ((long long)n * ho + oy) * ho + ox);
       }
-    atomicAdd(dw + (long long)c * 16 + t, a0);
-    atomicAdd(dw + (long long)(c + 1) * 16 + t, a1);
+      g_s[buf][threadIdx.x >> 4][threadIdx.x & 15] = g;
+    }
+    uint32_t u[PB];
+#pragma unroll
+    for (int j = 0; j < PB; ++j)
+      u[j] = (p0 + j < p_end) ? __ldg(reinterpret_cast<const uint32_t*>(a + (p0 + j) * C + c)) : 0u;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < PB; ++j) {
+      const float2 f = unpack_bf16(u[j]);
+#pragma unroll
+      for (int t = 0; t < 16; ++t) {
+        const float g = g_s[buf][j][t];
+        acc0[t] += g * f.x;
+        acc1[t] += g * f.y;
+      }
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < 16; ++t) {
+    atomicAdd(dw + (long long)c * 16 + t, acc0[t]);
+    atomicAdd(dw + (long long)(c + 1) * 16 + t, acc1[t]);
   }
 }
 
@@ -98,26 +148,38 @@ extern "C" int b2c_head_fprop(const void* a, const float* w, float* out, int N, 
     attr_done = true;
   }
   B2C_REQUIRE(smem <= 64 * 1024, "head_fprop: C=%d too large", C);
-  const long long npix = (long long)N * (h - 1) * (h - 1);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(out, 0, sizeof(float) * (size_t)N * (h - 1) * (h - 1), st);
+  if (e != cudaSuccess) { b2c_set_error("head_fprop memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+  const long long npix = (long long)N * h * h;
   long long blocks = (npix + 7) / 8;
-  if (blocks > 148 * 2) blocks = 148 * 2;
-  head_fprop_kernel<<<(unsigned)blocks, 256, smem, (cudaStream_t)stream>>>((const __nv_bfloat16*)a, w, out, N, h, C);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  head_fprop_kernel<<<(unsigned)blocks, 256, smem, st>>>((const __nv_bfloat16*)a, w, out, N, h, C);
   return b2c_check_launch("head_fprop");
 }
 
 extern "C" int b2c_head_dgrad(const float* gy, const float* w, void* ga, int N, int h, int C, void* stream) {
-  B2C_REQUIRE(C % 8 == 0, "head_dgrad: C=%d", C);
+  B2C_REQUIRE(C % 8 == 0 && (size_t)16 * C * sizeof(float) <= 64 * 1024, "head_dgrad: C=%d", C);
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaFuncSetAttribute(head_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    attr_done = true;
+  }
   const long long total = (long long)N * h * h * (C / 8);
   long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  head_dgrad_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(gy, w, (__nv_bfloat16*)ga, N, h, C);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  head_dgrad_kernel<<<(unsigned)blocks, 256, (size_t)16 * C * sizeof(float), (cudaStream_t)stream>>>(
+      gy, w, (__nv_bfloat16*)ga, N, h, C);
   return b2c_check_launch("head_dgrad");
 }
 
 // dw fp32 [C][4][4] is ACCUMULATED into (caller zeroes).
 extern "C" int b2c_head_wgrad(const void* a, const float* gy, float* dw, int N, int h, int C, void* stream) {
-  B2C_REQUIRE(C % 2 == 0, "head_wgrad: C=%d", C);
-  int splits = N < 16 ? N : 16;
-  head_wgrad_kernel<<<dim3(16, splits), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)a, gy, dw, N, h, C);
+  B2C_REQUIRE(C == 256 || C == 512, "head_wgrad: C=%d must be 256 or 512", C);
+  const long long npix = (long long)N * h * h;
+  long long blocks = npix / 32;
+  if (blocks > 148 * 2) blocks = 148 * 2;
+  if (blocks < 1) blocks = 1;
+  head_wgrad_kernel<<<(unsigned)blocks, C / 2, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)a, gy, dw, N, h, C);
   return b2c_check_launch("head_wgrad");
 }
