@@ -59,127 +59,189 @@ __device__ __forceinline__ void load_stats8(const float* zs, int n, int C, int c
   }
 }
 
-// Per-element quantities shared by reduce and apply.
+// Thread mapping shared by the reduce and apply kernels: block = 256 threads = (C/8 channel vectors) x (rows pixels);
+// grid = (splits over the plane, N images).  A thread keeps ONE channel vector for the whole kernel, so the per-(n,c)
+// statistics live in registers, and it walks its pixels U at a time with every load of the batch issued up front.
+constexpr int NORM_U = 4;
+template <int MODE> struct UF { static constexpr int v = MODE == 3 ? 2 : NORM_U; };  // batch depth (BWD2 is register-heavy)
+
 struct Elem { float xh[8], gn[8], hh[8], dact[8]; };
 
+// Raw loads of one pixel's channel vector (issued together for the U pixels of a batch).
+struct Raw { uint4 z, g, h; uint2 m; };
+
 template <int MODE>
-__device__ __forceinline__ void elem_load(const NormArgs& a, int n, long long pix, int c0, const float (&mean)[8],
-                                          const float (&rstd)[8], const float (&gv)[8], Elem& e) {
+__device__ __forceinline__ void raw_load(const NormArgs& a, long long pix, int c0, bool ok, Raw& r) {
+  r.z = r.g = r.h = make_uint4(0, 0, 0, 0);
+  r.m = make_uint2(0x01010101u, 0x01010101u);
+  if (!ok) return;
+  r.z = __ldg(reinterpret_cast<const uint4*>(a.z + pix * a.ldz + c0));
+  if (MODE == M_FWD || MODE == M_BWD || MODE == M_BWD2)
+    if (a.mask) r.m = __ldg(reinterpret_cast<const uint2*>(a.mask + pix * a.C + c0));
+  if (MODE == M_BWD || MODE == M_BWD2)
+    if (a.g) r.g = __ldg(reinterpret_cast<const uint4*>(a.g + pix * a.ldg + c0));
+  if (MODE == M_BWD2) r.h = __ldg(reinterpret_cast<const uint4*>(a.h + pix * a.ldh + c0));
+}
+__device__ __forceinline__ void cvt8(const uint4& u, float (&f)[8]) {
+  float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y), c = unpack_bf16(u.z), d = unpack_bf16(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ void cvt_mask8(const uint2& u, float (&k)[8]) {
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    k[e] = ((u.x >> (8 * e)) & 0xff) ? 1.f : 0.f;
+    k[4 + e] = ((u.y >> (8 * e)) & 0xff) ? 1.f : 0.f;
+  }
+}
+template <int MODE>
+__device__ __forceinline__ void elem_make(const NormArgs& a, const Raw& r, const float (&mean)[8], const float (&rstd)[8],
+                                          const float (&gv)[8], float kscale, Elem& e) {
   float z[8];
-  load8(a.z + pix * a.ldz + c0, z);
+  cvt8(r.z, z);
 #pragma unroll
   for (int i = 0; i < 8; ++i) e.xh[i] = (z[i] - mean[i]) * rstd[i];
   if (MODE == M_BWD || MODE == M_BWD2) {
     float k[8], g[8];
-    load_mask8(a.mask, pix * a.C + c0, k);
-    if (a.g) load8(a.g + pix * a.ldg + c0, g);
+    cvt_mask8(r.m, k);
+    if (a.g) cvt8(r.g, g);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      e.dact[i] = (e.xh[i] > 0.f ? 1.f : a.slope) * k[i];
+      e.dact[i] = (e.xh[i] > 0.f ? 1.f : a.slope) * k[i] * kscale;
       e.gn[i] = (a.g ? g[i] : gv[i]) * e.dact[i];
     }
   }
-  if (MODE == M_BWD2) load8(a.h + pix * a.ldh + c0, e.hh);
+  if (MODE == M_BWD2) cvt8(r.h, e.hh);
 }
 
 template <int MODE>
 __global__ void __launch_bounds__(256) plane_reduce_kernel(NormArgs a) {
   constexpr int ns = NS<MODE>::v;
-  extern __shared__ float red[];  // [C][ns]
+  extern __shared__ float red[];  // [ns][rows][C] = ns * 2048 floats
   const int n = blockIdx.y, cvecs = a.C / 8, rows = 256 / cvecs;
   const int cv = threadIdx.x % cvecs, prow = threadIdx.x / cvecs, c0 = cv * 8;
-  for (int i = threadIdx.x; i < a.C * ns; i += 256) red[i] = 0.f;
-  __syncthreads();
   float mean[8], rstd[8], gv[8], acc[ns][8];
 #pragma unroll
   for (int s = 0; s < ns; ++s)
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[s][i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { mean[i] = 0.f; rstd[i] = 1.f; gv[i] = 0.f; }
   if (MODE != M_FWD) load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
   if ((MODE == M_BWD || MODE == M_BWD2) && !a.g) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) gv[i] = __ldg(a.gvec + (long long)n * a.C + c0 + i);
   }
+  const float kscale = a.mask ? 2.f : 1.f;
   const int p_begin = (int)((long long)a.HW * blockIdx.x / gridDim.x), p_end = (int)((long long)a.HW * (blockIdx.x + 1) / gridDim.x);
-  for (int p = p_begin + prow; p < p_end; p += rows) {
-    const long long pix = (long long)n * a.HW + p;
-    if (MODE == M_FWD) {
-      float z[8];
-      load8(a.z + pix * a.ldz + c0, z);
+  constexpr int U = UF<MODE>::v;
+  for (int p = p_begin + prow; p < p_end; p += rows * U) {
+    Raw r[U];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) { acc[0][i] += z[i]; acc[1][i] += z[i] * z[i]; }
-    } else {
-      Elem e;
-      elem_load<MODE>(a, n, pix, c0, mean, rstd, gv, e);
+    for (int u = 0; u < U; ++u)
+      raw_load<(MODE == M_FWD || MODE == M_POOL) ? M_POOL : MODE>(a, (long long)n * a.HW + p + u * rows, c0, p + u * rows < p_end, r[u]);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        if (MODE == M_POOL) acc[0][i] += e.xh[i] > 0.f ? e.xh[i] : e.xh[i] * a.slope;
-        if (MODE == M_BWD) { acc[0][i] += e.gn[i]; acc[1][i] += e.gn[i] * e.xh[i]; }
-        if (MODE == M_BWD2) {
-          acc[0][i] += e.hh[i]; acc[1][i] += e.hh[i] * e.xh[i]; acc[2][i] += e.gn[i];
-          acc[3][i] += e.gn[i] * e.xh[i]; acc[4 % ns][i] += e.hh[i] * e.gn[i];
+    for (int u = 0; u < U; ++u) {
+      if (p + u * rows >= p_end) continue;
+      if (MODE == M_FWD) {
+        float z[8];
+        cvt8(r[u].z, z);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { acc[0][i] += z[i]; acc[1][i] += z[i] * z[i]; }
+      } else {
+        Elem e;
+        elem_make<MODE>(a, r[u], mean, rstd, gv, kscale, e);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (MODE == M_POOL) acc[0][i] += e.xh[i] > 0.f ? e.xh[i] : e.xh[i] * a.slope;
+          if (MODE == M_BWD) { acc[0][i] += e.gn[i]; acc[1][i] += e.gn[i] * e.xh[i]; }
+          if (MODE == M_BWD2) {
+            acc[0][i] += e.hh[i]; acc[1][i] += e.hh[i] * e.xh[i]; acc[2][i] += e.gn[i];
+            acc[3][i] += e.gn[i] * e.xh[i]; acc[4 % ns][i] += e.hh[i] * e.gn[i];
+          }
         }
       }
     }
   }
+  // block reduction without atomics (shared fp32 atomicAdd is a CAS loop): red[s][prow][C], then one thread per (s, c)
 #pragma unroll
-  for (int s = 0; s < ns; ++s)
-#pragma unroll
-    for (int i = 0; i < 8; ++i) atomicAdd(&red[(c0 + i) * ns + s], acc[s][i]);
+  for (int s = 0; s < ns; ++s) {
+    float4* d = reinterpret_cast<float4*>(red + ((long long)s * rows + prow) * a.C + c0);
+    d[0] = make_float4(acc[s][0], acc[s][1], acc[s][2], acc[s][3]);
+    d[1] = make_float4(acc[s][4], acc[s][5], acc[s][6], acc[s][7]);
+  }
   __syncthreads();
-  for (int i = threadIdx.x; i < a.C * ns; i += 256) atomicAdd(a.sums + (long long)n * a.C * ns + i, red[i]);
+  for (int i = threadIdx.x; i < a.C * ns; i += 256) {
+    const int s = i / a.C, c = i % a.C;
+    float t = 0.f;
+    for (int r = 0; r < rows; ++r) t += red[((long long)s * rows + r) * a.C + c];
+    atomicAdd(a.sums + ((long long)n * a.C + c) * ns + s, t);
+  }
 }
 
-// Elementwise applies.  One thread = 8 channels of one pixel.
 template <int MODE>
 __global__ void __launch_bounds__(256) plane_apply_kernel(NormArgs a) {
   constexpr int ns = NS<MODE>::v;
-  const int cvecs = a.C / 8;
-  const long long total = (long long)a.N * a.HW * cvecs;
+  const int n = blockIdx.y, cvecs = a.C / 8, rows = 256 / cvecs;
+  const int cv = threadIdx.x % cvecs, prow = threadIdx.x / cvecs, c0 = cv * 8;
   const float inv = 1.f / (float)a.HW;
-  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
-    const int cv = (int)(i % cvecs), c0 = cv * 8;
-    const long long pix = i / cvecs;
-    const int n = (int)(pix / a.HW);
-    float mean[8], rstd[8], gv[8];
-    load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
-    if (MODE == M_FWD) {
-      float z[8], k[8], o[8];
-      load8(a.z + pix * a.ldz + c0, z);
-      load_mask8(a.mask, pix * a.C + c0, k);
+  float mean[8], rstd[8], gv[8], sm[ns][8];
+  load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float xh = (z[e] - mean[e]) * rstd[e];
-        o[e] = (xh > 0.f ? xh : xh * a.slope) * k[e];
-      }
-      store8(a.o0 + pix * a.ldo0 + c0, o);
-      if (a.o1) store8(a.o1 + pix * a.ldo1 + c0, o);
-    } else {
-      if (!a.g) {
+  for (int i = 0; i < 8; ++i) gv[i] = 0.f;
+  if (MODE != M_FWD) {
+    if (!a.g) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) gv[e] = __ldg(a.gvec + (long long)n * a.C + c0 + e);
-      }
-      Elem el;
-      elem_load<MODE>(a, n, pix, c0, mean, rstd, gv, el);
-      const float* s = a.sums + ((long long)n * a.C + c0) * ns;
-      if (MODE == M_BWD) {
-        float o[8];
+      for (int i = 0; i < 8; ++i) gv[i] = __ldg(a.gvec + (long long)n * a.C + c0 + i);
+    }
+    const float* s = a.sums + ((long long)n * a.C + c0) * ns;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o[e] = (el.gn[e] - s[e * ns] * inv - el.xh[e] * s[e * ns + 1] * inv) * rstd[e];
-        store8(a.o0 + pix * a.ldo0 + c0, o);
-      } else {  // M_BWD2: o0 = grad wrt g (the first-backward input), o1 = grad wrt z
-        float og[8], oz[8];
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int k = 0; k < ns; ++k) sm[k][i] = __ldg(s + i * ns + k) * inv;
+  }
+  const float kscale = a.mask ? 2.f : 1.f;
+  const int p_begin = (int)((long long)a.HW * blockIdx.x / gridDim.x), p_end = (int)((long long)a.HW * (blockIdx.x + 1) / gridDim.x);
+  constexpr int U = UF<MODE>::v;
+  for (int p = p_begin + prow; p < p_end; p += rows * U) {
+    Raw r[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) raw_load<MODE>(a, (long long)n * a.HW + p + u * rows, c0, p + u * rows < p_end, r[u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (p + u * rows >= p_end) continue;
+      const long long pix = (long long)n * a.HW + p + u * rows;
+      if (MODE == M_FWD) {
+        float z[8], k[8], o[8];
+        cvt8(r[u].z, z);
+        cvt_mask8(r[u].m, k);
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const float mh = s[e * ns] * inv, ma = s[e * ns + 1] * inv, mg = s[e * ns + 2] * inv, mc = s[e * ns + 3] * inv,
-                      mhg = s[e * ns + 4 % ns] * inv;
-          const float q = mhg - mh * mg - ma * mc;
-          const float Ph = el.hh[e] - mh - el.xh[e] * ma, Pg = el.gn[e] - mg - el.xh[e] * mc;
-          og[e] = Ph * rstd[e] * el.dact[e];
-          oz[e] = -(q * el.xh[e] + mc * Ph + ma * Pg) * rstd[e] * rstd[e];
+          const float xh = (z[e] - mean[e]) * rstd[e];
+          o[e] = (xh > 0.f ? xh : xh * a.slope) * k[e] * kscale;
         }
-        store8(a.o0 + pix * a.ldo0 + c0, og);
-        store8(a.o1 + pix * a.ldo1 + c0, oz);
+        store8(a.o0 + pix * a.ldo0 + c0, o);
+        if (a.o1) store8(a.o1 + pix * a.ldo1 + c0, o);
+      } else {
+        Elem el;
+        elem_make<MODE>(a, r[u], mean, rstd, gv, kscale, el);
+        if (MODE == M_BWD) {
+          float o[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) o[e] = (el.gn[e] - sm[0][e] - el.xh[e] * sm[1 % ns][e]) * rstd[e];
+          store8(a.o0 + pix * a.ldo0 + c0, o);
+        } else {  // M_BWD2: o0 = grad wrt g (the first-backward input), o1 = grad wrt z
+          float og[8], oz[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float mh = sm[0][e], ma = sm[1 % ns][e], mg = sm[2 % ns][e], mc = sm[3 % ns][e], mhg = sm[4 % ns][e];
+            const float q = mhg - mh * mg - ma * mc;
+            const float Ph = el.hh[e] - mh - el.xh[e] * ma, Pg = el.gn[e] - mg - el.xh[e] * mc;
+            og[e] = Ph * rstd[e] * el.dact[e];
+            oz[e] = -(q * el.xh[e] + mc * Ph + ma * Pg) * rstd[e] * rstd[e];
+          }
+          store8(a.o0 + pix * a.ldo0 + c0, og);
+          store8(a.o1 + pix * a.ldo1 + c0, oz);
+        }
       }
     }
   }
@@ -187,14 +249,15 @@ __global__ void __launch_bounds__(256) plane_apply_kernel(NormArgs a) {
 
 // ------------------------------------------------------------------------------------------------ host side
 static int norm_check(const NormArgs& a, const char* who) {
-  B2C_REQUIRE(a.C >= 8 && a.C <= 2048 && (a.C & (a.C - 1)) == 0, "%s: C=%d must be a power of two in [8,2048]", who, a.C);
+  B2C_REQUIRE(a.C >= 64 && a.C <= 2048 && (a.C & (a.C - 1)) == 0, "%s: C=%d must be a power of two in [64,2048]", who, a.C);
   B2C_REQUIRE(a.ldz % 8 == 0, "%s: ldz=%lld must be a multiple of 8", who, a.ldz);
   return B2C_OK;
 }
-static int reduce_splits(int N, int HW, int C) {
+// Splits of a plane so that the whole grid is ~`target` blocks and every thread still sees >= 2 batches of pixels.
+static int plane_splits(int N, int HW, int C, int target) {
   const int rows = 256 / (C / 8);
-  int s = 592 / (N > 0 ? N : 1);
-  const int cap = HW / (rows * 2);
+  int s = (target + N - 1) / (N > 0 ? N : 1);
+  const int cap = HW / (rows * NORM_U * 2);
   if (s > cap) s = cap;
   return s < 1 ? 1 : s;
 }
@@ -203,16 +266,14 @@ static int launch_reduce(const NormArgs& a, cudaStream_t st) {
   constexpr int ns = NS<MODE>::v;
   cudaError_t e = cudaMemsetAsync(a.sums, 0, sizeof(float) * (size_t)a.N * a.C * ns, st);
   if (e != cudaSuccess) { b2c_set_error("norm memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
-  dim3 grid(reduce_splits(a.N, a.HW, a.C), a.N);
-  plane_reduce_kernel<MODE><<<grid, 256, sizeof(float) * a.C * ns, st>>>(a);
+  dim3 grid(plane_splits(a.N, a.HW, a.C, 148 * 6), a.N);
+  plane_reduce_kernel<MODE><<<grid, 256, sizeof(float) * 2048 * ns, st>>>(a);
   return b2c_check_launch("plane_reduce");
 }
 template <int MODE>
 static int launch_apply(const NormArgs& a, cudaStream_t st) {
-  const long long total = (long long)a.N * a.HW * (a.C / 8);
-  long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  plane_apply_kernel<MODE><<<(unsigned)blocks, 256, 0, st>>>(a);
+  dim3 grid(plane_splits(a.N, a.HW, a.C, 148 * 8), a.N);
+  plane_apply_kernel<MODE><<<grid, 256, 0, st>>>(a);
   return b2c_check_launch("plane_apply");
 }
 static NormArgs base_args(const void* z, long long ldz, const float* zs, int N, int HW, int C, float slope) {

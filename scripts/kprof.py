@@ -63,3 +63,12 @@ for n, recs in timed.items():
         agg[key][0] += 1; agg[key][1] += a.elapsed_time(c); agg[key][2] = nb
 for (n, shp), (cnt, ms, nb) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print(f"{n:22s} {str(shp):22s} x{cnt/K:5.1f}/step {ms/K:7.3f} ms/step  {1e3*ms/cnt:7.1f} us/call  {nb/(ms/cnt)/1e6:7.0f} GB/s")
+
+print("\n-- tensor-core GEMM calls by shape --")
+agg = collections.defaultdict(lambda: [0, 0.0, 0.0])
+for n in bench.GEMM_KERNELS:
+    for a, c, sc in timed.get(n, []):
+        key = (n, sc[-6:] if n == "b2c_wgrad4s2_bf16" else sc[-5:])
+        agg[key][0] += 1; agg[key][1] += a.elapsed_time(c); agg[key][2] = bench.gemm_flops(n, sc)
+for (n, shp), (cnt, ms, fl) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+    print(f"{n:20s} {str(shp):32s} x{cnt/K:5.1f}/step {ms/K:7.3f} ms/step {1e3*ms/cnt:7.1f} us/call {fl/(ms/cnt)/1e9:7.0f} TFLOP/s")
