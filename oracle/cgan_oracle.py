@@ -126,6 +126,35 @@ def _inorm(x):
     return F.instance_norm(x, eps=1e-5)
 
 
+def g_down_block(w, h, norm, mask=None):
+    """UNetDown (cgan/models.py:54-66): conv k4s2p1 -> [IN] -> LeakyReLU(0.2) -> [dropout mask x2]."""
+    h = F.conv2d(h, _r(w) if norm else w, None, 2, 1)
+    if norm:
+        h = _inorm(_r(h))
+    h = F.leaky_relu(h, 0.2)
+    if mask is not None:
+        h = h * mask * 2.0
+    return _r(h)
+
+
+def g_up_block(w, h, skip, mask=None):
+    """UNetUp (cgan/models.py:68-83): convT k4s2p1 -> IN -> ReLU -> [dropout] -> cat((out, skip), 1)."""
+    h = _r(F.conv_transpose2d(h, _r(w), None, 2, 1))
+    h = F.relu(_inorm(h))
+    if mask is not None:
+        h = h * mask * 2.0
+    return torch.cat((_r(h), skip), 1)
+
+
+def g_tail(w_up4, fc_w, fc_b, h, delta_scale, taps=None):
+    """up4 + avg-pool + Linear(64,4) + Tanh + scale (cgan/models.py:112-123,139-141)."""
+    h = F.relu(_inorm(_r(F.conv_transpose2d(h, _r(w_up4), None, 2, 1))))
+    if taps is not None:
+        taps["up4"] = h
+    pooled = h.mean(dim=(2, 3))
+    return torch.tanh(F.linear(pooled, fc_w, fc_b)) * delta_scale
+
+
 def g_forward(g, x, delta_scale: float = 0.3, train: bool = True,
               masks: Optional[Sequence[torch.Tensor]] = None, taps: Optional[dict] = None):
     """masks: three {0,1} tensors for the dropout sites (down4, up1, up2) when train=True."""
@@ -133,32 +162,23 @@ def g_forward(g, x, delta_scale: float = 0.3, train: bool = True,
     h = x
     mi = 0
     for name, _, _, norm, drop in G_DOWN:
-        w = g[name + ".model.0.weight"]
-        h = F.conv2d(h, _r(w) if norm else w, None, 2, 1)
-        if norm:
-            h = _inorm(_r(h))
-        h = F.leaky_relu(h, 0.2)
+        m = None
         if drop and train:
-            h = h * masks[mi] * 2.0; mi += 1
-        h = _r(h)
+            m = masks[mi]; mi += 1
+        h = g_down_block(g[name + ".model.0.weight"], h, norm, m)
         if taps is not None:
             taps[name] = h
         skips.append(h)
     d1, d2, d3, d4 = skips
     h = d4
     for (name, _, _, drop), skip in zip(G_UP, (d3, d2, d1)):
-        h = _r(F.conv_transpose2d(h, _r(g[name + ".model.0.weight"]), None, 2, 1))
-        h = F.relu(_inorm(h))
+        m = None
         if drop and train:
-            h = h * masks[mi] * 2.0; mi += 1
-        h = torch.cat((_r(h), skip), 1)
+            m = masks[mi]; mi += 1
+        h = g_up_block(g[name + ".model.0.weight"], h, skip, m)
         if taps is not None:
             taps[name] = h
-    h = F.relu(_inorm(_r(F.conv_transpose2d(h, _r(g["up4.0.weight"]), None, 2, 1))))
-    if taps is not None:
-        taps["up4"] = h
-    pooled = h.mean(dim=(2, 3))
-    return torch.tanh(F.linear(pooled, g["fc_delta.1.weight"], g["fc_delta.1.bias"])) * delta_scale
+    return g_tail(g["up4.0.weight"], g["fc_delta.1.weight"], g["fc_delta.1.bias"], h, delta_scale, taps)
 
 
 def g_mask_shapes(B: int, S: int):
