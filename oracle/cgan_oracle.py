@@ -128,7 +128,7 @@ def _inorm(x):
 
 def g_down_block(w, h, norm, mask=None):
     """UNetDown (cgan/models.py:54-66): conv k4s2p1 -> [IN] -> LeakyReLU(0.2) -> [dropout mask x2]."""
-    h = F.conv2d(h, _r(w) if norm else w, None, 2, 1)
+    h = F.conv2d(_r(h), _r(w), None, 2, 1)  # every conv (first layer included) feeds bf16 operands to the tensor cores
     if norm:
         h = _inorm(_r(h))
     h = F.leaky_relu(h, 0.2)
@@ -205,7 +205,7 @@ def d_forward(d, pred, other, train: bool = True, taps: Optional[dict] = None):
     h = torch.cat([pred, other], 1)
     for idx, _, _, norm in D_BLOCKS:
         w = sn_weight(d, idx, train) if sn else d[f"model.{idx}.weight"]
-        h = F.conv2d(h, _r(w) if norm else w, d[f"model.{idx}.bias"], 2, 1)
+        h = F.conv2d(_r(h), _r(w), d[f"model.{idx}.bias"], 2, 1)
         if norm:
             h = _inorm(_r(h))
         h = _r(F.leaky_relu(h, 0.2))
