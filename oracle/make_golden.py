@@ -155,6 +155,6 @@ if __name__ == "__main__":
     gold = ROOT / "tests" / "golden"
     gold.mkdir(parents=True, exist_ok=True)
     (gold / "losses.json").write_text(json.dumps(loss_vectors()))
-    for B, S, steps in ((2, 64, 3), (4, 32, 2)):
+    for B, S, steps in ((2, 64, 3), (2, 128, 2)):
         (gold / f"step_B{B}_S{S}.json").write_text(json.dumps(run(B, S, steps)))
         print("wrote", B, S)
