@@ -20,6 +20,25 @@ import torch
 from . import losses, ops
 
 
+def allreduce_mean_(grads, group=None, world_size=None):
+    """In-place average of a list of gradient tensors over the ranks of `group` with ONE collective on a flat bucket
+    (every loss is a batch mean and every per-sample quantity is rank-local, so the average of the
+    per-shard gradients equals the single-GPU gradient on the concatenated batch).  Backend-agnostic (NCCL on the
+    B200s, gloo in the CPU tests)."""
+    import torch.distributed as dist
+    if world_size is None:
+        world_size = dist.get_world_size(group)
+    if world_size <= 1 or not grads:
+        return
+    flat = torch.cat([g.reshape(-1) for g in grads])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    flat.div_(world_size)
+    off = 0
+    for g in grads:
+        g.copy_(flat[off:off + g.numel()].view_as(g))
+        off += g.numel()
+
+
 @dataclass
 class StepOutput:
     scalars: Dict[str, torch.Tensor] = field(default_factory=dict)
@@ -41,17 +60,8 @@ class CGANTrainer:
 
     # ---- data parallel: average gradients over ranks (per-sample losses are batch means) ----
     def _allreduce(self, params):
-        if self.world_size <= 1:
-            return
-        import torch.distributed as dist
-        grads = [p.grad for p in params if p.grad is not None]
-        flat = torch.cat([g.reshape(-1) for g in grads])
-        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.pg)
-        flat.div_(self.world_size)
-        off = 0
-        for g in grads:
-            g.copy_(flat[off:off + g.numel()].view_as(g))
-            off += g.numel()
+        if self.world_size > 1:
+            allreduce_mean_([p.grad for p in params if p.grad is not None], self.pg, self.world_size)
 
     def critic_step(self, pred, gt, refined, c=0):
         netD, netG = self.netD, self.netG
