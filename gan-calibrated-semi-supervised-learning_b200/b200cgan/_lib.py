@@ -1,8 +1,7 @@
 """ctypes binding of libb2c.so (C-ABI declared in include/b2c.h).
 
 There is NO fallback: if the library is missing or a call fails, an exception is raised.  Signatures are read
-from the header so the binding cannot drift from the ABI.  A test-only emulation backend can be installed with
-``set_backend`` (tests/emu_backend.py); the package itself never does that.
+from the header so the binding cannot drift from the ABI.
 """
 from __future__ import annotations
 
@@ -95,12 +94,6 @@ def backend():
     if _backend is None:
         _backend = _Native()
     return _backend
-
-
-def set_backend(b):
-    """TEST HOOK ONLY (tests/emu_backend.py installs a torch-CPU emulation to check host logic without a GPU)."""
-    global _backend
-    _backend = b
 
 
 def call(name, *args):

@@ -97,7 +97,7 @@ class SpectralNormConv2dK4S2(nn.Module):
         W = self.weight_orig
         R, K = W.shape[0], W.numel() // W.shape[0]
         sig = torch.empty(2, dtype=torch.float32, device=W.device)
-        ws = torch.empty(K + R + 2, dtype=torch.float32, device=W.device)
+        ws = torch.empty((R + 31) // 32 * K + R, dtype=torch.float32, device=W.device)
         _lib.call("b2c_sn_power_iter", W.detach(), self.weight_u, self.weight_v, sig, ws, R, K, int(self.training))
         return ops.WeightCtx(W, sig, self.weight_u.clone(), self.weight_v.clone())
 

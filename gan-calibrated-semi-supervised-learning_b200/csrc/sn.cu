@@ -24,47 +24,96 @@ __device__ __forceinline__ float block_sum(float v, float* sh) {
   return r;
 }
 
-// t[k] = sum_r W[r][k] u[r];  scal[0] += sum t^2
-__global__ void sn_wtu_kernel(const float* __restrict__ W, const float* __restrict__ u, float* __restrict__ t,
-                              float* __restrict__ scal, int R, int K) {
-  __shared__ float sh[32];
+// Power iteration in three atomic-free launches (deterministic, so u/v stay bit-identical on every data-parallel rank):
+//   wtu   : part[rs][k] = sum_{r in row chunk rs} W[r][k] u[r]           grid (K/128, RS), 8 independent loads in flight
+//   wv    : t = sum_rs part[rs]  (every block re-derives it into shared memory, K <= 4096 floats), v = t / max(|t|, eps),
+//           s[r] = W[r] . v for the block's SN_ROWS rows (W streamed once, coalesced)
+//   finish: u = s / max(|s|, eps), sigma = u . s
+constexpr int SN_CHUNK = 32;  // rows per wtu block
+constexpr int SN_ROWS = 4;    // rows per wv block
+constexpr int SN_MAXK = 4096;
+
+__global__ void __launch_bounds__(128) sn_wtu_kernel(const float* __restrict__ W, const float* __restrict__ u,
+                                                      float* __restrict__ part, int R, int K) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r0 = blockIdx.y * SN_CHUNK;
+  if (k >= K) return;
   float acc = 0.f;
-  if (k < K)
-    for (int r = 0; r < R; ++r) acc += __ldg(W + (long long)r * K + k) * __ldg(u + r);
-  if (k < K) t[k] = acc;
-  const float ss = block_sum(k < K ? acc * acc : 0.f, sh);
-  if (threadIdx.x == 0) atomicAdd(scal, ss);
+  const int r1 = min(r0 + SN_CHUNK, R);
+  int r = r0;
+  for (; r + 8 <= r1; r += 8) {
+    float w[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) w[j] = __ldg(W + (long long)(r + j) * K + k);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc += w[j] * __ldg(u + r + j);
+  }
+  for (; r < r1; ++r) acc += __ldg(W + (long long)r * K + k) * __ldg(u + r);
+  part[(long long)blockIdx.y * K + k] = acc;
 }
 
-// v = t / max(||t||, eps) (written by block 0 when update_v);  s[r] = W[r].v ; scal[1] += sum s^2
-__global__ void sn_wv_kernel(const float* __restrict__ W, const float* __restrict__ t, float* __restrict__ v,
-                             float* __restrict__ s, float* __restrict__ scal, int R, int K, int update_v) {
-  const float inv = update_v ? 1.f / fmaxf(sqrtf(scal[0]), 1e-12f) : 1.f;
-  const float* src = update_v ? t : v;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
-  const int r = blockIdx.x * wpb + warp;
-  if (r < R) {
-    float acc = 0.f;
-    for (int k = lane; k < K; k += 32) acc += __ldg(W + (long long)r * K + k) * (src[k] * inv);
-    acc = warp_sum(acc);
-    if (lane == 0) {
-      s[r] = acc;
-      atomicAdd(scal + 1, acc * acc);
-    }
-  }
+__global__ void __launch_bounds__(256) sn_wv_kernel(const float* __restrict__ W, const float* __restrict__ part,
+                                                     float* __restrict__ v, float* __restrict__ s, int R, int K, int RS,
+                                                     int update_v) {
+  __shared__ float ts[SN_MAXK];
+  __shared__ float sh[32];
+  __shared__ float red[SN_ROWS][8];
+  float inv = 1.f;
   if (update_v) {
-    __syncthreads();  // all reads of t by this block are done; v != t so other blocks are unaffected
-    if (blockIdx.x == 0)
-      for (int k = threadIdx.x; k < K; k += blockDim.x) v[k] = t[k] * inv;
+    float ss = 0.f;
+    for (int k = threadIdx.x; k < K; k += 256) {
+      float t = 0.f;
+      for (int j = 0; j < RS; ++j) t += part[(long long)j * K + k];
+      ts[k] = t;
+      ss += t * t;
+    }
+    ss = block_sum(ss, sh);
+    inv = 1.f / fmaxf(sqrtf(ss), 1e-12f);
+    for (int k = threadIdx.x; k < K; k += 256) {
+      const float vk = ts[k] * inv;
+      ts[k] = vk;
+      if (blockIdx.x == 0) v[k] = vk;
+    }
+  } else {
+    for (int k = threadIdx.x; k < K; k += 256) ts[k] = v[k];
+  }
+  __syncthreads();
+  const int r0 = blockIdx.x * SN_ROWS;
+  float acc[SN_ROWS];
+#pragma unroll
+  for (int j = 0; j < SN_ROWS; ++j) acc[j] = 0.f;
+  for (int k = threadIdx.x; k < K; k += 256) {
+    const float vk = ts[k];
+#pragma unroll
+    for (int j = 0; j < SN_ROWS; ++j)
+      if (r0 + j < R) acc[j] += __ldg(W + (long long)(r0 + j) * K + k) * vk;
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < SN_ROWS; ++j) {
+    const float w = warp_sum(acc[j]);
+    if (lane == 0) red[j][warp] = w;
+  }
+  __syncthreads();
+  if (threadIdx.x < SN_ROWS && r0 + threadIdx.x < R) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[threadIdx.x][w];
+    s[r0 + threadIdx.x] = t;
   }
 }
 
 // train: u = s / max(||s||, eps), sigma = u.s ; eval: sigma = u_old.s.   sig[0] = sigma, sig[1] = 1/sigma
-__global__ void sn_finish_kernel(const float* __restrict__ s, float* __restrict__ u, const float* __restrict__ scal,
-                                 float* __restrict__ sig, int R, int update_u) {
+__global__ void sn_finish_kernel(const float* __restrict__ s, float* __restrict__ u, float* __restrict__ sig, int R,
+                                 int update_u) {
   __shared__ float sh[32];
-  const float inv = update_u ? 1.f / fmaxf(sqrtf(scal[1]), 1e-12f) : 1.f;
+  float inv = 1.f;
+  if (update_u) {
+    float ss = 0.f;
+    for (int r = threadIdx.x; r < R; r += blockDim.x) ss += s[r] * s[r];
+    ss = block_sum(ss, sh);
+    inv = 1.f / fmaxf(sqrtf(ss), 1e-12f);
+  }
   float acc = 0.f;
   for (int r = threadIdx.x; r < R; r += blockDim.x) {
     float ur;
@@ -75,16 +124,16 @@ __global__ void sn_finish_kernel(const float* __restrict__ s, float* __restrict_
   if (threadIdx.x == 0) { sig[0] = sigma; sig[1] = 1.f / sigma; }
 }
 
-// ws: fp32 scratch of K + R + 2 floats.  u[R], v[K] updated in place when train != 0.  sig[2] <- (sigma, 1/sigma).
+// ws: fp32 scratch of ceil(R/32)*K + R floats.  u[R], v[K] updated in place when train != 0.  sig[2] <- (sigma, 1/sigma).
 extern "C" int b2c_sn_power_iter(const float* W, float* u, float* v, float* sig, float* ws, int R, int K, int train,
                                  void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  float* t = ws; float* s = ws + K; float* scal = ws + K + R;
-  cudaError_t e = cudaMemsetAsync(scal, 0, 2 * sizeof(float), st);
-  if (e != cudaSuccess) { b2c_set_error("sn memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
-  if (train) sn_wtu_kernel<<<(K + 127) / 128, 128, 0, st>>>(W, u, t, scal, R, K);
-  sn_wv_kernel<<<(R + 7) / 8, 256, 0, st>>>(W, t, v, s, scal, R, K, train ? 1 : 0);
-  sn_finish_kernel<<<1, 256, 0, st>>>(s, u, scal, sig, R, train ? 1 : 0);
+  B2C_REQUIRE(K <= SN_MAXK, "sn_power_iter: K=%d exceeds %d", K, SN_MAXK);
+  const int RS = (R + SN_CHUNK - 1) / SN_CHUNK;
+  float* part = ws; float* s = ws + (long long)RS * K;
+  if (train) sn_wtu_kernel<<<dim3((K + 127) / 128, RS), 128, 0, st>>>(W, u, part, R, K);
+  sn_wv_kernel<<<(R + SN_ROWS - 1) / SN_ROWS, 256, 0, st>>>(W, part, v, s, R, K, RS, train ? 1 : 0);
+  sn_finish_kernel<<<1, 256, 0, st>>>(s, u, sig, R, train ? 1 : 0);
   return b2c_check_launch("sn_power_iter");
 }
 

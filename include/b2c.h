@@ -61,7 +61,7 @@ int b2c_lrelu_bwd(const void* g, const void* a, void* out, long long n, float sl
 int b2c_copy_strided(const void* src, long long lds, void* dst, long long ldd, long long npix, int C, void* stream);
 int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsigned long long offset, void* stream);
 
-/* ---- spectral norm (torch spectral_norm.py:92-114) ---- */
+/* ---- spectral norm (torch spectral_norm.py:92-114); ws: ceil(R/32)*K + R floats of scratch ---- */
 int b2c_sn_power_iter(const float* W, float* u, float* v, float* sig, float* ws, int R, int K, int train, void* stream);
 int b2c_sn_bwd(const float* dWe, const float* W, const float* u, const float* v, const float* sig, float* ws, float* dW,
                int R, int K, int accumulate, void* stream);

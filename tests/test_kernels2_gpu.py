@@ -99,12 +99,15 @@ def test_spectral_norm(L, R, K):
     W = torch.randn(R, K, generator=g) * 0.02
     u = F.normalize(torch.randn(R, generator=g), dim=0)
     v = F.normalize(torch.randn(K, generator=g), dim=0)
-    ud, vd, sig, ws = u.cuda(), v.cuda(), torch.empty(2, device="cuda"), torch.empty(K + R + 2, device="cuda")
+    ud, vd, sig, ws = u.cuda(), v.cuda(), torch.empty(2, device="cuda"), torch.empty((R + 31) // 32 * K + R, device="cuda")
     L.call("b2c_sn_power_iter", W.cuda(), ud, vd, sig, ws, R, K, 1)
     v1 = F.normalize(W.t() @ u, dim=0, eps=1e-12)
     u1 = F.normalize(W @ v1, dim=0, eps=1e-12)
     s1 = torch.dot(u1, W @ v1)
     assert rel(vd, v1) < 1e-5 and rel(ud, u1) < 1e-5 and rel(sig[:1], s1.view(1)) < 1e-5
+    ud2, vd2 = u.cuda(), v.cuda()  # atomic-free reductions: a second run is bit-identical (ranks stay in lock step)
+    L.call("b2c_sn_power_iter", W.cuda(), ud2, vd2, sig, ws, R, K, 1)
+    assert torch.equal(ud, ud2) and torch.equal(vd, vd2)
     L.call("b2c_sn_power_iter", W.cuda(), ud, vd, sig, ws, R, K, 0)  # eval: no iteration
     assert rel(ud, u1) < 1e-5 and rel(sig[:1], s1.view(1)) < 1e-5 and rel(sig[1:], 1 / s1.view(1)) < 1e-5
     dWe = torch.randn(R, K, generator=g)

@@ -103,7 +103,9 @@ def test_discriminator_forward_and_critic_grads(B, S):
     with O.emulate_bf16():
         sc2, grads2 = O.critic_grads(d_ref2, batch["pred"], batch["gt"], batch["refined"], alphas[0], 1.0)
     assert abs(float(gp) - sc["gp"]) <= TOL * abs(sc["gp"]) + 1e-4
-    assert abs(float(wd) - sc["wd"]) <= TOL * abs(sc["wd"]) + 2e-3
+    # wd is a difference of two O(0.3) score-map means, each within 2e-2 relative: absolute bound 5e-3.  (The plane-sum
+    # kernels reduce with fp32 atomics, so bf16 roundings downstream differ run to run at this same level.)
+    assert abs(float(wd) - sc["wd"]) <= TOL * abs(sc["wd"]) + 5e-3
     errs = {}
     for k, p in D.named_parameters():
         if k in O.D_BIAS_UNOBSERVABLE:
