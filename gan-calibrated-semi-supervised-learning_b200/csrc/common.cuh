@@ -142,6 +142,20 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn_ma
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// One lane of a converged warp (elect.sync): ptxas then knows the branch runs single-lane and emits UTMALDG / UTCHMMA
+// with uniform operands directly instead of a per-instruction lane-uniformisation loop (which `lane == 0` gets).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ---------------------------------------------------------------- small math / io helpers
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

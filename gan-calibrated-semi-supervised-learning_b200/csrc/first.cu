@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_ker
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
-    if (t == 0) {
+    if (t < 32 && elect_one()) {
       tc_fence_after();
       const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
 #pragma unroll
@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, 
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
-    if (t == 0) {
+    if (t < 32 && elect_one()) {
       mbar_wait(&tma_bar[it & 1], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB + (it & 1) * FT_B_BYTES);

@@ -61,9 +61,38 @@ __device__ __forceinline__ void load_stats8(const float* zs, int n, int C, int c
 
 // Thread mapping shared by the reduce and apply kernels: block = 256 threads = (C/8 channel vectors) x (rows pixels);
 // grid = (splits over the plane, N images).  A thread keeps ONE channel vector for the whole kernel, so the per-(n,c)
-// statistics live in registers, and it walks its pixels U at a time with every load of the batch issued up front.
-constexpr int NORM_U = 4;
-template <int MODE> struct UF { static constexpr int v = MODE == 3 ? 2 : NORM_U; };  // batch depth (BWD2 is register-heavy)
+// statistics live in registers.  Its pixels arrive through a per-thread cp.async ring in shared memory: NORM_STAGES
+// batches of NORM_U pixels, every tensor of a batch issued as 16-byte LDGSTS into slots that only this thread reads, so
+// NORM_STAGES-1 batches stay in flight while one is being consumed and no block-level barrier is needed.  The raw
+// operands never sit in registers across the wait, which keeps the register count low enough for 3 blocks per SM.
+constexpr int NORM_U = 2;
+constexpr int NORM_STAGES = 3;
+
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Ring layout (dynamic shared memory): z[S][U][256] uint4, then g, h (modes that read them), then m[S][U][256] uint2.
+template <int MODE>
+struct Ring {
+  static constexpr bool HAS_G = MODE == 2 || MODE == 3, HAS_H = MODE == 3, HAS_M = MODE != 1;
+  static constexpr int SLOTS = NORM_STAGES * NORM_U * 256;
+  static constexpr int BYTES = SLOTS * (16 + (HAS_G ? 16 : 0) + (HAS_H ? 16 : 0) + (HAS_M ? 8 : 0));
+  uint4 *z, *g, *h;
+  uint2* m;
+  __device__ __forceinline__ Ring(uint8_t* base) {
+    z = reinterpret_cast<uint4*>(base);
+    g = z + SLOTS;
+    h = g + (HAS_G ? SLOTS : 0);
+    m = reinterpret_cast<uint2*>(h + (HAS_H ? SLOTS : 0));
+  }
+};
 
 struct Elem { float xh[8], gn[8], hh[8], dact[8]; };
 
@@ -71,16 +100,59 @@ struct Elem { float xh[8], gn[8], hh[8], dact[8]; };
 struct Raw { uint4 z, g, h; uint2 m; };
 
 template <int MODE>
-__device__ __forceinline__ void raw_load(const NormArgs& a, long long pix, int c0, bool ok, Raw& r) {
-  r.z = r.g = r.h = make_uint4(0, 0, 0, 0);
+__device__ __forceinline__ void ring_issue(const NormArgs& a, const Ring<MODE>& rg, int slot, long long pix, int c0) {
+  cp_async16(rg.z + slot, a.z + pix * a.ldz + c0);
+  if (Ring<MODE>::HAS_M)
+    if (a.mask) cp_async8(rg.m + slot, a.mask + pix * a.C + c0);
+  if (Ring<MODE>::HAS_G)
+    if (a.g) cp_async16(rg.g + slot, a.g + pix * a.ldg + c0);
+  if (Ring<MODE>::HAS_H) cp_async16(rg.h + slot, a.h + pix * a.ldh + c0);
+}
+template <int MODE>
+__device__ __forceinline__ void ring_fetch(const NormArgs& a, const Ring<MODE>& rg, int slot, Raw& r) {
+  r.z = rg.z[slot];
+  r.g = r.h = make_uint4(0, 0, 0, 0);
   r.m = make_uint2(0x01010101u, 0x01010101u);
-  if (!ok) return;
-  r.z = __ldg(reinterpret_cast<const uint4*>(a.z + pix * a.ldz + c0));
-  if (MODE == M_FWD || MODE == M_BWD || MODE == M_BWD2)
-    if (a.mask) r.m = __ldg(reinterpret_cast<const uint2*>(a.mask + pix * a.C + c0));
-  if (MODE == M_BWD || MODE == M_BWD2)
-    if (a.g) r.g = __ldg(reinterpret_cast<const uint4*>(a.g + pix * a.ldg + c0));
-  if (MODE == M_BWD2) r.h = __ldg(reinterpret_cast<const uint4*>(a.h + pix * a.ldh + c0));
+  if (Ring<MODE>::HAS_M)
+    if (a.mask) r.m = rg.m[slot];
+  if (Ring<MODE>::HAS_G)
+    if (a.g) r.g = rg.g[slot];
+  if (Ring<MODE>::HAS_H) r.h = rg.h[slot];
+}
+// Walks this thread's pixels p = p0, p0 + rows, ... (< p_end) through the ring and calls body(pix, Raw) for each.
+template <int MODE, typename F>
+__device__ __forceinline__ void ring_walk(const NormArgs& a, uint8_t* smem, int n, int c0, int p0, int rows, int p_end,
+                                          F&& body) {
+  const Ring<MODE> rg(smem);
+  const int cnt = p0 < p_end ? (p_end - p0 + rows - 1) / rows : 0;
+  const int nb = (cnt + NORM_U - 1) / NORM_U;
+  const long long base = (long long)n * a.HW;
+  auto issue = [&](int b) {
+    if (b < nb) {
+#pragma unroll
+      for (int u = 0; u < NORM_U; ++u) {
+        const int i = b * NORM_U + u;
+        if (i < cnt) ring_issue<MODE>(a, rg, ((b % NORM_STAGES) * NORM_U + u) * 256 + threadIdx.x, base + p0 + i * rows, c0);
+      }
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int s = 0; s < NORM_STAGES - 1; ++s) issue(s);
+  for (int b = 0; b < nb; ++b) {
+    issue(b + NORM_STAGES - 1);
+    cp_async_wait<NORM_STAGES - 1>();
+#pragma unroll
+    for (int u = 0; u < NORM_U; ++u) {
+      const int i = b * NORM_U + u;
+      if (i < cnt) {
+        Raw r;
+        ring_fetch<MODE>(a, rg, ((b % NORM_STAGES) * NORM_U + u) * 256 + threadIdx.x, r);
+        body(base + p0 + i * rows, r);
+      }
+    }
+  }
+  cp_async_wait<0>();
 }
 __device__ __forceinline__ void cvt8(const uint4& u, float (&f)[8]) {
   float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y), c = unpack_bf16(u.z), d = unpack_bf16(u.w);
@@ -114,9 +186,11 @@ __device__ __forceinline__ void elem_make(const NormArgs& a, const Raw& r, const
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(256) plane_reduce_kernel(NormArgs a) {
+__global__ void __launch_bounds__(256, MODE == 3 ? 2 : 3) plane_reduce_kernel(NormArgs a) {
   constexpr int ns = NS<MODE>::v;
-  extern __shared__ float red[];  // [ns][rows][C] = ns * 2048 floats
+  constexpr int LM = (MODE == M_FWD || MODE == M_POOL) ? M_POOL : MODE;  // which tensors the ring carries
+  extern __shared__ __align__(16) uint8_t smem_dyn[];  // cp.async ring, then reused as red[ns][rows][C] (ns * 2048 floats)
+  float* red = reinterpret_cast<float*>(smem_dyn);
   const int n = blockIdx.y, cvecs = a.C / 8, rows = 256 / cvecs;
   const int cv = threadIdx.x % cvecs, prow = threadIdx.x / cvecs, c0 = cv * 8;
   float mean[8], rstd[8], gv[8], acc[ns][8];
@@ -133,35 +207,27 @@ __global__ void __launch_bounds__(256) plane_reduce_kernel(NormArgs a) {
   }
   const float kscale = a.mask ? 2.f : 1.f;
   const int p_begin = (int)((long long)a.HW * blockIdx.x / gridDim.x), p_end = (int)((long long)a.HW * (blockIdx.x + 1) / gridDim.x);
-  constexpr int U = UF<MODE>::v;
-  for (int p = p_begin + prow; p < p_end; p += rows * U) {
-    Raw r[U];
+  ring_walk<LM>(a, smem_dyn, n, c0, p_begin + prow, rows, p_end, [&](long long, const Raw& r) {
+    if (MODE == M_FWD) {
+      float z[8];
+      cvt8(r.z, z);
 #pragma unroll
-    for (int u = 0; u < U; ++u)
-      raw_load<(MODE == M_FWD || MODE == M_POOL) ? M_POOL : MODE>(a, (long long)n * a.HW + p + u * rows, c0, p + u * rows < p_end, r[u]);
+      for (int i = 0; i < 8; ++i) { acc[0][i] += z[i]; acc[1][i] += z[i] * z[i]; }
+    } else {
+      Elem e;
+      elem_make<MODE>(a, r, mean, rstd, gv, kscale, e);
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (p + u * rows >= p_end) continue;
-      if (MODE == M_FWD) {
-        float z[8];
-        cvt8(r[u].z, z);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { acc[0][i] += z[i]; acc[1][i] += z[i] * z[i]; }
-      } else {
-        Elem e;
-        elem_make<MODE>(a, r[u], mean, rstd, gv, kscale, e);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          if (MODE == M_POOL) acc[0][i] += e.xh[i] > 0.f ? e.xh[i] : e.xh[i] * a.slope;
-          if (MODE == M_BWD) { acc[0][i] += e.gn[i]; acc[1][i] += e.gn[i] * e.xh[i]; }
-          if (MODE == M_BWD2) {
-            acc[0][i] += e.hh[i]; acc[1][i] += e.hh[i] * e.xh[i]; acc[2][i] += e.gn[i];
-            acc[3][i] += e.gn[i] * e.xh[i]; acc[4 % ns][i] += e.hh[i] * e.gn[i];
-          }
+      for (int i = 0; i < 8; ++i) {
+        if (MODE == M_POOL) acc[0][i] += e.xh[i] > 0.f ? e.xh[i] : e.xh[i] * a.slope;
+        if (MODE == M_BWD) { acc[0][i] += e.gn[i]; acc[1][i] += e.gn[i] * e.xh[i]; }
+        if (MODE == M_BWD2) {
+          acc[0][i] += e.hh[i]; acc[1][i] += e.hh[i] * e.xh[i]; acc[2][i] += e.gn[i];
+          acc[3][i] += e.gn[i] * e.xh[i]; acc[4 % ns][i] += e.hh[i] * e.gn[i];
         }
       }
     }
-  }
+  });
+  __syncthreads();  // every thread is done with its ring slots before the ring is reused for the block reduction
   // block reduction without atomics (shared fp32 atomicAdd is a CAS loop): red[s][prow][C], then one thread per (s, c)
 #pragma unroll
   for (int s = 0; s < ns; ++s) {
@@ -179,8 +245,9 @@ __global__ void __launch_bounds__(256) plane_reduce_kernel(NormArgs a) {
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(256) plane_apply_kernel(NormArgs a) {
+__global__ void __launch_bounds__(256, MODE == 3 ? 2 : 3) plane_apply_kernel(NormArgs a) {
   constexpr int ns = NS<MODE>::v;
+  extern __shared__ __align__(16) uint8_t smem_dyn[];
   const int n = blockIdx.y, cvecs = a.C / 8, rows = 256 / cvecs;
   const int cv = threadIdx.x % cvecs, prow = threadIdx.x / cvecs, c0 = cv * 8;
   const float inv = 1.f / (float)a.HW;
@@ -201,50 +268,41 @@ __global__ void __launch_bounds__(256) plane_apply_kernel(NormArgs a) {
   }
   const float kscale = a.mask ? 2.f : 1.f;
   const int p_begin = (int)((long long)a.HW * blockIdx.x / gridDim.x), p_end = (int)((long long)a.HW * (blockIdx.x + 1) / gridDim.x);
-  constexpr int U = UF<MODE>::v;
-  for (int p = p_begin + prow; p < p_end; p += rows * U) {
-    Raw r[U];
+  ring_walk<MODE>(a, smem_dyn, n, c0, p_begin + prow, rows, p_end, [&](long long pix, const Raw& r) {
+    if (MODE == M_FWD) {
+      float z[8], k[8], o[8];
+      cvt8(r.z, z);
+      cvt_mask8(r.m, k);
 #pragma unroll
-    for (int u = 0; u < U; ++u) raw_load<MODE>(a, (long long)n * a.HW + p + u * rows, c0, p + u * rows < p_end, r[u]);
+      for (int e = 0; e < 8; ++e) {
+        const float xh = (z[e] - mean[e]) * rstd[e];
+        o[e] = (xh > 0.f ? xh : xh * a.slope) * k[e] * kscale;
+      }
+      store8(a.o0 + pix * a.ldo0 + c0, o);
+      if (a.o1) store8(a.o1 + pix * a.ldo1 + c0, o);
+    } else {
+      Elem el;
+      elem_make<MODE>(a, r, mean, rstd, gv, kscale, el);
+      if (MODE == M_BWD) {
+        float o[8];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (p + u * rows >= p_end) continue;
-      const long long pix = (long long)n * a.HW + p + u * rows;
-      if (MODE == M_FWD) {
-        float z[8], k[8], o[8];
-        cvt8(r[u].z, z);
-        cvt_mask8(r[u].m, k);
+        for (int e = 0; e < 8; ++e) o[e] = (el.gn[e] - sm[0][e] - el.xh[e] * sm[1 % ns][e]) * rstd[e];
+        store8(a.o0 + pix * a.ldo0 + c0, o);
+      } else {  // M_BWD2: o0 = grad wrt g (the first-backward input), o1 = grad wrt z
+        float og[8], oz[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const float xh = (z[e] - mean[e]) * rstd[e];
-          o[e] = (xh > 0.f ? xh : xh * a.slope) * k[e] * kscale;
+          const float mh = sm[0][e], ma = sm[1 % ns][e], mg = sm[2 % ns][e], mc = sm[3 % ns][e], mhg = sm[4 % ns][e];
+          const float q = mhg - mh * mg - ma * mc;
+          const float Ph = el.hh[e] - mh - el.xh[e] * ma, Pg = el.gn[e] - mg - el.xh[e] * mc;
+          og[e] = Ph * rstd[e] * el.dact[e];
+          oz[e] = -(q * el.xh[e] + mc * Ph + ma * Pg) * rstd[e] * rstd[e];
         }
-        store8(a.o0 + pix * a.ldo0 + c0, o);
-        if (a.o1) store8(a.o1 + pix * a.ldo1 + c0, o);
-      } else {
-        Elem el;
-        elem_make<MODE>(a, r[u], mean, rstd, gv, kscale, el);
-        if (MODE == M_BWD) {
-          float o[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) o[e] = (el.gn[e] - sm[0][e] - el.xh[e] * sm[1 % ns][e]) * rstd[e];
-          store8(a.o0 + pix * a.ldo0 + c0, o);
-        } else {  // M_BWD2: o0 = grad wrt g (the first-backward input), o1 = grad wrt z
-          float og[8], oz[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const float mh = sm[0][e], ma = sm[1 % ns][e], mg = sm[2 % ns][e], mc = sm[3 % ns][e], mhg = sm[4 % ns][e];
-            const float q = mhg - mh * mg - ma * mc;
-            const float Ph = el.hh[e] - mh - el.xh[e] * ma, Pg = el.gn[e] - mg - el.xh[e] * mc;
-            og[e] = Ph * rstd[e] * el.dact[e];
-            oz[e] = -(q * el.xh[e] + mc * Ph + ma * Pg) * rstd[e] * rstd[e];
-          }
-          store8(a.o0 + pix * a.ldo0 + c0, og);
-          store8(a.o1 + pix * a.ldo1 + c0, oz);
-        }
+        store8(a.o0 + pix * a.ldo0 + c0, og);
+        store8(a.o1 + pix * a.ldo1 + c0, oz);
       }
     }
-  }
+  });
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -257,7 +315,7 @@ static int norm_check(const NormArgs& a, const char* who) {
 static int plane_splits(int N, int HW, int C, int target) {
   const int rows = 256 / (C / 8);
   int s = (target + N - 1) / (N > 0 ? N : 1);
-  const int cap = HW / (rows * NORM_U * 2);
+  const int cap = HW / (rows * NORM_U * NORM_STAGES);
   if (s > cap) s = cap;
   return s < 1 ? 1 : s;
 }
@@ -266,14 +324,27 @@ static int launch_reduce(const NormArgs& a, cudaStream_t st) {
   constexpr int ns = NS<MODE>::v;
   cudaError_t e = cudaMemsetAsync(a.sums, 0, sizeof(float) * (size_t)a.N * a.C * ns, st);
   if (e != cudaSuccess) { b2c_set_error("norm memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+  constexpr int LM = (MODE == M_FWD || MODE == M_POOL) ? M_POOL : MODE;
+  constexpr size_t red_bytes = sizeof(float) * 2048 * ns, ring_bytes = Ring<LM>::BYTES;
+  constexpr size_t smem = red_bytes > ring_bytes ? red_bytes : ring_bytes;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaFuncSetAttribute(plane_reduce_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    attr_done = true;
+  }
   dim3 grid(plane_splits(a.N, a.HW, a.C, 148 * 6), a.N);
-  plane_reduce_kernel<MODE><<<grid, 256, sizeof(float) * 2048 * ns, st>>>(a);
+  plane_reduce_kernel<MODE><<<grid, 256, smem, st>>>(a);
   return b2c_check_launch("plane_reduce");
 }
 template <int MODE>
 static int launch_apply(const NormArgs& a, cudaStream_t st) {
-  dim3 grid(plane_splits(a.N, a.HW, a.C, 148 * 8), a.N);
-  plane_apply_kernel<MODE><<<grid, 256, 0, st>>>(a);
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaFuncSetAttribute(plane_apply_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Ring<MODE>::BYTES);
+    attr_done = true;
+  }
+  dim3 grid(plane_splits(a.N, a.HW, a.C, 148 * 6), a.N);
+  plane_apply_kernel<MODE><<<grid, 256, Ring<MODE>::BYTES, st>>>(a);
   return b2c_check_launch("plane_apply");
 }
 static NormArgs base_args(const void* z, long long ldz, const float* zs, int N, int HW, int C, float slope) {

@@ -33,7 +33,7 @@ struct TapGemmParams {
 
 template <int BN>
 struct TapGemmCfg {
-  static constexpr int STAGES = (BN == 128) ? 3 : (BN == 32 ? 6 : 4);
+  static constexpr int STAGES = (BN == 256) ? 2 : (BN == 128) ? 3 : (BN == 32 ? 6 : 4);
   static constexpr int A_BYTES = 128 * 128;
   static constexpr int B_BYTES = BN * 128;
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;
@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0, phase = 0;
       for (int tap = 0; tap < ntaps; ++tap) {
         for (int cc = 0; cc < p.kchunks; ++cc) {
@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
       int stage = 0, phase = 0;
       for (int it = 0; it < niters; ++it) {
@@ -249,7 +249,7 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     rc = b2c_make_tmap_bf16(&tmA, x, 4, dims, str, box);
   }
   if (rc) return rc;
-  const int BN = (Cout % 128 == 0) ? 128 : 64;
+  const int BN = (Cout % 256 == 0) ? 256 : (Cout % 128 == 0) ? 128 : 64;
   const int K = (mode == 0 ? 16 : 4) * Cin;
   const int rows = (mode == 0 ? 1 : 4) * Cout;
   {
@@ -260,6 +260,7 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     if (rc) return rc;
   }
   dim3 grid(p.tiles_x * p.tiles_y * tiles_n, Cout / BN, mode == 0 ? 1 : 4);
+  if (BN == 256) return launch_tapgemm<256>(tmA, tmB, p, grid, (cudaStream_t)stream);
   if (BN == 128) return launch_tapgemm<128>(tmA, tmB, p, grid, (cudaStream_t)stream);
   return launch_tapgemm<64>(tmA, tmB, p, grid, (cudaStream_t)stream);
 }

@@ -6,8 +6,11 @@
 // and the double-backward term of the gradient penalty (cgan/losses.py:213-220): small = g_z, large = cotangent h.
 //
 // GEMM per tap: D[128 a x NB b] += A^T B with the reduction over pixels.  Both operands sit in NHWC, i.e. the
-// reduction index (pixel) is the slow one: they are MN-major UMMA operands, loaded as [64 pixels x 64 channels]
-// 128B-swizzled TMA boxes (the "large" one through the same strided 5-D view the fprop kernel uses).  Split-K over
+// reduction index (pixel) is the slow one: they are MN-major UMMA operands, loaded as [32 pixels x 64 channels]
+// 128B-swizzled TMA boxes (the "large" one through the same strided 5-D view the fprop kernel uses).
+// The kernel is L2->SM bandwidth bound, so one CTA owns TPC = 512/NB taps of its (128 x NB) weight tile: the `small`
+// box of a pixel chunk is loaded ONCE and multiplied against TPC tap-shifted `large` boxes, with TPC accumulators side
+// by side in the 512 TMEM columns (105 FLOP per staged byte instead of 64 / 44 with one tap per CTA).  Split-K over
 // pixel chunks; partial tiles are reduced with vector fp32 atomics into a tap-major workspace ws[16][Cs][Cl].
 #include "common.cuh"
 #include "tmap.h"
@@ -16,7 +19,7 @@ using namespace b2c;
 
 struct WgradParams {
   int N, Cs, Cl;
-  int BW, BH, BI;          // 64-pixel box over the small tensor
+  int BW, BH, BI;          // 32-pixel box over the small tensor
   int tiles_x, tiles_y;    // box grid over (Hs, Ws)
   int nchunks;             // total pixel chunks
   int mtiles, ntiles;      // Cs/128, Cl/NB
@@ -25,17 +28,21 @@ struct WgradParams {
 
 template <int NB>
 struct WgradCfg {
-  static constexpr int STAGES = 4;
-  static constexpr int A_BYTES = 2 * 64 * 128;
-  static constexpr int B_BYTES = (NB / 64) * 64 * 128;
+  static constexpr int TPC = 512 / NB;                       // taps per CTA
+  static constexpr int STAGES = 5;
+  static constexpr int PIX = 32;                             // pixels (K) per stage = 2 MMAs of K=16
+  static constexpr int BOX_BYTES = PIX * 128;                // one [32 px x 64 ch] box
+  static constexpr int A_BYTES = 2 * BOX_BYTES;              // 128 channels of `small`
+  static constexpr int B_TAP_BYTES = (NB / 64) * BOX_BYTES;  // NB channels of `large` for one tap
+  static constexpr int B_BYTES = TPC * B_TAP_BYTES;
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;
 };
 
 template <int NB>
-__global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ CUtensorMap tmS,
+__global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUtensorMap tmS,
                                                     const __grid_constant__ CUtensorMap tmL, WgradParams p) {
   using Cfg = WgradCfg<NB>;
-  constexpr int STAGES = Cfg::STAGES;
+  constexpr int STAGES = Cfg::STAGES, TPC = Cfg::TPC;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
@@ -49,8 +56,7 @@ __global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ CUte
   int t = blockIdx.x;
   const int nt = t % p.ntiles; t /= p.ntiles;
   const int mt = t % p.mtiles; t /= p.mtiles;
-  const int tap = t;
-  const int ky = tap >> 2, kx = tap & 3;
+  const int tap0 = t * TPC;
   const int a0 = mt * 128, b0 = nt * NB;
   const int splits = gridDim.y;
   const int c_begin = (int)((long long)p.nchunks * blockIdx.y / splits);
@@ -67,7 +73,7 @@ __global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ CUte
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<NB>(tmem_slot);
+  if (warp == 1) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -75,36 +81,48 @@ __global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ CUte
 
   if (niters > 0) {
     if (warp == 0) {
-      if (lane == 0) {
-        const int fy = (ky - 1) >> 1, di = (ky - 1) & 1, fx = (kx - 1) >> 1, dj = (kx - 1) & 1;
+      if (elect_one()) {
         int stage = 0, phase = 0;
+        int tx = c_begin % p.tiles_x, ty = (c_begin / p.tiles_x) % p.tiles_y, tn = c_begin / (p.tiles_x * p.tiles_y);
         for (int c = c_begin; c < c_end; ++c) {
-          const int tx = c % p.tiles_x, ty = (c / p.tiles_x) % p.tiles_y, tn = c / (p.tiles_x * p.tiles_y);
           const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
+          if (++tx == p.tiles_x) { tx = 0; if (++ty == p.tiles_y) { ty = 0; ++tn; } }
           mbar_wait(&empty[stage], phase ^ 1);
           mbar_expect_tx(&full[stage], Cfg::A_BYTES + Cfg::B_BYTES);
           uint8_t* dA = sA + stage * Cfg::A_BYTES;
           uint8_t* dB = sB + stage * Cfg::B_BYTES;
           tma_load_4d(dA, &tmS, &full[stage], a0, x0, y0, n0);
-          tma_load_4d(dA + 8192, &tmS, &full[stage], a0 + 64, x0, y0, n0);
+          tma_load_4d(dA + Cfg::BOX_BYTES, &tmS, &full[stage], a0 + 64, x0, y0, n0);
 #pragma unroll
-          for (int j = 0; j < NB / 64; ++j)
-            tma_load_5d(dB + j * 8192, &tmL, &full[stage], dj * p.Cl + b0 + 64 * j, x0 + fx, di, y0 + fy, n0);
+          for (int tt = 0; tt < TPC; ++tt) {
+            const int ky = (tap0 + tt) >> 2, kx = (tap0 + tt) & 3;
+            const int fy = (ky - 1) >> 1, di = (ky - 1) & 1, fx = (kx - 1) >> 1, dj = (kx - 1) & 1;
+#pragma unroll
+            for (int j = 0; j < NB / 64; ++j)
+              tma_load_5d(dB + tt * Cfg::B_TAP_BYTES + j * Cfg::BOX_BYTES, &tmL, &full[stage],
+                          dj * p.Cl + b0 + 64 * j, x0 + fx, di, y0 + fy, n0);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     } else if (warp == 1) {
-      if (lane == 0) {
-        constexpr uint32_t idesc = umma_idesc_bf16(128, NB, 1, 1);
+      if (elect_one()) {
+        // taps sit side by side in shared memory (64-channel blocks BOX_BYTES apart) and in TMEM (NB columns each), so
+        // 256 / NB taps go into ONE N = 256 instruction: 4 MMAs per stage instead of 8 or 16
+        constexpr uint32_t idesc = umma_idesc_bf16(128, 256, 1, 1);
+        constexpr int TPM = 256 / NB;  // taps per MMA
         int stage = 0, phase = 0;
         for (int it = 0; it < niters; ++it) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(sA + stage * Cfg::A_BYTES), sb = smem_u32(sB + stage * Cfg::B_BYTES);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)  // 16 pixels (= 2 swizzle atoms of 8 k-rows) per MMA
-            umma_bf16(tmem_base, umma_desc_sw128(sa + k * 2048, 8192, 1024), umma_desc_sw128(sb + k * 2048, 8192, 1024),
-                      idesc, (uint32_t)((it | k) != 0));
+          for (int g = 0; g < TPC / TPM; ++g)
+#pragma unroll
+            for (int k = 0; k < 2; ++k)  // 16 pixels (= 2 swizzle atoms of 8 k-rows) per MMA
+              umma_bf16(tmem_base + g * 256, umma_desc_sw128(sa + k * 2048, Cfg::BOX_BYTES, 1024),
+                        umma_desc_sw128(sb + g * TPM * Cfg::B_TAP_BYTES + k * 2048, Cfg::BOX_BYTES, 1024), idesc,
+                        (uint32_t)((it | k) != 0));
           umma_commit(&empty[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -113,26 +131,29 @@ __global__ void __launch_bounds__(192) wgrad_kernel(const __grid_constant__ CUte
     } else {
       const int q = warp & 3;
       const int a = a0 + q * 32 + lane;
-      float* dst = p.ws + ((long long)tap * p.Cs + a) * p.Cl + b0;
       mbar_wait(tmem_full, 0);
       tc_fence_after();
 #pragma unroll 1
-      for (int c0 = 0; c0 < NB; c0 += 16) {
-        uint32_t v[16];
-        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + c0, v);
-        tmem_ld_wait();
+      for (int tt = ((warp - 2) >> 2) * (TPC / 2); tt < (((warp - 2) >> 2) + 1) * (TPC / 2); ++tt) {  // 2 warps per lane quarter
+        float* dst = p.ws + ((long long)(tap0 + tt) * p.Cs + a) * p.Cl + b0;
+#pragma unroll 1
+        for (int c0 = 0; c0 < NB; c0 += 16) {
+          uint32_t v[16];
+          tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + tt * NB + c0, v);
+          tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          float4 f = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
-                                 __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-          atomicAdd(reinterpret_cast<float4*>(dst + c0 + 4 * j), f);
+          for (int j = 0; j < 4; ++j) {
+            float4 f = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                   __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+            atomicAdd(reinterpret_cast<float4*>(dst + c0 + 4 * j), f);
+          }
         }
       }
       tc_fence_before();
     }
   }
   __syncthreads();
-  if (warp == 1) tmem_dealloc<NB>(tmem_base);
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
 // ws[tap][a][b] -> dw[a][b][ky][kx] (torch weight layout), optionally accumulating.
@@ -165,7 +186,7 @@ static int launch_wgrad(const CUtensorMap& tmS, const CUtensorMap& tmL, const Wg
     }
     attr_done = true;
   }
-  wgrad_kernel<NB><<<grid, 192, WgradCfg<NB>::SMEM, st>>>(tmS, tmL, p);
+  wgrad_kernel<NB><<<grid, 320, WgradCfg<NB>::SMEM, st>>>(tmS, tmL, p);
   return b2c_check_launch("wgrad_kernel");
 }
 
@@ -181,8 +202,8 @@ extern "C" int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* l
   B2C_REQUIRE(w_is_pow2(Hs) && w_is_pow2(Ws), "wgrad4s2: unsupported spatial size %dx%d", Hs, Ws);
   WgradParams p;
   p.N = N; p.Cs = Cs; p.Cl = Cl; p.ws = ws;
-  p.BW = Ws < 64 ? Ws : 64;
-  int rem = 64 / p.BW;
+  p.BW = Ws < 32 ? Ws : 32;
+  int rem = 32 / p.BW;
   p.BH = Hs < rem ? Hs : rem;
   p.BI = rem / p.BH;
   p.tiles_x = Ws / p.BW; p.tiles_y = Hs / p.BH;
@@ -206,8 +227,19 @@ extern "C" int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* l
     int rc = b2c_make_tmap_bf16(&tmL, large, 5, dims, str, box);
     if (rc) return rc;
   }
-  const int tiles = 16 * p.mtiles * p.ntiles;
-  int splits = (2 * (sm_count > 0 ? sm_count : 148) + tiles - 1) / tiles;
+  // One CTA per SM (it owns all 512 TMEM columns).  Pick the split-K factor by a small cost model: waves of CTAs times
+  // (pixel chunks per CTA + a fixed prologue/epilogue cost of about 12 chunk-times).
+  const int tiles = (16 / (512 / NB)) * p.mtiles * p.ntiles;
+  const int sms = sm_count > 0 ? sm_count : 148;
+  int splits = 1;
+  {
+    double best = 1e30;
+    for (int s = 1; s <= 2 * sms && s <= p.nchunks; ++s) {
+      const int waves = (tiles * s + sms - 1) / sms;
+      const double cost = waves * ((double)((p.nchunks + s - 1) / s) + 12.0);
+      if (cost < best - 1e-9) { best = cost; splits = s; }
+    }
+  }
   if (splits > p.nchunks) splits = p.nchunks;
   if (splits < 1) splits = 1;
   cudaError_t e = cudaMemsetAsync(ws, 0, sizeof(float) * 16 * (size_t)Cs * Cl, st);
