@@ -572,6 +572,7 @@ class FusedClipAdam:
         self.m = [torch.zeros_like(p, dtype=torch.float32) for p in self.params]
         self.v = [torch.zeros_like(p, dtype=torch.float32) for p in self.params]
         self.step_count = 0
+        self.step_base = None  # int64 device scalar added to step_count in the kernel (CUDA-graph replays)
         self.gnorm_sq = torch.zeros(1, dtype=torch.float32, device=self.params[0].device)
         n = len(self.params)
         self._n = (ctypes.c_longlong * n)(*[p.numel() for p in self.params])
@@ -592,5 +593,5 @@ class FusedClipAdam:
         _lib.call("b2c_multi_sumsq", self._arr(grads), self._n, n, self.gnorm_sq)
         _lib.call("b2c_multi_adam", self._arr([p.data for p in self.params]), self._arr(grads), self._arr(self.m),
                   self._arr(self.v), self._n, n, self.gnorm_sq, self.max_norm, self.lr, self.betas[0], self.betas[1],
-                  self.eps, self.step_count)
+                  self.eps, self.step_count, self.step_base)
         return self.gnorm_sq

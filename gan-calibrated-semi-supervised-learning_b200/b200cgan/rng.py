@@ -8,11 +8,17 @@ import torch
 
 from . import _lib
 
-_state = {"seed": 42, "offset": 0}
+_state = {"seed": 42, "offset": 0, "base": None}
 
 
 def manual_seed(seed: int, offset: int = 0):
     _state["seed"], _state["offset"] = int(seed), int(offset)
+
+
+def set_device_base(base):
+    """base: int64 device scalar added to the host offset inside the kernel (None = host offset only).  A captured
+    CUDA graph records host offsets relative to the start of the step and advances `base` between replays."""
+    _state["base"] = base
 
 
 def get_state():
@@ -21,6 +27,6 @@ def get_state():
 
 def next_mask(numel: int, device):
     m = torch.empty(numel, dtype=torch.uint8, device=device)
-    _lib.call("b2c_dropout_mask", m, numel, _state["seed"], _state["offset"])
+    _lib.call("b2c_dropout_mask", m, numel, _state["seed"], _state["offset"], _state["base"])
     _state["offset"] += numel
     return m

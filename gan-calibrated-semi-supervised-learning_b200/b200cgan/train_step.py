@@ -8,7 +8,11 @@ Differences from the reference loop, all outside the arithmetic:
   * the generator step skips D's backward (the reference computes it and zeroes it next step: dead work), but still
     runs D's forward in train mode, which advances the spectral-norm u/v buffers exactly like the reference (:361);
   * clip_grad_norm_ + Adam are one fused multi-tensor update per network;
-  * optional data-parallel gradient averaging (torch.distributed all-reduce) between backward and the update.
+  * optional data-parallel gradient averaging (torch.distributed all-reduce) between backward and the update;
+  * optional CUDA-graph mode (`use_cuda_graph=True`): after two eager steps the whole step (about 480 kernel launches
+    plus the autograd bookkeeping around them) is captured once and replayed; the dropout stream position and the Adam
+    step counts live in a device-side counter block that is advanced between replays, so every replay draws fresh
+    masks / interpolation coefficients and applies the right bias corrections.
 """
 from __future__ import annotations
 
@@ -17,7 +21,7 @@ from typing import Dict, Optional
 
 import torch
 
-from . import losses, ops
+from . import losses, ops, rng
 
 
 def allreduce_mean_(grads, group=None, world_size=None):
@@ -50,13 +54,17 @@ class StepOutput:
 
 class CGANTrainer:
     def __init__(self, netG, netD, *, lr=2e-4, beta1=0.5, beta2=0.999, n_critic=2, lambda_gp=1.0, lambda_iou=1.0,
-                 process_group=None, world_size=1):
+                 process_group=None, world_size=1, use_cuda_graph=False):
         self.netG, self.netD = netG, netD
         self.n_critic, self.lambda_gp, self.lambda_iou = n_critic, lambda_gp, lambda_iou
         self.optG = ops.FusedClipAdam(netG.parameters(), lr=lr, betas=(beta1, beta2))
         self.optD = ops.FusedClipAdam(netD.parameters(), lr=lr, betas=(beta1, beta2))
         self.pg, self.world_size = process_group, world_size
         self.alpha_source = None  # test hook: callable(critic_step) -> (B,1,1,1) tensor replacing torch.rand
+        self.use_cuda_graph = use_cuda_graph
+        self._graph = None        # captured step (torch.cuda.CUDAGraph)
+        self._eager_steps = 0
+        self._static_in = self._static_out = self._ctr = self._ctr_inc = None
 
     # ---- data parallel: average gradients over ranks (per-sample losses are batch means) ----
     def _allreduce(self, params):
@@ -103,6 +111,68 @@ class CGANTrainer:
         return (loss_reg.detach() + loss_wgan), loss_iou.detach(), loss_wgan, gn.clone(), delta_pred.detach()
 
     def step(self, pred, gt, refined, pred_box, delta_true) -> StepOutput:
+        """One train step.  Device tensors in, device scalars out (StepOutput.to_host() copies them to the host)."""
+        args = (pred, gt, refined, pred_box, delta_true)
+        if not self.use_cuda_graph or self.alpha_source is not None or \
+                any(s.injected is not None for s in self.netG.dropout_sites()):
+            return self._step_eager(*args)
+        if self._graph is None:
+            if self._eager_steps < 2:  # warm-up: function attributes, allocator, NCCL communicators
+                return self._step_eager(*args)
+            self._capture(args)
+        elif any(a.shape != s.shape for a, s in zip(args, self._static_in)):
+            raise ValueError("CUDA-graph mode was captured for inputs of shape %s" % (tuple(self._static_in[0].shape),))
+        for s, a in zip(self._static_in, args):
+            if s.data_ptr() != a.data_ptr():
+                s.copy_(a, non_blocking=True)
+        self._graph.replay()
+        self._ctr.add_(self._ctr_inc)  # dropout stream position, D / G Adam step counts
+        self.optD.host_steps += self.n_critic
+        self.optG.host_steps += 1
+        return self._static_out
+
+    def static_inputs(self):
+        """The captured step's input buffers (pred, gt, refined, pred_box, delta_true), or None before capture: a
+        caller may write the next batch straight into them (e.g. the H2D copy) and pass them to step()."""
+        return self._static_in
+
+    def disable_cuda_graph(self):
+        """Back to eager stepping (e.g. to bracket individual kernels with events): the device counters are folded back
+        into the host-side optimizer step counts and dropout stream position (one host sync)."""
+        if self._graph is not None:
+            pos, dsteps, gsteps = (int(v) for v in self._ctr.tolist())
+            rng.set_device_base(None)
+            rng.manual_seed(rng.get_state()["seed"], pos)
+            self.optD.step_base = self.optG.step_base = None
+            self.optD.step_count, self.optG.step_count = dsteps, gsteps
+            self._graph = None
+        self.use_cuda_graph = False
+
+    def _capture(self, args):
+        dev = args[0].device
+        self._static_in = [torch.empty_like(a) for a in args]
+        for s, a in zip(self._static_in, args):
+            s.copy_(a)
+        # device counter block: [dropout stream position, optD steps so far, optG steps so far]
+        st = rng.get_state()
+        self._ctr = torch.tensor([st["offset"], self.optD.step_count, self.optG.step_count], dtype=torch.int64, device=dev)
+        self.optD.host_steps, self.optG.host_steps = self.optD.step_count, self.optG.step_count
+        rng.manual_seed(st["seed"], 0)
+        rng.set_device_base(self._ctr[0:1])
+        self.optD.step_base, self.optG.step_base = self._ctr[1:2], self._ctr[2:3]
+        self.optD.step_count = self.optG.step_count = 0
+        torch.cuda.synchronize()
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._static_out = self._step_eager(*self._static_in)
+        # host-side ordinals recorded in the graph are relative to the start of a step; freeze them
+        per_step = rng.get_state()["offset"]
+        self._ctr_inc = torch.tensor([per_step, self.n_critic, 1], dtype=torch.int64, device=dev)
+        rng.manual_seed(st["seed"], 0)
+        self.optD.step_count = self.optG.step_count = 0
+
+    def _step_eager(self, pred, gt, refined, pred_box, delta_true) -> StepOutput:
+        self._eager_steps += 1
         self.netG.train(); self.netD.train()
         out = StepOutput()
         acc = None

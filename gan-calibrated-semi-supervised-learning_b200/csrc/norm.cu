@@ -444,7 +444,9 @@ __device__ __forceinline__ uint32_t mix32(uint64_t x) {
   x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
   return (uint32_t)x;
 }
-__global__ void dropout_mask_kernel(uint8_t* __restrict__ m, long long nvec, uint64_t seed, uint64_t offset) {
+__global__ void dropout_mask_kernel(uint8_t* __restrict__ m, long long nvec, uint64_t seed, uint64_t offset,
+                                    const long long* __restrict__ offset_base) {
+  if (offset_base) offset += (uint64_t)(*offset_base) / 8;  // device-side stream position (CUDA-graph replays)
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
     const uint32_t r = mix32((seed * 0x9E3779B97F4A7C15ULL) ^ (offset + (uint64_t)i));
     uint2 o;
@@ -453,10 +455,13 @@ __global__ void dropout_mask_kernel(uint8_t* __restrict__ m, long long nvec, uin
     *reinterpret_cast<uint2*>(m + i * 8) = o;
   }
 }
-extern "C" int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsigned long long offset, void* stream) {
-  B2C_REQUIRE(n % 8 == 0, "dropout_mask: n=%lld must be a multiple of 8", n);
+// Element i of the mask stream is a pure function of (seed, offset + *offset_base + i); offset_base (device, nullable)
+// lets a captured CUDA graph advance the stream between replays without re-recording the launch.
+extern "C" int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsigned long long offset,
+                                const long long* offset_base, void* stream) {
+  B2C_REQUIRE(n % 8 == 0 && offset % 8 == 0, "dropout_mask: n=%lld and offset must be multiples of 8", n);
   long long blocks = (n / 8 + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  dropout_mask_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(mask, n / 8, seed, offset);
+  dropout_mask_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(mask, n / 8, seed, offset / 8, offset_base);
   return b2c_check_launch("dropout_mask");
 }

@@ -35,7 +35,11 @@ __global__ void __launch_bounds__(256) multi_sumsq_kernel(TensorTable t, float* 
 }
 
 __global__ void __launch_bounds__(256) multi_adam_kernel(TensorTable t, const float* __restrict__ gnorm_sq, float max_norm,
-                                                         float lr, float beta1, float beta2, float eps, float bc1, float bc2) {
+                                                         float lr, float beta1, float beta2, float eps, int step_index,
+                                                         const long long* __restrict__ step_base) {
+  // bias corrections from the step count; the count may live on the device so a captured CUDA graph can be replayed
+  const double stepd = (double)step_index + (step_base ? (double)(*step_base) : 0.0);
+  const float bc1 = (float)(1.0 - pow((double)beta1, stepd)), bc2 = (float)(1.0 - pow((double)beta2, stepd));
   float* p = t.p[blockIdx.y]; float* m = t.m[blockIdx.y]; float* v = t.v[blockIdx.y];
   const float* g = t.g[blockIdx.y];
   const long long n = t.n[blockIdx.y];
@@ -72,13 +76,14 @@ extern "C" int b2c_multi_sumsq(float* const* g, const long long* n, int count, f
 }
 
 // One Adam step on `count` tensors; gnorm_sq (device scalar, nullable) drives the clip coefficient
-// min(1, max_norm / (sqrt(gnorm_sq) + 1e-6)).  step_index >= 1 is this optimizer's step count AFTER the increment.
+// min(1, max_norm / (sqrt(gnorm_sq) + 1e-6)).  The optimizer's step count AFTER the increment is
+// step_index + *step_base (step_base: device scalar, nullable) and must be >= 1.
 extern "C" int b2c_multi_adam(float* const* p, float* const* g, float* const* m, float* const* v, const long long* n,
                               int count, const float* gnorm_sq, float max_norm, float lr, float beta1, float beta2,
-                              float eps, int step_index, void* stream) {
+                              float eps, int step_index, const long long* step_base, void* stream) {
   TensorTable t;
   if (int rc = fill_table(t, p, g, m, v, n, count)) return rc;
-  const float bc1 = (float)(1.0 - pow((double)beta1, (double)step_index)), bc2 = (float)(1.0 - pow((double)beta2, (double)step_index));
-  multi_adam_kernel<<<dim3(128, count), 256, 0, (cudaStream_t)stream>>>(t, gnorm_sq, max_norm, lr, beta1, beta2, eps, bc1, bc2);
+  multi_adam_kernel<<<dim3(128, count), 256, 0, (cudaStream_t)stream>>>(t, gnorm_sq, max_norm, lr, beta1, beta2, eps,
+                                                                        step_index, step_base);
   return b2c_check_launch("multi_adam");
 }

@@ -59,7 +59,8 @@ int b2c_in_act_bwd2(const void* h, long long ldh, const void* g, long long ldg, 
                     long long ldgx, int N, int HW, int C, void* stream);
 int b2c_lrelu_bwd(const void* g, const void* a, void* out, long long n, float slope, void* stream);
 int b2c_copy_strided(const void* src, long long lds, void* dst, long long ldd, long long npix, int C, void* stream);
-int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsigned long long offset, void* stream);
+int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsigned long long offset,
+                     const long long* offset_base, void* stream); /* stream position = offset + *offset_base (device, nullable) */
 
 /* ---- spectral norm (torch spectral_norm.py:92-114); ws: ceil(R/32)*K + R floats of scratch ---- */
 int b2c_sn_power_iter(const float* W, float* u, float* v, float* sig, float* ws, int R, int K, int train, void* stream);
@@ -86,7 +87,7 @@ int b2c_pool_fc_bwd(const float* gdelta, const float* tanh_v, const float* poole
 int b2c_multi_sumsq(float* const* g, const long long* n, int count, float* out, void* stream);
 int b2c_multi_adam(float* const* p, float* const* g, float* const* m, float* const* v, const long long* n, int count,
                    const float* gnorm_sq, float max_norm, float lr, float beta1, float beta2, float eps, int step_index,
-                   void* stream);
+                   const long long* step_base, void* stream); /* step count = step_index + *step_base (device, nullable) */
 
 #ifdef __cplusplus
 }

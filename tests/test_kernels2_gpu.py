@@ -84,13 +84,17 @@ def test_lrelu_bwd_copy_dropout(L):
     L.call("b2c_copy_strided", a, 64, dst[..., 64:], 128, 4 * 64, 64)
     assert torch.equal(dst[..., 64:], a) and float(dst[..., :64].abs().sum()) == 0
     m = torch.empty(1 << 20, dtype=torch.uint8, device="cuda")
-    L.call("b2c_dropout_mask", m, m.numel(), 7, 0)
+    L.call("b2c_dropout_mask", m, m.numel(), 7, 0, None)
     assert set(m.unique().tolist()) == {0, 1} and abs(float(m.float().mean()) - 0.5) < 5e-3
     m2 = torch.empty_like(m)
-    L.call("b2c_dropout_mask", m2, m.numel(), 7, 0)
+    L.call("b2c_dropout_mask", m2, m.numel(), 7, 0, None)
     assert torch.equal(m, m2)
-    L.call("b2c_dropout_mask", m2, m.numel(), 8, 0)
+    L.call("b2c_dropout_mask", m2, m.numel(), 8, 0, None)
     assert not torch.equal(m, m2)
+    # stream position = host offset + device base (what a replayed CUDA graph advances)
+    L.call("b2c_dropout_mask", m, m.numel(), 7, 4096, None)
+    L.call("b2c_dropout_mask", m2, m.numel(), 7, 1024, torch.tensor([3072], dtype=torch.int64, device="cuda"))
+    assert torch.equal(m, m2)
 
 
 @pytest.mark.parametrize("R,K", [(64, 96), (128, 1024), (512, 4096)])
@@ -205,6 +209,7 @@ def test_clip_adam_matches_torch(L):
         dg = [x.cuda() for x in gs]
         L.call("b2c_multi_sumsq", arr(dg), cnt, n, nrm)
         assert abs(float(nrm.sqrt()) - float(tn)) / float(tn) < 1e-5
-        L.call("b2c_multi_adam", arr(dp), arr(dg), arr(dm), arr(dv), cnt, n, nrm, 1.0, 2e-4, 0.5, 0.999, 1e-8, step)
+        L.call("b2c_multi_adam", arr(dp), arr(dg), arr(dm), arr(dv), cnt, n, nrm, 1.0, 2e-4, 0.5, 0.999, 1e-8,
+               0 if step == 2 else step, torch.tensor([2], dtype=torch.int64, device="cuda") if step == 2 else None)
         for a, b in zip(dp, ref_p):
             assert rel(a, b) < 1e-6
