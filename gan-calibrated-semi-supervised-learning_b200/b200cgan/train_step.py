@@ -43,6 +43,38 @@ def allreduce_mean_(grads, group=None, world_size=None):
         off += g.numel()
 
 
+class HostPrefetcher:
+    """Double-buffered pinned-host -> device staging on a side stream, the data-loader half of the step: while step i
+    runs, the H2D copy of batch i+1 is already in flight.  submit(host tensors) enqueues a copy, take() returns the
+    device tensors of the oldest submitted batch (the current stream waits for its copy), release() marks them
+    reusable once the consumer has been enqueued."""
+
+    def __init__(self, example, device):
+        self.stream = torch.cuda.Stream(device)
+        self.bufs = [[torch.empty_like(t, device=device) for t in example] for _ in range(2)]
+        self.ready = [torch.cuda.Event() for _ in range(2)]
+        self.free = [torch.cuda.Event() for _ in range(2)]
+        self.n_sub = self.n_take = 0
+
+    def submit(self, host_tensors):
+        b = self.n_sub % 2
+        self.stream.wait_event(self.free[b])
+        with torch.cuda.stream(self.stream):
+            for d, h in zip(self.bufs[b], host_tensors):
+                d.copy_(h, non_blocking=True)
+            self.ready[b].record(self.stream)
+        self.n_sub += 1
+
+    def take(self):
+        b = self.n_take % 2
+        torch.cuda.current_stream().wait_event(self.ready[b])
+        self.n_take += 1
+        return self.bufs[b]
+
+    def release(self):
+        self.free[(self.n_take - 1) % 2].record(torch.cuda.current_stream())
+
+
 @dataclass
 class StepOutput:
     scalars: Dict[str, torch.Tensor] = field(default_factory=dict)

@@ -1,0 +1,217 @@
+// Parity-merged transposed convolution for Cout = 64 (sm_100a only): ConvTranspose2d(k4,s2,p1) fprop of the
+// generator's up3 / up4 (cgan/models.py:111-113) and the data gradient of every Conv2d(64 -> 128) (models.py:104,239).
+//
+// tapgemm.cu runs the four output parities (py,px) as four independent GEMMs with N = 64.  Those are bound by the
+// L2 -> shared-memory stream of the ACTIVATION operand: 16 boxes of [128 pixels x 64 channels] per 64-channel slice of
+// Cin, although only 9 distinct shifted boxes exist (parity (py,px) with tap (a,b) reads x[i+py+a-1, j+px+b-1], and
+// py+a-1, px+b-1 take the values -1, 0, +1).  Here one CTA owns all four parities of its 128 input-resolution pixels:
+// it walks the 9 shifts, loads each activation box ONCE and multiplies it against the 1, 2 or 4 weight slices
+// (parity, tap) that use that shift, into four 64-column accumulators side by side in TMEM (256 columns).
+// Staged bytes per pixel tile and 64-channel slice drop from 16*(16+8) = 384 KB to 9*16 + 16*8 = 272 KB.
+// Pipeline as in tapgemm.cu: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2-5 = epilogue; 2 CTAs per SM.
+// Activation boxes and weight slices travel through two separate mbarrier rings (a box is used by a variable number of
+// slices), produced and consumed in the same order, so both rings stay full: 96 KB in flight per CTA.
+#include "common.cuh"
+#include "tmap.h"
+
+using namespace b2c;
+
+struct ConvT64Params {
+  int N, H, W, Cin;      // input (N,H,W,Cin); output (N,2H,2W,64)
+  int BW, BH, BI;        // pixel box over the input grid, BW*BH*BI == 128
+  int tiles_x, tiles_y;
+  int kchunks;           // Cin / 64
+  __nv_bfloat16* y;
+  long long ldy;
+};
+
+namespace {
+constexpr int CT_NA = 3;                   // activation ring: [128 pixels][64 channels] bf16 boxes
+constexpr int CT_NB = 6;                   // weight ring: [64 cout][64 cin] bf16 slices (1, 2 or 4 consumed per box)
+constexpr int CT_A_BYTES = 128 * 128;
+constexpr int CT_SLICE_BYTES = 64 * 128;
+constexpr int CT_SMEM = CT_NA * CT_A_BYTES + CT_NB * CT_SLICE_BYTES + 256 + 1024;
+}  // namespace
+
+// Weight slices that read shift d in {-1,0,+1} along one axis: (parity bit, tap bit) pairs with parity + tap - 1 == d.
+__device__ __forceinline__ int axis_pairs(int d, int (&par)[2], int (&tap)[2]) {
+  if (d < 0) { par[0] = 0; tap[0] = 0; return 1; }
+  if (d > 0) { par[0] = 1; tap[0] = 1; return 1; }
+  par[0] = 0; tap[0] = 1; par[1] = 1; tap[1] = 0;
+  return 2;
+}
+
+__global__ void __launch_bounds__(192) convt64_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                      const __grid_constant__ CUtensorMap tmB, ConvT64Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + CT_NA * CT_A_BYTES;
+  uint64_t* fullA = reinterpret_cast<uint64_t*>(sB + CT_NB * CT_SLICE_BYTES);
+  uint64_t* emptyA = fullA + CT_NA;
+  uint64_t* fullB = emptyA + CT_NA;
+  uint64_t* emptyB = fullB + CT_NB;
+  uint64_t* tmem_full = emptyB + CT_NB;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile = blockIdx.x;
+  const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, tn = tile / (p.tiles_x * p.tiles_y);
+  const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < CT_NA; ++s) {
+      mbar_init(&fullA[s], 1);
+      mbar_init(&emptyA[s], 1);
+    }
+    for (int s = 0; s < CT_NB; ++s) {
+      mbar_init(&fullB[s], 1);
+      mbar_init(&emptyB[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<256>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int sa = 0, pa = 0, sb = 0, pb = 0;
+      for (int s = 0; s < 9; ++s) {
+        const int dy = s / 3 - 1, dx = s % 3 - 1;
+        int pyv[2], av[2], pxv[2], bv[2];
+        const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
+        for (int cc = 0; cc < p.kchunks; ++cc) {
+          mbar_wait(&emptyA[sa], pa ^ 1);
+          mbar_expect_tx(&fullA[sa], CT_A_BYTES);
+          tma_load_4d(sA + sa * CT_A_BYTES, &tmA, &fullA[sa], cc * 64, x0 + dx, y0 + dy, n0);
+          if (++sa == CT_NA) { sa = 0; pa ^= 1; }
+          for (int iy = 0; iy < ny; ++iy)
+            for (int ix = 0; ix < nx; ++ix) {
+              const int parity = pyv[iy] * 2 + pxv[ix], tap = av[iy] * 2 + bv[ix];
+              mbar_wait(&emptyB[sb], pb ^ 1);
+              mbar_expect_tx(&fullB[sb], CT_SLICE_BYTES);
+              tma_load_2d(sB + sb * CT_SLICE_BYTES, &tmB, &fullB[sb], tap * p.Cin + cc * 64, parity * 64);
+              if (++sb == CT_NB) { sb = 0; pb ^= 1; }
+            }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 0);
+      int sa = 0, pa = 0, sb = 0, pb = 0;
+      uint32_t touched = 0;  // parities whose accumulator already holds a partial sum
+      for (int s = 0; s < 9; ++s) {
+        const int dy = s / 3 - 1, dx = s % 3 - 1;
+        int pyv[2], av[2], pxv[2], bv[2];
+        const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
+        for (int cc = 0; cc < p.kchunks; ++cc) {
+          mbar_wait(&fullA[sa], pa);
+          const uint32_t a0 = smem_u32(sA + sa * CT_A_BYTES);
+          for (int iy = 0; iy < ny; ++iy)
+            for (int ix = 0; ix < nx; ++ix) {
+              const int parity = pyv[iy] * 2 + pxv[ix];
+              mbar_wait(&fullB[sb], pb);
+              tc_fence_after();
+              const uint32_t bs = smem_u32(sB + sb * CT_SLICE_BYTES);
+              const uint32_t had = (touched >> parity) & 1u;
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma_bf16(tmem_base + parity * 64, umma_desc_sw128(a0 + k * 32, 16, 1024),
+                          umma_desc_sw128(bs + k * 32, 16, 1024), idesc, (uint32_t)(had | (k != 0)));
+              touched |= 1u << parity;
+              umma_commit(&emptyB[sb]);
+              if (++sb == CT_NB) { sb = 0; pb ^= 1; }
+            }
+          umma_commit(&emptyA[sa]);
+          if (++sa == CT_NA) { sa = 0; pa ^= 1; }
+        }
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    const int r = q * 32 + lane;
+    const int bw = r % p.BW, bh = (r / p.BW) % p.BH, bi = r / (p.BW * p.BH);
+    const int n = n0 + bi;
+    const bool valid = n < p.N;
+    const int Ho = 2 * p.H, Wo = 2 * p.W;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int parity = 0; parity < 4; ++parity) {
+      const int oy = 2 * (y0 + bh) + (parity >> 1), ox = 2 * (x0 + bw) + (parity & 1);
+      __nv_bfloat16* dst = p.y + (((long long)n * Ho + oy) * Wo + ox) * p.ldy;
+#pragma unroll
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t v0[16], v1[16];
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + parity * 64 + c0;
+        tmem_ld16(taddr, v0);
+        tmem_ld16(taddr + 16, v1);
+        tmem_ld_wait();
+        if (valid) {
+          uint32_t o[16];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            o[j] = pack_bf16(__uint_as_float(v0[2 * j]), __uint_as_float(v0[2 * j + 1]));
+            o[8 + j] = pack_bf16(__uint_as_float(v1[2 * j]), __uint_as_float(v1[2 * j + 1]));
+          }
+          uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
+          d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+          d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+          d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
+          d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<256>(tmem_base);
+}
+
+// x: (N,H,W,Cin) bf16 with pixel stride ldx; wpack_t: [4 parities][64][4*Cin] bf16 (pack.cu); y: (N,2H,2W,64) bf16
+// with pixel stride ldy.  Called by b2c_convt4s2_bf16 (tapgemm.cu) when Cout == 64 and no bias is given.
+int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, int N, int H, int W,
+                    int Cin, void* stream) {
+  ConvT64Params p;
+  p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.kchunks = Cin / 64; p.y = (__nv_bfloat16*)y; p.ldy = ldy;
+  p.BW = W < 128 ? W : 128;
+  int rem = 128 / p.BW;
+  p.BH = H < rem ? H : rem;
+  p.BI = rem / p.BH;
+  B2C_REQUIRE(p.BW * p.BH * p.BI == 128 && p.BI <= 256, "convt64: unsupported spatial size %dx%d", H, W);
+  p.tiles_x = W / p.BW; p.tiles_y = H / p.BH;
+  const int tiles_n = (N + p.BI - 1) / p.BI;
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint64_t str[3] = {(uint64_t)2 * ldx, (uint64_t)2 * W * ldx, (uint64_t)2 * H * W * ldx};
+    uint32_t box[4] = {64, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BI};
+    if (int rc = b2c_make_tmap_bf16(&tmA, x, 4, dims, str, box)) return rc;
+  }
+  {
+    const uint64_t K = (uint64_t)4 * Cin;
+    uint64_t dims[2] = {K, 256};
+    uint64_t str[1] = {2 * K};
+    uint32_t box[2] = {64, 64};
+    if (int rc = b2c_make_tmap_bf16(&tmB, wpack_t, 2, dims, str, box)) return rc;
+  }
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(convt64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    if (e != cudaSuccess) {
+      b2c_set_error("cudaFuncSetAttribute(convt64): %s", cudaGetErrorString(e));
+      return B2C_ERR_CUDA;
+    }
+    attr_done = true;
+  }
+  convt64_kernel<<<p.tiles_x * p.tiles_y * tiles_n, 192, CT_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
+  return b2c_check_launch("convt64_kernel");
+}

@@ -13,6 +13,8 @@
 //               with Wd holding w[co][c][di+1-2fy][dj+1-2fx] where that tap exists, else 0.  fp32 NCHW output.
 // Pipeline: warp 0 = TMA producer, warp 1 = single-thread tcgen05.mma issuer (accumulator in TMEM),
 // warps 2-5 = epilogue (tcgen05.ld -> +bias -> bf16 -> NHWC stores).  2 CTAs/SM overlap epilogue with mainloop.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tmap.h"
 
@@ -319,7 +321,14 @@ extern "C" int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_
   return run_tapgemm(0, x, ldx, wpack_c, bias, y, ldy, N, H, W, Cin, Cout, stream);
 }
 
+int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, int N, int H, int W,
+                    int Cin, void* stream);  // convt64.cu
+
 extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y,
                                  long long ldy, int N, int H, int W, int Cin, int Cout, void* stream) {
+  static const bool merge = !(getenv("B2C_CONVT_MERGE") && getenv("B2C_CONVT_MERGE")[0] == '0');  // A/B switch for profiling
+  if (Cout == 64 && bias == nullptr && merge && Cin % 64 == 0 && ldx % 8 == 0 && ldy % 8 == 0 &&
+      ((uintptr_t)y & 15) == 0 && is_pow2(H) && is_pow2(W))
+    return b2c_run_convt64(x, ldx, wpack_t, y, ldy, N, H, W, Cin, stream);
   return run_tapgemm(1, x, ldx, wpack_t, bias, y, ldy, N, H, W, Cin, Cout, stream);
 }

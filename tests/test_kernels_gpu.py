@@ -52,7 +52,8 @@ def test_conv4s2(L, N, H, W, Cin, Cout):
 
 
 @pytest.mark.parametrize("N,H,W,Cin,Cout", [(2, 8, 8, 128, 64), (3, 16, 16, 64, 128), (2, 4, 4, 512, 256),
-                                            (1, 64, 64, 128, 64), (2, 128, 128, 128, 64), (5, 2, 2, 64, 64)])
+                                            (1, 64, 64, 128, 64), (2, 128, 128, 128, 64), (5, 2, 2, 64, 64),
+                                            (3, 32, 32, 256, 64), (130, 1, 1, 64, 64)])
 def test_convt4s2(L, N, H, W, Cin, Cout):
     g = torch.Generator().manual_seed(2)
     x = q(torch.randn(N, Cin, H, W, generator=g))
