@@ -148,12 +148,14 @@ def _conv_block(x, conv, slope, drop, training, skip=None, norm=True):
     if conv.in_channels < 64:
         assert not norm and drop is None
         return ops.FirstConv.apply(x, None, conv.param(), conv.bias, conv.weight_ctx(), slope)
-    z = ops.Conv4s2.apply(x, conv.param(), conv.bias, conv.weight_ctx(), norm)
     if not norm:
         raise NotImplementedError("un-normalised conv blocks with Cin >= 64 do not occur in the reference models")
+    wctx = conv.weight_ctx()
+    wctx.want_stats = True  # the InstanceNorm statistics come out of the GEMM epilogue
+    z = ops.Conv4s2.apply(x, conv.param(), conv.bias, wctx, norm)
     N, C, H, W = z.shape
     mask = drop.mask(N, H, W, C, z.device, training) if drop is not None else None
-    return ops.INAct.apply(z, slope, mask, skip)
+    return ops.INAct.apply(z, slope, mask, skip, wctx.take_stats())
 
 
 class UNetDown(nn.Module):
@@ -188,10 +190,12 @@ class UNetUp(nn.Module):
 
     def forward(self, x: torch.Tensor, skip_input: torch.Tensor) -> torch.Tensor:
         conv = self.model[0]
-        z = ops.ConvT4s2.apply(x, conv.weight, ops.WeightCtx(conv.weight))
+        wctx = ops.WeightCtx(conv.weight)
+        wctx.want_stats = True
+        z = ops.ConvT4s2.apply(x, conv.weight, wctx)
         N, C, H, W = z.shape
         mask = self.model[-1].mask(N, H, W, C, z.device, self.training) if self._has_drop else None
-        return ops.INAct.apply(z, 0.0, mask, skip_input)  # cat((x, skip), 1) written in place
+        return ops.INAct.apply(z, 0.0, mask, skip_input, wctx.take_stats())  # cat((x, skip), 1) written in place
 
 
 class GeneratorUNet(nn.Module):
@@ -225,9 +229,11 @@ class GeneratorUNet(nn.Module):
         u2 = self.up2(u1, d2)
         u3 = self.up3(u2, d1)
         conv = self.up4[0]
-        z = ops.ConvT4s2.apply(u3, conv.weight, ops.WeightCtx(conv.weight))
+        wctx = ops.WeightCtx(conv.weight)
+        wctx.want_stats = True
+        z = ops.ConvT4s2.apply(u3, conv.weight, wctx)
         fc = self.fc_delta[1]
-        return ops.INActPoolFC.apply(z, fc.weight, fc.bias, 0.0, self.delta_scale)
+        return ops.INActPoolFC.apply(z, fc.weight, fc.bias, 0.0, self.delta_scale, wctx.take_stats())
 
 
 class Discriminator(nn.Module):
@@ -259,6 +265,8 @@ class Discriminator(nn.Module):
         a = ops.FirstConv.apply(pred_patch, other_patch, c0.param(), c0.bias, c0.weight_ctx(), 0.2)  # cat fused
         for idx in (2, 5, 8):
             conv = self.model[idx]
-            z = ops.Conv4s2.apply(a, conv.param(), conv.bias, conv.weight_ctx(), True)
-            a = ops.INAct.apply(z, 0.2, None, None)
+            wctx = conv.weight_ctx()
+            wctx.want_stats = True
+            z = ops.Conv4s2.apply(a, conv.param(), conv.bias, wctx, True)
+            a = ops.INAct.apply(z, 0.2, None, None, wctx.take_stats())
         return ops.HeadConv.apply(a, self.model[11].weight)

@@ -53,6 +53,12 @@ class WeightCtx:
     def __init__(self, weight, sig=None, u=None, v=None):
         self.weight, self.sig, self.u, self.v = weight, sig, u, v
         self._c = self._t = None
+        self.want_stats = False  # ask the forward conv for the InstanceNorm statistics of its output ...
+        self._stats = None       # ... which take_stats() hands to INAct / INActPoolFC
+
+    def take_stats(self):
+        zs, self._stats = self._stats, None
+        return zs
 
     @property
     def inv_sigma(self):
@@ -85,20 +91,30 @@ class WeightCtx:
 
 
 # ------------------------------------------------------------------------------------------------ raw kernel helpers
-def _conv_raw(x, wctx, bias):
+def _stats_buf(N, C, device):
+    return torch.empty(N, C, 2, dtype=torch.float32, device=device)
+
+
+def _conv_raw(x, wctx, bias, want_stats=False):
     x = dense_nhwc(x)
     N, Cin, H, W = x.shape
     Cout = wctx.weight.shape[0]
     y = cl_empty(N, Cout, H // 2, W // 2, device=x.device)
-    _lib.call("b2c_conv4s2_bf16", x, Cin, wctx.pack_c(), bias, y, Cout, N, H, W, Cin, Cout)
+    zs = _stats_buf(N, Cout, x.device) if want_stats else None
+    _lib.call("b2c_conv4s2_bf16", x, Cin, wctx.pack_c(), bias, y, Cout, zs, N, H, W, Cin, Cout)
+    if want_stats:
+        wctx._stats = zs
     return y
 
 
-def _convt_raw(x, wpack_t, Cout):
+def _convt_raw(x, wpack_t, Cout, wctx=None):
     x, ld = as_nhwc(x)
     N, Cin, H, W = x.shape
     y = cl_empty(N, Cout, 2 * H, 2 * W, device=x.device)
-    _lib.call("b2c_convt4s2_bf16", x, ld, wpack_t, None, y, Cout, N, H, W, Cin, Cout)
+    zs = _stats_buf(N, Cout, x.device) if (wctx is not None and wctx.want_stats) else None
+    _lib.call("b2c_convt4s2_bf16", x, ld, wpack_t, None, y, Cout, zs, N, H, W, Cin, Cout)
+    if zs is not None:
+        wctx._stats = zs
     return y
 
 
@@ -122,7 +138,7 @@ class Conv4s2(torch.autograd.Function):
     def forward(ctx, x, weight, bias, wctx, bias_feeds_norm):
         ctx.wctx, ctx.has_bias, ctx.bias_feeds_norm = wctx, bias is not None, bias_feeds_norm
         ctx.save_for_backward(x)
-        return _conv_raw(x, wctx, bias)
+        return _conv_raw(x, wctx, bias, wctx.want_stats)
 
     @staticmethod
     def backward(ctx, gy):
@@ -171,7 +187,7 @@ class ConvT4s2(torch.autograd.Function):
     def forward(ctx, x, weight, wctx):
         ctx.wctx = wctx
         ctx.save_for_backward(x)
-        return _convt_raw(x, wctx.pack_t(), weight.shape[1])
+        return _convt_raw(x, wctx.pack_t(), weight.shape[1], wctx)
 
     @staticmethod
     @torch.autograd.function.once_differentiable
@@ -315,10 +331,11 @@ class INAct(torch.autograd.Function):
     keep-mask or None.  With `skip`, the result is cat((out, skip), 1) written in place (no separate concat pass)."""
 
     @staticmethod
-    def forward(ctx, z, slope, mask, skip):
+    def forward(ctx, z, slope, mask, skip, zs=None):
         z, ldz = as_nhwc(z)
         N, C, H, W = z.shape
-        zs = _in_stats(z, ldz)
+        if zs is None:
+            zs = _in_stats(z, ldz)
         Cs = 0 if skip is None else skip.shape[1]
         out = cl_empty(N, C + Cs, H, W, device=z.device)
         _lib.call("b2c_in_act_fwd", z, ldz, zs, mask, slope, out, C + Cs, None, 0, N, H * W, C)
@@ -337,7 +354,7 @@ class INAct(torch.autograd.Function):
             gz = INActBwd.apply(g[:, :ctx.C] if ctx.has_skip else g, z, zs, ctx.mask, ctx.slope)
         if ctx.has_skip and ctx.needs_input_grad[3]:
             gskip = g[:, ctx.C:]
-        return gz, None, None, gskip
+        return gz, None, None, gskip, None
 
 
 class INActBwd(torch.autograd.Function):
@@ -374,10 +391,11 @@ class INActPoolFC(torch.autograd.Function):
     without ever materialising the activated (B,64,S,S) tensor."""
 
     @staticmethod
-    def forward(ctx, z, fc_w, fc_b, slope, scale):
+    def forward(ctx, z, fc_w, fc_b, slope, scale, zs=None):
         z, ldz = as_nhwc(z)
         N, C, H, W = z.shape
-        zs = _in_stats(z, ldz)
+        if zs is None:
+            zs = _in_stats(z, ldz)
         ps = torch.empty(N, C, dtype=torch.float32, device=z.device)
         _lib.call("b2c_in_act_pool_fwd", z, ldz, zs, slope, ps, N, H * W, C)
         delta = torch.empty(N, 4, dtype=torch.float32, device=z.device)
@@ -399,7 +417,7 @@ class INActPoolFC(torch.autograd.Function):
         ws = torch.empty(N, C, 2, dtype=torch.float32, device=z.device)
         gz = cl_empty(N, C, H, W, device=z.device)
         _lib.call("b2c_in_act_bwd", None, 0, gvec, z, ldz, zs, None, ctx.slope, ws, gz, C, N, H * W, C)
-        return gz, dW, db, None, None
+        return gz, dW, db, None, None, None
 
 
 # ------------------------------------------------------------------------------------------------ PatchGAN head

@@ -23,6 +23,7 @@ struct ConvT64Params {
   int kchunks;           // Cin / 64
   __nv_bfloat16* y;
   long long ldy;
+  float* stats;          // nullable: [N][64][2] += per-(image, channel) (sum, sum of squares) of y; needs BI == 1
 };
 
 namespace {
@@ -144,30 +145,55 @@ __global__ void __launch_bounds__(192) convt64_kernel(const __grid_constant__ CU
     const int Ho = 2 * p.H, Wo = 2 * p.W;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
+    float2* red = reinterpret_cast<float2*>(sA);  // pipeline buffers are idle once tmem_full has fired
 #pragma unroll 1
-    for (int parity = 0; parity < 4; ++parity) {
-      const int oy = 2 * (y0 + bh) + (parity >> 1), ox = 2 * (x0 + bw) + (parity & 1);
-      __nv_bfloat16* dst = p.y + (((long long)n * Ho + oy) * Wo + ox) * p.ldy;
+    for (int c0 = 0; c0 < 64; c0 += 32) {
+      float f[32], sq[32];  // per-channel partial statistics of this pixel over the 4 parities
 #pragma unroll
-      for (int c0 = 0; c0 < 64; c0 += 32) {
+      for (int j = 0; j < 32; ++j) f[j] = sq[j] = 0.f;
+#pragma unroll 1
+      for (int parity = 0; parity < 4; ++parity) {
+        const int oy = 2 * (y0 + bh) + (parity >> 1), ox = 2 * (x0 + bw) + (parity & 1);
+        __nv_bfloat16* dst = p.y + (((long long)n * Ho + oy) * Wo + ox) * p.ldy;
         uint32_t v0[16], v1[16];
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + parity * 64 + c0;
         tmem_ld16(taddr, v0);
         tmem_ld16(taddr + 16, v1);
         tmem_ld_wait();
-        if (valid) {
-          uint32_t o[16];
+        uint32_t o[16];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            o[j] = pack_bf16(__uint_as_float(v0[2 * j]), __uint_as_float(v0[2 * j + 1]));
-            o[8 + j] = pack_bf16(__uint_as_float(v1[2 * j]), __uint_as_float(v1[2 * j + 1]));
-          }
+        for (int j = 0; j < 8; ++j) {
+          o[j] = pack_bf16(__uint_as_float(v0[2 * j]), __uint_as_float(v0[2 * j + 1]));
+          o[8 + j] = pack_bf16(__uint_as_float(v1[2 * j]), __uint_as_float(v1[2 * j + 1]));
+        }
+        if (valid) {
           uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
           d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
           d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
           d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
           d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
         }
+        if (p.stats) {  // statistics of the bf16-ROUNDED outputs (what the normalisation kernels will read)
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float2 t = unpack_bf16(o[j]);
+            f[2 * j] += t.x; f[2 * j + 1] += t.y;
+            sq[2 * j] += t.x * t.x; sq[2 * j + 1] += t.y * t.y;
+          }
+        }
+      }
+      if (p.stats) {  // lane L ends up with channel c0 + L of this warp's 32 pixels x 4 parities
+        const float s1 = warp_transpose_sum32(f), s2 = warp_transpose_sum32(sq);
+        red[q * 64 + c0 + lane] = make_float2(s1, s2);
+      }
+    }
+    if (p.stats) {  // combine the 4 epilogue warps, then one atomic per (channel, statistic) and CTA
+      named_bar_sync(1, 128);
+      if (r < 64) {
+        const float2 a = red[r], b = red[64 + r], c = red[128 + r], d = red[192 + r];
+        float* st = p.stats + ((long long)n0 * 64 + r) * 2;
+        atomicAdd(st, (a.x + b.x) + (c.x + d.x));
+        atomicAdd(st + 1, (a.y + b.y) + (c.y + d.y));
       }
     }
     tc_fence_before();
@@ -177,10 +203,13 @@ __global__ void __launch_bounds__(192) convt64_kernel(const __grid_constant__ CU
 }
 
 // x: (N,H,W,Cin) bf16 with pixel stride ldx; wpack_t: [4 parities][64][4*Cin] bf16 (pack.cu); y: (N,2H,2W,64) bf16
-// with pixel stride ldy.  Called by b2c_convt4s2_bf16 (tapgemm.cu) when Cout == 64 and no bias is given.
-int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, int N, int H, int W,
-                    int Cin, void* stream) {
+// with pixel stride ldy; stats as in b2c_convt4s2_bf16.  Called by b2c_convt4s2_bf16 (tapgemm.cu) when Cout == 64.
+extern "C" int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream);  // norm.cu
+
+int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, float* stats, int N, int H,
+                    int W, int Cin, void* stream) {
   ConvT64Params p;
+  p.stats = nullptr;
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.kchunks = Cin / 64; p.y = (__nv_bfloat16*)y; p.ldy = ldy;
   p.BW = W < 128 ? W : 128;
   int rem = 128 / p.BW;
@@ -212,6 +241,14 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, 
     }
     attr_done = true;
   }
+  const bool fuse_stats = stats && p.BI == 1;
+  if (fuse_stats) {
+    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * (size_t)N * 64, (cudaStream_t)stream);
+    if (e != cudaSuccess) { b2c_set_error("convt64 stats memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+    p.stats = stats;
+  }
   convt64_kernel<<<p.tiles_x * p.tiles_y * tiles_n, 192, CT_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
-  return b2c_check_launch("convt64_kernel");
+  int rc = b2c_check_launch("convt64_kernel");
+  if (rc == 0 && stats && !fuse_stats) rc = b2c_in_stats(y, ldy, stats, N, 4 * H * W, 64, stream);
+  return rc;
 }

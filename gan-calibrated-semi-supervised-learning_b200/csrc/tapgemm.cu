@@ -31,6 +31,7 @@ struct TapGemmParams {
   const float* bias;        // nullable, per output channel
   float* gx0;               // mode D1: fp32 (N,3,2Ho,2Wo) outputs (gx1 null when Cin = 3)
   float* gx1;
+  float* stats;             // nullable: [N][Cout][2] += per-(image, channel) (sum, sum of squares) of y; needs BI == 1
 };
 
 template <int BN>
@@ -160,26 +161,47 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
       tmem_ld16(taddr, v0);
       tmem_ld16(taddr + 16, v1);
       tmem_ld_wait();
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        f[j] = __uint_as_float(v0[j]);
+        f[16 + j] = __uint_as_float(v1[j]);
+      }
+      if (p.bias) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] += __ldg(p.bias + ncol0 + c0 + j);
+      }
       if (valid) {
         uint32_t o[16];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float a = __uint_as_float(v0[2 * j]), b = __uint_as_float(v0[2 * j + 1]);
-          float c = __uint_as_float(v1[2 * j]), d = __uint_as_float(v1[2 * j + 1]);
-          if (p.bias) {
-            a += __ldg(p.bias + ncol0 + c0 + 2 * j);
-            b += __ldg(p.bias + ncol0 + c0 + 2 * j + 1);
-            c += __ldg(p.bias + ncol0 + c0 + 16 + 2 * j);
-            d += __ldg(p.bias + ncol0 + c0 + 16 + 2 * j + 1);
-          }
-          o[j] = pack_bf16(a, b);
-          o[8 + j] = pack_bf16(c, d);
-        }
+        for (int j = 0; j < 16; ++j) o[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
         uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
         d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
         d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
         d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
         d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+      }
+      if (p.stats) {  // InstanceNorm statistics of this tile (all 128 rows belong to image n0): lane L gets channel c0 + L
+        float sq[32];   // of the bf16-ROUNDED values, i.e. of exactly what the normalisation kernels will read
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          f[j] = __bfloat162float(__float2bfloat16(f[j]));
+          sq[j] = f[j] * f[j];
+        }
+        const float s1 = warp_transpose_sum32(f), s2 = warp_transpose_sum32(sq);
+        // the pipeline buffers are idle once tmem_full has fired: use them to combine the 4 epilogue warps
+        float2* red = reinterpret_cast<float2*>(sA);
+        red[q * BN + c0 + lane] = make_float2(s1, s2);
+      }
+    }
+    if (BN != 32 && p.stats) {
+      named_bar_sync(1, 128);
+      const float2* red = reinterpret_cast<const float2*>(sA);
+      for (int c = r; c < BN; c += 128) {
+        const float2 a = red[c], b = red[BN + c], cc = red[2 * BN + c], d = red[3 * BN + c];
+        float* st = p.stats + ((long long)n0 * p.Cout + ncol0 + c) * 2;
+        atomicAdd(st, (a.x + b.x) + (cc.x + d.x));
+        atomicAdd(st + 1, (a.y + b.y) + (cc.y + d.y));
       }
     }
     tc_fence_before();
@@ -218,13 +240,15 @@ static int launch_tapgemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
   return b2c_check_launch("tapgemm_kernel");
 }
 
+extern "C" int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream);  // norm.cu
+
 static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack, const float* bias, void* y,
-                       long long ldy, int N, int H, int W, int Cin, int Cout, void* stream) {
+                       long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
   B2C_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "tapgemm: Cin=%d Cout=%d must be multiples of 64", Cin, Cout);
   B2C_REQUIRE(ldy % 8 == 0 && ((uintptr_t)y & 15) == 0, "tapgemm: output must be 16-byte aligned (ldy=%lld)", ldy);
   TapGemmParams p;
   p.mode = mode; p.N = N; p.Cin = Cin; p.Cout = Cout; p.kchunks = Cin / 64;
-  p.y = (__nv_bfloat16*)y; p.ldy = ldy; p.bias = bias; p.gx0 = p.gx1 = nullptr;
+  p.y = (__nv_bfloat16*)y; p.ldy = ldy; p.bias = bias; p.gx0 = p.gx1 = nullptr; p.stats = nullptr;
   int TH, TW;
   CUtensorMap tmA, tmB;
   if (mode == 0) {
@@ -261,10 +285,18 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     rc = b2c_make_tmap_bf16(&tmB, wpack, 2, dims, str, box);
     if (rc) return rc;
   }
+  const bool fuse_stats = stats && p.BI == 1;  // a tile must not straddle images
+  if (fuse_stats) {
+    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * (size_t)N * Cout, (cudaStream_t)stream);
+    if (e != cudaSuccess) { b2c_set_error("tapgemm stats memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+    p.stats = stats;
+  }
   dim3 grid(p.tiles_x * p.tiles_y * tiles_n, Cout / BN, mode == 0 ? 1 : 4);
-  if (BN == 256) return launch_tapgemm<256>(tmA, tmB, p, grid, (cudaStream_t)stream);
-  if (BN == 128) return launch_tapgemm<128>(tmA, tmB, p, grid, (cudaStream_t)stream);
-  return launch_tapgemm<64>(tmA, tmB, p, grid, (cudaStream_t)stream);
+  if (BN == 256) rc = launch_tapgemm<256>(tmA, tmB, p, grid, (cudaStream_t)stream);
+  else if (BN == 128) rc = launch_tapgemm<128>(tmA, tmB, p, grid, (cudaStream_t)stream);
+  else rc = launch_tapgemm<64>(tmA, tmB, p, grid, (cudaStream_t)stream);
+  if (rc == 0 && stats && !fuse_stats) rc = b2c_in_stats(y, ldy, stats, N, p.Ho * p.Wo, Cout, stream);  // tiny planes
+  return rc;
 }
 
 // Wd[(di*16 + dj*8 + c)][(tap9*64 + co)] for mode D1 (32 x 576 bf16), scaled by 1/sigma.
@@ -317,18 +349,18 @@ extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_
 }
 
 extern "C" int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* bias, void* y,
-                                long long ldy, int N, int H, int W, int Cin, int Cout, void* stream) {
-  return run_tapgemm(0, x, ldx, wpack_c, bias, y, ldy, N, H, W, Cin, Cout, stream);
+                                long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
+  return run_tapgemm(0, x, ldx, wpack_c, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
 }
 
-int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, int N, int H, int W,
-                    int Cin, void* stream);  // convt64.cu
+int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, float* stats, int N, int H,
+                    int W, int Cin, void* stream);  // convt64.cu
 
 extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y,
-                                 long long ldy, int N, int H, int W, int Cin, int Cout, void* stream) {
+                                 long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
   static const bool merge = !(getenv("B2C_CONVT_MERGE") && getenv("B2C_CONVT_MERGE")[0] == '0');  // A/B switch for profiling
   if (Cout == 64 && bias == nullptr && merge && Cin % 64 == 0 && ldx % 8 == 0 && ldy % 8 == 0 &&
       ((uintptr_t)y & 15) == 0 && is_pow2(H) && is_pow2(W))
-    return b2c_run_convt64(x, ldx, wpack_t, y, ldy, N, H, W, Cin, stream);
-  return run_tapgemm(1, x, ldx, wpack_t, bias, y, ldy, N, H, W, Cin, Cout, stream);
+    return b2c_run_convt64(x, ldx, wpack_t, y, ldy, stats, N, H, W, Cin, stream);
+  return run_tapgemm(1, x, ldx, wpack_t, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
 }

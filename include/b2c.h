@@ -23,11 +23,14 @@ int b2c_pack_w_t(const float* w, const float* inv_sigma, void* out_bf16, int D0,
 /* ---- tcgen05 implicit-GEMM convolutions ----
  * conv4s2 : nn.Conv2d(k4,s2,p1) fprop (cgan/models.py:57,236) and ConvTranspose2d dgrad.   x dense (N,H,W,Cin).
  * convt4s2: nn.ConvTranspose2d(k4,s2,p1) fprop (cgan/models.py:72,113) and Conv2d dgrad.   y is (N,2H,2W,Cout).
- * wgrad4s2: weight gradient of both (autograd of the above; cgan/cgan_train_enhanced.py:330,366). */
+ * wgrad4s2: weight gradient of both (autograd of the above; cgan/cgan_train_enhanced.py:330,366).
+ * stats (nullable, fp32 [N][Cout][2]) <- per-(image, channel) (sum, sum of squares) of the bf16 output, i.e. what
+ * b2c_in_stats computes: the InstanceNorm2d that follows every such conv (cgan/models.py:59,73,114,241) gets its
+ * statistics from the GEMM epilogue instead of re-reading the tensor. */
 int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* bias, void* y, long long ldy,
-                     int N, int H, int W, int Cin, int Cout, void* stream);
+                     float* stats, int N, int H, int W, int Cin, int Cout, void* stream);
 int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y, long long ldy,
-                      int N, int H, int W, int Cin, int Cout, void* stream);
+                      float* stats, int N, int H, int W, int Cin, int Cout, void* stream);
 int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* large, long long ldl, float* ws, float* dw,
                       int accumulate, int N, int Hs, int Ws, int Cs, int Cl, int sm_count, void* stream);
 

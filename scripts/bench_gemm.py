@@ -27,13 +27,13 @@ WGRAD = [(64, 64, 128, 64), (32, 32, 256, 128), (16, 16, 512, 256), (128, 128, 1
 if which in ("conv", "all"):
     for H, W, Cin, Cout in CONV:
         x, w, y = bf(B, H, W, Cin), bf(Cout, 16 * Cin), bf(B, H // 2, W // 2, Cout)
-        t = timeit(lambda: L.call("b2c_conv4s2_bf16", x, Cin, w, None, y, Cout, B, H, W, Cin, Cout))
+        t = timeit(lambda: L.call("b2c_conv4s2_bf16", x, Cin, w, None, y, Cout, None, B, H, W, Cin, Cout))
         fl = 2.0 * B * (H // 2) * (W // 2) * Cout * 16 * Cin
         print(f"conv4s2  ({B},{H},{W},{Cin},{Cout}): {t*1e3:8.1f} us {fl/t/1e9:7.0f} TFLOP/s")
 if which in ("convt", "all"):
     for H, W, Cin, Cout in CONVT:
         x, w, y = bf(B, H, W, Cin), bf(4, Cout, 4 * Cin), bf(B, 2 * H, 2 * W, Cout)
-        t = timeit(lambda: L.call("b2c_convt4s2_bf16", x, Cin, w, None, y, Cout, B, H, W, Cin, Cout))
+        t = timeit(lambda: L.call("b2c_convt4s2_bf16", x, Cin, w, None, y, Cout, None, B, H, W, Cin, Cout))
         fl = 2.0 * B * H * W * Cout * 16 * Cin
         print(f"convt4s2 ({B},{H},{W},{Cin},{Cout}): {t*1e3:8.1f} us {fl/t/1e9:7.0f} TFLOP/s")
 if which in ("wgrad", "all"):

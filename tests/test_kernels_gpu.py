@@ -45,7 +45,11 @@ def test_conv4s2(L, N, H, W, Cin, Cout):
     wp = torch.empty(Cout, 16 * Cin, dtype=torch.bfloat16, device="cuda")
     L.call("b2c_pack_w_c", w.cuda(), None, wp, Cout, Cin)
     y = torch.empty(N, H // 2, W // 2, Cout, dtype=torch.bfloat16, device="cuda")
-    L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, b.cuda(), y, Cout, N, H, W, Cin, Cout)
+    zs = torch.full((N, Cout, 2), 7.0, device="cuda")  # fused InstanceNorm statistics of the bf16 output
+    L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, b.cuda(), y, Cout, zs, N, H, W, Cin, Cout)
+    yf = y.float()
+    assert float((zs[:, :, 0] - yf.sum((1, 2))).abs().max()) < 1e-3 * float(yf.abs().sum((1, 2)).max())
+    assert rel(zs[:, :, 1], (yf * yf).sum((1, 2))) < 1e-4
     torch.cuda.synchronize()
     ref = F.conv2d(x, q(w), b, 2, 1)
     assert rel(nchw(y), ref) < 1e-2
@@ -61,7 +65,11 @@ def test_convt4s2(L, N, H, W, Cin, Cout):
     wp = torch.empty(4, Cout, 4 * Cin, dtype=torch.bfloat16, device="cuda")
     L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
     y = torch.empty(N, 2 * H, 2 * W, Cout, dtype=torch.bfloat16, device="cuda")
-    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, N, H, W, Cin, Cout)
+    zs = torch.full((N, Cout, 2), 7.0, device="cuda")
+    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, zs, N, H, W, Cin, Cout)
+    yf = y.float()
+    assert rel(zs[:, :, 1], (yf * yf).sum((1, 2))) < 1e-4
+    assert float((zs[:, :, 0] - yf.sum((1, 2))).abs().max()) < 1e-3 * float(yf.abs().sum((1, 2)).max())
     torch.cuda.synchronize()
     ref = F.conv_transpose2d(x, q(w), None, 2, 1)
     assert rel(nchw(y), ref) < 1e-2
@@ -76,7 +84,7 @@ def test_conv_dgrad_is_convt(L):
     wp = torch.empty(4, Cin, 4 * Cout, dtype=torch.bfloat16, device="cuda")
     L.call("b2c_pack_w_t", w.cuda(), None, wp, Cout, Cin)
     dx = torch.empty(N, H, W, Cin, dtype=torch.bfloat16, device="cuda")
-    L.call("b2c_convt4s2_bf16", nhwc(gy), Cout, wp, None, dx, Cin, N, H // 2, W // 2, Cout, Cin)
+    L.call("b2c_convt4s2_bf16", nhwc(gy), Cout, wp, None, dx, Cin, None, N, H // 2, W // 2, Cout, Cin)
     torch.cuda.synchronize()
     ref = torch.nn.grad.conv2d_input((N, Cin, H, W), q(w), gy, 2, 1)
     assert rel(nchw(dx), ref) < 1e-2
