@@ -34,18 +34,23 @@ struct TapGemmParams {
   float* stats;             // nullable: [N][Cout][2] += per-(image, channel) (sum, sum of squares) of y; needs BI == 1
 };
 
-template <int BN>
+// MT = number of 128-row pixel tiles per CTA.  The kernels are bound by the L2 -> shared-memory stream, so with MT = 2
+// every weight slice staged in shared memory feeds two accumulators (TMEM columns [0,BN) and [BN,2BN)): 87 instead of
+// 64 FLOP per staged byte at BN = 128, 131 instead of 87 at BN = 256.
+template <int BN, int MT>
 struct TapGemmCfg {
-  static constexpr int STAGES = (BN == 256) ? 2 : (BN == 128) ? 3 : (BN == 32 ? 6 : 4);
-  static constexpr int A_BYTES = 128 * 128;
+  static constexpr int STAGES = (MT == 2) ? (BN == 256 ? 3 : 2) : (BN == 256) ? 2 : (BN == 128) ? 3 : (BN == 32 ? 6 : 4);
+  static constexpr int A_BYTES = MT * 128 * 128;
   static constexpr int B_BYTES = BN * 128;
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;
+  static constexpr int THREADS = 64 + 128 * MT;
+  static constexpr int TMEM_COLS = BN * MT;
 };
 
-template <int BN>
-__global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                      const __grid_constant__ CUtensorMap tmB, TapGemmParams p) {
-  using Cfg = TapGemmCfg<BN>;
+template <int BN, int MT>
+__global__ void __launch_bounds__(64 + 128 * MT) tapgemm_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                const __grid_constant__ CUtensorMap tmB, TapGemmParams p) {
+  using Cfg = TapGemmCfg<BN, MT>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -75,7 +80,7 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<BN>(tmem_slot);
+  if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -114,9 +119,11 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
         tc_fence_after();
         const uint32_t a0 = smem_u32(sA + stage * Cfg::A_BYTES), b0 = smem_u32(sB + stage * Cfg::B_BYTES);
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          umma_bf16(tmem_base, umma_desc_sw128(a0 + k * 32, 16, 1024), umma_desc_sw128(b0 + k * 32, 16, 1024), idesc,
-                    (uint32_t)((it | k) != 0));
+        for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(tmem_base + mt * BN, umma_desc_sw128(a0 + mt * 16384 + k * 32, 16, 1024),
+                      umma_desc_sw128(b0 + k * 32, 16, 1024), idesc, (uint32_t)((it | k) != 0));
         umma_commit(&empty[stage]);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
@@ -124,7 +131,9 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
     }
   } else {
     const int q = warp & 3;  // TMEM lane quarter this warp may read
-    const int r = q * 32 + lane;
+    const int mt = (warp - 2) >> 2;
+    const int r = mt * 128 + q * 32 + lane;  // row of the CTA's pixel box
+    const uint32_t tmem_acc = tmem_base + mt * BN;
     const int bw = r % p.BW, bh = (r / p.BW) % p.BH, bi = r / (p.BW * p.BH);
     const int n = n0 + bi;
     int oy = y0 + bh, ox = x0 + bw;
@@ -135,7 +144,7 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
     tc_fence_after();
     if (BN == 32) {  // mode D1: column = di*16 + dj*8 + c  ->  fp32 NCHW, one float2 (dj = 0,1) per (c, di)
       uint32_t v0[16], v1[16];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+      const uint32_t taddr = tmem_acc + ((uint32_t)(q * 32) << 16);
       tmem_ld16(taddr, v0);
       tmem_ld16(taddr + 16, v1);
       tmem_ld_wait();
@@ -157,7 +166,7 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
 #pragma unroll 1
     for (int c0 = 0; c0 < BN; c0 += 32) {
       uint32_t v0[16], v1[16];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + c0;
+      const uint32_t taddr = tmem_acc + ((uint32_t)(q * 32) << 16) + c0;
       tmem_ld16(taddr, v0);
       tmem_ld16(taddr + 16, v1);
       tmem_ld_wait();
@@ -191,23 +200,25 @@ __global__ void __launch_bounds__(192) tapgemm_kernel(const __grid_constant__ CU
         const float s1 = warp_transpose_sum32(f), s2 = warp_transpose_sum32(sq);
         // the pipeline buffers are idle once tmem_full has fired: use them to combine the 4 epilogue warps
         float2* red = reinterpret_cast<float2*>(sA);
-        red[q * BN + c0 + lane] = make_float2(s1, s2);
+        red[(warp - 2) * BN + c0 + lane] = make_float2(s1, s2);
       }
     }
     if (BN != 32 && p.stats) {
-      named_bar_sync(1, 128);
+      named_bar_sync(1, 128 * MT);
       const float2* red = reinterpret_cast<const float2*>(sA);
-      for (int c = r; c < BN; c += 128) {
-        const float2 a = red[c], b = red[BN + c], cc = red[2 * BN + c], d = red[3 * BN + c];
+      for (int c = r; c < BN; c += 128 * MT) {
+        float sx = 0.f, sy = 0.f;
+#pragma unroll
+        for (int w = 0; w < 4 * MT; ++w) { sx += red[w * BN + c].x; sy += red[w * BN + c].y; }
         float* st = p.stats + ((long long)n0 * p.Cout + ncol0 + c) * 2;
-        atomicAdd(st, (a.x + b.x) + (cc.x + d.x));
-        atomicAdd(st + 1, (a.y + b.y) + (cc.y + d.y));
+        atomicAdd(st, sx);
+        atomicAdd(st + 1, sy);
       }
     }
     tc_fence_before();
   }
   __syncthreads();
-  if (warp == 1) tmem_dealloc<BN>(tmem_base);
+  if (warp == 1) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -223,20 +234,20 @@ static int pick_box(int TH, int TW, int rows, int* BW, int* BH, int* BI) {
   return (*BW) * (*BH) * (*BI) == rows && *BI <= 256;
 }
 
-template <int BN>
+template <int BN, int MT = 1>
 static int launch_tapgemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const TapGemmParams& p, dim3 grid,
                           cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(tapgemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         TapGemmCfg<BN>::SMEM);
+    cudaError_t e = cudaFuncSetAttribute(tapgemm_kernel<BN, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         TapGemmCfg<BN, MT>::SMEM);
     if (e != cudaSuccess) {
       b2c_set_error("cudaFuncSetAttribute(tapgemm): %s", cudaGetErrorString(e));
       return B2C_ERR_CUDA;
     }
     attr_done = true;
   }
-  tapgemm_kernel<BN><<<grid, 192, TapGemmCfg<BN>::SMEM, st>>>(tmA, tmB, p);
+  tapgemm_kernel<BN, MT><<<grid, TapGemmCfg<BN, MT>::THREADS, TapGemmCfg<BN, MT>::SMEM, st>>>(tmA, tmB, p);
   return b2c_check_launch("tapgemm_kernel");
 }
 
@@ -259,7 +270,12 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     B2C_REQUIRE(ldx % 8 == 0, "convt4s2: ldx=%lld must be a multiple of 8", ldx);
     p.Ho = 2 * H; p.Wo = 2 * W; TH = H; TW = W;
   }
-  B2C_REQUIRE(pick_box(TH, TW, 128, &p.BW, &p.BH, &p.BI), "tapgemm: unsupported spatial size %dx%d (need powers of two)", TH, TW);
+  const int BN = (Cout % 256 == 0) ? 256 : (Cout % 128 == 0) ? 128 : 64;
+  // two pixel tiles per CTA when the weight operand is wide enough to be worth sharing and there are enough tiles
+  static const bool allow_mt2 = !(getenv("B2C_TAPGEMM_MT2") && getenv("B2C_TAPGEMM_MT2")[0] == '0');
+  int MT = 1;
+  if (allow_mt2 && BN >= 128 && (long long)N * TH * TW >= 256LL * 64) MT = 2;
+  B2C_REQUIRE(pick_box(TH, TW, 128 * MT, &p.BW, &p.BH, &p.BI), "tapgemm: unsupported spatial size %dx%d (need powers of two)", TH, TW);
   p.tiles_x = TW / p.BW; p.tiles_y = TH / p.BH;
   const int tiles_n = (N + p.BI - 1) / p.BI;
   int rc;
@@ -275,7 +291,6 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     rc = b2c_make_tmap_bf16(&tmA, x, 4, dims, str, box);
   }
   if (rc) return rc;
-  const int BN = (Cout % 256 == 0) ? 256 : (Cout % 128 == 0) ? 128 : 64;
   const int K = (mode == 0 ? 16 : 4) * Cin;
   const int rows = (mode == 0 ? 1 : 4) * Cout;
   {
@@ -292,7 +307,9 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     p.stats = stats;
   }
   dim3 grid(p.tiles_x * p.tiles_y * tiles_n, Cout / BN, mode == 0 ? 1 : 4);
-  if (BN == 256) rc = launch_tapgemm<256>(tmA, tmB, p, grid, (cudaStream_t)stream);
+  if (BN == 256 && MT == 2) rc = launch_tapgemm<256, 2>(tmA, tmB, p, grid, (cudaStream_t)stream);
+  else if (BN == 128 && MT == 2) rc = launch_tapgemm<128, 2>(tmA, tmB, p, grid, (cudaStream_t)stream);
+  else if (BN == 256) rc = launch_tapgemm<256>(tmA, tmB, p, grid, (cudaStream_t)stream);
   else if (BN == 128) rc = launch_tapgemm<128>(tmA, tmB, p, grid, (cudaStream_t)stream);
   else rc = launch_tapgemm<64>(tmA, tmB, p, grid, (cudaStream_t)stream);
   if (rc == 0 && stats && !fuse_stats) rc = b2c_in_stats(y, ldy, stats, N, p.Ho * p.Wo, Cout, stream);  // tiny planes

@@ -33,7 +33,8 @@ def L():
 
 
 CONV_CASES = [(2, 16, 16, 64, 128), (3, 32, 32, 64, 64), (2, 8, 8, 256, 512), (1, 128, 128, 64, 128), (5, 4, 4, 128, 256),
-              (2, 256, 256, 64, 64)]
+              (2, 256, 256, 64, 64),
+              (4, 128, 128, 64, 128), (17, 64, 64, 64, 256), (65, 32, 32, 128, 128)]  # two pixel tiles per CTA (MT = 2)
 
 
 @pytest.mark.parametrize("N,H,W,Cin,Cout", CONV_CASES)
@@ -57,7 +58,8 @@ def test_conv4s2(L, N, H, W, Cin, Cout):
 
 @pytest.mark.parametrize("N,H,W,Cin,Cout", [(2, 8, 8, 128, 64), (3, 16, 16, 64, 128), (2, 4, 4, 512, 256),
                                             (1, 64, 64, 128, 64), (2, 128, 128, 128, 64), (5, 2, 2, 64, 64),
-                                            (3, 32, 32, 256, 64), (130, 1, 1, 64, 64)])
+                                            (3, 32, 32, 256, 64), (130, 1, 1, 64, 64),
+                                            (16, 32, 32, 128, 128), (65, 16, 16, 64, 256)])  # MT = 2
 def test_convt4s2(L, N, H, W, Cin, Cout):
     g = torch.Generator().manual_seed(2)
     x = q(torch.randn(N, Cin, H, W, generator=g))
