@@ -8,9 +8,9 @@
 // it walks the 9 shifts, loads each activation box ONCE and multiplies it against the 1, 2 or 4 weight slices
 // (parity, tap) that use that shift, into four 64-column accumulators side by side in TMEM (256 columns).
 // Staged bytes per pixel tile and 64-channel slice drop from 16*(16+8) = 384 KB to 9*16 + 16*8 = 272 KB.
-// Pipeline as in tapgemm.cu: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2-5 = epilogue; 2 CTAs per SM.
+// Warp roles as in tapgemm.cu: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2-5 = epilogue.
 // Activation boxes and weight slices travel through two separate mbarrier rings (a box is used by a variable number of
-// slices), produced and consumed in the same order, so both rings stay full: 96 KB in flight per CTA.
+// slices), produced and consumed in the same order, so both rings stay full: 192 KB in flight per SM.
 #include "common.cuh"
 #include "tmap.h"
 
@@ -27,11 +27,12 @@ struct ConvT64Params {
 };
 
 namespace {
-constexpr int CT_NA = 3;                   // activation ring: [128 pixels][64 channels] bf16 boxes
-constexpr int CT_NB = 6;                   // weight ring: [64 cout][64 cin] bf16 slices (1, 2 or 4 consumed per box)
+constexpr int CT_NA = 6;                   // activation ring: [128 pixels][64 channels] bf16 boxes
+constexpr int CT_NB = 12;                  // weight ring: [64 cout][64 cin] bf16 slices (1, 2 or 4 consumed per box)
 constexpr int CT_A_BYTES = 128 * 128;
 constexpr int CT_SLICE_BYTES = 64 * 128;
-constexpr int CT_SMEM = CT_NA * CT_A_BYTES + CT_NB * CT_SLICE_BYTES + 256 + 1024;
+constexpr int CT_RED_BYTES = 4 * 64 * 8;   // statistics scratch of the 4 epilogue warps
+constexpr int CT_SMEM = CT_NA * CT_A_BYTES + CT_NB * CT_SLICE_BYTES + CT_RED_BYTES + 512 + 1024;
 }  // namespace
 
 // Weight slices that read shift d in {-1,0,+1} along one axis: (parity bit, tap bit) pairs with parity + tap - 1 == d.
@@ -42,23 +43,26 @@ __device__ __forceinline__ int axis_pairs(int d, int (&par)[2], int (&tap)[2]) {
   return 2;
 }
 
-__global__ void __launch_bounds__(192) convt64_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                      const __grid_constant__ CUtensorMap tmB, ConvT64Params p) {
+// PERSISTENT: one CTA per SM walks pixel tiles blockIdx.x, blockIdx.x + gridDim.x, ...  The TMA producer runs ahead
+// across tile boundaries (the rings never drain), and the 512 TMEM columns hold two 256-column accumulator sets, so the
+// epilogue of tile i (TMEM -> bf16 NHWC stores + InstanceNorm statistics) overlaps the MMAs of tile i + 1.
+__global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                         const __grid_constant__ CUtensorMap tmB, ConvT64Params p,
+                                                         int ntiles) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + CT_NA * CT_A_BYTES;
-  uint64_t* fullA = reinterpret_cast<uint64_t*>(sB + CT_NB * CT_SLICE_BYTES);
+  float2* red = reinterpret_cast<float2*>(sB + CT_NB * CT_SLICE_BYTES);
+  uint64_t* fullA = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(red) + CT_RED_BYTES);
   uint64_t* emptyA = fullA + CT_NA;
   uint64_t* fullB = emptyA + CT_NA;
   uint64_t* emptyB = fullB + CT_NB;
-  uint64_t* tmem_full = emptyB + CT_NB;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tmem_full = emptyB + CT_NB;   // [2]
+  uint64_t* tmem_empty = tmem_full + 2;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tile = blockIdx.x;
-  const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, tn = tile / (p.tiles_x * p.tiles_y);
-  const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -71,10 +75,13 @@ __global__ void __launch_bounds__(192) convt64_kernel(const __grid_constant__ CU
       mbar_init(&fullB[s], 1);
       mbar_init(&emptyB[s], 1);
     }
-    mbar_init(tmem_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 4);  // one arrival per epilogue warp
+    }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<256>(tmem_slot);
+  if (warp == 1) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -83,123 +90,144 @@ __global__ void __launch_bounds__(192) convt64_kernel(const __grid_constant__ CU
   if (warp == 0) {
     if (elect_one()) {
       int sa = 0, pa = 0, sb = 0, pb = 0;
-      for (int s = 0; s < 9; ++s) {
-        const int dy = s / 3 - 1, dx = s % 3 - 1;
-        int pyv[2], av[2], pxv[2], bv[2];
-        const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
-        for (int cc = 0; cc < p.kchunks; ++cc) {
-          mbar_wait(&emptyA[sa], pa ^ 1);
-          mbar_expect_tx(&fullA[sa], CT_A_BYTES);
-          tma_load_4d(sA + sa * CT_A_BYTES, &tmA, &fullA[sa], cc * 64, x0 + dx, y0 + dy, n0);
-          if (++sa == CT_NA) { sa = 0; pa ^= 1; }
-          for (int iy = 0; iy < ny; ++iy)
-            for (int ix = 0; ix < nx; ++ix) {
-              const int parity = pyv[iy] * 2 + pxv[ix], tap = av[iy] * 2 + bv[ix];
-              mbar_wait(&emptyB[sb], pb ^ 1);
-              mbar_expect_tx(&fullB[sb], CT_SLICE_BYTES);
-              tma_load_2d(sB + sb * CT_SLICE_BYTES, &tmB, &fullB[sb], tap * p.Cin + cc * 64, parity * 64);
-              if (++sb == CT_NB) { sb = 0; pb ^= 1; }
-            }
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, tn = tile / (p.tiles_x * p.tiles_y);
+        const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
+        for (int s = 0; s < 9; ++s) {
+          const int dy = s / 3 - 1, dx = s % 3 - 1;
+          int pyv[2], av[2], pxv[2], bv[2];
+          const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
+          for (int cc = 0; cc < p.kchunks; ++cc) {
+            mbar_wait(&emptyA[sa], pa ^ 1);
+            mbar_expect_tx(&fullA[sa], CT_A_BYTES);
+            tma_load_4d(sA + sa * CT_A_BYTES, &tmA, &fullA[sa], cc * 64, x0 + dx, y0 + dy, n0);
+            if (++sa == CT_NA) { sa = 0; pa ^= 1; }
+            for (int iy = 0; iy < ny; ++iy)
+              for (int ix = 0; ix < nx; ++ix) {
+                const int parity = pyv[iy] * 2 + pxv[ix], tap = av[iy] * 2 + bv[ix];
+                mbar_wait(&emptyB[sb], pb ^ 1);
+                mbar_expect_tx(&fullB[sb], CT_SLICE_BYTES);
+                tma_load_2d(sB + sb * CT_SLICE_BYTES, &tmB, &fullB[sb], tap * p.Cin + cc * 64, parity * 64);
+                if (++sb == CT_NB) { sb = 0; pb ^= 1; }
+              }
+          }
         }
       }
     }
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 0);
-      int sa = 0, pa = 0, sb = 0, pb = 0;
-      uint32_t touched = 0;  // parities whose accumulator already holds a partial sum
-      for (int s = 0; s < 9; ++s) {
-        const int dy = s / 3 - 1, dx = s % 3 - 1;
-        int pyv[2], av[2], pxv[2], bv[2];
-        const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
-        for (int cc = 0; cc < p.kchunks; ++cc) {
-          mbar_wait(&fullA[sa], pa);
-          const uint32_t a0 = smem_u32(sA + sa * CT_A_BYTES);
-          for (int iy = 0; iy < ny; ++iy)
-            for (int ix = 0; ix < nx; ++ix) {
-              const int parity = pyv[iy] * 2 + pxv[ix];
-              mbar_wait(&fullB[sb], pb);
-              tc_fence_after();
-              const uint32_t bs = smem_u32(sB + sb * CT_SLICE_BYTES);
-              const uint32_t had = (touched >> parity) & 1u;
+      int sa = 0, pa = 0, sb = 0, pb = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+        const int buf = lt & 1;
+        const uint32_t acc = tmem_base + buf * 256;
+        mbar_wait(&tmem_empty[buf], ((lt >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator set
+        tc_fence_after();
+        uint32_t touched = 0;  // parities whose accumulator already holds a partial sum
+        for (int s = 0; s < 9; ++s) {
+          const int dy = s / 3 - 1, dx = s % 3 - 1;
+          int pyv[2], av[2], pxv[2], bv[2];
+          const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
+          for (int cc = 0; cc < p.kchunks; ++cc) {
+            mbar_wait(&fullA[sa], pa);
+            const uint32_t a0 = smem_u32(sA + sa * CT_A_BYTES);
+            for (int iy = 0; iy < ny; ++iy)
+              for (int ix = 0; ix < nx; ++ix) {
+                const int parity = pyv[iy] * 2 + pxv[ix];
+                mbar_wait(&fullB[sb], pb);
+                tc_fence_after();
+                const uint32_t bs = smem_u32(sB + sb * CT_SLICE_BYTES);
+                const uint32_t had = (touched >> parity) & 1u;
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
-                umma_bf16(tmem_base + parity * 64, umma_desc_sw128(a0 + k * 32, 16, 1024),
-                          umma_desc_sw128(bs + k * 32, 16, 1024), idesc, (uint32_t)(had | (k != 0)));
-              touched |= 1u << parity;
-              umma_commit(&emptyB[sb]);
-              if (++sb == CT_NB) { sb = 0; pb ^= 1; }
-            }
-          umma_commit(&emptyA[sa]);
-          if (++sa == CT_NA) { sa = 0; pa ^= 1; }
+                for (int k = 0; k < 4; ++k)
+                  umma_bf16(acc + parity * 64, umma_desc_sw128(a0 + k * 32, 16, 1024),
+                            umma_desc_sw128(bs + k * 32, 16, 1024), idesc, (uint32_t)(had | (k != 0)));
+                touched |= 1u << parity;
+                umma_commit(&emptyB[sb]);
+                if (++sb == CT_NB) { sb = 0; pb ^= 1; }
+              }
+            umma_commit(&emptyA[sa]);
+            if (++sa == CT_NA) { sa = 0; pa ^= 1; }
+          }
         }
+        umma_commit(&tmem_full[buf]);
       }
-      umma_commit(tmem_full);
     }
   } else {
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     const int r = q * 32 + lane;
     const int bw = r % p.BW, bh = (r / p.BW) % p.BH, bi = r / (p.BW * p.BH);
-    const int n = n0 + bi;
-    const bool valid = n < p.N;
     const int Ho = 2 * p.H, Wo = 2 * p.W;
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
-    float2* red = reinterpret_cast<float2*>(sA);  // pipeline buffers are idle once tmem_full has fired
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+      const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, tn = tile / (p.tiles_x * p.tiles_y);
+      const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
+      const int n = n0 + bi;
+      const bool valid = n < p.N;
+      const int buf = lt & 1;
+      const uint32_t acc = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
+      mbar_wait(&tmem_full[buf], (lt >> 1) & 1);
+      tc_fence_after();
 #pragma unroll 1
-    for (int c0 = 0; c0 < 64; c0 += 32) {
-      float f[32], sq[32];  // per-channel partial statistics of this pixel over the 4 parities
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        float f[32], sq[32];  // per-channel partial statistics of this pixel over the 4 parities
 #pragma unroll
-      for (int j = 0; j < 32; ++j) f[j] = sq[j] = 0.f;
+        for (int j = 0; j < 32; ++j) f[j] = sq[j] = 0.f;
 #pragma unroll 1
-      for (int parity = 0; parity < 4; ++parity) {
-        const int oy = 2 * (y0 + bh) + (parity >> 1), ox = 2 * (x0 + bw) + (parity & 1);
-        __nv_bfloat16* dst = p.y + (((long long)n * Ho + oy) * Wo + ox) * p.ldy;
-        uint32_t v0[16], v1[16];
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + parity * 64 + c0;
-        tmem_ld16(taddr, v0);
-        tmem_ld16(taddr + 16, v1);
-        tmem_ld_wait();
-        uint32_t o[16];
+        for (int parity = 0; parity < 4; ++parity) {
+          const int oy = 2 * (y0 + bh) + (parity >> 1), ox = 2 * (x0 + bw) + (parity & 1);
+          __nv_bfloat16* dst = p.y + (((long long)n * Ho + oy) * Wo + ox) * p.ldy;
+          uint32_t v0[16], v1[16];
+          tmem_ld16(acc + parity * 64 + c0, v0);
+          tmem_ld16(acc + parity * 64 + c0 + 16, v1);
+          tmem_ld_wait();
+          if (c0 == 32 && parity == 3) {  // last read of this accumulator set: hand it back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+          }
+          uint32_t o[16];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          o[j] = pack_bf16(__uint_as_float(v0[2 * j]), __uint_as_float(v0[2 * j + 1]));
-          o[8 + j] = pack_bf16(__uint_as_float(v1[2 * j]), __uint_as_float(v1[2 * j + 1]));
-        }
-        if (valid) {
-          uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
-          d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
-          d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
-          d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
-          d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
-        }
-        if (p.stats) {  // statistics of the bf16-ROUNDED outputs (what the normalisation kernels will read)
+          for (int j = 0; j < 8; ++j) {
+            o[j] = pack_bf16(__uint_as_float(v0[2 * j]), __uint_as_float(v0[2 * j + 1]));
+            o[8 + j] = pack_bf16(__uint_as_float(v1[2 * j]), __uint_as_float(v1[2 * j + 1]));
+          }
+          if (valid) {
+            uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
+            d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+            d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+            d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
+            d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+          }
+          if (p.stats) {  // statistics of the bf16-ROUNDED outputs (what the normalisation kernels will read)
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float2 t = unpack_bf16(o[j]);
-            f[2 * j] += t.x; f[2 * j + 1] += t.y;
-            sq[2 * j] += t.x * t.x; sq[2 * j + 1] += t.y * t.y;
+            for (int j = 0; j < 16; ++j) {
+              const float2 t = unpack_bf16(o[j]);
+              f[2 * j] += t.x; f[2 * j + 1] += t.y;
+              sq[2 * j] += t.x * t.x; sq[2 * j + 1] += t.y * t.y;
+            }
           }
         }
+        if (p.stats) {  // lane L ends up with channel c0 + L of this warp's 32 pixels x 4 parities
+          const float s1 = warp_transpose_sum32(f), s2 = warp_transpose_sum32(sq);
+          red[q * 64 + c0 + lane] = make_float2(s1, s2);
+        }
       }
-      if (p.stats) {  // lane L ends up with channel c0 + L of this warp's 32 pixels x 4 parities
-        const float s1 = warp_transpose_sum32(f), s2 = warp_transpose_sum32(sq);
-        red[q * 64 + c0 + lane] = make_float2(s1, s2);
+      if (p.stats) {  // combine the 4 epilogue warps, then one atomic per (channel, statistic) and tile
+        named_bar_sync(1, 128);
+        if (r < 64) {
+          const float2 a = red[r], b = red[64 + r], c = red[128 + r], d = red[192 + r];
+          float* st = p.stats + ((long long)n0 * 64 + r) * 2;
+          atomicAdd(st, (a.x + b.x) + (c.x + d.x));
+          atomicAdd(st + 1, (a.y + b.y) + (c.y + d.y));
+        }
+        named_bar_sync(1, 128);  // scratch may be overwritten by the next tile
       }
     }
-    if (p.stats) {  // combine the 4 epilogue warps, then one atomic per (channel, statistic) and CTA
-      named_bar_sync(1, 128);
-      if (r < 64) {
-        const float2 a = red[r], b = red[64 + r], c = red[128 + r], d = red[192 + r];
-        float* st = p.stats + ((long long)n0 * 64 + r) * 2;
-        atomicAdd(st, (a.x + b.x) + (c.x + d.x));
-        atomicAdd(st + 1, (a.y + b.y) + (c.y + d.y));
-      }
-    }
-    tc_fence_before();
   }
+  tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<256>(tmem_base);
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
 // x: (N,H,W,Cin) bf16 with pixel stride ldx; wpack_t: [4 parities][64][4*Cin] bf16 (pack.cu); y: (N,2H,2W,64) bf16
@@ -247,7 +275,14 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, 
     if (e != cudaSuccess) { b2c_set_error("convt64 stats memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
     p.stats = stats;
   }
-  convt64_kernel<<<p.tiles_x * p.tiles_y * tiles_n, 192, CT_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
+  const int ntiles = p.tiles_x * p.tiles_y * tiles_n;
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+  }
+  convt64_kernel<<<ntiles < sms ? ntiles : sms, 192, CT_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p, ntiles);
   int rc = b2c_check_launch("convt64_kernel");
   if (rc == 0 && stats && !fuse_stats) rc = b2c_in_stats(y, ldy, stats, N, 4 * H * W, 64, stream);
   return rc;

@@ -274,7 +274,7 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
   // two pixel tiles per CTA when the weight operand is wide enough to be worth sharing and there are enough tiles
   static const bool allow_mt2 = !(getenv("B2C_TAPGEMM_MT2") && getenv("B2C_TAPGEMM_MT2")[0] == '0');
   int MT = 1;
-  if (allow_mt2 && BN >= 128 && (long long)N * TH * TW >= 256LL * 64) MT = 2;
+  if (allow_mt2 && BN == 256 && (long long)N * TH * TW >= 256LL * 64) MT = 2;  // measured: no gain at BN = 128
   B2C_REQUIRE(pick_box(TH, TW, 128 * MT, &p.BW, &p.BH, &p.BI), "tapgemm: unsupported spatial size %dx%d (need powers of two)", TH, TW);
   p.tiles_x = TW / p.BW; p.tiles_y = TH / p.BH;
   const int tiles_n = (N + p.BI - 1) / p.BI;
