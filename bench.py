@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=4, help="patches per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="step eagerly instead of replaying the captured CUDA graph")
+    ap.add_argument("--mode", default="train", choices=["train", "infer"],
+                    help="infer = BASELINE configs[4]: generator-only eval forward (cgan/inference.py:170-171), default batch 256")
     return ap.parse_args()
 
 
@@ -332,9 +334,82 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def run_infer(args):
+    """BASELINE configs[4]: generator-only eval forward on B synthetic patches (pseudo-label calibration throughput).
+    One line, same keys; `value` = patches/s with inputs resident, `e2e` = through b200cgan.inference.calibrate_patches
+    (pinned host patches in, (B,4) deltas back on the host)."""
+    import torch
+    if args.impl == "reference":
+        sys.path.insert(0, str(ROOT / "oracle"))
+        import cgan_oracle as O
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        st = O.init_state(42)
+        x = torch.rand(args.cpu_sample, 3, args.img_size, args.img_size) * 2 - 1
+        ts = []
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            with torch.no_grad():
+                O.g_forward(st["G"], x, 0.3, train=False)
+            if i >= args.warmup:
+                ts.append(time.perf_counter() - t0)
+        v = args.cpu_sample * len(ts) / sum(ts)
+        print(json.dumps({"impl": "reference", "metric": "cgan_infer_patches_per_s", "value": v, "unit": UNIT,
+                          "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True,
+                          "dtype": "f32", "data": "synthetic",
+                          "config": {"workload": f"G eval forward, {args.img_size}x{args.img_size}, CPU sample of {args.cpu_sample}"},
+                          "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                           "sample": f"{args.cpu_sample} patches per forward"},
+                          "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+        return
+    from b200cgan import _lib, inference
+    from b200cgan.models import GeneratorUNet, weights_init_normal
+    S, B, K, W = args.img_size, (args.batch if args.batch != 64 else 256), args.steps, max(args.warmup, 3)
+    torch.manual_seed(42)
+    G = GeneratorUNet(0.3)
+    G.apply(weights_init_normal)
+    G = G.cuda().eval()
+    host = [(torch.rand(B, 3, S, S, generator=torch.Generator().manual_seed(i)) * 2 - 1).pin_memory() for i in range(2)]
+    dev = [h.cuda() for h in host]
+    with torch.no_grad():
+        for i in range(W):
+            G(dev[i % 2])
+        torch.cuda.synchronize()
+        l0 = _lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(K):
+            d = G(dev[i % 2])
+        e1.record()
+        torch.cuda.synchronize()
+        launches = _lib.launch_count() - l0
+        ms = e0.elapsed_time(e1)
+        inference.calibrate_patches(G, host[0], B)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for i in range(K):
+            out = inference.calibrate_patches(G, host[i % 2], B)
+        f1.record()
+        torch.cuda.synchronize()
+        ms2 = f0.elapsed_time(f1)
+    fg = conv_flops_per_patch(S)[0]
+    print(json.dumps({"metric": "cgan_infer_patches_per_s", "value": B * K / (ms / 1e3), "unit": UNIT, "n_gpus": 1,
+                      "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+                      "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                      "config": {"workload": f"BASELINE configs[4]: GeneratorUNet eval forward, batch {B} synthetic {S}x{S} patches",
+                                 "img_size": S, "batch_per_gpu": B, "l2": "two input batches alternate; activations (>1 GB) exceed L2"},
+                      "e2e": {"value": B * K / (ms2 / 1e3), "unit": UNIT, "h2d_bytes_per_step": host[0].numel() * 4,
+                              "d2h_bytes_per_step": B * 16, "ms_per_step": ms2 / K},
+                      "gpu_launches": launches, "useful_conv_tflops": fg * B / (ms / K) / 1e9,
+                      "finite": bool(torch.isfinite(d).all()) and bool(torch.isfinite(out).all())}), flush=True)
+
+
 if __name__ == "__main__":
     a = parse()
-    if a.impl == "reference":
+    if a.mode == "infer":
+        if int(os.environ.get("RANK", "0")) == 0:
+            run_infer(a)
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_b200(a)
