@@ -8,11 +8,14 @@ forwards + gradient penalty with double backward + clip + Adam each) and one gen
 256x256 patches per GPU.  N>1: one rank per GPU (torchrun), batch sharded, gradient all-reduce over NCCL.
 
 The JSON line (rank 0) carries
-  value        patches/s with the step's inputs already resident in HBM (CUDA events, max over ranks)
-  e2e          the same step through the public API (b200cgan.train_step.CGANTrainer.step) from PINNED HOST buffers:
-               per-step H2D of the patches/boxes and D2H of the logged scalars inside the timed region
+  value        patches/s with the step's inputs already resident in HBM: CUDA-graph replays of CGANTrainer.step
+               (CUDA events, barrier + sync both sides, max over ranks); --no-graph steps eagerly instead
+  e2e          the same step through the public API from PINNED HOST buffers: per-step H2D of the patches/boxes
+               (train_step.HostPrefetcher: the copy of batch i+1 overlaps step i) and D2H of the 9 logged scalars,
+               all inside the timed region
   roofline     the dominant tensor-core kernel family: algorithmic FLOPs per launch / CUDA-event duration per launch,
-               measured live in the timed region, against MEASURED_PEAKS.json (sustained bf16 TFLOP/s)
+               measured live in a third, eager pass of the same K steps (events cannot bracket kernels inside a graph
+               replay), against MEASURED_PEAKS.json (sustained bf16 TFLOP/s); traffic = ncu DRAM bytes per launch
   cpu_baseline the CPU oracle (oracle/cgan_oracle.py, a port of the reference's torch-CPU fp32 path) on a bounded
                sample of the workload, all host cores, rank 0 at N=1 only
 `--impl reference` times that CPU oracle alone (the reference is Python/PyTorch and /root/reference does not travel
@@ -300,8 +303,12 @@ def run_b200(args):
     dom = max(fam, key=lambda n: fam[n]["ms_per_step"])
     total_ms = sum(f["ms_per_step"] for f in fam.values())
     total_tf = sum(f["tflops"] * f["ms_per_step"] for f in fam.values()) / total_ms if total_ms else 0.0
+    traffic = None  # ncu dram__bytes_read+write per launch of the dominant family (one --set full capture of a step)
+    tf = ROOT / "profiles" / "r01_traffic.json"
+    if tf.exists():
+        traffic = json.loads(tf.read_text()).get(dom, {}).get("dram_bytes_per_launch")
     roofline = {"bound": "tensor", "kernel": dom, "achieved": fam[dom]["tflops"], "peak": peak_tf, "unit": "TFLOP/s",
-                "frac": fam[dom]["tflops"] / peak_tf, "traffic": None, "peak_source": peak_src + " bf16_tflops_sustained",
+                "frac": fam[dom]["tflops"] / peak_tf, "traffic": traffic, "peak_source": peak_src + " bf16_tflops_sustained",
                 "flop_per_launch": fam[dom]["flop_per_launch"], "ms_per_launch": fam[dom]["ms_per_launch"],
                 "share_of_step": fam[dom]["ms_per_step"] / (ms_dev / K),
                 "all_tensor_kernels": {"tflops": total_tf, "frac": total_tf / peak_tf,

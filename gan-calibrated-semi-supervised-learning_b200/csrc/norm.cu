@@ -65,7 +65,7 @@ __device__ __forceinline__ void load_stats8(const float* zs, int n, int C, int c
 // batches of NORM_U pixels, every tensor of a batch issued as 16-byte LDGSTS into slots that only this thread reads, so
 // NORM_STAGES-1 batches stay in flight while one is being consumed and no block-level barrier is needed.  The raw
 // operands never sit in registers across the wait, which keeps the register count low enough for 3 blocks per SM.
-constexpr int NORM_U = 2;
+constexpr int NORM_U = 2;   // pixels per batch (x2 for the single-tensor modes, see Ring<MODE>::U)
 constexpr int NORM_STAGES = 3;
 
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
@@ -82,7 +82,8 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 template <int MODE>
 struct Ring {
   static constexpr bool HAS_G = MODE == 2 || MODE == 3, HAS_H = MODE == 3, HAS_M = MODE != 1;
-  static constexpr int SLOTS = NORM_STAGES * NORM_U * 256;
+  static constexpr int U = (MODE == 0 || MODE == 1) ? 2 * NORM_U : NORM_U;  // single-tensor modes: deeper batches
+  static constexpr int SLOTS = NORM_STAGES * U * 256;
   static constexpr int BYTES = SLOTS * (16 + (HAS_G ? 16 : 0) + (HAS_H ? 16 : 0) + (HAS_M ? 8 : 0));
   uint4 *z, *g, *h;
   uint2* m;
@@ -125,14 +126,15 @@ __device__ __forceinline__ void ring_walk(const NormArgs& a, uint8_t* smem, int 
                                           F&& body) {
   const Ring<MODE> rg(smem);
   const int cnt = p0 < p_end ? (p_end - p0 + rows - 1) / rows : 0;
-  const int nb = (cnt + NORM_U - 1) / NORM_U;
+  constexpr int U = Ring<MODE>::U;
+  const int nb = (cnt + U - 1) / U;
   const long long base = (long long)n * a.HW;
   auto issue = [&](int b) {
     if (b < nb) {
 #pragma unroll
-      for (int u = 0; u < NORM_U; ++u) {
-        const int i = b * NORM_U + u;
-        if (i < cnt) ring_issue<MODE>(a, rg, ((b % NORM_STAGES) * NORM_U + u) * 256 + threadIdx.x, base + p0 + i * rows, c0);
+      for (int u = 0; u < U; ++u) {
+        const int i = b * U + u;
+        if (i < cnt) ring_issue<MODE>(a, rg, ((b % NORM_STAGES) * U + u) * 256 + threadIdx.x, base + p0 + i * rows, c0);
       }
     }
     cp_async_commit();
@@ -143,11 +145,11 @@ __device__ __forceinline__ void ring_walk(const NormArgs& a, uint8_t* smem, int 
     issue(b + NORM_STAGES - 1);
     cp_async_wait<NORM_STAGES - 1>();
 #pragma unroll
-    for (int u = 0; u < NORM_U; ++u) {
-      const int i = b * NORM_U + u;
+    for (int u = 0; u < U; ++u) {
+      const int i = b * U + u;
       if (i < cnt) {
         Raw r;
-        ring_fetch<MODE>(a, rg, ((b % NORM_STAGES) * NORM_U + u) * 256 + threadIdx.x, r);
+        ring_fetch<MODE>(a, rg, ((b % NORM_STAGES) * U + u) * 256 + threadIdx.x, r);
         body(base + p0 + i * rows, r);
       }
     }

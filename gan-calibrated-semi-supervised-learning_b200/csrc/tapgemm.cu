@@ -39,7 +39,7 @@ struct TapGemmParams {
 // 64 FLOP per staged byte at BN = 128, 131 instead of 87 at BN = 256.
 template <int BN, int MT>
 struct TapGemmCfg {
-  static constexpr int STAGES = (MT == 2) ? (BN == 256 ? 3 : 2) : (BN == 256) ? 2 : (BN == 128) ? 3 : (BN == 32 ? 6 : 4);
+  static constexpr int STAGES = (MT == 2) ? (BN == 256 ? 3 : 2) : (BN == 256) ? 2 : (BN == 128) ? 3 : (BN == 32 ? 5 : 4);  // BN = 32 (first-layer dgrad): 5 x 20 KB so that 2 CTAs fit per SM
   static constexpr int A_BYTES = MT * 128 * 128;
   static constexpr int B_BYTES = BN * 128;
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;
