@@ -24,6 +24,7 @@ struct ConvT64Params {
   __nv_bfloat16* y;
   long long ldy;
   float* stats;          // nullable: [N][64][2] += per-(image, channel) (sum, sum of squares) of y; needs BI == 1
+  int f32out;            // fp32 check mode (b2c_set_f32_output): y is float*, accumulators stored unrounded
 };
 
 namespace {
@@ -192,7 +193,16 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
             o[j] = pack_bf16(__uint_as_float(v0[2 * j]), __uint_as_float(v0[2 * j + 1]));
             o[8 + j] = pack_bf16(__uint_as_float(v1[2 * j]), __uint_as_float(v1[2 * j + 1]));
           }
-          if (valid) {
+          if (valid && p.f32out) {
+            float4* d4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.y) + (dst - p.y) + c0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              d4[j] = make_float4(__uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]),
+                                  __uint_as_float(v0[4 * j + 3]));
+              d4[4 + j] = make_float4(__uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]),
+                                      __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
+            }
+          } else if (valid) {
             uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
             d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
             d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
@@ -236,8 +246,10 @@ extern "C" int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int 
 
 int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, float* stats, int N, int H,
                     int W, int Cin, void* stream) {
+  extern int g_f32_output;  // tapgemm.cu
   ConvT64Params p;
   p.stats = nullptr;
+  p.f32out = g_f32_output;
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.kchunks = Cin / 64; p.y = (__nv_bfloat16*)y; p.ldy = ldy;
   p.BW = W < 128 ? W : 128;
   int rem = 128 / p.BW;

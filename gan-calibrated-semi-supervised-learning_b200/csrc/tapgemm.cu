@@ -32,6 +32,7 @@ struct TapGemmParams {
   float* gx0;               // mode D1: fp32 (N,3,2Ho,2Wo) outputs (gx1 null when Cin = 3)
   float* gx1;
   float* stats;             // nullable: [N][Cout][2] += per-(image, channel) (sum, sum of squares) of y; needs BI == 1
+  int f32out;               // fp32 check mode: y is float* and the accumulators are stored unrounded
 };
 
 // MT = number of 128-row pixel tiles per CTA.  The kernels are bound by the L2 -> shared-memory stream, so with MT = 2
@@ -180,7 +181,11 @@ __global__ void __launch_bounds__(64 + 128 * MT) tapgemm_kernel(const __grid_con
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] += __ldg(p.bias + ncol0 + c0 + j);
       }
-      if (valid) {
+      if (valid && p.f32out) {
+        float4* d4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.y) + (dst - p.y) + c0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) d4[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+      } else if (valid) {
         uint32_t o[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) o[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
@@ -253,6 +258,15 @@ static int launch_tapgemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
 
 extern "C" int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream);  // norm.cu
 
+// fp32 check mode (BASELINE north_star: "<= 1e-4 for an fp32 check mode"): while on, conv4s2 / convt4s2 treat `y` as
+// float* (ldy in floats) and store the fp32 TMEM accumulators (+bias) without the bf16 rounding, so a test can hold the
+// tensor-core arithmetic itself to 1e-4 against an fp64 reference on the same (bf16) operands.  Not used by the step.
+int g_f32_output = 0;
+extern "C" int b2c_set_f32_output(int on, void* /*stream: unused, uniform call shape*/) {
+  g_f32_output = on ? 1 : 0;
+  return B2C_OK;
+}
+
 static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack, const float* bias, void* y,
                        long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
   B2C_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "tapgemm: Cin=%d Cout=%d must be multiples of 64", Cin, Cout);
@@ -260,6 +274,7 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
   TapGemmParams p;
   p.mode = mode; p.N = N; p.Cin = Cin; p.Cout = Cout; p.kchunks = Cin / 64;
   p.y = (__nv_bfloat16*)y; p.ldy = ldy; p.bias = bias; p.gx0 = p.gx1 = nullptr; p.stats = nullptr;
+  p.f32out = g_f32_output;
   int TH, TW;
   CUtensorMap tmA, tmB;
   if (mode == 0) {
@@ -340,7 +355,7 @@ extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_
   B2C_REQUIRE(ws && ((uintptr_t)ws & 15) == 0, "first_dgrad: workspace missing or unaligned");
   TapGemmParams p;
   p.mode = 2; p.N = N; p.Cin = 64; p.Cout = 32; p.kchunks = 1;
-  p.y = nullptr; p.ldy = 0; p.bias = nullptr; p.gx0 = gx0; p.gx1 = gx1;
+  p.y = nullptr; p.ldy = 0; p.bias = nullptr; p.gx0 = gx0; p.gx1 = gx1; p.stats = nullptr; p.f32out = 0;
   p.Ho = H / 2; p.Wo = W / 2;
   B2C_REQUIRE(pick_box(p.Ho, p.Wo, 128, &p.BW, &p.BH, &p.BI), "first_dgrad: unsupported spatial size %dx%d", H, W);
   p.tiles_x = p.Wo / p.BW; p.tiles_y = p.Ho / p.BH;
@@ -376,6 +391,7 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, 
 extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y,
                                  long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
   static const bool merge = !(getenv("B2C_CONVT_MERGE") && getenv("B2C_CONVT_MERGE")[0] == '0');  // A/B switch for profiling
+  if (g_f32_output) B2C_REQUIRE(stats == nullptr, "fp32 check mode: fused statistics are not available");
   if (Cout == 64 && bias == nullptr && merge && Cin % 64 == 0 && ldx % 8 == 0 && ldy % 8 == 0 &&
       ((uintptr_t)y & 15) == 0 && is_pow2(H) && is_pow2(W))
     return b2c_run_convt64(x, ldx, wpack_t, y, ldy, stats, N, H, W, Cin, stream);

@@ -31,6 +31,8 @@ int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const fl
                      float* stats, int N, int H, int W, int Cin, int Cout, void* stream);
 int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y, long long ldy,
                       float* stats, int N, int H, int W, int Cin, int Cout, void* stream);
+int b2c_set_f32_output(int on, void* stream); /* fp32 CHECK MODE for the two entry points above: while on, `y` is float*
+                                               * (ldy in floats) and receives the unrounded fp32 accumulators; tests only */
 int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* large, long long ldl, float* ws, float* dw,
                       int accumulate, int N, int Hs, int Ws, int Cs, int Cl, int sm_count, void* stream);
 

@@ -77,6 +77,36 @@ def test_convt4s2(L, N, H, W, Cin, Cout):
     assert rel(nchw(y), ref) < 1e-2
 
 
+@pytest.mark.parametrize("mode,N,H,W,Cin,Cout", [("c", 2, 32, 32, 64, 128), ("c", 2, 16, 16, 256, 512), ("c", 17, 64, 64, 64, 256),
+                                                 ("t", 2, 16, 16, 256, 128), ("t", 2, 32, 32, 128, 64), ("t", 3, 8, 8, 512, 256)])
+def test_fp32_check_mode(L, mode, N, H, W, Cin, Cout):
+    """BASELINE north_star fp32 check (<= 1e-4): the same tensor-core kernels with fp32 stores instead of bf16, against an
+    fp64 reference on the same bf16 operands - isolates the arithmetic (tcgen05, fp32 TMEM accumulation over K up to
+    4096) from the bf16 storage rounding that the 2e-2 criterion covers."""
+    g = torch.Generator().manual_seed(9)
+    x = q(torch.randn(N, Cin, H, W, generator=g))
+    L.call("b2c_set_f32_output", 1)
+    try:
+        if mode == "c":
+            w = torch.randn(Cout, Cin, 4, 4, generator=g) * 0.05
+            wp = torch.empty(Cout, 16 * Cin, dtype=torch.bfloat16, device="cuda")
+            L.call("b2c_pack_w_c", w.cuda(), None, wp, Cout, Cin)
+            y = torch.empty(N, H // 2, W // 2, Cout, dtype=torch.float32, device="cuda")
+            L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, None, N, H, W, Cin, Cout)
+            ref = F.conv2d(x.double(), q(w).double(), None, 2, 1)
+        else:
+            w = torch.randn(Cin, Cout, 4, 4, generator=g) * 0.05
+            wp = torch.empty(4, Cout, 4 * Cin, dtype=torch.bfloat16, device="cuda")
+            L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
+            y = torch.empty(N, 2 * H, 2 * W, Cout, dtype=torch.float32, device="cuda")
+            L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, None, N, H, W, Cin, Cout)
+            ref = F.conv_transpose2d(x.double(), q(w).double(), None, 2, 1)
+        torch.cuda.synchronize()
+    finally:
+        L.call("b2c_set_f32_output", 0)
+    assert rel(y.permute(0, 3, 1, 2), ref) < 1e-4
+
+
 def test_conv_dgrad_is_convt(L):
     """dgrad of Conv2d(k4,s2,p1) == convt4s2 with the conv weight packed in T-form."""
     g = torch.Generator().manual_seed(3)
@@ -102,11 +132,11 @@ def test_wgrad4s2(L, N, Hs, Ws, Cs, Cl):
     dw = torch.empty(Cs, Cl, 4, 4, dtype=torch.float32, device="cuda")
     L.call("b2c_wgrad4s2_bf16", nhwc(small), Cs, nhwc(large), Cl, ws, dw, 0, N, Hs, Ws, Cs, Cl, 148)
     torch.cuda.synchronize()
-    ref = torch.nn.grad.conv2d_weight(large, (Cs, Cl, 4, 4), small, 2, 1)
-    assert rel(dw, ref) < 2e-3
+    ref = torch.nn.grad.conv2d_weight(large.double(), (Cs, Cl, 4, 4), small.double(), 2, 1)
+    assert rel(dw, ref) < 1e-4  # fp32 output: the fp32 check criterion applies directly
     L.call("b2c_wgrad4s2_bf16", nhwc(small), Cs, nhwc(large), Cl, ws, dw, 1, N, Hs, Ws, Cs, Cl, 148)
     torch.cuda.synchronize()
-    assert rel(dw, 2 * ref) < 2e-3
+    assert rel(dw, 2 * ref) < 1e-4
 
 
 @pytest.mark.parametrize("cin,N,S,interp", [(3, 3, 32, True), (6, 3, 32, True), (6, 2, 128, False), (3, 5, 64, False),
