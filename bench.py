@@ -85,7 +85,7 @@ def gemm_flops(name, a):
     if name == "b2c_wgrad4s2_bf16":      # lds, ldl, accumulate, N, Hs, Ws, Cs, Cl, sm_count
         _, _, _, N, Hs, Ws, Cs, Cl, _ = a
         return 2.0 * N * Hs * Ws * Cs * 16 * Cl
-    _, _, N, H, W, Cin, Cout = a          # ldx, ldy, N, H, W, Cin, Cout
+    N, H, W, Cin, Cout = a[-5:]           # ..., N, H, W, Cin, Cout
     if name == "b2c_conv4s2_bf16":
         return 2.0 * N * (H // 2) * (W // 2) * Cout * 16 * Cin
     return 2.0 * N * H * W * Cout * 16 * Cin

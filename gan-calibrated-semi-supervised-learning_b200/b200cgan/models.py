@@ -262,11 +262,12 @@ class Discriminator(nn.Module):
 
     def forward(self, pred_patch: torch.Tensor, other_patch: torch.Tensor) -> torch.Tensor:
         c0 = self.model[0]
-        a = ops.FirstConv.apply(pred_patch, other_patch, c0.param(), c0.bias, c0.weight_ctx(), 0.2)  # cat fused
+        # cat fused; the LeakyReLU backward of this layer is fused into model[2]'s data gradient (premasked / in_lrelu_slope)
+        a = ops.FirstConv.apply(pred_patch, other_patch, c0.param(), c0.bias, c0.weight_ctx(), 0.2, True)
         for idx in (2, 5, 8):
             conv = self.model[idx]
             wctx = conv.weight_ctx()
             wctx.want_stats = True
-            z = ops.Conv4s2.apply(a, conv.param(), conv.bias, wctx, True)
+            z = ops.Conv4s2.apply(a, conv.param(), conv.bias, wctx, True, 0.2 if idx == 2 else None)
             a = ops.INAct.apply(z, 0.2, None, None, wctx.take_stats())
         return ops.HeadConv.apply(a, self.model[11].weight)

@@ -107,12 +107,12 @@ def _conv_raw(x, wctx, bias, want_stats=False):
     return y
 
 
-def _convt_raw(x, wpack_t, Cout, wctx=None):
+def _convt_raw(x, wpack_t, Cout, wctx=None, act=None, slope=1.0):
     x, ld = as_nhwc(x)
     N, Cin, H, W = x.shape
     y = cl_empty(N, Cout, 2 * H, 2 * W, device=x.device)
     zs = _stats_buf(N, Cout, x.device) if (wctx is not None and wctx.want_stats) else None
-    _lib.call("b2c_convt4s2_bf16", x, ld, wpack_t, None, y, Cout, zs, N, H, W, Cin, Cout)
+    _lib.call("b2c_convt4s2_bf16", x, ld, wpack_t, None, y, Cout, zs, act, float(slope), N, H, W, Cin, Cout)
     if zs is not None:
         wctx._stats = zs
     return y
@@ -135,8 +135,11 @@ class Conv4s2(torch.autograd.Function):
     """y = conv2d(x, W_eff, bias, stride 2, pad 1).  Replaces nn.Conv2d at cgan/models.py:57,236 (Cin >= 64)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, wctx, bias_feeds_norm):
+    def forward(ctx, x, weight, bias, wctx, bias_feeds_norm, in_lrelu_slope=None):
+        """in_lrelu_slope: x is the output of a LeakyReLU(slope) whose producer leaves its activation backward to this
+        conv (FirstConv(premasked=True)): the returned input gradient is already multiplied by LeakyReLU'."""
         ctx.wctx, ctx.has_bias, ctx.bias_feeds_norm = wctx, bias is not None, bias_feeds_norm
+        ctx.in_lrelu_slope = in_lrelu_slope
         ctx.save_for_backward(x)
         return _conv_raw(x, wctx, bias, wctx.want_stats)
 
@@ -145,7 +148,13 @@ class Conv4s2(torch.autograd.Function):
         (x,) = ctx.saved_tensors
         gx = gw = gb = None
         if ctx.needs_input_grad[0]:
-            gx = Conv4s2Dgrad.apply(gy, ctx.wctx.weight, ctx.wctx, x.shape[2], x.shape[3])
+            if ctx.in_lrelu_slope is None:
+                gx = Conv4s2Dgrad.apply(gy, ctx.wctx.weight, ctx.wctx, x.shape[2], x.shape[3])
+            elif x.shape[1] == 64:  # fused into the dgrad epilogue (Cout = 64 kernel)
+                gx = Conv4s2Dgrad.apply(gy, ctx.wctx.weight, ctx.wctx, x.shape[2], x.shape[3], x, ctx.in_lrelu_slope)
+            else:
+                gx = LReluBwd.apply(Conv4s2Dgrad.apply(gy, ctx.wctx.weight, ctx.wctx, x.shape[2], x.shape[3]), x,
+                                    ctx.in_lrelu_slope)
         if ctx.needs_input_grad[1]:
             with torch.no_grad():
                 gw = ctx.wctx.finish_wgrad(_wgrad_raw(gy.detach(), x))
@@ -155,29 +164,36 @@ class Conv4s2(torch.autograd.Function):
                     gb = torch.zeros(gy.shape[1], dtype=torch.float32, device=gy.device)
                 else:
                     gb = channel_sum(gy.detach())
-        return gx, gw, gb, None, None
+        return gx, gw, gb, None, None, None
 
 
 class Conv4s2Dgrad(torch.autograd.Function):
     """dx = dgrad(gy, W_eff) = convT(gy, W_eff).  Differentiable: d/d gy = conv(h, W_eff), d/d W_eff = wgrad(gy, h)."""
 
     @staticmethod
-    def forward(ctx, gy, weight, wctx, H, W):
-        ctx.wctx = wctx
-        ctx.save_for_backward(gy)
+    def forward(ctx, gy, weight, wctx, H, W, act=None, slope=1.0):
+        """act / slope: out = dgrad * LeakyReLU'(act) (the activation backward of the layer below, fused)."""
+        ctx.wctx, ctx.slope, ctx.has_act = wctx, slope, act is not None
         Cin = wctx.weight.shape[1]
-        return _convt_raw(gy, wctx.pack_t(), Cin)
+        if act is not None:
+            act = dense_nhwc(act)
+            ctx.save_for_backward(gy, act)
+        else:
+            ctx.save_for_backward(gy)
+        return _convt_raw(gy, wctx.pack_t(), Cin, None, act, slope)
 
     @staticmethod
     def backward(ctx, h):
-        (gy,) = ctx.saved_tensors
+        gy = ctx.saved_tensors[0]
+        if ctx.has_act:  # out = m * dgrad(gy): the cotangent reaches dgrad as m * h
+            h = LReluBwd.apply(h, ctx.saved_tensors[1], ctx.slope)
         g_gy = gw = None
         if ctx.needs_input_grad[0]:
             g_gy = Conv4s2.apply(h, ctx.wctx.weight, None, ctx.wctx, False)
         if ctx.needs_input_grad[1]:
             with torch.no_grad():
                 gw = ctx.wctx.finish_wgrad(_wgrad_raw(gy.detach(), h.detach()))
-        return g_gy, gw, None, None, None
+        return g_gy, gw, None, None, None, None, None
 
 
 class ConvT4s2(torch.autograd.Function):
@@ -246,8 +262,11 @@ class FirstConv(torch.autograd.Function):
     """act = LeakyReLU_slope(conv2d(cat(a0, a1), W_eff, bias, 2, 1)) on NCHW fp32 inputs (cgan/models.py:103,245,257)."""
 
     @staticmethod
-    def forward(ctx, a0, a1, weight, bias, wctx, slope):
+    def forward(ctx, a0, a1, weight, bias, wctx, slope, premasked=False):
+        """premasked: the (only) consumer of the output is a Conv4s2(in_lrelu_slope=slope), which returns its input
+        gradient already multiplied by LeakyReLU' - no separate activation-backward pass here."""
         y = _first_fprop_raw(a0, a1, wctx, bias, slope)
+        ctx.premasked = premasked
         ctx.wctx, ctx.slope, ctx.has_a1, ctx.has_bias = wctx, slope, a1 is not None, bias is not None
         ctx.save_for_backward(a0, a1, y)
         return y
@@ -255,7 +274,7 @@ class FirstConv(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         a0, a1, y = ctx.saved_tensors
-        gz = LReluBwd.apply(g, y, ctx.slope) if ctx.slope != 1.0 else g
+        gz = LReluBwd.apply(g, y, ctx.slope) if (ctx.slope != 1.0 and not ctx.premasked) else g
         g0 = g1 = gw = gb = None
         if ctx.needs_input_grad[0] or (ctx.has_a1 and ctx.needs_input_grad[1]):
             g0, g1 = FirstDgrad.apply(gz, ctx.wctx.weight, ctx.wctx, ctx.has_a1)
@@ -265,7 +284,7 @@ class FirstConv(torch.autograd.Function):
             with torch.no_grad():
                 dwe, gb = _first_wgrad_raw(a0, a1, gz, ctx.wctx, ctx.has_bias)
                 gw = ctx.wctx.finish_wgrad(dwe)
-        return g0, g1, gw, gb, None, None
+        return g0, g1, gw, gb, None, None, None
 
 
 class FirstDgrad(torch.autograd.Function):

@@ -25,6 +25,8 @@ struct ConvT64Params {
   long long ldy;
   float* stats;          // nullable: [N][64][2] += per-(image, channel) (sum, sum of squares) of y; needs BI == 1
   int f32out;            // fp32 check mode (b2c_set_f32_output): y is float*, accumulators stored unrounded
+  const __nv_bfloat16* act;  // nullable: dense (N,2H,2W,64) activation a = LeakyReLU(z); y *= (a > 0 ? 1 : slope), i.e. the
+  float slope;               // backward of the LeakyReLU that produced this conv's input, fused into its data gradient
 };
 
 namespace {
@@ -187,6 +189,22 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty[buf]);
           }
+          if (p.act && valid) {  // fused LeakyReLU backward: scale by the slope where the forward activation was <= 0
+            const uint4* a4 = reinterpret_cast<const uint4*>(p.act + (((long long)n * Ho + oy) * Wo + ox) * 64 + c0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 u = __ldg(a4 + j);
+              const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 t = unpack_bf16(w4[e]);
+                uint32_t* v = j < 2 ? v0 : v1;
+                const int i0 = (j & 1) * 8 + 2 * e;
+                if (!(t.x > 0.f)) v[i0] = __float_as_uint(__uint_as_float(v[i0]) * p.slope);
+                if (!(t.y > 0.f)) v[i0 + 1] = __float_as_uint(__uint_as_float(v[i0 + 1]) * p.slope);
+              }
+            }
+          }
           uint32_t o[16];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -244,12 +262,13 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
 // with pixel stride ldy; stats as in b2c_convt4s2_bf16.  Called by b2c_convt4s2_bf16 (tapgemm.cu) when Cout == 64.
 extern "C" int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream);  // norm.cu
 
-int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, float* stats, int N, int H,
-                    int W, int Cin, void* stream) {
+int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, float* stats,
+                    const void* act, float slope, int N, int H, int W, int Cin, void* stream) {
   extern int g_f32_output;  // tapgemm.cu
   ConvT64Params p;
   p.stats = nullptr;
   p.f32out = g_f32_output;
+  p.act = (const __nv_bfloat16*)act; p.slope = slope;
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.kchunks = Cin / 64; p.y = (__nv_bfloat16*)y; p.ldy = ldy;
   p.BW = W < 128 ? W : 128;
   int rem = 128 / p.BW;

@@ -385,15 +385,17 @@ extern "C" int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_
   return run_tapgemm(0, x, ldx, wpack_c, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
 }
 
-int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, float* stats, int N, int H,
-                    int W, int Cin, void* stream);  // convt64.cu
+int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, float* stats,
+                    const void* act, float slope, int N, int H, int W, int Cin, void* stream);  // convt64.cu
 
 extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y,
-                                 long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
+                                 long long ldy, float* stats, const void* act, float slope, int N, int H, int W, int Cin,
+                                 int Cout, void* stream) {
   static const bool merge = !(getenv("B2C_CONVT_MERGE") && getenv("B2C_CONVT_MERGE")[0] == '0');  // A/B switch for profiling
   if (g_f32_output) B2C_REQUIRE(stats == nullptr, "fp32 check mode: fused statistics are not available");
   if (Cout == 64 && bias == nullptr && merge && Cin % 64 == 0 && ldx % 8 == 0 && ldy % 8 == 0 &&
       ((uintptr_t)y & 15) == 0 && is_pow2(H) && is_pow2(W))
-    return b2c_run_convt64(x, ldx, wpack_t, y, ldy, stats, N, H, W, Cin, stream);
+    return b2c_run_convt64(x, ldx, wpack_t, y, ldy, stats, act, slope, N, H, W, Cin, stream);
+  B2C_REQUIRE(act == nullptr, "convt4s2: the fused LeakyReLU backward needs the Cout = 64 kernel (Cout=%d, bias=%p)", Cout, (const void*)bias);
   return run_tapgemm(1, x, ldx, wpack_t, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
 }

@@ -30,7 +30,10 @@ int b2c_pack_w_t(const float* w, const float* inv_sigma, void* out_bf16, int D0,
 int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* bias, void* y, long long ldy,
                      float* stats, int N, int H, int W, int Cin, int Cout, void* stream);
 int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y, long long ldy,
-                      float* stats, int N, int H, int W, int Cin, int Cout, void* stream);
+                      float* stats, const void* act, float slope, int N, int H, int W, int Cin, int Cout, void* stream);
+/* act (nullable, Cout = 64 only): dense bf16 (N,2H,2W,64) output of the LeakyReLU(slope) that feeds the conv whose data
+ * gradient this call computes; y is multiplied by (act > 0 ? 1 : slope), i.e. LeakyReLU's backward (cgan/models.py:60,245)
+ * is fused into the dgrad epilogue instead of a separate full-tensor pass. */
 int b2c_set_f32_output(int on, void* stream); /* fp32 CHECK MODE for the two entry points above: while on, `y` is float*
                                                * (ldy in floats) and receives the unrounded fp32 accumulators; tests only */
 int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* large, long long ldl, float* ws, float* dw,

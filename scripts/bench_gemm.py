@@ -33,7 +33,7 @@ if which in ("conv", "all"):
 if which in ("convt", "all"):
     for H, W, Cin, Cout in CONVT:
         x, w, y = bf(B, H, W, Cin), bf(4, Cout, 4 * Cin), bf(B, 2 * H, 2 * W, Cout)
-        t = timeit(lambda: L.call("b2c_convt4s2_bf16", x, Cin, w, None, y, Cout, None, B, H, W, Cin, Cout))
+        t = timeit(lambda: L.call("b2c_convt4s2_bf16", x, Cin, w, None, y, Cout, None, None, 1.0, B, H, W, Cin, Cout))
         fl = 2.0 * B * H * W * Cout * 16 * Cin
         print(f"convt4s2 ({B},{H},{W},{Cin},{Cout}): {t*1e3:8.1f} us {fl/t/1e9:7.0f} TFLOP/s")
 if which in ("wgrad", "all"):

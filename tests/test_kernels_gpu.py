@@ -68,7 +68,7 @@ def test_convt4s2(L, N, H, W, Cin, Cout):
     L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
     y = torch.empty(N, 2 * H, 2 * W, Cout, dtype=torch.bfloat16, device="cuda")
     zs = torch.full((N, Cout, 2), 7.0, device="cuda")
-    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, zs, N, H, W, Cin, Cout)
+    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, zs, None, 1.0, N, H, W, Cin, Cout)
     yf = y.float()
     assert rel(zs[:, :, 1], (yf * yf).sum((1, 2))) < 1e-4
     assert float((zs[:, :, 0] - yf.sum((1, 2))).abs().max()) < 1e-3 * float(yf.abs().sum((1, 2)).max())
@@ -99,12 +99,28 @@ def test_fp32_check_mode(L, mode, N, H, W, Cin, Cout):
             wp = torch.empty(4, Cout, 4 * Cin, dtype=torch.bfloat16, device="cuda")
             L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
             y = torch.empty(N, 2 * H, 2 * W, Cout, dtype=torch.float32, device="cuda")
-            L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, None, N, H, W, Cin, Cout)
+            L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, None, None, 1.0, N, H, W, Cin, Cout)
             ref = F.conv_transpose2d(x.double(), q(w).double(), None, 2, 1)
         torch.cuda.synchronize()
     finally:
         L.call("b2c_set_f32_output", 0)
     assert rel(y.permute(0, 3, 1, 2), ref) < 1e-4
+
+
+def test_convt64_fused_lrelu_backward(L):
+    """convt4s2 with `act`: y = convT(x) * (act > 0 ? 1 : slope), the LeakyReLU backward fused into the dgrad epilogue."""
+    g = torch.Generator().manual_seed(5)
+    N, H, W, Cin, Cout = 3, 16, 16, 128, 64
+    x = q(torch.randn(N, Cin, H, W, generator=g))
+    w = torch.randn(Cin, Cout, 4, 4, generator=g) * 0.05
+    act = q(torch.randn(N, Cout, 2 * H, 2 * W, generator=g))
+    wp = torch.empty(4, Cout, 4 * Cin, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
+    y = torch.empty(N, 2 * H, 2 * W, Cout, dtype=torch.bfloat16, device="cuda")
+    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, None, nhwc(act), 0.2, N, H, W, Cin, Cout)
+    torch.cuda.synchronize()
+    ref = F.conv_transpose2d(x, q(w), None, 2, 1) * torch.where(act > 0, 1.0, 0.2)
+    assert rel(nchw(y), ref) < 1e-2
 
 
 def test_conv_dgrad_is_convt(L):
@@ -116,7 +132,7 @@ def test_conv_dgrad_is_convt(L):
     wp = torch.empty(4, Cin, 4 * Cout, dtype=torch.bfloat16, device="cuda")
     L.call("b2c_pack_w_t", w.cuda(), None, wp, Cout, Cin)
     dx = torch.empty(N, H, W, Cin, dtype=torch.bfloat16, device="cuda")
-    L.call("b2c_convt4s2_bf16", nhwc(gy), Cout, wp, None, dx, Cin, None, N, H // 2, W // 2, Cout, Cin)
+    L.call("b2c_convt4s2_bf16", nhwc(gy), Cout, wp, None, dx, Cin, None, None, 1.0, N, H // 2, W // 2, Cout, Cin)
     torch.cuda.synchronize()
     ref = torch.nn.grad.conv2d_input((N, Cin, H, W), q(w), gy, 2, 1)
     assert rel(nchw(dx), ref) < 1e-2
