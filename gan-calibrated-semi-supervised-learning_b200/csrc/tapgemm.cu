@@ -226,6 +226,192 @@ __global__ void __launch_bounds__(64 + 128 * MT) tapgemm_kernel(const __grid_con
   if (warp == 1) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
+// ------------------------------------------------------------------------------------------------ persistent variant
+// Same tile math as tapgemm_kernel<BN,1> (modes C4S2 / T4S2), but ONE CTA per SM walks tiles t = blockIdx.x,
+// blockIdx.x + gridDim.x, ... (pixel tile fastest, then output-channel block, then parity, so CTAs running side by side
+// share their weight slices in L2).  The TMA ring (192 KB) never drains across tiles and TMEM holds two accumulators,
+// so the epilogue of tile i overlaps the MMAs of tile i+1.  Used for BN = 128, whose tiles have short K (1024-2048)
+// and were prologue/epilogue bound as one-shot CTAs.
+template <int BN>
+struct TapGemmPCfg {
+  static constexpr int A_BYTES = 128 * 128;
+  static constexpr int B_BYTES = BN * 128;
+  static constexpr int STAGES = (192 * 1024) / (A_BYTES + B_BYTES);
+  static constexpr int RED_BYTES = 4 * BN * 8;
+  static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + RED_BYTES + 512 + 1024;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                    const __grid_constant__ CUtensorMap tmB, TapGemmParams p,
+                                                                    int ptiles, int nblocks, int total) {
+  using Cfg = TapGemmPCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * Cfg::A_BYTES;
+  float2* red = reinterpret_cast<float2*>(sB + STAGES * Cfg::B_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(red) + Cfg::RED_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;  // [2]
+  uint64_t* tmem_empty = tmem_full + 2;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ntaps = p.mode == 0 ? 16 : 4;
+  const int niters = ntaps * p.kchunks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 4);  // one arrival per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<2 * BN>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0, phase = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int pt = t % ptiles, nb = (t / ptiles) % nblocks, parity = t / (ptiles * nblocks);
+        const int tx = pt % p.tiles_x, ty = (pt / p.tiles_x) % p.tiles_y, tn = pt / (p.tiles_x * p.tiles_y);
+        const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
+        const int py = parity >> 1, px = parity & 1, ncol0 = nb * BN;
+        for (int tap = 0; tap < ntaps; ++tap) {
+          for (int cc = 0; cc < p.kchunks; ++cc) {
+            mbar_wait(&empty[stage], phase ^ 1);
+            mbar_expect_tx(&full[stage], Cfg::A_BYTES + Cfg::B_BYTES);
+            void* dA = sA + stage * Cfg::A_BYTES;
+            if (p.mode == 0) {
+              const int ky = tap >> 2, kx = tap & 3;
+              const int fy = (ky - 1) >> 1, di = (ky - 1) & 1, fx = (kx - 1) >> 1, dj = (kx - 1) & 1;
+              tma_load_5d(dA, &tmA, &full[stage], dj * p.Cin + cc * 64, x0 + fx, di, y0 + fy, n0);
+            } else {
+              const int a = tap >> 1, b = tap & 1;
+              tma_load_4d(dA, &tmA, &full[stage], cc * 64, x0 + px + b - 1, y0 + py + a - 1, n0);
+            }
+            tma_load_2d(sB + stage * Cfg::B_BYTES, &tmB, &full[stage], tap * p.Cin + cc * 64, parity * p.Cout + ncol0);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+      int stage = 0, phase = 0, lt = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x, ++lt) {
+        const int buf = lt & 1;
+        mbar_wait(&tmem_empty[buf], ((lt >> 1) & 1) ^ 1);
+        tc_fence_after();
+        for (int it = 0; it < niters; ++it) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a0 = smem_u32(sA + stage * Cfg::A_BYTES), b0 = smem_u32(sB + stage * Cfg::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(tmem_base + buf * BN, umma_desc_sw128(a0 + k * 32, 16, 1024), umma_desc_sw128(b0 + k * 32, 16, 1024),
+                      idesc, (uint32_t)((it | k) != 0));
+          umma_commit(&empty[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tmem_full[buf]);
+      }
+    }
+  } else {
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    const int r = q * 32 + lane;
+    const int bw = r % p.BW, bh = (r / p.BW) % p.BH, bi = r / (p.BW * p.BH);
+    int lt = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x, ++lt) {
+      const int pt = t % ptiles, nb = (t / ptiles) % nblocks, parity = t / (ptiles * nblocks);
+      const int tx = pt % p.tiles_x, ty = (pt / p.tiles_x) % p.tiles_y, tn = pt / (p.tiles_x * p.tiles_y);
+      const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
+      const int py = parity >> 1, px = parity & 1, ncol0 = nb * BN;
+      const int n = n0 + bi;
+      int oy = y0 + bh, ox = x0 + bw;
+      if (p.mode == 1) { oy = 2 * oy + py; ox = 2 * ox + px; }
+      const bool valid = n < p.N;
+      const long long pix_off = (((long long)n * p.Ho + oy) * p.Wo + ox) * p.ldy + ncol0;
+      const int buf = lt & 1;
+      const uint32_t acc = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
+      mbar_wait(&tmem_full[buf], (lt >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t v0[16], v1[16];
+        tmem_ld16(acc + c0, v0);
+        tmem_ld16(acc + c0 + 16, v1);
+        tmem_ld_wait();
+        if (c0 == BN - 32) {  // last read of this accumulator: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+        }
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          f[j] = __uint_as_float(v0[j]);
+          f[16 + j] = __uint_as_float(v1[j]);
+        }
+        if (p.bias) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] += __ldg(p.bias + ncol0 + c0 + j);
+        }
+        if (valid && p.f32out) {
+          float4* d4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.y) + pix_off + c0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) d4[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+        } else if (valid) {
+          uint32_t o[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) o[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
+          uint4* d4 = reinterpret_cast<uint4*>(p.y + pix_off + c0);
+          d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+          d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+          d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
+          d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+        }
+        if (p.stats) {  // statistics of the bf16-ROUNDED values; lane L gets channel c0 + L
+          float sq[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            f[j] = __bfloat162float(__float2bfloat16(f[j]));
+            sq[j] = f[j] * f[j];
+          }
+          const float s1 = warp_transpose_sum32(f), s2 = warp_transpose_sum32(sq);
+          red[q * BN + c0 + lane] = make_float2(s1, s2);
+        }
+      }
+      if (p.stats) {
+        named_bar_sync(1, 128);
+        for (int c = r; c < BN; c += 128) {
+          const float2 a = red[c], b = red[BN + c], cc = red[2 * BN + c], d = red[3 * BN + c];
+          float* st = p.stats + ((long long)n0 * p.Cout + ncol0 + c) * 2;
+          atomicAdd(st, (a.x + b.x) + (cc.x + d.x));
+          atomicAdd(st + 1, (a.y + b.y) + (cc.y + d.y));
+        }
+        named_bar_sync(1, 128);  // scratch may be overwritten by the next tile
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 static bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
@@ -286,8 +472,9 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     p.Ho = 2 * H; p.Wo = 2 * W; TH = H; TW = W;
   }
   const int BN = (Cout % 256 == 0) ? 256 : (Cout % 128 == 0) ? 128 : 64;
-  // two pixel tiles per CTA when the weight operand is wide enough to be worth sharing and there are enough tiles
-  static const bool allow_mt2 = !(getenv("B2C_TAPGEMM_MT2") && getenv("B2C_TAPGEMM_MT2")[0] == '0');
+  // Two pixel tiles per CTA (MT = 2) is kept as an experiment switch (B2C_TAPGEMM_MT2=1): measured, the persistent
+  // one-tile kernel below beats it on every shape of the step (no wave quantisation, overlapped epilogue).
+  static const bool allow_mt2 = getenv("B2C_TAPGEMM_MT2") && getenv("B2C_TAPGEMM_MT2")[0] == '1';
   int MT = 1;
   if (allow_mt2 && BN == 256 && (long long)N * TH * TW >= 256LL * 64) MT = 2;  // measured: no gain at BN = 128
   B2C_REQUIRE(pick_box(TH, TW, 128 * MT, &p.BW, &p.BH, &p.BI), "tapgemm: unsupported spatial size %dx%d (need powers of two)", TH, TW);
@@ -322,7 +509,24 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     p.stats = stats;
   }
   dim3 grid(p.tiles_x * p.tiles_y * tiles_n, Cout / BN, mode == 0 ? 1 : 4);
-  if (BN == 256 && MT == 2) rc = launch_tapgemm<256, 2>(tmA, tmB, p, grid, (cudaStream_t)stream);
+  static const bool persistent = !(getenv("B2C_TAPGEMM_PERSIST") && getenv("B2C_TAPGEMM_PERSIST")[0] == '0');
+  if ((BN == 128 || BN == 256) && MT == 1 && persistent) {
+    static int sms = 0;
+    if (!sms) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+      cudaFuncSetAttribute(tapgemm_persistent_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<128>::SMEM);
+      cudaFuncSetAttribute(tapgemm_persistent_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<256>::SMEM);
+    }
+    const int ptiles = (int)grid.x, nblocks = (int)grid.y, total = (int)(grid.x * grid.y * grid.z);
+    const int ctas = total < sms ? total : sms;
+    if (BN == 128)
+      tapgemm_persistent_kernel<128><<<ctas, 192, TapGemmPCfg<128>::SMEM, (cudaStream_t)stream>>>(tmA, tmB, p, ptiles, nblocks, total);
+    else
+      tapgemm_persistent_kernel<256><<<ctas, 192, TapGemmPCfg<256>::SMEM, (cudaStream_t)stream>>>(tmA, tmB, p, ptiles, nblocks, total);
+    rc = b2c_check_launch("tapgemm_persistent_kernel");
+  } else if (BN == 256 && MT == 2) rc = launch_tapgemm<256, 2>(tmA, tmB, p, grid, (cudaStream_t)stream);
   else if (BN == 128 && MT == 2) rc = launch_tapgemm<128, 2>(tmA, tmB, p, grid, (cudaStream_t)stream);
   else if (BN == 256) rc = launch_tapgemm<256>(tmA, tmB, p, grid, (cudaStream_t)stream);
   else if (BN == 128) rc = launch_tapgemm<128>(tmA, tmB, p, grid, (cudaStream_t)stream);
