@@ -4,8 +4,9 @@
 // caller's NCHW fp32 patches exactly once and keep the arithmetic off the CUDA cores.  Each thread owns one output
 // pixel of a 128-pixel tile: it gathers its 4x4xCin receptive field with coalesced 8-byte loads (+ warp shuffles for
 // the two halo columns), applies the optional GP interpolation x = alpha*a + (1-alpha)*b (cgan/losses.py:203-204) and
-// the channel concat (cgan/models.py:257), and writes one 256-byte im2col row k = tap*8 + c (bf16, channels padded
-// to 8) straight into the 128B-swizzled UMMA layout in shared memory.  That tile is
+// the channel concat (cgan/models.py:257), and writes one im2col row k = (c*4 + ky)*4 + kx (bf16, the weight tensor's
+// own order, K = 16*Cin, no padding) straight into the 128B-swizzled UMMA layout in shared memory.  The loads of tile
+// i+1 are issued before the epilogue of tile i and consumed after it, so their latency hides behind it.  That tile is
 //   fprop : the K-major  A operand of  y[128 pix x 64 co]  = A . W^T      (+bias, LeakyReLU, bf16 NHWC store)
 //   wgrad : the MN-major A operand of  dW[128 k  x 64 co] += A^T . gz     (gz tile by TMA; fp32 TMEM accumulation over
 //           all tiles of the CTA; one atomic flush per CTA; bias gradient = the all-ones im2col column k = 127)
@@ -27,93 +28,90 @@ static constexpr int FT_B_BYTES = 128 * 128;       // fprop: [2 k-blocks][64 co]
 static constexpr int FT_SMEM = FT_A_BYTES + 2 * FT_B_BYTES + 1024 + 64;   // wgrad (double-buffered gz tile)
 static constexpr int FT_SMEM_FPROP = FT_A_BYTES + FT_B_BYTES + 1024 + 64;
 
-// Receptive field of one output pixel: v[c][ky] = (x[2ox], x[2ox+1]), l[c][ky] = x[2ox-1], r[c][ky] = x[2ox+2].
-template <int CIN>
-struct Field {
+// Raw receptive field of one output pixel as it comes back from global memory: v[c][ky] = (x[2ox], x[2ox+1]);
+// h[c][ky] = the halo element only the warp-edge lanes fetch (lane 0: x[2ox-1], lane 31: x[2ox+2]; 0 elsewhere) -
+// every other lane takes its two halo columns from its neighbours by shuffle.
+template <int CIN, bool INTERP>
+struct Raw {
   float2 v[CIN][4];
-  float l[CIN][4], r[CIN][4];
+  float h[CIN][4];
+  float2 u[INTERP ? CIN : 1][4];
+  float hb[INTERP ? CIN : 1][4];
+  float al;
+  int ox;
 };
 
-// Two phases so that every global load of the field is in flight before the first dependent instruction: phase 1
-// issues the 4*CIN row loads (+ the predicated halo loads of the warp-edge lanes), phase 2 exchanges halo columns.
+// Phase 1: issue every global load of the field (4*CIN 8-byte row loads + one predicated halo load each); nothing here
+// depends on a loaded value, so the whole field is in flight while the caller runs the previous tile's epilogue.
 template <int CIN, bool INTERP>
-__device__ __forceinline__ void gather_field(const FirstIn& in, long long pix, long long npix, int Ho, int Wo, int H,
-                                             int W, Field<CIN>& f) {
+__device__ __forceinline__ void issue_field(const FirstIn& in, int pix, int npix, int Ho, int Wo, int H, int W,
+                                            Raw<CIN, INTERP>& f) {
   const int lane = threadIdx.x & 31;
   const bool live = pix < npix;
   int ox = 0, oy = 0, n = 0;
   if (live) {
-    ox = (int)(pix % Wo);
-    oy = (int)((pix / Wo) % Ho);
-    n = (int)(pix / ((long long)Wo * Ho));
+    ox = pix % Wo;
+    const int q = pix / Wo;
+    oy = q % Ho;
+    n = q / Ho;
   }
-  constexpr bool interp = INTERP;
-  const float al = (interp && live) ? __ldg(in.alpha + n) : 1.f;
-  const float be = 1.f - al;
-  const bool want_l = lane == 0 && ox > 0, want_r = lane == 31 && ox < Wo - 1;
-  float2 u[CIN][4];
-  float lb[CIN][4], rb[CIN][4];
+  f.ox = ox;
+  f.al = (INTERP && live) ? __ldg(in.alpha + n) : 1.f;
+  const bool want = live && ((lane == 0 && ox > 0) || (lane == 31 && ox < Wo - 1));
+  const int hoff = lane == 0 ? -1 : 2;
+  const long long img = (long long)n * 3 * H * W + 2 * ox;
 #pragma unroll
   for (int c = 0; c < CIN; ++c) {
     const int part = c / 3, cc = c % 3;
-    const long long plane = ((long long)n * 3 + cc) * H;
+    const float* pa0 = in.a[part] + img;
+    const float* pb0 = INTERP ? in.b[part] + img : nullptr;
 #pragma unroll
     for (int ky = 0; ky < 4; ++ky) {
       const int iy = 2 * oy + ky - 1;
       const bool row_ok = live && iy >= 0 && iy < H;
-      const long long off = row_ok ? (plane + iy) * W + 2 * ox : 0;
-      const float* pa = in.a[part] + off;
-      f.v[c][ky] = row_ok ? __ldg(reinterpret_cast<const float2*>(pa)) : make_float2(0.f, 0.f);
-      f.l[c][ky] = (row_ok && want_l) ? __ldg(pa - 1) : 0.f;
-      f.r[c][ky] = (row_ok && want_r) ? __ldg(pa + 2) : 0.f;
-      if (interp) {
-        const float* pb = in.b[part] + off;
-        u[c][ky] = row_ok ? __ldg(reinterpret_cast<const float2*>(pb)) : make_float2(0.f, 0.f);
-        lb[c][ky] = (row_ok && want_l) ? __ldg(pb - 1) : 0.f;
-        rb[c][ky] = (row_ok && want_r) ? __ldg(pb + 2) : 0.f;
+      const int off = row_ok ? (cc * H + iy) * W : 0;
+      f.v[c][ky] = row_ok ? __ldg(reinterpret_cast<const float2*>(pa0 + off)) : make_float2(0.f, 0.f);
+      f.h[c][ky] = (row_ok && want) ? __ldg(pa0 + off + hoff) : 0.f;
+      if (INTERP) {
+        f.u[c][ky] = row_ok ? __ldg(reinterpret_cast<const float2*>(pb0 + off)) : make_float2(0.f, 0.f);
+        f.hb[c][ky] = (row_ok && want) ? __ldg(pb0 + off + hoff) : 0.f;
       }
     }
   }
+}
+
+// Phase 2: optional GP interpolation, halo exchange, bf16 packing and the swizzled im2col row of pixel `row`:
+// k = (c*4 + ky)*4 + kx, i.e. the weight tensor's own [c][ky][kx] order, so a 16-byte chunk is two (c,ky) groups of
+// (left, x0, x1, right).  K = 16*CIN: 2*CIN chunks, no channel padding.
+template <int CIN, bool INTERP>
+__device__ __forceinline__ void pack_store_field(uint8_t* sA, int row, int Wo, const Raw<CIN, INTERP>& f) {
+  const int lane = threadIdx.x & 31;
+  const bool edge_l = lane == 0 || f.ox == 0, edge_r = lane == 31 || f.ox == Wo - 1;
+  const float al = f.al, be = 1.f - f.al;
+  uint8_t* base = sA + (row >> 3) * 1024 + (row & 7) * 128;
+  uint32_t p[4];
 #pragma unroll
   for (int c = 0; c < CIN; ++c) {
 #pragma unroll
     for (int ky = 0; ky < 4; ++ky) {
       float2 t = f.v[c][ky];
-      float le = f.l[c][ky], re = f.r[c][ky];
-      if (interp) {
-        t.x = al * t.x + be * u[c][ky].x;
-        t.y = al * t.y + be * u[c][ky].y;
-        le = al * le + be * lb[c][ky];
-        re = al * re + be * rb[c][ky];
-        f.v[c][ky] = t;
+      float hh = f.h[c][ky];
+      if (INTERP) {
+        t.x = al * t.x + be * f.u[c][ky].x;
+        t.y = al * t.y + be * f.u[c][ky].y;
+        hh = al * hh + be * f.hb[c][ky];
       }
-      // halo columns come from the neighbouring lanes (same image row) except at warp / image-row edges
       const float lft = __shfl_up_sync(0xffffffffu, t.y, 1);
       const float rgt = __shfl_down_sync(0xffffffffu, t.x, 1);
-      f.l[c][ky] = (lane == 0 || ox == 0) ? le : lft;
-      f.r[c][ky] = (lane == 31 || ox == Wo - 1) ? re : rgt;
-    }
-  }
-}
-
-// Write im2col row `row` (k = tap*8 + c) into the swizzled tile; `ones` puts 1.0 into the padding slot k = 127.
-template <int CIN>
-__device__ __forceinline__ void store_field(uint8_t* sA, int row, const Field<CIN>& f, bool ones) {
-  uint8_t* base = sA + (row >> 3) * 1024 + (row & 7) * 128;
-#pragma unroll
-  for (int ky = 0; ky < 4; ++ky) {
-#pragma unroll
-    for (int kx = 0; kx < 4; ++kx) {
-      float e[8];
-#pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        if (c < CIN) e[c] = kx == 0 ? f.l[c][ky] : kx == 1 ? f.v[c][ky].x : kx == 2 ? f.v[c][ky].y : f.r[c][ky];
-        else e[c] = 0.f;
+      const float l = edge_l ? (lane == 0 ? hh : 0.f) : lft;
+      const float r = edge_r ? (lane == 31 ? hh : 0.f) : rgt;
+      const int g = c * 4 + ky;
+      p[(g & 1) * 2] = pack_bf16(l, t.x);
+      p[(g & 1) * 2 + 1] = pack_bf16(t.y, r);
+      if (g & 1) {
+        const int j = g >> 1;
+        *reinterpret_cast<uint4*>(base + (j >> 3) * 16384 + (((j & 7) ^ (row & 7)) << 4)) = make_uint4(p[0], p[1], p[2], p[3]);
       }
-      const int tap = ky * 4 + kx;
-      if (tap == 15 && ones) e[7] = 1.f;
-      const uint4 u = make_uint4(pack_bf16(e[0], e[1]), pack_bf16(e[2], e[3]), pack_bf16(e[4], e[5]), pack_bf16(e[6], e[7]));
-      *reinterpret_cast<uint4*>(base + (tap >> 3) * 16384 + (((tap & 7) ^ (row & 7)) << 4)) = u;
     }
   }
 }
@@ -135,24 +133,25 @@ __global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_ker
 
   const int t = threadIdx.x, warp = t >> 5;
   const int Ho = H / 2, Wo = W / 2;
-  const long long npix = (long long)N * Ho * Wo;
-  const int ntiles = (int)((npix + 127) / 128);
+  const int npix = N * Ho * Wo;   // host checks < 2^31 - 128
+  const int ntiles = (npix + 127) / 128;
 
   if (t == 0) {
     mbar_init(mma_bar, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<64>(tmem_slot);
-  // weights: B[co][k = tap*8 + c] = w[co][c][tap] / sigma, K-major, two 64-wide k-blocks of [64 rows x 128 B]
+  // weights: B[co][k] = w[co][c][ky][kx] / sigma in the tensor's own order, K-major, k-blocks of [64 rows x 128 B]
   {
     const float s = inv_sigma ? __ldg(inv_sigma) : 1.f;
-    for (int i = t; i < 64 * 16; i += FT_THREADS) {
-      const int co = i >> 4, tap = i & 15;
-      float e[8];
-#pragma unroll
-      for (int c = 0; c < 8; ++c) e[c] = c < CIN ? __ldg(w + ((long long)co * CIN + c) * 16 + tap) * s : 0.f;
-      const uint4 u = make_uint4(pack_bf16(e[0], e[1]), pack_bf16(e[2], e[3]), pack_bf16(e[4], e[5]), pack_bf16(e[6], e[7]));
-      *reinterpret_cast<uint4*>(sB + (tap >> 3) * 8192 + (co >> 3) * 1024 + (co & 7) * 128 + (((tap & 7) ^ (co & 7)) << 4)) = u;
+    constexpr int NCH = 2 * CIN;
+    for (int i = t; i < 64 * NCH; i += FT_THREADS) {
+      const int co = i / NCH, j = i % NCH;
+      const float4 lo = __ldg(reinterpret_cast<const float4*>(w + (long long)co * (16 * CIN) + j * 8));
+      const float4 hi = __ldg(reinterpret_cast<const float4*>(w + (long long)co * (16 * CIN) + j * 8 + 4));
+      const uint4 u = make_uint4(pack_bf16(lo.x * s, lo.y * s), pack_bf16(lo.z * s, lo.w * s), pack_bf16(hi.x * s, hi.y * s),
+                                 pack_bf16(hi.z * s, hi.w * s));
+      *reinterpret_cast<uint4*>(sB + (j >> 3) * 8192 + (co >> 3) * 1024 + (co & 7) * 128 + (((j & 7) ^ (co & 7)) << 4)) = u;
     }
     if (t < 64) bias_s[t] = bias ? __ldg(bias + t) : 0.f;
   }
@@ -162,12 +161,12 @@ __global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_ker
   const uint32_t tmem_base = *tmem_slot;
   constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 0);
 
-  Field<CIN> f;
+  Raw<CIN, INTERP> f;
   int tile = blockIdx.x;
-  if (tile < ntiles) gather_field<CIN, INTERP>(in, (long long)tile * 128 + t, npix, Ho, Wo, H, W, f);
+  if (tile < ntiles) issue_field<CIN, INTERP>(in, tile * 128 + t, npix, Ho, Wo, H, W, f);
   uint32_t phase = 0;
   for (; tile < ntiles; tile += gridDim.x) {
-    store_field<CIN>(sA, t, f, false);
+    pack_store_field<CIN, INTERP>(sA, t, Wo, f);
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
@@ -175,14 +174,15 @@ __global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_ker
       tc_fence_after();
       const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
 #pragma unroll
-      for (int k = 0; k < 8; ++k)
+      for (int k = 0; k < CIN; ++k)  // K = 16*CIN
         umma_bf16(tmem_base, umma_desc_sw128(a0 + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
                   umma_desc_sw128(b0 + (k >> 2) * 8192 + (k & 3) * 32, 16, 1024), idesc, (uint32_t)(k != 0));
       umma_commit(mma_bar);
     }
-    const long long pix = (long long)tile * 128 + t;
+    const int pix = tile * 128 + t;
     const int next = tile + gridDim.x;
-    if (next < ntiles) gather_field<CIN, INTERP>(in, (long long)next * 128 + t, npix, Ho, Wo, H, W, f);  // overlaps the MMA
+    // the next tile's loads fly during this tile's MMA + epilogue; they are consumed at the top of the loop
+    if (next < ntiles) issue_field<CIN, INTERP>(in, next * 128 + t, npix, Ho, Wo, H, W, f);
     mbar_wait(mma_bar, phase);
     phase ^= 1;
     tc_fence_after();
@@ -204,11 +204,10 @@ __global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_ker
           o[j] = pack_bf16(a, b);
           o[8 + j] = pack_bf16(c, d);
         }
-        uint4* d4 = reinterpret_cast<uint4*>(y + pix * 64 + c0);
-        d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
-        d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
-        d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
-        d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+        // whole 32-byte sectors per store (STG.256)
+        __nv_bfloat16* dst = y + (long long)pix * 64 + c0;
+        st_global_v8(dst, o);
+        st_global_v8(dst + 16, o + 8);
       }
     }
   }
@@ -233,8 +232,8 @@ __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, 
 
   const int t = threadIdx.x, warp = t >> 5;
   const int Ho = H / 2, Wo = W / 2;
-  const long long npix = (long long)N * Ho * Wo;
-  const int ntiles = (int)((npix + 127) / 128);
+  const int npix = N * Ho * Wo;   // host checks < 2^31 - 128
+  const int ntiles = (npix + 127) / 128;
 
   int tile = blockIdx.x;
   if (t == 0) {
@@ -255,8 +254,12 @@ __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, 
   const uint32_t tmem_base = *tmem_slot;
   constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);
 
-  Field<CIN> f;
-  if (tile < ntiles) gather_field<CIN, INTERP>(in, (long long)tile * 128 + t, npix, Ho, Wo, H, W, f);
+  // k = 127 (last element of chunk 15) is the all-ones im2col column whose dW row is the bias gradient; rows past npix
+  // meet zero-filled gz rows, so it never changes.  Chunks 2*CIN..14 are never written: their dW rows are not flushed.
+  *reinterpret_cast<uint4*>(sA + 16384 + (t >> 3) * 1024 + (t & 7) * 128 + ((7 ^ (t & 7)) << 4)) =
+      make_uint4(0u, 0u, 0u, pack_bf16(0.f, 1.f));
+  Raw<CIN, INTERP> f;
+  if (tile < ntiles) issue_field<CIN, INTERP>(in, tile * 128 + t, npix, Ho, Wo, H, W, f);
   uint32_t it = 0;
   for (; tile < ntiles; tile += gridDim.x, ++it) {
     if (it > 0) mbar_wait(mma_bar, (it - 1) & 1);  // the previous tile's MMAs are done reading sA and sB[(it-1)&1]
@@ -265,7 +268,7 @@ __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, 
       mbar_expect_tx(&tma_bar[(it + 1) & 1], FT_B_BYTES);
       tma_load_2d(sB + ((it + 1) & 1) * FT_B_BYTES, &tmG, &tma_bar[(it + 1) & 1], 0, next * 128);
     }
-    store_field<CIN>(sA, t, f, (long long)tile * 128 + t < npix);
+    pack_store_field<CIN, INTERP>(sA, t, Wo, f);
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
@@ -279,12 +282,12 @@ __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, 
                   idesc, (uint32_t)((it | (uint32_t)k) != 0));
       umma_commit(mma_bar);
     }
-    if (next < ntiles) gather_field<CIN, INTERP>(in, (long long)next * 128 + t, npix, Ho, Wo, H, W, f);
+    if (next < ntiles) issue_field<CIN, INTERP>(in, next * 128 + t, npix, Ho, Wo, H, W, f);
   }
   if (it > 0) {
     mbar_wait(mma_bar, (it - 1) & 1);
     tc_fence_after();
-    const int tap = t >> 3, c = t & 7;
+    // TMEM lane t = im2col column k = t = (c*4 + ky)*4 + kx: dw[co][k] in the weight tensor's own layout.
     // CTAs finish together: rotate the column order per CTA so concurrent flushes hit different addresses
     const int rot = (blockIdx.x * 16) & 63;
 #pragma unroll 1
@@ -293,9 +296,9 @@ __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, 
       uint32_t v[16];
       tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + c0, v);
       tmem_ld_wait();
-      if (c < CIN) {
+      if (t < 16 * CIN) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) atomicAdd(dw + ((long long)(c0 + j) * CIN + c) * 16 + tap, __uint_as_float(v[j]));
+        for (int j = 0; j < 16; ++j) atomicAdd(dw + (long long)(c0 + j) * (16 * CIN) + t, __uint_as_float(v[j]));
       } else if (t == 127 && db) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) atomicAdd(db + c0 + j, __uint_as_float(v[j]));
@@ -324,8 +327,9 @@ static int first_attr(K kernel) {
   return B2C_OK;
 }
 
-static int first_check(const float* a0, const float* b0, const float* alpha, int H, int W) {
+static int first_check(const float* a0, const float* b0, const float* alpha, int N, int H, int W) {
   B2C_REQUIRE(H % 2 == 0 && W % 2 == 0, "first layer: odd size %dx%d", H, W);
+  B2C_REQUIRE((long long)N * (H / 2) * (W / 2) < (1ll << 31) - 128 * 1024, "first layer: %d x %d x %d patches exceed 2^31 output pixels", N, H, W);
   B2C_REQUIRE(((uintptr_t)a0 & 7) == 0, "first layer: input must be 8-byte aligned");
   B2C_REQUIRE(!alpha || b0, "first layer: alpha given without interpolation partners");
   return B2C_OK;
@@ -362,7 +366,7 @@ static int launch_first_wgrad(const FirstIn& in, const CUtensorMap& tmG, float* 
 extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                                const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
                                float slope, void* stream) {
-  int rc = first_check(a0, b0, alpha, H, W);
+  int rc = first_check(a0, b0, alpha, N, H, W);
   if (rc) return rc;
   FirstIn in = make_in(a0, a1, b0, b1, alpha);
   const long long npix = (long long)N * (H / 2) * (W / 2);
@@ -380,7 +384,7 @@ extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0
 // dw: fp32 [64][Cin][4][4], db: fp32 [64] or null; both are ACCUMULATED into (caller zeroes).  gz: dense NHWC bf16.
 extern "C" int b2c_first_wgrad(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                                const void* gz, float* dw, float* db, int N, int H, int W, void* stream) {
-  int rc = first_check(a0, b0, alpha, H, W);
+  int rc = first_check(a0, b0, alpha, N, H, W);
   if (rc) return rc;
   FirstIn in = make_in(a0, a1, b0, b1, alpha);
   const long long npix = (long long)N * (H / 2) * (W / 2);

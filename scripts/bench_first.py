@@ -1,36 +1,33 @@
-"""Micro-benchmark of the first-layer kernels at the bench shape (B=64, S=256): us/call and achieved GB/s."""
+"""Micro-benchmark of the first-layer kernels (Cin=6, D.model.0) at B x S x S: python scripts/bench_first.py [B] [S] [iters]"""
 import sys
 sys.path[:0] = ["gan-calibrated-semi-supervised-learning_b200"]
 import torch
 from b200cgan import _lib as L
-N, S = 64, 256
-a0, a1 = torch.randn(N, 3, S, S, device="cuda"), torch.randn(N, 3, S, S, device="cuda")
-w = torch.randn(64, 6, 4, 4, device="cuda") * 0.1
-w3 = torch.randn(64, 3, 4, 4, device="cuda") * 0.1
-b = torch.randn(64, device="cuda")
-y = torch.empty(N, S // 2, S // 2, 64, dtype=torch.bfloat16, device="cuda")
-gz = torch.randn(N, S // 2, S // 2, 64, device="cuda").to(torch.bfloat16)
-gx0, gx1 = torch.empty_like(a0), torch.empty_like(a1)
-ws = torch.empty(32 * 576, dtype=torch.bfloat16, device="cuda")
-dw, db = torch.zeros(64, 6, 4, 4, device="cuda"), torch.zeros(64, device="cuda")
-dw3 = torch.zeros(64, 3, 4, 4, device="cuda")
-flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-inb, outb = 2 * a0.numel() * 4, y.numel() * 2
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+S = int(sys.argv[2]) if len(sys.argv) > 2 else 256
+iters = int(sys.argv[3]) if len(sys.argv) > 3 else 10
+dev = "cuda"
+a0 = torch.randn(B, 3, S, S, device=dev); a1 = torch.randn(B, 3, S, S, device=dev)
+w = torch.randn(64, 6, 4, 4, device=dev) * 0.1
+isg = torch.ones(1, device=dev); bias = torch.randn(64, device=dev)
+y = torch.empty(B, S // 2, S // 2, 64, device=dev, dtype=torch.bfloat16)
+gz = torch.randn(B, S // 2, S // 2, 64, device=dev).to(torch.bfloat16)
+dw = torch.zeros(64, 6, 4, 4, device=dev); db = torch.zeros(64, device=dev)
+g0 = torch.empty_like(a0); g1 = torch.empty_like(a1)
+ws = torch.empty(32 * 576, dtype=torch.bfloat16, device=dev)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+nb_in, nb_map = 2 * a0.numel() * 4, y.numel() * 2
 cases = {
-    "fprop6": (lambda: L.call("b2c_first_fprop", a0, a1, None, None, None, w, None, b, y, N, S, S, 0.2), inb + outb),
-    "fprop3": (lambda: L.call("b2c_first_fprop", a0, None, None, None, None, w3, None, None, y, N, S, S, 0.2), inb // 2 + outb),
-    "wgrad6": (lambda: L.call("b2c_first_wgrad", a0, a1, None, None, None, gz, dw, db, N, S, S), inb + outb),
-    "wgrad3": (lambda: L.call("b2c_first_wgrad", a0, None, None, None, None, gz, dw3, None, N, S, S), inb // 2 + outb),
-    "dgrad6": (lambda: L.call("b2c_first_dgrad", gz, w, None, gx0, gx1, ws, N, S, S), inb + outb),
+    "first_fprop": (lambda: L.call("b2c_first_fprop", a0, a1, None, None, None, w, isg, bias, y, B, S, S, 0.2), nb_in + nb_map),
+    "first_wgrad": (lambda: L.call("b2c_first_wgrad", a0, a1, None, None, None, gz, dw, db, B, S, S), nb_in + nb_map),
+    "first_dgrad": (lambda: L.call("b2c_first_dgrad", gz, w, isg, g0, g1, ws, B, S, S), nb_in + nb_map),
 }
-for name, (fn, nbytes) in cases.items():
-    for _ in range(3):
-        fn()
-    ts = []
-    for _ in range(10):
+for name, (fn, nb) in cases.items():
+    fn(); ts = []
+    for _ in range(iters):
         flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); fn(); e1.record(); torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1))
     t = sorted(ts)[len(ts) // 2]
-    print(f"{name}: {t*1e3:8.1f} us  {nbytes/t/1e6:8.1f} GB/s (algorithmic {nbytes/1e6:.0f} MB)")
+    print(f"{name:12s} B={B} S={S}: {t*1e3:8.1f} us  {nb/t/1e6:8.0f} GB/s of {nb/1e6:.0f} MB")
