@@ -27,6 +27,7 @@ struct ConvT64Params {
   int f32out;            // fp32 check mode (b2c_set_f32_output): y is float*, accumulators stored unrounded
   const __nv_bfloat16* act;  // nullable: dense (N,2H,2W,64) activation a = LeakyReLU(z); y *= (a > 0 ? 1 : slope), i.e. the
   float slope;               // backward of the LeakyReLU that produced this conv's input, fused into its data gradient
+  int st256;                 // y and ldy allow 32-byte stores
 };
 
 namespace {
@@ -49,6 +50,10 @@ __device__ __forceinline__ int axis_pairs(int d, int (&par)[2], int (&tap)[2]) {
 // PERSISTENT: one CTA per SM walks pixel tiles blockIdx.x, blockIdx.x + gridDim.x, ...  The TMA producer runs ahead
 // across tile boundaries (the rings never drain), and the 512 TMEM columns hold two 256-column accumulator sets, so the
 // epilogue of tile i (TMEM -> bf16 NHWC stores + InstanceNorm statistics) overlaps the MMAs of tile i + 1.
+// ACT = the fused LeakyReLU-backward variant (never combined with statistics): the 4 x 128-byte activation rows a thread
+// needs for its tile are fetched with 256-bit loads BEFORE it waits for the accumulator, so their latency hides behind the
+// MMAs instead of being paid once per 32-channel chunk.
+template <bool ACT>
 __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__ CUtensorMap tmA,
                                                          const __grid_constant__ CUtensorMap tmB, ConvT64Params p,
                                                          int ntiles) {
@@ -169,14 +174,24 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
       const bool valid = n < p.N;
       const int buf = lt & 1;
       const uint32_t acc = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
+      uint32_t am[ACT ? 4 : 1][ACT ? 32 : 1];
+      if (ACT && valid) {
+#pragma unroll
+        for (int parity = 0; parity < 4; ++parity) {
+          const int oy = 2 * (y0 + bh) + (parity >> 1), ox = 2 * (x0 + bw) + (parity & 1);
+          const __nv_bfloat16* a = p.act + (((long long)n * Ho + oy) * Wo + ox) * 64;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) ld_global_nc_v8(a + 16 * j, &am[ACT ? parity : 0][ACT ? 8 * j : 0]);
+        }
+      }
       mbar_wait(&tmem_full[buf], (lt >> 1) & 1);
       tc_fence_after();
-#pragma unroll 1
+#pragma unroll(ACT ? 2 : 1)
       for (int c0 = 0; c0 < 64; c0 += 32) {
         float f[32], sq[32];  // per-channel partial statistics of this pixel over the 4 parities
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = sq[j] = 0.f;
-#pragma unroll 1
+#pragma unroll(ACT ? 4 : 1)
         for (int parity = 0; parity < 4; ++parity) {
           const int oy = 2 * (y0 + bh) + (parity >> 1), ox = 2 * (x0 + bw) + (parity & 1);
           __nv_bfloat16* dst = p.y + (((long long)n * Ho + oy) * Wo + ox) * p.ldy;
@@ -189,20 +204,14 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty[buf]);
           }
-          if (p.act && valid) {  // fused LeakyReLU backward: scale by the slope where the forward activation was <= 0
-            const uint4* a4 = reinterpret_cast<const uint4*>(p.act + (((long long)n * Ho + oy) * Wo + ox) * 64 + c0);
+          if (ACT && valid) {  // fused LeakyReLU backward: scale by the slope where the forward activation was <= 0
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint4 u = __ldg(a4 + j);
-              const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float2 t = unpack_bf16(w4[e]);
-                uint32_t* v = j < 2 ? v0 : v1;
-                const int i0 = (j & 1) * 8 + 2 * e;
-                if (!(t.x > 0.f)) v[i0] = __float_as_uint(__uint_as_float(v[i0]) * p.slope);
-                if (!(t.y > 0.f)) v[i0 + 1] = __float_as_uint(__uint_as_float(v[i0 + 1]) * p.slope);
-              }
+            for (int i = 0; i < 16; ++i) {
+              const float2 t = unpack_bf16(am[ACT ? parity : 0][ACT ? c0 / 2 + i : 0]);
+              uint32_t* v = i < 8 ? v0 : v1;
+              const int i0 = (2 * i) & 15;
+              if (!(t.x > 0.f)) v[i0] = __float_as_uint(__uint_as_float(v[i0]) * p.slope);
+              if (!(t.y > 0.f)) v[i0 + 1] = __float_as_uint(__uint_as_float(v[i0 + 1]) * p.slope);
             }
           }
           uint32_t o[16];
@@ -221,13 +230,18 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
                                       __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
             }
           } else if (valid) {
-            uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
-            d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
-            d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
-            d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
-            d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+            if (p.st256) {  // whole 32-byte sectors per store
+              st_global_v8(dst + c0, o);
+              st_global_v8(dst + c0 + 16, o + 8);
+            } else {
+              uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
+              d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+              d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+              d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
+              d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+            }
           }
-          if (p.stats) {  // statistics of the bf16-ROUNDED outputs (what the normalisation kernels will read)
+          if (!ACT && p.stats) {  // statistics of the bf16-ROUNDED outputs (what the normalisation kernels will read)
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               const float2 t = unpack_bf16(o[j]);
@@ -236,12 +250,12 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
             }
           }
         }
-        if (p.stats) {  // lane L ends up with channel c0 + L of this warp's 32 pixels x 4 parities
+        if (!ACT && p.stats) {  // lane L ends up with channel c0 + L of this warp's 32 pixels x 4 parities
           const float s1 = warp_transpose_sum32(f), s2 = warp_transpose_sum32(sq);
           red[q * 64 + c0 + lane] = make_float2(s1, s2);
         }
       }
-      if (p.stats) {  // combine the 4 epilogue warps, then one atomic per (channel, statistic) and tile
+      if (!ACT && p.stats) {  // combine the 4 epilogue warps, then one atomic per (channel, statistic) and tile
         named_bar_sync(1, 128);
         if (r < 64) {
           const float2 a = red[r], b = red[64 + r], c = red[128 + r], d = red[192 + r];
@@ -269,6 +283,7 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, 
   p.stats = nullptr;
   p.f32out = g_f32_output;
   p.act = (const __nv_bfloat16*)act; p.slope = slope;
+  p.st256 = (((uintptr_t)y & 31) == 0 && ldy % 16 == 0) ? 1 : 0;
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.kchunks = Cin / 64; p.y = (__nv_bfloat16*)y; p.ldy = ldy;
   p.BW = W < 128 ? W : 128;
   int rem = 128 / p.BW;
@@ -293,13 +308,16 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, 
   }
   static bool attr_done = false;
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(convt64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(convt64_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
     if (e != cudaSuccess) {
       b2c_set_error("cudaFuncSetAttribute(convt64): %s", cudaGetErrorString(e));
       return B2C_ERR_CUDA;
     }
     attr_done = true;
   }
+  B2C_REQUIRE(!(act && stats), "convt64: the fused LeakyReLU backward and the statistics epilogue are exclusive");
+  B2C_REQUIRE(!act || ((uintptr_t)act & 31) == 0, "convt64: act must be 32-byte aligned");
   const bool fuse_stats = stats && p.BI == 1;
   if (fuse_stats) {
     cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * (size_t)N * 64, (cudaStream_t)stream);
@@ -313,7 +331,8 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, 
     cudaGetDevice(&dev);
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
   }
-  convt64_kernel<<<ntiles < sms ? ntiles : sms, 192, CT_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p, ntiles);
+  if (act) convt64_kernel<true><<<ntiles < sms ? ntiles : sms, 192, CT_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p, ntiles);
+  else convt64_kernel<false><<<ntiles < sms ? ntiles : sms, 192, CT_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p, ntiles);
   int rc = b2c_check_launch("convt64_kernel");
   if (rc == 0 && stats && !fuse_stats) rc = b2c_in_stats(y, ldy, stats, N, 4 * H * W, 64, stream);
   return rc;

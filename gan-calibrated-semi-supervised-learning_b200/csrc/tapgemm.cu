@@ -33,6 +33,7 @@ struct TapGemmParams {
   float* gx1;
   float* stats;             // nullable: [N][Cout][2] += per-(image, channel) (sum, sum of squares) of y; needs BI == 1
   int f32out;               // fp32 check mode: y is float* and the accumulators are stored unrounded
+  int st256;                // y and ldy allow 32-byte (STG.256) stores
 };
 
 // MT = number of 128-row pixel tiles per CTA.  The kernels are bound by the L2 -> shared-memory stream, so with MT = 2
@@ -189,11 +190,16 @@ __global__ void __launch_bounds__(64 + 128 * MT) tapgemm_kernel(const __grid_con
         uint32_t o[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) o[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
-        uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
-        d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
-        d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
-        d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
-        d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+        if (p.st256) {
+          st_global_v8(dst + c0, o);
+          st_global_v8(dst + c0 + 16, o + 8);
+        } else {
+          uint4* d4 = reinterpret_cast<uint4*>(dst + c0);
+          d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+          d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+          d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
+          d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+        }
       }
       if (p.stats) {  // InstanceNorm statistics of this tile (all 128 rows belong to image n0): lane L gets channel c0 + L
         float sq[32];   // of the bf16-ROUNDED values, i.e. of exactly what the normalisation kernels will read
@@ -378,11 +384,16 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
           uint32_t o[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) o[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
-          uint4* d4 = reinterpret_cast<uint4*>(p.y + pix_off + c0);
-          d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
-          d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
-          d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
-          d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+          if (p.st256) {
+            st_global_v8(p.y + pix_off + c0, o);
+            st_global_v8(p.y + pix_off + c0 + 16, o + 8);
+          } else {
+            uint4* d4 = reinterpret_cast<uint4*>(p.y + pix_off + c0);
+            d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+            d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+            d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
+            d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+          }
         }
         if (p.stats) {  // statistics of the bf16-ROUNDED values; lane L gets channel c0 + L
           float sq[32];
@@ -460,6 +471,7 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
   TapGemmParams p;
   p.mode = mode; p.N = N; p.Cin = Cin; p.Cout = Cout; p.kchunks = Cin / 64;
   p.y = (__nv_bfloat16*)y; p.ldy = ldy; p.bias = bias; p.gx0 = p.gx1 = nullptr; p.stats = nullptr;
+  p.st256 = (((uintptr_t)y & 31) == 0 && ldy % 16 == 0) ? 1 : 0;
   p.f32out = g_f32_output;
   int TH, TW;
   CUtensorMap tmA, tmB;
@@ -559,7 +571,7 @@ extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_
   B2C_REQUIRE(ws && ((uintptr_t)ws & 15) == 0, "first_dgrad: workspace missing or unaligned");
   TapGemmParams p;
   p.mode = 2; p.N = N; p.Cin = 64; p.Cout = 32; p.kchunks = 1;
-  p.y = nullptr; p.ldy = 0; p.bias = nullptr; p.gx0 = gx0; p.gx1 = gx1; p.stats = nullptr; p.f32out = 0;
+  p.y = nullptr; p.ldy = 0; p.bias = nullptr; p.gx0 = gx0; p.gx1 = gx1; p.stats = nullptr; p.f32out = 0; p.st256 = 0;
   p.Ho = H / 2; p.Wo = W / 2;
   B2C_REQUIRE(pick_box(p.Ho, p.Wo, 128, &p.BW, &p.BH, &p.BI), "first_dgrad: unsupported spatial size %dx%d", H, W);
   p.tiles_x = p.Wo / p.BW; p.tiles_y = p.Ho / p.BH;
