@@ -247,7 +247,8 @@ struct TapGemmPCfg {
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + RED_BYTES + 512 + 1024;
 };
 
-template <int BN>
+// MODE (0 = C4S2 conv, 1 = T4S2 transposed conv) is a template parameter so that profiles name the two families apart.
+template <int BN, int MODE>
 __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                     const __grid_constant__ CUtensorMap tmB, TapGemmParams p,
                                                                     int ptiles, int nblocks, int total) {
@@ -265,7 +266,7 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ntaps = p.mode == 0 ? 16 : 4;
+  const int ntaps = MODE == 0 ? 16 : 4;
   const int niters = ntaps * p.kchunks;
 
   if (warp == 0 && lane == 0) {
@@ -300,7 +301,7 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
             mbar_wait(&empty[stage], phase ^ 1);
             mbar_expect_tx(&full[stage], Cfg::A_BYTES + Cfg::B_BYTES);
             void* dA = sA + stage * Cfg::A_BYTES;
-            if (p.mode == 0) {
+            if (MODE == 0) {
               const int ky = tap >> 2, kx = tap & 3;
               const int fy = (ky - 1) >> 1, di = (ky - 1) & 1, fx = (kx - 1) >> 1, dj = (kx - 1) & 1;
               tma_load_5d(dA, &tmA, &full[stage], dj * p.Cin + cc * 64, x0 + fx, di, y0 + fy, n0);
@@ -348,7 +349,7 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
       const int py = parity >> 1, px = parity & 1, ncol0 = nb * BN;
       const int n = n0 + bi;
       int oy = y0 + bh, ox = x0 + bw;
-      if (p.mode == 1) { oy = 2 * oy + py; ox = 2 * ox + px; }
+      if (MODE == 1) { oy = 2 * oy + py; ox = 2 * ox + px; }
       const bool valid = n < p.N;
       const long long pix_off = (((long long)n * p.Ho + oy) * p.Wo + ox) * p.ldy + ncol0;
       const int buf = lt & 1;
@@ -528,15 +529,22 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
       int dev = 0;
       cudaGetDevice(&dev);
       if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
-      cudaFuncSetAttribute(tapgemm_persistent_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<128>::SMEM);
-      cudaFuncSetAttribute(tapgemm_persistent_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<256>::SMEM);
+      cudaFuncSetAttribute(tapgemm_persistent_kernel<128, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<128>::SMEM);
+      cudaFuncSetAttribute(tapgemm_persistent_kernel<128, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<128>::SMEM);
+      cudaFuncSetAttribute(tapgemm_persistent_kernel<256, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<256>::SMEM);
+      cudaFuncSetAttribute(tapgemm_persistent_kernel<256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<256>::SMEM);
     }
     const int ptiles = (int)grid.x, nblocks = (int)grid.y, total = (int)(grid.x * grid.y * grid.z);
     const int ctas = total < sms ? total : sms;
-    if (BN == 128)
-      tapgemm_persistent_kernel<128><<<ctas, 192, TapGemmPCfg<128>::SMEM, (cudaStream_t)stream>>>(tmA, tmB, p, ptiles, nblocks, total);
+    const cudaStream_t st = (cudaStream_t)stream;
+    if (BN == 128 && mode == 0)
+      tapgemm_persistent_kernel<128, 0><<<ctas, 192, TapGemmPCfg<128>::SMEM, st>>>(tmA, tmB, p, ptiles, nblocks, total);
+    else if (BN == 128)
+      tapgemm_persistent_kernel<128, 1><<<ctas, 192, TapGemmPCfg<128>::SMEM, st>>>(tmA, tmB, p, ptiles, nblocks, total);
+    else if (mode == 0)
+      tapgemm_persistent_kernel<256, 0><<<ctas, 192, TapGemmPCfg<256>::SMEM, st>>>(tmA, tmB, p, ptiles, nblocks, total);
     else
-      tapgemm_persistent_kernel<256><<<ctas, 192, TapGemmPCfg<256>::SMEM, (cudaStream_t)stream>>>(tmA, tmB, p, ptiles, nblocks, total);
+      tapgemm_persistent_kernel<256, 1><<<ctas, 192, TapGemmPCfg<256>::SMEM, st>>>(tmA, tmB, p, ptiles, nblocks, total);
     rc = b2c_check_launch("tapgemm_persistent_kernel");
   } else if (BN == 256 && MT == 2) rc = launch_tapgemm<256, 2>(tmA, tmB, p, grid, (cudaStream_t)stream);
   else if (BN == 128 && MT == 2) rc = launch_tapgemm<128, 2>(tmA, tmB, p, grid, (cudaStream_t)stream);

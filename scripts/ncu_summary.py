@@ -1,7 +1,7 @@
 """Summarise an `ncu --set full` capture (exported with `ncu -i rep --page raw --csv`) per launch and per kernel family.
 Usage: python scripts/ncu_summary.py raw.csv [traffic.json]
-Families follow the C-ABI entry points: convT = convt64_kernel + tapgemm_kernel launched with 4 parities (grid.z = 4),
-conv = the other tapgemm_kernel<64|128|256> launches, wgrad = wgrad_kernel."""
+Families follow the C-ABI entry points: convT = convt64_kernel + tapgemm_persistent_kernel<BN, 1> + tapgemm_kernel launched
+with 4 parities (grid.z = 4), conv = tapgemm_persistent_kernel<BN, 0> + the other tapgemm_kernel launches, wgrad = wgrad_kernel."""
 import collections
 import csv
 import json
@@ -42,6 +42,9 @@ def family(name, grid):
         return "b2c_wgrad4s2_bf16"
     if "tapgemm_kernel<(int)32" in name or "tapgemm_kernel<32" in name:
         return "b2c_first_dgrad"
+    m = re.search(r"tapgemm_persistent_kernel<\(?(?:int\))?\d+, \(?(?:int\))?(\d)>", name)
+    if m:
+        return "b2c_convt4s2_bf16" if m.group(1) == "1" else "b2c_conv4s2_bf16"
     if "tapgemm" in name:
         z = int(re.findall(r"\d+", grid)[2])
         return "b2c_convt4s2_bf16" if z == 4 else "b2c_conv4s2_bf16"
@@ -54,7 +57,7 @@ for r in rows[2:]:
     name, grid = r[C["name"]], r[C["grid"]]
     us, by = val(r, "dur"), val(r, "rd") + val(r, "wr")
     t = float(r[C["tensor"]]) if C["tensor"] is not None and r[C["tensor"]] not in ("", "n/a") else 0.0
-    print(f"{re.sub(r'[(].*', '', name)[:44]:44s} {grid:>16s} {us:8.1f} {by/1e6:8.1f} {t:8.1f} "
+    print(f"{re.sub(r'[(]FirstIn.*|[(]CUtensorMap.*|[(]const.*', '', name).replace('(int)', '').replace('(bool)', '')[:44]:44s} {grid:>16s} {us:8.1f} {by/1e6:8.1f} {t:8.1f} "
           f"{float(r[C['lts']]):6.1f} {float(r[C['dram']]):6.1f} {r[C['regs']]:>5s}")
     f = fam[family(name, grid)]
     f[0] += 1; f[1] += us; f[2] += by; f[3] += t * us
