@@ -413,6 +413,12 @@ def run_infer(args):
 
 if __name__ == "__main__":
     a = parse()
+    # The contract is ONE JSON line on stdout.  Libraries (NCCL prints its version banner to stdout) must not share it:
+    # file descriptor 1 is pointed at stderr for the run and the JSON line goes to the saved original.
+    sys.stdout.flush()
+    _json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = _json_out
     if a.mode == "infer":
         if int(os.environ.get("RANK", "0")) == 0:
             run_infer(a)

@@ -31,8 +31,15 @@ struct ConvT64Params {
 };
 
 namespace {
-constexpr int CT_NA = 6;                   // activation ring: [128 pixels][64 channels] bf16 boxes
-constexpr int CT_NB = 12;                  // weight ring: [64 cout][64 cin] bf16 slices (1, 2 or 4 consumed per box)
+constexpr int CT_NA = 5;                   // activation ring: [128 pixels][64 channels] bf16 boxes
+constexpr int CT_NB = 16;                  // weight ring: [64 cout][64 cin] bf16 slices (1, 2 or 4 consumed per box)
+// Shift order: centre first, then the two vertical neighbours, then the rest.  The centre box feeds all four parities and
+// a vertical neighbour feeds parities (0,1) or (2,3), whose accumulators are adjacent TMEM columns: their 4 / 2 weight
+// slices sit in consecutive ring slots (a tile consumes 16*kchunks slots and those groups start at multiples of 4 / 2,
+// so they never wrap) and are multiplied by ONE N = 256 / N = 128 MMA per k-step instead of 4 / 2 N = 64 MMAs that would
+// each re-read the activation box from shared memory (the shared-memory port is what bounds this kernel).  Centre first
+// also makes the accumulate flag uniform over a merged group.
+__device__ __forceinline__ int ct_shift(int i) { return (int)((0x862053714ull >> (4 * i)) & 15ull); }
 constexpr int CT_A_BYTES = 128 * 128;
 constexpr int CT_SLICE_BYTES = 64 * 128;
 constexpr int CT_RED_BYTES = 4 * 64 * 8;   // statistics scratch of the 4 epilogue warps
@@ -101,7 +108,8 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, tn = tile / (p.tiles_x * p.tiles_y);
         const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
-        for (int s = 0; s < 9; ++s) {
+        for (int si = 0; si < 9; ++si) {
+          const int s = ct_shift(si);
           const int dy = s / 3 - 1, dx = s % 3 - 1;
           int pyv[2], av[2], pxv[2], bv[2];
           const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
@@ -124,7 +132,8 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 0);
+      constexpr uint32_t idesc64 = umma_idesc_bf16(128, 64, 0, 0), idesc128 = umma_idesc_bf16(128, 128, 0, 0),
+                         idesc256 = umma_idesc_bf16(128, 256, 0, 0);
       int sa = 0, pa = 0, sb = 0, pb = 0, lt = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
         const int buf = lt & 1;
@@ -132,16 +141,32 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
         mbar_wait(&tmem_empty[buf], ((lt >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator set
         tc_fence_after();
         uint32_t touched = 0;  // parities whose accumulator already holds a partial sum
-        for (int s = 0; s < 9; ++s) {
+        for (int si = 0; si < 9; ++si) {
+          const int s = ct_shift(si);
           const int dy = s / 3 - 1, dx = s % 3 - 1;
           int pyv[2], av[2], pxv[2], bv[2];
           const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
           for (int cc = 0; cc < p.kchunks; ++cc) {
             mbar_wait(&fullA[sa], pa);
             const uint32_t a0 = smem_u32(sA + sa * CT_A_BYTES);
-            for (int iy = 0; iy < ny; ++iy)
-              for (int ix = 0; ix < nx; ++ix) {
-                const int parity = pyv[iy] * 2 + pxv[ix];
+            if (dx == 0) {  // merged group: parities (2*py, 2*py+1) for a vertical neighbour, all four for the centre
+              const int g = 2 * ny, parity0 = pyv[0] * 2;
+              for (int i = 0; i < g; ++i) mbar_wait(&fullB[sb + i], pb);
+              tc_fence_after();
+              const uint32_t bs = smem_u32(sB + sb * CT_SLICE_BYTES);
+              const uint32_t had = (touched >> parity0) & 1u;
+              const uint32_t idesc = g == 4 ? idesc256 : idesc128;
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma_bf16(acc + parity0 * 64, umma_desc_sw128(a0 + k * 32, 16, 1024), umma_desc_sw128(bs + k * 32, 16, 1024),
+                          idesc, (uint32_t)(had | (k != 0)));
+              touched |= (g == 4 ? 0xFu : 0x3u) << parity0;
+              for (int i = 0; i < g; ++i) umma_commit(&emptyB[sb + i]);
+              sb += g;
+              if (sb == CT_NB) { sb = 0; pb ^= 1; }
+            } else {
+              for (int iy = 0; iy < ny; ++iy) {
+                const int parity = pyv[iy] * 2 + pxv[0];
                 mbar_wait(&fullB[sb], pb);
                 tc_fence_after();
                 const uint32_t bs = smem_u32(sB + sb * CT_SLICE_BYTES);
@@ -149,11 +174,12 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
                   umma_bf16(acc + parity * 64, umma_desc_sw128(a0 + k * 32, 16, 1024),
-                            umma_desc_sw128(bs + k * 32, 16, 1024), idesc, (uint32_t)(had | (k != 0)));
+                            umma_desc_sw128(bs + k * 32, 16, 1024), idesc64, (uint32_t)(had | (k != 0)));
                 touched |= 1u << parity;
                 umma_commit(&emptyB[sb]);
                 if (++sb == CT_NB) { sb = 0; pb ^= 1; }
               }
+            }
             umma_commit(&emptyA[sa]);
             if (++sa == CT_NA) { sa = 0; pa ^= 1; }
           }
