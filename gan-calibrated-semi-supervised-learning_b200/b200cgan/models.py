@@ -221,13 +221,14 @@ class GeneratorUNet(nn.Module):
         return [self.down4.model[-1], self.up1.model[-1], self.up2.model[-1]]
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        d1 = self.down1(x)
-        d2 = self.down2(d1)
-        d3 = self.down3(d2)
+        # each skip tensor has two consumers; SkipTap sums their gradients with one strided kernel
+        d1, s1 = ops.SkipTap.apply(self.down1(x))
+        d2, s2 = ops.SkipTap.apply(self.down2(d1))
+        d3, s3 = ops.SkipTap.apply(self.down3(d2))
         d4 = self.down4(d3)
-        u1 = self.up1(d4, d3)
-        u2 = self.up2(u1, d2)
-        u3 = self.up3(u2, d1)
+        u1 = self.up1(d4, s3)
+        u2 = self.up2(u1, s2)
+        u3 = self.up3(u2, s1)
         conv = self.up4[0]
         wctx = ops.WeightCtx(conv.weight)
         wctx.want_stats = True

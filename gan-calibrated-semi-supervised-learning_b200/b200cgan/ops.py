@@ -376,6 +376,38 @@ class INAct(torch.autograd.Function):
         return gz, None, None, gskip, None
 
 
+class SkipTap(torch.autograd.Function):
+    """(x, x) for a tensor with two consumers (U-Net skip, cgan/models.py:224-230): the two incoming gradients - one dense,
+    one a channel slice of the concat gradient - are summed by one strided kernel instead of autograd's generic add."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.view_as(x), x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, ga, gb):
+        if ga is None or gb is None:
+            return ga if gb is None else gb
+        return AddStrided.apply(ga, gb)
+
+
+class AddStrided(torch.autograd.Function):
+    """a + b on NHWC bf16 tensors that may be channel slices; linear, so its backward passes g to both."""
+
+    @staticmethod
+    def forward(ctx, a, b):
+        a, lda = as_nhwc(a)
+        b, ldb = as_nhwc(b)
+        N, C, H, W = a.shape
+        out = cl_empty(N, C, H, W, device=a.device)
+        _lib.call("b2c_add_strided", a, lda, b, ldb, out, C, N * H * W, C)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, g
+
+
 class INActBwd(torch.autograd.Function):
     """g_z = d/dz of dropout(act(IN(z))) applied to g.  Its backward is the InstanceNorm backward-of-backward."""
 

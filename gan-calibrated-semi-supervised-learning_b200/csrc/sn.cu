@@ -25,52 +25,57 @@ __device__ __forceinline__ float block_sum(float v, float* sh) {
 }
 
 // Power iteration in three atomic-free launches (deterministic, so u/v stay bit-identical on every data-parallel rank):
-//   wtu   : part[rs][k] = sum_{r in row chunk rs} W[r][k] u[r]           grid (K/128, RS), 8 independent loads in flight
-//   wv    : t = sum_rs part[rs]  (every block re-derives it into shared memory, K <= 4096 floats), v = t / max(|t|, eps),
-//           s[r] = W[r] . v for the block's SN_ROWS rows (W streamed once, coalesced)
+//   wtu   : one block per 32-column strip of W: t[k] = sum_r W[r][k] u[r] over ALL rows (16 warps take rows r = warp mod 16,
+//           8 independent 128-byte row loads in flight per warp, fixed-order combine in shared memory) and the strip's
+//           sum of t^2 - no partial-sum array for the next kernel to re-reduce
+//   wv    : v = t / max(|t|, eps) (|t|^2 = fixed-order sum of the <= 128 strip partials, re-derived by every block into
+//           shared memory, K <= 4096 floats), s[r] = W[r] . v for the block's SN_ROWS rows (W streamed once, coalesced)
 //   finish: u = s / max(|s|, eps), sigma = u . s
-constexpr int SN_CHUNK = 32;  // rows per wtu block
+constexpr int SN_STRIP = 32;  // columns per wtu block
 constexpr int SN_ROWS = 4;    // rows per wv block
 constexpr int SN_MAXK = 4096;
 
-__global__ void __launch_bounds__(128) sn_wtu_kernel(const float* __restrict__ W, const float* __restrict__ u,
-                                                      float* __restrict__ part, int R, int K) {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  const int r0 = blockIdx.y * SN_CHUNK;
-  if (k >= K) return;
+__global__ void __launch_bounds__(512) sn_wtu_kernel(const float* __restrict__ W, const float* __restrict__ u,
+                                                      float* __restrict__ t, float* __restrict__ ssp, int R, int K) {
+  __shared__ float red[16][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int k = blockIdx.x * SN_STRIP + lane;
   float acc = 0.f;
-  const int r1 = min(r0 + SN_CHUNK, R);
-  int r = r0;
-  for (; r + 8 <= r1; r += 8) {
-    float w[8];
+  if (k < K) {
+    int r = warp;
+    for (; r + 7 * 16 < R; r += 8 * 16) {
+      float w[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) w[j] = __ldg(W + (long long)(r + j) * K + k);
+      for (int j = 0; j < 8; ++j) w[j] = __ldg(W + (long long)(r + 16 * j) * K + k);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc += w[j] * __ldg(u + r + j);
+      for (int j = 0; j < 8; ++j) acc += w[j] * __ldg(u + r + 16 * j);
+    }
+    for (; r < R; r += 16) acc += __ldg(W + (long long)r * K + k) * __ldg(u + r);
   }
-  for (; r < r1; ++r) acc += __ldg(W + (long long)r * K + k) * __ldg(u + r);
-  part[(long long)blockIdx.y * K + k] = acc;
+  red[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0) {
+    float tk = 0.f;
+#pragma unroll
+    for (int w = 0; w < 16; ++w) tk += red[w][lane];
+    if (k < K) t[k] = tk; else tk = 0.f;
+    const float ss = warp_sum(tk * tk);
+    if (lane == 0) ssp[blockIdx.x] = ss;
+  }
 }
 
-__global__ void __launch_bounds__(256) sn_wv_kernel(const float* __restrict__ W, const float* __restrict__ part,
-                                                     float* __restrict__ v, float* __restrict__ s, int R, int K, int RS,
-                                                     int update_v) {
+__global__ void __launch_bounds__(256) sn_wv_kernel(const float* __restrict__ W, const float* __restrict__ t,
+                                                     const float* __restrict__ ssp, float* __restrict__ v,
+                                                     float* __restrict__ s, int R, int K, int NS, int update_v) {
   __shared__ float ts[SN_MAXK];
-  __shared__ float sh[32];
   __shared__ float red[SN_ROWS][8];
-  float inv = 1.f;
   if (update_v) {
-    float ss = 0.f;
+    float ss = 0.f;  // every warp derives the same value in the same order
+    for (int i = threadIdx.x & 31; i < NS; i += 32) ss += ssp[i];
+    ss = warp_sum(ss);
+    const float inv = 1.f / fmaxf(sqrtf(ss), 1e-12f);
     for (int k = threadIdx.x; k < K; k += 256) {
-      float t = 0.f;
-      for (int j = 0; j < RS; ++j) t += part[(long long)j * K + k];
-      ts[k] = t;
-      ss += t * t;
-    }
-    ss = block_sum(ss, sh);
-    inv = 1.f / fmaxf(sqrtf(ss), 1e-12f);
-    for (int k = threadIdx.x; k < K; k += 256) {
-      const float vk = ts[k] * inv;
+      const float vk = t[k] * inv;
       ts[k] = vk;
       if (blockIdx.x == 0) v[k] = vk;
     }
@@ -96,10 +101,10 @@ __global__ void __launch_bounds__(256) sn_wv_kernel(const float* __restrict__ W,
   }
   __syncthreads();
   if (threadIdx.x < SN_ROWS && r0 + threadIdx.x < R) {
-    float t = 0.f;
+    float tt = 0.f;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) t += red[threadIdx.x][w];
-    s[r0 + threadIdx.x] = t;
+    for (int w = 0; w < 8; ++w) tt += red[threadIdx.x][w];
+    s[r0 + threadIdx.x] = tt;
   }
 }
 
@@ -124,15 +129,16 @@ __global__ void sn_finish_kernel(const float* __restrict__ s, float* __restrict_
   if (threadIdx.x == 0) { sig[0] = sigma; sig[1] = 1.f / sigma; }
 }
 
-// ws: fp32 scratch of ceil(R/32)*K + R floats.  u[R], v[K] updated in place when train != 0.  sig[2] <- (sigma, 1/sigma).
+// ws: fp32 scratch of K + ceil(K/32) + R floats (ceil(R/32)*K + R is enough whenever R > 32).  u[R], v[K] updated in place
+// when train != 0.  sig[2] <- (sigma, 1/sigma).
 extern "C" int b2c_sn_power_iter(const float* W, float* u, float* v, float* sig, float* ws, int R, int K, int train,
                                  void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   B2C_REQUIRE(K <= SN_MAXK, "sn_power_iter: K=%d exceeds %d", K, SN_MAXK);
-  const int RS = (R + SN_CHUNK - 1) / SN_CHUNK;
-  float* part = ws; float* s = ws + (long long)RS * K;
-  if (train) sn_wtu_kernel<<<dim3((K + 127) / 128, RS), 128, 0, st>>>(W, u, part, R, K);
-  sn_wv_kernel<<<(R + SN_ROWS - 1) / SN_ROWS, 256, 0, st>>>(W, part, v, s, R, K, RS, train ? 1 : 0);
+  const int NS = (K + SN_STRIP - 1) / SN_STRIP;
+  float* t = ws; float* ssp = ws + K; float* s = ssp + NS;
+  if (train) sn_wtu_kernel<<<NS, 512, 0, st>>>(W, u, t, ssp, R, K);
+  sn_wv_kernel<<<(R + SN_ROWS - 1) / SN_ROWS, 256, 0, st>>>(W, t, ssp, v, s, R, K, NS, train ? 1 : 0);
   sn_finish_kernel<<<1, 256, 0, st>>>(s, u, sig, R, train ? 1 : 0);
   return b2c_check_launch("sn_power_iter");
 }

@@ -67,10 +67,14 @@ int b2c_in_act_bwd2(const void* h, long long ldh, const void* g, long long ldg, 
                     long long ldgx, int N, int HW, int C, void* stream);
 int b2c_lrelu_bwd(const void* g, const void* a, void* out, long long n, float slope, void* stream);
 int b2c_copy_strided(const void* src, long long lds, void* dst, long long ldd, long long npix, int C, void* stream);
+/* out = a + b on NHWC channel slices (pixel strides lda/ldb/ldo): gradient accumulation of a U-Net skip tensor that feeds
+   both the next down block and the concat (cgan/models.py:82,224-230), replacing autograd's strided add. */
+int b2c_add_strided(const void* a, long long lda, const void* b, long long ldb, void* out, long long ldo, long long npix,
+                    int C, void* stream);
 int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsigned long long offset,
                      const long long* offset_base, void* stream); /* stream position = offset + *offset_base (device, nullable) */
 
-/* ---- spectral norm (torch spectral_norm.py:92-114); ws: ceil(R/32)*K + R floats of scratch ---- */
+/* ---- spectral norm (torch spectral_norm.py:92-114); ws: K + ceil(K/32) + R floats of scratch (ceil(R/32)*K + R suffices for R > 32) ---- */
 int b2c_sn_power_iter(const float* W, float* u, float* v, float* sig, float* ws, int R, int K, int train, void* stream);
 int b2c_sn_bwd(const float* dWe, const float* W, const float* u, const float* v, const float* sig, float* ws, float* dW,
                int R, int K, int accumulate, void* stream);
