@@ -11,6 +11,7 @@
 // Warp roles as in tapgemm.cu: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2-5 = epilogue.
 // Activation boxes and weight slices travel through two separate mbarrier rings (a box is used by a variable number of
 // slices), produced and consumed in the same order, so both rings stay full: 192 KB in flight per SM.
+#include <cstdlib>
 #include "common.cuh"
 #include "tmap.h"
 
@@ -28,23 +29,25 @@ struct ConvT64Params {
   const __nv_bfloat16* act;  // nullable: dense (N,2H,2W,64) activation a = LeakyReLU(z); y *= (a > 0 ? 1 : slope), i.e. the
   float slope;               // backward of the LeakyReLU that produced this conv's input, fused into its data gradient
   int st256;                 // y and ldy allow 32-byte stores
+  int nmerge;                // centre-first shift order with merged N = 256 / 128 MMAs (B2C_CONVT_NMERGE=1 enables)
 };
 
 namespace {
-constexpr int CT_NA = 5;                   // activation ring: [128 pixels][64 channels] bf16 boxes
-constexpr int CT_NB = 16;                  // weight ring: [64 cout][64 cin] bf16 slices (1, 2 or 4 consumed per box)
-// Shift order: centre first, then the two vertical neighbours, then the rest.  The centre box feeds all four parities and
-// a vertical neighbour feeds parities (0,1) or (2,3), whose accumulators are adjacent TMEM columns: their 4 / 2 weight
-// slices sit in consecutive ring slots (a tile consumes 16*kchunks slots and those groups start at multiples of 4 / 2,
-// so they never wrap) and are multiplied by ONE N = 256 / N = 128 MMA per k-step instead of 4 / 2 N = 64 MMAs that would
-// each re-read the activation box from shared memory (the shared-memory port is what bounds this kernel).  Centre first
-// also makes the accumulate flag uniform over a merged group.
-__device__ __forceinline__ int ct_shift(int i) { return (int)((0x862053714ull >> (4 * i)) & 15ull); }
+constexpr int CT_NA = 6;                   // activation ring: [128 pixels][64 channels] bf16 boxes
+constexpr int CT_NB = 12;                  // weight ring: [64 cout][64 cin] bf16 slices (1, 2 or 4 consumed per box)
 constexpr int CT_A_BYTES = 128 * 128;
 constexpr int CT_SLICE_BYTES = 64 * 128;
 constexpr int CT_RED_BYTES = 4 * 64 * 8;   // statistics scratch of the 4 epilogue warps
 constexpr int CT_SMEM = CT_NA * CT_A_BYTES + CT_NB * CT_SLICE_BYTES + CT_RED_BYTES + 512 + 1024;
 }  // namespace
+
+// Shift visiting order.  Raster (merge = 0): s = 0..8.  Merged: centre, the two vertical neighbours, then the rest - the
+// centre box feeds all four parities and a vertical neighbour feeds parities (0,1) or (2,3), whose accumulators are adjacent
+// TMEM columns, so their 4 / 2 weight slices (consecutive ring slots; a tile consumes 16*kchunks slots and these groups start
+// at multiples of 4 / 2, so with CT_NB = 12 they never wrap) are multiplied by ONE N = 256 / N = 128 MMA per k-step instead
+// of 4 / 2 N = 64 MMAs that each re-read the activation box from shared memory.  Centre first makes the accumulate flag
+// uniform over a merged group.
+__device__ __forceinline__ int ct_shift(int i, int merge) { return merge ? (int)((0x862053714ull >> (4 * i)) & 15ull) : i; }
 
 // Weight slices that read shift d in {-1,0,+1} along one axis: (parity bit, tap bit) pairs with parity + tap - 1 == d.
 __device__ __forceinline__ int axis_pairs(int d, int (&par)[2], int (&tap)[2]) {
@@ -109,7 +112,7 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
         const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, tn = tile / (p.tiles_x * p.tiles_y);
         const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
         for (int si = 0; si < 9; ++si) {
-          const int s = ct_shift(si);
+          const int s = ct_shift(si, p.nmerge);
           const int dy = s / 3 - 1, dx = s % 3 - 1;
           int pyv[2], av[2], pxv[2], bv[2];
           const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
@@ -142,15 +145,16 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
         tc_fence_after();
         uint32_t touched = 0;  // parities whose accumulator already holds a partial sum
         for (int si = 0; si < 9; ++si) {
-          const int s = ct_shift(si);
+          const int s = ct_shift(si, p.nmerge);
           const int dy = s / 3 - 1, dx = s % 3 - 1;
           int pyv[2], av[2], pxv[2], bv[2];
           const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
           for (int cc = 0; cc < p.kchunks; ++cc) {
             mbar_wait(&fullA[sa], pa);
             const uint32_t a0 = smem_u32(sA + sa * CT_A_BYTES);
-            if (dx == 0) {  // merged group: parities (2*py, 2*py+1) for a vertical neighbour, all four for the centre
-              const int g = 2 * ny, parity0 = pyv[0] * 2;
+            const int g = ny * nx;
+            if (dx == 0 && p.nmerge && sb + g <= CT_NB) {  // merged: parities (2py, 2py+1), or all four for the centre
+              const int parity0 = pyv[0] * 2;
               for (int i = 0; i < g; ++i) mbar_wait(&fullB[sb + i], pb);
               tc_fence_after();
               const uint32_t bs = smem_u32(sB + sb * CT_SLICE_BYTES);
@@ -165,8 +169,8 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
               sb += g;
               if (sb == CT_NB) { sb = 0; pb ^= 1; }
             } else {
-              for (int iy = 0; iy < ny; ++iy) {
-                const int parity = pyv[iy] * 2 + pxv[0];
+              for (int i = 0; i < g; ++i) {
+                const int parity = pyv[i / nx] * 2 + pxv[i % nx];
                 mbar_wait(&fullB[sb], pb);
                 tc_fence_after();
                 const uint32_t bs = smem_u32(sB + sb * CT_SLICE_BYTES);
@@ -310,6 +314,8 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, 
   p.f32out = g_f32_output;
   p.act = (const __nv_bfloat16*)act; p.slope = slope;
   p.st256 = (((uintptr_t)y & 31) == 0 && ldy % 16 == 0) ? 1 : 0;
+  static const int nmerge = (getenv("B2C_CONVT_NMERGE") && getenv("B2C_CONVT_NMERGE")[0] == '1') ? 1 : 0;
+  p.nmerge = nmerge;
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.kchunks = Cin / 64; p.y = (__nv_bfloat16*)y; p.ldy = ldy;
   p.BW = W < 128 ? W : 128;
   int rem = 128 / p.BW;
