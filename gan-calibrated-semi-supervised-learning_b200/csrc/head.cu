@@ -5,88 +5,128 @@
 
 using namespace b2c;
 
-// Each input pixel is read ONCE: a warp owns a pixel, computes its 16 per-tap dot products
-// P[t] = a[n,iy,ix,:] . w[:,t] and scatters them to the (up to 16) score pixels they belong to,
-// out[n,iy-ky+1,ix-kx+1] += P[ky*4+kx].  `out` must be zeroed by the caller (the C entry point does it).
-__global__ void __launch_bounds__(256) head_fprop_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ w,
-                                                         float* __restrict__ out, int N, int h, int C) {
-  extern __shared__ float w_s[];  // [16 taps][C]
+// Stage w[c][16 taps] as w_s[tap][C] with the 8-float groups of a row XOR-swizzled by the tap (the plain transpose is a
+// 16-way bank conflict); readers use hw_off(t, c) for an aligned group of 4 or 8 channels.
+__device__ __forceinline__ int hw_off(int t, int c, int C) { return t * C + ((((c >> 3) ^ t) << 3) | (c & 7)); }
+__device__ __forceinline__ void head_stage_w(const float* __restrict__ w, float* w_s, int C) {
   for (int i = threadIdx.x; i < 16 * C; i += blockDim.x) {
     const int c = i / 16, t = i % 16;
-    w_s[t * C + c] = w[i];
+    w_s[hw_off(t, c, C)] = w[i];
   }
   __syncthreads();
+}
+
+// Each input pixel is read ONCE: a warp owns HP consecutive pixels, computes their 16 per-tap dot products
+// P[t] = a[n,iy,ix,:] . w[:,t] (one pass over the shared-memory weights serves all HP pixels) and scatters them to the
+// (up to 16) score pixels they belong to, out[n,iy-ky+1,ix-kx+1] += P[ky*4+kx].  `out` must be zeroed by the caller
+// (the C entry point does it).
+constexpr int HP = 4;
+__global__ void __launch_bounds__(256) head_fprop_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ w,
+                                                         float* __restrict__ out, int N, int h, int C) {
+  extern __shared__ float w_s[];  // [16 taps][C], swizzled
+  head_stage_w(w, w_s, C);
   const int ho = h - 1;
   const long long npix = (long long)N * h * h;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
-  for (long long pix = (long long)blockIdx.x * wpb + warp; pix < npix; pix += (long long)gridDim.x * wpb) {
-    const int ix = (int)(pix % h), iy = (int)((pix / h) % h), n = (int)(pix / ((long long)h * h));
-    float acc[16];
+  for (long long p0 = ((long long)blockIdx.x * wpb + warp) * HP; p0 < npix; p0 += (long long)gridDim.x * wpb * HP) {
+    float acc[HP][16];
 #pragma unroll
-    for (int t = 0; t < 16; ++t) acc[t] = 0.f;
-    const __nv_bfloat16* row = a + pix * C;
+    for (int q = 0; q < HP; ++q)
+#pragma unroll
+      for (int t = 0; t < 16; ++t) acc[q][t] = 0.f;
     for (int c = lane * 8; c < C; c += 256) {
-      const uint4 u = __ldg(reinterpret_cast<const uint4*>(row + c));
-      const float2 f0 = unpack_bf16(u.x), f1 = unpack_bf16(u.y), f2 = unpack_bf16(u.z), f3 = unpack_bf16(u.w);
+      float f[HP][8];
+#pragma unroll
+      for (int q = 0; q < HP; ++q) {
+        const uint4 u = p0 + q < npix ? __ldg(reinterpret_cast<const uint4*>(a + (p0 + q) * C + c)) : make_uint4(0, 0, 0, 0);
+        const float2 f0 = unpack_bf16(u.x), f1 = unpack_bf16(u.y), f2 = unpack_bf16(u.z), f3 = unpack_bf16(u.w);
+        f[q][0] = f0.x; f[q][1] = f0.y; f[q][2] = f1.x; f[q][3] = f1.y;
+        f[q][4] = f2.x; f[q][5] = f2.y; f[q][6] = f3.x; f[q][7] = f3.y;
+      }
 #pragma unroll
       for (int t = 0; t < 16; ++t) {
-        const float4 w0 = *reinterpret_cast<const float4*>(w_s + t * C + c);
-        const float4 w1 = *reinterpret_cast<const float4*>(w_s + t * C + c + 4);
-        acc[t] += f0.x * w0.x + f0.y * w0.y + f1.x * w0.z + f1.y * w0.w + f2.x * w1.x + f2.y * w1.y + f3.x * w1.z + f3.y * w1.w;
+        const float* wp = w_s + hw_off(t, c, C);
+        const float4 w0 = *reinterpret_cast<const float4*>(wp);
+        const float4 w1 = *reinterpret_cast<const float4*>(wp + 4);
+#pragma unroll
+        for (int q = 0; q < HP; ++q)
+          acc[q][t] += f[q][0] * w0.x + f[q][1] * w0.y + f[q][2] * w0.z + f[q][3] * w0.w + f[q][4] * w1.x + f[q][5] * w1.y +
+                       f[q][6] * w1.z + f[q][7] * w1.w;
       }
     }
-    // 16 values x 32 lanes -> lane t (< 16) ends up with the full sum of tap t (halving butterfly)
 #pragma unroll
-    for (int half = 8, off = 16; half >= 1; half >>= 1, off >>= 1) {
-      const bool upper = (lane & off) != 0;
+    for (int q = 0; q < HP; ++q) {
+      // 16 values x 32 lanes -> lane t (< 16) ends up with the full sum of tap t (halving butterfly)
 #pragma unroll
-      for (int j = 0; j < half; ++j) {
-        const float send = upper ? acc[j] : acc[j + half];
-        const float keep = upper ? acc[j + half] : acc[j];
-        acc[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+      for (int half = 8, off = 16; half >= 1; half >>= 1, off >>= 1) {
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int j = 0; j < half; ++j) {
+          const float send = upper ? acc[q][j] : acc[q][j + half];
+          const float keep = upper ? acc[q][j + half] : acc[q][j];
+          acc[q][j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
       }
-    }
-    float v = acc[0] + __shfl_xor_sync(0xffffffffu, acc[0], 1);
-    // after the butterfly lane L holds tap index built from its bits: bit4->+8, bit3->+4, bit2->+2, bit1->+1
-    const int t = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
-    if ((lane & 1) == 0) {
-      const int oy = iy - (t >> 2) + 1, ox = ix - (t & 3) + 1;
-      if (oy >= 0 && oy < ho && ox >= 0 && ox < ho) atomicAdd(out + ((long long)n * ho + oy) * ho + ox, v);
+      const float v = acc[q][0] + __shfl_xor_sync(0xffffffffu, acc[q][0], 1);
+      // after the butterfly lane L holds tap index built from its bits: bit4->+8, bit3->+4, bit2->+2, bit1->+1
+      const int t = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+      const long long pix = p0 + q;
+      if ((lane & 1) == 0 && pix < npix) {
+        const int ix = (int)(pix % h), iy = (int)((pix / h) % h), n = (int)(pix / ((long long)h * h));
+        const int oy = iy - (t >> 2) + 1, ox = ix - (t & 3) + 1;
+        if (oy >= 0 && oy < ho && ox >= 0 && ox < ho) atomicAdd(out + ((long long)n * ho + oy) * ho + ox, v);
+      }
     }
   }
 }
 
-// ga[n,iy,ix,c] = sum_{ky,kx} gy[n,iy-ky+1,ix-kx+1] * w[c][ky][kx].  64 threads x 8 channels per pixel; the weights
-// sit in shared memory as [tap][C] so a thread reads its 8 channels of a tap with two 16-byte loads.
+// ga[n,iy,ix,c] = sum_{ky,kx} gy[n,iy-ky+1,ix-kx+1] * w[c][ky][kx].  A thread owns 8 channels of DP horizontally adjacent
+// pixels, so every 32-byte weight read from shared memory feeds DP outputs; h must be a multiple of DP.
+constexpr int DP = 2;
 __global__ void __launch_bounds__(256) head_dgrad_kernel(const float* __restrict__ gy, const float* __restrict__ w,
                                                          __nv_bfloat16* __restrict__ ga, int N, int h, int C) {
-  extern __shared__ float w_s[];  // [16 taps][C]
-  for (int i = threadIdx.x; i < 16 * C; i += blockDim.x) {
-    const int c = i / 16, t = i % 16;
-    w_s[t * C + c] = w[i];
-  }
-  __syncthreads();
+  extern __shared__ float w_s[];  // [16 taps][C], swizzled
+  head_stage_w(w, w_s, C);
   const int ho = h - 1;
   const int cvecs = C / 8;
-  const long long total = (long long)N * h * h * cvecs;
+  const long long total = (long long)N * h * (h / DP) * cvecs;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int cv = (int)(i % cvecs);
-    const long long pix = i / cvecs;
-    const int ix = (int)(pix % h), iy = (int)((pix / h) % h), n = (int)(pix / ((long long)h * h));
-    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long long pp = i / cvecs;  // pixel pair
+    const int ix0 = (int)(pp % (h / DP)) * DP, iy = (int)((pp / (h / DP)) % h), n = (int)(pp / ((long long)(h / DP) * h));
+    float acc[DP][8];
+#pragma unroll
+    for (int q = 0; q < DP; ++q)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[q][j] = 0.f;
 #pragma unroll
     for (int t = 0; t < 16; ++t) {
-      const int oy = iy - (t >> 2) + 1, ox = ix - (t & 3) + 1;
-      if (oy < 0 || oy >= ho || ox < 0 || ox >= ho) continue;
-      const float g = __ldg(gy + ((long long)n * ho + oy) * ho + ox);
-      const float4 w0 = *reinterpret_cast<const float4*>(w_s + t * C + cv * 8);
-      const float4 w1 = *reinterpret_cast<const float4*>(w_s + t * C + cv * 8 + 4);
-      acc[0] += g * w0.x; acc[1] += g * w0.y; acc[2] += g * w0.z; acc[3] += g * w0.w;
-      acc[4] += g * w1.x; acc[5] += g * w1.y; acc[6] += g * w1.z; acc[7] += g * w1.w;
+      const int oy = iy - (t >> 2) + 1;
+      if (oy < 0 || oy >= ho) continue;
+      float g[DP];
+      bool any = false;
+#pragma unroll
+      for (int q = 0; q < DP; ++q) {
+        const int ox = ix0 + q - (t & 3) + 1;
+        g[q] = (ox >= 0 && ox < ho) ? __ldg(gy + ((long long)n * ho + oy) * ho + ox) : 0.f;
+        any |= (ox >= 0 && ox < ho);
+      }
+      if (!any) continue;
+      const float* wp = w_s + hw_off(t, cv * 8, C);
+      const float4 w0 = *reinterpret_cast<const float4*>(wp);
+      const float4 w1 = *reinterpret_cast<const float4*>(wp + 4);
+#pragma unroll
+      for (int q = 0; q < DP; ++q) {
+        acc[q][0] += g[q] * w0.x; acc[q][1] += g[q] * w0.y; acc[q][2] += g[q] * w0.z; acc[q][3] += g[q] * w0.w;
+        acc[q][4] += g[q] * w1.x; acc[q][5] += g[q] * w1.y; acc[q][6] += g[q] * w1.z; acc[q][7] += g[q] * w1.w;
+      }
     }
-    uint4 o = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]), pack_bf16(acc[4], acc[5]),
-                         pack_bf16(acc[6], acc[7]));
-    *reinterpret_cast<uint4*>(ga + pix * C + cv * 8) = o;
+#pragma unroll
+    for (int q = 0; q < DP; ++q) {
+      const long long pix = ((long long)n * h + iy) * h + ix0 + q;
+      *reinterpret_cast<uint4*>(ga + pix * C + cv * 8) = make_uint4(pack_bf16(acc[q][0], acc[q][1]), pack_bf16(acc[q][2], acc[q][3]),
+                                                                  pack_bf16(acc[q][4], acc[q][5]), pack_bf16(acc[q][6], acc[q][7]));
+    }
   }
 }
 
@@ -132,10 +172,12 @@ __global__ void __launch_bounds__(256) head_wgrad_kernel(const __nv_bfloat16* __
       }
     }
   }
+  // the 2 x 16 taps of this thread are 128 contiguous bytes of dw: 8 vector reductions instead of 32 scalar atomics
+  float4* d4 = reinterpret_cast<float4*>(dw + (long long)c * 16);
 #pragma unroll
-  for (int t = 0; t < 16; ++t) {
-    atomicAdd(dw + (long long)c * 16 + t, acc0[t]);
-    atomicAdd(dw + (long long)(c + 1) * 16 + t, acc1[t]);
+  for (int j = 0; j < 4; ++j) {
+    atomicAdd(d4 + j, make_float4(acc0[4 * j], acc0[4 * j + 1], acc0[4 * j + 2], acc0[4 * j + 3]));
+    atomicAdd(d4 + 4 + j, make_float4(acc1[4 * j], acc1[4 * j + 1], acc1[4 * j + 2], acc1[4 * j + 3]));
   }
 }
 
@@ -152,20 +194,21 @@ extern "C" int b2c_head_fprop(const void* a, const float* w, float* out, int N, 
   cudaError_t e = cudaMemsetAsync(out, 0, sizeof(float) * (size_t)N * (h - 1) * (h - 1), st);
   if (e != cudaSuccess) { b2c_set_error("head_fprop memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
   const long long npix = (long long)N * h * h;
-  long long blocks = (npix + 7) / 8;
+  long long blocks = (npix + 8 * HP - 1) / (8 * HP);
   if (blocks > 148 * 4) blocks = 148 * 4;
   head_fprop_kernel<<<(unsigned)blocks, 256, smem, st>>>((const __nv_bfloat16*)a, w, out, N, h, C);
   return b2c_check_launch("head_fprop");
 }
 
 extern "C" int b2c_head_dgrad(const float* gy, const float* w, void* ga, int N, int h, int C, void* stream) {
-  B2C_REQUIRE(C % 8 == 0 && (size_t)16 * C * sizeof(float) <= 64 * 1024, "head_dgrad: C=%d", C);
+  B2C_REQUIRE(C % 128 == 0 && (size_t)16 * C * sizeof(float) <= 64 * 1024, "head_dgrad: C=%d must be a multiple of 128, <= 1024", C);
+  B2C_REQUIRE(h % DP == 0, "head_dgrad: h=%d must be even", h);
   static bool attr_done = false;
   if (!attr_done) {
     cudaFuncSetAttribute(head_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     attr_done = true;
   }
-  const long long total = (long long)N * h * h * (C / 8);
+  const long long total = (long long)N * h * (h / DP) * (C / 8);
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 4) blocks = 148 * 4;
   head_dgrad_kernel<<<(unsigned)blocks, 256, (size_t)16 * C * sizeof(float), (cudaStream_t)stream>>>(
