@@ -11,7 +11,6 @@
 // Warp roles as in tapgemm.cu: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2-5 = epilogue.
 // Activation boxes and weight slices travel through two separate mbarrier rings (a box is used by a variable number of
 // slices), produced and consumed in the same order, so both rings stay full: 192 KB in flight per SM.
-#include <cstdlib>
 #include "common.cuh"
 #include "tmap.h"
 
@@ -29,7 +28,6 @@ struct ConvT64Params {
   const __nv_bfloat16* act;  // nullable: dense (N,2H,2W,64) activation a = LeakyReLU(z); y *= (a > 0 ? 1 : slope), i.e. the
   float slope;               // backward of the LeakyReLU that produced this conv's input, fused into its data gradient
   int st256;                 // y and ldy allow 32-byte stores
-  int nmerge;                // centre-first shift order with merged N = 256 / 128 MMAs (B2C_CONVT_NMERGE=1 enables)
 };
 
 namespace {
@@ -40,14 +38,6 @@ constexpr int CT_SLICE_BYTES = 64 * 128;
 constexpr int CT_RED_BYTES = 4 * 64 * 8;   // statistics scratch of the 4 epilogue warps
 constexpr int CT_SMEM = CT_NA * CT_A_BYTES + CT_NB * CT_SLICE_BYTES + CT_RED_BYTES + 512 + 1024;
 }  // namespace
-
-// Shift visiting order.  Raster (merge = 0): s = 0..8.  Merged: centre, the two vertical neighbours, then the rest - the
-// centre box feeds all four parities and a vertical neighbour feeds parities (0,1) or (2,3), whose accumulators are adjacent
-// TMEM columns, so their 4 / 2 weight slices (consecutive ring slots; a tile consumes 16*kchunks slots and these groups start
-// at multiples of 4 / 2, so with CT_NB = 12 they never wrap) are multiplied by ONE N = 256 / N = 128 MMA per k-step instead
-// of 4 / 2 N = 64 MMAs that each re-read the activation box from shared memory.  Centre first makes the accumulate flag
-// uniform over a merged group.
-__device__ __forceinline__ int ct_shift(int i, int merge) { return merge ? (int)((0x862053714ull >> (4 * i)) & 15ull) : i; }
 
 // Weight slices that read shift d in {-1,0,+1} along one axis: (parity bit, tap bit) pairs with parity + tap - 1 == d.
 __device__ __forceinline__ int axis_pairs(int d, int (&par)[2], int (&tap)[2]) {
@@ -111,8 +101,7 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, tn = tile / (p.tiles_x * p.tiles_y);
         const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
-        for (int si = 0; si < 9; ++si) {
-          const int s = ct_shift(si, p.nmerge);
+        for (int s = 0; s < 9; ++s) {
           const int dy = s / 3 - 1, dx = s % 3 - 1;
           int pyv[2], av[2], pxv[2], bv[2];
           const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
@@ -135,55 +124,43 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      constexpr uint32_t idesc64 = umma_idesc_bf16(128, 64, 0, 0), idesc128 = umma_idesc_bf16(128, 128, 0, 0),
-                         idesc256 = umma_idesc_bf16(128, 256, 0, 0);
+      // This ONE thread paces the tensor pipe: an N = 64 MMA is 32 cycles of tensor work, so a slice (4 MMAs) must be
+      // issued in < 128 cycles.  The 9 shifts are unrolled with compile-time parities / accumulate flags (no local
+      // arrays, no divisions) and the descriptors are a constant high word + (base >> 4) + slot * size + 2k.
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 0);
+      constexpr uint32_t DHI = (1024u >> 4) | (1u << 14) | (2u << 29);  // SBO = 1024 B, descriptor version, SWIZZLE_128B
+      const uint32_t a_lo0 = (smem_u32(sA) >> 4) | (1u << 16), b_lo0 = (smem_u32(sB) >> 4) | (1u << 16);  // LBO = 16 B
+      auto desc = [](uint32_t lo) { return ((uint64_t)DHI << 32) | lo; };
       int sa = 0, pa = 0, sb = 0, pb = 0, lt = 0;
+      const int kchunks = p.kchunks;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
         const int buf = lt & 1;
         const uint32_t acc = tmem_base + buf * 256;
         mbar_wait(&tmem_empty[buf], ((lt >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator set
         tc_fence_after();
-        uint32_t touched = 0;  // parities whose accumulator already holds a partial sum
-        for (int si = 0; si < 9; ++si) {
-          const int s = ct_shift(si, p.nmerge);
-          const int dy = s / 3 - 1, dx = s % 3 - 1;
-          int pyv[2], av[2], pxv[2], bv[2];
-          const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
-          for (int cc = 0; cc < p.kchunks; ++cc) {
-            mbar_wait(&fullA[sa], pa);
-            const uint32_t a0 = smem_u32(sA + sa * CT_A_BYTES);
-            const int g = ny * nx;
-            if (dx == 0 && p.nmerge && sb + g <= CT_NB) {  // merged: parities (2py, 2py+1), or all four for the centre
-              const int parity0 = pyv[0] * 2;
-              for (int i = 0; i < g; ++i) mbar_wait(&fullB[sb + i], pb);
-              tc_fence_after();
-              const uint32_t bs = smem_u32(sB + sb * CT_SLICE_BYTES);
-              const uint32_t had = (touched >> parity0) & 1u;
-              const uint32_t idesc = g == 4 ? idesc256 : idesc128;
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
-                umma_bf16(acc + parity0 * 64, umma_desc_sw128(a0 + k * 32, 16, 1024), umma_desc_sw128(bs + k * 32, 16, 1024),
-                          idesc, (uint32_t)(had | (k != 0)));
-              touched |= (g == 4 ? 0xFu : 0x3u) << parity0;
-              for (int i = 0; i < g; ++i) umma_commit(&emptyB[sb + i]);
-              sb += g;
-              if (sb == CT_NB) { sb = 0; pb ^= 1; }
-            } else {
-              for (int i = 0; i < g; ++i) {
-                const int parity = pyv[i / nx] * 2 + pxv[i % nx];
+        for (int s = 0; s < 9; ++s) {
+          const int dy = s / 3 - 1, dx = s % 3 - 1;
+          for (int cc = 0; cc < kchunks; ++cc) {
+            mbar_wait(&fullA[sa], pa);
+            const uint32_t alo = a_lo0 + sa * (CT_A_BYTES >> 4);
+#pragma unroll
+            for (int py = (dy > 0 ? 1 : 0); py <= (dy < 0 ? 0 : 1); ++py)
+#pragma unroll
+              for (int px = (dx > 0 ? 1 : 0); px <= (dx < 0 ? 0 : 1); ++px) {
+                const int parity = py * 2 + px;
+                // raster order: parity 0 is first written by shift 0, parity 1 by shift 1, parity 2 by 3, parity 3 by 4
+                const bool later = s != (parity == 0 ? 0 : parity == 1 ? 1 : parity == 2 ? 3 : 4);
                 mbar_wait(&fullB[sb], pb);
                 tc_fence_after();
-                const uint32_t bs = smem_u32(sB + sb * CT_SLICE_BYTES);
-                const uint32_t had = (touched >> parity) & 1u;
+                const uint32_t blo = b_lo0 + sb * (CT_SLICE_BYTES >> 4);
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
-                  umma_bf16(acc + parity * 64, umma_desc_sw128(a0 + k * 32, 16, 1024),
-                            umma_desc_sw128(bs + k * 32, 16, 1024), idesc64, (uint32_t)(had | (k != 0)));
-                touched |= 1u << parity;
+                  umma_bf16(acc + parity * 64, desc(alo + 2 * k), desc(blo + 2 * k), idesc,
+                            (later || k != 0) ? 1u : (uint32_t)(cc != 0));
                 umma_commit(&emptyB[sb]);
                 if (++sb == CT_NB) { sb = 0; pb ^= 1; }
               }
-            }
             umma_commit(&emptyA[sa]);
             if (++sa == CT_NA) { sa = 0; pa ^= 1; }
           }
@@ -314,8 +291,6 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, 
   p.f32out = g_f32_output;
   p.act = (const __nv_bfloat16*)act; p.slope = slope;
   p.st256 = (((uintptr_t)y & 31) == 0 && ldy % 16 == 0) ? 1 : 0;
-  static const int nmerge = (getenv("B2C_CONVT_NMERGE") && getenv("B2C_CONVT_NMERGE")[0] == '1') ? 1 : 0;
-  p.nmerge = nmerge;
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.kchunks = Cin / 64; p.y = (__nv_bfloat16*)y; p.ldy = ldy;
   p.BW = W < 128 ? W : 128;
   int rem = 128 / p.BW;

@@ -9,9 +9,13 @@ using namespace b2c;
 // 16-way bank conflict); readers use hw_off(t, c) for an aligned group of 4 or 8 channels.
 __device__ __forceinline__ int hw_off(int t, int c, int C) { return t * C + ((((c >> 3) ^ t) << 3) | (c & 7)); }
 __device__ __forceinline__ void head_stage_w(const float* __restrict__ w, float* w_s, int C) {
-  for (int i = threadIdx.x; i < 16 * C; i += blockDim.x) {
-    const int c = i / 16, t = i % 16;
-    w_s[hw_off(t, c, C)] = w[i];
+  for (int i = threadIdx.x; i < 4 * C; i += blockDim.x) {  // one float4 = 4 consecutive taps of a channel
+    const int c = i / 4, t0 = (i % 4) * 4;
+    const float4 v = __ldg(reinterpret_cast<const float4*>(w) + i);
+    w_s[hw_off(t0, c, C)] = v.x;
+    w_s[hw_off(t0 + 1, c, C)] = v.y;
+    w_s[hw_off(t0 + 2, c, C)] = v.z;
+    w_s[hw_off(t0 + 3, c, C)] = v.w;
   }
   __syncthreads();
 }
@@ -195,7 +199,7 @@ extern "C" int b2c_head_fprop(const void* a, const float* w, float* out, int N, 
   if (e != cudaSuccess) { b2c_set_error("head_fprop memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
   const long long npix = (long long)N * h * h;
   long long blocks = (npix + 8 * HP - 1) / (8 * HP);
-  if (blocks > 148 * 4) blocks = 148 * 4;
+  if (blocks > 148 * 2) blocks = 148 * 2;  // the 32 KB weight staging is paid per block
   head_fprop_kernel<<<(unsigned)blocks, 256, smem, st>>>((const __nv_bfloat16*)a, w, out, N, h, C);
   return b2c_check_launch("head_fprop");
 }
@@ -210,7 +214,7 @@ extern "C" int b2c_head_dgrad(const float* gy, const float* w, void* ga, int N, 
   }
   const long long total = (long long)N * h * (h / DP) * (C / 8);
   long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 4) blocks = 148 * 4;
+  if (blocks > 148 * 3) blocks = 148 * 3;  // the 32 KB weight staging is paid per block
   head_dgrad_kernel<<<(unsigned)blocks, 256, (size_t)16 * C * sizeof(float), (cudaStream_t)stream>>>(
       gy, w, (__nv_bfloat16*)ga, N, h, C);
   return b2c_check_launch("head_dgrad");

@@ -3,6 +3,7 @@
 // compute_gradient_penalty, cgan/losses.py:213-220, pushes through D).  Formulas: SURVEY.md App. C.
 // Layout NHWC bf16 (pixel stride ld), statistics fp32.  Every pass is either a per-(n,c) plane reduction
 // (128-bit loads, shared-memory + global fp32 atomics) or an elementwise apply (128-bit loads/stores).
+#include <cstdlib>
 #include "common.cuh"
 
 using namespace b2c;
@@ -307,6 +308,95 @@ __global__ void __launch_bounds__(256, MODE == 3 ? 2 : 3) plane_apply_kernel(Nor
   });
 }
 
+// Single-pass InstanceNorm backward for SMALL planes (HW <= 1024).  The two-kernel path reads g and z twice and, on planes
+// this small, spends most of its time in launch ramp and reduction tails.  Here a block owns (image n, a group of
+// cvb = 2048/HW channel vectors) and every thread exactly FB_PIX pixels of one channel vector: all of the block's
+// operands (<= 80 KB) are requested by cp.async up front - the whole plane slice is in flight at once - the per-channel
+// sums are reduced by shuffles + one shared-memory exchange, and the second pass reads the operands back from shared
+// memory.  g, z and the mask cross HBM once; one launch instead of two + a memset.
+constexpr int FB_PIX = 8;
+__global__ void __launch_bounds__(256, 2) plane_fused_bwd_kernel(NormArgs a, int cvb) {
+  extern __shared__ __align__(16) uint8_t smem_dyn[];
+  uint4* sz = reinterpret_cast<uint4*>(smem_dyn);            // [FB_PIX][256]
+  uint4* sg = sz + FB_PIX * 256;
+  uint2* smk = reinterpret_cast<uint2*>(sg + FB_PIX * 256);  // [FB_PIX][256]
+  float* red = reinterpret_cast<float*>(smk + FB_PIX * 256);  // [2][8 warps][cvb * 8]
+  const int n = blockIdx.y, rows = 256 / cvb, cgf = cvb * 8;
+  const int cv = threadIdx.x % cvb, prow = threadIdx.x / cvb, c0 = (blockIdx.x * cvb + cv) * 8;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long base = (long long)n * a.HW + prow;
+#pragma unroll
+  for (int j = 0; j < FB_PIX; ++j) {
+    const long long pix = base + (long long)j * rows;
+    const int slot = j * 256 + threadIdx.x;
+    cp_async16(sz + slot, a.z + pix * a.ldz + c0);
+    if (a.g) cp_async16(sg + slot, a.g + pix * a.ldg + c0);
+    if (a.mask) cp_async8(smk + slot, a.mask + pix * a.C + c0);
+  }
+  cp_async_commit();
+  float mean[8], rstd[8], gv[8], acc[2][8];
+  load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { gv[i] = a.g ? 0.f : __ldg(a.gvec + (long long)n * a.C + c0 + i); acc[0][i] = acc[1][i] = 0.f; }
+  const float kscale = a.mask ? 2.f : 1.f;
+  cp_async_wait<0>();
+  auto fetch = [&](int j, Raw& r) {
+    const int slot = j * 256 + threadIdx.x;
+    r.z = sz[slot];
+    r.g = a.g ? sg[slot] : make_uint4(0, 0, 0, 0);
+    r.h = make_uint4(0, 0, 0, 0);
+    r.m = a.mask ? smk[slot] : make_uint2(0x01010101u, 0x01010101u);
+  };
+#pragma unroll
+  for (int j = 0; j < FB_PIX; ++j) {
+    Raw r;
+    fetch(j, r);
+    Elem e;
+    elem_make<M_BWD>(a, r, mean, rstd, gv, kscale, e);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { acc[0][i] += e.gn[i]; acc[1][i] += e.gn[i] * e.xh[i]; }
+  }
+  // lanes with equal (lane % cvb) hold the same channel vector: butterfly over the other lane bits, then across warps
+#pragma unroll
+  for (int s = 0; s < 2; ++s)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float v = acc[s][i];
+      for (int o = 16; o >= cvb; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      acc[s][i] = v;
+    }
+  if (lane < cvb) {
+#pragma unroll
+    for (int s = 0; s < 2; ++s)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) red[(s * 8 + warp) * cgf + cv * 8 + i] = acc[s][i];
+  }
+  __syncthreads();
+  const float inv = 1.f / (float)a.HW;
+  float sm[2][8];
+#pragma unroll
+  for (int s = 0; s < 2; ++s)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += red[(s * 8 + w) * cgf + cv * 8 + i];
+      if (prow == 0) a.sums[((long long)n * a.C + c0 + i) * 2 + s] = t;
+      sm[s][i] = t * inv;
+    }
+#pragma unroll
+  for (int j = 0; j < FB_PIX; ++j) {
+    Raw r;
+    fetch(j, r);
+    Elem e;
+    elem_make<M_BWD>(a, r, mean, rstd, gv, kscale, e);
+    float o[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = (e.gn[i] - sm[0][i] - e.xh[i] * sm[1][i]) * rstd[i];
+    store8(a.o0 + (base + (long long)j * rows) * a.ldo0 + c0, o);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 static int norm_check(const NormArgs& a, const char* who) {
   B2C_REQUIRE(a.C >= 64 && a.C <= 2048 && (a.C & (a.C - 1)) == 0, "%s: C=%d must be a power of two in [64,2048]", who, a.C);
@@ -387,6 +477,21 @@ extern "C" int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, c
   a.o0 = (__nv_bfloat16*)gz; a.ldo0 = ldgz;
   if (int rc = norm_check(a, "in_act_bwd")) return rc;
   B2C_REQUIRE((g != nullptr) != (gvec != nullptr), "in_act_bwd: exactly one of g / gvec");
+  // small planes: one fused launch with the block's slice of the plane resident in shared memory
+  static const bool fused_ok = !(getenv("B2C_NORM_FUSED") && getenv("B2C_NORM_FUSED")[0] == '0');
+  if (fused_ok && HW >= 64 && HW <= 1024 && (HW & (HW - 1)) == 0) {
+    const int cvb = 2048 / HW;  // channel vectors per block so that every thread owns FB_PIX pixels
+    if (cvb <= C / 8 && (C / 8) % cvb == 0) {
+      const int smem = FB_PIX * 256 * (16 + 16 + 8) + 2 * 8 * cvb * 8 * (int)sizeof(float);
+      static bool attr_done = false;
+      if (!attr_done) {
+        cudaFuncSetAttribute(plane_fused_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_PIX * 256 * 40 + 16 * 1024);
+        attr_done = true;
+      }
+      plane_fused_bwd_kernel<<<dim3(C / 8 / cvb, N), 256, smem, (cudaStream_t)stream>>>(a, cvb);
+      return b2c_check_launch("plane_fused_bwd");
+    }
+  }
   if (int rc = launch_reduce<M_BWD>(a, (cudaStream_t)stream)) return rc;
   return launch_apply<M_BWD>(a, (cudaStream_t)stream);
 }
