@@ -136,6 +136,17 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr, uint32_t lbo
   d |= (uint64_t)2 << 61;  // SWIZZLE_128B
   return d;
 }
+// The same descriptor split into a constant high word and a low word that is linear in the shared-memory address
+// (address >> 4 in bits 0-13, LBO >> 4 in bits 16-29): an MMA issue loop adds slot * (bytes >> 4) + k * (step >> 4) to the
+// low word instead of rebuilding the descriptor (the single issuing thread paces the tensor pipe).  Valid while the
+// address stays below 256 KB, which shared memory always does.
+__device__ __forceinline__ uint32_t umma_desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+  return ((saddr & 0x3FFFF) >> 4) | (((lbo_bytes >> 4) & 0x3FFF) << 16);
+}
+__host__ __device__ constexpr uint32_t umma_desc_hi_sw128(uint32_t sbo_bytes) {
+  return ((sbo_bytes >> 4) & 0x3FFF) | (1u << 14) | (2u << 29);
+}
+__device__ __forceinline__ uint64_t umma_desc_join(uint32_t hi, uint32_t lo) { return ((uint64_t)hi << 32) | lo; }
 // Instruction descriptor for kind::f16 with bf16 A/B, fp32 D.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn_major, int b_mn_major) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |

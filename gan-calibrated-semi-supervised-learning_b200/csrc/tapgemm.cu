@@ -115,17 +115,19 @@ __global__ void __launch_bounds__(64 + 128 * MT) tapgemm_kernel(const __grid_con
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+      constexpr uint32_t DHI = umma_desc_hi_sw128(1024);
+      const uint32_t a_lo0 = umma_desc_lo(smem_u32(sA), 16), b_lo0 = umma_desc_lo(smem_u32(sB), 16);
       int stage = 0, phase = 0;
       for (int it = 0; it < niters; ++it) {
         mbar_wait(&full[stage], phase);
         tc_fence_after();
-        const uint32_t a0 = smem_u32(sA + stage * Cfg::A_BYTES), b0 = smem_u32(sB + stage * Cfg::B_BYTES);
+        const uint32_t alo = a_lo0 + stage * (Cfg::A_BYTES >> 4), blo = b_lo0 + stage * (Cfg::B_BYTES >> 4);
 #pragma unroll
         for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            umma_bf16(tmem_base + mt * BN, umma_desc_sw128(a0 + mt * 16384 + k * 32, 16, 1024),
-                      umma_desc_sw128(b0 + k * 32, 16, 1024), idesc, (uint32_t)((it | k) != 0));
+            umma_bf16(tmem_base + mt * BN, umma_desc_join(DHI, alo + mt * (16384 >> 4) + 2 * k), umma_desc_join(DHI, blo + 2 * k),
+                      idesc, k != 0 ? 1u : (uint32_t)(it != 0));
         umma_commit(&empty[stage]);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
@@ -318,6 +320,8 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+      constexpr uint32_t DHI = umma_desc_hi_sw128(1024);
+      const uint32_t a_lo0 = umma_desc_lo(smem_u32(sA), 16), b_lo0 = umma_desc_lo(smem_u32(sB), 16);
       int stage = 0, phase = 0, lt = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x, ++lt) {
         const int buf = lt & 1;
@@ -326,11 +330,11 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
         for (int it = 0; it < niters; ++it) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const uint32_t a0 = smem_u32(sA + stage * Cfg::A_BYTES), b0 = smem_u32(sB + stage * Cfg::B_BYTES);
+          const uint32_t alo = a_lo0 + stage * (Cfg::A_BYTES >> 4), blo = b_lo0 + stage * (Cfg::B_BYTES >> 4);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            umma_bf16(tmem_base + buf * BN, umma_desc_sw128(a0 + k * 32, 16, 1024), umma_desc_sw128(b0 + k * 32, 16, 1024),
-                      idesc, (uint32_t)((it | k) != 0));
+            umma_bf16(tmem_base + buf * BN, umma_desc_join(DHI, alo + 2 * k), umma_desc_join(DHI, blo + 2 * k), idesc,
+                      k != 0 ? 1u : (uint32_t)(it != 0));
           umma_commit(&empty[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
