@@ -8,9 +8,11 @@
 // it walks the 9 shifts, loads each activation box ONCE and multiplies it against the 1, 2 or 4 weight slices
 // (parity, tap) that use that shift, into four 64-column accumulators side by side in TMEM (256 columns).
 // Staged bytes per pixel tile and 64-channel slice drop from 16*(16+8) = 384 KB to 9*16 + 16*8 = 272 KB.
-// Warp roles as in tapgemm.cu: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2-5 = epilogue.
+// Warp roles: warp 0 = TMA producer of the activation ring, warp 6 = TMA producer of the weight ring, warp 1 = tcgen05.mma
+// issuer, warps 2-5 = epilogue.
 // Activation boxes and weight slices travel through two separate mbarrier rings (a box is used by a variable number of
 // slices), produced and consumed in the same order, so both rings stay full: 192 KB in flight per SM.
+#include <cstdlib>
 #include "common.cuh"
 #include "tmap.h"
 
@@ -39,6 +41,16 @@ constexpr int CT_RED_BYTES = 4 * 64 * 8;   // statistics scratch of the 4 epilog
 constexpr int CT_SMEM = CT_NA * CT_A_BYTES + CT_NB * CT_SLICE_BYTES + CT_RED_BYTES + 512 + 1024;
 }  // namespace
 
+// Shift visiting order.  Raster: s = 0..8.  MERGE: centre, the two vertical neighbours, then the rest - the centre box
+// feeds all four parities and a vertical neighbour feeds parities (0,1) or (2,3), whose accumulators are adjacent TMEM
+// columns, so their 4 / 2 weight slices (consecutive ring slots: a tile consumes 16*kchunks slots and these groups start at
+// multiples of 4 / 2, so with CT_NB = 12 they never wrap) are multiplied by ONE N = 256 / N = 128 MMA per k-step.  Centre
+// first makes the accumulate flag uniform over a merged group.
+template <bool MERGE>
+__device__ __forceinline__ constexpr int ct_shift(int i) {
+  return MERGE ? (i == 0 ? 4 : i == 1 ? 1 : i == 2 ? 7 : i == 3 ? 3 : i == 4 ? 5 : i == 5 ? 0 : i == 6 ? 2 : i == 7 ? 6 : 8) : i;
+}
+
 // Weight slices that read shift d in {-1,0,+1} along one axis: (parity bit, tap bit) pairs with parity + tap - 1 == d.
 __device__ __forceinline__ int axis_pairs(int d, int (&par)[2], int (&tap)[2]) {
   if (d < 0) { par[0] = 0; tap[0] = 0; return 1; }
@@ -53,8 +65,8 @@ __device__ __forceinline__ int axis_pairs(int d, int (&par)[2], int (&tap)[2]) {
 // ACT = the fused LeakyReLU-backward variant (never combined with statistics): the 4 x 128-byte activation rows a thread
 // needs for its tile are fetched with 256-bit loads BEFORE it waits for the accumulator, so their latency hides behind the
 // MMAs instead of being paid once per 32-channel chunk.
-template <bool ACT>
-__global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__ CUtensorMap tmA,
+template <bool ACT, bool MERGE>
+__global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__ CUtensorMap tmA,
                                                          const __grid_constant__ CUtensorMap tmB, ConvT64Params p,
                                                          int ntiles) {
   extern __shared__ uint8_t smem_raw[];
@@ -97,25 +109,47 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
 
   if (warp == 0) {
     if (elect_one()) {
-      int sa = 0, pa = 0, sb = 0, pb = 0;
+      // Activation-box producer.  25 TMA loads per 64-channel slice of Cin and pixel tile would leave ONE thread ~80
+      // tensor-pipe cycles per load; the two rings are independent, so this thread feeds the activation ring (9 boxes)
+      // and warp 6 the weight ring (16 slices).  Shifts are unrolled with compile-time offsets, like the MMA loop.
+      int sa = 0, pa = 0;
+      const int kchunks = p.kchunks;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, tn = tile / (p.tiles_x * p.tiles_y);
         const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
-        for (int s = 0; s < 9; ++s) {
+#pragma unroll
+        for (int si = 0; si < 9; ++si) {
+          const int s = ct_shift<MERGE>(si);
           const int dy = s / 3 - 1, dx = s % 3 - 1;
-          int pyv[2], av[2], pxv[2], bv[2];
-          const int ny = axis_pairs(dy, pyv, av), nx = axis_pairs(dx, pxv, bv);
-          for (int cc = 0; cc < p.kchunks; ++cc) {
+          for (int cc = 0; cc < kchunks; ++cc) {
             mbar_wait(&emptyA[sa], pa ^ 1);
             mbar_expect_tx(&fullA[sa], CT_A_BYTES);
             tma_load_4d(sA + sa * CT_A_BYTES, &tmA, &fullA[sa], cc * 64, x0 + dx, y0 + dy, n0);
             if (++sa == CT_NA) { sa = 0; pa ^= 1; }
-            for (int iy = 0; iy < ny; ++iy)
-              for (int ix = 0; ix < nx; ++ix) {
-                const int parity = pyv[iy] * 2 + pxv[ix], tap = av[iy] * 2 + bv[ix];
+          }
+        }
+      }
+    }
+  } else if (warp == 6) {
+    if (elect_one()) {
+      // Weight-slice producer: same walk, the 1 / 2 / 4 (parity, tap) slices of every (shift, channel slice).
+      int sb = 0, pb = 0;
+      const int kchunks = p.kchunks, Cin = p.Cin;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+#pragma unroll
+        for (int si = 0; si < 9; ++si) {
+          const int s = ct_shift<MERGE>(si);
+          const int dy = s / 3 - 1, dx = s % 3 - 1;
+          for (int cc = 0; cc < kchunks; ++cc) {
+#pragma unroll
+            for (int py = (dy > 0 ? 1 : 0); py <= (dy < 0 ? 0 : 1); ++py)
+#pragma unroll
+              for (int px = (dx > 0 ? 1 : 0); px <= (dx < 0 ? 0 : 1); ++px) {
+                // parity (py,px) reads shift (dy,dx) through tap (a,b) with py + a - 1 == dy, px + b - 1 == dx
+                const int parity = py * 2 + px, tap = (dy - py + 1) * 2 + (dx - px + 1);
                 mbar_wait(&emptyB[sb], pb ^ 1);
                 mbar_expect_tx(&fullB[sb], CT_SLICE_BYTES);
-                tma_load_2d(sB + sb * CT_SLICE_BYTES, &tmB, &fullB[sb], tap * p.Cin + cc * 64, parity * 64);
+                tma_load_2d(sB + sb * CT_SLICE_BYTES, &tmB, &fullB[sb], tap * Cin + cc * 64, parity * 64);
                 if (++sb == CT_NB) { sb = 0; pb ^= 1; }
               }
           }
@@ -139,28 +173,48 @@ __global__ void __launch_bounds__(192, 1) convt64_kernel(const __grid_constant__
         mbar_wait(&tmem_empty[buf], ((lt >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator set
         tc_fence_after();
 #pragma unroll
-        for (int s = 0; s < 9; ++s) {
+        for (int si = 0; si < 9; ++si) {
+          const int s = ct_shift<MERGE>(si);
           const int dy = s / 3 - 1, dx = s % 3 - 1;
           for (int cc = 0; cc < kchunks; ++cc) {
             mbar_wait(&fullA[sa], pa);
             const uint32_t alo = a_lo0 + sa * (CT_A_BYTES >> 4);
+            if (MERGE && dx == 0) {
+              // one N = 256 (centre) / N = 128 (vertical neighbour) MMA per k-step over g adjacent slices and parities
+              constexpr uint32_t idesc128 = umma_idesc_bf16(128, 128, 0, 0), idesc256 = umma_idesc_bf16(128, 256, 0, 0);
+              const int g = dy == 0 ? 4 : 2, parity0 = dy > 0 ? 2 : 0;
 #pragma unroll
-            for (int py = (dy > 0 ? 1 : 0); py <= (dy < 0 ? 0 : 1); ++py)
+              for (int i = 0; i < g; ++i) mbar_wait(&fullB[sb + i], pb);
+              tc_fence_after();
+              const uint32_t blo = b_lo0 + sb * (CT_SLICE_BYTES >> 4);
 #pragma unroll
-              for (int px = (dx > 0 ? 1 : 0); px <= (dx < 0 ? 0 : 1); ++px) {
-                const int parity = py * 2 + px;
-                // raster order: parity 0 is first written by shift 0, parity 1 by shift 1, parity 2 by 3, parity 3 by 4
-                const bool later = s != (parity == 0 ? 0 : parity == 1 ? 1 : parity == 2 ? 3 : 4);
-                mbar_wait(&fullB[sb], pb);
-                tc_fence_after();
-                const uint32_t blo = b_lo0 + sb * (CT_SLICE_BYTES >> 4);
+              for (int k = 0; k < 4; ++k)
+                umma_bf16(acc + parity0 * 64, desc(alo + 2 * k), desc(blo + 2 * k), g == 4 ? idesc256 : idesc128,
+                          (si != 0 || k != 0) ? 1u : (uint32_t)(cc != 0));
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                  umma_bf16(acc + parity * 64, desc(alo + 2 * k), desc(blo + 2 * k), idesc,
-                            (later || k != 0) ? 1u : (uint32_t)(cc != 0));
-                umma_commit(&emptyB[sb]);
-                if (++sb == CT_NB) { sb = 0; pb ^= 1; }
-              }
+              for (int i = 0; i < g; ++i) umma_commit(&emptyB[sb + i]);
+              sb += g;
+              if (sb == CT_NB) { sb = 0; pb ^= 1; }
+            } else {
+#pragma unroll
+              for (int py = (dy > 0 ? 1 : 0); py <= (dy < 0 ? 0 : 1); ++py)
+#pragma unroll
+                for (int px = (dx > 0 ? 1 : 0); px <= (dx < 0 ? 0 : 1); ++px) {
+                  const int parity = py * 2 + px;
+                  // raster order: parity 0 is first written by shift 0, parity 1 by shift 1, parity 2 by 3, parity 3 by 4;
+                  // MERGE: the centre (first) writes all four
+                  const bool later = MERGE ? true : s != (parity == 0 ? 0 : parity == 1 ? 1 : parity == 2 ? 3 : 4);
+                  mbar_wait(&fullB[sb], pb);
+                  tc_fence_after();
+                  const uint32_t blo = b_lo0 + sb * (CT_SLICE_BYTES >> 4);
+#pragma unroll
+                  for (int k = 0; k < 4; ++k)
+                    umma_bf16(acc + parity * 64, desc(alo + 2 * k), desc(blo + 2 * k), idesc,
+                              (later || k != 0) ? 1u : (uint32_t)(cc != 0));
+                  umma_commit(&emptyB[sb]);
+                  if (++sb == CT_NB) { sb = 0; pb ^= 1; }
+                }
+            }
             umma_commit(&emptyA[sa]);
             if (++sa == CT_NA) { sa = 0; pa ^= 1; }
           }
@@ -315,8 +369,10 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, 
   }
   static bool attr_done = false;
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(convt64_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(convt64_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
     if (e != cudaSuccess) {
       b2c_set_error("cudaFuncSetAttribute(convt64): %s", cudaGetErrorString(e));
       return B2C_ERR_CUDA;
@@ -338,8 +394,16 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, 
     cudaGetDevice(&dev);
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
   }
-  if (act) convt64_kernel<true><<<ntiles < sms ? ntiles : sms, 192, CT_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p, ntiles);
-  else convt64_kernel<false><<<ntiles < sms ? ntiles : sms, 192, CT_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p, ntiles);
+  static const bool merge = getenv("B2C_CONVT_NMERGE") && getenv("B2C_CONVT_NMERGE")[0] == '1';
+  const int ctas = ntiles < sms ? ntiles : sms;
+  const cudaStream_t st = (cudaStream_t)stream;
+  if (merge) {
+    if (act) convt64_kernel<true, true><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    else convt64_kernel<false, true><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+  } else {
+    if (act) convt64_kernel<true, false><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    else convt64_kernel<false, false><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+  }
   int rc = b2c_check_launch("convt64_kernel");
   if (rc == 0 && stats && !fuse_stats) rc = b2c_in_stats(y, ldy, stats, N, 4 * H * W, 64, stream);
   return rc;
