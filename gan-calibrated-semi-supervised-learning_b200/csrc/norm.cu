@@ -176,14 +176,19 @@ __device__ __forceinline__ void elem_make(const NormArgs& a, const Raw& r, const
 #pragma unroll
   for (int i = 0; i < 8; ++i) e.xh[i] = (z[i] - mean[i]) * rstd[i];
   if (MODE == M_BWD || MODE == M_BWD2) {
-    float k[8], g[8];
-    cvt_mask8(r.m, k);
+    float g[8];
     if (a.g) cvt8(r.g, g);
+    if (a.mask) {  // dropout sites only (3 layers of G): the mask decode is ~6 instructions per element
+      float k[8];
+      cvt_mask8(r.m, k);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      e.dact[i] = (e.xh[i] > 0.f ? 1.f : a.slope) * k[i] * kscale;
-      e.gn[i] = (a.g ? g[i] : gv[i]) * e.dact[i];
+      for (int i = 0; i < 8; ++i) e.dact[i] = (e.xh[i] > 0.f ? 1.f : a.slope) * k[i] * kscale;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) e.dact[i] = e.xh[i] > 0.f ? 1.f : a.slope;
     }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) e.gn[i] = (a.g ? g[i] : gv[i]) * e.dact[i];
   }
   if (MODE == M_BWD2) cvt8(r.h, e.hh);
 }
@@ -273,13 +278,18 @@ __global__ void __launch_bounds__(256, MODE == 3 ? 2 : 3) plane_apply_kernel(Nor
   const int p_begin = (int)((long long)a.HW * blockIdx.x / gridDim.x), p_end = (int)((long long)a.HW * (blockIdx.x + 1) / gridDim.x);
   ring_walk<MODE>(a, smem_dyn, n, c0, p_begin + prow, rows, p_end, [&](long long pix, const Raw& r) {
     if (MODE == M_FWD) {
-      float z[8], k[8], o[8];
+      float z[8], o[8];
       cvt8(r.z, z);
-      cvt_mask8(r.m, k);
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         const float xh = (z[e] - mean[e]) * rstd[e];
-        o[e] = (xh > 0.f ? xh : xh * a.slope) * k[e] * kscale;
+        o[e] = xh > 0.f ? xh : xh * a.slope;
+      }
+      if (a.mask) {
+        float k[8];
+        cvt_mask8(r.m, k);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] *= k[e] * kscale;
       }
       store8(a.o0 + pix * a.ldo0 + c0, o);
       if (a.o1) store8(a.o1 + pix * a.ldo1 + c0, o);

@@ -86,6 +86,11 @@ def test_lrelu_bwd_copy_dropout(L):
     dst = torch.zeros(4, 8, 8, 128, dtype=torch.bfloat16, device="cuda")
     L.call("b2c_copy_strided", a, 64, dst[..., 64:], 128, 4 * 64, 64)
     assert torch.equal(dst[..., 64:], a) and float(dst[..., :64].abs().sum()) == 0
+    # gradient sum of a skip tensor: dense tensor + channel slice of a concat gradient
+    cat = torch.randn(4, 8, 8, 128, generator=g).to(torch.bfloat16).cuda()
+    tot = torch.empty_like(a)
+    L.call("b2c_add_strided", a, 64, cat[..., 64:], 128, tot, 64, 4 * 64, 64)
+    assert torch.equal(tot, (a.float() + cat[..., 64:].float()).to(torch.bfloat16))
     m = torch.empty(1 << 20, dtype=torch.uint8, device="cuda")
     L.call("b2c_dropout_mask", m, m.numel(), 7, 0, None)
     assert set(m.unique().tolist()) == {0, 1} and abs(float(m.float().mean()) - 0.5) < 5e-3
