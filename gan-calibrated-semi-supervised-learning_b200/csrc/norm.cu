@@ -46,7 +46,8 @@ __device__ __forceinline__ void load_mask8(const uint8_t* m, long long idx, floa
     k[4 + e] = ((u.y >> (8 * e)) & 0xff) ? 2.f : 0.f;
   }
 }
-// mean / rstd of 8 consecutive channels from the raw sums.
+// Normalisation constants of 8 consecutive channels from the raw sums: rstd and shift = -mean * rstd, so that
+// x_hat = fma(z, rstd, shift) is one instruction per element (`mean` below holds the shift).
 __device__ __forceinline__ void load_stats8(const float* zs, int n, int C, int c0, int HW, float (&mean)[8], float (&rstd)[8]) {
   const float inv = 1.f / (float)HW;
   const float4* p = reinterpret_cast<const float4*>(zs + ((long long)n * C + c0) * 2);
@@ -54,9 +55,9 @@ __device__ __forceinline__ void load_stats8(const float* zs, int n, int C, int c
   for (int j = 0; j < 4; ++j) {
     const float4 v = __ldg(p + j);
     const float m0 = v.x * inv, m1 = v.z * inv;
-    mean[2 * j] = m0; mean[2 * j + 1] = m1;
     rstd[2 * j] = rsqrtf(fmaxf(v.y * inv - m0 * m0, 0.f) + 1e-5f);
     rstd[2 * j + 1] = rsqrtf(fmaxf(v.w * inv - m1 * m1, 0.f) + 1e-5f);
+    mean[2 * j] = -m0 * rstd[2 * j]; mean[2 * j + 1] = -m1 * rstd[2 * j + 1];
   }
 }
 
@@ -174,7 +175,7 @@ __device__ __forceinline__ void elem_make(const NormArgs& a, const Raw& r, const
   float z[8];
   cvt8(r.z, z);
 #pragma unroll
-  for (int i = 0; i < 8; ++i) e.xh[i] = (z[i] - mean[i]) * rstd[i];
+  for (int i = 0; i < 8; ++i) e.xh[i] = fmaf(z[i], rstd[i], mean[i]);  // mean = -mean * rstd (load_stats8)
   if (MODE == M_BWD || MODE == M_BWD2) {
     float g[8];
     if (a.g) cvt8(r.g, g);
@@ -282,7 +283,7 @@ __global__ void __launch_bounds__(256, MODE == 3 ? 2 : 3) plane_apply_kernel(Nor
       cvt8(r.z, z);
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
-        const float xh = (z[e] - mean[e]) * rstd[e];
+        const float xh = fmaf(z[e], rstd[e], mean[e]);  // mean = -mean * rstd (load_stats8)
         o[e] = xh > 0.f ? xh : xh * a.slope;
       }
       if (a.mask) {
