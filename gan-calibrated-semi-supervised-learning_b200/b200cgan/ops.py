@@ -85,7 +85,7 @@ class WeightCtx:
         R = self.weight.shape[0]
         K = self.weight.numel() // R
         dw = torch.empty_like(dwe)
-        ws = torch.empty(1, dtype=torch.float32, device=dwe.device)
+        ws = torch.empty(592, dtype=torch.float32, device=dwe.device)
         _lib.call("b2c_sn_bwd", dwe, self.weight.detach(), self.u, self.v, self.sig, ws, dw, R, K, 0)
         return dw
 

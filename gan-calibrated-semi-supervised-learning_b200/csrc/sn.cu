@@ -143,19 +143,23 @@ extern "C" int b2c_sn_power_iter(const float* W, float* u, float* v, float* sig,
   return b2c_check_launch("sn_power_iter");
 }
 
-__global__ void sn_dot_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out, long long n) {
+// <dWe, W> in two atomic-free stages: one partial per block, summed in a fixed order by every block of sn_bwd_kernel.
+__global__ void sn_dot_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ part, long long n) {
   __shared__ float sh[32];
   float acc = 0.f;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     acc += __ldg(a + i) * __ldg(b + i);
   const float r = block_sum(acc, sh);
-  if (threadIdx.x == 0) atomicAdd(out, r);
+  if (threadIdx.x == 0) part[blockIdx.x] = r;
 }
 __global__ void sn_bwd_kernel(const float* __restrict__ dWe, const float* __restrict__ u, const float* __restrict__ v,
-                              const float* __restrict__ sig, const float* __restrict__ dot, float* __restrict__ dW, int R,
-                              int K, int accumulate) {
+                              const float* __restrict__ sig, const float* __restrict__ part, int nparts,
+                              float* __restrict__ dW, int R, int K, int accumulate) {
+  float dot = 0.f;  // every warp derives the same value in the same order
+  for (int i = threadIdx.x & 31; i < nparts; i += 32) dot += __ldg(part + i);
+  dot = warp_sum(dot);
   const float inv = sig[1];
-  const float coef = dot[0] * inv;  // <dWe, We> = <dWe, W> / sigma
+  const float coef = dot * inv;  // <dWe, We> = <dWe, W> / sigma
   const long long n = (long long)R * K;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const int r = (int)(i / K), k = (int)(i % K);
@@ -163,16 +167,14 @@ __global__ void sn_bwd_kernel(const float* __restrict__ dWe, const float* __rest
     dW[i] = accumulate ? dW[i] + g : g;
   }
 }
-// u, v, sig: the values used by THAT forward instance (saved copies).  ws: 1 float scratch.
+// u, v, sig: the values used by THAT forward instance (saved copies).  ws: min(592, ceil(R*K/1024)) floats of scratch.
 extern "C" int b2c_sn_bwd(const float* dWe, const float* W, const float* u, const float* v, const float* sig, float* ws,
                           float* dW, int R, int K, int accumulate, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e = cudaMemsetAsync(ws, 0, sizeof(float), st);
-  if (e != cudaSuccess) { b2c_set_error("sn_bwd memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
   const long long n = (long long)R * K;
   int blocks = (int)((n + 1023) / 1024);
   if (blocks > 592) blocks = 592;
   sn_dot_kernel<<<blocks, 256, 0, st>>>(dWe, W, ws, n);
-  sn_bwd_kernel<<<blocks, 256, 0, st>>>(dWe, u, v, sig, ws, dW, R, K, accumulate);
+  sn_bwd_kernel<<<blocks, 256, 0, st>>>(dWe, u, v, sig, ws, blocks, dW, R, K, accumulate);
   return b2c_check_launch("sn_bwd");
 }

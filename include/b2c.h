@@ -76,6 +76,7 @@ int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsign
 
 /* ---- spectral norm (torch spectral_norm.py:92-114); ws: K + ceil(K/32) + R floats of scratch (ceil(R/32)*K + R suffices for R > 32) ---- */
 int b2c_sn_power_iter(const float* W, float* u, float* v, float* sig, float* ws, int R, int K, int train, void* stream);
+/* b2c_sn_bwd: ws = min(592, ceil(R*K/1024)) floats of scratch (block partials of <dWe, W>, summed in a fixed order) */
 int b2c_sn_bwd(const float* dWe, const float* W, const float* u, const float* v, const float* sig, float* ws, float* dW,
                int R, int K, int accumulate, void* stream);
 
