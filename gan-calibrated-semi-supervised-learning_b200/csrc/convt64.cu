@@ -11,7 +11,7 @@
 // Warp roles: warp 0 = TMA producer of the activation ring, warp 6 = TMA producer of the weight ring, warp 1 = tcgen05.mma
 // issuer, warps 2-5 = epilogue.
 // Activation boxes and weight slices travel through two separate mbarrier rings (a box is used by a variable number of
-// slices), produced and consumed in the same order, so both rings stay full: 192 KB in flight per SM.
+// slices), produced and consumed in the same order, so both rings stay full: 208 KB in flight per SM.
 #include <cstdlib>
 #include "common.cuh"
 #include "tmap.h"
@@ -33,7 +33,7 @@ struct ConvT64Params {
 };
 
 namespace {
-constexpr int CT_NA = 6;                   // activation ring: [128 pixels][64 channels] bf16 boxes
+constexpr int CT_NA = 7;                   // activation ring: [128 pixels][64 channels] bf16 boxes
 constexpr int CT_NB = 12;                  // weight ring: [64 cout][64 cin] bf16 slices (1, 2 or 4 consumed per box)
 constexpr int CT_A_BYTES = 128 * 128;
 constexpr int CT_SLICE_BYTES = 64 * 128;
