@@ -72,23 +72,49 @@ def conv_flops_per_patch(S):
     return fg, fg1, fd, fd1
 
 
-def useful_flops_per_patch(S, c=N_CRITIC):
+def useful_flops_per_patch(S, c=N_CRITIC, live_critic_g=False):
+    """SURVEY.md §8d model.  With `refined` given as an input (every BASELINE config) the critic steps' no-grad generator
+    forward has no consumer and is not executed, so its c * F_G is NOT counted; with a refine_fn it is live."""
     fg, fg1, fd, fd1 = conv_flops_per_patch(S)
-    return (c + 3) * fg - fg1 + (12 * c + 1) * fd - 3 * c * fd1
+    return ((c if live_critic_g else 0) + 3) * fg - fg1 + (12 * c + 1) * fd - 3 * c * fd1
 
 
 GEMM_KERNELS = ("b2c_conv4s2_bf16", "b2c_convt4s2_bf16", "b2c_wgrad4s2_bf16")
+BW_KERNELS = ("b2c_in_act_fwd", "b2c_in_act_bwd", "b2c_in_act_bwd2", "b2c_in_act_pool_fwd", "b2c_first_fprop",
+              "b2c_first_wgrad", "b2c_first_dgrad", "b2c_multi_adam", "b2c_lrelu_bwd", "b2c_head_fprop", "b2c_head_dgrad",
+              "b2c_head_wgrad")
 
 
-def gemm_flops(name, a):
-    """Algorithmic FLOPs of one launch from its scalar C-ABI arguments (include/b2c.h)."""
-    if name == "b2c_wgrad4s2_bf16":      # lds, ldl, accumulate, N, Hs, Ws, Cs, Cl, sm_count
-        _, _, _, N, Hs, Ws, Cs, Cl, _ = a
-        return 2.0 * N * Hs * Ws * Cs * 16 * Cl
-    N, H, W, Cin, Cout = a[-5:]           # ..., N, H, W, Cin, Cout
-    if name == "b2c_conv4s2_bf16":
-        return 2.0 * N * (H // 2) * (W // 2) * Cout * 16 * Cin
-    return 2.0 * N * H * W * Cout * 16 * Cin
+def bw_bytes(name, a):
+    """Algorithmic bytes of one launch of a bandwidth kernel (each distinct tensor once) from its C-ABI
+    argument pattern (include/b2c.h; scalars as given, pointers as True / False = given / NULL), or None."""
+    if name == "b2c_in_act_fwd":         # z, ldz, zs, mask, slope, o0, ldo0, o1, ldo1, N, HW, C
+        N, HW, C = a[-3:]
+        return N * HW * C * (2 * (2 + (1 if a[7] else 0)) + (1 if a[3] else 0))
+    if name == "b2c_in_act_pool_fwd":
+        N, HW, C = a[-3:]
+        return N * HW * C * 2
+    if name == "b2c_in_act_bwd":         # g, ldg, gvec, fwd_sums, z, ldz, zs, mask, slope, ws, gz, ldgz, N, HW, C
+        N, HW, C = a[-3:]
+        return N * HW * C * (2 * (3 if a[0] else 2) + (1 if a[7] else 0))
+    if name == "b2c_in_act_bwd2":
+        N, HW, C = a[-3:]
+        return N * HW * C * 2 * 5
+    if name == "b2c_lrelu_bwd":          # g, a, out, n, slope
+        return a[3] * 2 * 3
+    if name == "b2c_first_fprop":        # a0, a1, b0, b1, alpha, w, inv_sigma, bias, y, N, H, W, slope
+        N, H, W = a[9:12]
+        return N * 3 * H * W * 4 * (2 if a[1] else 1) * (2 if a[2] else 1) + N * (H // 2) * (W // 2) * 64 * 2
+    if name == "b2c_first_wgrad":        # a0, a1, b0, b1, alpha, gz, dw, db, scale, wdot, part, nparts, N, H, W
+        N, H, W = a[-3:]
+        return N * 3 * H * W * 4 * (2 if a[1] else 1) * (2 if a[2] else 1) + N * (H // 2) * (W // 2) * 64 * 2
+    if name == "b2c_first_dgrad":        # gz, w, inv_sigma, gx0, gx1, ws, N, H, W
+        N, H, W = a[-3:]
+        return N * 3 * H * W * 4 * (2 if a[4] else 1) + N * (H // 2) * (W // 2) * 64 * 2
+    if name in ("b2c_head_fprop", "b2c_head_dgrad", "b2c_head_wgrad"):
+        N, h, C = a[-3:]
+        return N * h * h * C * 2
+    return None
 
 
 # --------------------------------------------------------------------------------------------- clocks
@@ -275,7 +301,7 @@ def run_b200(args):
     tr.disable_cuda_graph()
     tr.step(*[resident[0][k] for k in keys])
     barrier()
-    timed = _lib.time_kernels(GEMM_KERNELS)
+    timed = _lib.time_kernels(GEMM_KERNELS + BW_KERNELS)
     g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     g0.record()
     for i in range(K):
@@ -284,6 +310,19 @@ def run_b200(args):
     barrier()
     ms_eager = g0.elapsed_time(g1)
     _lib.time_kernels(None)
+    bwfam = {}
+    adam_bytes = [28 * tr.optD.total] * N_CRITIC + [28 * tr.optG.total]  # launch order within a step: D, D, G
+    for name in BW_KERNELS:
+        recs = timed.pop(name, [])
+        if not recs:
+            continue
+        ms = sum(a.elapsed_time(b) for a, b, _ in recs)
+        if name == "b2c_multi_adam":
+            nb = sum(adam_bytes[i % len(adam_bytes)] for i in range(len(recs)))
+        else:
+            nb = sum(bw_bytes(name, sc) or 0 for _, _, sc in recs)
+        bwfam[name] = {"launches_per_step": len(recs) / K, "ms_per_step": ms / K, "gbs": nb / ms / 1e6 if ms else 0.0,
+                       "bytes_per_launch": nb / len(recs), "ms_per_launch": ms / len(recs)}
     fam = {}
     for name, recs in timed.items():
         ms = sum(a.elapsed_time(b) for a, b, _ in recs)
@@ -304,15 +343,31 @@ def run_b200(args):
     total_ms = sum(f["ms_per_step"] for f in fam.values())
     total_tf = sum(f["tflops"] * f["ms_per_step"] for f in fam.values()) / total_ms if total_ms else 0.0
     traffic = None  # ncu dram__bytes_read+write per launch of the dominant family (one --set full capture of a step)
-    tf = ROOT / "profiles" / "r01_traffic.json"
-    if tf.exists():
-        traffic = json.loads(tf.read_text()).get(dom, {}).get("dram_bytes_per_launch")
+    for tfn in ("r02_traffic.json", "r01_traffic.json"):
+        tf = ROOT / "profiles" / tfn
+        if tf.exists():
+            traffic = json.loads(tf.read_text()).get(dom, {}).get("dram_bytes_per_launch")
+            break
     roofline = {"bound": "tensor", "kernel": dom, "achieved": fam[dom]["tflops"], "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": fam[dom]["tflops"] / peak_tf, "traffic": traffic, "peak_source": peak_src + " bf16_tflops_sustained",
                 "flop_per_launch": fam[dom]["flop_per_launch"], "ms_per_launch": fam[dom]["ms_per_launch"],
                 "share_of_step": fam[dom]["ms_per_step"] / (ms_dev / K),
                 "all_tensor_kernels": {"tflops": total_tf, "frac": total_tf / peak_tf,
                                        "share_of_step": total_ms / (ms_dev / K)}}
+    peak_bw = peaks.get("hbm_gbs", 6500.0)
+    roofline_bw = None
+    if bwfam:
+        bdom = max(bwfam, key=lambda n: bwfam[n]["ms_per_step"])
+        bms = sum(f["ms_per_step"] for f in bwfam.values())
+        bgbs = sum(f["gbs"] * f["ms_per_step"] for f in bwfam.values()) / bms if bms else 0.0
+        roofline_bw = {"bound": "hbm", "kernel": bdom, "achieved": bwfam[bdom]["gbs"], "peak": peak_bw, "unit": "GB/s",
+                       "frac": bwfam[bdom]["gbs"] / peak_bw, "peak_source": peak_src + " hbm_gbs",
+                       "bytes_per_launch": bwfam[bdom]["bytes_per_launch"], "ms_per_launch": bwfam[bdom]["ms_per_launch"],
+                       "share_of_step": bwfam[bdom]["ms_per_step"] / (ms_dev / K),
+                       "all_bandwidth_kernels": {"gbs": bgbs, "frac": bgbs / peak_bw, "share_of_step": bms / (ms_dev / K)},
+                       "per_kernel": {n: {"gbs": round(f["gbs"], 1), "frac": round(f["gbs"] / peak_bw, 3),
+                                          "ms_per_step": round(f["ms_per_step"], 4),
+                                          "launches_per_step": f["launches_per_step"]} for n, f in bwfam.items()}}
     value = world * B * K / (ms_dev / 1e3)
     useful = useful_flops_per_patch(S)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
@@ -327,7 +382,7 @@ def run_b200(args):
             "e2e": {"value": world * B * K / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K},
             "gpu_launches": launches, "cuda_graph": not args.no_graph, "eager_ms_per_step": ms_eager / K,
-            "roofline": roofline, "kernels": fam, "clocks": clk,
+            "roofline": roofline, "roofline_bw": roofline_bw, "kernels": fam, "clocks": clk,
             "useful_conv_tflops": useful * B / (ms_dev / K) / 1e9, "finite": finite}
     if world == 1 and not args.no_cpu_baseline:
         v, spstep, cores = cpu_oracle_run(S, args.cpu_sample, 2, 1)

@@ -25,7 +25,7 @@ def parse_header(path: Path = HEADER):
     """-> {name: (restype, [(ctype, is_pointer)])} for every b2c_* prototype."""
     text = re.sub(r"/\*.*?\*/", "", path.read_text(), flags=re.S)
     protos = {}
-    for m in re.finditer(r"(const char\*|int)\s+(b2c_\w+)\s*\(([^)]*)\)\s*;", text):
+    for m in re.finditer(r"(const char\*|long long|int)\s+(b2c_\w+)\s*\(([^)]*)\)\s*;", text):
         ret, name, args = m.group(1), m.group(2), m.group(3).strip()
         sig = []
         if args and args != "void":
@@ -36,7 +36,7 @@ def parse_header(path: Path = HEADER):
                 else:
                     ty = re.sub(r"\s+\w+$", "", a).replace("const ", "").strip()
                     sig.append((_CTYPES[ty], False))
-        protos[name] = (ctypes.c_char_p if ret.startswith("const char") else ctypes.c_int, sig)
+        protos[name] = ({"const char*": ctypes.c_char_p, "long long": ctypes.c_longlong}.get(ret, ctypes.c_int), sig)
     return protos
 
 
@@ -58,7 +58,7 @@ class _Native:
             fn.argtypes = [t for t, _ in sig]
             self.fns[name] = fn
         self.launches = 0
-        self.timed = None  # bench hook: {kernel name: [(start_event, end_event, scalar args)]} (see time_kernels)
+        self.timed = None  # bench hook: {kernel name: [(start_event, end_event, argument pattern)]} (see time_kernels)
 
     def call(self, name, *args):
         fn = self.fns[name]
@@ -80,7 +80,8 @@ class _Native:
         rc = fn(*conv, stream.cuda_stream)
         if rec is not None:
             ev1.record(stream)
-            rec.append((ev0, ev1, tuple(a for a in args if isinstance(a, (int, float)))))
+            # scalars as they are, every other argument as "was it given": enough to size the launch (bench.py, kprof.py)
+            rec.append((ev0, ev1, tuple(a if isinstance(a, (int, float)) else (a is not None) for a in args)))
         self.launches += 1
         if rc != 0:
             raise B2CError(f"{name} failed ({rc}): {self.lib.b2c_last_error().decode()}")
@@ -98,6 +99,11 @@ def backend():
 
 def call(name, *args):
     backend().call(name, *args)
+
+
+def query(name, *args):
+    """Host-side helper entry points that return a value and launch nothing (e.g. workspace sizes)."""
+    return backend().fns[name](*args)
 
 
 def launch_count() -> int:

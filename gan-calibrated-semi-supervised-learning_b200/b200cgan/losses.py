@@ -50,15 +50,36 @@ def iou_metric(pred_boxes, target_boxes, eps=1e-6):
     return ops.iou_rows(pred_boxes, target_boxes, eps)
 
 
-def compute_gradient_penalty(discriminator, real_samples, fake_samples, device):
+def compute_gradient_penalty(discriminator, real_samples, fake_samples, device, alpha=None):
     """WGAN-GP penalty on per-sample interpolates of (pred, other) pairs   (cgan/losses.py:185-233).
-    The double backward runs through ops.Conv4s2Dgrad / INActBwd / FirstDgrad / HeadDgrad."""
+    The double backward runs through ops.Conv4s2Dgrad / INActBwd / FirstDgrad / HeadDgrad.
+
+    alpha (optional, (B,1,1,1) or (B,)): the interpolation coefficients; default: B draws from the counter-based stream
+    (b200cgan.rng, keyed by global sample index), where the reference calls torch.rand (cgan/losses.py:199).
+    For a b200cgan Discriminator the interpolates are never materialised: alpha * real + (1 - alpha) * fake is formed
+    inside the first conv's gather (and again inside its weight-gradient kernel), and the tensors differentiated
+    against are uninitialised placeholders of the interpolates' shape.  During the inputs-only first backward the
+    weight-gradient branches are switched off (they would be computed and thrown away)."""
+    from . import rng
+    from .models import Discriminator
     batch_size = real_samples[0].size(0)
-    alpha = torch.rand(batch_size, 1, 1, 1, device=device)
-    ip = torch.lerp(fake_samples[0], real_samples[0], alpha).detach().requires_grad_(True)
-    io = torch.lerp(fake_samples[1], real_samples[1], alpha).detach().requires_grad_(True)
-    d_interpolated = discriminator(ip, io)
-    g0, g1 = torch.autograd.grad(outputs=d_interpolated, inputs=[ip, io],
-                                 grad_outputs=torch.ones_like(d_interpolated),
-                                 create_graph=True, retain_graph=True, only_inputs=True)
+    dev = real_samples[0].device
+    if alpha is None:
+        alpha = rng.next_uniform(batch_size, dev)
+    alpha = alpha.to(dev)
+    if isinstance(discriminator, Discriminator):
+        interp = ops.Interp(real_samples[0], real_samples[1], fake_samples[0], fake_samples[1], alpha)
+        ip = torch.empty_like(interp.a0).requires_grad_(True)  # placeholders: only their autograd identity is used
+        io = torch.empty_like(interp.a1).requires_grad_(True)
+        d_interpolated = discriminator(ip, io, _interp=interp)
+    else:
+        a = alpha.reshape(-1, 1, 1, 1)
+        ip = torch.lerp(fake_samples[0], real_samples[0], a).detach().requires_grad_(True)
+        io = torch.lerp(fake_samples[1], real_samples[1], a).detach().requires_grad_(True)
+        d_interpolated = discriminator(ip, io)
+    ones = torch.empty_like(d_interpolated)
+    ops.fill_(ones, 1.0)
+    with ops.backward_flags(weight_grads=False):
+        g0, g1 = torch.autograd.grad(outputs=d_interpolated, inputs=[ip, io], grad_outputs=ones,
+                                     create_graph=True, retain_graph=True, only_inputs=True)
     return ops.GradNormPenalty.apply(g0, g1)

@@ -94,15 +94,37 @@ class SpectralNormConv2dK4S2(nn.Module):
         return self.weight_orig
 
     def weight_ctx(self):
-        W = self.weight_orig
-        R, K = W.shape[0], W.numel() // W.shape[0]
-        sig = torch.empty(2, dtype=torch.float32, device=W.device)
-        ws = torch.empty((R + 31) // 32 * K + R, dtype=torch.float32, device=W.device)
-        _lib.call("b2c_sn_power_iter", W.detach(), self.weight_u, self.weight_v, sig, ws, R, K, int(self.training))
-        return ops.WeightCtx(W, sig, self.weight_u.clone(), self.weight_v.clone())
+        return sn_weight_ctxs([self])[0]
 
     def extra_repr(self):
         return f"{self.in_channels}, {self.out_channels}, kernel_size=(4, 4), stride=(2, 2), padding=(1, 1), spectral_norm"
+
+
+def sn_weight_ctxs(convs):
+    """One power iteration (train mode) + sigma for ALL spectral-norm convs of a Discriminator forward in three launches
+    (b2c_sn_power_iter_multi), with the per-forward-instance (sigma, u, v) snapshots the backward of THAT forward needs
+    written by the same kernels into one scratch allocation.  -> [ops.WeightCtx] in the order of `convs`."""
+    import ctypes
+    n = len(convs)
+    dev = convs[0].weight_orig.device
+    shapes = [(c.weight_orig.shape[0], c.weight_orig.numel() // c.weight_orig.shape[0]) for c in convs]
+    a4 = lambda v: (v + 3) // 4 * 4
+    sizes = [(4, a4(R), a4(K), a4(K + (K + 31) // 32 + R)) for R, K in shapes]  # sig, u_snap, v_snap, ws
+    buf = torch.empty(sum(sum(t) for t in sizes), dtype=torch.float32, device=dev)
+    views, off = [], 0
+    for (R, K), t in zip(shapes, sizes):
+        sig = buf[off:off + 2]; off += t[0]
+        us = buf[off:off + R]; off += t[1]
+        vs = buf[off:off + K]; off += t[2]
+        ws = buf[off:off + t[3]]; off += t[3]
+        views.append((sig, us, vs, ws))
+    P, I = ctypes.c_void_p, ctypes.c_int
+    arr = lambda ts: (P * n)(*[t.data_ptr() for t in ts])
+    _lib.call("b2c_sn_power_iter_multi", arr([c.weight_orig for c in convs]), arr([c.weight_u for c in convs]),
+              arr([c.weight_v for c in convs]), arr([v[0] for v in views]), arr([v[3] for v in views]),
+              arr([v[1] for v in views]), arr([v[2] for v in views]), (I * n)(*[r for r, _ in shapes]),
+              (I * n)(*[k for _, k in shapes]), n, int(convs[0].training))
+    return [ops.WeightCtx(c.weight_orig, v[0], v[1], v[2]) for c, v in zip(convs, views)]
 
 
 class ConvTranspose2dK4S2(nn.Module):
@@ -220,6 +242,11 @@ class GeneratorUNet(nn.Module):
     def dropout_sites(self):
         return [self.down4.model[-1], self.up1.model[-1], self.up2.model[-1]]
 
+    @staticmethod
+    def dropout_numels(B, S):
+        """Elements drawn per train-mode forward at the three sites (down4, up1, up2), in order."""
+        return [B * 512 * (S // 16) ** 2, B * 256 * (S // 8) ** 2, B * 128 * (S // 4) ** 2]
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         # each skip tensor has two consumers; SkipTap sums their gradients with one strided kernel
         d1, s1 = ops.SkipTap.apply(self.down1(x))
@@ -261,14 +288,32 @@ class Discriminator(nn.Module):
             HeadConv2d(512),
         ])
 
-    def forward(self, pred_patch: torch.Tensor, other_patch: torch.Tensor) -> torch.Tensor:
+    def weight_ctxs(self):
+        """Per-forward weight contexts of model.{0,2,5,8}: with spectral norm, all four power iterations of this forward
+        in three launches (torch runs the hook of every wrapped conv at the top of its forward, spectral_norm.py:92-114)."""
+        convs = [self.model[i] for i in (0, 2, 5, 8)]
+        if isinstance(convs[0], SpectralNormConv2dK4S2):
+            return sn_weight_ctxs(convs)
+        return [c.weight_ctx() for c in convs]
+
+    def first_block(self, pred_patch, other_patch, wctx, _interp=None):
+        """model.0-1: SN-conv(6 -> 64) + bias + LeakyReLU on cat(pred, other) (cat fused).  The LeakyReLU backward of this
+        layer is fused into model.2's data gradient (premasked / in_lrelu_slope)."""
         c0 = self.model[0]
-        # cat fused; the LeakyReLU backward of this layer is fused into model[2]'s data gradient (premasked / in_lrelu_slope)
-        a = ops.FirstConv.apply(pred_patch, other_patch, c0.param(), c0.bias, c0.weight_ctx(), 0.2, True)
-        for idx in (2, 5, 8):
-            conv = self.model[idx]
-            wctx = conv.weight_ctx()
-            wctx.want_stats = True
-            z = ops.Conv4s2.apply(a, conv.param(), conv.bias, wctx, True, 0.2 if idx == 2 else None)
-            a = ops.INAct.apply(z, 0.2, None, None, wctx.take_stats())
+        return ops.FirstConv.apply(pred_patch, other_patch, c0.param(), c0.bias, wctx, 0.2, True, _interp)
+
+    def norm_block(self, idx, a, wctx):
+        """model.{2,5,8} + InstanceNorm + LeakyReLU."""
+        conv = self.model[idx]
+        wctx.want_stats = True  # InstanceNorm statistics from the GEMM epilogue
+        z = ops.Conv4s2.apply(a, conv.param(), conv.bias, wctx, True, 0.2 if idx == 2 else None)
+        return ops.INAct.apply(z, 0.2, None, None, wctx.take_stats())
+
+    def forward(self, pred_patch: torch.Tensor, other_patch: torch.Tensor, _interp=None) -> torch.Tensor:
+        """_interp (ops.Interp, internal): the gradient penalty's interpolates (cgan/losses.py:203-204) are formed inside
+        the first-layer gather; pred_patch / other_patch are then autograd placeholders for them."""
+        ctxs = self.weight_ctxs()
+        a = self.first_block(pred_patch, other_patch, ctxs[0], _interp)
+        for idx, wctx in zip((2, 5, 8), ctxs[1:]):
+            a = self.norm_block(idx, a, wctx)
         return ops.HeadConv.apply(a, self.model[11].weight)

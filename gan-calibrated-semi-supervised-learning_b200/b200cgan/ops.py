@@ -18,6 +18,115 @@ BF16 = torch.bfloat16
 CL = torch.channels_last
 
 
+# ------------------------------------------------------------------------------------------------ backward switches
+class _Flags:
+    """Which parts of a backward pass are live.  torch.autograd.Function.needs_input_grad is static, so the pass
+    autograd.grad(inputs=[interpolates], create_graph=True) of the gradient penalty (cgan/losses.py:213-220) would also
+    compute every weight gradient (and throw it away), and d_loss.backward() would compute the gradient of the
+    interpolates once more.  compute_gradient_penalty / CGANTrainer switch those dead branches off."""
+    weight_grads = True   # False inside the inputs-only first backward of the gradient penalty
+    first_dgrad = True    # False inside CGANTrainer's d_loss.backward(): nobody reads d loss / d patches
+
+
+FLAGS = _Flags()
+
+
+class backward_flags:
+    def __init__(self, **kw):
+        self.kw = kw
+
+    def __enter__(self):
+        self.prev = {k: getattr(FLAGS, k) for k in self.kw}
+        for k, v in self.kw.items():
+            setattr(FLAGS, k, v)
+
+    def __exit__(self, *a):
+        for k, v in self.prev.items():
+            setattr(FLAGS, k, v)
+
+
+# ------------------------------------------------------------------------------------------------ gradient sinks
+# A parameter with a sink (installed by FusedClipAdam: a view into the network's flat fp32 gradient bucket, also visible as
+# param.grad) receives its weight gradients IN PLACE from the kernels: every wgrad-type kernel accumulates into the sink,
+# backward() returns None for that parameter, and autograd launches no add kernels (a D weight gets 3-4 contributions per
+# critic step: real, fake and the two terms of the penalty).  Parameters without a sink get ordinary returned gradients,
+# so the modules also work under a plain torch loop (torch.optim.Adam + clip_grad_norm_).
+def sink_of(param):
+    return getattr(param, "_b2c_sink", None)
+
+
+_SN_PENDING = {}  # id(weight_orig) -> (param, [(u, v, sig, part, nparts)]): rank-1 terms owed to the sink (flush_sn_pending)
+
+
+def _sn_defer(wctx, part, nparts):
+    _SN_PENDING.setdefault(id(wctx.weight), (wctx.weight, []))[1].append((wctx.u, wctx.v, wctx.sig, part, nparts))
+
+
+def flush_sn_pending():
+    """Spectral-norm backward, second half: the weight-gradient kernels put sum_i dWe_i / sigma_i into the sinks; this ONE
+    launch subtracts sum_i (<dWe_i, W> / sigma_i^2) u_i v_i^T for every layer and forward instance."""
+    if not _SN_PENDING:
+        return
+    items = list(_SN_PENDING.values())
+    _SN_PENDING.clear()
+    nl = len(items)
+    ninst = [len(lst) for _, lst in items]
+    tot = sum(ninst)
+    P, I = ctypes.c_void_p, ctypes.c_int
+    grad = (P * nl)(*[sink_of(p).data_ptr() for p, _ in items])
+    R = (I * nl)(*[p.shape[0] for p, _ in items])
+    K = (I * nl)(*[p.numel() // p.shape[0] for p, _ in items])
+    flat = [inst for _, lst in items for inst in lst]
+    _lib.call("b2c_sn_rank1", grad, R, K, (I * nl)(*ninst), nl, (P * tot)(*[f[0].data_ptr() for f in flat]),
+              (P * tot)(*[f[1].data_ptr() for f in flat]), (P * tot)(*[f[2].data_ptr() for f in flat]),
+              (P * tot)(*[f[3].data_ptr() for f in flat]), (I * tot)(*[f[4] for f in flat]))
+
+
+# ------------------------------------------------------------------------------------------------ packed weights
+_PACKS = {}  # id(param) -> {"key": ..., "c": tensor | None, "t": tensor | None}; buffers are persistent (CUDA-graph safe)
+
+
+def _pack_entry(param):
+    key = (param._version, getattr(param, "_b2c_epoch", 0), param.data_ptr())
+    e = _PACKS.get(id(param))
+    if e is None:
+        e = _PACKS[id(param)] = {"key": key, "c": None, "t": None, "c_ok": False, "t_ok": False, "ref": param}
+    elif e["key"] != key or e["ref"] is not param:
+        e.update(key=key, c_ok=False, t_ok=False, ref=param)
+    return e
+
+
+def invalidate_packs():
+    """Forget which bf16 packs are current (buffers stay): the next use of every weight re-packs it.  CGANTrainer calls
+    this before capturing a CUDA graph so that the capture contains every pack the replays need."""
+    for e in _PACKS.values():
+        e["c_ok"] = e["t_ok"] = False
+
+
+def packed_c(param):
+    """bf16 [D0][16*D1] K-major operand of the UN-SCALED master weight; re-packed only after the weight changed
+    (torch version counter, or FusedClipAdam's epoch stamp) - once per optimizer step instead of once per forward."""
+    e = _pack_entry(param)
+    if not e["c_ok"]:
+        d0, d1 = param.shape[:2]
+        if e["c"] is None:
+            e["c"] = torch.empty(d0, 16 * d1, dtype=BF16, device=param.device)
+        _lib.call("b2c_pack_w_c", param.detach(), None, e["c"], d0, d1)
+        e["c_ok"] = True
+    return e["c"]
+
+
+def packed_t(param):
+    e = _pack_entry(param)
+    if not e["t_ok"]:
+        d0, d1 = param.shape[:2]
+        if e["t"] is None:
+            e["t"] = torch.empty(4, d1, 4 * d0, dtype=BF16, device=param.device)
+        _lib.call("b2c_pack_w_t", param.detach(), None, e["t"], d0, d1)
+        e["t_ok"] = True
+    return e["t"]
+
+
 def cl_empty(N, C, H, W, dtype=BF16, device=None):
     return torch.empty((N, C, H, W), dtype=dtype, device=device or torch.device("cuda"), memory_format=CL)
 
@@ -47,12 +156,12 @@ def dense_nhwc(t):
 
 
 class WeightCtx:
-    """One forward instance of a conv weight: the fp32 master tensor, the spectral-norm (u, v, sigma) snapshot used by
-    THAT forward (torch spectral_norm.py:97-112 advances u/v every train-mode forward) and lazily packed bf16 forms."""
+    """One forward instance of a conv weight: the fp32 master parameter and the spectral-norm (u, v, sigma) snapshot used
+    by THAT forward (torch spectral_norm.py:97-112 advances u/v every train-mode forward).  The tensor-core operands are
+    the cached packs of the un-scaled weight; 1/sigma rides along as the `scale` of the GEMM epilogues."""
 
     def __init__(self, weight, sig=None, u=None, v=None):
         self.weight, self.sig, self.u, self.v = weight, sig, u, v
-        self._c = self._t = None
         self.want_stats = False  # ask the forward conv for the InstanceNorm statistics of its output ...
         self._stats = None       # ... which take_stats() hands to INAct / INActPoolFC
 
@@ -65,21 +174,13 @@ class WeightCtx:
         return None if self.sig is None else self.sig[1:]
 
     def pack_c(self):
-        if self._c is None:
-            d0, d1 = self.weight.shape[:2]
-            self._c = torch.empty(d0, 16 * d1, dtype=BF16, device=self.weight.device)
-            _lib.call("b2c_pack_w_c", self.weight.detach(), self.inv_sigma, self._c, d0, d1)
-        return self._c
+        return packed_c(self.weight)
 
     def pack_t(self):
-        if self._t is None:
-            d0, d1 = self.weight.shape[:2]
-            self._t = torch.empty(4, d1, 4 * d0, dtype=BF16, device=self.weight.device)
-            _lib.call("b2c_pack_w_t", self.weight.detach(), self.inv_sigma, self._t, d0, d1)
-        return self._t
+        return packed_t(self.weight)
 
     def finish_wgrad(self, dwe):
-        """dL/dW_eff -> dL/dW_orig through W_eff = W / sigma(u, v)   (SURVEY.md App. B)."""
+        """dL/dW_eff -> dL/dW_orig through W_eff = W / sigma(u, v)   (SURVEY.md App. B); sink-less path."""
         if self.sig is None:
             return dwe
         R = self.weight.shape[0]
@@ -101,33 +202,48 @@ def _conv_raw(x, wctx, bias, want_stats=False):
     Cout = wctx.weight.shape[0]
     y = cl_empty(N, Cout, H // 2, W // 2, device=x.device)
     zs = _stats_buf(N, Cout, x.device) if want_stats else None
-    _lib.call("b2c_conv4s2_bf16", x, Cin, wctx.pack_c(), bias, y, Cout, zs, N, H, W, Cin, Cout)
+    _lib.call("b2c_conv4s2_bf16", x, Cin, wctx.pack_c(), wctx.inv_sigma, bias, y, Cout, zs, N, H, W, Cin, Cout)
     if want_stats:
         wctx._stats = zs
     return y
 
 
-def _convt_raw(x, wpack_t, Cout, wctx=None, act=None, slope=1.0):
+def _convt_raw(x, wpack_t, Cout, wctx=None, act=None, slope=1.0, scale=None):
     x, ld = as_nhwc(x)
     N, Cin, H, W = x.shape
     y = cl_empty(N, Cout, 2 * H, 2 * W, device=x.device)
     zs = _stats_buf(N, Cout, x.device) if (wctx is not None and wctx.want_stats) else None
-    _lib.call("b2c_convt4s2_bf16", x, ld, wpack_t, None, y, Cout, zs, act, float(slope), N, H, W, Cin, Cout)
+    _lib.call("b2c_convt4s2_bf16", x, ld, wpack_t, scale, None, y, Cout, zs, act, float(slope), N, H, W, Cin, Cout)
     if zs is not None:
         wctx._stats = zs
     return y
 
 
-def _wgrad_raw(small, large):
-    """-> fp32 [Cs][Cl][4][4] = sum small[n,sy,sx,a] large[n,2sy+ky-1,2sx+kx-1,b]."""
+def _wgrad(wctx, small, large):
+    """Weight gradient sum small[n,sy,sx,a] large[n,2sy+ky-1,2sx+kx-1,b] -> [Cs][Cl][4][4] of wctx.weight.  With a sink:
+    accumulated in place (times 1/sigma, rank-1 term deferred) and None is returned; else returned as a tensor."""
     small, lds = as_nhwc(small)
     large = dense_nhwc(large)
     N, Cs, Hs, Ws = small.shape
     Cl = large.shape[1]
-    ws = torch.empty(16, Cs, Cl, dtype=torch.float32, device=small.device)
-    dw = torch.empty(Cs, Cl, 4, 4, dtype=torch.float32, device=small.device)
-    _lib.call("b2c_wgrad4s2_bf16", small, lds, large, Cl, ws, dw, 0, N, Hs, Ws, Cs, Cl, _lib.sm_count())
-    return dw
+    dev = small.device
+    nws = _lib.query("b2c_wgrad4s2_ws_floats", N, Hs, Ws, Cs, Cl, _lib.sm_count())
+    ws = torch.empty(nws, dtype=torch.float32, device=dev)
+    sink = sink_of(wctx.weight)
+    if sink is None:
+        dw = torch.empty(Cs, Cl, 4, 4, dtype=torch.float32, device=dev)
+        _lib.call("b2c_wgrad4s2_bf16", small, lds, large, Cl, ws, nws, dw, 0, None, None, None, None, N, Hs, Ws, Cs, Cl,
+                  _lib.sm_count())
+        return wctx.finish_wgrad(dw)
+    if wctx.sig is None:
+        _lib.call("b2c_wgrad4s2_bf16", small, lds, large, Cl, ws, nws, sink, 1, None, None, None, None, N, Hs, Ws, Cs, Cl,
+                  _lib.sm_count())
+    else:
+        part, nparts = torch.empty(1024, dtype=torch.float32, device=dev), ctypes.c_int(0)
+        _lib.call("b2c_wgrad4s2_bf16", small, lds, large, Cl, ws, nws, sink, 1, wctx.inv_sigma, wctx.weight.detach(), part,
+                  ctypes.byref(nparts), N, Hs, Ws, Cs, Cl, _lib.sm_count())
+        _sn_defer(wctx, part, nparts.value)
+    return None
 
 
 # ------------------------------------------------------------------------------------------------ conv k4 s2 p1
@@ -139,6 +255,7 @@ class Conv4s2(torch.autograd.Function):
         """in_lrelu_slope: x is the output of a LeakyReLU(slope) whose producer leaves its activation backward to this
         conv (FirstConv(premasked=True)): the returned input gradient is already multiplied by LeakyReLU'."""
         ctx.wctx, ctx.has_bias, ctx.bias_feeds_norm = wctx, bias is not None, bias_feeds_norm
+        ctx.bias_param = bias if isinstance(bias, torch.nn.Parameter) else None
         ctx.in_lrelu_slope = in_lrelu_slope
         ctx.save_for_backward(x)
         return _conv_raw(x, wctx, bias, wctx.want_stats)
@@ -155,15 +272,19 @@ class Conv4s2(torch.autograd.Function):
             else:
                 gx = LReluBwd.apply(Conv4s2Dgrad.apply(gy, ctx.wctx.weight, ctx.wctx, x.shape[2], x.shape[3]), x,
                                     ctx.in_lrelu_slope)
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and FLAGS.weight_grads:
             with torch.no_grad():
-                gw = ctx.wctx.finish_wgrad(_wgrad_raw(gy.detach(), x))
-        if ctx.has_bias and ctx.needs_input_grad[2]:
+                gw = _wgrad(ctx.wctx, gy.detach(), x)
+        if ctx.has_bias and ctx.needs_input_grad[2] and FLAGS.weight_grads:
             with torch.no_grad():
+                bsink = sink_of(ctx.bias_param) if ctx.bias_param is not None else None
                 if ctx.bias_feeds_norm:  # an affine-less InstanceNorm follows: d/d bias == 0 exactly
-                    gb = torch.zeros(gy.shape[1], dtype=torch.float32, device=gy.device)
+                    gb = None if bsink is not None else torch.zeros(gy.shape[1], dtype=torch.float32, device=gy.device)
                 else:
                     gb = channel_sum(gy.detach())
+                    if bsink is not None:
+                        bsink.add_(gb)
+                        gb = None
         return gx, gw, gb, None, None, None
 
 
@@ -180,7 +301,7 @@ class Conv4s2Dgrad(torch.autograd.Function):
             ctx.save_for_backward(gy, act)
         else:
             ctx.save_for_backward(gy)
-        return _convt_raw(gy, wctx.pack_t(), Cin, None, act, slope)
+        return _convt_raw(gy, wctx.pack_t(), Cin, None, act, slope, wctx.inv_sigma)
 
     @staticmethod
     def backward(ctx, h):
@@ -190,9 +311,9 @@ class Conv4s2Dgrad(torch.autograd.Function):
         g_gy = gw = None
         if ctx.needs_input_grad[0]:
             g_gy = Conv4s2.apply(h, ctx.wctx.weight, None, ctx.wctx, False)
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and FLAGS.weight_grads:
             with torch.no_grad():
-                gw = ctx.wctx.finish_wgrad(_wgrad_raw(gy.detach(), h.detach()))
+                gw = _wgrad(ctx.wctx, gy.detach(), h.detach())
         return g_gy, gw, None, None, None, None, None
 
 
@@ -212,8 +333,8 @@ class ConvT4s2(torch.autograd.Function):
         gx = gw = None
         if ctx.needs_input_grad[0]:
             gx = _conv_raw(gy, ctx.wctx, None)  # C-form pack of (Cin, Cout, 4, 4): output channels = Cin
-        if ctx.needs_input_grad[1]:
-            gw = _wgrad_raw(x, gy)
+        if ctx.needs_input_grad[1] and FLAGS.weight_grads:
+            gw = _wgrad(ctx.wctx, x, gy)
         return gx, gw, None
 
 
@@ -240,51 +361,98 @@ def _f32c(t):
     return None if t is None else t.detach().to(torch.float32).contiguous()
 
 
-def _first_fprop_raw(a0, a1, wctx, bias, slope):
-    a0, a1 = _f32c(a0), _f32c(a1)
+class Interp:
+    """GP interpolation x = alpha * a + (1 - alpha) * b (cgan/losses.py:203-204) fused into the first-layer gathers:
+    a0/a1 = real (pred, other), b0/b1 = fake, alpha: fp32 (N,) device tensor."""
+
+    def __init__(self, a0, a1, b0, b1, alpha):
+        self.a0, self.a1, self.b0, self.b1 = _f32c(a0), _f32c(a1), _f32c(b0), _f32c(b1)
+        self.alpha = alpha.detach().to(torch.float32).reshape(-1).contiguous()
+
+
+def _first_fprop_raw(a0, a1, wctx, bias, slope, interp=None):
+    if interp is not None:
+        a0, a1, b0, b1, al = interp.a0, interp.a1, interp.b0, interp.b1, interp.alpha
+    else:
+        a0, a1, b0, b1, al = _f32c(a0), _f32c(a1), None, None, None
     N, _, H, W = a0.shape
     y = cl_empty(N, 64, H // 2, W // 2, device=a0.device)
-    _lib.call("b2c_first_fprop", a0, a1, None, None, None, wctx.weight.detach(), wctx.inv_sigma, bias, y, N, H, W, slope)
+    _lib.call("b2c_first_fprop", a0, a1, b0, b1, al, wctx.weight.detach(), wctx.inv_sigma, bias, y, N, H, W, slope)
     return y
 
 
-def _first_wgrad_raw(a0, a1, gz, wctx, want_bias):
-    a0, a1 = _f32c(a0), _f32c(a1)
+def _first_wgrad(a0, a1, gz, wctx, bias_param, interp=None):
+    """-> (gw, gb); None where the gradient went into the parameter's sink."""
+    if interp is not None:
+        a0, a1, b0, b1, al = interp.a0, interp.a1, interp.b0, interp.b1, interp.alpha
+    else:
+        a0, a1, b0, b1, al = _f32c(a0), _f32c(a1), None, None, None
     gz = dense_nhwc(gz.detach())
     N, _, H, W = a0.shape
-    dw = torch.zeros_like(wctx.weight, dtype=torch.float32)
-    db = torch.zeros(64, dtype=torch.float32, device=dw.device) if want_bias else None
-    _lib.call("b2c_first_wgrad", a0, a1, None, None, None, gz, dw, db, N, H, W)
-    return dw, db
+    dev = gz.device
+    wsink = sink_of(wctx.weight)
+    bsink = sink_of(bias_param) if bias_param is not None else None
+    if wsink is None:
+        dw = torch.empty_like(wctx.weight, dtype=torch.float32)
+        _lib.call("b2c_zero", dw, dw.numel() * 4)
+        db = None
+        if bias_param is not None and bsink is None:
+            db = torch.empty(64, dtype=torch.float32, device=dev)
+            _lib.call("b2c_zero", db, 256)
+        _lib.call("b2c_first_wgrad", a0, a1, b0, b1, al, gz, dw, db if bsink is None else bsink, None, None, None, None,
+                  N, H, W)
+        return wctx.finish_wgrad(dw), db
+    db = None
+    if bias_param is not None and bsink is None:
+        db = torch.empty(64, dtype=torch.float32, device=dev)
+        _lib.call("b2c_zero", db, 256)
+    dbp = bsink if bsink is not None else db
+    if wctx.sig is None:
+        _lib.call("b2c_first_wgrad", a0, a1, b0, b1, al, gz, wsink, dbp, None, None, None, None, N, H, W)
+    else:
+        part, nparts = torch.empty(1024, dtype=torch.float32, device=dev), ctypes.c_int(0)
+        _lib.call("b2c_first_wgrad", a0, a1, b0, b1, al, gz, wsink, dbp, wctx.inv_sigma, wctx.weight.detach(), part,
+                  ctypes.byref(nparts), N, H, W)
+        _sn_defer(wctx, part, nparts.value)
+    return None, db
 
 
 class FirstConv(torch.autograd.Function):
     """act = LeakyReLU_slope(conv2d(cat(a0, a1), W_eff, bias, 2, 1)) on NCHW fp32 inputs (cgan/models.py:103,245,257)."""
 
     @staticmethod
-    def forward(ctx, a0, a1, weight, bias, wctx, slope, premasked=False):
+    def forward(ctx, a0, a1, weight, bias, wctx, slope, premasked=False, interp=None):
         """premasked: the (only) consumer of the output is a Conv4s2(in_lrelu_slope=slope), which returns its input
-        gradient already multiplied by LeakyReLU' - no separate activation-backward pass here."""
-        y = _first_fprop_raw(a0, a1, wctx, bias, slope)
-        ctx.premasked = premasked
+        gradient already multiplied by LeakyReLU' - no separate activation-backward pass here.
+        interp: the layer input is alpha * real + (1 - alpha) * fake, formed inside the gather; a0 / a1 are then only
+        autograd PLACEHOLDERS of the interpolates (uninitialised, never read) that receive d out / d interpolate."""
+        y = _first_fprop_raw(a0, a1, wctx, bias, slope, interp)
+        ctx.premasked, ctx.interp = premasked, interp
         ctx.wctx, ctx.slope, ctx.has_a1, ctx.has_bias = wctx, slope, a1 is not None, bias is not None
-        ctx.save_for_backward(a0, a1, y)
+        ctx.bias_param = bias if isinstance(bias, torch.nn.Parameter) else None
+        if interp is None:
+            ctx.save_for_backward(a0, a1, y)
+        else:
+            ctx.save_for_backward(y)
         return y
 
     @staticmethod
     def backward(ctx, g):
-        a0, a1, y = ctx.saved_tensors
+        if ctx.interp is None:
+            a0, a1, y = ctx.saved_tensors
+        else:
+            a0 = a1 = None
+            (y,) = ctx.saved_tensors
         gz = LReluBwd.apply(g, y, ctx.slope) if (ctx.slope != 1.0 and not ctx.premasked) else g
         g0 = g1 = gw = gb = None
-        if ctx.needs_input_grad[0] or (ctx.has_a1 and ctx.needs_input_grad[1]):
+        if (ctx.needs_input_grad[0] or (ctx.has_a1 and ctx.needs_input_grad[1])) and FLAGS.first_dgrad:
             g0, g1 = FirstDgrad.apply(gz, ctx.wctx.weight, ctx.wctx, ctx.has_a1)
             if not ctx.has_a1:
                 g1 = None
-        if ctx.needs_input_grad[2] or (ctx.has_bias and ctx.needs_input_grad[3]):
+        if (ctx.needs_input_grad[2] or (ctx.has_bias and ctx.needs_input_grad[3])) and FLAGS.weight_grads:
             with torch.no_grad():
-                dwe, gb = _first_wgrad_raw(a0, a1, gz, ctx.wctx, ctx.has_bias)
-                gw = ctx.wctx.finish_wgrad(dwe)
-        return g0, g1, gw, gb, None, None, None
+                gw, gb = _first_wgrad(a0, a1, gz, ctx.wctx, ctx.bias_param if ctx.has_bias else None, ctx.interp)
+        return g0, g1, gw, gb, None, None, None, None
 
 
 class FirstDgrad(torch.autograd.Function):
@@ -301,7 +469,7 @@ class FirstDgrad(torch.autograd.Function):
         ws = torch.empty(32 * 576, dtype=BF16, device=gzd.device)
         _lib.call("b2c_first_dgrad", gzd, wctx.weight.detach(), wctx.inv_sigma, g0, g1, ws, N, 2 * Ho, 2 * Wo)
         if g1 is None:
-            g1 = g0.new_zeros(())
+            g1 = g0.new_empty(())
             ctx.mark_non_differentiable(g1)
         return g0, g1
 
@@ -312,10 +480,9 @@ class FirstDgrad(torch.autograd.Function):
         g_gz = gw = None
         if ctx.needs_input_grad[0]:
             g_gz = FirstConv.apply(h0, h1, ctx.wctx.weight, None, ctx.wctx, 1.0)
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and FLAGS.weight_grads:
             with torch.no_grad():
-                dwe, _ = _first_wgrad_raw(h0, h1, gz, ctx.wctx, False)
-                gw = ctx.wctx.finish_wgrad(dwe)
+                gw, _ = _first_wgrad(h0, h1, gz, ctx.wctx, None)
         return g_gz, gw, None, None
 
 
@@ -418,7 +585,7 @@ class INActBwd(torch.autograd.Function):
         N, C, H, W = z.shape
         ws = torch.empty(N, C, 2, dtype=torch.float32, device=z.device)
         gz = cl_empty(N, C, H, W, device=z.device)
-        _lib.call("b2c_in_act_bwd", g, ldg, None, z, ldz, zs, mask, slope, ws, gz, C, N, H * W, C)
+        _lib.call("b2c_in_act_bwd", g, ldg, None, None, z, ldz, zs, mask, slope, ws, gz, C, N, H * W, C)
         ctx.mask, ctx.slope = mask, slope
         ctx.save_for_backward(g, z, zs)
         return gz
@@ -447,12 +614,12 @@ class INActPoolFC(torch.autograd.Function):
         N, C, H, W = z.shape
         if zs is None:
             zs = _in_stats(z, ldz)
-        ps = torch.empty(N, C, dtype=torch.float32, device=z.device)
+        ps = torch.empty(2, N, C, dtype=torch.float32, device=z.device)  # planar (sum act(x_hat), sum act'(x_hat))
         _lib.call("b2c_in_act_pool_fwd", z, ldz, zs, slope, ps, N, H * W, C)
         delta = torch.empty(N, 4, dtype=torch.float32, device=z.device)
         th = torch.empty_like(delta)
         _lib.call("b2c_pool_fc_fwd", ps, fc_w.detach(), fc_b.detach(), scale, H * W, delta, th, N, C)
-        ctx.slope, ctx.scale = slope, scale
+        ctx.slope, ctx.scale, ctx.fc_b = slope, scale, fc_b
         ctx.save_for_backward(z, zs, ps, th, fc_w)
         return delta
 
@@ -462,13 +629,16 @@ class INActPoolFC(torch.autograd.Function):
         z, zs, ps, th, fc_w = ctx.saved_tensors
         z, ldz = as_nhwc(z)
         N, C, H, W = z.shape
-        dW, db = torch.empty_like(fc_w), torch.empty(4, dtype=torch.float32, device=z.device)
+        wsink, bsink = sink_of(fc_w), sink_of(ctx.fc_b)
+        dW = wsink if wsink is not None else torch.empty_like(fc_w)
+        db = bsink if bsink is not None else torch.empty(4, dtype=torch.float32, device=z.device)
         gvec = torch.empty(N, C, dtype=torch.float32, device=z.device)
         _lib.call("b2c_pool_fc_bwd", gd.contiguous(), th, ps, fc_w.detach(), ctx.scale, H * W, dW, db, gvec, N, C)
         ws = torch.empty(N, C, 2, dtype=torch.float32, device=z.device)
         gz = cl_empty(N, C, H, W, device=z.device)
-        _lib.call("b2c_in_act_bwd", None, 0, gvec, z, ldz, zs, None, ctx.slope, ws, gz, C, N, H * W, C)
-        return gz, dW, db, None, None, None
+        # the plane sums of this backward follow from the forward's (sum act, sum act'): ONE apply pass over z
+        _lib.call("b2c_in_act_bwd", None, 0, gvec, ps, z, ldz, zs, None, ctx.slope, ws, gz, C, N, H * W, C)
+        return gz, (None if wsink is not None else dW), (None if bsink is not None else db), None, None, None
 
 
 # ------------------------------------------------------------------------------------------------ PatchGAN head
@@ -490,7 +660,7 @@ class HeadConv(torch.autograd.Function):
         ga = gw = None
         if ctx.needs_input_grad[0]:
             ga = HeadDgrad.apply(gy, weight, a.shape[2])
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and FLAGS.weight_grads:
             with torch.no_grad():
                 gw = _head_wgrad_raw(a, gy.detach(), weight)
         return ga, gw
@@ -499,7 +669,12 @@ class HeadConv(torch.autograd.Function):
 def _head_wgrad_raw(a, gy, weight):
     a = dense_nhwc(a)
     N, C, h, _ = a.shape
-    dw = torch.zeros_like(weight, dtype=torch.float32)
+    sink = sink_of(weight)
+    if sink is not None:  # accumulated in place
+        _lib.call("b2c_head_wgrad", a, gy.to(torch.float32).contiguous(), sink, N, h, C)
+        return None
+    dw = torch.empty_like(weight, dtype=torch.float32)
+    _lib.call("b2c_zero", dw, dw.numel() * 4)
     _lib.call("b2c_head_wgrad", a, gy.to(torch.float32).contiguous(), dw, N, h, C)
     return dw
 
@@ -520,7 +695,7 @@ class HeadDgrad(torch.autograd.Function):
         g_gy = gw = None
         if ctx.needs_input_grad[0]:
             g_gy = HeadConv.apply(hh, weight)
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and FLAGS.weight_grads:
             with torch.no_grad():
                 gw = _head_wgrad_raw(hh.detach(), gy, weight)
         return g_gy, gw, None
@@ -531,11 +706,11 @@ class MapMean(torch.autograd.Function):
     """mean over every element of an fp32 map (torch.mean at cgan/cgan_train_enhanced.py:327,362)."""
 
     @staticmethod
-    def forward(ctx, x):
+    def forward(ctx, x, scale=1.0):
         x = x.contiguous()
-        ctx.shape = x.shape
-        out = torch.zeros(1, dtype=torch.float32, device=x.device)
-        _lib.call("b2c_rowsum", x, x.numel(), 1, 0, 1.0 / x.numel(), out)
+        ctx.shape, ctx.scale = x.shape, scale
+        out = torch.empty(1, dtype=torch.float32, device=x.device)
+        _lib.call("b2c_map_mean", x, x.numel(), scale / x.numel(), out)
         return out.reshape(())
 
     @staticmethod
@@ -545,25 +720,47 @@ class MapMean(torch.autograd.Function):
         for s in ctx.shape:
             n *= s
         out = torch.empty(ctx.shape, dtype=torch.float32, device=g.device)
-        _lib.call("b2c_fill_scaled", out, n, g.contiguous(), 1.0 / n)
+        _lib.call("b2c_fill_scaled", out, n, g.contiguous(), ctx.scale / n)
+        return out, None
+
+
+class CriticLoss(torch.autograd.Function):
+    """d_loss = -(mean(real) - mean(fake)) + lambda_gp * gp in one launch (cgan/cgan_train_enhanced.py:327-328).
+    Returns a 3-vector (d_loss, wd, gp); differentiate element 0."""
+
+    @staticmethod
+    def forward(ctx, real, fake, gp, lambda_gp):
+        real, fake = real.contiguous(), fake.contiguous()
+        out = torch.empty(3, dtype=torch.float32, device=real.device)
+        _lib.call("b2c_critic_loss", real, real.numel(), fake, fake.numel(), gp.reshape(1), float(lambda_gp), out)
+        ctx.shapes, ctx.lam = (real.shape, fake.shape), float(lambda_gp)
         return out
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g):
+        g0 = g[0:1].contiguous()
+        gr = torch.empty(ctx.shapes[0], dtype=torch.float32, device=g.device)
+        gf = torch.empty(ctx.shapes[1], dtype=torch.float32, device=g.device)
+        _lib.call("b2c_critic_loss_bwd", g0, gr, gr.numel(), gf, gf.numel())
+        ggp = g0.reshape(()) if ctx.lam == 1.0 else g0.reshape(()) * ctx.lam
+        return gr, gf, ggp, None
 
 
 class GradNormPenalty(torch.autograd.Function):
     """mean_b (sqrt(|g0_b|^2 + |g1_b|^2 + 1e-12) - 1)^2   (cgan/losses.py:223-231).  Backward emits the seed of the
-    double backward, (2/B)(1 - 1/r_b) g, in one pass per tensor."""
+    double backward, (2/B)(1 - 1/r_b) g, in one pass per tensor.  Reductions are two-stage, fixed order."""
 
     @staticmethod
     def forward(ctx, g0, g1):
         g0, g1 = g0.contiguous(), g1.contiguous()
         B = g0.shape[0]
         n = g0.numel() // B
-        ss = torch.zeros(B, dtype=torch.float32, device=g0.device)
-        _lib.call("b2c_rowsum", g0, n, B, 1, 1.0, ss)
-        _lib.call("b2c_rowsum", g1, n, B, 1, 1.0, ss)
+        part, splits = torch.empty(32 * B, dtype=torch.float32, device=g0.device), ctypes.c_int(0)
+        _lib.call("b2c_gp_sumsq", g0, g1, n, B, part, ctypes.byref(splits))
         gp = torch.empty(1, dtype=torch.float32, device=g0.device)
         coef = torch.empty(B, dtype=torch.float32, device=g0.device)
-        _lib.call("b2c_gp_tail", ss, gp, coef, B)
+        _lib.call("b2c_gp_tail", part, splits.value, gp, coef, B)
         ctx.save_for_backward(g0, g1, coef)
         return gp.reshape(())
 
@@ -622,6 +819,12 @@ class EIoU(torch.autograd.Function):
         return gp, None, None
 
 
+def fill_(t, value):
+    """t[...] = value for a contiguous fp32 tensor (b2c_fill_scaled instead of an ATen fill kernel)."""
+    _lib.call("b2c_fill_scaled", t, t.numel(), None, float(value))
+    return t
+
+
 def iou_rows(pred, target, eps=1e-6):
     pred, target = pred.to(torch.float32).contiguous(), target.to(torch.float32).contiguous()
     out = torch.empty(pred.shape[0], dtype=torch.float32, device=pred.device)
@@ -631,36 +834,83 @@ def iou_rows(pred, target, eps=1e-6):
 
 # ------------------------------------------------------------------------------------------------ optimizer
 class FusedClipAdam:
-    """clip_grad_norm_(max_norm) + Adam in two multi-tensor launches (cgan/cgan_train_enhanced.py:256-257,331-332,368-369).
-    Torch-default Adam semantics (eps 1e-8, no weight decay, bias correction), one shared step counter."""
+    """clip_grad_norm_(max_norm) + Adam in two launches over FLAT buckets (cgan/cgan_train_enhanced.py:256-257,331-332,
+    368-369).  Torch-default Adam semantics (eps 1e-8, no weight decay, bias correction), one shared step counter.
+
+    The parameters are re-homed as views of one contiguous fp32 buffer, their gradients as views of a second one (the
+    gradient SINK the weight-gradient kernels accumulate into, also visible as param.grad), moments likewise: zero_grad is
+    one memset, the norm one two-stage reduction, the update one 128-bit vectorised kernel, and a data-parallel all-reduce
+    runs on the bucket itself (no gather / scatter copies).  `lr` lives on the device, so a scheduler can change it while
+    the step is replayed from a captured CUDA graph."""
 
     def __init__(self, params, lr=2e-4, betas=(0.5, 0.999), eps=1e-8, max_norm=1.0):
         self.params = [p for p in params]
-        assert 1 <= len(self.params) <= 16
-        self.lr, self.betas, self.eps, self.max_norm = lr, betas, eps, max_norm
-        self.m = [torch.zeros_like(p, dtype=torch.float32) for p in self.params]
-        self.v = [torch.zeros_like(p, dtype=torch.float32) for p in self.params]
+        assert self.params and all(p.is_cuda and p.dtype == torch.float32 for p in self.params)
+        dev = self.params[0].device
+        self.betas, self.eps, self.max_norm = betas, eps, max_norm
+        offs, total = [], 0
+        for p in self.params:
+            offs.append(total)
+            total += (p.numel() + 3) // 4 * 4  # 16-byte aligned slices
+        self.total = total
+        self.flat_p = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_m = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_v = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.slices = []
+        for p, o in zip(self.params, offs):
+            n = p.numel()
+            self.flat_p[o:o + n].copy_(p.data.reshape(-1))
+            p.data = self.flat_p[o:o + n].view_as(p)
+            p._b2c_sink = self.flat_g[o:o + n].view_as(p)
+            p.grad = p._b2c_sink
+            self.slices.append((o, n))
         self.step_count = 0
         self.step_base = None  # int64 device scalar added to step_count in the kernel (CUDA-graph replays)
-        self.gnorm_sq = torch.zeros(1, dtype=torch.float32, device=self.params[0].device)
-        n = len(self.params)
-        self._n = (ctypes.c_longlong * n)(*[p.numel() for p in self.params])
-        self._arr = lambda ts: (ctypes.c_void_p * n)(*[t.data_ptr() for t in ts])
+        self.grad_scale = 1.0  # data parallel: 1 / world_size (the all-reduce SUMs)
+        self.gnorm_sq = torch.zeros(1, dtype=torch.float32, device=dev)  # |clipped-from gradient|^2 of the last step
+        self._part = torch.empty(1024, dtype=torch.float32, device=dev)
+        self.lr_dev = torch.full((1,), float(lr), dtype=torch.float32, device=dev)
+        self._lr = float(lr)
+        self._n = (ctypes.c_longlong * 1)(total)
+        self._arr = lambda t: (ctypes.c_void_p * 1)(t.data_ptr())
+
+    @property
+    def lr(self):
+        return self._lr
+
+    @lr.setter
+    def lr(self, value):  # e.g. ReduceLROnPlateau (cgan_train_enhanced.py:427-428); takes effect in captured graphs too
+        self._lr = float(value)
+        self.lr_dev.fill_(self._lr)
+
+    def m_of(self, i):
+        o, n = self.slices[i]
+        return self.flat_m[o:o + n].view_as(self.params[i])
+
+    def v_of(self, i):
+        o, n = self.slices[i]
+        return self.flat_v[o:o + n].view_as(self.params[i])
 
     def zero_grad(self):
+        _lib.call("b2c_zero", self.flat_g, self.total * 4)
         for p in self.params:
-            p.grad = None
+            if p.grad is not p._b2c_sink:
+                p.grad = p._b2c_sink
 
     def step(self):
         """Returns the device scalar holding the squared pre-clip gradient norm (no host sync)."""
-        n = len(self.params)
-        grads = []
-        for p in self.params:
-            g = p.grad if p.grad is not None else torch.zeros_like(p)
-            grads.append(g.to(torch.float32).contiguous())
+        for p in self.params:  # a gradient that arrived through autograd (plain tensor) instead of the sink
+            if p.grad is not None and p.grad.data_ptr() != p._b2c_sink.data_ptr():
+                p._b2c_sink.copy_(p.grad)
+                p.grad = p._b2c_sink
         self.step_count += 1
-        _lib.call("b2c_multi_sumsq", self._arr(grads), self._n, n, self.gnorm_sq)
-        _lib.call("b2c_multi_adam", self._arr([p.data for p in self.params]), self._arr(grads), self._arr(self.m),
-                  self._arr(self.v), self._n, n, self.gnorm_sq, self.max_norm, self.lr, self.betas[0], self.betas[1],
-                  self.eps, self.step_count, self.step_base)
+        nparts = ctypes.c_int(0)
+        _lib.call("b2c_multi_sumsq", self._arr(self.flat_g), self._n, 1, self._part, ctypes.byref(nparts))
+        _lib.call("b2c_multi_adam", self._arr(self.flat_p), self._arr(self.flat_g), self._arr(self.flat_m),
+                  self._arr(self.flat_v), self._n, 1, self._part, nparts.value, self.gnorm_sq, float(self.grad_scale),
+                  float(self.max_norm), self._lr, self.lr_dev, self.betas[0], self.betas[1], self.eps, self.step_count,
+                  self.step_base)
+        for p in self.params:
+            p._b2c_epoch = getattr(p, "_b2c_epoch", 0) + 1  # cached bf16 packs of this weight are stale now
         return self.gnorm_sq

@@ -2,13 +2,18 @@
 of the reference trainer (cgan/cgan_train_enhanced.py:297-369) over the B200 modules.
 
 Differences from the reference loop, all outside the arithmetic:
-  * `refined_patch` is an input tensor (the reference re-crops it on the CPU with PIL from G's delta, :311-315,358-360,
-    non-differentiably; SURVEY.md §2 #5 keeps that file I/O out of the hot path);
-  * no .item() host syncs: logged scalars stay on the device until `StepOutput.to_host()` is called;
+  * `refined_patch` is either an input tensor (every BASELINE config: synthetic paired patches) or, with `refine_fn`,
+    recomputed on the device from G's current delta in every critic step and in the generator step, as the reference
+    does on the CPU with PIL (:311-315,358-360; b200cgan.refine is the CUDA crop + letterbox + bicubic kernel).  Without
+    `refine_fn` the critic steps' no-grad generator forward (:311) has no consumer and is not executed; its dropout
+    draws are skipped in the random stream so that the masks of the later forwards do not depend on that choice;
+  * no .item() host syncs: logged scalars stay on the device until `StepOutput.to_host()` makes ONE copy;
   * the generator step skips D's backward (the reference computes it and zeroes it next step: dead work), but still
     runs D's forward in train mode, which advances the spectral-norm u/v buffers exactly like the reference (:361);
-  * clip_grad_norm_ + Adam are one fused multi-tensor update per network;
-  * optional data-parallel gradient averaging (torch.distributed all-reduce) between backward and the update;
+  * parameters, gradients and Adam moments of each network live in flat fp32 buckets (ops.FusedClipAdam): the weight-
+    gradient kernels accumulate straight into the gradient bucket, zero_grad is one memset, clip_grad_norm_ + Adam are two
+    launches per network, and the optional data-parallel all-reduce (torch.distributed) runs on the bucket itself with
+    the 1/world_size folded into the Adam kernel;
   * optional CUDA-graph mode (`use_cuda_graph=True`): after two eager steps the whole step (about 480 kernel launches
     plus the autograd bookkeeping around them) is captured once and replayed; the dropout stream position and the Adam
     step counts live in a device-side counter block that is advanced between replays, so every replay draws fresh
@@ -16,7 +21,6 @@ Differences from the reference loop, all outside the arithmetic:
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field
 from typing import Dict, Optional
 
 import torch
@@ -75,88 +79,167 @@ class HostPrefetcher:
         self.free[(self.n_take - 1) % 2].record(torch.cuda.current_stream())
 
 
-@dataclass
 class StepOutput:
-    scalars: Dict[str, torch.Tensor] = field(default_factory=dict)
-    delta: Optional[torch.Tensor] = None
+    """Logged scalars of one step, kept on the device.  to_host() concatenates them and makes ONE device->host copy."""
+
+    def __init__(self, n_critic, lambda_iou):
+        self.n_critic, self.lambda_iou = n_critic, lambda_iou
+        self.critic = []      # per critic step: 3-vector (d_loss, wd, gp)
+        self.gnorm_sq = None  # (n_critic + 1,): squared pre-clip gradient norms of the D updates, then of the G update
+        self.loss_iou = self.loss_wgan = None
+        self.delta: Optional[torch.Tensor] = None
+
+    def _decode(self, v):
+        c = self.n_critic
+        out = {"d_loss": sum(v[3 * i] for i in range(c)) / c, "wd": sum(v[3 * i + 1] for i in range(c)) / c,
+               "gp": sum(v[3 * i + 2] for i in range(c)) / c}
+        for i in range(c):
+            out["d_gradnorm_%d" % i] = v[3 * c + i] ** 0.5
+        out["g_gradnorm"] = v[4 * c] ** 0.5
+        out["loss_iou"], out["loss_wgan"] = v[4 * c + 1], v[4 * c + 2]
+        out["loss_G"] = self.lambda_iou * out["loss_iou"] + out["loss_wgan"]
+        return out
+
+    def _flat(self):
+        return torch.cat([t.reshape(-1) for t in (*self.critic, self.gnorm_sq, self.loss_iou, self.loss_wgan)])
 
     def to_host(self):
-        return {k: float(v) for k, v in self.scalars.items()}
+        return self._decode(self._flat().tolist())
+
+    @property
+    def scalars(self) -> Dict[str, torch.Tensor]:
+        """The same quantities as device tensors (no host sync)."""
+        return self._decode(self._flat())
+
+
+def masks_to_device(masks, device="cuda"):
+    """{0,1} NCHW dropout masks (one per site) -> the dense u8 NHWC buffers DropoutSite.injected expects."""
+    return [m.permute(0, 2, 3, 1).contiguous().to(torch.uint8).to(device).reshape(-1) for m in masks]
 
 
 class CGANTrainer:
     def __init__(self, netG, netD, *, lr=2e-4, beta1=0.5, beta2=0.999, n_critic=2, lambda_gp=1.0, lambda_iou=1.0,
-                 process_group=None, world_size=1, use_cuda_graph=False):
+                 process_group=None, world_size=1, use_cuda_graph=False, refine_fn=None):
         self.netG, self.netD = netG, netD
         self.n_critic, self.lambda_gp, self.lambda_iou = n_critic, lambda_gp, lambda_iou
         self.optG = ops.FusedClipAdam(netG.parameters(), lr=lr, betas=(beta1, beta2))
         self.optD = ops.FusedClipAdam(netD.parameters(), lr=lr, betas=(beta1, beta2))
         self.pg, self.world_size = process_group, world_size
-        self.alpha_source = None  # test hook: callable(critic_step) -> (B,1,1,1) tensor replacing torch.rand
+        self.optG.grad_scale = self.optD.grad_scale = 1.0 / max(world_size, 1)
+        self.refine_fn = refine_fn  # callable(delta (B,4)) -> refined patches (B,3,S,S); None: `refined` is an input
+        # parity hooks: callable(critic_step) -> (B,) / (B,1,1,1) alpha, callable(g_call) -> 3 dense u8 NHWC masks, where
+        # g_call counts the reference's generator forwards of a batch (critic step c -> c, generator step -> n_critic)
+        self.alpha_source = None
+        self.mask_source = None
         self.use_cuda_graph = use_cuda_graph
         self._graph = None        # captured step (torch.cuda.CUDAGraph)
         self._eager_steps = 0
         self._static_in = self._static_out = self._ctr = self._ctr_inc = None
+        self._static_alpha = self._static_masks = None  # device buffers the captured graph reads the injected draws from
 
-    # ---- data parallel: average gradients over ranks (per-sample losses are batch means) ----
-    def _allreduce(self, params):
+    # ---- data parallel: SUM the flat gradient bucket over ranks; the 1/world is applied inside the Adam kernel ----
+    def _allreduce(self, opt):
         if self.world_size > 1:
-            allreduce_mean_([p.grad for p in params if p.grad is not None], self.pg, self.world_size)
+            import torch.distributed as dist
+            dist.all_reduce(opt.flat_g, op=dist.ReduceOp.SUM, group=self.pg)
 
-    def critic_step(self, pred, gt, refined, c=0):
+    def _seed3(self, dev):  # d/d (d_loss, wd, gp) = (1, 0, 0): persistent, so backward() launches no fill kernel
+        if getattr(self, "_s3", None) is None or self._s3.device != dev:
+            self._s3 = torch.tensor([1.0, 0.0, 0.0], dtype=torch.float32, device=dev)
+        return self._s3
+
+    def _seed1(self, dev):
+        if getattr(self, "_s1", None) is None or self._s1.device != dev:
+            self._s1 = torch.tensor(float(self.lambda_iou), dtype=torch.float32, device=dev)
+        return self._s1
+
+    # ---- random draws -------------------------------------------------------------------------------------------------
+    def _alpha(self, c, B, dev):
+        if self._static_alpha is not None:
+            return self._static_alpha[c]
+        if self.alpha_source is not None:
+            return self.alpha_source(c).to(dev, torch.float32).reshape(-1)
+        return None  # compute_gradient_penalty draws from the counter-based stream
+
+    def _set_masks(self, gcall):
+        sites = self.netG.dropout_sites()
+        if self._static_masks is not None:
+            ms = self._static_masks[gcall]
+        elif self.mask_source is not None:
+            ms = self.mask_source(gcall)
+        else:
+            ms = [None] * len(sites)
+        for site, m in zip(sites, ms):
+            site.injected = m
+
+    def _skip_generator_draws(self, pred):
+        """The reference's critic-step generator forward (:311) is not executed when nobody consumes its delta; keep the
+        random stream where it would be."""
+        if self.mask_source is None and self._static_masks is None:
+            for n in self.netG.dropout_numels(pred.shape[0], pred.shape[2]):
+                rng.skip(n)
+
+    # ---- the two halves of a step ---------------------------------------------------------------------------------------
+    def critic_step(self, pred, gt, refined, c=0, gnorm_out=None):
         netD, netG = self.netD, self.netG
         self.optD.zero_grad()
         real_validity = netD(pred, gt)
-        with torch.no_grad():
-            netG(pred)  # reference :311: train-mode forward; its delta only feeds the CPU re-crop we take as input
-        fake_validity = netD(pred, refined)
-        if self.alpha_source is not None:
-            orig = torch.rand
-            torch.rand = lambda *a, **k: self.alpha_source(c)
-            try:
-                gp = losses.compute_gradient_penalty(netD, (pred, gt), (pred, refined), pred.device)
-            finally:
-                torch.rand = orig
+        if self.refine_fn is not None:
+            self._set_masks(c)
+            with torch.no_grad():
+                refined = self.refine_fn(netG(pred))  # reference :311-315: fake patch from G's CURRENT delta
         else:
-            gp = losses.compute_gradient_penalty(netD, (pred, gt), (pred, refined), pred.device)
-        wd = ops.MapMean.apply(real_validity) - ops.MapMean.apply(fake_validity)
-        d_loss = -wd + self.lambda_gp * gp
-        d_loss.backward()
-        self._allreduce(self.optD.params)
-        gn = self.optD.step()
-        return d_loss.detach(), gp.detach(), wd.detach(), gn.clone()
+            self._skip_generator_draws(pred)
+        fake_validity = netD(pred, refined)
+        gp = losses.compute_gradient_penalty(netD, (pred, gt), (pred, refined), pred.device,
+                                             alpha=self._alpha(c, pred.shape[0], pred.device))
+        cl = ops.CriticLoss.apply(real_validity, fake_validity, gp, self.lambda_gp)  # (d_loss, wd, gp)
+        with ops.backward_flags(first_dgrad=False):  # nobody reads d loss / d interpolates
+            torch.autograd.backward(cl, self._seed3(cl.device))  # d_loss = cl[0]
+        ops.flush_sn_pending()
+        self._allreduce(self.optD)
+        if gnorm_out is not None:
+            self.optD.gnorm_sq = gnorm_out
+        self.optD.step()
+        return cl.detach()
 
-    def generator_step(self, pred, refined, pred_box, delta_true):
+    def generator_step(self, pred, refined, pred_box, delta_true, gnorm_out=None):
         netD, netG = self.netD, self.netG
         self.optG.zero_grad()
+        self._set_masks(self.n_critic)
         delta_pred = netG(pred)
         calibrated = losses.apply_delta_to_bbox(pred_box, delta_pred, training=True)
         with torch.no_grad():
             gt_boxes = losses.apply_delta_to_bbox(pred_box, delta_true, training=True)
         loss_iou = ops.EIoU.apply(calibrated, gt_boxes, 1e-6)
         with torch.no_grad():
-            loss_wgan = -ops.MapMean.apply(netD(pred, refined))
-        loss_reg = self.lambda_iou * loss_iou
-        loss_reg.backward()
-        self._allreduce(self.optG.params)
-        gn = self.optG.step()
-        return (loss_reg.detach() + loss_wgan), loss_iou.detach(), loss_wgan, gn.clone(), delta_pred.detach()
+            if self.refine_fn is not None:
+                refined = self.refine_fn(delta_pred.detach())  # reference :358-360
+            loss_wgan = ops.MapMean.apply(netD(pred, refined), -1.0)  # D still runs in train mode (advances u / v)
+        torch.autograd.backward(loss_iou, self._seed1(loss_iou.device))  # loss_G's live part: lambda_iou * loss_iou
+        self._allreduce(self.optG)
+        if gnorm_out is not None:
+            self.optG.gnorm_sq = gnorm_out
+        self.optG.step()
+        return loss_iou.detach(), loss_wgan, delta_pred.detach()
 
+    # ---- public entry point ----------------------------------------------------------------------------------------------
     def step(self, pred, gt, refined, pred_box, delta_true) -> StepOutput:
-        """One train step.  Device tensors in, device scalars out (StepOutput.to_host() copies them to the host)."""
+        """One train step.  Device tensors in, device scalars out (StepOutput.to_host() copies them to the host).
+        `refined` may be None when a refine_fn is installed."""
         args = (pred, gt, refined, pred_box, delta_true)
-        if not self.use_cuda_graph or self.alpha_source is not None or \
-                any(s.injected is not None for s in self.netG.dropout_sites()):
+        if not self.use_cuda_graph:
             return self._step_eager(*args)
         if self._graph is None:
             if self._eager_steps < 2:  # warm-up: function attributes, allocator, NCCL communicators
                 return self._step_eager(*args)
             self._capture(args)
-        elif any(a.shape != s.shape for a, s in zip(args, self._static_in)):
+        elif any(a is not None and a.shape != s.shape for a, s in zip(args, self._static_in)):
             raise ValueError("CUDA-graph mode was captured for inputs of shape %s" % (tuple(self._static_in[0].shape),))
         for s, a in zip(self._static_in, args):
-            if s.data_ptr() != a.data_ptr():
+            if a is not None and s.data_ptr() != a.data_ptr():
                 s.copy_(a, non_blocking=True)
+        self._load_injected()
         self._graph.replay()
         self._ctr.add_(self._ctr_inc)  # dropout stream position, D / G Adam step counts
         self.optD.host_steps += self.n_critic
@@ -178,13 +261,32 @@ class CGANTrainer:
             self.optD.step_base = self.optG.step_base = None
             self.optD.step_count, self.optG.step_count = dsteps, gsteps
             self._graph = None
+            self._static_alpha = self._static_masks = None
         self.use_cuda_graph = False
+
+    def _load_injected(self):
+        """Parity runs in graph mode: this step's injected alpha / masks go into the buffers the captured kernels read."""
+        if self._static_alpha is not None:
+            for c, buf in enumerate(self._static_alpha):
+                buf.copy_(self.alpha_source(c).to(buf.device, torch.float32).reshape(-1), non_blocking=True)
+        if self._static_masks is not None:
+            for gcall, bufs in self._static_masks.items():
+                for buf, m in zip(bufs, self.mask_source(gcall)):
+                    buf.copy_(m, non_blocking=True)
 
     def _capture(self, args):
         dev = args[0].device
-        self._static_in = [torch.empty_like(a) for a in args]
+        self._static_in = [None if a is None else torch.empty_like(a) for a in args]
         for s, a in zip(self._static_in, args):
-            s.copy_(a)
+            if a is not None:
+                s.copy_(a)
+        B = args[0].shape[0]
+        if self.alpha_source is not None:
+            self._static_alpha = [torch.empty(B, dtype=torch.float32, device=dev) for _ in range(self.n_critic)]
+        if self.mask_source is not None:
+            live = ([*range(self.n_critic)] if self.refine_fn is not None else []) + [self.n_critic]
+            self._static_masks = {g: [torch.empty_like(m) for m in self.mask_source(g)] for g in live}
+        self._load_injected()
         # device counter block: [dropout stream position, optD steps so far, optG steps so far]
         st = rng.get_state()
         self._ctr = torch.tensor([st["offset"], self.optD.step_count, self.optG.step_count], dtype=torch.int64, device=dev)
@@ -193,6 +295,7 @@ class CGANTrainer:
         rng.set_device_base(self._ctr[0:1])
         self.optD.step_base, self.optG.step_base = self._ctr[1:2], self._ctr[2:3]
         self.optD.step_count = self.optG.step_count = 0
+        ops.invalidate_packs()  # the capture must contain every weight pack the replays need
         torch.cuda.synchronize()
         self._graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._graph):
@@ -206,15 +309,10 @@ class CGANTrainer:
     def _step_eager(self, pred, gt, refined, pred_box, delta_true) -> StepOutput:
         self._eager_steps += 1
         self.netG.train(); self.netD.train()
-        out = StepOutput()
-        acc = None
+        out = StepOutput(self.n_critic, self.lambda_iou)
+        out.gnorm_sq = torch.empty(self.n_critic + 1, dtype=torch.float32, device=pred.device)
         for c in range(self.n_critic):
-            r = self.critic_step(pred, gt, refined, c)
-            out.scalars["d_gradnorm_%d" % c] = r[3].sqrt().reshape(())
-            acc = list(r[:3]) if acc is None else [a + b for a, b in zip(acc, r[:3])]
-        for k, v in zip(("d_loss", "gp", "wd"), acc):
-            out.scalars[k] = v / self.n_critic
-        lg, liou, lw, gn, delta = self.generator_step(pred, refined, pred_box, delta_true)
-        out.scalars.update({"loss_G": lg, "loss_iou": liou, "loss_wgan": lw, "g_gradnorm": gn.sqrt().reshape(())})
-        out.delta = delta
+            out.critic.append(self.critic_step(pred, gt, refined, c, out.gnorm_sq[c:c + 1]))
+        out.loss_iou, out.loss_wgan, out.delta = self.generator_step(pred, refined, pred_box, delta_true,
+                                                                     out.gnorm_sq[self.n_critic:])
         return out

@@ -30,6 +30,7 @@ struct ConvT64Params {
   const __nv_bfloat16* act;  // nullable: dense (N,2H,2W,64) activation a = LeakyReLU(z); y *= (a > 0 ? 1 : slope), i.e. the
   float slope;               // backward of the LeakyReLU that produced this conv's input, fused into its data gradient
   int st256;                 // y and ldy allow 32-byte stores
+  const float* scale;        // nullable device scalar multiplying the accumulators (spectral norm 1/sigma)
 };
 
 namespace {
@@ -227,6 +228,7 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
     const int r = q * 32 + lane;
     const int bw = r % p.BW, bh = (r / p.BW) % p.BH, bi = r / (p.BW * p.BH);
     const int Ho = 2 * p.H, Wo = 2 * p.W;
+    const float osc = p.scale ? __ldg(p.scale) : 1.f;
     int lt = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
       const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, tn = tile / (p.tiles_x * p.tiles_y);
@@ -264,6 +266,13 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+          }
+          if (p.scale) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              v0[i] = __float_as_uint(__uint_as_float(v0[i]) * osc);
+              v1[i] = __float_as_uint(__uint_as_float(v1[i]) * osc);
+            }
           }
           if (ACT && valid) {  // fused LeakyReLU backward: scale by the slope where the forward activation was <= 0
 #pragma unroll
@@ -337,13 +346,13 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
 // with pixel stride ldy; stats as in b2c_convt4s2_bf16.  Called by b2c_convt4s2_bf16 (tapgemm.cu) when Cout == 64.
 extern "C" int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream);  // norm.cu
 
-int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, float* stats,
-                    const void* act, float slope, int N, int H, int W, int Cin, void* stream) {
+int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const float* scale, void* y, long long ldy,
+                    float* stats, const void* act, float slope, int N, int H, int W, int Cin, void* stream) {
   extern int g_f32_output;  // tapgemm.cu
   ConvT64Params p;
   p.stats = nullptr;
   p.f32out = g_f32_output;
-  p.act = (const __nv_bfloat16*)act; p.slope = slope;
+  p.act = (const __nv_bfloat16*)act; p.slope = slope; p.scale = scale;
   p.st256 = (((uintptr_t)y & 31) == 0 && ldy % 16 == 0) ? 1 : 0;
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.kchunks = Cin / 64; p.y = (__nv_bfloat16*)y; p.ldy = ldy;
   p.BW = W < 128 ? W : 128;

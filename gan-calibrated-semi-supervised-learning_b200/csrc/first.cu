@@ -221,6 +221,8 @@ __global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_ker
 template <int CIN, bool INTERP>
 __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, const __grid_constant__ CUtensorMap tmG,
                                                                     float* __restrict__ dw, float* __restrict__ db,
+                                                                    const float* __restrict__ scale,
+                                                                    const float* __restrict__ wdot, float* __restrict__ part,
                                                                     int N, int H, int W) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -284,7 +286,9 @@ __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, 
     }
     if (next < ntiles) issue_field<CIN, INTERP>(in, next * 128 + t, npix, Ho, Wo, H, W, f);
   }
+  float dot = 0.f;  // <this CTA's partial dW (unscaled), wdot>: deferred rank-1 term of the spectral-norm backward
   if (it > 0) {
+    const float sc = scale ? __ldg(scale) : 1.f;
     mbar_wait(mma_bar, (it - 1) & 1);
     tc_fence_after();
     // TMEM lane t = im2col column k = t = (c*4 + ky)*4 + kx: dw[co][k] in the weight tensor's own layout.
@@ -298,12 +302,23 @@ __global__ void __launch_bounds__(FT_THREADS) first_wgrad_tc_kernel(FirstIn in, 
       tmem_ld_wait();
       if (t < 16 * CIN) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) atomicAdd(dw + (long long)(c0 + j) * (16 * CIN) + t, __uint_as_float(v[j]));
+        for (int j = 0; j < 16; ++j) {
+          const long long idx = (long long)(c0 + j) * (16 * CIN) + t;
+          if (wdot) dot += __uint_as_float(v[j]) * __ldg(wdot + idx);
+          atomicAdd(dw + idx, __uint_as_float(v[j]) * sc);
+        }
       } else if (t == 127 && db) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) atomicAdd(db + c0 + j, __uint_as_float(v[j]));
       }
     }
+  }
+  if (part) {
+    __shared__ float dsh[4];
+    dot = warp_sum(dot);
+    if ((t & 31) == 0) dsh[warp] = dot;
+    __syncthreads();
+    if (t == 0) part[blockIdx.x] = (dsh[0] + dsh[1]) + (dsh[2] + dsh[3]);
   }
   tc_fence_before();
   __syncthreads();
@@ -350,15 +365,15 @@ static int launch_first_fprop(const FirstIn& in, const float* w, const float* in
 }
 
 template <int CIN, bool INTERP>
-static int launch_first_wgrad(const FirstIn& in, const CUtensorMap& tmG, float* dw, float* db, int N, int H, int W,
-                              unsigned blocks, cudaStream_t st) {
+static int launch_first_wgrad(const FirstIn& in, const CUtensorMap& tmG, float* dw, float* db, const float* scale,
+                              const float* wdot, float* part, int N, int H, int W, unsigned blocks, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
     int rc = first_attr(first_wgrad_tc_kernel<CIN, INTERP>);
     if (rc) return rc;
     attr_done = true;
   }
-  first_wgrad_tc_kernel<CIN, INTERP><<<blocks, FT_THREADS, FT_SMEM, st>>>(in, tmG, dw, db, N, H, W);
+  first_wgrad_tc_kernel<CIN, INTERP><<<blocks, FT_THREADS, FT_SMEM, st>>>(in, tmG, dw, db, scale, wdot, part, N, H, W);
   return b2c_check_launch("first_wgrad");
 }
 
@@ -382,10 +397,14 @@ extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0
 }
 
 // dw: fp32 [64][Cin][4][4], db: fp32 [64] or null; both are ACCUMULATED into (caller zeroes).  gz: dense NHWC bf16.
+// scale (device scalar, nullable) multiplies what is added to dw (spectral norm: 1/sigma); wdot/part/nparts_host (nullable,
+// together): part[0..*nparts_host) <- per-CTA partials of <dW_unscaled, wdot> for b2c_sn_rank1 (room for 1024 floats).
 extern "C" int b2c_first_wgrad(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
-                               const void* gz, float* dw, float* db, int N, int H, int W, void* stream) {
+                               const void* gz, float* dw, float* db, const float* scale, const float* wdot, float* part,
+                               int* nparts_host, int N, int H, int W, void* stream) {
   int rc = first_check(a0, b0, alpha, N, H, W);
   if (rc) return rc;
+  B2C_REQUIRE((wdot == nullptr) == (part == nullptr), "first_wgrad: wdot and part go together");
   FirstIn in = make_in(a0, a1, b0, b1, alpha);
   const long long npix = (long long)N * (H / 2) * (W / 2);
   CUtensorMap tmG;
@@ -398,11 +417,12 @@ extern "C" int b2c_first_wgrad(const float* a0, const float* a1, const float* b0
   }
   long long blocks = (npix + 127) / 128;
   if (blocks > 148 * 4) blocks = 148 * 4;
+  if (nparts_host) *nparts_host = (int)blocks;
   cudaStream_t st = (cudaStream_t)stream;
   if (a1) {
-    if (alpha) return launch_first_wgrad<6, true>(in, tmG, dw, db, N, H, W, (unsigned)blocks, st);
-    return launch_first_wgrad<6, false>(in, tmG, dw, db, N, H, W, (unsigned)blocks, st);
+    if (alpha) return launch_first_wgrad<6, true>(in, tmG, dw, db, scale, wdot, part, N, H, W, (unsigned)blocks, st);
+    return launch_first_wgrad<6, false>(in, tmG, dw, db, scale, wdot, part, N, H, W, (unsigned)blocks, st);
   }
-  if (alpha) return launch_first_wgrad<3, true>(in, tmG, dw, db, N, H, W, (unsigned)blocks, st);
-  return launch_first_wgrad<3, false>(in, tmG, dw, db, N, H, W, (unsigned)blocks, st);
+  if (alpha) return launch_first_wgrad<3, true>(in, tmG, dw, db, scale, wdot, part, N, H, W, (unsigned)blocks, st);
+  return launch_first_wgrad<3, false>(in, tmG, dw, db, scale, wdot, part, N, H, W, (unsigned)blocks, st);
 }

@@ -25,7 +25,7 @@ int b2c_check_launch(const char* what) {
 }
 
 extern "C" const char* b2c_last_error(void) { return g_err; }
-extern "C" int b2c_abi_version(void) { return 1; }
+extern "C" int b2c_abi_version(void) { return 2; }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,

@@ -154,12 +154,53 @@ extern "C" int b2c_rowsum(const float* x, long long n, int B, int square, float 
   return b2c_check_launch("rowsum");
 }
 
-// Gradient penalty tail (losses.py:226-231): r_b = sqrt(ss_b + 1e-12); gp = mean((r_b-1)^2); coef_b = (2/B)(1-1/r_b)
-__global__ void gp_tail_kernel(const float* __restrict__ ss, float* __restrict__ gp, float* __restrict__ coef, int B) {
+// Per-sample sum of squares of the two input-gradient tensors (cgan/losses.py:223-226), stage 1: part[b][split], no atomics.
+__global__ void __launch_bounds__(256) gp_sumsq_kernel(const float* __restrict__ g0, const float* __restrict__ g1, long long n4,
+                                                        float* __restrict__ part) {
+  __shared__ float sh[8];
+  const float4* r0 = reinterpret_cast<const float4*>(g0) + (long long)blockIdx.y * n4;
+  const float4* r1 = g1 ? reinterpret_cast<const float4*>(g1) + (long long)blockIdx.y * n4 : nullptr;
+  float acc = 0.f;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    const float4 v = __ldg(r0 + i);
+    acc += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+    if (r1) {
+      const float4 w = __ldg(r1 + i);
+      acc += (w.x * w.x + w.y * w.y) + (w.z * w.z + w.w * w.w);
+    }
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += sh[w];
+    part[blockIdx.y * gridDim.x + blockIdx.x] = s;
+  }
+}
+// g0, g1 (nullable): [B][n] fp32, n % 4 == 0; part: [B][splits] with splits = *splits_host (<= 32; room for 32 * B floats).
+extern "C" int b2c_gp_sumsq(const float* g0, const float* g1, long long n, int B, float* part, int* splits_host, void* stream) {
+  B2C_REQUIRE(n % 4 == 0, "gp_sumsq: n=%lld must be a multiple of 4", n);
+  long long splits = (n / 4 + 4095) / 4096;
+  const long long cap = 1184 / (B > 0 ? B : 1) + 1;
+  if (splits > cap) splits = cap;
+  if (splits > 32) splits = 32;
+  if (splits < 1) splits = 1;
+  if (splits_host) *splits_host = (int)splits;
+  gp_sumsq_kernel<<<dim3((unsigned)splits, B), 256, 0, (cudaStream_t)stream>>>(g0, g1, n / 4, part);
+  return b2c_check_launch("gp_sumsq");
+}
+
+// Gradient penalty tail (losses.py:226-231): r_b = sqrt(ss_b + 1e-12); gp = mean((r_b-1)^2); coef_b = (2/B)(1-1/r_b);
+// ss_b = fixed-order sum of ss[b][0..splits).
+__global__ void gp_tail_kernel(const float* __restrict__ ss, int splits, float* __restrict__ gp, float* __restrict__ coef, int B) {
   __shared__ float sh[32];
   float acc = 0.f;
   for (int b = threadIdx.x; b < B; b += blockDim.x) {
-    const float r = sqrtf(ss[b] + 1e-12f);
+    float t = 0.f;
+    for (int s = 0; s < splits; ++s) t += ss[b * splits + s];
+    const float r = sqrtf(t + 1e-12f);
     acc += (r - 1.f) * (r - 1.f);
     coef[b] = (2.f / (float)B) * (1.f - 1.f / r);
   }
@@ -172,8 +213,8 @@ __global__ void gp_tail_kernel(const float* __restrict__ ss, float* __restrict__
     gp[0] = s / (float)B;
   }
 }
-extern "C" int b2c_gp_tail(const float* ss, float* gp, float* coef, int B, void* stream) {
-  gp_tail_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(ss, gp, coef, B);
+extern "C" int b2c_gp_tail(const float* ss, int splits, float* gp, float* coef, int B, void* stream) {
+  gp_tail_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(ss, splits, gp, coef, B);
   return b2c_check_launch("gp_tail");
 }
 
@@ -207,6 +248,76 @@ extern "C" int b2c_fill_scaled(float* out, long long n, const float* gscale, flo
   if (blocks > 592) blocks = 592;
   fill_scaled_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(out, n, gscale, value);
   return b2c_check_launch("fill_scaled");
+}
+
+// ---------------------------------------------------------------- Wasserstein terms (cgan/cgan_train_enhanced.py:327-328,362)
+__device__ __forceinline__ float block_sum_1024(float v, float* sh) {
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float r = 0.f;
+  if (threadIdx.x < 32) {
+    r = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
+    r = warp_sum(r);
+    if (threadIdx.x == 0) sh[0] = r;
+  }
+  __syncthreads();
+  r = sh[0];
+  __syncthreads();
+  return r;
+}
+// out[0] = scale * sum(x) (single block, fixed order: deterministic): torch.mean over a PatchGAN score map.
+__global__ void __launch_bounds__(1024) map_mean_kernel(const float* __restrict__ x, long long n, float scale, float* __restrict__ out) {
+  __shared__ float sh[32];
+  float acc = 0.f;
+  for (long long i = threadIdx.x; i < n; i += 1024) acc += __ldg(x + i);
+  const float t = block_sum_1024(acc, sh);
+  if (threadIdx.x == 0) out[0] = t * scale;
+}
+extern "C" int b2c_map_mean(const float* x, long long n, float scale, float* out, void* stream) {
+  map_mean_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(x, n, scale, out);
+  return b2c_check_launch("map_mean");
+}
+// The critic objective in one launch: wd = mean(real) - mean(fake); d_loss = -wd + lambda_gp * gp.  out[0..2] = (d_loss, wd, gp).
+__global__ void __launch_bounds__(1024) critic_loss_kernel(const float* __restrict__ real, long long n_real,
+                                                           const float* __restrict__ fake, long long n_fake,
+                                                           const float* __restrict__ gp, float lambda_gp, float* __restrict__ out) {
+  __shared__ float sh[32];
+  float a = 0.f, b = 0.f;
+  for (long long i = threadIdx.x; i < n_real; i += 1024) a += __ldg(real + i);
+  for (long long i = threadIdx.x; i < n_fake; i += 1024) b += __ldg(fake + i);
+  const float sr = block_sum_1024(a, sh), sf = block_sum_1024(b, sh);
+  if (threadIdx.x == 0) {
+    const float wd = sr / (float)n_real - sf / (float)n_fake, g = gp ? gp[0] : 0.f;
+    out[0] = -wd + lambda_gp * g; out[1] = wd; out[2] = g;
+  }
+}
+extern "C" int b2c_critic_loss(const float* real, long long n_real, const float* fake, long long n_fake, const float* gp,
+                               float lambda_gp, float* out3, void* stream) {
+  critic_loss_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(real, n_real, fake, n_fake, gp, lambda_gp, out3);
+  return b2c_check_launch("critic_loss");
+}
+// Its backward for the two score maps: g_real[i] = -(*gscale) / n_real, g_fake[i] = +(*gscale) / n_fake.
+__global__ void critic_loss_bwd_kernel(const float* __restrict__ gscale, float* __restrict__ g_real, long long n_real,
+                                       float* __restrict__ g_fake, long long n_fake) {
+  const float g = gscale ? *gscale : 1.f;
+  const float vr = -g / (float)n_real, vf = g / (float)n_fake;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_real + n_fake; i += (long long)gridDim.x * blockDim.x) {
+    if (i < n_real) g_real[i] = vr; else g_fake[i - n_real] = vf;
+  }
+}
+extern "C" int b2c_critic_loss_bwd(const float* gscale, float* g_real, long long n_real, float* g_fake, long long n_fake,
+                                   void* stream) {
+  long long blocks = (n_real + n_fake + 255) / 256;
+  if (blocks > 592) blocks = 592;
+  critic_loss_bwd_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(gscale, g_real, n_real, g_fake, n_fake);
+  return b2c_check_launch("critic_loss_bwd");
+}
+// cudaMemsetAsync through the C-ABI (gradient buckets are zeroed with one memset node instead of a fill kernel).
+extern "C" int b2c_zero(void* p, long long bytes, void* stream) {
+  cudaError_t e = cudaMemsetAsync(p, 0, (size_t)bytes, (cudaStream_t)stream);
+  if (e != cudaSuccess) { b2c_set_error("b2c_zero: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+  return B2C_OK;
 }
 
 // ---------------------------------------------------------------- G head: pooled -> Linear(C,4) -> tanh -> * scale

@@ -5,6 +5,7 @@
 // (128-bit loads, shared-memory + global fp32 atomics) or an elementwise apply (128-bit loads/stores).
 #include <cstdlib>
 #include "common.cuh"
+#include "tmap.h"
 
 using namespace b2c;
 
@@ -15,6 +16,8 @@ struct NormArgs {
   const __nv_bfloat16* h; long long ldh;   // cotangent on g_z (double backward)
   const uint8_t* mask;                     // dense dropout keep-mask [N*HW*C] or null
   const float* zs;                         // [N][C][2] raw (sum z, sum z^2)
+  const float* fsums;                      // gvec mode only, nullable: planar [2][N][C] (sum act(x_hat), sum act'(x_hat)) from
+                                           // b2c_in_act_pool_fwd: the backward's plane sums follow without a reduction pass
   float* sums;                             // [N][C][NS] plane sums produced by reduce / consumed by apply
   __nv_bfloat16* o0; long long ldo0;
   __nv_bfloat16* o1; long long ldo1;
@@ -23,7 +26,7 @@ struct NormArgs {
 };
 
 enum { M_FWD = 0, M_POOL = 1, M_BWD = 2, M_BWD2 = 3 };
-template <int MODE> struct NS { static constexpr int v = MODE == M_FWD ? 2 : MODE == M_POOL ? 1 : MODE == M_BWD ? 2 : 5; };
+template <int MODE> struct NS { static constexpr int v = MODE == M_FWD ? 2 : MODE == M_POOL ? 2 : MODE == M_BWD ? 2 : 5; };
 
 __device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
   const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
@@ -227,7 +230,10 @@ __global__ void __launch_bounds__(256, MODE == 3 ? 2 : 3) plane_reduce_kernel(No
       elem_make<MODE>(a, r, mean, rstd, gv, kscale, e);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        if (MODE == M_POOL) acc[0][i] += e.xh[i] > 0.f ? e.xh[i] : e.xh[i] * a.slope;
+        if (MODE == M_POOL) {  // sum act(x_hat) and sum act'(x_hat): the second one lets the backward skip its reduction
+          const float da = e.xh[i] > 0.f ? 1.f : a.slope;
+          acc[0][i] += e.xh[i] * da; acc[1][i] += da;
+        }
         if (MODE == M_BWD) { acc[0][i] += e.gn[i]; acc[1][i] += e.gn[i] * e.xh[i]; }
         if (MODE == M_BWD2) {
           acc[0][i] += e.hh[i]; acc[1][i] += e.hh[i] * e.xh[i]; acc[2][i] += e.gn[i];
@@ -249,7 +255,8 @@ __global__ void __launch_bounds__(256, MODE == 3 ? 2 : 3) plane_reduce_kernel(No
     const int s = i / a.C, c = i % a.C;
     float t = 0.f;
     for (int r = 0; r < rows; ++r) t += red[((long long)s * rows + r) * a.C + c];
-    atomicAdd(a.sums + ((long long)n * a.C + c) * ns + s, t);
+    if (MODE == M_POOL) atomicAdd(a.sums + ((long long)s * a.N + n) * a.C + c, t);  // planar [2][N][C]
+    else atomicAdd(a.sums + ((long long)n * a.C + c) * ns + s, t);
   }
 }
 
@@ -269,11 +276,20 @@ __global__ void __launch_bounds__(256, MODE == 3 ? 2 : 3) plane_apply_kernel(Nor
 #pragma unroll
       for (int i = 0; i < 8; ++i) gv[i] = __ldg(a.gvec + (long long)n * a.C + c0 + i);
     }
-    const float* s = a.sums + ((long long)n * a.C + c0) * ns;
+    if (MODE == M_BWD && a.fsums) {  // g = gv * act'(x_hat): sum g = gv * sum act', sum g x_hat = gv * sum act(x_hat)
+      const float* f = a.fsums + (long long)n * a.C + c0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < 8; ++i) {
+        sm[0][i] = gv[i] * __ldg(f + (long long)a.N * a.C + i) * inv;
+        sm[1 % ns][i] = gv[i] * __ldg(f + i) * inv;
+      }
+    } else {
+      const float* s = a.sums + ((long long)n * a.C + c0) * ns;
 #pragma unroll
-      for (int k = 0; k < ns; ++k) sm[k][i] = __ldg(s + i * ns + k) * inv;
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int k = 0; k < ns; ++k) sm[k][i] = __ldg(s + i * ns + k) * inv;
+    }
   }
   const float kscale = a.mask ? 2.f : 1.f;
   const int p_begin = (int)((long long)a.HW * blockIdx.x / gridDim.x), p_end = (int)((long long)a.HW * (blockIdx.x + 1) / gridDim.x);
@@ -408,6 +424,298 @@ __global__ void __launch_bounds__(256, 2) plane_fused_bwd_kernel(NormArgs a, int
   }
 }
 
+// ------------------------------------------------------------------------------------------------ cluster kernel
+// Single-launch InstanceNorm backward / backward-of-backward whose operands cross HBM ONCE.
+// A work unit is (image n, group of 64 channels = 128-byte rows); a thread-block CLUSTER of CS CTAs splits its HW pixels.
+// Per CTA: a producer warp streams [64 pixels x 64 channels] boxes of every operand with TMA (128B swizzle) through an
+// mbarrier ring; 256 consumer threads (8 channel vectors x 32 pixel rows) read them with conflict-free LDS.128.
+//   phase 1: plane sums in registers -> shuffle / shared-memory block reduction -> the CS partial vectors are exchanged
+//            through DISTRIBUTED SHARED MEMORY (every CTA sums its peers' partials in rank order: deterministic, identical
+//            on all CTAs, no global atomics, no memset) behind one cluster barrier;
+//   phase 2: the same boxes once more -> outputs.  If the CTA's slice fits the ring it is still RESIDENT in shared memory;
+//            otherwise the producer re-streams it, from L2 (the unit was read microseconds ago and all units in flight are
+//            a few tens of MB), and has the first boxes loaded before the cluster barrier completes.
+// Algorithmic bytes: bwd 3T (g, z in; gz out), bwd2 5T (h, g, z in; gg, gx out), T = N*HW*C*2 - what HBM actually moves.
+constexpr int CK_PIXB = 64;                       // pixels per box
+constexpr int CK_BOX_BYTES = CK_PIXB * 128;       // 8 KB per operand and stage
+constexpr int CK_THREADS = 288;                   // 8 consumer warps + 1 producer warp
+
+template <int MODE> struct CkCfg {
+  static constexpr int NT = MODE == M_BWD2 ? 3 : 2;      // operands streamed: z, g (, h)
+  static constexpr int NSUM = MODE == M_BWD2 ? 5 : 2;
+  static constexpr int STAGE_BYTES = NT * CK_BOX_BYTES;
+  static constexpr int AUX_BYTES = (NSUM * 8 * 64 + 2 * NSUM * 64) * 4 + 2 * 32 * 8;  // red + part + tot, barriers
+  static constexpr int smem(int stages) { return 1024 + stages * STAGE_BYTES + AUX_BYTES; }
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+__device__ __forceinline__ float ld_dsmem_f32(const float* local, uint32_t rank) {
+  uint32_t ra; float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(smem_u32(local)), "r"(rank));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+  return v;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(CK_THREADS) plane_cluster_kernel(const __grid_constant__ CUtensorMap tmZ,
+                                                                   const __grid_constant__ CUtensorMap tmG,
+                                                                   const __grid_constant__ CUtensorMap tmH, NormArgs a,
+                                                                   int CS, int nst, int RS) {
+  using Cfg = CkCfg<MODE>;
+  constexpr int NSUM = Cfg::NSUM;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* red = reinterpret_cast<float*>(ring + (size_t)RS * Cfg::STAGE_BYTES);  // [NSUM][8 warps][64]
+  float* part = red + NSUM * 8 * 64;                                            // [NSUM][64]: this CTA's partial sums
+  float* tot = part + NSUM * 64;                                                // [NSUM][64]: unit totals
+  uint64_t* full = reinterpret_cast<uint64_t*>(tot + NSUM * 64);
+  uint64_t* empty = full + 32;
+
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int rank = blockIdx.x % CS, cg = blockIdx.y, n = blockIdx.z;
+  const bool resident = nst <= RS;
+  const long long pix0 = (long long)n * a.HW + (long long)rank * nst * CK_PIXB;  // first pixel row of this CTA's slice
+
+  if (t == 0) {
+    tma_prefetch_desc(&tmZ);
+    tma_prefetch_desc(&tmG);
+    if (MODE == M_BWD2) tma_prefetch_desc(&tmH);
+    for (int s2 = 0; s2 < RS; ++s2) {
+      mbar_init(&full[s2], 1);
+      mbar_init(&empty[s2], 8);  // one arrival per consumer warp
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  if (warp == 8) {
+    // The producer joins the cluster barrier BETWEEN the two phases' loads: its phase-2 loads wait for ring slots that the
+    // consumers only free after that barrier, so it must have arrived before it blocks (and it never blocks before having
+    // the first RS boxes of phase 2 in flight).
+    auto issue = [&](int k) {
+      const int slot = k % RS;
+      if (k >= RS) mbar_wait(&empty[slot], ((k / RS) - 1) & 1);
+      mbar_expect_tx(&full[slot], Cfg::STAGE_BYTES);
+      uint8_t* dst = ring + (size_t)slot * Cfg::STAGE_BYTES;
+      const int row = (int)(pix0 + (long long)(k % nst) * CK_PIXB);
+      tma_load_2d(dst, &tmZ, &full[slot], cg * 64, row);
+      tma_load_2d(dst + CK_BOX_BYTES, &tmG, &full[slot], cg * 64, row);
+      if (MODE == M_BWD2) tma_load_2d(dst + 2 * CK_BOX_BYTES, &tmH, &full[slot], cg * 64, row);
+    };
+    if (elect_one())
+      for (int k = 0; k < nst; ++k) issue(k);
+    __syncwarp();
+    if (CS > 1) cluster_arrive();
+    if (!resident && elect_one())
+      for (int k = nst; k < 2 * nst; ++k) issue(k);
+    __syncwarp();
+    if (CS > 1) { cluster_wait(); cluster_arrive(); cluster_wait(); }
+    return;
+  } else {
+    const int cv = t & 7, prow = t >> 3;  // 8 channel vectors x 32 pixel rows
+    const int c0 = cg * 64 + cv * 8;
+    float mean[8], rstd[8], acc[NSUM][8];
+    load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
+#pragma unroll
+    for (int s2 = 0; s2 < NSUM; ++s2)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[s2][i] = 0.f;
+    const float slope = a.slope;
+    // ---- phase 1: plane sums
+    for (int k = 0; k < nst; ++k) {
+      const int slot = k % RS;
+      mbar_wait(&full[slot], (k / RS) & 1);
+      const uint8_t* st = ring + (size_t)slot * Cfg::STAGE_BYTES;
+#pragma unroll
+      for (int u = 0; u < CK_PIXB / 32; ++u) {
+        const int r = u * 32 + prow;
+        const int off = r * 128 + ((cv ^ (r & 7)) << 4);
+        float z[8], g[8];
+        cvt8(*reinterpret_cast<const uint4*>(st + off), z);
+        cvt8(*reinterpret_cast<const uint4*>(st + CK_BOX_BYTES + off), g);
+        if (MODE == M_BWD) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float xh = fmaf(z[i], rstd[i], mean[i]);
+            const float gn = xh > 0.f ? g[i] : g[i] * slope;
+            acc[0][i] += gn; acc[1][i] = fmaf(gn, xh, acc[1][i]);
+          }
+        } else {
+          float h[8];
+          cvt8(*reinterpret_cast<const uint4*>(st + 2 * CK_BOX_BYTES + off), h);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float xh = fmaf(z[i], rstd[i], mean[i]);
+            const float gn = xh > 0.f ? g[i] : g[i] * slope;
+            acc[0][i] += h[i]; acc[1][i] = fmaf(h[i], xh, acc[1][i]); acc[2 % NSUM][i] += gn;
+            acc[3 % NSUM][i] = fmaf(gn, xh, acc[3 % NSUM][i]); acc[4 % NSUM][i] = fmaf(h[i], gn, acc[4 % NSUM][i]);
+          }
+        }
+      }
+      if (!resident) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[slot]);
+      }
+    }
+    // block reduction: lanes with equal (lane & 7) hold the same channel vector
+#pragma unroll
+    for (int s2 = 0; s2 < NSUM; ++s2)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float v = acc[s2][i];
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        if (lane < 8) red[(s2 * 8 + warp) * 64 + cv * 8 + i] = v;
+      }
+    named_bar_sync(1, 256);
+    for (int i = t; i < NSUM * 64; i += 256) {
+      const int s2 = i >> 6, c = i & 63;
+      float v = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) v += red[(s2 * 8 + w) * 64 + c];
+      part[i] = v;
+    }
+  }
+  // ---- exchange the CS partial vectors through distributed shared memory (consumer warps only from here on)
+  if (CS > 1) {
+    cluster_arrive();
+    cluster_wait();
+  } else {
+    named_bar_sync(1, 256);
+  }
+  {
+    for (int i = t; i < NSUM * 64; i += 256) {
+      float v = 0.f;
+      if (CS > 1) {
+        for (int r = 0; r < CS; ++r) v += ld_dsmem_f32(part + i, (uint32_t)r);
+      } else {
+        v = part[i];
+      }
+      tot[i] = v;
+    }
+    named_bar_sync(1, 256);
+  }
+  if (CS > 1) cluster_arrive();  // peers may exit only after everyone has read their `part` (waited on before exit)
+  {
+    const int cv = t & 7, prow = t >> 3;
+    const int c0 = cg * 64 + cv * 8;
+    float mean[8], rstd[8], sm[NSUM][8];
+    load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
+    const float inv = 1.f / (float)a.HW, slope = a.slope;
+#pragma unroll
+    for (int s2 = 0; s2 < NSUM; ++s2)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) sm[s2][i] = tot[s2 * 64 + cv * 8 + i] * inv;
+    // ---- phase 2: outputs
+    for (int k = 0; k < nst; ++k) {
+      const int kk = resident ? k : nst + k;
+      const int slot = kk % RS;
+      if (!resident) mbar_wait(&full[slot], (kk / RS) & 1);
+      const uint8_t* st = ring + (size_t)slot * Cfg::STAGE_BYTES;
+#pragma unroll
+      for (int u = 0; u < CK_PIXB / 32; ++u) {
+        const int r = u * 32 + prow;
+        const int off = r * 128 + ((cv ^ (r & 7)) << 4);
+        const long long pix = pix0 + (long long)k * CK_PIXB + r;
+        float z[8], g[8];
+        cvt8(*reinterpret_cast<const uint4*>(st + off), z);
+        cvt8(*reinterpret_cast<const uint4*>(st + CK_BOX_BYTES + off), g);
+        if (MODE == M_BWD) {
+          float o[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float xh = fmaf(z[i], rstd[i], mean[i]);
+            const float gn = xh > 0.f ? g[i] : g[i] * slope;
+            o[i] = (gn - sm[0][i] - xh * sm[1][i]) * rstd[i];
+          }
+          store8(a.o0 + pix * a.ldo0 + c0, o);
+        } else {
+          float h[8], og[8], oz[8];
+          cvt8(*reinterpret_cast<const uint4*>(st + 2 * CK_BOX_BYTES + off), h);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float xh = fmaf(z[i], rstd[i], mean[i]);
+            const float da = xh > 0.f ? 1.f : slope;
+            const float gn = g[i] * da;
+            const float mh = sm[0][i], ma = sm[1][i], mg = sm[2 % NSUM][i], mc = sm[3 % NSUM][i], mhg = sm[4 % NSUM][i];
+            const float q = mhg - mh * mg - ma * mc;
+            const float Ph = h[i] - mh - xh * ma, Pg = gn - mg - xh * mc;
+            og[i] = Ph * rstd[i] * da;
+            oz[i] = -(q * xh + mc * Ph + ma * Pg) * rstd[i] * rstd[i];
+          }
+          store8(a.o0 + pix * a.ldo0 + c0, og);
+          store8(a.o1 + pix * a.ldo1 + c0, oz);
+        }
+      }
+      if (!resident) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[slot]);
+      }
+    }
+  }
+  if (CS > 1) cluster_wait();
+}
+
+// rank-2 map over an NHWC bf16 tensor seen as [N*HW pixel rows][C] with pixel stride ld; box = [CK_PIXB rows][64 channels].
+static int ck_tmap(CUtensorMap* tm, const void* base, long long ld, long long npix, int C) {
+  uint64_t dims[2] = {(uint64_t)C, (uint64_t)npix};
+  uint64_t str[1] = {(uint64_t)2 * ld};
+  uint32_t box[2] = {64, (uint32_t)CK_PIXB};
+  return b2c_make_tmap_bf16(tm, base, 2, dims, str, box);
+}
+
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && v[0]) ? atoi(v) : dflt;
+}
+
+// Returns 1 if the shape is not eligible (caller falls back to the two-pass kernels), 0 when launched, < 0 on error.
+template <int MODE>
+static int try_cluster(const NormArgs& a, cudaStream_t st) {
+  using Cfg = CkCfg<MODE>;
+  static const int enable = env_int("B2C_NORM_CLUSTER", 1);
+  if (!enable || a.mask || !a.g || a.C % 64 != 0 || a.HW % CK_PIXB != 0) return 1;
+  if ((reinterpret_cast<uintptr_t>(a.z) | reinterpret_cast<uintptr_t>(a.g) | reinterpret_cast<uintptr_t>(a.h)) & 15) return 1;
+  if (a.ldg % 8 || (MODE == M_BWD2 && a.ldh % 8)) return 1;
+  // cluster size: slices of <= 512 pixels, at most 8 CTAs (portable cluster size); ring: resident whenever the slice is <= 4 boxes
+  static const int cs_env = env_int("B2C_NORM_CS", 0), rs_env = env_int("B2C_NORM_RS", 0);
+  int CS = 1;
+  const int boxes = a.HW / CK_PIXB;
+  while (CS < 8 && boxes / CS > (MODE == M_BWD2 ? 4 : 4) && (boxes % (2 * CS)) == 0) CS *= 2;
+  if (cs_env > 0 && boxes % cs_env == 0 && cs_env <= 8) CS = cs_env;
+  const int nst = boxes / CS;
+  if (nst > 4 && nst * Cfg::NT > 24) return 1;  // streaming mode: the units in flight (~440/CS of them) must stay L2-resident
+  int RS = nst < 4 ? nst : 4;
+  if (rs_env > 0) RS = rs_env < nst ? rs_env : nst;
+  if (RS > 24) RS = 24;
+  const int smem = Cfg::smem(RS);
+  if (smem > 220 * 1024) return 1;
+  static int attr_smem = 0;
+  if (smem > attr_smem) {
+    cudaError_t e = cudaFuncSetAttribute(plane_cluster_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e != cudaSuccess) { b2c_set_error("plane_cluster attr: %s", cudaGetErrorString(e)); return -B2C_ERR_CUDA; }
+    attr_smem = 220 * 1024;
+  }
+  CUtensorMap tmZ, tmG, tmH;
+  const long long npix = (long long)a.N * a.HW;
+  if (ck_tmap(&tmZ, a.z, a.ldz, npix, a.C) || ck_tmap(&tmG, a.g, a.ldg, npix, a.C)) return -B2C_ERR_DRIVER;
+  if (MODE == M_BWD2) { if (ck_tmap(&tmH, a.h, a.ldh, npix, a.C)) return -B2C_ERR_DRIVER; } else tmH = tmZ;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(CS, a.C / 64, a.N);
+  cfg.blockDim = dim3(CK_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, plane_cluster_kernel<MODE>, tmZ, tmG, tmH, a, CS, nst, RS);
+  if (e != cudaSuccess) { b2c_set_error("plane_cluster launch: %s", cudaGetErrorString(e)); return -B2C_ERR_CUDA; }
+  return 0;
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 static int norm_check(const NormArgs& a, const char* who) {
   B2C_REQUIRE(a.C >= 64 && a.C <= 2048 && (a.C & (a.C - 1)) == 0, "%s: C=%d must be a power of two in [64,2048]", who, a.C);
@@ -471,7 +779,8 @@ extern "C" int b2c_in_act_fwd(const void* z, long long ldz, const float* zs, con
   if (int rc = norm_check(a, "in_act_fwd")) return rc;
   return launch_apply<M_FWD>(a, (cudaStream_t)stream);
 }
-// pooled_sums[N][C] <- sum over the plane of act(IN(z))   (global average pool numerator; models.py:118,139)
+// pooled_sums: planar [2][N][C] <- (sum over the plane of act(IN(z)), sum of act'(IN(z))): the global-average-pool numerator
+// (models.py:118,139) and what lets b2c_in_act_bwd(gvec, fwd_sums = pooled_sums) skip its reduction pass
 extern "C" int b2c_in_act_pool_fwd(const void* z, long long ldz, const float* zs, float slope, float* pooled_sums, int N,
                                    int HW, int C, void* stream) {
   NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
@@ -480,14 +789,23 @@ extern "C" int b2c_in_act_pool_fwd(const void* z, long long ldz, const float* zs
   return launch_reduce<M_POOL>(a, (cudaStream_t)stream);
 }
 // gz <- d/dz of dropout(act(IN(z))) given g (full tensor) or gvec (per-(n,c) broadcast).  ws: fp32 [N][C][2] scratch.
-extern "C" int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const void* z, long long ldz,
-                              const float* zs, const uint8_t* mask, float slope, float* ws, void* gz, long long ldgz,
-                              int N, int HW, int C, void* stream) {
+extern "C" int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const float* fwd_sums, const void* z,
+                              long long ldz, const float* zs, const uint8_t* mask, float slope, float* ws, void* gz,
+                              long long ldgz, int N, int HW, int C, void* stream) {
   NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
   a.g = (const __nv_bfloat16*)g; a.ldg = ldg; a.gvec = gvec; a.mask = mask; a.sums = ws;
   a.o0 = (__nv_bfloat16*)gz; a.ldo0 = ldgz;
   if (int rc = norm_check(a, "in_act_bwd")) return rc;
   B2C_REQUIRE((g != nullptr) != (gvec != nullptr), "in_act_bwd: exactly one of g / gvec");
+  B2C_REQUIRE(!fwd_sums || (gvec && !mask), "in_act_bwd: fwd_sums needs gvec mode without a dropout mask");
+  if (fwd_sums) {  // plane sums follow from the forward's (sum act, sum act'): one apply pass, 2T bytes
+    a.fsums = fwd_sums;
+    return launch_apply<M_BWD>(a, (cudaStream_t)stream);
+  }
+  {
+    const int rc = try_cluster<M_BWD>(a, (cudaStream_t)stream);
+    if (rc <= 0) return -rc;
+  }
   // small planes: one fused launch with the block's slice of the plane resident in shared memory
   static const bool fused_ok = !(getenv("B2C_NORM_FUSED") && getenv("B2C_NORM_FUSED")[0] == '0');
   if (fused_ok && HW >= 64 && HW <= 1024 && (HW & (HW - 1)) == 0) {
@@ -514,6 +832,10 @@ extern "C" int b2c_in_act_bwd2(const void* h, long long ldh, const void* g, long
   a.g = (const __nv_bfloat16*)g; a.ldg = ldg; a.h = (const __nv_bfloat16*)h; a.ldh = ldh; a.mask = mask; a.sums = ws;
   a.o0 = (__nv_bfloat16*)gg; a.ldo0 = ldgg; a.o1 = (__nv_bfloat16*)gx; a.ldo1 = ldgx;
   if (int rc = norm_check(a, "in_act_bwd2")) return rc;
+  {
+    const int rc = try_cluster<M_BWD2>(a, (cudaStream_t)stream);
+    if (rc <= 0) return -rc;
+  }
   if (int rc = launch_reduce<M_BWD2>(a, (cudaStream_t)stream)) return rc;
   return launch_apply<M_BWD2>(a, (cudaStream_t)stream);
 }
@@ -604,6 +926,25 @@ __global__ void dropout_mask_kernel(uint8_t* __restrict__ m, long long nvec, uin
     *reinterpret_cast<uint2*>(m + i * 8) = o;
   }
 }
+// out[i] = uniform [0,1) from the same counter-based stream (GP interpolation coefficients, cgan/losses.py:199): element i is
+// a pure function of (seed, offset + *offset_base + i), 24 random bits.
+__global__ void uniform_kernel(float* __restrict__ out, long long n, uint64_t seed, uint64_t offset,
+                               const long long* __restrict__ offset_base) {
+  if (offset_base) offset += (uint64_t)(*offset_base);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const uint32_t r = mix32((seed * 0x9E3779B97F4A7C15ULL) ^ (0xA5A5A5A5A5A5A5A5ULL + offset + (uint64_t)i));
+    out[i] = (float)(r >> 8) * (1.0f / 16777216.0f);
+  }
+}
+extern "C" int b2c_uniform(float* out, long long n, unsigned long long seed, unsigned long long offset,
+                           const long long* offset_base, void* stream) {
+  long long blocks = (n + 255) / 256;
+  if (blocks > 592) blocks = 592;
+  if (blocks < 1) blocks = 1;
+  uniform_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(out, n, seed, offset, offset_base);
+  return b2c_check_launch("uniform");
+}
+
 // Element i of the mask stream is a pure function of (seed, offset + *offset_base + i); offset_base (device, nullable)
 // lets a captured CUDA graph advance the stream between replays without re-recording the launch.
 extern "C" int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsigned long long offset,

@@ -178,3 +178,205 @@ extern "C" int b2c_sn_bwd(const float* dWe, const float* W, const float* u, cons
   sn_bwd_kernel<<<blocks, 256, 0, st>>>(dWe, u, v, sig, ws, blocks, dW, R, K, accumulate);
   return b2c_check_launch("sn_bwd");
 }
+
+// ------------------------------------------------------------------------------------------------ batched variants
+// All spectral-norm layers of one Discriminator forward in THREE launches (blockIdx.y = layer) instead of three per layer,
+// and the per-forward-instance snapshots of u / v (the backward of THAT forward needs them; torch clones the buffers at
+// spectral_norm.py:108-110) written by the same kernels instead of separate copies.
+#define B2C_SN_MAX_LAYERS 8
+struct SnLayer {
+  const float* W; float* u; float* v; float* sig; float* ws; float* u_snap; float* v_snap;
+  int R, K;
+};
+struct SnTable { SnLayer l[B2C_SN_MAX_LAYERS]; };
+
+__global__ void __launch_bounds__(512) sn_wtu_multi_kernel(SnTable tb) {
+  const SnLayer& L = tb.l[blockIdx.y];
+  const int R = L.R, K = L.K;
+  if ((int)blockIdx.x * SN_STRIP >= K) return;
+  __shared__ float red[16][33];
+  const float* __restrict__ W = L.W; const float* __restrict__ u = L.u;
+  float* t = L.ws; float* ssp = L.ws + K;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int k = blockIdx.x * SN_STRIP + lane;
+  float acc = 0.f;
+  if (k < K) {
+    int r = warp;
+    for (; r + 7 * 16 < R; r += 8 * 16) {
+      float w[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = __ldg(W + (long long)(r + 16 * j) * K + k);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc += w[j] * __ldg(u + r + 16 * j);
+    }
+    for (; r < R; r += 16) acc += __ldg(W + (long long)r * K + k) * __ldg(u + r);
+  }
+  red[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0) {
+    float tk = 0.f;
+#pragma unroll
+    for (int w = 0; w < 16; ++w) tk += red[w][lane];
+    if (k < K) t[k] = tk; else tk = 0.f;
+    const float ss = warp_sum(tk * tk);
+    if (lane == 0) ssp[blockIdx.x] = ss;
+  }
+}
+
+__global__ void __launch_bounds__(256) sn_wv_multi_kernel(SnTable tb, int update_v) {
+  const SnLayer& L = tb.l[blockIdx.y];
+  const int R = L.R, K = L.K;
+  const int r0 = blockIdx.x * SN_ROWS;
+  if (r0 >= R) return;
+  __shared__ float ts[SN_MAXK];
+  __shared__ float red[SN_ROWS][8];
+  const int NS = (K + SN_STRIP - 1) / SN_STRIP;
+  const float* __restrict__ W = L.W;
+  const float* t = L.ws; const float* ssp = L.ws + K; float* s = L.ws + K + NS;
+  if (update_v) {
+    float ss = 0.f;  // every warp derives the same value in the same order
+    for (int i = threadIdx.x & 31; i < NS; i += 32) ss += ssp[i];
+    ss = warp_sum(ss);
+    const float inv = 1.f / fmaxf(sqrtf(ss), 1e-12f);
+    for (int k = threadIdx.x; k < K; k += 256) {
+      const float vk = t[k] * inv;
+      ts[k] = vk;
+      if (blockIdx.x == 0) { L.v[k] = vk; if (L.v_snap) L.v_snap[k] = vk; }
+    }
+  } else {
+    for (int k = threadIdx.x; k < K; k += 256) {
+      const float vk = L.v[k];
+      ts[k] = vk;
+      if (blockIdx.x == 0 && L.v_snap) L.v_snap[k] = vk;
+    }
+  }
+  __syncthreads();
+  float acc[SN_ROWS];
+#pragma unroll
+  for (int j = 0; j < SN_ROWS; ++j) acc[j] = 0.f;
+  for (int k = threadIdx.x; k < K; k += 256) {
+    const float vk = ts[k];
+#pragma unroll
+    for (int j = 0; j < SN_ROWS; ++j)
+      if (r0 + j < R) acc[j] += __ldg(W + (long long)(r0 + j) * K + k) * vk;
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < SN_ROWS; ++j) {
+    const float w = warp_sum(acc[j]);
+    if (lane == 0) red[j][warp] = w;
+  }
+  __syncthreads();
+  if (threadIdx.x < SN_ROWS && r0 + threadIdx.x < R) {
+    float tt = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) tt += red[threadIdx.x][w];
+    s[r0 + threadIdx.x] = tt;
+  }
+}
+
+__global__ void __launch_bounds__(256) sn_finish_multi_kernel(SnTable tb, int update_u) {
+  const SnLayer& L = tb.l[blockIdx.x];
+  const int R = L.R, K = L.K;
+  const float* s = L.ws + K + (K + SN_STRIP - 1) / SN_STRIP;
+  __shared__ float sh[32];
+  float inv = 1.f;
+  if (update_u) {
+    float ss = 0.f;
+    for (int r = threadIdx.x; r < R; r += blockDim.x) ss += s[r] * s[r];
+    ss = block_sum(ss, sh);
+    inv = 1.f / fmaxf(sqrtf(ss), 1e-12f);
+  }
+  float acc = 0.f;
+  for (int r = threadIdx.x; r < R; r += blockDim.x) {
+    float ur;
+    if (update_u) { ur = s[r] * inv; L.u[r] = ur; } else ur = L.u[r];
+    if (L.u_snap) L.u_snap[r] = ur;
+    acc += ur * s[r];
+  }
+  const float sigma = block_sum(acc, sh);
+  if (threadIdx.x == 0) { L.sig[0] = sigma; L.sig[1] = 1.f / sigma; }
+}
+
+// count <= 8 layers; per layer: W [R][K], u [R], v [K] (updated in place when train != 0), sig [2] <- (sigma, 1/sigma),
+// ws: K + ceil(K/32) + R floats of scratch, u_snap [R] / v_snap [K] (nullable) <- the u / v this forward used.
+extern "C" int b2c_sn_power_iter_multi(const float* const* W, float* const* u, float* const* v, float* const* sig,
+                                       float* const* ws, float* const* u_snap, float* const* v_snap, const int* R,
+                                       const int* K, int count, int train, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  B2C_REQUIRE(count >= 1 && count <= B2C_SN_MAX_LAYERS, "sn_power_iter_multi: %d layers (max %d)", count, B2C_SN_MAX_LAYERS);
+  SnTable tb;
+  int maxK = 0, maxR = 0;
+  for (int i = 0; i < count; ++i) {
+    B2C_REQUIRE(K[i] <= SN_MAXK, "sn_power_iter_multi: K=%d exceeds %d", K[i], SN_MAXK);
+    tb.l[i].W = W[i]; tb.l[i].u = u[i]; tb.l[i].v = v[i]; tb.l[i].sig = sig[i]; tb.l[i].ws = ws[i];
+    tb.l[i].u_snap = u_snap ? u_snap[i] : nullptr; tb.l[i].v_snap = v_snap ? v_snap[i] : nullptr;
+    tb.l[i].R = R[i]; tb.l[i].K = K[i];
+    if (K[i] > maxK) maxK = K[i];
+    if (R[i] > maxR) maxR = R[i];
+  }
+  if (train) sn_wtu_multi_kernel<<<dim3((maxK + SN_STRIP - 1) / SN_STRIP, count), 512, 0, st>>>(tb);
+  sn_wv_multi_kernel<<<dim3((maxR + SN_ROWS - 1) / SN_ROWS, count), 256, 0, st>>>(tb, train ? 1 : 0);
+  sn_finish_multi_kernel<<<count, 256, 0, st>>>(tb, train ? 1 : 0);
+  return b2c_check_launch("sn_power_iter_multi");
+}
+
+// Deferred rank-1 term of the spectral-norm backward.  The weight-gradient kernels accumulate dWe / sigma_i straight into
+// the gradient of weight_orig and leave block partials of <dWe, W> (b2c_wgrad4s2_bf16 / b2c_first_wgrad: `part`); once per
+// backward this kernel subtracts, for every layer, sum_i (<dWe_i, W> / sigma_i^2) u_i v_i^T over the forward instances i
+// (real / fake / interpolated critic passes each carry their own u, v, sigma): dW = (dWe - <dWe, We> u v^T) / sigma.
+#define B2C_SN_MAX_INST 8
+struct SnR1Inst { const float* u; const float* v; const float* sig; const float* part; int nparts; };
+struct SnR1Layer { float* grad; int R, K, ninst; SnR1Inst inst[B2C_SN_MAX_INST]; };
+struct SnR1Table { SnR1Layer l[B2C_SN_MAX_LAYERS]; };
+
+__global__ void __launch_bounds__(256) sn_rank1_kernel(SnR1Table tb) {
+  const SnR1Layer& L = tb.l[blockIdx.y];
+  float coef[B2C_SN_MAX_INST];
+#pragma unroll
+  for (int j = 0; j < B2C_SN_MAX_INST; ++j) {
+    coef[j] = 0.f;
+    if (j < L.ninst) {
+      float dot = 0.f;  // every warp derives the same value in the same order
+      for (int i = threadIdx.x & 31; i < L.inst[j].nparts; i += 32) dot += __ldg(L.inst[j].part + i);
+      dot = warp_sum(dot);
+      const float inv = __ldg(L.inst[j].sig + 1);
+      coef[j] = dot * inv * inv;
+    }
+  }
+  const long long n = (long long)L.R * L.K;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(i / L.K), k = (int)(i % L.K);
+    float corr = 0.f;
+#pragma unroll
+    for (int j = 0; j < B2C_SN_MAX_INST; ++j)
+      if (j < L.ninst) corr += coef[j] * __ldg(L.inst[j].u + r) * __ldg(L.inst[j].v + k);
+    L.grad[i] -= corr;
+  }
+}
+
+// nlayers <= 8 gradient tensors grad[l] ([R][K] fp32, updated in place); their ninst[l] <= 8 instances are given as flat
+// arrays in layer order: u [R], v [K], sig [2] = (sigma, 1/sigma), part [nparts] (block partials of <dWe, W>).
+extern "C" int b2c_sn_rank1(float* const* grad, const int* R, const int* K, const int* ninst, int nlayers,
+                            const float* const* u, const float* const* v, const float* const* sig,
+                            const float* const* part, const int* nparts, void* stream) {
+  B2C_REQUIRE(nlayers >= 1 && nlayers <= B2C_SN_MAX_LAYERS, "sn_rank1: %d layers (max %d)", nlayers, B2C_SN_MAX_LAYERS);
+  SnR1Table tb;
+  int k = 0;
+  long long maxn = 0;
+  for (int l = 0; l < nlayers; ++l) {
+    B2C_REQUIRE(ninst[l] >= 0 && ninst[l] <= B2C_SN_MAX_INST, "sn_rank1: %d instances (max %d)", ninst[l], B2C_SN_MAX_INST);
+    tb.l[l].grad = grad[l]; tb.l[l].R = R[l]; tb.l[l].K = K[l]; tb.l[l].ninst = ninst[l];
+    for (int j = 0; j < ninst[l]; ++j, ++k) {
+      tb.l[l].inst[j].u = u[k]; tb.l[l].inst[j].v = v[k]; tb.l[l].inst[j].sig = sig[k];
+      tb.l[l].inst[j].part = part[k]; tb.l[l].inst[j].nparts = nparts[k];
+    }
+    const long long n = (long long)R[l] * K[l];
+    if (n > maxn) maxn = n;
+  }
+  long long blocks = (maxn + 1023) / 1024;
+  if (blocks > 592) blocks = 592;
+  if (blocks < 1) blocks = 1;
+  sn_rank1_kernel<<<dim3((unsigned)blocks, nlayers), 256, 0, (cudaStream_t)stream>>>(tb);
+  return b2c_check_launch("sn_rank1");
+}

@@ -29,6 +29,7 @@ struct TapGemmParams {
   __nv_bfloat16* y;
   long long ldy;            // output pixel stride in elements
   const float* bias;        // nullable, per output channel
+  const float* scale;       // nullable device scalar: y = acc * scale + bias (spectral norm: 1/sigma, W_eff = W/sigma)
   float* gx0;               // mode D1: fp32 (N,3,2Ho,2Wo) outputs (gx1 null when Cin = 3)
   float* gx1;
   float* stats;             // nullable: [N][Cout][2] += per-(image, channel) (sum, sum of squares) of y; needs BI == 1
@@ -179,6 +180,11 @@ __global__ void __launch_bounds__(64 + 128 * MT) tapgemm_kernel(const __grid_con
       for (int j = 0; j < 16; ++j) {
         f[j] = __uint_as_float(v0[j]);
         f[16 + j] = __uint_as_float(v1[j]);
+      }
+      if (p.scale) {
+        const float sc = __ldg(p.scale);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] *= sc;
       }
       if (p.bias) {
 #pragma unroll
@@ -377,6 +383,11 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
           f[j] = __uint_as_float(v0[j]);
           f[16 + j] = __uint_as_float(v1[j]);
         }
+        if (p.scale) {
+          const float sc = __ldg(p.scale);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] *= sc;
+        }
         if (p.bias) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] += __ldg(p.bias + ncol0 + c0 + j);
@@ -469,13 +480,13 @@ extern "C" int b2c_set_f32_output(int on, void* /*stream: unused, uniform call s
   return B2C_OK;
 }
 
-static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack, const float* bias, void* y,
+static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack, const float* scale, const float* bias, void* y,
                        long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
   B2C_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "tapgemm: Cin=%d Cout=%d must be multiples of 64", Cin, Cout);
   B2C_REQUIRE(ldy % 8 == 0 && ((uintptr_t)y & 15) == 0, "tapgemm: output must be 16-byte aligned (ldy=%lld)", ldy);
   TapGemmParams p;
   p.mode = mode; p.N = N; p.Cin = Cin; p.Cout = Cout; p.kchunks = Cin / 64;
-  p.y = (__nv_bfloat16*)y; p.ldy = ldy; p.bias = bias; p.gx0 = p.gx1 = nullptr; p.stats = nullptr;
+  p.y = (__nv_bfloat16*)y; p.ldy = ldy; p.bias = bias; p.scale = scale; p.gx0 = p.gx1 = nullptr; p.stats = nullptr;
   p.st256 = (((uintptr_t)y & 31) == 0 && ldy % 16 == 0) ? 1 : 0;
   p.f32out = g_f32_output;
   int TH, TW;
@@ -583,7 +594,7 @@ extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_
   B2C_REQUIRE(ws && ((uintptr_t)ws & 15) == 0, "first_dgrad: workspace missing or unaligned");
   TapGemmParams p;
   p.mode = 2; p.N = N; p.Cin = 64; p.Cout = 32; p.kchunks = 1;
-  p.y = nullptr; p.ldy = 0; p.bias = nullptr; p.gx0 = gx0; p.gx1 = gx1; p.stats = nullptr; p.f32out = 0; p.st256 = 0;
+  p.y = nullptr; p.ldy = 0; p.bias = nullptr; p.scale = nullptr; p.gx0 = gx0; p.gx1 = gx1; p.stats = nullptr; p.f32out = 0; p.st256 = 0;
   p.Ho = H / 2; p.Wo = W / 2;
   B2C_REQUIRE(pick_box(p.Ho, p.Wo, 128, &p.BW, &p.BH, &p.BI), "first_dgrad: unsupported spatial size %dx%d", H, W);
   p.tiles_x = p.Wo / p.BW; p.tiles_y = p.Ho / p.BH;
@@ -608,22 +619,22 @@ extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_
   return launch_tapgemm<32>(tmA, tmB, p, grid, st);
 }
 
-extern "C" int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* bias, void* y,
-                                long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
-  return run_tapgemm(0, x, ldx, wpack_c, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
+extern "C" int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* scale, const float* bias,
+                                void* y, long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
+  return run_tapgemm(0, x, ldx, wpack_c, scale, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
 }
 
-int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, void* y, long long ldy, float* stats,
-                    const void* act, float slope, int N, int H, int W, int Cin, void* stream);  // convt64.cu
+int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const float* scale, void* y, long long ldy,
+                    float* stats, const void* act, float slope, int N, int H, int W, int Cin, void* stream);  // convt64.cu
 
-extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y,
-                                 long long ldy, float* stats, const void* act, float slope, int N, int H, int W, int Cin,
-                                 int Cout, void* stream) {
+extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* scale, const float* bias,
+                                 void* y, long long ldy, float* stats, const void* act, float slope, int N, int H, int W,
+                                 int Cin, int Cout, void* stream) {
   static const bool merge = !(getenv("B2C_CONVT_MERGE") && getenv("B2C_CONVT_MERGE")[0] == '0');  // A/B switch for profiling
   if (g_f32_output) B2C_REQUIRE(stats == nullptr, "fp32 check mode: fused statistics are not available");
   if (Cout == 64 && bias == nullptr && merge && Cin % 64 == 0 && ldx % 8 == 0 && ldy % 8 == 0 &&
       ((uintptr_t)y & 15) == 0 && is_pow2(H) && is_pow2(W))
-    return b2c_run_convt64(x, ldx, wpack_t, y, ldy, stats, act, slope, N, H, W, Cin, stream);
+    return b2c_run_convt64(x, ldx, wpack_t, scale, y, ldy, stats, act, slope, N, H, W, Cin, stream);
   B2C_REQUIRE(act == nullptr, "convt4s2: the fused LeakyReLU backward needs the Cout = 64 kernel (Cout=%d, bias=%p)", Cout, (const void*)bias);
-  return run_tapgemm(1, x, ldx, wpack_t, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
+  return run_tapgemm(1, x, ldx, wpack_t, scale, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
 }

@@ -23,7 +23,9 @@ struct WgradParams {
   int tiles_x, tiles_y;    // box grid over (Hs, Ws)
   int nchunks;             // total pixel chunks
   int mtiles, ntiles;      // Cs/128, Cl/NB
-  float* ws;               // [16][Cs][Cl]
+  float* ws;               // [16][Cs][Cl] (atomic mode) or [splits][16][Cs][Cl] (deterministic mode)
+  long long slab;          // 0: split-K partials are reduced with fp32 vector atomics into one slab (ws zeroed by the host);
+                           // else: floats per slab, split s stores its partial tile into slab s (no atomics, no memset)
 };
 
 template <int NB>
@@ -135,7 +137,7 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
       tc_fence_after();
 #pragma unroll 1
       for (int tt = ((warp - 2) >> 2) * (TPC / 2); tt < (((warp - 2) >> 2) + 1) * (TPC / 2); ++tt) {  // 2 warps per lane quarter
-        float* dst = p.ws + ((long long)(tap0 + tt) * p.Cs + a) * p.Cl + b0;
+        float* dst = p.ws + (long long)blockIdx.y * p.slab + ((long long)(tap0 + tt) * p.Cs + a) * p.Cl + b0;
 #pragma unroll 1
         for (int c0 = 0; c0 < NB; c0 += 16) {
           uint32_t v[16];
@@ -145,7 +147,8 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
           for (int j = 0; j < 4; ++j) {
             float4 f = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
                                    __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-            atomicAdd(reinterpret_cast<float4*>(dst + c0 + 4 * j), f);
+            if (p.slab) *reinterpret_cast<float4*>(dst + c0 + 4 * j) = f;
+            else atomicAdd(reinterpret_cast<float4*>(dst + c0 + 4 * j), f);
           }
         }
       }
@@ -156,19 +159,50 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
   if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
-// ws[tap][a][b] -> dw[a][b][ky][kx] (torch weight layout), optionally accumulating.
-__global__ void wgrad_unpack_kernel(const float* __restrict__ ws, float* __restrict__ dw, int Cs, int Cl, int accumulate) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // over Cs*Cl
-  if (i >= (long long)Cs * Cl) return;
-  float v[16];
+// ws[split][tap][a][b] -> dw[a][b][ky][kx] (torch weight layout): fixed-order sum over the split-K slabs, optional
+// device-scalar scale (spectral norm: dW_orig gets dWe / sigma), optional accumulation into dw, and optionally the block
+// partials of <dWe, wdot> (unscaled; wdot in dw's layout) for the deferred rank-1 term of the spectral-norm backward
+// (b2c_sn_rank1): part[blockIdx.x], summed later in a fixed order - no atomics anywhere.
+__global__ void __launch_bounds__(256) wgrad_unpack_kernel(const float* __restrict__ ws, long long slab, int nslabs,
+                                                           float* __restrict__ dw, int Cs, int Cl, int accumulate,
+                                                           const float* __restrict__ scale, const float* __restrict__ wdot,
+                                                           float* __restrict__ part) {
+  __shared__ float sh[8];
+  const long long n = (long long)Cs * Cl;
+  const float sc = scale ? __ldg(scale) : 1.f;
+  float dot = 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    float v[16];
 #pragma unroll
-  for (int t = 0; t < 16; ++t) v[t] = ws[(long long)t * Cs * Cl + i];
-  float4* o = reinterpret_cast<float4*>(dw + i * 16);
+    for (int t = 0; t < 16; ++t) v[t] = ws[(long long)t * n + i];
+    for (int sl = 1; sl < nslabs; ++sl) {
+      const float* w2 = ws + (long long)sl * slab;
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    float4 f = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-    if (accumulate) { float4 g = o[j]; f.x += g.x; f.y += g.y; f.z += g.z; f.w += g.w; }
-    o[j] = f;
+      for (int t = 0; t < 16; ++t) v[t] += w2[(long long)t * n + i];
+    }
+    float4* o = reinterpret_cast<float4*>(dw + i * 16);
+    const float4* wd = reinterpret_cast<const float4*>(wdot + i * 16);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (wdot) {
+        const float4 w4 = __ldg(wd + j);
+        dot += v[4 * j] * w4.x + v[4 * j + 1] * w4.y + v[4 * j + 2] * w4.z + v[4 * j + 3] * w4.w;
+      }
+      float4 f = make_float4(v[4 * j] * sc, v[4 * j + 1] * sc, v[4 * j + 2] * sc, v[4 * j + 3] * sc);
+      if (accumulate) { float4 g = o[j]; f.x += g.x; f.y += g.y; f.z += g.z; f.w += g.w; }
+      o[j] = f;
+    }
+  }
+  if (part) {
+    dot = warp_sum(dot);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = dot;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += sh[w];
+      part[blockIdx.x] = t;
+    }
   }
 }
 
@@ -190,26 +224,65 @@ static int launch_wgrad(const CUtensorMap& tmS, const CUtensorMap& tmL, const Wg
   return b2c_check_launch("wgrad_kernel");
 }
 
-// small: (N,Hs,Ws,Cs) bf16 with pixel stride lds; large: dense (N,2Hs,2Ws,Cl) bf16; ws: fp32 [16][Cs][Cl] workspace
-// (zeroed here); dw: fp32 [Cs][Cl][4][4].  sm_count sizes the split-K factor.
+struct WgradPlan { int BW, BH, BI, tiles_x, tiles_y, nchunks, NB, tiles, splits; };
+static WgradPlan wgrad_plan(int N, int Hs, int Ws, int Cs, int Cl, int sm_count) {
+  WgradPlan q;
+  q.BW = Ws < 32 ? Ws : 32;
+  int rem = 32 / q.BW;
+  q.BH = Hs < rem ? Hs : rem;
+  q.BI = rem / q.BH;
+  q.tiles_x = Ws / q.BW; q.tiles_y = Hs / q.BH;
+  const int tiles_n = (N + q.BI - 1) / q.BI;
+  q.nchunks = q.tiles_x * q.tiles_y * tiles_n;
+  q.NB = (Cl % 128 == 0) ? 128 : 64;
+  // One CTA per SM (it owns all 512 TMEM columns).  Pick the split-K factor by a small cost model: waves of CTAs times
+  // (pixel chunks per CTA + a fixed prologue/epilogue cost of about 12 chunk-times).
+  q.tiles = (16 / (512 / q.NB)) * (Cs / 128) * (Cl / q.NB);
+  const int sms = sm_count > 0 ? sm_count : 148;
+  int splits = 1;
+  double best = 1e30;
+  for (int s = 1; s <= 2 * sms && s <= q.nchunks; ++s) {
+    const int waves = (q.tiles * s + sms - 1) / sms;
+    const double cost = waves * ((double)((q.nchunks + s - 1) / s) + 12.0);
+    if (cost < best - 1e-9) { best = cost; splits = s; }
+  }
+  if (splits > q.nchunks) splits = q.nchunks;
+  if (splits < 1) splits = 1;
+  q.splits = splits;
+  return q;
+}
+
+// Workspace (in floats) that makes b2c_wgrad4s2_bf16 deterministic for this shape: one [16][Cs][Cl] slab per split-K
+// partition.  With less (but >= 16*Cs*Cl) the partitions are reduced with fp32 atomics instead (run-to-run rounding noise).
+extern "C" long long b2c_wgrad4s2_ws_floats(int N, int Hs, int Ws, int Cs, int Cl, int sm_count) {
+  if (Hs <= 0 || Ws <= 0 || Cs <= 0 || Cl <= 0 || N <= 0) return 0;
+  const WgradPlan q = wgrad_plan(N, Hs, Ws, Cs, Cl, sm_count);
+  return (long long)q.splits * 16 * Cs * Cl;
+}
+
+// small: (N,Hs,Ws,Cs) bf16 with pixel stride lds; large: dense (N,2Hs,2Ws,Cl) bf16; ws: fp32 workspace of ws_floats
+// floats (see b2c_wgrad4s2_ws_floats); dw: fp32 [Cs][Cl][4][4], overwritten or (accumulate) added to, times *scale
+// (device scalar, nullable).  wdot/part/nparts_host (all nullable): part[0..*nparts_host) receive block partials of
+// <dW_unscaled, wdot> (spectral-norm backward, see b2c_sn_rank1); part needs room for 1024 floats.
+// sm_count sizes the split-K factor.
 extern "C" int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* large, long long ldl, float* ws,
-                                 float* dw, int accumulate, int N, int Hs, int Ws, int Cs, int Cl, int sm_count,
+                                 long long ws_floats, float* dw, int accumulate, const float* scale, const float* wdot,
+                                 float* part, int* nparts_host, int N, int Hs, int Ws, int Cs, int Cl, int sm_count,
                                  void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   B2C_REQUIRE(Cs % 128 == 0 && Cl % 64 == 0, "wgrad4s2: Cs=%d must be a multiple of 128, Cl=%d of 64", Cs, Cl);
   B2C_REQUIRE(ldl == Cl, "wgrad4s2: large operand must be dense NHWC (ldl=%lld, Cl=%d)", ldl, Cl);
   B2C_REQUIRE(lds % 8 == 0, "wgrad4s2: lds=%lld must be a multiple of 8", lds);
   B2C_REQUIRE(w_is_pow2(Hs) && w_is_pow2(Ws), "wgrad4s2: unsupported spatial size %dx%d", Hs, Ws);
+  B2C_REQUIRE((wdot == nullptr) == (part == nullptr), "wgrad4s2: wdot and part go together");
+  const WgradPlan q = wgrad_plan(N, Hs, Ws, Cs, Cl, sm_count);
+  const long long slab = (long long)16 * Cs * Cl;
+  B2C_REQUIRE(ws_floats >= slab, "wgrad4s2: workspace of %lld floats < %lld", ws_floats, slab);
+  const bool det = ws_floats >= slab * q.splits;
   WgradParams p;
-  p.N = N; p.Cs = Cs; p.Cl = Cl; p.ws = ws;
-  p.BW = Ws < 32 ? Ws : 32;
-  int rem = 32 / p.BW;
-  p.BH = Hs < rem ? Hs : rem;
-  p.BI = rem / p.BH;
-  p.tiles_x = Ws / p.BW; p.tiles_y = Hs / p.BH;
-  const int tiles_n = (N + p.BI - 1) / p.BI;
-  p.nchunks = p.tiles_x * p.tiles_y * tiles_n;
-  const int NB = (Cl % 128 == 0) ? 128 : 64;
+  p.N = N; p.Cs = Cs; p.Cl = Cl; p.ws = ws; p.slab = det ? slab : 0;
+  p.BW = q.BW; p.BH = q.BH; p.BI = q.BI; p.tiles_x = q.tiles_x; p.tiles_y = q.tiles_y; p.nchunks = q.nchunks;
+  const int NB = q.NB;
   p.mtiles = Cs / 128; p.ntiles = Cl / NB;
   CUtensorMap tmS, tmL;
   {
@@ -227,30 +300,20 @@ extern "C" int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* l
     int rc = b2c_make_tmap_bf16(&tmL, large, 5, dims, str, box);
     if (rc) return rc;
   }
-  // One CTA per SM (it owns all 512 TMEM columns).  Pick the split-K factor by a small cost model: waves of CTAs times
-  // (pixel chunks per CTA + a fixed prologue/epilogue cost of about 12 chunk-times).
-  const int tiles = (16 / (512 / NB)) * p.mtiles * p.ntiles;
-  const int sms = sm_count > 0 ? sm_count : 148;
-  int splits = 1;
-  {
-    double best = 1e30;
-    for (int s = 1; s <= 2 * sms && s <= p.nchunks; ++s) {
-      const int waves = (tiles * s + sms - 1) / sms;
-      const double cost = waves * ((double)((p.nchunks + s - 1) / s) + 12.0);
-      if (cost < best - 1e-9) { best = cost; splits = s; }
+  if (!det) {
+    cudaError_t e = cudaMemsetAsync(ws, 0, sizeof(float) * (size_t)slab, st);
+    if (e != cudaSuccess) {
+      b2c_set_error("wgrad4s2 memset: %s", cudaGetErrorString(e));
+      return B2C_ERR_CUDA;
     }
   }
-  if (splits > p.nchunks) splits = p.nchunks;
-  if (splits < 1) splits = 1;
-  cudaError_t e = cudaMemsetAsync(ws, 0, sizeof(float) * 16 * (size_t)Cs * Cl, st);
-  if (e != cudaSuccess) {
-    b2c_set_error("wgrad4s2 memset: %s", cudaGetErrorString(e));
-    return B2C_ERR_CUDA;
-  }
-  dim3 grid(tiles, splits);
+  dim3 grid(q.tiles, q.splits);
   int rc = NB == 128 ? launch_wgrad<128>(tmS, tmL, p, grid, st) : launch_wgrad<64>(tmS, tmL, p, grid, st);
   if (rc) return rc;
   const long long n = (long long)Cs * Cl;
-  wgrad_unpack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(ws, dw, Cs, Cl, accumulate);
+  long long blocks = (n + 255) / 256;
+  if (blocks > 1024) blocks = 1024;
+  if (nparts_host) *nparts_host = (int)blocks;
+  wgrad_unpack_kernel<<<(unsigned)blocks, 256, 0, st>>>(ws, slab, det ? q.splits : 1, dw, Cs, Cl, accumulate, scale, wdot, part);
   return b2c_check_launch("wgrad_unpack_kernel");
 }

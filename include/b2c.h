@@ -14,9 +14,12 @@ extern "C" {
 #endif
 
 const char* b2c_last_error(void);
-int b2c_abi_version(void);
+int b2c_abi_version(void); /* 2: epilogue scale, deterministic split-K / statistics reductions, batched spectral norm, flat Adam */
+int b2c_zero(void* p, long long bytes, void* stream); /* cudaMemsetAsync: gradient buckets (optimizer.zero_grad, cgan_train_enhanced.py:305,346) */
 
-/* ---- weight packing (+ spectral-norm 1/sigma; torch spectral_norm.py:111-112 via cgan/models.py:238) ---- */
+/* ---- weight packing: fp32 master weights -> bf16 tensor-core operands.  inv_sigma (nullable) folds the spectral-norm
+ * 1/sigma in (torch spectral_norm.py:111-112 via cgan/models.py:238); the train step passes NULL here, packs once per
+ * optimizer step and applies 1/sigma as the `scale` of the GEMM epilogues instead ---- */
 int b2c_pack_w_c(const float* w, const float* inv_sigma, void* out_bf16, int D0, int D1, void* stream);
 int b2c_pack_w_t(const float* w, const float* inv_sigma, void* out_bf16, int D0, int D1, void* stream);
 
@@ -27,17 +30,27 @@ int b2c_pack_w_t(const float* w, const float* inv_sigma, void* out_bf16, int D0,
  * stats (nullable, fp32 [N][Cout][2]) <- per-(image, channel) (sum, sum of squares) of the bf16 output, i.e. what
  * b2c_in_stats computes: the InstanceNorm2d that follows every such conv (cgan/models.py:59,73,114,241) gets its
  * statistics from the GEMM epilogue instead of re-reading the tensor. */
-int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* bias, void* y, long long ldy,
-                     float* stats, int N, int H, int W, int Cin, int Cout, void* stream);
-int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* bias, void* y, long long ldy,
-                      float* stats, const void* act, float slope, int N, int H, int W, int Cin, int Cout, void* stream);
+/* scale (nullable device scalar): y = acc * scale + bias, i.e. W_eff = W * scale: the spectral-norm 1/sigma of THIS forward
+ * instance without re-packing the weights. */
+int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* scale, const float* bias, void* y,
+                     long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream);
+int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* scale, const float* bias, void* y,
+                      long long ldy, float* stats, const void* act, float slope, int N, int H, int W, int Cin, int Cout,
+                      void* stream);
 /* act (nullable, Cout = 64 only): dense bf16 (N,2H,2W,64) output of the LeakyReLU(slope) that feeds the conv whose data
  * gradient this call computes; y is multiplied by (act > 0 ? 1 : slope), i.e. LeakyReLU's backward (cgan/models.py:60,245)
  * is fused into the dgrad epilogue instead of a separate full-tensor pass. */
 int b2c_set_f32_output(int on, void* stream); /* fp32 CHECK MODE for the two entry points above: while on, `y` is float*
                                                * (ldy in floats) and receives the unrounded fp32 accumulators; tests only */
-int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* large, long long ldl, float* ws, float* dw,
-                      int accumulate, int N, int Hs, int Ws, int Cs, int Cl, int sm_count, void* stream);
+/* wgrad4s2: dw[Cs][Cl][4][4] (=|+=) scale * sum_pix small (x) large.  ws: fp32 workspace of ws_floats floats; with
+ * b2c_wgrad4s2_ws_floats(...) floats the split-K partials are reduced in a fixed order (deterministic), with less (>= 16*Cs*Cl)
+ * by fp32 atomics.  scale: nullable device scalar (spectral norm: 1/sigma, so dw is the gradient of weight_orig up to the
+ * rank-1 term).  wdot / part / nparts_host (nullable, together): part[0..*nparts_host) <- block partials of
+ * <dw_unscaled, wdot> for b2c_sn_rank1 (part: room for 1024 floats; nparts_host: HOST int). */
+long long b2c_wgrad4s2_ws_floats(int N, int Hs, int Ws, int Cs, int Cl, int sm_count);
+int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* large, long long ldl, float* ws, long long ws_floats,
+                      float* dw, int accumulate, const float* scale, const float* wdot, float* part, int* nparts_host,
+                      int N, int Hs, int Ws, int Cs, int Cl, int sm_count, void* stream);
 
 /* ---- first layers, Cin = 3 / 6, NCHW fp32 in (cgan/models.py:103,245,257; interpolation cgan/losses.py:203-204) ---- */
 int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
@@ -46,7 +59,8 @@ int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const flo
 int b2c_first_dgrad(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1, void* ws, int N,
                     int H, int W, void* stream); /* ws: >= 36864 bytes of scratch for the packed tap weights */
 int b2c_first_wgrad(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
-                    const void* gz, float* dw, float* db, int N, int H, int W, void* stream);
+                    const void* gz, float* dw, float* db, const float* scale, const float* wdot, float* part,
+                    int* nparts_host, int N, int H, int W, void* stream); /* dw/db ACCUMULATED into; scale/wdot/part as in wgrad4s2 */
 
 /* ---- PatchGAN head Conv2d(512,1,k4,s1,p1) (cgan/models.py:252) ---- */
 int b2c_head_fprop(const void* a, const float* w, float* out, int N, int h, int C, void* stream);
@@ -57,11 +71,15 @@ int b2c_head_wgrad(const void* a, const float* gy, float* dw, int N, int h, int 
 int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream);
 int b2c_in_act_fwd(const void* z, long long ldz, const float* zs, const uint8_t* mask, float slope, void* o0,
                    long long ldo0, void* o1, long long ldo1, int N, int HW, int C, void* stream);
+/* pooled_sums: planar fp32 [2][N][C] = (sum act(x_hat), sum act'(x_hat)) per plane */
 int b2c_in_act_pool_fwd(const void* z, long long ldz, const float* zs, float slope, float* pooled_sums, int N, int HW,
                         int C, void* stream);
-int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const void* z, long long ldz, const float* zs,
-                   const uint8_t* mask, float slope, float* ws, void* gz, long long ldgz, int N, int HW, int C,
-                   void* stream);
+/* g: full gradient tensor, or gvec: per-(n,c) broadcast gradient with (optionally) fwd_sums = the pooled_sums of the forward,
+ * which makes the backward a single apply pass.  Planes of >= 64 pixels without a mask run as ONE cluster kernel (TMA ring,
+ * plane sums exchanged through distributed shared memory, operands cross HBM once); ws: fp32 [N][C][2] scratch otherwise. */
+int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const float* fwd_sums, const void* z, long long ldz,
+                   const float* zs, const uint8_t* mask, float slope, float* ws, void* gz, long long ldgz, int N, int HW,
+                   int C, void* stream);
 int b2c_in_act_bwd2(const void* h, long long ldh, const void* g, long long ldg, const void* z, long long ldz,
                     const float* zs, const uint8_t* mask, float slope, float* ws, void* gg, long long ldgg, void* gx,
                     long long ldgx, int N, int HW, int C, void* stream);
@@ -73,12 +91,25 @@ int b2c_add_strided(const void* a, long long lda, const void* b, long long ldb, 
                     int C, void* stream);
 int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long seed, unsigned long long offset,
                      const long long* offset_base, void* stream); /* stream position = offset + *offset_base (device, nullable) */
+/* out[i] = U[0,1) from the same counter-based stream: the GP interpolation coefficients (torch.rand at cgan/losses.py:199) */
+int b2c_uniform(float* out, long long n, unsigned long long seed, unsigned long long offset, const long long* offset_base,
+                void* stream);
 
 /* ---- spectral norm (torch spectral_norm.py:92-114); ws: K + ceil(K/32) + R floats of scratch (ceil(R/32)*K + R suffices for R > 32) ---- */
 int b2c_sn_power_iter(const float* W, float* u, float* v, float* sig, float* ws, int R, int K, int train, void* stream);
 /* b2c_sn_bwd: ws = min(592, ceil(R*K/1024)) floats of scratch (block partials of <dWe, W>, summed in a fixed order) */
 int b2c_sn_bwd(const float* dWe, const float* W, const float* u, const float* v, const float* sig, float* ws, float* dW,
                int R, int K, int accumulate, void* stream);
+/* All spectral-norm layers of one Discriminator forward (cgan/models.py:245-250) in three launches; arrays are HOST arrays of
+ * `count` (<= 8) device pointers / sizes; u_snap / v_snap (nullable arrays): copies of the u / v this forward used. */
+int b2c_sn_power_iter_multi(const float* const* W, float* const* u, float* const* v, float* const* sig, float* const* ws,
+                            float* const* u_snap, float* const* v_snap, const int* R, const int* K, int count, int train,
+                            void* stream);
+/* Deferred rank-1 term of the spectral-norm backward, once per backward for all layers: grad[l] -= sum_i (<dWe_i, W> /
+ * sigma_i^2) u_i v_i^T over the forward instances i of layer l (flat HOST arrays in layer order; part_i[nparts_i] = block
+ * partials of <dWe_i, W> left by b2c_wgrad4s2_bf16 / b2c_first_wgrad). */
+int b2c_sn_rank1(float* const* grad, const int* R, const int* K, const int* ninst, int nlayers, const float* const* u,
+                 const float* const* v, const float* const* sig, const float* const* part, const int* nparts, void* stream);
 
 /* ---- losses (cgan/losses.py:19-73,99-183,223-231; cgan/cgan_train_enhanced.py:327-328,362) ---- */
 int b2c_apply_delta(const float* bbox, const float* delta, int training, float* out, const float* gout, float* gdelta,
@@ -86,7 +117,13 @@ int b2c_apply_delta(const float* bbox, const float* delta, int training, float* 
 int b2c_eiou(const float* pred, const float* tgt, float eps, float* loss, const float* gscale, float* gpred,
              float* iou_out, int B, void* stream);
 int b2c_rowsum(const float* x, long long n, int B, int square, float scale, float* out, void* stream);
-int b2c_gp_tail(const float* ss, float* gp, float* coef, int B, void* stream);
+int b2c_gp_sumsq(const float* g0, const float* g1, long long n, int B, float* part, int* splits_host, void* stream);
+int b2c_gp_tail(const float* ss, int splits, float* gp, float* coef, int B, void* stream); /* ss: [B][splits] from b2c_gp_sumsq */
+int b2c_map_mean(const float* x, long long n, float scale, float* out, void* stream); /* out[0] = scale * sum(x), one block */
+/* d_loss = -(mean(real) - mean(fake)) + lambda_gp * gp in one launch (cgan_train_enhanced.py:327-328): out3 = (d_loss, wd, gp) */
+int b2c_critic_loss(const float* real, long long n_real, const float* fake, long long n_fake, const float* gp,
+                    float lambda_gp, float* out3, void* stream);
+int b2c_critic_loss_bwd(const float* gscale, float* g_real, long long n_real, float* g_fake, long long n_fake, void* stream);
 int b2c_scale_rows(const float* x, const float* coef, const float* gscale, float* out, long long n, int B, void* stream);
 int b2c_fill_scaled(float* out, long long n, const float* gscale, float value, void* stream);
 
@@ -97,10 +134,16 @@ int b2c_pool_fc_bwd(const float* gdelta, const float* tanh_v, const float* poole
                     int HW, float* dW, float* db, float* gvec, int N, int C, void* stream);
 
 /* ---- clip_grad_norm_(1.0) + Adam (cgan/cgan_train_enhanced.py:256-257,331-332,368-369) ---- */
-int b2c_multi_sumsq(float* const* g, const long long* n, int count, float* out, void* stream);
+/* part[0..*nparts_host) <- per-block partials of sum g^2 (room for 1024 floats; every slot written, no atomics) */
+int b2c_multi_sumsq(float* const* g, const long long* n, int count, float* part, int* nparts_host, void* stream);
+/* g_eff = grad_scale * g (data parallel: 1/world after a SUM all-reduce); clip coefficient min(1, max_norm / (|g_eff| + 1e-6))
+ * from the fixed-order sum of gnorm_part[nparts] (nullable); gnorm_sq_out[0] (nullable) <- |g_eff|^2; lr_dev (nullable device
+ * scalar) overrides lr (ReduceLROnPlateau, cgan_train_enhanced.py:260-261,427-428, under a captured CUDA graph); step count =
+ * step_index + *step_base (device, nullable).  128-bit vectorised when the tensors allow it. */
 int b2c_multi_adam(float* const* p, float* const* g, float* const* m, float* const* v, const long long* n, int count,
-                   const float* gnorm_sq, float max_norm, float lr, float beta1, float beta2, float eps, int step_index,
-                   const long long* step_base, void* stream); /* step count = step_index + *step_base (device, nullable) */
+                   const float* gnorm_part, int nparts, float* gnorm_sq_out, float grad_scale, float max_norm, float lr,
+                   const float* lr_dev, float beta1, float beta2, float eps, int step_index, const long long* step_base,
+                   void* stream);
 
 #ifdef __cplusplus
 }

@@ -15,6 +15,8 @@ G, D = GeneratorUNet(0.3), Discriminator(True)
 G.apply(weights_init_normal); D.apply(weights_init_normal)
 G, D = G.cuda(), D.cuda()
 tr = CGANTrainer(G, D)
+import os
+if os.environ.get('KPROF_GRAPH_WARM'): pass
 b = {k: v.cuda() for k, v in bench.synth_host_batches(B, S, 0, 1)[0].items()}
 keys = ("pred", "gt", "refined", "pred_box", "delta_true")
 for _ in range(3):
@@ -39,36 +41,23 @@ print(f"step {tot:.2f} ms; inside b2c calls {acc:.2f} ms; outside {tot-acc:.2f} 
 for ms, n, cnt in rows:
     print(f"{n:28s} {cnt:6.1f}/step {ms:8.3f} ms {100*ms/tot:5.1f}%  {1e3*ms/cnt:8.1f} us/call")
 
-print("\n-- InstanceNorm-family calls by shape (algorithmic bytes: each distinct tensor once) --")
-def nbytes(name, sc):
-    if name == "b2c_in_stats":      # ldz, N, HW, C
-        _, N, HW, C = sc; return N*HW*C*2
-    if name == "b2c_in_act_fwd":    # ldz, slope, ldo0, ldo1, N, HW, C
-        N, HW, C = sc[-3:]; return N*HW*C*2*2
-    if name == "b2c_in_act_pool_fwd":
-        N, HW, C = sc[-3:]; return N*HW*C*2
-    if name == "b2c_in_act_bwd":    # ldg, ldz, slope, ldgz, N, HW, C
-        N, HW, C = sc[-3:]; return N*HW*C*2*(3 if sc[0] else 2)
-    if name == "b2c_in_act_bwd2":
-        N, HW, C = sc[-3:]; return N*HW*C*2*5
-    if name == "b2c_lrelu_bwd":
-        return sc[0]*2*3
-    return None
+print("\n-- bandwidth kernels by shape (algorithmic bytes: each distinct tensor once) --")
 agg = collections.defaultdict(lambda: [0, 0.0, 0])
 for n, recs in timed.items():
     for a, c, sc in recs:
-        nb = nbytes(n, sc)
+        nb = bench.bw_bytes(n, sc)
         if nb is None: continue
-        key = (n, sc[-3:] if n != "b2c_lrelu_bwd" else sc[:1])
+        shp = tuple(v for v in sc[-4:] if isinstance(v, int) and not isinstance(v, bool))[-3:]
+        key = (n, shp, tuple(bool(v) for v in sc[:5] if isinstance(v, bool)))
         agg[key][0] += 1; agg[key][1] += a.elapsed_time(c); agg[key][2] = nb
-for (n, shp), (cnt, ms, nb) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-    print(f"{n:22s} {str(shp):22s} x{cnt/K:5.1f}/step {ms/K:7.3f} ms/step  {1e3*ms/cnt:7.1f} us/call  {nb/(ms/cnt)/1e6:7.0f} GB/s")
+for (n, shp, pat), (cnt, ms, nb) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+    print(f"{n:22s} {str(shp):22s} {''.join('x' if p else '-' for p in pat):6s} x{cnt/K:5.1f}/step {ms/K:7.3f} ms/step  {1e3*ms/cnt:7.1f} us/call  {nb/(ms/cnt)/1e6:7.0f} GB/s")
 
 print("\n-- tensor-core GEMM calls by shape --")
 agg = collections.defaultdict(lambda: [0, 0.0, 0.0])
 for n in bench.GEMM_KERNELS:
     for a, c, sc in timed.get(n, []):
-        key = (n, sc[-6:] if n == "b2c_wgrad4s2_bf16" else sc[-5:])
+        key = (n, sc[-6:-1] if n == "b2c_wgrad4s2_bf16" else sc[-5:])
         agg[key][0] += 1; agg[key][1] += a.elapsed_time(c); agg[key][2] = bench.gemm_flops(n, sc)
 for (n, shp), (cnt, ms, fl) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print(f"{n:20s} {str(shp):32s} x{cnt/K:5.1f}/step {ms/K:7.3f} ms/step {1e3*ms/cnt:7.1f} us/call {fl/(ms/cnt)/1e9:7.0f} TFLOP/s")

@@ -16,7 +16,7 @@ def test_header_parses_and_library_exports_every_symbol():
     missing = [n for n in protos if not hasattr(lib, n)]
     assert not missing, missing
     lib.b2c_abi_version.restype = ctypes.c_int
-    assert lib.b2c_abi_version() == 1
+    assert lib.b2c_abi_version() == 2
 
 
 def test_binding_has_no_cpu_fallback():

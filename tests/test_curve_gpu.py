@@ -36,18 +36,11 @@ def gpu_curves(steps, B, S, n_critic, lambda_gp):
     G.load_state_dict(st["G"]); D.load_state_dict(st["D"])
     G, D = G.cuda(), D.cuda()
     tr = CGANTrainer(G, D, n_critic=n_critic, lambda_gp=lambda_gp)
-    state = {"masks": None, "calls": 0, "alphas": None}
-
-    def pre_hook(mod, inp):
-        for site, m in zip(G.dropout_sites(), state["masks"][state["calls"]]):
-            site.injected = m.permute(0, 2, 3, 1).contiguous().to(torch.uint8).cuda().reshape(-1)
-        state["calls"] += 1
-    G.register_forward_pre_hook(pre_hook)
-    tr.alpha_source = lambda c: state["alphas"][c].cuda()
+    from test_models_gpu import attach_sources
     curves = {k: [] for k in KEYS}
     for step in range(steps):
         batch, masks, alphas = O.make_batch(B, S, step)
-        state.update(masks=masks, calls=0, alphas=alphas)
+        attach_sources(tr, masks, alphas)
         out = tr.step(*[batch[k].cuda() for k in ("pred", "gt", "refined", "pred_box", "delta_true")]).to_host()
         for k in KEYS:
             curves[k].append(out[k])

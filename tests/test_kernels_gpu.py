@@ -47,12 +47,13 @@ def test_conv4s2(L, N, H, W, Cin, Cout):
     L.call("b2c_pack_w_c", w.cuda(), None, wp, Cout, Cin)
     y = torch.empty(N, H // 2, W // 2, Cout, dtype=torch.bfloat16, device="cuda")
     zs = torch.full((N, Cout, 2), 7.0, device="cuda")  # fused InstanceNorm statistics of the bf16 output
-    L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, b.cuda(), y, Cout, zs, N, H, W, Cin, Cout)
+    sc = torch.tensor([0.75], device="cuda")  # epilogue scale (spectral-norm 1/sigma): y = acc * scale + bias
+    L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, sc, b.cuda(), y, Cout, zs, N, H, W, Cin, Cout)
     yf = y.float()
     assert float((zs[:, :, 0] - yf.sum((1, 2))).abs().max()) < 1e-3 * float(yf.abs().sum((1, 2)).max())
     assert rel(zs[:, :, 1], (yf * yf).sum((1, 2))) < 1e-4
     torch.cuda.synchronize()
-    ref = F.conv2d(x, q(w), b, 2, 1)
+    ref = F.conv2d(x, q(w) * 0.75, b, 2, 1)
     assert rel(nchw(y), ref) < 1e-2
 
 
@@ -68,12 +69,13 @@ def test_convt4s2(L, N, H, W, Cin, Cout):
     L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
     y = torch.empty(N, 2 * H, 2 * W, Cout, dtype=torch.bfloat16, device="cuda")
     zs = torch.full((N, Cout, 2), 7.0, device="cuda")
-    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, zs, None, 1.0, N, H, W, Cin, Cout)
+    sc = torch.tensor([1.5], device="cuda")
+    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, sc, None, y, Cout, zs, None, 1.0, N, H, W, Cin, Cout)
     yf = y.float()
     assert rel(zs[:, :, 1], (yf * yf).sum((1, 2))) < 1e-4
     assert float((zs[:, :, 0] - yf.sum((1, 2))).abs().max()) < 1e-3 * float(yf.abs().sum((1, 2)).max())
     torch.cuda.synchronize()
-    ref = F.conv_transpose2d(x, q(w), None, 2, 1)
+    ref = F.conv_transpose2d(x, q(w) * 1.5, None, 2, 1)
     assert rel(nchw(y), ref) < 1e-2
 
 
@@ -92,14 +94,14 @@ def test_fp32_check_mode(L, mode, N, H, W, Cin, Cout):
             wp = torch.empty(Cout, 16 * Cin, dtype=torch.bfloat16, device="cuda")
             L.call("b2c_pack_w_c", w.cuda(), None, wp, Cout, Cin)
             y = torch.empty(N, H // 2, W // 2, Cout, dtype=torch.float32, device="cuda")
-            L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, None, N, H, W, Cin, Cout)
+            L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, None, None, y, Cout, None, N, H, W, Cin, Cout)
             ref = F.conv2d(x.double(), q(w).double(), None, 2, 1)
         else:
             w = torch.randn(Cin, Cout, 4, 4, generator=g) * 0.05
             wp = torch.empty(4, Cout, 4 * Cin, dtype=torch.bfloat16, device="cuda")
             L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
             y = torch.empty(N, 2 * H, 2 * W, Cout, dtype=torch.float32, device="cuda")
-            L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, None, None, 1.0, N, H, W, Cin, Cout)
+            L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, None, y, Cout, None, None, 1.0, N, H, W, Cin, Cout)
             ref = F.conv_transpose2d(x.double(), q(w).double(), None, 2, 1)
         torch.cuda.synchronize()
     finally:
@@ -117,7 +119,7 @@ def test_convt64_fused_lrelu_backward(L):
     wp = torch.empty(4, Cout, 4 * Cin, dtype=torch.bfloat16, device="cuda")
     L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
     y = torch.empty(N, 2 * H, 2 * W, Cout, dtype=torch.bfloat16, device="cuda")
-    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, y, Cout, None, nhwc(act), 0.2, N, H, W, Cin, Cout)
+    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, None, y, Cout, None, nhwc(act), 0.2, N, H, W, Cin, Cout)
     torch.cuda.synchronize()
     ref = F.conv_transpose2d(x, q(w), None, 2, 1) * torch.where(act > 0, 1.0, 0.2)
     assert rel(nchw(y), ref) < 1e-2
@@ -132,7 +134,7 @@ def test_conv_dgrad_is_convt(L):
     wp = torch.empty(4, Cin, 4 * Cout, dtype=torch.bfloat16, device="cuda")
     L.call("b2c_pack_w_t", w.cuda(), None, wp, Cout, Cin)
     dx = torch.empty(N, H, W, Cin, dtype=torch.bfloat16, device="cuda")
-    L.call("b2c_convt4s2_bf16", nhwc(gy), Cout, wp, None, dx, Cin, None, None, 1.0, N, H // 2, W // 2, Cout, Cin)
+    L.call("b2c_convt4s2_bf16", nhwc(gy), Cout, wp, None, None, dx, Cin, None, None, 1.0, N, H // 2, W // 2, Cout, Cin)
     torch.cuda.synchronize()
     ref = torch.nn.grad.conv2d_input((N, Cin, H, W), q(w), gy, 2, 1)
     assert rel(nchw(dx), ref) < 1e-2
@@ -144,15 +146,31 @@ def test_wgrad4s2(L, N, Hs, Ws, Cs, Cl):
     g = torch.Generator().manual_seed(4)
     small = q(torch.randn(N, Cs, Hs, Ws, generator=g))
     large = q(torch.randn(N, Cl, 2 * Hs, 2 * Ws, generator=g))
-    ws = torch.empty(16, Cs, Cl, dtype=torch.float32, device="cuda")
-    dw = torch.empty(Cs, Cl, 4, 4, dtype=torch.float32, device="cuda")
-    L.call("b2c_wgrad4s2_bf16", nhwc(small), Cs, nhwc(large), Cl, ws, dw, 0, N, Hs, Ws, Cs, Cl, 148)
-    torch.cuda.synchronize()
     ref = torch.nn.grad.conv2d_weight(large.double(), (Cs, Cl, 4, 4), small.double(), 2, 1)
-    assert rel(dw, ref) < 1e-4  # fp32 output: the fp32 check criterion applies directly
-    L.call("b2c_wgrad4s2_bf16", nhwc(small), Cs, nhwc(large), Cl, ws, dw, 1, N, Hs, Ws, Cs, Cl, 148)
+    nws = L.query("b2c_wgrad4s2_ws_floats", N, Hs, Ws, Cs, Cl, 148)
+    assert nws >= 16 * Cs * Cl and nws % (16 * Cs * Cl) == 0
+    dw = torch.empty(Cs, Cl, 4, 4, dtype=torch.float32, device="cuda")
+    runs = []
+    for nf in (nws, 16 * Cs * Cl):  # deterministic split-K slabs, then the atomic fallback with a one-slab workspace
+        ws = torch.empty(nf, dtype=torch.float32, device="cuda")
+        L.call("b2c_wgrad4s2_bf16", nhwc(small), Cs, nhwc(large), Cl, ws, nf, dw, 0, None, None, None, None, N, Hs, Ws, Cs,
+               Cl, 148)
+        torch.cuda.synchronize()
+        assert rel(dw, ref) < 1e-4  # fp32 output: the fp32 check criterion applies directly
+        runs.append(dw.clone())
+    ws = torch.empty(nws, dtype=torch.float32, device="cuda")
+    L.call("b2c_wgrad4s2_bf16", nhwc(small), Cs, nhwc(large), Cl, ws, nws, dw, 0, None, None, None, None, N, Hs, Ws, Cs, Cl, 148)
+    assert torch.equal(dw, runs[0])  # bit-identical from run to run
+    # accumulate + scale + the <dW, W> partials of the spectral-norm backward
+    wdot = torch.randn(Cs, Cl, 4, 4, generator=g).cuda()
+    part, nparts = torch.full((1024,), 9.0, device="cuda"), ctypes.c_int(0)
+    sc = torch.tensor([0.5], device="cuda")
+    L.call("b2c_wgrad4s2_bf16", nhwc(small), Cs, nhwc(large), Cl, ws, nws, dw, 1, sc, wdot, part, ctypes.byref(nparts), N, Hs,
+           Ws, Cs, Cl, 148)
     torch.cuda.synchronize()
-    assert rel(dw, 2 * ref) < 1e-4
+    assert rel(dw, 1.5 * ref) < 1e-4
+    dot = float(part[:nparts.value].double().sum())
+    assert abs(dot - float((ref * wdot.cpu().double()).sum())) <= 1e-4 * float(ref.norm() * wdot.norm())
 
 
 @pytest.mark.parametrize("cin,N,S,interp", [(3, 3, 32, True), (6, 3, 32, True), (6, 2, 128, False), (3, 5, 64, False),
@@ -186,10 +204,17 @@ def test_first_layer(L, cin, N, S, interp):
     assert rel(got, refdx) < 1e-4
     dw = torch.zeros(64, cin, 4, 4, device="cuda")
     db = torch.zeros(64, device="cuda")
-    L.call("b2c_first_wgrad", a0, a1, b0, b1, al_d, nhwc(gz), dw, db, N, S, S)
+    L.call("b2c_first_wgrad", a0, a1, b0, b1, al_d, nhwc(gz), dw, db, None, None, None, None, N, S, S)
     refdw = torch.nn.grad.conv2d_weight(xi, (64, cin, 4, 4), gz, 2, 1)
     assert rel(dw, refdw) < 1e-4
     assert rel(db, gz.sum((0, 2, 3))) < 1e-4
+    # accumulate with a scale (1/sigma) and leave the <dW, W> partials of the spectral-norm backward
+    part, nparts = torch.full((1024,), 9.0, device="cuda"), ctypes.c_int(0)
+    L.call("b2c_first_wgrad", a0, a1, b0, b1, al_d, nhwc(gz), dw, None, sig.cuda()[1:], w.cuda(), part,
+           ctypes.byref(nparts), N, S, S)
+    assert rel(dw, 1.5 * refdw) < 1e-4
+    dot = float(part[:nparts.value].double().sum())
+    assert abs(dot - float((refdw.double() * w.double()).sum())) <= 1e-4 * float(refdw.norm() * w.norm())
 
 
 def test_head(L):

@@ -19,14 +19,8 @@ def test_one_step_vs_oracle(B, S):
     G, D = G.cuda(), D.cuda()
     tr = CGANTrainer(G, D, n_critic=2, lambda_gp=1.0)
     batch, masks, alphas = O.make_batch(B, S, 0)
-    calls = {"n": 0}
-
-    def pre_hook(mod, inp):
-        for site, m in zip(G.dropout_sites(), masks[calls["n"]]):
-            site.injected = m.permute(0, 2, 3, 1).contiguous().to(torch.uint8).cuda().reshape(-1)
-        calls["n"] += 1
-    G.register_forward_pre_hook(pre_hook)
-    tr.alpha_source = lambda c: alphas[c].cuda()
+    from test_models_gpu import attach_sources
+    attach_sources(tr, masks, alphas)
     out = tr.step(*[batch[k].cuda() for k in ("pred", "gt", "refined", "pred_box", "delta_true")])
     got = out.to_host()
     ref = O.train_step(st, batch, masks, alphas, n_critic=2, lambda_gp=1.0)
