@@ -117,6 +117,17 @@ def bw_bytes(name, a):
     return None
 
 
+def gemm_flops(name, a):
+    """Algorithmic FLOPs of one launch from its C-ABI argument pattern (include/b2c.h; trailing arguments are the sizes)."""
+    if name == "b2c_wgrad4s2_bf16":      # ..., N, Hs, Ws, Cs, Cl, sm_count
+        N, Hs, Ws, Cs, Cl = a[-6:-1]
+        return 2.0 * N * Hs * Ws * Cs * 16 * Cl
+    N, H, W, Cin, Cout = a[-5:]           # ..., N, H, W, Cin, Cout
+    if name == "b2c_conv4s2_bf16":
+        return 2.0 * N * (H // 2) * (W // 2) * Cout * 16 * Cin
+    return 2.0 * N * H * W * Cout * 16 * Cin
+
+
 # --------------------------------------------------------------------------------------------- clocks
 class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"

@@ -167,6 +167,7 @@ class WeightCtx:
 
     def take_stats(self):
         zs, self._stats = self._stats, None
+        self.want_stats = False  # later uses of this context (double backward) are plain convs
         return zs
 
     @property
@@ -219,6 +220,9 @@ def _convt_raw(x, wpack_t, Cout, wctx=None, act=None, slope=1.0, scale=None):
     return y
 
 
+_WGRAD_DET = __import__("os").environ.get("B2C_WGRAD_DET", "0") == "1"
+
+
 def _wgrad(wctx, small, large):
     """Weight gradient sum small[n,sy,sx,a] large[n,2sy+ky-1,2sx+kx-1,b] -> [Cs][Cl][4][4] of wctx.weight.  With a sink:
     accumulated in place (times 1/sigma, rank-1 term deferred) and None is returned; else returned as a tensor."""
@@ -227,7 +231,9 @@ def _wgrad(wctx, small, large):
     N, Cs, Hs, Ws = small.shape
     Cl = large.shape[1]
     dev = small.device
-    nws = _lib.query("b2c_wgrad4s2_ws_floats", N, Hs, Ws, Cs, Cl, _lib.sm_count())
+    # one [16][Cs][Cl] slab: split-K partials are reduced with fp32 vector atomics.  B2C_WGRAD_DET=1 asks for one slab per
+    # split instead (fixed-order reduction, bit-reproducible, measured 1.2-2.6x slower at the step's shapes: 9-74 splits)
+    nws = _lib.query("b2c_wgrad4s2_ws_floats", N, Hs, Ws, Cs, Cl, _lib.sm_count()) if _WGRAD_DET else 16 * Cs * Cl
     ws = torch.empty(nws, dtype=torch.float32, device=dev)
     sink = sink_of(wctx.weight)
     if sink is None:

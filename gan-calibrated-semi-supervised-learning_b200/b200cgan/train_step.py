@@ -136,6 +136,8 @@ class CGANTrainer:
         self._eager_steps = 0
         self._static_in = self._static_out = self._ctr = self._ctr_inc = None
         self._static_alpha = self._static_masks = None  # device buffers the captured graph reads the injected draws from
+        dev = self.optD.flat_p.device
+        self._seed3(dev); self._seed1(dev)  # backward seeds: created now, not inside a graph capture
 
     # ---- data parallel: SUM the flat gradient bucket over ranks; the 1/world is applied inside the Adam kernel ----
     def _allreduce(self, opt):

@@ -141,9 +141,11 @@ __global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_ker
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<64>(tmem_slot);
-  // weights: B[co][k] = w[co][c][ky][kx] / sigma in the tensor's own order, K-major, k-blocks of [64 rows x 128 B]
+  // weights: B[co][k] = bf16(w[co][c][ky][kx]) in the tensor's own order, K-major, k-blocks of [64 rows x 128 B]; the
+  // spectral-norm 1/sigma multiplies the fp32 accumulators in the epilogue (same rounding point as the tapgemm kernels)
+  const float osc = inv_sigma ? __ldg(inv_sigma) : 1.f;
   {
-    const float s = inv_sigma ? __ldg(inv_sigma) : 1.f;
+    const float s = 1.f;
     constexpr int NCH = 2 * CIN;
     for (int i = t; i < 64 * NCH; i += FT_THREADS) {
       const int co = i / NCH, j = i % NCH;
@@ -197,8 +199,8 @@ __global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_ker
         uint32_t o[16];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          float a = __uint_as_float(v0[2 * j]) + bias_s[c0 + 2 * j], b = __uint_as_float(v0[2 * j + 1]) + bias_s[c0 + 2 * j + 1];
-          float c = __uint_as_float(v1[2 * j]) + bias_s[c0 + 16 + 2 * j], d = __uint_as_float(v1[2 * j + 1]) + bias_s[c0 + 17 + 2 * j];
+          float a = fmaf(__uint_as_float(v0[2 * j]), osc, bias_s[c0 + 2 * j]), b = fmaf(__uint_as_float(v0[2 * j + 1]), osc, bias_s[c0 + 2 * j + 1]);
+          float c = fmaf(__uint_as_float(v1[2 * j]), osc, bias_s[c0 + 16 + 2 * j]), d = fmaf(__uint_as_float(v1[2 * j + 1]), osc, bias_s[c0 + 17 + 2 * j]);
           a = a > 0.f ? a : a * slope; b = b > 0.f ? b : b * slope;
           c = c > 0.f ? c : c * slope; d = d > 0.f ? d : d * slope;
           o[j] = pack_bf16(a, b);

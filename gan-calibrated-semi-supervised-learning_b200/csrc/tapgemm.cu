@@ -153,6 +153,14 @@ __global__ void __launch_bounds__(64 + 128 * MT) tapgemm_kernel(const __grid_con
       tmem_ld16(taddr, v0);
       tmem_ld16(taddr + 16, v1);
       tmem_ld_wait();
+      if (p.scale) {  // spectral-norm 1/sigma on the fp32 accumulators (the packed tap weights are bf16(w))
+        const float sc = __ldg(p.scale);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          v0[j] = __float_as_uint(__uint_as_float(v0[j]) * sc);
+          v1[j] = __float_as_uint(__uint_as_float(v1[j]) * sc);
+        }
+      }
       if (valid) {
         const int H = 2 * p.Ho, W = 2 * p.Wo;
         const int cin = p.gx1 ? 6 : 3;
@@ -594,12 +602,12 @@ extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_
   B2C_REQUIRE(ws && ((uintptr_t)ws & 15) == 0, "first_dgrad: workspace missing or unaligned");
   TapGemmParams p;
   p.mode = 2; p.N = N; p.Cin = 64; p.Cout = 32; p.kchunks = 1;
-  p.y = nullptr; p.ldy = 0; p.bias = nullptr; p.scale = nullptr; p.gx0 = gx0; p.gx1 = gx1; p.stats = nullptr; p.f32out = 0; p.st256 = 0;
+  p.y = nullptr; p.ldy = 0; p.bias = nullptr; p.scale = inv_sigma; p.gx0 = gx0; p.gx1 = gx1; p.stats = nullptr; p.f32out = 0; p.st256 = 0;
   p.Ho = H / 2; p.Wo = W / 2;
   B2C_REQUIRE(pick_box(p.Ho, p.Wo, 128, &p.BW, &p.BH, &p.BI), "first_dgrad: unsupported spatial size %dx%d", H, W);
   p.tiles_x = p.Wo / p.BW; p.tiles_y = p.Ho / p.BH;
   const int tiles_n = (N + p.BI - 1) / p.BI;
-  pack_w_d1_kernel<<<(32 * 576 + 255) / 256, 256, 0, st>>>(w, inv_sigma, (__nv_bfloat16*)ws, gx1 ? 6 : 3);
+  pack_w_d1_kernel<<<(32 * 576 + 255) / 256, 256, 0, st>>>(w, nullptr, (__nv_bfloat16*)ws, gx1 ? 6 : 3);
   int rc = b2c_check_launch("pack_w_d1_kernel");
   if (rc) return rc;
   CUtensorMap tmA, tmB;

@@ -197,15 +197,17 @@ def sn_weight(d, idx: int, train: bool):
             u.copy_(F.normalize(torch.mv(wm, v), dim=0, eps=1e-12))
     uc, vc = u.clone(), v.clone()
     sigma = torch.dot(uc, torch.mv(wm, vc))
-    return w / sigma
+    # bf16-storage emulation (no-op otherwise): the tensor-core operand is the bf16 master weight, 1/sigma is applied to
+    # the fp32 accumulators (the weights are packed once per optimizer step, sigma changes every forward)
+    return _r(w) / sigma
 
 
 def d_forward(d, pred, other, train: bool = True, taps: Optional[dict] = None):
     sn = "model.0.weight_orig" in d
     h = torch.cat([pred, other], 1)
     for idx, _, _, norm in D_BLOCKS:
-        w = sn_weight(d, idx, train) if sn else d[f"model.{idx}.weight"]
-        h = F.conv2d(_r(h), _r(w), d[f"model.{idx}.bias"], 2, 1)
+        w = sn_weight(d, idx, train) if sn else _r(d[f"model.{idx}.weight"])
+        h = F.conv2d(_r(h), w, d[f"model.{idx}.bias"], 2, 1)
         if norm:
             h = _inorm(_r(h))
         h = _r(F.leaky_relu(h, 0.2))

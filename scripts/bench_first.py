@@ -19,7 +19,7 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 nb_in, nb_map = 2 * a0.numel() * 4, y.numel() * 2
 cases = {
     "first_fprop": (lambda: L.call("b2c_first_fprop", a0, a1, None, None, None, w, isg, bias, y, B, S, S, 0.2), nb_in + nb_map),
-    "first_wgrad": (lambda: L.call("b2c_first_wgrad", a0, a1, None, None, None, gz, dw, db, B, S, S), nb_in + nb_map),
+    "first_wgrad": (lambda: L.call("b2c_first_wgrad", a0, a1, None, None, None, gz, dw, db, None, None, None, None, B, S, S), nb_in + nb_map),
     "first_dgrad": (lambda: L.call("b2c_first_dgrad", gz, w, isg, g0, g1, ws, B, S, S), nb_in + nb_map),
 }
 for name, (fn, nb) in cases.items():

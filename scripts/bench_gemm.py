@@ -27,19 +27,22 @@ WGRAD = [(64, 64, 128, 64), (32, 32, 256, 128), (16, 16, 512, 256), (128, 128, 1
 if which in ("conv", "all"):
     for H, W, Cin, Cout in CONV:
         x, w, y = bf(B, H, W, Cin), bf(Cout, 16 * Cin), bf(B, H // 2, W // 2, Cout)
-        t = timeit(lambda: L.call("b2c_conv4s2_bf16", x, Cin, w, None, y, Cout, None, B, H, W, Cin, Cout))
+        t = timeit(lambda: L.call("b2c_conv4s2_bf16", x, Cin, w, None, None, y, Cout, None, B, H, W, Cin, Cout))
         fl = 2.0 * B * (H // 2) * (W // 2) * Cout * 16 * Cin
         print(f"conv4s2  ({B},{H},{W},{Cin},{Cout}): {t*1e3:8.1f} us {fl/t/1e9:7.0f} TFLOP/s")
 if which in ("convt", "all"):
     for H, W, Cin, Cout in CONVT:
         x, w, y = bf(B, H, W, Cin), bf(4, Cout, 4 * Cin), bf(B, 2 * H, 2 * W, Cout)
-        t = timeit(lambda: L.call("b2c_convt4s2_bf16", x, Cin, w, None, y, Cout, None, None, 1.0, B, H, W, Cin, Cout))
+        t = timeit(lambda: L.call("b2c_convt4s2_bf16", x, Cin, w, None, None, y, Cout, None, None, 1.0, B, H, W, Cin, Cout))
         fl = 2.0 * B * H * W * Cout * 16 * Cin
         print(f"convt4s2 ({B},{H},{W},{Cin},{Cout}): {t*1e3:8.1f} us {fl/t/1e9:7.0f} TFLOP/s")
 if which in ("wgrad", "all"):
     for Hs, Ws, Cs, Cl in WGRAD:
         sm, lg = bf(B, Hs, Ws, Cs), bf(B, 2 * Hs, 2 * Ws, Cl)
-        ws = torch.empty(16, Cs, Cl, device="cuda"); dw = torch.empty(Cs, Cl, 4, 4, device="cuda")
-        t = timeit(lambda: L.call("b2c_wgrad4s2_bf16", sm, Cs, lg, Cl, ws, dw, 0, B, Hs, Ws, Cs, Cl, 148))
+        dw = torch.empty(Cs, Cl, 4, 4, device="cuda")
         fl = 2.0 * B * Hs * Ws * Cs * 16 * Cl
-        print(f"wgrad4s2 ({B},{Hs},{Ws},{Cs},{Cl}): {t*1e3:8.1f} us {fl/t/1e9:7.0f} TFLOP/s")
+        ndet = L.query("b2c_wgrad4s2_ws_floats", B, Hs, Ws, Cs, Cl, 148)
+        for tag, nf in (("atomic", 16 * Cs * Cl), ("det", ndet)):
+            ws = torch.empty(nf, device="cuda")
+            t = timeit(lambda: L.call("b2c_wgrad4s2_bf16", sm, Cs, lg, Cl, ws, nf, dw, 0, None, None, None, None, B, Hs, Ws, Cs, Cl, 148))
+            print(f"wgrad4s2 ({B},{Hs},{Ws},{Cs},{Cl}) {tag:6s} splits={nf // (16 * Cs * Cl):3d}: {t*1e3:8.1f} us {fl/t/1e9:7.0f} TFLOP/s")

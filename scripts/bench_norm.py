@@ -13,7 +13,7 @@ T = N * HW * C * 2
 cases = {
     "in_stats": (lambda: L.call("b2c_in_stats", z, C, zs, N, HW, C), T),
     "in_act_fwd": (lambda: L.call("b2c_in_act_fwd", z, C, zs, None, 0.2, o0, C, None, 0, N, HW, C), 2 * T),
-    "in_act_bwd": (lambda: L.call("b2c_in_act_bwd", g, C, None, z, C, zs, None, 0.2, ws, o0, C, N, HW, C), 3 * T),
+    "in_act_bwd": (lambda: L.call("b2c_in_act_bwd", g, C, None, None, z, C, zs, None, 0.2, ws, o0, C, N, HW, C), 3 * T),
     "in_act_bwd2": (lambda: L.call("b2c_in_act_bwd2", h, C, g, C, z, C, zs, None, 0.2, ws, o0, C, o1, C, N, HW, C), 5 * T),
 }
 for name, (fn, nb) in cases.items():

@@ -29,14 +29,14 @@ def oracle_norm_block(a, w_orig, u, v, bias):
     """SN-conv -> InstanceNorm -> LeakyReLU (cgan/models.py:236-242) with the given power-iteration vectors."""
     wm = w_orig.reshape(w_orig.shape[0], -1)
     sigma = torch.dot(u, torch.mv(wm, v))
-    z = F.conv2d(_r(a), _r(w_orig / sigma), bias, 2, 1)
+    z = F.conv2d(_r(a), _r(w_orig) / sigma, bias, 2, 1)  # bf16 master weight, 1/sigma on the fp32 accumulators
     return _r(F.leaky_relu(F.instance_norm(_r(z), eps=1e-5), 0.2))
 
 
 def oracle_first_block(x, w_orig, u, v, bias):
     wm = w_orig.reshape(w_orig.shape[0], -1)
     sigma = torch.dot(u, torch.mv(wm, v))
-    return _r(F.leaky_relu(F.conv2d(_r(x), _r(w_orig / sigma), bias, 2, 1), 0.2))
+    return _r(F.leaky_relu(F.conv2d(_r(x), _r(w_orig) / sigma, bias, 2, 1), 0.2))
 
 
 def vjp2(fn, a_in, g_out, k, h, params):
@@ -149,7 +149,7 @@ def test_discriminator_blocks_teacher_forced_second_order(B, S):
     w_c = st["D"]["model.0.weight_orig"].clone().requires_grad_(True)
     b_c = st["D"]["model.0.bias"].clone()
     wm = w_c.reshape(64, -1)
-    z0 = F.conv2d(_r(x_c), _r(w_c / torch.dot(c(wctx.u), torch.mv(wm, c(wctx.v)))), b_c, 2, 1)
+    z0 = F.conv2d(_r(x_c), _r(w_c) / torch.dot(c(wctx.u), torch.mv(wm, c(wctx.v))), b_c, 2, 1)
     (gi_c,) = torch.autograd.grad(z0, x_c, g_c, create_graph=True)
     rg = torch.autograd.grad([z0, gi_c], [g_c, w_c], [c(rec[0]["k"]), torch.cat([c(hx[0]), c(hx[1])], 1)])
     errs = {"a_out": rel(a_out, _r(F.leaky_relu(z0, 0.2))), "g_in": rel(torch.cat([gi[0], gi[1]], 1), gi_c),
