@@ -458,8 +458,57 @@ __device__ __forceinline__ float ld_dsmem_f32(const float* local, uint32_t rank)
   return v;
 }
 
+// ---- packed fp32x2 arithmetic (sm_100: FFMA2 / FADD2 / FMUL2 process two independent fp32 lanes per instruction).  The
+// kernel below is bound by instruction issue as much as by memory (ncu: 62 % issue-active at 36 thread-instructions per
+// element before this), so the per-element math runs on pairs: a packed bf16x2 word unpacks into one fp32x2 register pair.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 f2_pack(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(__float_as_uint(lo)), "r"(__float_as_uint(hi)));
+  return r;
+}
+__device__ __forceinline__ void f2_split(f32x2 v, float& lo, float& hi) {
+  uint32_t a, b;
+  asm("mov.b64 {%0, %1}, %2;" : "=r"(a), "=r"(b) : "l"(v));
+  lo = __uint_as_float(a); hi = __uint_as_float(b);
+}
+__device__ __forceinline__ f32x2 f2_bf16x2(uint32_t w) {  // (bf16 lo, bf16 hi) -> (fp32, fp32): exact
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(w << 16), "r"(w & 0xffff0000u));
+  return r;
+}
+__device__ __forceinline__ f32x2 f2_fma(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ f32x2 f2_mul(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 f2_add(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// (x > 0 ? 1 : slope) per lane as k0 + k1 * step(x), k0 = slope, k1 = 1 - slope: two FSET + one FFMA2 (same x > 0 rule as
+// torch's leaky_relu backward, including x == 0 -> slope)
+__device__ __forceinline__ f32x2 f2_dact(f32x2 xh, f32x2 k0, f32x2 k1) {
+  float lo, hi, sl, sh;
+  f2_split(xh, lo, hi);
+  asm("set.gt.f32.f32 %0, %1, 0f00000000;" : "=f"(sl) : "f"(lo));
+  asm("set.gt.f32.f32 %0, %1, 0f00000000;" : "=f"(sh) : "f"(hi));
+  return f2_fma(f2_pack(sl, sh), k1, k0);
+}
+__device__ __forceinline__ uint32_t f2_to_bf16x2(f32x2 v) {
+  float lo, hi;
+  f2_split(v, lo, hi);
+  return pack_bf16(lo, hi);
+}
+
 template <int MODE>
-__global__ void __launch_bounds__(CK_THREADS) plane_cluster_kernel(const __grid_constant__ CUtensorMap tmZ,
+__global__ void __launch_bounds__(CK_THREADS, MODE == M_BWD2 ? 2 : 3) plane_cluster_kernel(const __grid_constant__ CUtensorMap tmZ,
                                                                    const __grid_constant__ CUtensorMap tmG,
                                                                    const __grid_constant__ CUtensorMap tmH, NormArgs a,
                                                                    int CS, int nst, int RS) {
@@ -474,7 +523,7 @@ __global__ void __launch_bounds__(CK_THREADS) plane_cluster_kernel(const __grid_
   uint64_t* empty = full + 32;
 
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-  const int rank = blockIdx.x % CS, cg = blockIdx.y, n = blockIdx.z;
+  const int rank = blockIdx.x, cg = blockIdx.y, n = blockIdx.z;  // gridDim.x == CS: blockIdx.x is the rank in the cluster
   const bool resident = nst <= RS;
   const long long pix0 = (long long)n * a.HW + (long long)rank * nst * CK_PIXB;  // first pixel row of this CTA's slice
 
@@ -494,165 +543,203 @@ __global__ void __launch_bounds__(CK_THREADS) plane_cluster_kernel(const __grid_
     // The producer joins the cluster barrier BETWEEN the two phases' loads: its phase-2 loads wait for ring slots that the
     // consumers only free after that barrier, so it must have arrived before it blocks (and it never blocks before having
     // the first RS boxes of phase 2 in flight).
-    auto issue = [&](int k) {
-      const int slot = k % RS;
-      if (k >= RS) mbar_wait(&empty[slot], ((k / RS) - 1) & 1);
+    int slot = 0, round = 0;  // load k goes to slot k % RS; round = k / RS
+    auto issue = [&](int box) {
+      if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
       mbar_expect_tx(&full[slot], Cfg::STAGE_BYTES);
       uint8_t* dst = ring + (size_t)slot * Cfg::STAGE_BYTES;
-      const int row = (int)(pix0 + (long long)(k % nst) * CK_PIXB);
+      const int row = (int)(pix0 + (long long)box * CK_PIXB);
       tma_load_2d(dst, &tmZ, &full[slot], cg * 64, row);
       tma_load_2d(dst + CK_BOX_BYTES, &tmG, &full[slot], cg * 64, row);
       if (MODE == M_BWD2) tma_load_2d(dst + 2 * CK_BOX_BYTES, &tmH, &full[slot], cg * 64, row);
+      if (++slot == RS) { slot = 0; ++round; }
     };
     if (elect_one())
       for (int k = 0; k < nst; ++k) issue(k);
     __syncwarp();
     if (CS > 1) cluster_arrive();
-    if (!resident && elect_one())
-      for (int k = nst; k < 2 * nst; ++k) issue(k);
+    if (!resident && elect_one()) {
+      // both elect_one() branches run on the same lane, but `slot` / `round` live in that lane's registers only if it is
+      // the same lane: elect.sync picks the lowest active lane both times
+      for (int k = 0; k < nst; ++k) issue(k);
+    }
     __syncwarp();
     if (CS > 1) { cluster_wait(); cluster_arrive(); cluster_wait(); }
     return;
-  } else {
-    const int cv = t & 7, prow = t >> 3;  // 8 channel vectors x 32 pixel rows
-    const int c0 = cg * 64 + cv * 8;
-    float mean[8], rstd[8], acc[NSUM][8];
-    load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
+  }
+
+  // ---------------------------------------------------------------- consumers: 8 channel vectors x 32 pixel rows
+  const int cv = t & 7, prow = t >> 3;
+  const int c0 = cg * 64 + cv * 8;
+  const int off0 = prow * 128 + ((cv ^ (prow & 7)) << 4);  // this thread's 16 bytes of row prow (row u*32 + prow: + u * 4096)
+  f32x2 rstd2[4], shift2[4];
+  {
+    float mean[8], rstd[8];
+    load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);  // `mean` holds -mean * rstd
 #pragma unroll
-    for (int s2 = 0; s2 < NSUM; ++s2)
+    for (int j = 0; j < 4; ++j) { rstd2[j] = f2_pack(rstd[2 * j], rstd[2 * j + 1]); shift2[j] = f2_pack(mean[2 * j], mean[2 * j + 1]); }
+  }
+  const f32x2 k0 = f2_pack(a.slope, a.slope), k1 = f2_pack(1.f - a.slope, 1.f - a.slope);
+  f32x2 acc[NSUM][4];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) acc[s2][i] = 0.f;
-    const float slope = a.slope;
-    // ---- phase 1: plane sums
-    for (int k = 0; k < nst; ++k) {
-      const int slot = k % RS;
-      mbar_wait(&full[slot], (k / RS) & 1);
-      const uint8_t* st = ring + (size_t)slot * Cfg::STAGE_BYTES;
+  for (int s2 = 0; s2 < NSUM; ++s2)
 #pragma unroll
-      for (int u = 0; u < CK_PIXB / 32; ++u) {
-        const int r = u * 32 + prow;
-        const int off = r * 128 + ((cv ^ (r & 7)) << 4);
-        float z[8], g[8];
-        cvt8(*reinterpret_cast<const uint4*>(st + off), z);
-        cvt8(*reinterpret_cast<const uint4*>(st + CK_BOX_BYTES + off), g);
+    for (int j = 0; j < 4; ++j) acc[s2][j] = 0ull;
+  int slot = 0, par = 0;
+  // ---- phase 1: plane sums
+  for (int k = 0; k < nst; ++k) {
+    mbar_wait(&full[slot], par);
+    const uint8_t* st = ring + (size_t)slot * Cfg::STAGE_BYTES + off0;
+#pragma unroll(MODE == M_BWD2 ? 1 : 2)
+    for (int u = 0; u < CK_PIXB / 32; ++u) {
+      const uint4 zw = *reinterpret_cast<const uint4*>(st + u * 4096);
+      const uint4 gw = *reinterpret_cast<const uint4*>(st + CK_BOX_BYTES + u * 4096);
+      const uint32_t zq[4] = {zw.x, zw.y, zw.z, zw.w}, gq[4] = {gw.x, gw.y, gw.z, gw.w};
+      uint32_t hq[4] = {0, 0, 0, 0};
+      if (MODE == M_BWD2) {
+        const uint4 hw = *reinterpret_cast<const uint4*>(st + 2 * CK_BOX_BYTES + u * 4096);
+        hq[0] = hw.x; hq[1] = hw.y; hq[2] = hw.z; hq[3] = hw.w;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const f32x2 xh = f2_fma(f2_bf16x2(zq[j]), rstd2[j], shift2[j]);
+        const f32x2 gn = f2_mul(f2_bf16x2(gq[j]), f2_dact(xh, k0, k1));
         if (MODE == M_BWD) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float xh = fmaf(z[i], rstd[i], mean[i]);
-            const float gn = xh > 0.f ? g[i] : g[i] * slope;
-            acc[0][i] += gn; acc[1][i] = fmaf(gn, xh, acc[1][i]);
-          }
+          acc[0][j] = f2_add(acc[0][j], gn);
+          acc[1][j] = f2_fma(gn, xh, acc[1][j]);
         } else {
-          float h[8];
-          cvt8(*reinterpret_cast<const uint4*>(st + 2 * CK_BOX_BYTES + off), h);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float xh = fmaf(z[i], rstd[i], mean[i]);
-            const float gn = xh > 0.f ? g[i] : g[i] * slope;
-            acc[0][i] += h[i]; acc[1][i] = fmaf(h[i], xh, acc[1][i]); acc[2 % NSUM][i] += gn;
-            acc[3 % NSUM][i] = fmaf(gn, xh, acc[3 % NSUM][i]); acc[4 % NSUM][i] = fmaf(h[i], gn, acc[4 % NSUM][i]);
-          }
+          const f32x2 h = f2_bf16x2(hq[j]);
+          acc[0][j] = f2_add(acc[0][j], h);
+          acc[1][j] = f2_fma(h, xh, acc[1][j]);
+          acc[2 % NSUM][j] = f2_add(acc[2 % NSUM][j], gn);
+          acc[3 % NSUM][j] = f2_fma(gn, xh, acc[3 % NSUM][j]);
+          acc[4 % NSUM][j] = f2_fma(h, gn, acc[4 % NSUM][j]);
         }
       }
-      if (!resident) {
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[slot]);
-      }
     }
-    // block reduction: lanes with equal (lane & 7) hold the same channel vector
-#pragma unroll
-    for (int s2 = 0; s2 < NSUM; ++s2)
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        float v = acc[s2][i];
-        v += __shfl_xor_sync(0xffffffffu, v, 8);
-        v += __shfl_xor_sync(0xffffffffu, v, 16);
-        if (lane < 8) red[(s2 * 8 + warp) * 64 + cv * 8 + i] = v;
-      }
-    named_bar_sync(1, 256);
-    for (int i = t; i < NSUM * 64; i += 256) {
-      const int s2 = i >> 6, c = i & 63;
-      float v = 0.f;
-#pragma unroll
-      for (int w = 0; w < 8; ++w) v += red[(s2 * 8 + w) * 64 + c];
-      part[i] = v;
+    if (!resident) {
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
     }
+    if (++slot == RS) { slot = 0; par ^= 1; }
   }
-  // ---- exchange the CS partial vectors through distributed shared memory (consumer warps only from here on)
+  // block reduction: lanes with equal (lane & 7) hold the same channel vector
+#pragma unroll
+  for (int s2 = 0; s2 < NSUM; ++s2)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float v0, v1;
+      f2_split(acc[s2][j], v0, v1);
+      v0 += __shfl_xor_sync(0xffffffffu, v0, 8); v1 += __shfl_xor_sync(0xffffffffu, v1, 8);
+      v0 += __shfl_xor_sync(0xffffffffu, v0, 16); v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
+      if (lane < 8) {
+        red[(s2 * 8 + warp) * 64 + cv * 8 + 2 * j] = v0;
+        red[(s2 * 8 + warp) * 64 + cv * 8 + 2 * j + 1] = v1;
+      }
+    }
+  named_bar_sync(1, 256);
+  for (int i = t; i < NSUM * 64; i += 256) {
+    const int s2 = i >> 6, c = i & 63;
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += red[(s2 * 8 + w) * 64 + c];
+    part[i] = v;
+  }
+  // ---- exchange the CS partial vectors through distributed shared memory
   if (CS > 1) {
     cluster_arrive();
     cluster_wait();
   } else {
     named_bar_sync(1, 256);
   }
-  {
-    for (int i = t; i < NSUM * 64; i += 256) {
-      float v = 0.f;
-      if (CS > 1) {
-        for (int r = 0; r < CS; ++r) v += ld_dsmem_f32(part + i, (uint32_t)r);
-      } else {
-        v = part[i];
-      }
-      tot[i] = v;
+  for (int i = t; i < NSUM * 64; i += 256) {
+    float v = part[i];
+    if (CS > 1) {
+      float pv[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) pv[r] = r < CS ? ld_dsmem_f32(part + i, (uint32_t)r) : 0.f;  // all loads in flight at once
+      v = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) v += pv[r];  // rank order: identical on every CTA of the cluster
     }
-    named_bar_sync(1, 256);
+    tot[i] = v;
   }
+  named_bar_sync(1, 256);
   if (CS > 1) cluster_arrive();  // peers may exit only after everyone has read their `part` (waited on before exit)
-  {
-    const int cv = t & 7, prow = t >> 3;
-    const int c0 = cg * 64 + cv * 8;
-    float mean[8], rstd[8], sm[NSUM][8];
-    load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
-    const float inv = 1.f / (float)a.HW, slope = a.slope;
+  // ---- phase 2: outputs
+  const float inv = 1.f / (float)a.HW;
+  f32x2 sm[NSUM][4];
 #pragma unroll
-    for (int s2 = 0; s2 < NSUM; ++s2)
+  for (int s2 = 0; s2 < NSUM; ++s2)
 #pragma unroll
-      for (int i = 0; i < 8; ++i) sm[s2][i] = tot[s2 * 64 + cv * 8 + i] * inv;
-    // ---- phase 2: outputs
-    for (int k = 0; k < nst; ++k) {
-      const int kk = resident ? k : nst + k;
-      const int slot = kk % RS;
-      if (!resident) mbar_wait(&full[slot], (kk / RS) & 1);
-      const uint8_t* st = ring + (size_t)slot * Cfg::STAGE_BYTES;
+    for (int j = 0; j < 4; ++j) sm[s2][j] = f2_pack(tot[s2 * 64 + cv * 8 + 2 * j] * inv, tot[s2 * 64 + cv * 8 + 2 * j + 1] * inv);
+  // bwd : o = (gn - m0 - xh m1) rstd = fma(gn, rstd, fma(xh, c1, c0)),  c0 = -m0 rstd, c1 = -m1 rstd
+  // bwd2: Ph = h - mh - xh ma, Pg = gn - mg - xh mc, q = mhg - mh mg - ma mc,
+  //       og = Ph rstd dact,  oz = -(q xh + mc Ph + ma Pg) rstd^2
+  // bwd2 expanded so that every output is a short FMA chain over per-channel constants:
+  //   og = (h rstd + E + xh F) dact,            E = -mh rstd, F = -ma rstd
+  //   oz = A xh + B h + Cg gn + D,              A = -rstd^2 (q - 2 ma mc), B = -rstd^2 mc, Cg = -rstd^2 ma, D = rstd^2 (mc mh + ma mg)
+  f32x2 c0v[4], c1v[4], cA[MODE == M_BWD2 ? 4 : 1], cB[MODE == M_BWD2 ? 4 : 1], cC[MODE == M_BWD2 ? 4 : 1], cD[MODE == M_BWD2 ? 4 : 1];
+  const f32x2 neg1 = f2_pack(-1.f, -1.f);
 #pragma unroll
-      for (int u = 0; u < CK_PIXB / 32; ++u) {
-        const int r = u * 32 + prow;
-        const int off = r * 128 + ((cv ^ (r & 7)) << 4);
-        const long long pix = pix0 + (long long)k * CK_PIXB + r;
-        float z[8], g[8];
-        cvt8(*reinterpret_cast<const uint4*>(st + off), z);
-        cvt8(*reinterpret_cast<const uint4*>(st + CK_BOX_BYTES + off), g);
-        if (MODE == M_BWD) {
-          float o[8];
+  for (int j = 0; j < 4; ++j) {
+    if (MODE == M_BWD) {
+      c0v[j] = f2_mul(f2_mul(sm[0][j], rstd2[j]), neg1);
+      c1v[j] = f2_mul(f2_mul(sm[1][j], rstd2[j]), neg1);
+    } else {
+      const f32x2 mh = sm[0][j], ma = sm[1][j], mg = sm[2 % NSUM][j], mc = sm[3 % NSUM][j], mhg = sm[4 % NSUM][j];
+      const f32x2 nr2 = f2_mul(f2_mul(rstd2[j], rstd2[j]), neg1);                         // -rstd^2
+      const f32x2 q = f2_fma(f2_fma(mh, mg, f2_mul(ma, mc)), neg1, mhg);                   // mhg - mh mg - ma mc
+      const f32x2 mamc = f2_mul(ma, mc);
+      cA[j % (MODE == M_BWD2 ? 4 : 1)] = f2_mul(nr2, f2_fma(f2_add(mamc, mamc), neg1, q));
+      cB[j % (MODE == M_BWD2 ? 4 : 1)] = f2_mul(nr2, mc);
+      cC[j % (MODE == M_BWD2 ? 4 : 1)] = f2_mul(nr2, ma);
+      cD[j % (MODE == M_BWD2 ? 4 : 1)] = f2_mul(f2_mul(nr2, neg1), f2_fma(mc, mh, f2_mul(ma, mg)));
+      c0v[j] = f2_mul(f2_mul(mh, rstd2[j]), neg1);                                         // E
+      c1v[j] = f2_mul(f2_mul(ma, rstd2[j]), neg1);                                         // F
+    }
+  }
+  const long long obase = (pix0 + prow) * 1;  // pixel row of u = 0, stage 0
+  for (int k = 0; k < nst; ++k) {
+    if (!resident) mbar_wait(&full[slot], par);
+    const uint8_t* st = ring + (size_t)(resident ? k : slot) * Cfg::STAGE_BYTES + off0;
+#pragma unroll(MODE == M_BWD2 ? 1 : 2)
+    for (int u = 0; u < CK_PIXB / 32; ++u) {
+      const long long pix = obase + (long long)k * CK_PIXB + u * 32;
+      const uint4 zw = *reinterpret_cast<const uint4*>(st + u * 4096);
+      const uint4 gw = *reinterpret_cast<const uint4*>(st + CK_BOX_BYTES + u * 4096);
+      const uint32_t zq[4] = {zw.x, zw.y, zw.z, zw.w}, gq[4] = {gw.x, gw.y, gw.z, gw.w};
+      if (MODE == M_BWD) {
+        uint32_t o[4];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float xh = fmaf(z[i], rstd[i], mean[i]);
-            const float gn = xh > 0.f ? g[i] : g[i] * slope;
-            o[i] = (gn - sm[0][i] - xh * sm[1][i]) * rstd[i];
-          }
-          store8(a.o0 + pix * a.ldo0 + c0, o);
-        } else {
-          float h[8], og[8], oz[8];
-          cvt8(*reinterpret_cast<const uint4*>(st + 2 * CK_BOX_BYTES + off), h);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float xh = fmaf(z[i], rstd[i], mean[i]);
-            const float da = xh > 0.f ? 1.f : slope;
-            const float gn = g[i] * da;
-            const float mh = sm[0][i], ma = sm[1][i], mg = sm[2 % NSUM][i], mc = sm[3 % NSUM][i], mhg = sm[4 % NSUM][i];
-            const float q = mhg - mh * mg - ma * mc;
-            const float Ph = h[i] - mh - xh * ma, Pg = gn - mg - xh * mc;
-            og[i] = Ph * rstd[i] * da;
-            oz[i] = -(q * xh + mc * Ph + ma * Pg) * rstd[i] * rstd[i];
-          }
-          store8(a.o0 + pix * a.ldo0 + c0, og);
-          store8(a.o1 + pix * a.ldo1 + c0, oz);
+        for (int j = 0; j < 4; ++j) {
+          const f32x2 xh = f2_fma(f2_bf16x2(zq[j]), rstd2[j], shift2[j]);
+          const f32x2 gn = f2_mul(f2_bf16x2(gq[j]), f2_dact(xh, k0, k1));
+          o[j] = f2_to_bf16x2(f2_fma(gn, rstd2[j], f2_fma(xh, c1v[j], c0v[j])));
         }
+        *reinterpret_cast<uint4*>(a.o0 + pix * a.ldo0 + c0) = make_uint4(o[0], o[1], o[2], o[3]);
+      } else {
+        const uint4 hw = *reinterpret_cast<const uint4*>(st + 2 * CK_BOX_BYTES + u * 4096);
+        const uint32_t hq[4] = {hw.x, hw.y, hw.z, hw.w};
+        uint32_t og[4], oz[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          constexpr int M4 = MODE == M_BWD2 ? 4 : 1;
+          const f32x2 xh = f2_fma(f2_bf16x2(zq[j]), rstd2[j], shift2[j]);
+          const f32x2 da = f2_dact(xh, k0, k1);
+          const f32x2 gn = f2_mul(f2_bf16x2(gq[j]), da);
+          const f32x2 h = f2_bf16x2(hq[j]);
+          og[j] = f2_to_bf16x2(f2_mul(f2_fma(h, rstd2[j], f2_fma(xh, c1v[j], c0v[j])), da));
+          oz[j] = f2_to_bf16x2(f2_fma(xh, cA[j % M4], f2_fma(h, cB[j % M4], f2_fma(gn, cC[j % M4], cD[j % M4]))));
+        }
+        *reinterpret_cast<uint4*>(a.o0 + pix * a.ldo0 + c0) = make_uint4(og[0], og[1], og[2], og[3]);
+        *reinterpret_cast<uint4*>(a.o1 + pix * a.ldo1 + c0) = make_uint4(oz[0], oz[1], oz[2], oz[3]);
       }
-      if (!resident) {
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[slot]);
-      }
+    }
+    if (!resident) {
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
+      if (++slot == RS) { slot = 0; par ^= 1; }
     }
   }
   if (CS > 1) cluster_wait();
