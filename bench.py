@@ -54,7 +54,29 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="step eagerly instead of replaying the captured CUDA graph")
     ap.add_argument("--mode", default="train", choices=["train", "infer"],
                     help="infer = BASELINE configs[4]: generator-only eval forward (cgan/inference.py:170-171), default batch 256")
-    return ap.parse_args()
+    ap.add_argument("--config", default=None, choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"],
+                    help="BASELINE.json configs by number: cfg1 = B 4 S 256 (the CPU plumbing case), cfg2/cfg3 = B 64/GPU S 256 "
+                         "(default; cfg3 is cfg2 under torchrun), cfg4 = B 16/GPU S 512, cfg5 = generator-only forward, B 256")
+    a = ap.parse_args()
+    if a.config == "cfg1":
+        a.batch, a.img_size = 4, 256
+    elif a.config == "cfg4":
+        a.batch, a.img_size = 16, 512
+    elif a.config == "cfg5":
+        a.mode = "infer"
+    return a
+
+
+def workload_config(args, world):
+    """The `config` block, identical for the B200 arm and the reference arm (the reference arm steps a bounded SAMPLE of this
+    workload, described in its cpu_baseline.sample)."""
+    S, B = args.img_size, args.batch
+    name = {(64, 256): "configs[1]" if world == 1 else "configs[2]", (16, 512): "configs[3]", (4, 256): "configs[0]"}.get((B, S), "custom")
+    return {"workload": f"BASELINE {name}: cGAN G+D train step (n_critic={N_CRITIC}, lambda_gp={LAMBDA_GP}, spectral norm, "
+                        f"clip+Adam), bf16 storage / fp32 accumulate, batch {B} synthetic {S}x{S} paired patches per GPU",
+            "img_size": S, "batch_per_gpu": B, "global_batch": B * world, "parallelism": f"dp{world}",
+            "l2": "per-step working set (activation stash > 4 GB at B=64,S=256) far exceeds the 126 MB L2; two input "
+                  "batches alternate"}
 
 
 # --------------------------------------------------------------------------------------------- FLOP model (SURVEY §8d)
@@ -128,6 +150,73 @@ def gemm_flops(name, a):
     return 2.0 * N * H * W * Cout * 16 * Cin
 
 
+def kernel_families(timed, K, adam_bytes):
+    """Aggregate the CUDA-event records of _lib.time_kernels over K steps -> (tensor-core families, bandwidth families)."""
+    timed = dict(timed)
+    bwfam = {}
+    for name in BW_KERNELS:
+        recs = timed.pop(name, [])
+        if not recs:
+            continue
+        ms = sum(a.elapsed_time(b) for a, b, _ in recs)
+        if name == "b2c_multi_adam":  # launch order within a step: D, D, G
+            nb = sum(adam_bytes[i % len(adam_bytes)] for i in range(len(recs)))
+        else:
+            nb = sum(bw_bytes(name, sc) or 0 for _, _, sc in recs)
+        bwfam[name] = {"launches_per_step": len(recs) / K, "ms_per_step": ms / K, "gbs": nb / ms / 1e6 if ms else 0.0,
+                       "bytes_per_launch": nb / len(recs), "ms_per_launch": ms / len(recs)}
+    fam = {}
+    for name, recs in timed.items():
+        if not recs:
+            continue
+        ms = sum(a.elapsed_time(b) for a, b, _ in recs)
+        fl = sum(gemm_flops(name, sc) for _, _, sc in recs)
+        fam[name] = {"launches_per_step": len(recs) / K, "ms_per_step": ms / K, "tflops": fl / ms / 1e9 if ms else 0.0,
+                     "flop_per_launch": fl / max(len(recs), 1), "ms_per_launch": ms / max(len(recs), 1)}
+    return fam, bwfam
+
+
+def roofline_blocks(fam, bwfam, ms_step):
+    """-> (`roofline`: dominant tensor-core family vs the measured sustained bf16 peak, `roofline_bw`: dominant bandwidth
+    kernel vs the measured HBM copy bandwidth), both from durations measured live with CUDA events."""
+    peaks = {}
+    pk = ROOT / "MEASURED_PEAKS.json"
+    if pk.exists():
+        peaks = json.loads(pk.read_text())
+    peak_tf, peak_src = peaks.get("bf16_tflops_sustained", 1400.0), ("measured" if peaks else "fallback")
+    peak_bw = peaks.get("hbm_gbs", 6500.0)
+    roofline = None
+    if fam:
+        dom = max(fam, key=lambda n: fam[n]["ms_per_step"])
+        total_ms = sum(f["ms_per_step"] for f in fam.values())
+        total_tf = sum(f["tflops"] * f["ms_per_step"] for f in fam.values()) / total_ms if total_ms else 0.0
+        traffic = None  # ncu dram__bytes_read+write per launch of the dominant family (one --set full capture of a step)
+        for tfn in ("r02_traffic.json", "r01_traffic.json"):
+            tf = ROOT / "profiles" / tfn
+            if tf.exists():
+                traffic = json.loads(tf.read_text()).get(dom, {}).get("dram_bytes_per_launch")
+                break
+        roofline = {"bound": "tensor", "kernel": dom, "achieved": fam[dom]["tflops"], "peak": peak_tf, "unit": "TFLOP/s",
+                    "frac": fam[dom]["tflops"] / peak_tf, "traffic": traffic, "peak_source": peak_src + " bf16_tflops_sustained",
+                    "flop_per_launch": fam[dom]["flop_per_launch"], "ms_per_launch": fam[dom]["ms_per_launch"],
+                    "share_of_step": fam[dom]["ms_per_step"] / ms_step,
+                    "all_tensor_kernels": {"tflops": total_tf, "frac": total_tf / peak_tf, "share_of_step": total_ms / ms_step}}
+    roofline_bw = None
+    if bwfam:
+        bdom = max(bwfam, key=lambda n: bwfam[n]["ms_per_step"])
+        bms = sum(f["ms_per_step"] for f in bwfam.values())
+        bgbs = sum(f["gbs"] * f["ms_per_step"] for f in bwfam.values()) / bms if bms else 0.0
+        roofline_bw = {"bound": "hbm", "kernel": bdom, "achieved": bwfam[bdom]["gbs"], "peak": peak_bw, "unit": "GB/s",
+                       "frac": bwfam[bdom]["gbs"] / peak_bw, "peak_source": peak_src + " hbm_gbs",
+                       "bytes_per_launch": bwfam[bdom]["bytes_per_launch"], "ms_per_launch": bwfam[bdom]["ms_per_launch"],
+                       "share_of_step": bwfam[bdom]["ms_per_step"] / ms_step,
+                       "all_bandwidth_kernels": {"gbs": bgbs, "frac": bgbs / peak_bw, "share_of_step": bms / ms_step},
+                       "per_kernel": {n: {"gbs": round(f["gbs"], 1), "frac": round(f["gbs"] / peak_bw, 3),
+                                          "ms_per_step": round(f["ms_per_step"], 4),
+                                          "launches_per_step": f["launches_per_step"]} for n, f in bwfam.items()}}
+    return roofline, roofline_bw
+
+
 # --------------------------------------------------------------------------------------------- clocks
 class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -199,8 +288,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": spstep * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"cGAN G+D train step, n_critic={N_CRITIC}, {S}x{S} patches, CPU sample of "
-                                   f"{sample} patches/step", "img_size": S, "batch_per_gpu": args.batch},
+            "config": workload_config(args, max(args.gpus, 1)),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -321,75 +409,18 @@ def run_b200(args):
     barrier()
     ms_eager = g0.elapsed_time(g1)
     _lib.time_kernels(None)
-    bwfam = {}
-    adam_bytes = [28 * tr.optD.total] * N_CRITIC + [28 * tr.optG.total]  # launch order within a step: D, D, G
-    for name in BW_KERNELS:
-        recs = timed.pop(name, [])
-        if not recs:
-            continue
-        ms = sum(a.elapsed_time(b) for a, b, _ in recs)
-        if name == "b2c_multi_adam":
-            nb = sum(adam_bytes[i % len(adam_bytes)] for i in range(len(recs)))
-        else:
-            nb = sum(bw_bytes(name, sc) or 0 for _, _, sc in recs)
-        bwfam[name] = {"launches_per_step": len(recs) / K, "ms_per_step": ms / K, "gbs": nb / ms / 1e6 if ms else 0.0,
-                       "bytes_per_launch": nb / len(recs), "ms_per_launch": ms / len(recs)}
-    fam = {}
-    for name, recs in timed.items():
-        ms = sum(a.elapsed_time(b) for a, b, _ in recs)
-        fl = sum(gemm_flops(name, sc) for _, _, sc in recs)
-        fam[name] = {"launches_per_step": len(recs) / K, "ms_per_step": ms / K, "tflops": fl / ms / 1e9 if ms else 0.0,
-                     "flop_per_launch": fl / max(len(recs), 1), "ms_per_launch": ms / max(len(recs), 1)}
-
+    fam, bwfam = kernel_families(timed, K, [28 * tr.optD.total] * N_CRITIC + [28 * tr.optG.total])
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    peaks = {}
-    pk = ROOT / "MEASURED_PEAKS.json"
-    if pk.exists():
-        peaks = json.loads(pk.read_text())
-    peak_tf, peak_src = peaks.get("bf16_tflops_sustained", 1400.0), ("measured" if peaks else "fallback")
-    dom = max(fam, key=lambda n: fam[n]["ms_per_step"])
-    total_ms = sum(f["ms_per_step"] for f in fam.values())
-    total_tf = sum(f["tflops"] * f["ms_per_step"] for f in fam.values()) / total_ms if total_ms else 0.0
-    traffic = None  # ncu dram__bytes_read+write per launch of the dominant family (one --set full capture of a step)
-    for tfn in ("r02_traffic.json", "r01_traffic.json"):
-        tf = ROOT / "profiles" / tfn
-        if tf.exists():
-            traffic = json.loads(tf.read_text()).get(dom, {}).get("dram_bytes_per_launch")
-            break
-    roofline = {"bound": "tensor", "kernel": dom, "achieved": fam[dom]["tflops"], "peak": peak_tf, "unit": "TFLOP/s",
-                "frac": fam[dom]["tflops"] / peak_tf, "traffic": traffic, "peak_source": peak_src + " bf16_tflops_sustained",
-                "flop_per_launch": fam[dom]["flop_per_launch"], "ms_per_launch": fam[dom]["ms_per_launch"],
-                "share_of_step": fam[dom]["ms_per_step"] / (ms_dev / K),
-                "all_tensor_kernels": {"tflops": total_tf, "frac": total_tf / peak_tf,
-                                       "share_of_step": total_ms / (ms_dev / K)}}
-    peak_bw = peaks.get("hbm_gbs", 6500.0)
-    roofline_bw = None
-    if bwfam:
-        bdom = max(bwfam, key=lambda n: bwfam[n]["ms_per_step"])
-        bms = sum(f["ms_per_step"] for f in bwfam.values())
-        bgbs = sum(f["gbs"] * f["ms_per_step"] for f in bwfam.values()) / bms if bms else 0.0
-        roofline_bw = {"bound": "hbm", "kernel": bdom, "achieved": bwfam[bdom]["gbs"], "peak": peak_bw, "unit": "GB/s",
-                       "frac": bwfam[bdom]["gbs"] / peak_bw, "peak_source": peak_src + " hbm_gbs",
-                       "bytes_per_launch": bwfam[bdom]["bytes_per_launch"], "ms_per_launch": bwfam[bdom]["ms_per_launch"],
-                       "share_of_step": bwfam[bdom]["ms_per_step"] / (ms_dev / K),
-                       "all_bandwidth_kernels": {"gbs": bgbs, "frac": bgbs / peak_bw, "share_of_step": bms / (ms_dev / K)},
-                       "per_kernel": {n: {"gbs": round(f["gbs"], 1), "frac": round(f["gbs"] / peak_bw, 3),
-                                          "ms_per_step": round(f["ms_per_step"], 4),
-                                          "launches_per_step": f["launches_per_step"]} for n, f in bwfam.items()}}
+    roofline, roofline_bw = roofline_blocks(fam, bwfam, ms_dev / K)
     value = world * B * K / (ms_dev / 1e3)
     useful = useful_flops_per_patch(S)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"BASELINE configs[1]: cGAN G+D train step (n_critic={N_CRITIC}, lambda_gp={LAMBDA_GP}, "
-                                   f"spectral norm, clip+Adam), bf16 storage / fp32 accumulate, batch {B} synthetic "
-                                   f"{S}x{S} paired patches per GPU", "img_size": S, "batch_per_gpu": B,
-                       "global_batch": B * world, "parallelism": f"dp{world}",
-                       "l2": "per-step working set (activation stash > 5 GB at B=64,S=256) far exceeds the 126 MB L2; "
-                             "two input batches alternate"},
+            "config": workload_config(args, world),
             "e2e": {"value": world * B * K / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K},
             "gpu_launches": launches, "cuda_graph": not args.no_graph, "eager_ms_per_step": ms_eager / K,
@@ -465,6 +496,29 @@ def run_infer(args):
         f1.record()
         torch.cuda.synchronize()
         ms2 = f0.elapsed_time(f1)
+        timed = _lib.time_kernels(GEMM_KERNELS + BW_KERNELS)
+        for i in range(K):
+            G(dev[i % 2])
+        torch.cuda.synchronize()
+        _lib.time_kernels(None)
+    fam, bwfam = kernel_families(timed, K, [0])
+    roofline, roofline_bw = roofline_blocks(fam, bwfam, ms / K)
+    cpu = None
+    if not args.no_cpu_baseline:
+        sys.path.insert(0, str(ROOT / "oracle"))
+        import cgan_oracle as O
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        st = O.init_state(42)
+        xs = torch.rand(args.cpu_sample * 4, 3, S, S) * 2 - 1
+        with torch.no_grad():
+            O.g_forward(st["G"], xs, 0.3, train=False)
+            t0 = time.perf_counter()
+            for _ in range(2):
+                O.g_forward(st["G"], xs, 0.3, train=False)
+            dt = (time.perf_counter() - t0) / 2
+        cpu = {"value": xs.shape[0] / dt, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{xs.shape[0]} patches {S}x{S} per forward, 2 forwards after 1 warm-up, fp32 torch CPU oracle"}
     fg = conv_flops_per_patch(S)[0]
     print(json.dumps({"metric": "cgan_infer_patches_per_s", "value": B * K / (ms / 1e3), "unit": UNIT, "n_gpus": 1,
                       "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
@@ -474,6 +528,7 @@ def run_infer(args):
                       "e2e": {"value": B * K / (ms2 / 1e3), "unit": UNIT, "h2d_bytes_per_step": host[0].numel() * 4,
                               "d2h_bytes_per_step": B * 16, "ms_per_step": ms2 / K},
                       "gpu_launches": launches, "useful_conv_tflops": fg * B / (ms / K) / 1e9,
+                      "roofline": roofline, "roofline_bw": roofline_bw, "kernels": fam, "cpu_baseline": cpu,
                       "finite": bool(torch.isfinite(d).all()) and bool(torch.isfinite(out).all())}), flush=True)
 
 

@@ -194,7 +194,8 @@ class WeightCtx:
 
 # ------------------------------------------------------------------------------------------------ raw kernel helpers
 def _stats_buf(N, C, device):
-    return torch.empty(N, C, 2, dtype=torch.float32, device=device)
+    """InstanceNorm statistics (sum z, sum z^2) per (image, channel): 64-bit fixed point, value = int64 * 2^-30."""
+    return torch.empty(N, C, 2, dtype=torch.int64, device=device)
 
 
 def _conv_raw(x, wctx, bias, want_stats=False):
@@ -348,11 +349,11 @@ def channel_sum(g):
     """sum over (n, h, w) of an NHWC bf16 tensor -> fp32 [C] (bias gradient)."""
     g, ld = as_nhwc(g)
     N, C, H, W = g.shape
-    zs = torch.empty(N, C, 2, dtype=torch.float32, device=g.device)
+    zs = _stats_buf(N, C, g.device)
     _lib.call("b2c_in_stats", g, ld, zs, N, H * W, C)
     out = torch.zeros(C, dtype=torch.float32, device=g.device)
     # zs[:, :, 0] summed over n: one strided rowsum per channel is wasteful; transpose-free trick: rowsum over (N) rows
-    tmp = zs[:, :, 0].t().contiguous()  # [C][N], tiny
+    tmp = (zs[:, :, 0].to(torch.float64) * 2.0 ** -30).to(torch.float32).t().contiguous()  # [C][N], tiny
     if N % 4 == 0:
         _lib.call("b2c_rowsum", tmp, N, C, 0, 1.0, out)
     else:
@@ -513,7 +514,7 @@ class LReluBwd(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------ InstanceNorm + act (+dropout, +concat)
 def _in_stats(z, ld):
     N, C, H, W = z.shape
-    zs = torch.empty(N, C, 2, dtype=torch.float32, device=z.device)
+    zs = _stats_buf(N, C, z.device)
     _lib.call("b2c_in_stats", z, ld, zs, N, H * W, C)
     return zs
 
@@ -620,7 +621,7 @@ class INActPoolFC(torch.autograd.Function):
         N, C, H, W = z.shape
         if zs is None:
             zs = _in_stats(z, ldz)
-        ps = torch.empty(2, N, C, dtype=torch.float32, device=z.device)  # planar (sum act(x_hat), sum act'(x_hat))
+        ps = torch.empty(2, N, C, dtype=torch.int64, device=z.device)  # planar fixed-point (sum act(x_hat), sum act'(x_hat))
         _lib.call("b2c_in_act_pool_fwd", z, ldz, zs, slope, ps, N, H * W, C)
         delta = torch.empty(N, 4, dtype=torch.float32, device=z.device)
         th = torch.empty_like(delta)

@@ -190,6 +190,16 @@ __device__ __forceinline__ float warp_transpose_sum32(float (&v)[32]) {
   }
   return v[0];
 }
+// InstanceNorm statistics (sum z, sum z^2 per (image, channel)) are accumulated from many tiles / CTAs.  Float atomics would
+// make them depend on the arrival order (run-to-run noise that bf16 roundings downstream amplify, and a generator whose
+// output is not reproducible); they are therefore kept as 64-bit FIXED-POINT sums (2^-30 resolution, +-8.6e9 range): integer
+// addition is associative, so the result is bit-identical whatever the order.
+constexpr float B2C_STAT_SCALE = 1073741824.f;
+__device__ __forceinline__ void stat_add(long long* p, float v) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(p), (unsigned long long)__float2ll_rn(v * B2C_STAT_SCALE));
+}
+__device__ __forceinline__ float stat_get(long long v) { return __ll2float_rn(v) * (1.f / B2C_STAT_SCALE); }
+
 // Named barrier over a subset of the CTA's warps (the 4 epilogue warps), id 1..15.
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");

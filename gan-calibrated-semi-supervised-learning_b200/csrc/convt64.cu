@@ -25,7 +25,7 @@ struct ConvT64Params {
   int kchunks;           // Cin / 64
   __nv_bfloat16* y;
   long long ldy;
-  float* stats;          // nullable: [N][64][2] += per-(image, channel) (sum, sum of squares) of y; needs BI == 1
+  long long* stats;      // nullable: [N][64][2] += fixed-point (stat_add) per-(image, channel) (sum, sum of squares) of y; needs BI == 1
   int f32out;            // fp32 check mode (b2c_set_f32_output): y is float*, accumulators stored unrounded
   const __nv_bfloat16* act;  // nullable: dense (N,2H,2W,64) activation a = LeakyReLU(z); y *= (a > 0 ? 1 : slope), i.e. the
   float slope;               // backward of the LeakyReLU that produced this conv's input, fused into its data gradient
@@ -329,9 +329,9 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
         named_bar_sync(1, 128);
         if (r < 64) {
           const float2 a = red[r], b = red[64 + r], c = red[128 + r], d = red[192 + r];
-          float* st = p.stats + ((long long)n0 * 64 + r) * 2;
-          atomicAdd(st, (a.x + b.x) + (c.x + d.x));
-          atomicAdd(st + 1, (a.y + b.y) + (c.y + d.y));
+          long long* st = p.stats + ((long long)n0 * 64 + r) * 2;
+          stat_add(st, (a.x + b.x) + (c.x + d.x));
+          stat_add(st + 1, (a.y + b.y) + (c.y + d.y));
         }
         named_bar_sync(1, 128);  // scratch may be overwritten by the next tile
       }
@@ -344,10 +344,10 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
 
 // x: (N,H,W,Cin) bf16 with pixel stride ldx; wpack_t: [4 parities][64][4*Cin] bf16 (pack.cu); y: (N,2H,2W,64) bf16
 // with pixel stride ldy; stats as in b2c_convt4s2_bf16.  Called by b2c_convt4s2_bf16 (tapgemm.cu) when Cout == 64.
-extern "C" int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream);  // norm.cu
+extern "C" int b2c_in_stats(const void* z, long long ldz, long long* zs, int N, int HW, int C, void* stream);  // norm.cu
 
 int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const float* scale, void* y, long long ldy,
-                    float* stats, const void* act, float slope, int N, int H, int W, int Cin, void* stream) {
+                    long long* stats, const void* act, float slope, int N, int H, int W, int Cin, void* stream) {
   extern int g_f32_output;  // tapgemm.cu
   ConvT64Params p;
   p.stats = nullptr;
@@ -392,7 +392,7 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const flo
   B2C_REQUIRE(!act || ((uintptr_t)act & 31) == 0, "convt64: act must be 32-byte aligned");
   const bool fuse_stats = stats && p.BI == 1;
   if (fuse_stats) {
-    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * (size_t)N * 64, (cudaStream_t)stream);
+    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(long long) * 2 * (size_t)N * 64, (cudaStream_t)stream);
     if (e != cudaSuccess) { b2c_set_error("convt64 stats memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
     p.stats = stats;
   }

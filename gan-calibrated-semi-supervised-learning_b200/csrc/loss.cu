@@ -321,20 +321,20 @@ extern "C" int b2c_zero(void* p, long long bytes, void* stream) {
 }
 
 // ---------------------------------------------------------------- G head: pooled -> Linear(C,4) -> tanh -> * scale
-// pooled_sums[N][C] are plane SUMS of the activated up4 output (norm.cu M_POOL); HW divides them.
-__global__ void pool_fc_fwd_kernel(const float* __restrict__ ps, const float* __restrict__ W, const float* __restrict__ bias,
+// pooled_sums[N][C] are plane SUMS of the activated up4 output (norm.cu M_POOL) in 64-bit fixed point (stat_get); HW divides them.
+__global__ void pool_fc_fwd_kernel(const long long* __restrict__ ps, const float* __restrict__ W, const float* __restrict__ bias,
                                    float scale, float inv_hw, float* __restrict__ delta, float* __restrict__ tanh_out, int N, int C) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N * 4) return;
   const int n = i >> 2, j = i & 3;
   float acc = bias[j];
-  for (int c = 0; c < C; ++c) acc += W[j * C + c] * ps[n * C + c] * inv_hw;
+  for (int c = 0; c < C; ++c) acc += W[j * C + c] * stat_get(ps[n * C + c]) * inv_hw;
   const float t = tanhf(acc);
   tanh_out[i] = t;
   delta[i] = t * scale;
 }
 // gdelta[N][4] -> dW[4][C], db[4] (overwritten), gvec[N][C] = d loss / d (each element of the activated plane)
-__global__ void pool_fc_bwd_kernel(const float* __restrict__ gdelta, const float* __restrict__ tanh_v, const float* __restrict__ ps,
+__global__ void pool_fc_bwd_kernel(const float* __restrict__ gdelta, const float* __restrict__ tanh_v, const long long* __restrict__ ps,
                                    const float* __restrict__ W, float scale, float inv_hw, float* __restrict__ dW,
                                    float* __restrict__ db, float* __restrict__ gvec, int N, int C) {
   extern __shared__ float dpre[];  // [N][4]
@@ -343,7 +343,7 @@ __global__ void pool_fc_bwd_kernel(const float* __restrict__ gdelta, const float
   for (int i = threadIdx.x; i < 4 * C; i += blockDim.x) {
     const int j = i / C, c = i % C;
     float acc = 0.f;
-    for (int n = 0; n < N; ++n) acc += dpre[n * 4 + j] * ps[n * C + c] * inv_hw;
+    for (int n = 0; n < N; ++n) acc += dpre[n * 4 + j] * stat_get(ps[n * C + c]) * inv_hw;
     dW[i] = acc;
   }
   if (threadIdx.x < 4) {
@@ -358,12 +358,12 @@ __global__ void pool_fc_bwd_kernel(const float* __restrict__ gdelta, const float
     gvec[i] = acc * inv_hw;
   }
 }
-extern "C" int b2c_pool_fc_fwd(const float* pooled_sums, const float* W, const float* bias, float scale, int HW,
+extern "C" int b2c_pool_fc_fwd(const long long* pooled_sums, const float* W, const float* bias, float scale, int HW,
                                float* delta, float* tanh_out, int N, int C, void* stream) {
   pool_fc_fwd_kernel<<<(N * 4 + 127) / 128, 128, 0, (cudaStream_t)stream>>>(pooled_sums, W, bias, scale, 1.f / (float)HW, delta, tanh_out, N, C);
   return b2c_check_launch("pool_fc_fwd");
 }
-extern "C" int b2c_pool_fc_bwd(const float* gdelta, const float* tanh_v, const float* pooled_sums, const float* W,
+extern "C" int b2c_pool_fc_bwd(const float* gdelta, const float* tanh_v, const long long* pooled_sums, const float* W,
                                float scale, int HW, float* dW, float* db, float* gvec, int N, int C, void* stream) {
   B2C_REQUIRE(N * 16 <= 48 * 1024, "pool_fc_bwd: N=%d too large", N);
   pool_fc_bwd_kernel<<<1, 512, N * 4 * sizeof(float), (cudaStream_t)stream>>>(gdelta, tanh_v, pooled_sums, W, scale, 1.f / (float)HW, dW, db, gvec, N, C);

@@ -15,8 +15,8 @@ struct NormArgs {
   const float* gvec;                       // alternative: grad broadcast per (n,c) (pooled head), already / HW
   const __nv_bfloat16* h; long long ldh;   // cotangent on g_z (double backward)
   const uint8_t* mask;                     // dense dropout keep-mask [N*HW*C] or null
-  const float* zs;                         // [N][C][2] raw (sum z, sum z^2)
-  const float* fsums;                      // gvec mode only, nullable: planar [2][N][C] (sum act(x_hat), sum act'(x_hat)) from
+  const long long* zs;                     // [N][C][2] raw (sum z, sum z^2), 64-bit fixed point (common.cuh: stat_add / stat_get)
+  const long long* fsums;                  // gvec mode only, nullable: planar fixed-point [2][N][C] (sum act(x_hat), sum act'(x_hat)) from
                                            // b2c_in_act_pool_fwd: the backward's plane sums follow without a reduction pass
   float* sums;                             // [N][C][NS] plane sums produced by reduce / consumed by apply
   __nv_bfloat16* o0; long long ldo0;
@@ -51,16 +51,15 @@ __device__ __forceinline__ void load_mask8(const uint8_t* m, long long idx, floa
 }
 // Normalisation constants of 8 consecutive channels from the raw sums: rstd and shift = -mean * rstd, so that
 // x_hat = fma(z, rstd, shift) is one instruction per element (`mean` below holds the shift).
-__device__ __forceinline__ void load_stats8(const float* zs, int n, int C, int c0, int HW, float (&mean)[8], float (&rstd)[8]) {
+__device__ __forceinline__ void load_stats8(const long long* zs, int n, int C, int c0, int HW, float (&mean)[8], float (&rstd)[8]) {
   const float inv = 1.f / (float)HW;
-  const float4* p = reinterpret_cast<const float4*>(zs + ((long long)n * C + c0) * 2);
+  const longlong2* p = reinterpret_cast<const longlong2*>(zs + ((long long)n * C + c0) * 2);
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const float4 v = __ldg(p + j);
-    const float m0 = v.x * inv, m1 = v.z * inv;
-    rstd[2 * j] = rsqrtf(fmaxf(v.y * inv - m0 * m0, 0.f) + 1e-5f);
-    rstd[2 * j + 1] = rsqrtf(fmaxf(v.w * inv - m1 * m1, 0.f) + 1e-5f);
-    mean[2 * j] = -m0 * rstd[2 * j]; mean[2 * j + 1] = -m1 * rstd[2 * j + 1];
+  for (int j = 0; j < 8; ++j) {
+    const longlong2 v = __ldg(p + j);
+    const float m = stat_get(v.x) * inv;
+    rstd[j] = rsqrtf(fmaxf(stat_get(v.y) * inv - m * m, 0.f) + 1e-5f);
+    mean[j] = -m * rstd[j];
   }
 }
 
@@ -255,7 +254,8 @@ __global__ void __launch_bounds__(256, MODE == 3 ? 2 : 3) plane_reduce_kernel(No
     const int s = i / a.C, c = i % a.C;
     float t = 0.f;
     for (int r = 0; r < rows; ++r) t += red[((long long)s * rows + r) * a.C + c];
-    if (MODE == M_POOL) atomicAdd(a.sums + ((long long)s * a.N + n) * a.C + c, t);  // planar [2][N][C]
+    if (MODE == M_POOL) stat_add(reinterpret_cast<long long*>(a.sums) + ((long long)s * a.N + n) * a.C + c, t);  // planar [2][N][C], fixed point
+    else if (MODE == M_FWD) stat_add(reinterpret_cast<long long*>(a.sums) + ((long long)n * a.C + c) * ns + s, t);  // fixed point
     else atomicAdd(a.sums + ((long long)n * a.C + c) * ns + s, t);
   }
 }
@@ -277,11 +277,11 @@ __global__ void __launch_bounds__(256, MODE == 3 ? 2 : 3) plane_apply_kernel(Nor
       for (int i = 0; i < 8; ++i) gv[i] = __ldg(a.gvec + (long long)n * a.C + c0 + i);
     }
     if (MODE == M_BWD && a.fsums) {  // g = gv * act'(x_hat): sum g = gv * sum act', sum g x_hat = gv * sum act(x_hat)
-      const float* f = a.fsums + (long long)n * a.C + c0;
+      const long long* f = a.fsums + (long long)n * a.C + c0;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        sm[0][i] = gv[i] * __ldg(f + (long long)a.N * a.C + i) * inv;
-        sm[1 % ns][i] = gv[i] * __ldg(f + i) * inv;
+        sm[0][i] = gv[i] * stat_get(__ldg(f + (long long)a.N * a.C + i)) * inv;
+        sm[1 % ns][i] = gv[i] * stat_get(__ldg(f + i)) * inv;
       }
     } else {
       const float* s = a.sums + ((long long)n * a.C + c0) * ns;
@@ -820,7 +820,7 @@ static int plane_splits(int N, int HW, int C, int target) {
 template <int MODE>
 static int launch_reduce(const NormArgs& a, cudaStream_t st) {
   constexpr int ns = NS<MODE>::v;
-  cudaError_t e = cudaMemsetAsync(a.sums, 0, sizeof(float) * (size_t)a.N * a.C * ns, st);
+  cudaError_t e = cudaMemsetAsync(a.sums, 0, ((MODE == M_FWD || MODE == M_POOL) ? sizeof(long long) : sizeof(float)) * (size_t)a.N * a.C * ns, st);
   if (e != cudaSuccess) { b2c_set_error("norm memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
   constexpr int LM = (MODE == M_FWD || MODE == M_POOL) ? M_POOL : MODE;
   constexpr size_t red_bytes = sizeof(float) * 2048 * ns, ring_bytes = Ring<LM>::BYTES;
@@ -845,21 +845,21 @@ static int launch_apply(const NormArgs& a, cudaStream_t st) {
   plane_apply_kernel<MODE><<<grid, 256, Ring<MODE>::BYTES, st>>>(a);
   return b2c_check_launch("plane_apply");
 }
-static NormArgs base_args(const void* z, long long ldz, const float* zs, int N, int HW, int C, float slope) {
+static NormArgs base_args(const void* z, long long ldz, const long long* zs, int N, int HW, int C, float slope) {
   NormArgs a = {};
   a.z = (const __nv_bfloat16*)z; a.ldz = ldz; a.zs = zs; a.N = N; a.HW = HW; a.C = C; a.slope = slope;
   return a;
 }
 
 // zs[N][C][2] <- (sum z, sum z^2) per plane.
-extern "C" int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream) {
+extern "C" int b2c_in_stats(const void* z, long long ldz, long long* zs, int N, int HW, int C, void* stream) {
   NormArgs a = base_args(z, ldz, nullptr, N, HW, C, 0.f);
-  a.sums = zs;
+  a.sums = reinterpret_cast<float*>(zs);
   if (int rc = norm_check(a, "in_stats")) return rc;
   return launch_reduce<M_FWD>(a, (cudaStream_t)stream);
 }
 // o0 (and optionally o1) <- dropout(act(IN(z))).  mask: dense u8 keep-mask or null; kept values are scaled by 2.
-extern "C" int b2c_in_act_fwd(const void* z, long long ldz, const float* zs, const uint8_t* mask, float slope, void* o0,
+extern "C" int b2c_in_act_fwd(const void* z, long long ldz, const long long* zs, const uint8_t* mask, float slope, void* o0,
                               long long ldo0, void* o1, long long ldo1, int N, int HW, int C, void* stream) {
   NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
   a.mask = mask; a.o0 = (__nv_bfloat16*)o0; a.ldo0 = ldo0; a.o1 = (__nv_bfloat16*)o1; a.ldo1 = ldo1;
@@ -868,16 +868,16 @@ extern "C" int b2c_in_act_fwd(const void* z, long long ldz, const float* zs, con
 }
 // pooled_sums: planar [2][N][C] <- (sum over the plane of act(IN(z)), sum of act'(IN(z))): the global-average-pool numerator
 // (models.py:118,139) and what lets b2c_in_act_bwd(gvec, fwd_sums = pooled_sums) skip its reduction pass
-extern "C" int b2c_in_act_pool_fwd(const void* z, long long ldz, const float* zs, float slope, float* pooled_sums, int N,
-                                   int HW, int C, void* stream) {
+extern "C" int b2c_in_act_pool_fwd(const void* z, long long ldz, const long long* zs, float slope, long long* pooled_sums,
+                                   int N, int HW, int C, void* stream) {
   NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
-  a.sums = pooled_sums;
+  a.sums = reinterpret_cast<float*>(pooled_sums);
   if (int rc = norm_check(a, "in_act_pool_fwd")) return rc;
   return launch_reduce<M_POOL>(a, (cudaStream_t)stream);
 }
 // gz <- d/dz of dropout(act(IN(z))) given g (full tensor) or gvec (per-(n,c) broadcast).  ws: fp32 [N][C][2] scratch.
-extern "C" int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const float* fwd_sums, const void* z,
-                              long long ldz, const float* zs, const uint8_t* mask, float slope, float* ws, void* gz,
+extern "C" int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const long long* fwd_sums, const void* z,
+                              long long ldz, const long long* zs, const uint8_t* mask, float slope, float* ws, void* gz,
                               long long ldgz, int N, int HW, int C, void* stream) {
   NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
   a.g = (const __nv_bfloat16*)g; a.ldg = ldg; a.gvec = gvec; a.mask = mask; a.sums = ws;
@@ -913,7 +913,7 @@ extern "C" int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, c
 }
 // Double backward of b2c_in_act_bwd: cotangent h on gz -> gg (wrt g) and gx (wrt z).  ws: fp32 [N][C][5] scratch.
 extern "C" int b2c_in_act_bwd2(const void* h, long long ldh, const void* g, long long ldg, const void* z, long long ldz,
-                               const float* zs, const uint8_t* mask, float slope, float* ws, void* gg, long long ldgg,
+                               const long long* zs, const uint8_t* mask, float slope, float* ws, void* gg, long long ldgg,
                                void* gx, long long ldgx, int N, int HW, int C, void* stream) {
   NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
   a.g = (const __nv_bfloat16*)g; a.ldg = ldg; a.h = (const __nv_bfloat16*)h; a.ldh = ldh; a.mask = mask; a.sums = ws;

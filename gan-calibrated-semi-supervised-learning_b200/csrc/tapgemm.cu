@@ -32,7 +32,7 @@ struct TapGemmParams {
   const float* scale;       // nullable device scalar: y = acc * scale + bias (spectral norm: 1/sigma, W_eff = W/sigma)
   float* gx0;               // mode D1: fp32 (N,3,2Ho,2Wo) outputs (gx1 null when Cin = 3)
   float* gx1;
-  float* stats;             // nullable: [N][Cout][2] += per-(image, channel) (sum, sum of squares) of y; needs BI == 1
+  long long* stats;         // nullable: [N][Cout][2] += fixed-point (stat_add) per-(image, channel) (sum, sum of squares) of y; needs BI == 1
   int f32out;               // fp32 check mode: y is float* and the accumulators are stored unrounded
   int st256;                // y and ldy allow 32-byte (STG.256) stores
 };
@@ -237,9 +237,9 @@ __global__ void __launch_bounds__(64 + 128 * MT) tapgemm_kernel(const __grid_con
         float sx = 0.f, sy = 0.f;
 #pragma unroll
         for (int w = 0; w < 4 * MT; ++w) { sx += red[w * BN + c].x; sy += red[w * BN + c].y; }
-        float* st = p.stats + ((long long)n0 * p.Cout + ncol0 + c) * 2;
-        atomicAdd(st, sx);
-        atomicAdd(st + 1, sy);
+        long long* st = p.stats + ((long long)n0 * p.Cout + ncol0 + c) * 2;
+        stat_add(st, sx);
+        stat_add(st + 1, sy);
       }
     }
     tc_fence_before();
@@ -434,9 +434,9 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
         named_bar_sync(1, 128);
         for (int c = r; c < BN; c += 128) {
           const float2 a = red[c], b = red[BN + c], cc = red[2 * BN + c], d = red[3 * BN + c];
-          float* st = p.stats + ((long long)n0 * p.Cout + ncol0 + c) * 2;
-          atomicAdd(st, (a.x + b.x) + (cc.x + d.x));
-          atomicAdd(st + 1, (a.y + b.y) + (cc.y + d.y));
+          long long* st = p.stats + ((long long)n0 * p.Cout + ncol0 + c) * 2;
+          stat_add(st, (a.x + b.x) + (cc.x + d.x));
+          stat_add(st + 1, (a.y + b.y) + (cc.y + d.y));
         }
         named_bar_sync(1, 128);  // scratch may be overwritten by the next tile
       }
@@ -477,7 +477,7 @@ static int launch_tapgemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
   return b2c_check_launch("tapgemm_kernel");
 }
 
-extern "C" int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream);  // norm.cu
+extern "C" int b2c_in_stats(const void* z, long long ldz, long long* zs, int N, int HW, int C, void* stream);  // norm.cu
 
 // fp32 check mode (BASELINE north_star: "<= 1e-4 for an fp32 check mode"): while on, conv4s2 / convt4s2 treat `y` as
 // float* (ldy in floats) and store the fp32 TMEM accumulators (+bias) without the bf16 rounding, so a test can hold the
@@ -489,7 +489,7 @@ extern "C" int b2c_set_f32_output(int on, void* /*stream: unused, uniform call s
 }
 
 static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack, const float* scale, const float* bias, void* y,
-                       long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
+                       long long ldy, long long* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
   B2C_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "tapgemm: Cin=%d Cout=%d must be multiples of 64", Cin, Cout);
   B2C_REQUIRE(ldy % 8 == 0 && ((uintptr_t)y & 15) == 0, "tapgemm: output must be 16-byte aligned (ldy=%lld)", ldy);
   TapGemmParams p;
@@ -540,7 +540,7 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
   }
   const bool fuse_stats = stats && p.BI == 1;  // a tile must not straddle images
   if (fuse_stats) {
-    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(float) * 2 * (size_t)N * Cout, (cudaStream_t)stream);
+    cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(long long) * 2 * (size_t)N * Cout, (cudaStream_t)stream);
     if (e != cudaSuccess) { b2c_set_error("tapgemm stats memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
     p.stats = stats;
   }
@@ -628,15 +628,15 @@ extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_
 }
 
 extern "C" int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* scale, const float* bias,
-                                void* y, long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
+                                void* y, long long ldy, long long* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
   return run_tapgemm(0, x, ldx, wpack_c, scale, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
 }
 
 int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const float* scale, void* y, long long ldy,
-                    float* stats, const void* act, float slope, int N, int H, int W, int Cin, void* stream);  // convt64.cu
+                    long long* stats, const void* act, float slope, int N, int H, int W, int Cin, void* stream);  // convt64.cu
 
 extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* scale, const float* bias,
-                                 void* y, long long ldy, float* stats, const void* act, float slope, int N, int H, int W,
+                                 void* y, long long ldy, long long* stats, const void* act, float slope, int N, int H, int W,
                                  int Cin, int Cout, void* stream) {
   static const bool merge = !(getenv("B2C_CONVT_MERGE") && getenv("B2C_CONVT_MERGE")[0] == '0');  // A/B switch for profiling
   if (g_f32_output) B2C_REQUIRE(stats == nullptr, "fp32 check mode: fused statistics are not available");

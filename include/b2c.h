@@ -27,15 +27,16 @@ int b2c_pack_w_t(const float* w, const float* inv_sigma, void* out_bf16, int D0,
  * conv4s2 : nn.Conv2d(k4,s2,p1) fprop (cgan/models.py:57,236) and ConvTranspose2d dgrad.   x dense (N,H,W,Cin).
  * convt4s2: nn.ConvTranspose2d(k4,s2,p1) fprop (cgan/models.py:72,113) and Conv2d dgrad.   y is (N,2H,2W,Cout).
  * wgrad4s2: weight gradient of both (autograd of the above; cgan/cgan_train_enhanced.py:330,366).
- * stats (nullable, fp32 [N][Cout][2]) <- per-(image, channel) (sum, sum of squares) of the bf16 output, i.e. what
+ * stats (nullable, int64 [N][Cout][2]) <- per-(image, channel) (sum, sum of squares) of the bf16 output, i.e. what
  * b2c_in_stats computes: the InstanceNorm2d that follows every such conv (cgan/models.py:59,73,114,241) gets its
- * statistics from the GEMM epilogue instead of re-reading the tensor. */
+ * statistics from the GEMM epilogue instead of re-reading the tensor.  Statistics are 64-bit FIXED-POINT sums, value =
+ * int64 * 2^-30: integer atomics are order-independent, so a forward pass is bit-reproducible. */
 /* scale (nullable device scalar): y = acc * scale + bias, i.e. W_eff = W * scale: the spectral-norm 1/sigma of THIS forward
  * instance without re-packing the weights. */
 int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* scale, const float* bias, void* y,
-                     long long ldy, float* stats, int N, int H, int W, int Cin, int Cout, void* stream);
+                     long long ldy, long long* stats, int N, int H, int W, int Cin, int Cout, void* stream);
 int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* scale, const float* bias, void* y,
-                      long long ldy, float* stats, const void* act, float slope, int N, int H, int W, int Cin, int Cout,
+                      long long ldy, long long* stats, const void* act, float slope, int N, int H, int W, int Cin, int Cout,
                       void* stream);
 /* act (nullable, Cout = 64 only): dense bf16 (N,2H,2W,64) output of the LeakyReLU(slope) that feeds the conv whose data
  * gradient this call computes; y is multiplied by (act > 0 ? 1 : slope), i.e. LeakyReLU's backward (cgan/models.py:60,245)
@@ -68,20 +69,20 @@ int b2c_head_dgrad(const float* gy, const float* w, void* ga, int N, int h, int 
 int b2c_head_wgrad(const void* a, const float* gy, float* dw, int N, int h, int C, void* stream);
 
 /* ---- InstanceNorm2d + LeakyReLU/ReLU + Dropout(0.5) (cgan/models.py:59-62,73-77,114,241-242) ---- */
-int b2c_in_stats(const void* z, long long ldz, float* zs, int N, int HW, int C, void* stream);
-int b2c_in_act_fwd(const void* z, long long ldz, const float* zs, const uint8_t* mask, float slope, void* o0,
+int b2c_in_stats(const void* z, long long ldz, long long* zs, int N, int HW, int C, void* stream); /* zs: int64 [N][C][2], see above */
+int b2c_in_act_fwd(const void* z, long long ldz, const long long* zs, const uint8_t* mask, float slope, void* o0,
                    long long ldo0, void* o1, long long ldo1, int N, int HW, int C, void* stream);
-/* pooled_sums: planar fp32 [2][N][C] = (sum act(x_hat), sum act'(x_hat)) per plane */
-int b2c_in_act_pool_fwd(const void* z, long long ldz, const float* zs, float slope, float* pooled_sums, int N, int HW,
+/* pooled_sums: planar int64 fixed-point [2][N][C] = (sum act(x_hat), sum act'(x_hat)) per plane (value = int64 * 2^-30) */
+int b2c_in_act_pool_fwd(const void* z, long long ldz, const long long* zs, float slope, long long* pooled_sums, int N, int HW,
                         int C, void* stream);
 /* g: full gradient tensor, or gvec: per-(n,c) broadcast gradient with (optionally) fwd_sums = the pooled_sums of the forward,
  * which makes the backward a single apply pass.  Planes of >= 64 pixels without a mask run as ONE cluster kernel (TMA ring,
  * plane sums exchanged through distributed shared memory, operands cross HBM once); ws: fp32 [N][C][2] scratch otherwise. */
-int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const float* fwd_sums, const void* z, long long ldz,
-                   const float* zs, const uint8_t* mask, float slope, float* ws, void* gz, long long ldgz, int N, int HW,
+int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const long long* fwd_sums, const void* z, long long ldz,
+                   const long long* zs, const uint8_t* mask, float slope, float* ws, void* gz, long long ldgz, int N, int HW,
                    int C, void* stream);
 int b2c_in_act_bwd2(const void* h, long long ldh, const void* g, long long ldg, const void* z, long long ldz,
-                    const float* zs, const uint8_t* mask, float slope, float* ws, void* gg, long long ldgg, void* gx,
+                    const long long* zs, const uint8_t* mask, float slope, float* ws, void* gg, long long ldgg, void* gx,
                     long long ldgx, int N, int HW, int C, void* stream);
 int b2c_lrelu_bwd(const void* g, const void* a, void* out, long long n, float slope, void* stream);
 int b2c_copy_strided(const void* src, long long lds, void* dst, long long ldd, long long npix, int C, void* stream);
@@ -128,9 +129,9 @@ int b2c_scale_rows(const float* x, const float* coef, const float* gscale, float
 int b2c_fill_scaled(float* out, long long n, const float* gscale, float value, void* stream);
 
 /* ---- G head AvgPool -> Linear(64,4) -> Tanh -> *delta_scale (cgan/models.py:118-123,139-141) ---- */
-int b2c_pool_fc_fwd(const float* pooled_sums, const float* W, const float* bias, float scale, int HW, float* delta,
+int b2c_pool_fc_fwd(const long long* pooled_sums, const float* W, const float* bias, float scale, int HW, float* delta,
                     float* tanh_out, int N, int C, void* stream);
-int b2c_pool_fc_bwd(const float* gdelta, const float* tanh_v, const float* pooled_sums, const float* W, float scale,
+int b2c_pool_fc_bwd(const float* gdelta, const float* tanh_v, const long long* pooled_sums, const float* W, float scale,
                     int HW, float* dW, float* db, float* gvec, int N, int C, void* stream);
 
 /* ---- clip_grad_norm_(1.0) + Adam (cgan/cgan_train_enhanced.py:256-257,331-332,368-369) ---- */

@@ -7,7 +7,7 @@ N, HW, C = (int(v) for v in sys.argv[1:4])
 iters = int(sys.argv[4]) if len(sys.argv) > 4 else 10
 bf = lambda: torch.randn(N, HW, C, device="cuda").to(torch.bfloat16)
 z, g, h, o0, o1 = bf(), bf(), bf(), bf(), bf()
-zs = torch.empty(N, C, 2, device="cuda"); ws = torch.empty(N, C, 5, device="cuda")
+zs = torch.empty(N, C, 2, dtype=torch.int64, device="cuda"); ws = torch.empty(N, C, 5, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 T = N * HW * C * 2
 cases = {

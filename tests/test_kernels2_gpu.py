@@ -33,7 +33,7 @@ def test_instance_norm_act_fwd_bwd_bwd2(L, N, C, H, slope, drop):
     m = (torch.rand(N, C, H, H, generator=g) < 0.5).float() if drop else None
     mk = mask_nhwc(m) if drop else None
     zd = nhwc(z)
-    zs = torch.empty(N, C, 2, device="cuda")
+    zs = torch.empty(N, C, 2, dtype=torch.int64, device="cuda")
     L.call("b2c_in_stats", zd, C, zs, N, HW, C)
     out = torch.empty(N, H, H, C, dtype=torch.bfloat16, device="cuda")
     out2 = torch.empty(N, H, H, 2 * C, dtype=torch.bfloat16, device="cuda")
@@ -65,11 +65,12 @@ def test_instance_norm_act_fwd_bwd_bwd2(L, N, C, H, slope, drop):
     assert rel(nchw(gx), gx_ref) < 1.5e-2
     # pooled variant (G head): pooled sums and broadcast-gradient backward
     if not drop:
-        ps = torch.empty(2, N, C, device="cuda")  # planar (sum act(x_hat), sum act'(x_hat))
+        ps = torch.empty(2, N, C, dtype=torch.int64, device="cuda")  # planar fixed-point (sum act(x_hat), sum act'(x_hat))
         L.call("b2c_in_act_pool_fwd", zd, C, zs, slope, ps, N, HW, C)
-        assert rel(ps[0].cpu() / HW, ref.mean((2, 3))) < 1e-3
+        psf = ps.double().cpu() * 2.0 ** -30
+        assert rel(psf[0] / HW, ref.mean((2, 3))) < 1e-3
         xh = F.instance_norm(z.double(), eps=1e-5)
-        assert rel(ps[1].cpu(), torch.where(xh > 0, 1.0, slope).sum((2, 3))) < 2e-3
+        assert rel(psf[1], torch.where(xh > 0, 1.0, slope).sum((2, 3))) < 2e-3
         gv = torch.randn(N, C, generator=g)
         (gzp_ref,) = torch.autograd.grad(fwd(zz), zz, gv.double()[:, :, None, None].expand(N, C, H, H))
         for fs in (None, ps):  # two-pass reduction, then the single apply pass fed by the forward's plane sums
@@ -89,7 +90,7 @@ def test_instance_norm_cluster_kernels(L, N, C, H, ld):
     HW, slope = H * H, 0.2
     z = q(torch.randn(N, C, H, H, generator=g) * 1.3 - 0.2)
     zd = nhwc(z)
-    zs = torch.empty(N, C, 2, device="cuda")
+    zs = torch.empty(N, C, 2, dtype=torch.int64, device="cuda")
     L.call("b2c_in_stats", zd, C, zs, N, HW, C)
     zz = z.double().requires_grad_(True)
     ref = F.leaky_relu(F.instance_norm(zz, eps=1e-5), slope)
@@ -298,7 +299,9 @@ def test_pool_fc_tanh(L):
     ps = torch.randn(N, C, generator=g) * HW
     W, b = torch.randn(4, C, generator=g) * 0.1, torch.randn(4, generator=g) * 0.1
     delta, th = torch.empty(N, 4, device="cuda"), torch.empty(N, 4, device="cuda")
-    L.call("b2c_pool_fc_fwd", ps.cuda(), W.cuda(), b.cuda(), 0.3, HW, delta, th, N, C)
+    psi = (ps.double() * 2.0 ** 30).round().to(torch.int64).cuda()  # pooled sums travel as 64-bit fixed point
+    ps = psi.double().cpu() * 2.0 ** -30
+    L.call("b2c_pool_fc_fwd", psi, W.cuda(), b.cuda(), 0.3, HW, delta, th, N, C)
     pl = (ps / HW).double().requires_grad_(True)
     Wd, bd = W.double().requires_grad_(True), b.double().requires_grad_(True)
     ref = torch.tanh(F.linear(pl, Wd, bd)) * 0.3
@@ -306,7 +309,7 @@ def test_pool_fc_tanh(L):
     gd = torch.randn(N, 4, generator=g)
     ref.backward(gd.double())
     dW, db, gv = torch.empty(4, C, device="cuda"), torch.empty(4, device="cuda"), torch.empty(N, C, device="cuda")
-    L.call("b2c_pool_fc_bwd", gd.cuda(), th, ps.cuda(), W.cuda(), 0.3, HW, dW, db, gv, N, C)
+    L.call("b2c_pool_fc_bwd", gd.cuda(), th, psi, W.cuda(), 0.3, HW, dW, db, gv, N, C)
     assert rel(dW, Wd.grad) < 1e-4 and rel(db, bd.grad) < 1e-4 and rel(gv.cpu() * HW, pl.grad) < 1e-4
 
 

@@ -46,9 +46,10 @@ def test_conv4s2(L, N, H, W, Cin, Cout):
     wp = torch.empty(Cout, 16 * Cin, dtype=torch.bfloat16, device="cuda")
     L.call("b2c_pack_w_c", w.cuda(), None, wp, Cout, Cin)
     y = torch.empty(N, H // 2, W // 2, Cout, dtype=torch.bfloat16, device="cuda")
-    zs = torch.full((N, Cout, 2), 7.0, device="cuda")  # fused InstanceNorm statistics of the bf16 output
+    zsi = torch.full((N, Cout, 2), 7, dtype=torch.int64, device="cuda")  # fused InstanceNorm statistics of the bf16 output
     sc = torch.tensor([0.75], device="cuda")  # epilogue scale (spectral-norm 1/sigma): y = acc * scale + bias
-    L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, sc, b.cuda(), y, Cout, zs, N, H, W, Cin, Cout)
+    L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, sc, b.cuda(), y, Cout, zsi, N, H, W, Cin, Cout)
+    zs = zsi.double() * 2.0 ** -30  # 64-bit fixed-point sums
     yf = y.float()
     assert float((zs[:, :, 0] - yf.sum((1, 2))).abs().max()) < 1e-3 * float(yf.abs().sum((1, 2)).max())
     assert rel(zs[:, :, 1], (yf * yf).sum((1, 2))) < 1e-4
@@ -68,9 +69,10 @@ def test_convt4s2(L, N, H, W, Cin, Cout):
     wp = torch.empty(4, Cout, 4 * Cin, dtype=torch.bfloat16, device="cuda")
     L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
     y = torch.empty(N, 2 * H, 2 * W, Cout, dtype=torch.bfloat16, device="cuda")
-    zs = torch.full((N, Cout, 2), 7.0, device="cuda")
+    zsi = torch.full((N, Cout, 2), 7, dtype=torch.int64, device="cuda")
     sc = torch.tensor([1.5], device="cuda")
-    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, sc, None, y, Cout, zs, None, 1.0, N, H, W, Cin, Cout)
+    L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, sc, None, y, Cout, zsi, None, 1.0, N, H, W, Cin, Cout)
+    zs = zsi.double() * 2.0 ** -30
     yf = y.float()
     assert rel(zs[:, :, 1], (yf * yf).sum((1, 2))) < 1e-4
     assert float((zs[:, :, 0] - yf.sum((1, 2))).abs().max()) < 1e-3 * float(yf.abs().sum((1, 2)).max())
