@@ -128,6 +128,17 @@ int b2c_critic_loss_bwd(const float* gscale, float* g_real, long long n_real, fl
 int b2c_scale_rows(const float* x, const float* coef, const float* gscale, float* out, long long n, int B, void* stream);
 int b2c_fill_scaled(float* out, long long n, const float* gscale, float value, void* stream);
 
+/* ---- refined patches / letterbox on the device: crop -> grey-pad to a square -> PIL-BICUBIC resize (bit-identical restatement
+ * of Pillow's ImagingResample) -> ToTensor + Normalize(0.5, 0.5).  mode 0: CalibratorDataset._letterbox (cgan/dataset.py:103-124);
+ * mode 1: get_refined_patch_batch (cgan/cgan_train_enhanced.py:37-137: hard-clamp delta update, [0.1,0.9]/[0.05,0.8] clamps,
+ * "< 10 px -> pred_box" fallback); mode 2: inference crop_patch + letterbox (cgan/inference.py:51-66).  images: uint8 HWC RGB
+ * images back to back (img_off/img_h/img_w per image), sample_img[B]: image of each sample, qmax >= largest image side. ---- */
+long long b2c_refine_ws_bytes(int B, int S, int qmax);
+int b2c_refine_patches(const uint8_t* images, const long long* img_off, const int* img_h, const int* img_w,
+                       const int* sample_img, const float* pred_box, const float* delta, int mode, const float* fallback,
+                       void* ws, long long ws_bytes, float* out, uint8_t* out_u8, float* box_out, int B, int S, int qmax,
+                       void* stream);
+
 /* ---- G head AvgPool -> Linear(64,4) -> Tanh -> *delta_scale (cgan/models.py:118-123,139-141) ---- */
 int b2c_pool_fc_fwd(const long long* pooled_sums, const float* W, const float* bias, float scale, int HW, float* delta,
                     float* tanh_out, int N, int C, void* stream);
