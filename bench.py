@@ -54,6 +54,11 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="step eagerly instead of replaying the captured CUDA graph")
     ap.add_argument("--mode", default="train", choices=["train", "infer"],
                     help="infer = BASELINE configs[4]: generator-only eval forward (cgan/inference.py:170-171), default batch 256")
+    ap.add_argument("--refine", action="store_true",
+                    help="the reference's real data flow: uint8 images resident in HBM, pred / gt patches letterboxed on the "
+                         "device, the fake patch re-cropped from the generator's CURRENT delta in every critic step and in the "
+                         "generator step (b200cgan.refine; cgan_train_enhanced.py:311-315,358-360) - the critic-step generator "
+                         "forwards are live work in this mode")
     ap.add_argument("--config", default=None, choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"],
                     help="BASELINE.json configs by number: cfg1 = B 4 S 256 (the CPU plumbing case), cfg2/cfg3 = B 64/GPU S 256 "
                          "(default; cfg3 is cfg2 under torchrun), cfg4 = B 16/GPU S 512, cfg5 = generator-only forward, B 256")
@@ -332,10 +337,28 @@ def run_b200(args):
     G, D = GeneratorUNet(0.3), Discriminator(True)
     G.apply(weights_init_normal); D.apply(weights_init_normal)
     G, D = G.to(dev), D.to(dev)
-    rng.manual_seed(42 + rank)
-    tr = CGANTrainer(G, D, n_critic=N_CRITIC, lambda_gp=LAMBDA_GP, world_size=world, use_cuda_graph=not args.no_graph)
+    rng.manual_seed(42)  # one stream for the whole job; each rank reads the slice of its global sample indices (rng.set_shard)
     host = synth_host_batches(B, S, rank)
     resident = [{k: v.to(dev) for k, v in b.items()} for b in host]
+    refine_fn = None
+    if args.refine:
+        from b200cgan import refine
+        gi = torch.Generator("cpu").manual_seed(77 + rank)
+        bank = refine.DeviceImageBank([torch.randint(0, 256, (480, 640, 3), dtype=torch.uint8, generator=gi) for _ in range(32)], dev)
+        sample_img = torch.randint(0, 32, (B,), generator=gi).to(dev, torch.int32)
+        box_buf = resident[0]["pred_box"].clone()  # persistent: the captured graph's refine kernel reads it
+        for b in resident:  # patches come from the images; both batches share the boxes the refine kernel sees
+            b["pred_box"] = box_buf
+            b["pred"] = refine.letterbox_patches(bank, sample_img, box_buf, S)
+            b["gt"] = refine.letterbox_patches(bank, sample_img, (box_buf * 1.02).clamp(0.05, 0.9), S)
+            b["refined"] = None
+        for hb, b in zip(host, resident):
+            hb["pred"], hb["gt"] = b["pred"].cpu().pin_memory(), b["gt"].cpu().pin_memory()
+            hb["pred_box"] = box_buf.cpu().pin_memory()
+            hb["refined"] = None
+        refine_fn = refine.make_refine_fn(bank, sample_img, box_buf, S, fallback=None)
+    tr = CGANTrainer(G, D, n_critic=N_CRITIC, lambda_gp=LAMBDA_GP, world_size=world, rank=rank if world > 1 else None,
+                     use_cuda_graph=not args.no_graph, refine_fn=refine_fn)
     keys = ("pred", "gt", "refined", "pred_box", "delta_true")
 
     def barrier():
@@ -372,17 +395,19 @@ def run_b200(args):
     finite = all(bool(torch.isfinite(v).all()) for v in out.scalars.values())
 
     # ---- end-to-end leg: pinned host -> device every step, scalars back to the host every step
-    h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+    h2d = sum(v.numel() * v.element_size() for v in host[0].values() if v is not None)
     from b200cgan.train_step import HostPrefetcher
-    pf = HostPrefetcher([host[0][k] for k in keys], dev)  # copy of batch i+1 overlaps step i (side stream)
+    live = [k for k in keys if host[0][k] is not None]
+    pf = HostPrefetcher([host[0][k] for k in live], dev)  # copy of batch i+1 overlaps step i (side stream)
 
     def e2e_steps(n):
         nbytes = 0
-        pf.submit([host[0][k] for k in keys])
+        pf.submit([host[0][k] for k in live])
         for i in range(n):
             if i + 1 < n:
-                pf.submit([host[(i + 1) % 2][k] for k in keys])
-            o = tr.step(*pf.take())
+                pf.submit([host[(i + 1) % 2][k] for k in live])
+            got = dict(zip(live, pf.take()))
+            o = tr.step(*[got.get(k) for k in keys])
             pf.release()
             nbytes = 4 * len(o.to_host())  # the 9 logged scalars come back to the host every step
         return nbytes
@@ -416,7 +441,7 @@ def run_b200(args):
         return
     roofline, roofline_bw = roofline_blocks(fam, bwfam, ms_dev / K)
     value = world * B * K / (ms_dev / 1e3)
-    useful = useful_flops_per_patch(S)
+    useful = useful_flops_per_patch(S, live_critic_g=args.refine)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
@@ -424,6 +449,8 @@ def run_b200(args):
             "e2e": {"value": world * B * K / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K},
             "gpu_launches": launches, "cuda_graph": not args.no_graph, "eager_ms_per_step": ms_eager / K,
+            "refine": ("device: fake patches re-cropped from G's current delta (3 crops + 2 extra generator forwards per step)"
+                       if args.refine else "input tensor (BASELINE configs: synthetic paired patches)"),
             "roofline": roofline, "roofline_bw": roofline_bw, "kernels": fam, "clocks": clk,
             "useful_conv_tflops": useful * B / (ms_dev / K) / 1e9, "finite": finite}
     if world == 1 and not args.no_cpu_baseline:

@@ -55,6 +55,21 @@ def sink_of(param):
     return getattr(param, "_b2c_sink", None)
 
 
+_SINK_LISTENER = None  # callable(param) invoked after every kernel that accumulated into param's sink (train_step.GradBuckets)
+
+
+def set_sink_listener(fn):
+    global _SINK_LISTENER
+    _SINK_LISTENER = fn
+
+
+def _sink_written(*params):
+    if _SINK_LISTENER is not None:
+        for p in params:
+            if p is not None:
+                _SINK_LISTENER(p)
+
+
 _SN_PENDING = {}  # id(weight_orig) -> (param, [(u, v, sig, part, nparts)]): rank-1 terms owed to the sink (flush_sn_pending)
 
 
@@ -62,13 +77,19 @@ def _sn_defer(wctx, part, nparts):
     _SN_PENDING.setdefault(id(wctx.weight), (wctx.weight, []))[1].append((wctx.u, wctx.v, wctx.sig, part, nparts))
 
 
-def flush_sn_pending():
+def flush_sn_pending(params=None):
     """Spectral-norm backward, second half: the weight-gradient kernels put sum_i dWe_i / sigma_i into the sinks; this ONE
-    launch subtracts sum_i (<dWe_i, W> / sigma_i^2) u_i v_i^T for every layer and forward instance."""
+    launch subtracts sum_i (<dWe_i, W> / sigma_i^2) u_i v_i^T for every layer and forward instance.
+    params: only these parameters (a gradient bucket about to be all-reduced); default: everything pending."""
     if not _SN_PENDING:
         return
-    items = list(_SN_PENDING.values())
-    _SN_PENDING.clear()
+    if params is None:
+        items = list(_SN_PENDING.values())
+        _SN_PENDING.clear()
+    else:
+        items = [_SN_PENDING.pop(id(p)) for p in params if id(p) in _SN_PENDING]
+        if not items:
+            return
     nl = len(items)
     ninst = [len(lst) for _, lst in items]
     tot = sum(ninst)
@@ -250,6 +271,7 @@ def _wgrad(wctx, small, large):
         _lib.call("b2c_wgrad4s2_bf16", small, lds, large, Cl, ws, nws, sink, 1, wctx.inv_sigma, wctx.weight.detach(), part,
                   ctypes.byref(nparts), N, Hs, Ws, Cs, Cl, _lib.sm_count())
         _sn_defer(wctx, part, nparts.value)
+    _sink_written(wctx.weight)
     return None
 
 
@@ -421,6 +443,7 @@ def _first_wgrad(a0, a1, gz, wctx, bias_param, interp=None):
         _lib.call("b2c_first_wgrad", a0, a1, b0, b1, al, gz, wsink, dbp, wctx.inv_sigma, wctx.weight.detach(), part,
                   ctypes.byref(nparts), N, H, W)
         _sn_defer(wctx, part, nparts.value)
+    _sink_written(wctx.weight, bias_param if bsink is not None else None)
     return None, db
 
 
@@ -645,6 +668,7 @@ class INActPoolFC(torch.autograd.Function):
         gz = cl_empty(N, C, H, W, device=z.device)
         # the plane sums of this backward follow from the forward's (sum act, sum act'): ONE apply pass over z
         _lib.call("b2c_in_act_bwd", None, 0, gvec, ps, z, ldz, zs, None, ctx.slope, ws, gz, C, N, H * W, C)
+        _sink_written(fc_w if wsink is not None else None, ctx.fc_b if bsink is not None else None)
         return gz, (None if wsink is not None else dW), (None if bsink is not None else db), None, None, None
 
 
@@ -679,6 +703,7 @@ def _head_wgrad_raw(a, gy, weight):
     sink = sink_of(weight)
     if sink is not None:  # accumulated in place
         _lib.call("b2c_head_wgrad", a, gy.to(torch.float32).contiguous(), sink, N, h, C)
+        _sink_written(weight)
         return None
     dw = torch.empty_like(weight, dtype=torch.float32)
     _lib.call("b2c_zero", dw, dw.numel() * 4)

@@ -79,6 +79,71 @@ class HostPrefetcher:
         self.free[(self.n_take - 1) % 2].record(torch.cuda.current_stream())
 
 
+class GradBuckets:
+    """Gradient all-reduce overlapped with backward (north_star).  The flat gradient bucket of a network is cut
+    into contiguous slices in REVERSE parameter order - the order in which backward completes them (D: model.11 -> model.8 ->
+    model.5 -> model.2 / model.0; G: fc -> up4 -> ... -> down1).  The weight-gradient kernels report every write into a
+    parameter's sink (ops.set_sink_listener); the number of writes each parameter receives per backward is learned in the
+    first step, and from then on a slice is SUM-all-reduced on a side stream the moment its last write has been enqueued
+    (after that slice's spectral-norm rank-1 terms were flushed), while backward keeps running on the main stream.  finish()
+    reduces whatever is left and joins the streams.  The 1/world factor is applied inside the Adam kernel."""
+
+    def __init__(self, opt, group, min_bytes=4 << 20):
+        self.opt, self.group = opt, group
+        self.index = {id(p): i for i, p in enumerate(opt.params)}
+        self.expected = None            # writes per parameter and backward (learned)
+        self.counts = [0] * len(opt.params)
+        self.stream = torch.cuda.Stream(opt.flat_g.device)
+        self.slices = []                # (lo, hi, [param indices]) in completion order
+        idxs, lo_hi = [], None
+        for i in reversed(range(len(opt.params))):
+            o, n = opt.slices[i]
+            lo_hi = (o, lo_hi[1]) if lo_hi else (o, o + (n + 3) // 4 * 4)
+            idxs.append(i)
+            if (lo_hi[1] - lo_hi[0]) * 4 >= min_bytes or i == 0:
+                self.slices.append((lo_hi[0], lo_hi[1], idxs))
+                idxs, lo_hi = [], None
+        self.done = [False] * len(self.slices)
+        self.learning = True
+
+    def begin(self):
+        self.counts = [0] * len(self.counts)
+        self.done = [False] * len(self.slices)
+
+    def on_write(self, param):
+        i = self.index.get(id(param))
+        if i is None:
+            return
+        self.counts[i] += 1
+        if self.expected is None:
+            return
+        for k, (lo, hi, idxs) in enumerate(self.slices):
+            if self.done[k]:
+                continue
+            if all(self.counts[j] >= self.expected[j] for j in idxs):
+                self._reduce(k)
+            else:
+                break  # slices complete in order
+
+    def _reduce(self, k):
+        import torch.distributed as dist
+        lo, hi, idxs = self.slices[k]
+        ops.flush_sn_pending([self.opt.params[j] for j in idxs])
+        main = torch.cuda.current_stream()
+        self.stream.wait_stream(main)
+        with torch.cuda.stream(self.stream):
+            dist.all_reduce(self.opt.flat_g[lo:hi], op=dist.ReduceOp.SUM, group=self.group)
+        self.done[k] = True
+
+    def finish(self):
+        if self.expected is None:
+            self.expected = list(self.counts)  # learned: from the next backward on, slices go out as they complete
+        for k in range(len(self.slices)):
+            if not self.done[k]:
+                self._reduce(k)
+        torch.cuda.current_stream().wait_stream(self.stream)
+
+
 class StepOutput:
     """Logged scalars of one step, kept on the device.  to_host() concatenates them and makes ONE device->host copy."""
 
@@ -119,7 +184,7 @@ def masks_to_device(masks, device="cuda"):
 
 class CGANTrainer:
     def __init__(self, netG, netD, *, lr=2e-4, beta1=0.5, beta2=0.999, n_critic=2, lambda_gp=1.0, lambda_iou=1.0,
-                 process_group=None, world_size=1, use_cuda_graph=False, refine_fn=None):
+                 process_group=None, world_size=1, rank=None, use_cuda_graph=False, refine_fn=None):
         self.netG, self.netD = netG, netD
         self.n_critic, self.lambda_gp, self.lambda_iou = n_critic, lambda_gp, lambda_iou
         self.optG = ops.FusedClipAdam(netG.parameters(), lr=lr, betas=(beta1, beta2))
@@ -138,12 +203,23 @@ class CGANTrainer:
         self._static_alpha = self._static_masks = None  # device buffers the captured graph reads the injected draws from
         dev = self.optD.flat_p.device
         self._seed3(dev); self._seed1(dev)  # backward seeds: created now, not inside a graph capture
+        self._buckets = {}
+        if world_size > 1:
+            self._buckets = {id(self.optD): GradBuckets(self.optD, process_group), id(self.optG): GradBuckets(self.optG, process_group)}
+            if rank is not None:
+                rng.set_shard(rank, world_size)  # draws keyed by GLOBAL sample index: 1 x (N*B) == N x B
 
-    # ---- data parallel: SUM the flat gradient bucket over ranks; the 1/world is applied inside the Adam kernel ----
+    # ---- data parallel: SUM the flat gradient buckets over ranks, slice by slice as backward completes them (GradBuckets);
+    # ---- the 1/world is applied inside the Adam kernel ----
     def _allreduce(self, opt):
         if self.world_size > 1:
-            import torch.distributed as dist
-            dist.all_reduce(opt.flat_g, op=dist.ReduceOp.SUM, group=self.pg)
+            self._buckets[id(opt)].finish()
+
+    def _begin_backward(self, opt):
+        if self.world_size > 1:
+            b = self._buckets[id(opt)]
+            b.begin()
+            ops.set_sink_listener(b.on_write)
 
     def _seed3(self, dev):  # d/d (d_loss, wd, gp) = (1, 0, 0): persistent, so backward() launches no fill kernel
         if getattr(self, "_s3", None) is None or self._s3.device != dev:
@@ -196,8 +272,10 @@ class CGANTrainer:
         gp = losses.compute_gradient_penalty(netD, (pred, gt), (pred, refined), pred.device,
                                              alpha=self._alpha(c, pred.shape[0], pred.device))
         cl = ops.CriticLoss.apply(real_validity, fake_validity, gp, self.lambda_gp)  # (d_loss, wd, gp)
+        self._begin_backward(self.optD)
         with ops.backward_flags(first_dgrad=False):  # nobody reads d loss / d interpolates
             torch.autograd.backward(cl, self._seed3(cl.device))  # d_loss = cl[0]
+        ops.set_sink_listener(None)
         ops.flush_sn_pending()
         self._allreduce(self.optD)
         if gnorm_out is not None:
@@ -218,7 +296,9 @@ class CGANTrainer:
             if self.refine_fn is not None:
                 refined = self.refine_fn(delta_pred.detach())  # reference :358-360
             loss_wgan = ops.MapMean.apply(netD(pred, refined), -1.0)  # D still runs in train mode (advances u / v)
+        self._begin_backward(self.optG)
         torch.autograd.backward(loss_iou, self._seed1(loss_iou.device))  # loss_G's live part: lambda_iou * loss_iou
+        ops.set_sink_listener(None)
         self._allreduce(self.optG)
         if gnorm_out is not None:
             self.optG.gnorm_sq = gnorm_out
