@@ -7,8 +7,8 @@ Same CLI flags, file formats, checkpoint handling and box arithmetic as cgan/inf
 device work: every box of the image is cropped/letterboxed on the host exactly as the reference does
 (cgan/inference.py:51-66) and the whole stack of patches goes through ONE generator forward on the B200 kernels
 (the reference loops box by box with batch 1, cgan/inference.py:161-171).  InstanceNorm statistics are per sample, so
-batching does not change any output.  Only `generator_type: unet` is supported (SURVEY.md §8f lists the simple
-regressor as the next row); there is no CPU path.
+batching does not change any output.  Both generator types of the reference (`unet`, `simple`; cgan/inference.py:131-135)
+are supported; there is no CPU path.
 """
 from __future__ import annotations
 
@@ -19,7 +19,7 @@ from typing import List, Sequence
 
 import torch
 
-from .models import GeneratorUNet
+from .models import GeneratorSimpleRegressor, GeneratorUNet
 
 
 # ------------------------------------------------------------------------------------------------ YOLO txt I/O
@@ -117,9 +117,10 @@ def main(argv=None):
         raise SystemExit("b200cgan.inference: no CUDA device (this package has no CPU path)")
     from PIL import Image
     state, delta_scale, gen_type = resolve_checkpoint(args.weights, "cpu")
-    if gen_type != "unet":
-        raise SystemExit(f"b200cgan.inference: generator_type={gen_type!r} is not built (unet only)")
-    netG = GeneratorUNet(delta_scale=delta_scale)
+    if gen_type == "simple":  # cgan/inference.py:131-135
+        netG = GeneratorSimpleRegressor(delta_scale=delta_scale)
+    else:
+        netG = GeneratorUNet(delta_scale=delta_scale)
     netG.load_state_dict(state)
     netG = netG.cuda()
     img = Image.open(args.image).convert("RGB")

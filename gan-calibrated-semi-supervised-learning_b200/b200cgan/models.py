@@ -264,6 +264,60 @@ class GeneratorUNet(nn.Module):
         return ops.INActPoolFC.apply(z, fc.weight, fc.bias, 0.0, self.delta_scale, wctx.take_stats())
 
 
+class Conv2dK3S1(nn.Module):
+    """nn.Conv2d(cin, cout, 3, padding=1) with bias: the 9-tap tcgen05 GEMM (first layer, Cin = 3: CUDA cores)."""
+
+    def __init__(self, in_ch, out_ch):
+        super().__init__()
+        self.in_channels, self.out_channels = in_ch, out_ch
+        self.weight = nn.Parameter(torch.empty(out_ch, in_ch, 3, 3))
+        self.bias = nn.Parameter(torch.empty(out_ch))
+        _torch_conv_init(self.weight, self.bias, in_ch * 9)
+
+    def extra_repr(self):
+        return f"{self.in_channels}, {self.out_channels}, kernel_size=(3, 3), stride=(1, 1), padding=(1, 1)"
+
+
+class GeneratorSimpleRegressor(nn.Module):
+    """The reference's alternative generator (cgan/models.py:147-216; generator_type: "simple", cgan/config.yaml:21):
+    4 blocks of [Conv3x3 + InstanceNorm + ReLU] x 2 + MaxPool2d(2), then AvgPool -> Linear 512-256-64-4 -> Tanh -> * delta_scale.
+    Same constructor, state-dict keys (features.{0,3,7,10,14,17,21,24}.{weight,bias}, regressor.{2,5,8}.{weight,bias};
+    4 833 412 parameters) and forward signature.  The forward pass runs on the B200 kernels in both modes (train mode draws
+    the two Dropout(0.5) masks of the head from b200cgan.rng); a backward pass through it is not built (SURVEY.md §8 f1 is
+    the generator-only / inference use of this model), so calling it with autograd enabled raises instead of silently
+    returning a tensor without a graph."""
+
+    CHANNELS = [(3, 64), (64, 64), (64, 128), (128, 128), (128, 256), (256, 256), (256, 512), (512, 512)]
+
+    def __init__(self, delta_scale: float = None):
+        super().__init__()
+        if delta_scale is None:
+            delta_scale = _default("delta_scale")
+        self.delta_scale = float(delta_scale)
+        layers = []
+        for i, (cin, cout) in enumerate(self.CHANNELS):
+            layers += [Conv2dK3S1(cin, cout), nn.InstanceNorm2d(cout), nn.ReLU(inplace=True)]
+            if i % 2 == 1:
+                layers.append(nn.MaxPool2d(2, 2))
+        self.features = nn.Sequential(*layers)
+        self.regressor = nn.Sequential(nn.AdaptiveAvgPool2d(1), nn.Flatten(), nn.Linear(512, 256), nn.ReLU(inplace=True),
+                                       nn.Dropout(0.5), nn.Linear(256, 64), nn.ReLU(inplace=True), nn.Dropout(0.5),
+                                       nn.Linear(64, 4), nn.Tanh())
+
+    def dropout_sites(self):
+        return []
+
+    @staticmethod
+    def dropout_numels(B, S):
+        return [B * 256, B * 64]
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            raise NotImplementedError("GeneratorSimpleRegressor: only the forward pass is built (inference / no_grad); "
+                                      "train the U-Net generator, or wrap the call in torch.no_grad()")
+        return ops.simple_regressor_forward(self, x)
+
+
 class Discriminator(nn.Module):
     """Spectral-norm PatchGAN critic on (pred_patch, other_patch) pairs: 2 x (B,3,S,S) -> (B,1,S/16-1,S/16-1), no sigmoid."""
 

@@ -113,7 +113,7 @@ def _pack_entry(param):
     if e is None:
         e = _PACKS[id(param)] = {"key": key, "c": None, "t": None, "c_ok": False, "t_ok": False, "ref": param}
     elif e["key"] != key or e["ref"] is not param:
-        e.update(key=key, c_ok=False, t_ok=False, ref=param)
+        e.update(key=key, c_ok=False, t_ok=False, k3_ok=False, ref=param)
     return e
 
 
@@ -121,7 +121,7 @@ def invalidate_packs():
     """Forget which bf16 packs are current (buffers stay): the next use of every weight re-packs it.  CGANTrainer calls
     this before capturing a CUDA graph so that the capture contains every pack the replays need."""
     for e in _PACKS.values():
-        e["c_ok"] = e["t_ok"] = False
+        e["c_ok"] = e["t_ok"] = e["k3_ok"] = False
 
 
 def packed_c(param):
@@ -849,6 +849,54 @@ class EIoU(torch.autograd.Function):
         gp = torch.empty_like(pred)
         _lib.call("b2c_eiou", pred, target, ctx.eps, None, g.contiguous(), gp, None, pred.shape[0])
         return gp, None, None
+
+
+# ------------------------------------------------------------------------------------------------ simple regressor (forward)
+def packed_k3(param):
+    """bf16 [Cout][9*Cin] operand of a 3x3 conv weight, cached like packed_c / packed_t."""
+    e = _pack_entry(param)
+    if not e.get("k3_ok") or e.get("k3") is None:
+        co, ci = param.shape[:2]
+        if e.get("k3") is None:
+            e["k3"] = torch.empty(co, 9 * ci, dtype=BF16, device=param.device)
+        _lib.call("b2c_pack_w_k3", param.detach(), e["k3"], co, ci, 0)
+        e["k3_ok"] = True
+    return e["k3"]
+
+
+@torch.no_grad()
+def simple_regressor_forward(net, x):
+    """GeneratorSimpleRegressor.forward (cgan/models.py:213-216) on the kernels: (B,3,S,S) fp32 -> (B,4)."""
+    from . import rng
+    x = x.detach().to(torch.float32).contiguous()
+    N, _, H, W = x.shape
+    dev = x.device
+    convs = [m for m in net.features if m.__class__.__name__ == "Conv2dK3S1"]
+    a = None
+    for i, conv in enumerate(convs):
+        cout = conv.out_channels
+        z = cl_empty(N, cout, H, W, device=dev)
+        zs = _stats_buf(N, cout, dev)
+        if i == 0:
+            _lib.call("b2c_conv3x3_first", x, conv.weight.detach(), conv.bias.detach(), z, N, H, W)
+            _lib.call("b2c_in_stats", z, cout, zs, N, H * W, cout)
+        else:
+            _lib.call("b2c_conv3s1_bf16", a, conv.in_channels, packed_k3(conv.weight), None, conv.bias.detach(), z, cout, zs,
+                      N, H, W, conv.in_channels, cout)
+        a = cl_empty(N, cout, H, W, device=dev)
+        _lib.call("b2c_in_act_fwd", z, cout, zs, None, 0.0, a, cout, None, 0, N, H * W, cout)
+        if i % 2 == 1:
+            p = cl_empty(N, cout, H // 2, W // 2, device=dev)
+            _lib.call("b2c_maxpool2_fwd", a, p, N, H, W, cout)
+            a, H, W = p, H // 2, W // 2
+    l1, l2, l3 = net.regressor[2], net.regressor[5], net.regressor[8]
+    m1 = m2 = None
+    if net.training:  # Dropout(0.5) after each hidden ReLU
+        m1, m2 = rng.next_mask(N * 256, dev), rng.next_mask(N * 64, dev)
+    delta = torch.empty(N, 4, dtype=torch.float32, device=dev)
+    _lib.call("b2c_simple_head_fwd", a, H * W, l1.weight.detach(), l1.bias.detach(), l2.weight.detach(), l2.bias.detach(),
+              l3.weight.detach(), l3.bias.detach(), m1, m2, float(net.delta_scale), delta, None, N)
+    return delta
 
 
 def fill_(t, value):

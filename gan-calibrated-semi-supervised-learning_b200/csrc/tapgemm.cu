@@ -7,6 +7,8 @@
 //               plain TMA box; the conv's zero padding is TMA out-of-bounds fill (no padded copies, no im2col).
 //   mode T4S2 : y[n,2i+py,2j+px,:] = sum_{a,b}  x[n,i+py+a-1,j+px+b-1,:] . Wt[py,px][:, (a,b,:)]     (4 taps x 4 parities)
 //               = ConvTranspose2d(k4,s2,p1) and also the data gradient of C4S2.
+//   mode C3S1 : y[n,oy,ox,:]       = sum_{ky,kx} x[n,oy+ky-1,ox+kx-1,:] . Wk[:, (ky,kx,:)]           (9 taps, stride 1, pad 1)
+//               Conv2d(k3,s1,p1) of the alternative generator GeneratorSimpleRegressor (cgan/models.py:162-192).
 //   mode D1   : data gradient of the FIRST conv (Cin = 3/6, Cout = 64; cgan/models.py:103,245), needed only under the
 //               gradient penalty (cgan/losses.py:213-220).  One GEMM row per 2x2 block (i,j) of input pixels:
 //               gx[n,c,2i+di,2j+dj] = sum_{fy,fx,co} gz[n,i+fy,j+fx,co] . Wd[(di,dj,c)][(fy,fx,co)]   (9 taps, N = 32)
@@ -21,7 +23,7 @@
 using namespace b2c;
 
 struct TapGemmParams {
-  int mode;  // 0 = C4S2, 1 = T4S2, 2 = D1
+  int mode;  // 0 = C4S2, 1 = T4S2, 2 = D1, 3 = C3S1
   int N, Ho, Wo, Cin, Cout;
   int BW, BH, BI;           // pixel box, BW*BH*BI == 128
   int tiles_x, tiles_y;     // tile grid over the tile space (C: output pixels; T: input-resolution pixels)
@@ -70,7 +72,7 @@ __global__ void __launch_bounds__(64 + 128 * MT) tapgemm_kernel(const __grid_con
   const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
   const int ncol0 = blockIdx.y * BN;
   const int parity = blockIdx.z, py = parity >> 1, px = parity & 1;
-  const int ntaps = p.mode == 0 ? 16 : (p.mode == 1 ? 4 : 9);
+  const int ntaps = p.mode == 0 ? 16 : (p.mode == 1 ? 4 : 9);  // D1 and C3S1: 3 x 3 taps
   const int niters = ntaps * p.kchunks;
 
   if (warp == 0 && lane == 0) {
@@ -104,8 +106,8 @@ __global__ void __launch_bounds__(64 + 128 * MT) tapgemm_kernel(const __grid_con
           } else if (p.mode == 1) {
             const int a = tap >> 1, b = tap & 1;
             tma_load_4d(dA, &tmA, &full[stage], cc * 64, x0 + px + b - 1, y0 + py + a - 1, n0);
-          } else {
-            tma_load_4d(dA, &tmA, &full[stage], 0, x0 + tap % 3 - 1, y0 + tap / 3 - 1, n0);
+          } else {  // D1 (one 64-channel chunk) and C3S1: the 3 x 3 neighbourhood, stride 1
+            tma_load_4d(dA, &tmA, &full[stage], cc * 64, x0 + tap % 3 - 1, y0 + tap / 3 - 1, n0);
           }
           tma_load_2d(sB + stage * Cfg::B_BYTES, &tmB, &full[stage], tap * p.Cin + cc * 64,
                       parity * p.Cout + ncol0);
@@ -263,7 +265,7 @@ struct TapGemmPCfg {
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + RED_BYTES + 512 + 1024;
 };
 
-// MODE (0 = C4S2 conv, 1 = T4S2 transposed conv) is a template parameter so that profiles name the two families apart.
+// MODE (0 = C4S2 conv, 1 = T4S2 transposed conv, 2 = C3S1 conv) is a template parameter so that profiles name the families apart.
 template <int BN, int MODE>
 __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                     const __grid_constant__ CUtensorMap tmB, TapGemmParams p,
@@ -282,7 +284,7 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ntaps = MODE == 0 ? 16 : 4;
+  const int ntaps = MODE == 0 ? 16 : (MODE == 1 ? 4 : 9);
   const int niters = ntaps * p.kchunks;
 
   if (warp == 0 && lane == 0) {
@@ -321,9 +323,11 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
               const int ky = tap >> 2, kx = tap & 3;
               const int fy = (ky - 1) >> 1, di = (ky - 1) & 1, fx = (kx - 1) >> 1, dj = (kx - 1) & 1;
               tma_load_5d(dA, &tmA, &full[stage], dj * p.Cin + cc * 64, x0 + fx, di, y0 + fy, n0);
-            } else {
+            } else if (MODE == 1) {
               const int a = tap >> 1, b = tap & 1;
               tma_load_4d(dA, &tmA, &full[stage], cc * 64, x0 + px + b - 1, y0 + py + a - 1, n0);
+            } else {
+              tma_load_4d(dA, &tmA, &full[stage], cc * 64, x0 + tap % 3 - 1, y0 + tap / 3 - 1, n0);
             }
             tma_load_2d(sB + stage * Cfg::B_BYTES, &tmB, &full[stage], tap * p.Cin + cc * 64, parity * p.Cout + ncol0);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -503,6 +507,9 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     B2C_REQUIRE(ldx == Cin, "conv4s2: input must be dense NHWC (ldx=%lld, Cin=%d)", ldx, Cin);
     B2C_REQUIRE(H % 2 == 0 && W % 2 == 0, "conv4s2: odd input size %dx%d", H, W);
     p.Ho = H / 2; p.Wo = W / 2; TH = p.Ho; TW = p.Wo;
+  } else if (mode == 3) {
+    B2C_REQUIRE(ldx % 8 == 0, "conv3s1: ldx=%lld must be a multiple of 8", ldx);
+    p.Ho = H; p.Wo = W; TH = H; TW = W;
   } else {
     B2C_REQUIRE(ldx % 8 == 0, "convt4s2: ldx=%lld must be a multiple of 8", ldx);
     p.Ho = 2 * H; p.Wo = 2 * W; TH = H; TW = W;
@@ -529,8 +536,8 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     rc = b2c_make_tmap_bf16(&tmA, x, 4, dims, str, box);
   }
   if (rc) return rc;
-  const int K = (mode == 0 ? 16 : 4) * Cin;
-  const int rows = (mode == 0 ? 1 : 4) * Cout;
+  const int K = (mode == 0 ? 16 : mode == 3 ? 9 : 4) * Cin;
+  const int rows = (mode == 1 ? 4 : 1) * Cout;
   {
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
     uint64_t str[1] = {(uint64_t)2 * K};
@@ -544,7 +551,7 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     if (e != cudaSuccess) { b2c_set_error("tapgemm stats memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
     p.stats = stats;
   }
-  dim3 grid(p.tiles_x * p.tiles_y * tiles_n, Cout / BN, mode == 0 ? 1 : 4);
+  dim3 grid(p.tiles_x * p.tiles_y * tiles_n, Cout / BN, mode == 1 ? 4 : 1);
   static const bool persistent = !(getenv("B2C_TAPGEMM_PERSIST") && getenv("B2C_TAPGEMM_PERSIST")[0] == '0');
   if ((BN == 128 || BN == 256) && MT == 1 && persistent) {
     static int sms = 0;
@@ -556,11 +563,17 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
       cudaFuncSetAttribute(tapgemm_persistent_kernel<128, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<128>::SMEM);
       cudaFuncSetAttribute(tapgemm_persistent_kernel<256, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<256>::SMEM);
       cudaFuncSetAttribute(tapgemm_persistent_kernel<256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<256>::SMEM);
+      cudaFuncSetAttribute(tapgemm_persistent_kernel<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<128>::SMEM);
+      cudaFuncSetAttribute(tapgemm_persistent_kernel<256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmPCfg<256>::SMEM);
     }
     const int ptiles = (int)grid.x, nblocks = (int)grid.y, total = (int)(grid.x * grid.y * grid.z);
     const int ctas = total < sms ? total : sms;
     const cudaStream_t st = (cudaStream_t)stream;
-    if (BN == 128 && mode == 0)
+    if (BN == 128 && mode == 3)
+      tapgemm_persistent_kernel<128, 2><<<ctas, 192, TapGemmPCfg<128>::SMEM, st>>>(tmA, tmB, p, ptiles, nblocks, total);
+    else if (mode == 3)
+      tapgemm_persistent_kernel<256, 2><<<ctas, 192, TapGemmPCfg<256>::SMEM, st>>>(tmA, tmB, p, ptiles, nblocks, total);
+    else if (BN == 128 && mode == 0)
       tapgemm_persistent_kernel<128, 0><<<ctas, 192, TapGemmPCfg<128>::SMEM, st>>>(tmA, tmB, p, ptiles, nblocks, total);
     else if (BN == 128)
       tapgemm_persistent_kernel<128, 1><<<ctas, 192, TapGemmPCfg<128>::SMEM, st>>>(tmA, tmB, p, ptiles, nblocks, total);
@@ -625,6 +638,12 @@ extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_
   }
   dim3 grid(p.tiles_x * p.tiles_y * tiles_n, 1, 1);
   return launch_tapgemm<32>(tmA, tmB, p, grid, st);
+}
+
+// Conv2d(k3,s1,p1) (cgan/models.py:162-192): x (N,H,W,Cin) bf16 with pixel stride ldx, wpack_k3: [Cout][9*Cin] bf16 (b2c_pack_w_k3).
+extern "C" int b2c_conv3s1_bf16(const void* x, long long ldx, const void* wpack_k3, const float* scale, const float* bias,
+                                void* y, long long ldy, long long* stats, int N, int H, int W, int Cin, int Cout, void* stream) {
+  return run_tapgemm(3, x, ldx, wpack_k3, scale, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
 }
 
 extern "C" int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_c, const float* scale, const float* bias,

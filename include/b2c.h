@@ -53,6 +53,19 @@ int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* large, long 
                       float* dw, int accumulate, const float* scale, const float* wdot, float* part, int* nparts_host,
                       int N, int Hs, int Ws, int Cs, int Cl, int sm_count, void* stream);
 
+/* ---- GeneratorSimpleRegressor (cgan/models.py:147-216, generator_type "simple"): Conv2d(k3,s1,p1) on the same tcgen05 tap
+ * GEMM (9 taps), its weight packing (flip != 0: the data-gradient form), the first 3x3 conv on the NCHW fp32 patch,
+ * MaxPool2d(2,2) forward / backward, and the regression head AvgPool -> Linear 512-256-64-4 -> Tanh -> * delta_scale ---- */
+int b2c_pack_w_k3(const float* w, void* out_bf16, int Cout, int Cin, int flip, void* stream);
+int b2c_conv3s1_bf16(const void* x, long long ldx, const void* wpack_k3, const float* scale, const float* bias, void* y,
+                     long long ldy, long long* stats, int N, int H, int W, int Cin, int Cout, void* stream);
+int b2c_conv3x3_first(const float* x, const float* w, const float* bias, void* y, int N, int H, int W, void* stream);
+int b2c_maxpool2_fwd(const void* a, void* out, int N, int H, int W, int C, void* stream);
+int b2c_maxpool2_bwd(const void* a, const void* g, void* ga, int N, int H, int W, int C, void* stream);
+int b2c_simple_head_fwd(const void* a, int HW, const float* W1, const float* b1, const float* W2, const float* b2,
+                        const float* W3, const float* b3, const uint8_t* m1, const uint8_t* m2, float scale, float* delta,
+                        float* acts, int N, void* stream);
+
 /* ---- first layers, Cin = 3 / 6, NCHW fp32 in (cgan/models.py:103,245,257; interpolation cgan/losses.py:203-204) ---- */
 int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                     const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,

@@ -12,6 +12,7 @@ is pinned against outputs of the UNMODIFIED reference modules run in the build c
 
 Reference lines restated (paths relative to /root/reference):
   g_forward           cgan/models.py:54-83,89-141      (UNetDown / UNetUp / GeneratorUNet)
+  simple_forward      cgan/models.py:147-216           (GeneratorSimpleRegressor, eval mode)
   sn_weight           torch/nn/utils/spectral_norm.py:92-114 (legacy hook attached at cgan/models.py:236-238)
   d_forward           cgan/models.py:222-258           (Discriminator)
   init_state          cgan/models.py:37-48 + cgan/cgan_train_enhanced.py:229-232,256-257
@@ -179,6 +180,24 @@ def g_forward(g, x, delta_scale: float = 0.3, train: bool = True,
         if taps is not None:
             taps[name] = h
     return g_tail(g["up4.0.weight"], g["fc_delta.1.weight"], g["fc_delta.1.bias"], h, delta_scale, taps)
+
+
+SIMPLE_CONVS = [0, 3, 7, 10, 14, 17, 21, 24]  # indices of the Conv2d entries of GeneratorSimpleRegressor.features
+
+
+def simple_forward(g, x, delta_scale: float = 0.3):
+    """GeneratorSimpleRegressor in eval mode (cgan/models.py:162-216): [conv3x3 + IN + ReLU] x 2 + maxpool, four times;
+    avg-pool -> Linear 512-256-64-4 (ReLU between, dropout off) -> tanh -> * delta_scale.  g: its state dict."""
+    h = x
+    for i, idx in enumerate(SIMPLE_CONVS):
+        h = F.conv2d(_r(h), _r(g[f"features.{idx}.weight"]), g[f"features.{idx}.bias"], 1, 1)
+        h = _r(F.relu(_inorm(_r(h))))
+        if i % 2 == 1:
+            h = F.max_pool2d(h, 2, 2)
+    f = h.mean(dim=(2, 3))
+    h1 = F.relu(F.linear(f, g["regressor.2.weight"], g["regressor.2.bias"]))
+    h2 = F.relu(F.linear(h1, g["regressor.5.weight"], g["regressor.5.bias"]))
+    return torch.tanh(F.linear(h2, g["regressor.8.weight"], g["regressor.8.bias"])) * delta_scale
 
 
 def g_mask_shapes(B: int, S: int):
