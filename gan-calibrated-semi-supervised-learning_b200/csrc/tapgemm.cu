@@ -451,6 +451,220 @@ __global__ void __launch_bounds__(192, 1) tapgemm_persistent_kernel(const __grid
   if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
 }
 
+// ------------------------------------------------------------------------------------------------ CTA-pair variant
+// The same persistent kernel on CTA PAIRS (cluster 2x1x1, tcgen05 cta_group::2): the two SMs of a TPC take two adjacent
+// pixel tiles of the same output-channel block and run ONE 256 x BN MMA per k-step.  Each CTA stages its own 128-pixel
+// activation box and only HALF of the weight slice (BN/2 rows); the tensor cores read the other half from the peer's shared
+// memory.  Per FLOP that halves the shared-memory fill and the B-operand reads, which is what bounds the one-CTA kernel
+// (128 B/clk of operand reads at BN = 128).  Measured notes: (1) the MMAs alone (no operand pipeline) run at
+// 1.6-2.0 PFLOP/s in this form; (2) a remote mbarrier arrive must use the DEFAULT semantics - an explicit .release.cluster
+// fences the arriving thread for ~1000 cycles and serialised the whole pipeline (350 instead of 990 TFLOP/s); (3) with that
+// fixed the MMA thread waits on `full` about half of the time at BN = 128: one TMA-issuing thread per CTA is the next limit.
+// Protocol (as in CUTLASS's 2SM kernels): both CTAs issue their TMA
+// loads against the LEADER's `full` barrier (count 2: one arrive per producer + all transaction bytes); the leader's MMA thread
+// issues tcgen05.mma.cta_group::2 and commits with a multicast arrive on the `empty` / `tmem_full` barriers of both CTAs; the
+// epilogue warps of both CTAs drain their own 128 TMEM lanes and arrive on the leader's `tmem_empty`.
+template <int BN>
+struct TapGemmP2Cfg {
+  static constexpr int A_BYTES = 128 * 128;
+  static constexpr int B_BYTES = (BN / 2) * 128;     // this CTA's half of the weight slice
+  static constexpr int STAGES = (192 * 1024) / (A_BYTES + B_BYTES);
+  static constexpr int RED_BYTES = 4 * BN * 8;
+  static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + RED_BYTES + 1024 + 1024;
+};
+
+template <int BN, int MODE>
+__global__ void __launch_bounds__(192, 1) tapgemm_pair_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                              const __grid_constant__ CUtensorMap tmB, TapGemmParams p,
+                                                              int ptiles, int nblocks, int total2) {
+  using Cfg = TapGemmP2Cfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * Cfg::A_BYTES;
+  float2* red = reinterpret_cast<float2*>(sB + STAGES * Cfg::B_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(red) + Cfg::RED_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;      // [2]
+  uint64_t* tmem_empty = tmem_full + 2;      // [2] (used in the leader only)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank_u32();
+  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  const int ntaps = MODE == 0 ? 16 : (MODE == 1 ? 4 : 9);
+  const int niters = ntaps * p.kchunks;
+  const int ptiles2 = ptiles >> 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 2);   // (leader's) one arrive per producer of the pair + the transaction bytes of both
+      mbar_init(&empty[s], 1);  // multicast commit from the leader's MMA thread
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 8);  // 4 epilogue warps x 2 CTAs
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc2<2 * BN>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0, phase = 0;
+      for (int t = pair; t < total2; t += npairs) {
+        const int pt = 2 * (t % ptiles2) + (int)rank, nb = (t / ptiles2) % nblocks, parity = t / (ptiles2 * nblocks);
+        const int tx = pt % p.tiles_x, ty = (pt / p.tiles_x) % p.tiles_y, tn = pt / (p.tiles_x * p.tiles_y);
+        const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
+        const int py = parity >> 1, px = parity & 1, ncol0 = nb * BN + (int)rank * (BN / 2);
+        for (int tap = 0; tap < ntaps; ++tap) {
+          for (int cc = 0; cc < p.kchunks; ++cc) {
+            mbar_wait(&empty[stage], phase ^ 1);
+            // both CTAs load against the LEADER's barrier (cta_group::2 TMA): no relay hop between "landed" and "MMA may start"
+            const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
+            if (rank == 0) mbar_expect_tx(&full[stage], 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
+            else mbar_arrive_cluster(lead_full);
+            void* dA = sA + stage * Cfg::A_BYTES;
+            if (MODE == 0) {
+              const int ky = tap >> 2, kx = tap & 3;
+              const int fy = (ky - 1) >> 1, di = (ky - 1) & 1, fx = (kx - 1) >> 1, dj = (kx - 1) & 1;
+              tma2_load_5d(dA, &tmA, lead_full, dj * p.Cin + cc * 64, x0 + fx, di, y0 + fy, n0);
+            } else if (MODE == 1) {
+              const int a = tap >> 1, b = tap & 1;
+              tma2_load_4d(dA, &tmA, lead_full, cc * 64, x0 + px + b - 1, y0 + py + a - 1, n0);
+            } else {
+              tma2_load_4d(dA, &tmA, lead_full, cc * 64, x0 + tap % 3 - 1, y0 + tap / 3 - 1, n0);
+            }
+            tma2_load_2d(sB + stage * Cfg::B_BYTES, &tmB, lead_full, tap * p.Cin + cc * 64, parity * p.Cout + ncol0);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(256, BN, 0, 0);
+      constexpr uint32_t DHI = umma_desc_hi_sw128(1024);
+      const uint32_t a_lo0 = umma_desc_lo(smem_u32(sA), 16), b_lo0 = umma_desc_lo(smem_u32(sB), 16);
+      int stage = 0, phase = 0, lt = 0;
+      for (int t = pair; t < total2; t += npairs, ++lt) {
+        const int buf = lt & 1;
+        mbar_wait_cluster(&tmem_empty[buf], ((lt >> 1) & 1) ^ 1);  // arrivals come from both CTAs
+        tc_fence_after();
+        for (int it = 0; it < niters; ++it) {
+          mbar_wait_cluster(&full[stage], phase);  // both CTAs' boxes have landed
+          tc_fence_after();
+          const uint32_t alo = a_lo0 + stage * (Cfg::A_BYTES >> 4), blo = b_lo0 + stage * (Cfg::B_BYTES >> 4);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma2_bf16(tmem_base + buf * BN, umma_desc_join(DHI, alo + 2 * k), umma_desc_join(DHI, blo + 2 * k), idesc,
+                       k != 0 ? 1u : (uint32_t)(it != 0));
+          // EXPERIMENT: release ring slots in groups of `p.f32out >> 8` stages (one multicast commit each)
+          umma2_commit(&empty[stage]);  // frees the ring slot in BOTH CTAs
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma2_commit(&tmem_full[buf]);
+      }
+    }
+  } else {
+    const int q = warp & 3;  // TMEM lane quarter this warp may read (warps 2-5)
+    const int r = q * 32 + lane;
+    const int bw = r % p.BW, bh = (r / p.BW) % p.BH, bi = r / (p.BW * p.BH);
+    int lt = 0;
+    for (int t = pair; t < total2; t += npairs, ++lt) {
+      const int pt = 2 * (t % ptiles2) + (int)rank, nb = (t / ptiles2) % nblocks, parity = t / (ptiles2 * nblocks);
+      const int tx = pt % p.tiles_x, ty = (pt / p.tiles_x) % p.tiles_y, tn = pt / (p.tiles_x * p.tiles_y);
+      const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
+      const int py = parity >> 1, px = parity & 1, ncol0 = nb * BN;
+      const int n = n0 + bi;
+      int oy = y0 + bh, ox = x0 + bw;
+      if (MODE == 1) { oy = 2 * oy + py; ox = 2 * ox + px; }
+      const bool valid = n < p.N;
+      const long long pix_off = (((long long)n * p.Ho + oy) * p.Wo + ox) * p.ldy + ncol0;
+      const int buf = lt & 1;
+      const uint32_t acc = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
+      mbar_wait(&tmem_full[buf], (lt >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t v0[16], v1[16];
+        tmem_ld16(acc + c0, v0);
+        tmem_ld16(acc + c0 + 16, v1);
+        tmem_ld_wait();
+        if (c0 == BN - 32) {  // last read of this accumulator: hand it back to the leader's MMA thread
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tmem_empty[buf]), 0));
+        }
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          f[j] = __uint_as_float(v0[j]);
+          f[16 + j] = __uint_as_float(v1[j]);
+        }
+        if (p.scale) {
+          const float sc = __ldg(p.scale);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] *= sc;
+        }
+        if (p.bias) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] += __ldg(p.bias + ncol0 + c0 + j);
+        }
+        if (valid && p.f32out) {
+          float4* d4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.y) + pix_off + c0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) d4[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+        } else if (valid) {
+          uint32_t o[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) o[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
+          if (p.st256) {
+            st_global_v8(p.y + pix_off + c0, o);
+            st_global_v8(p.y + pix_off + c0 + 16, o + 8);
+          } else {
+            uint4* d4 = reinterpret_cast<uint4*>(p.y + pix_off + c0);
+            d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+            d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+            d4[2] = make_uint4(o[8], o[9], o[10], o[11]);
+            d4[3] = make_uint4(o[12], o[13], o[14], o[15]);
+          }
+        }
+        if (p.stats) {  // statistics of the bf16-ROUNDED values; lane L gets channel c0 + L
+          float sq[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            f[j] = __bfloat162float(__float2bfloat16(f[j]));
+            sq[j] = f[j] * f[j];
+          }
+          const float s1 = warp_transpose_sum32(f), s2 = warp_transpose_sum32(sq);
+          red[q * BN + c0 + lane] = make_float2(s1, s2);
+        }
+      }
+      if (p.stats) {
+        named_bar_sync(1, 128);
+        for (int c = r; c < BN; c += 128) {
+          const float2 a = red[c], b = red[BN + c], cc = red[2 * BN + c], d = red[3 * BN + c];
+          long long* st = p.stats + ((long long)n0 * p.Cout + ncol0 + c) * 2;
+          stat_add(st, (a.x + b.x) + (cc.x + d.x));
+          stat_add(st + 1, (a.y + b.y) + (cc.y + d.y));
+        }
+        named_bar_sync(1, 128);  // scratch may be overwritten by the next tile
+      }
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();  // both CTAs are done with each other's shared memory / TMEM before either leaves
+  if (warp == 1) tmem_dealloc2<2 * BN>(tmem_base);
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 static bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
@@ -538,10 +752,17 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
   if (rc) return rc;
   const int K = (mode == 0 ? 16 : mode == 3 ? 9 : 4) * Cin;
   const int rows = (mode == 1 ? 4 : 1) * Cout;
+  // CTA pairs (cta_group::2, 256-row MMAs) for the persistent BN = 128 / 256 kernels: needs an even number of pixel tiles;
+  // B2C_TAPGEMM_2CTA=0 switches it off, =128 / =256 restricts it to one tile width (A/B runs)
+  static const int pair_env = getenv("B2C_TAPGEMM_2CTA") ? atoi(getenv("B2C_TAPGEMM_2CTA")) : 1;
+  static const bool persistent_env = !(getenv("B2C_TAPGEMM_PERSIST") && getenv("B2C_TAPGEMM_PERSIST")[0] == '0');
+  const int ptiles_all = p.tiles_x * p.tiles_y * tiles_n;
+  const bool use_pair = persistent_env && MT == 1 && (BN == 128 || BN == 256) && pair_env && (pair_env == 1 || pair_env == BN) &&
+                        ptiles_all % 2 == 0;
   {
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
     uint64_t str[1] = {(uint64_t)2 * K};
-    uint32_t box[2] = {64, (uint32_t)BN};
+    uint32_t box[2] = {64, (uint32_t)(use_pair ? BN / 2 : BN)};  // a CTA of a pair stages half of the weight slice
     rc = b2c_make_tmap_bf16(&tmB, wpack, 2, dims, str, box);
     if (rc) return rc;
   }
@@ -569,6 +790,42 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
     const int ptiles = (int)grid.x, nblocks = (int)grid.y, total = (int)(grid.x * grid.y * grid.z);
     const int ctas = total < sms ? total : sms;
     const cudaStream_t st = (cudaStream_t)stream;
+    if (use_pair) {
+      static bool attr2 = false;
+      if (!attr2) {
+        cudaFuncSetAttribute(tapgemm_pair_kernel<128, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmP2Cfg<128>::SMEM);
+        cudaFuncSetAttribute(tapgemm_pair_kernel<128, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmP2Cfg<128>::SMEM);
+        cudaFuncSetAttribute(tapgemm_pair_kernel<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmP2Cfg<128>::SMEM);
+        cudaFuncSetAttribute(tapgemm_pair_kernel<256, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmP2Cfg<256>::SMEM);
+        cudaFuncSetAttribute(tapgemm_pair_kernel<256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmP2Cfg<256>::SMEM);
+        cudaFuncSetAttribute(tapgemm_pair_kernel<256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TapGemmP2Cfg<256>::SMEM);
+        attr2 = true;
+      }
+      const int total2 = total / 2;
+      int pairs = sms / 2;
+      if (pairs > total2) pairs = total2;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(2 * pairs);
+      cfg.blockDim = dim3(192);
+      cfg.dynamicSmemBytes = BN == 128 ? TapGemmP2Cfg<128>::SMEM : TapGemmP2Cfg<256>::SMEM;
+      cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr; cfg.numAttrs = 1;
+      cudaError_t e;
+      const int kmode = mode == 3 ? 2 : mode;
+      if (BN == 128 && kmode == 0) e = cudaLaunchKernelEx(&cfg, tapgemm_pair_kernel<128, 0>, tmA, tmB, p, ptiles, nblocks, total2);
+      else if (BN == 128 && kmode == 1) e = cudaLaunchKernelEx(&cfg, tapgemm_pair_kernel<128, 1>, tmA, tmB, p, ptiles, nblocks, total2);
+      else if (BN == 128) e = cudaLaunchKernelEx(&cfg, tapgemm_pair_kernel<128, 2>, tmA, tmB, p, ptiles, nblocks, total2);
+      else if (kmode == 0) e = cudaLaunchKernelEx(&cfg, tapgemm_pair_kernel<256, 0>, tmA, tmB, p, ptiles, nblocks, total2);
+      else if (kmode == 1) e = cudaLaunchKernelEx(&cfg, tapgemm_pair_kernel<256, 1>, tmA, tmB, p, ptiles, nblocks, total2);
+      else e = cudaLaunchKernelEx(&cfg, tapgemm_pair_kernel<256, 2>, tmA, tmB, p, ptiles, nblocks, total2);
+      if (e != cudaSuccess) { b2c_set_error("tapgemm_pair_kernel launch: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+      rc = b2c_check_launch("tapgemm_pair_kernel");
+      if (rc == 0 && stats && !fuse_stats) rc = b2c_in_stats(y, ldy, stats, N, p.Ho * p.Wo, Cout, stream);
+      return rc;
+    }
     if (BN == 128 && mode == 3)
       tapgemm_persistent_kernel<128, 2><<<ctas, 192, TapGemmPCfg<128>::SMEM, st>>>(tmA, tmB, p, ptiles, nblocks, total);
     else if (mode == 3)
