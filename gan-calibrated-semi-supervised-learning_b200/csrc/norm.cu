@@ -444,7 +444,7 @@ template <int MODE> struct CkCfg {
   static constexpr int NT = MODE == M_BWD2 ? 3 : 2;      // operands streamed: z, g (, h)
   static constexpr int NSUM = MODE == M_BWD2 ? 5 : 2;
   static constexpr int STAGE_BYTES = NT * CK_BOX_BYTES;
-  static constexpr int AUX_BYTES = (NSUM * 8 * 64 + 2 * NSUM * 64) * 4 + 2 * 32 * 8;  // red + part + tot, barriers
+  static constexpr int AUX_BYTES = (NSUM * 8 * 64 + 3 * NSUM * 64) * 4 + 2 * 32 * 8;  // red + part[2] + tot, barriers
   static constexpr int smem(int stages) { return 1024 + stages * STAGE_BYTES + AUX_BYTES; }
 };
 
@@ -511,21 +511,24 @@ template <int MODE>
 __global__ void __launch_bounds__(CK_THREADS, MODE == M_BWD2 ? 2 : 3) plane_cluster_kernel(const __grid_constant__ CUtensorMap tmZ,
                                                                    const __grid_constant__ CUtensorMap tmG,
                                                                    const __grid_constant__ CUtensorMap tmH, NormArgs a,
-                                                                   int CS, int nst, int RS) {
+                                                                   int CS, int nst, int RS, int nunits) {
+  // PERSISTENT: a cluster walks the units u = cluster, cluster + #clusters, ... (unit = (image, 64-channel group)).  The TMA ring
+  // keeps running across units - while the consumers finish the outputs of unit u the first boxes of unit u+1 are already
+  // landing - and the barrier / descriptor / launch prologue is paid once per CTA instead of once per 64-128 KB of data.
   using Cfg = CkCfg<MODE>;
   constexpr int NSUM = Cfg::NSUM;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* red = reinterpret_cast<float*>(ring + (size_t)RS * Cfg::STAGE_BYTES);  // [NSUM][8 warps][64]
-  float* part = red + NSUM * 8 * 64;                                            // [NSUM][64]: this CTA's partial sums
-  float* tot = part + NSUM * 64;                                                // [NSUM][64]: unit totals
+  float* part = red + NSUM * 8 * 64;                                            // [2][NSUM][64]: this CTA's partial sums (by unit parity)
+  float* tot = part + 2 * NSUM * 64;                                            // [NSUM][64]: unit totals
   uint64_t* full = reinterpret_cast<uint64_t*>(tot + NSUM * 64);
   uint64_t* empty = full + 32;
 
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-  const int rank = blockIdx.x, cg = blockIdx.y, n = blockIdx.z;  // gridDim.x == CS: blockIdx.x is the rank in the cluster
-  const bool resident = nst <= RS;
-  const long long pix0 = (long long)n * a.HW + (long long)rank * nst * CK_PIXB;  // first pixel row of this CTA's slice
+  const int rank = blockIdx.x % CS, cluster = blockIdx.x / CS, nclusters = gridDim.x / CS;
+  const int ncg = a.C / 64;
+  const bool resident = nst <= RS;  // the slice of a unit fits the ring: phase 2 re-reads shared memory instead of re-streaming
 
   if (t == 0) {
     tma_prefetch_desc(&tmZ);
@@ -540,209 +543,216 @@ __global__ void __launch_bounds__(CK_THREADS, MODE == M_BWD2 ? 2 : 3) plane_clus
   __syncthreads();
 
   if (warp == 8) {
-    // The producer joins the cluster barrier BETWEEN the two phases' loads: its phase-2 loads wait for ring slots that the
-    // consumers only free after that barrier, so it must have arrived before it blocks (and it never blocks before having
-    // the first RS boxes of phase 2 in flight).
-    int slot = 0, round = 0;  // load k goes to slot k % RS; round = k / RS
-    auto issue = [&](int box) {
+    // Producer.  Per unit it joins the cluster barrier BETWEEN the two phases' loads: its phase-2 loads wait for ring slots
+    // that the consumers only free after that barrier, so it must have arrived before it can block on them.
+    int slot = 0, round = 0;  // load k (counted over the whole kernel) goes to slot k % RS; round = k / RS
+    auto issue = [&](int cg, long long row0, int box) {
       if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
       mbar_expect_tx(&full[slot], Cfg::STAGE_BYTES);
       uint8_t* dst = ring + (size_t)slot * Cfg::STAGE_BYTES;
-      const int row = (int)(pix0 + (long long)box * CK_PIXB);
+      const int row = (int)(row0 + (long long)box * CK_PIXB);
       tma_load_2d(dst, &tmZ, &full[slot], cg * 64, row);
       tma_load_2d(dst + CK_BOX_BYTES, &tmG, &full[slot], cg * 64, row);
       if (MODE == M_BWD2) tma_load_2d(dst + 2 * CK_BOX_BYTES, &tmH, &full[slot], cg * 64, row);
       if (++slot == RS) { slot = 0; ++round; }
     };
-    if (elect_one())
-      for (int k = 0; k < nst; ++k) issue(k);
-    __syncwarp();
-    if (CS > 1) cluster_arrive();
-    if (!resident && elect_one()) {
-      // both elect_one() branches run on the same lane, but `slot` / `round` live in that lane's registers only if it is
-      // the same lane: elect.sync picks the lowest active lane both times
-      for (int k = 0; k < nst; ++k) issue(k);
+    const bool lead = elect_one();
+    for (int u = cluster; u < nunits; u += nclusters) {
+      const int n = u / ncg, cg = u % ncg;
+      const long long row0 = (long long)n * a.HW + (long long)rank * nst * CK_PIXB;
+      if (lead)
+        for (int k = 0; k < nst; ++k) issue(cg, row0, k);
+      __syncwarp();
+      if (CS > 1) cluster_arrive();
+      if (lead && !resident)
+        for (int k = 0; k < nst; ++k) issue(cg, row0, k);
+      __syncwarp();
+      if (CS > 1) cluster_wait();
     }
-    __syncwarp();
-    if (CS > 1) { cluster_wait(); cluster_arrive(); cluster_wait(); }
+    if (CS > 1) { cluster_arrive(); cluster_wait(); }  // nobody leaves while a peer may still read its partial sums
     return;
   }
 
   // ---------------------------------------------------------------- consumers: 8 channel vectors x 32 pixel rows
   const int cv = t & 7, prow = t >> 3;
-  const int c0 = cg * 64 + cv * 8;
   const int off0 = prow * 128 + ((cv ^ (prow & 7)) << 4);  // this thread's 16 bytes of row prow (row u*32 + prow: + u * 4096)
-  f32x2 rstd2[4], shift2[4];
-  {
-    float mean[8], rstd[8];
-    load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);  // `mean` holds -mean * rstd
-#pragma unroll
-    for (int j = 0; j < 4; ++j) { rstd2[j] = f2_pack(rstd[2 * j], rstd[2 * j + 1]); shift2[j] = f2_pack(mean[2 * j], mean[2 * j + 1]); }
-  }
   const f32x2 k0 = f2_pack(a.slope, a.slope), k1 = f2_pack(1.f - a.slope, 1.f - a.slope);
-  f32x2 acc[NSUM][4];
-#pragma unroll
-  for (int s2 = 0; s2 < NSUM; ++s2)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) acc[s2][j] = 0ull;
-  int slot = 0, par = 0;
-  // ---- phase 1: plane sums
-  for (int k = 0; k < nst; ++k) {
-    mbar_wait(&full[slot], par);
-    const uint8_t* st = ring + (size_t)slot * Cfg::STAGE_BYTES + off0;
-#pragma unroll(MODE == M_BWD2 ? 1 : 2)
-    for (int u = 0; u < CK_PIXB / 32; ++u) {
-      const uint4 zw = *reinterpret_cast<const uint4*>(st + u * 4096);
-      const uint4 gw = *reinterpret_cast<const uint4*>(st + CK_BOX_BYTES + u * 4096);
-      const uint32_t zq[4] = {zw.x, zw.y, zw.z, zw.w}, gq[4] = {gw.x, gw.y, gw.z, gw.w};
-      uint32_t hq[4] = {0, 0, 0, 0};
-      if (MODE == M_BWD2) {
-        const uint4 hw = *reinterpret_cast<const uint4*>(st + 2 * CK_BOX_BYTES + u * 4096);
-        hq[0] = hw.x; hq[1] = hw.y; hq[2] = hw.z; hq[3] = hw.w;
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const f32x2 xh = f2_fma(f2_bf16x2(zq[j]), rstd2[j], shift2[j]);
-        const f32x2 gn = f2_mul(f2_bf16x2(gq[j]), f2_dact(xh, k0, k1));
-        if (MODE == M_BWD) {
-          acc[0][j] = f2_add(acc[0][j], gn);
-          acc[1][j] = f2_fma(gn, xh, acc[1][j]);
-        } else {
-          const f32x2 h = f2_bf16x2(hq[j]);
-          acc[0][j] = f2_add(acc[0][j], h);
-          acc[1][j] = f2_fma(h, xh, acc[1][j]);
-          acc[2 % NSUM][j] = f2_add(acc[2 % NSUM][j], gn);
-          acc[3 % NSUM][j] = f2_fma(gn, xh, acc[3 % NSUM][j]);
-          acc[4 % NSUM][j] = f2_fma(h, gn, acc[4 % NSUM][j]);
-        }
-      }
-    }
-    if (!resident) {
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty[slot]);
-    }
-    if (++slot == RS) { slot = 0; par ^= 1; }
-  }
-  // block reduction: lanes with equal (lane & 7) hold the same channel vector
-#pragma unroll
-  for (int s2 = 0; s2 < NSUM; ++s2)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float v0, v1;
-      f2_split(acc[s2][j], v0, v1);
-      v0 += __shfl_xor_sync(0xffffffffu, v0, 8); v1 += __shfl_xor_sync(0xffffffffu, v1, 8);
-      v0 += __shfl_xor_sync(0xffffffffu, v0, 16); v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
-      if (lane < 8) {
-        red[(s2 * 8 + warp) * 64 + cv * 8 + 2 * j] = v0;
-        red[(s2 * 8 + warp) * 64 + cv * 8 + 2 * j + 1] = v1;
-      }
-    }
-  named_bar_sync(1, 256);
-  for (int i = t; i < NSUM * 64; i += 256) {
-    const int s2 = i >> 6, c = i & 63;
-    float v = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) v += red[(s2 * 8 + w) * 64 + c];
-    part[i] = v;
-  }
-  // ---- exchange the CS partial vectors through distributed shared memory
-  if (CS > 1) {
-    cluster_arrive();
-    cluster_wait();
-  } else {
-    named_bar_sync(1, 256);
-  }
-  for (int i = t; i < NSUM * 64; i += 256) {
-    float v = part[i];
-    if (CS > 1) {
-      float pv[8];
-#pragma unroll
-      for (int r = 0; r < 8; ++r) pv[r] = r < CS ? ld_dsmem_f32(part + i, (uint32_t)r) : 0.f;  // all loads in flight at once
-      v = 0.f;
-#pragma unroll
-      for (int r = 0; r < 8; ++r) v += pv[r];  // rank order: identical on every CTA of the cluster
-    }
-    tot[i] = v;
-  }
-  named_bar_sync(1, 256);
-  if (CS > 1) cluster_arrive();  // peers may exit only after everyone has read their `part` (waited on before exit)
-  // ---- phase 2: outputs
-  const float inv = 1.f / (float)a.HW;
-  f32x2 sm[NSUM][4];
-#pragma unroll
-  for (int s2 = 0; s2 < NSUM; ++s2)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) sm[s2][j] = f2_pack(tot[s2 * 64 + cv * 8 + 2 * j] * inv, tot[s2 * 64 + cv * 8 + 2 * j + 1] * inv);
-  // bwd : o = (gn - m0 - xh m1) rstd = fma(gn, rstd, fma(xh, c1, c0)),  c0 = -m0 rstd, c1 = -m1 rstd
-  // bwd2: Ph = h - mh - xh ma, Pg = gn - mg - xh mc, q = mhg - mh mg - ma mc,
-  //       og = Ph rstd dact,  oz = -(q xh + mc Ph + ma Pg) rstd^2
-  // bwd2 expanded so that every output is a short FMA chain over per-channel constants:
-  //   og = (h rstd + E + xh F) dact,            E = -mh rstd, F = -ma rstd
-  //   oz = A xh + B h + Cg gn + D,              A = -rstd^2 (q - 2 ma mc), B = -rstd^2 mc, Cg = -rstd^2 ma, D = rstd^2 (mc mh + ma mg)
-  f32x2 c0v[4], c1v[4], cA[MODE == M_BWD2 ? 4 : 1], cB[MODE == M_BWD2 ? 4 : 1], cC[MODE == M_BWD2 ? 4 : 1], cD[MODE == M_BWD2 ? 4 : 1];
   const f32x2 neg1 = f2_pack(-1.f, -1.f);
+  const float inv = 1.f / (float)a.HW;
+  int slot = 0, par = 0, ui = 0;
+  for (int u = cluster; u < nunits; u += nclusters, ++ui) {
+    const int n = u / ncg, cg = u % ncg;
+    const int c0 = cg * 64 + cv * 8;
+    const long long pix0 = (long long)n * a.HW + (long long)rank * nst * CK_PIXB;
+    float* upart = part + (ui & 1) * NSUM * 64;
+    f32x2 rstd2[4], shift2[4];
+    {
+      float mean[8], rstd[8];
+      load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);  // `mean` holds -mean * rstd
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    if (MODE == M_BWD) {
-      c0v[j] = f2_mul(f2_mul(sm[0][j], rstd2[j]), neg1);
-      c1v[j] = f2_mul(f2_mul(sm[1][j], rstd2[j]), neg1);
-    } else {
-      const f32x2 mh = sm[0][j], ma = sm[1][j], mg = sm[2 % NSUM][j], mc = sm[3 % NSUM][j], mhg = sm[4 % NSUM][j];
-      const f32x2 nr2 = f2_mul(f2_mul(rstd2[j], rstd2[j]), neg1);                         // -rstd^2
-      const f32x2 q = f2_fma(f2_fma(mh, mg, f2_mul(ma, mc)), neg1, mhg);                   // mhg - mh mg - ma mc
-      const f32x2 mamc = f2_mul(ma, mc);
-      cA[j % (MODE == M_BWD2 ? 4 : 1)] = f2_mul(nr2, f2_fma(f2_add(mamc, mamc), neg1, q));
-      cB[j % (MODE == M_BWD2 ? 4 : 1)] = f2_mul(nr2, mc);
-      cC[j % (MODE == M_BWD2 ? 4 : 1)] = f2_mul(nr2, ma);
-      cD[j % (MODE == M_BWD2 ? 4 : 1)] = f2_mul(f2_mul(nr2, neg1), f2_fma(mc, mh, f2_mul(ma, mg)));
-      c0v[j] = f2_mul(f2_mul(mh, rstd2[j]), neg1);                                         // E
-      c1v[j] = f2_mul(f2_mul(ma, rstd2[j]), neg1);                                         // F
+      for (int j = 0; j < 4; ++j) { rstd2[j] = f2_pack(rstd[2 * j], rstd[2 * j + 1]); shift2[j] = f2_pack(mean[2 * j], mean[2 * j + 1]); }
     }
-  }
-  const long long obase = (pix0 + prow) * 1;  // pixel row of u = 0, stage 0
-  for (int k = 0; k < nst; ++k) {
-    if (!resident) mbar_wait(&full[slot], par);
-    const uint8_t* st = ring + (size_t)(resident ? k : slot) * Cfg::STAGE_BYTES + off0;
+    f32x2 acc[NSUM][4];
+#pragma unroll
+    for (int s2 = 0; s2 < NSUM; ++s2)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[s2][j] = 0ull;
+    const int slot0 = slot;  // where this unit's first box sits (resident mode re-reads from here)
+    // ---- phase 1: plane sums
+    for (int k = 0; k < nst; ++k) {
+      mbar_wait(&full[slot], par);
+      const uint8_t* st = ring + (size_t)slot * Cfg::STAGE_BYTES + off0;
 #pragma unroll(MODE == M_BWD2 ? 1 : 2)
-    for (int u = 0; u < CK_PIXB / 32; ++u) {
-      const long long pix = obase + (long long)k * CK_PIXB + u * 32;
-      const uint4 zw = *reinterpret_cast<const uint4*>(st + u * 4096);
-      const uint4 gw = *reinterpret_cast<const uint4*>(st + CK_BOX_BYTES + u * 4096);
-      const uint32_t zq[4] = {zw.x, zw.y, zw.z, zw.w}, gq[4] = {gw.x, gw.y, gw.z, gw.w};
-      if (MODE == M_BWD) {
-        uint32_t o[4];
+      for (int v = 0; v < CK_PIXB / 32; ++v) {
+        const uint4 zw = *reinterpret_cast<const uint4*>(st + v * 4096);
+        const uint4 gw = *reinterpret_cast<const uint4*>(st + CK_BOX_BYTES + v * 4096);
+        const uint32_t zq[4] = {zw.x, zw.y, zw.z, zw.w}, gq[4] = {gw.x, gw.y, gw.z, gw.w};
+        uint32_t hq[4] = {0, 0, 0, 0};
+        if (MODE == M_BWD2) {
+          const uint4 hw = *reinterpret_cast<const uint4*>(st + 2 * CK_BOX_BYTES + v * 4096);
+          hq[0] = hw.x; hq[1] = hw.y; hq[2] = hw.z; hq[3] = hw.w;
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const f32x2 xh = f2_fma(f2_bf16x2(zq[j]), rstd2[j], shift2[j]);
           const f32x2 gn = f2_mul(f2_bf16x2(gq[j]), f2_dact(xh, k0, k1));
-          o[j] = f2_to_bf16x2(f2_fma(gn, rstd2[j], f2_fma(xh, c1v[j], c0v[j])));
+          if (MODE == M_BWD) {
+            acc[0][j] = f2_add(acc[0][j], gn);
+            acc[1][j] = f2_fma(gn, xh, acc[1][j]);
+          } else {
+            const f32x2 h = f2_bf16x2(hq[j]);
+            acc[0][j] = f2_add(acc[0][j], h);
+            acc[1][j] = f2_fma(h, xh, acc[1][j]);
+            acc[2 % NSUM][j] = f2_add(acc[2 % NSUM][j], gn);
+            acc[3 % NSUM][j] = f2_fma(gn, xh, acc[3 % NSUM][j]);
+            acc[4 % NSUM][j] = f2_fma(h, gn, acc[4 % NSUM][j]);
+          }
         }
-        *reinterpret_cast<uint4*>(a.o0 + pix * a.ldo0 + c0) = make_uint4(o[0], o[1], o[2], o[3]);
-      } else {
-        const uint4 hw = *reinterpret_cast<const uint4*>(st + 2 * CK_BOX_BYTES + u * 4096);
-        const uint32_t hq[4] = {hw.x, hw.y, hw.z, hw.w};
-        uint32_t og[4], oz[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          constexpr int M4 = MODE == M_BWD2 ? 4 : 1;
-          const f32x2 xh = f2_fma(f2_bf16x2(zq[j]), rstd2[j], shift2[j]);
-          const f32x2 da = f2_dact(xh, k0, k1);
-          const f32x2 gn = f2_mul(f2_bf16x2(gq[j]), da);
-          const f32x2 h = f2_bf16x2(hq[j]);
-          og[j] = f2_to_bf16x2(f2_mul(f2_fma(h, rstd2[j], f2_fma(xh, c1v[j], c0v[j])), da));
-          oz[j] = f2_to_bf16x2(f2_fma(xh, cA[j % M4], f2_fma(h, cB[j % M4], f2_fma(gn, cC[j % M4], cD[j % M4]))));
-        }
-        *reinterpret_cast<uint4*>(a.o0 + pix * a.ldo0 + c0) = make_uint4(og[0], og[1], og[2], og[3]);
-        *reinterpret_cast<uint4*>(a.o1 + pix * a.ldo1 + c0) = make_uint4(oz[0], oz[1], oz[2], oz[3]);
       }
-    }
-    if (!resident) {
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty[slot]);
+      if (!resident) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[slot]);
+      }
       if (++slot == RS) { slot = 0; par ^= 1; }
     }
+    // block reduction: lanes with equal (lane & 7) hold the same channel vector
+#pragma unroll
+    for (int s2 = 0; s2 < NSUM; ++s2)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float v0, v1;
+        f2_split(acc[s2][j], v0, v1);
+        v0 += __shfl_xor_sync(0xffffffffu, v0, 8); v1 += __shfl_xor_sync(0xffffffffu, v1, 8);
+        v0 += __shfl_xor_sync(0xffffffffu, v0, 16); v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
+        if (lane < 8) {
+          red[(s2 * 8 + warp) * 64 + cv * 8 + 2 * j] = v0;
+          red[(s2 * 8 + warp) * 64 + cv * 8 + 2 * j + 1] = v1;
+        }
+      }
+    named_bar_sync(1, 256);
+    for (int i = t; i < NSUM * 64; i += 256) {
+      const int s2 = i >> 6, c = i & 63;
+      float v = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) v += red[(s2 * 8 + w) * 64 + c];
+      upart[i] = v;
+    }
+    // ---- exchange the CS partial vectors through distributed shared memory.  `part` is double-buffered by unit parity, so
+    // ONE cluster barrier per unit suffices: a CTA overwrites part[b] two units later, after a barrier that every peer could
+    // only reach once it had read part[b].
+    if (CS > 1) {
+      cluster_arrive();
+      cluster_wait();
+    } else {
+      named_bar_sync(1, 256);
+    }
+    for (int i = t; i < NSUM * 64; i += 256) {
+      float v = upart[i];
+      if (CS > 1) {
+        float pv[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) pv[r] = r < CS ? ld_dsmem_f32(upart + i, (uint32_t)r) : 0.f;  // all loads in flight at once
+        v = 0.f;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) v += pv[r];  // rank order: identical on every CTA of the cluster
+      }
+      tot[i] = v;
+    }
+    named_bar_sync(1, 256);
+    // ---- phase 2: outputs
+    f32x2 sm[NSUM][4];
+#pragma unroll
+    for (int s2 = 0; s2 < NSUM; ++s2)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sm[s2][j] = f2_pack(tot[s2 * 64 + cv * 8 + 2 * j] * inv, tot[s2 * 64 + cv * 8 + 2 * j + 1] * inv);
+    // bwd : o = (gn - m0 - xh m1) rstd = fma(gn, rstd, fma(xh, c1, c0)),  c0 = -m0 rstd, c1 = -m1 rstd
+    // bwd2 expanded so that every output is a short FMA chain over per-channel constants:
+    //   og = (h rstd + E + xh F) dact,            E = -mh rstd, F = -ma rstd
+    //   oz = A xh + B h + Cg gn + D,              A = -rstd^2 (q - 2 ma mc), B = -rstd^2 mc, Cg = -rstd^2 ma, D = rstd^2 (mc mh + ma mg)
+    constexpr int M4 = MODE == M_BWD2 ? 4 : 1;
+    f32x2 c0v[4], c1v[4], cA[M4], cB[M4], cC[M4], cD[M4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (MODE == M_BWD) {
+        c0v[j] = f2_mul(f2_mul(sm[0][j], rstd2[j]), neg1);
+        c1v[j] = f2_mul(f2_mul(sm[1][j], rstd2[j]), neg1);
+      } else {
+        const f32x2 mh = sm[0][j], ma = sm[1][j], mg = sm[2 % NSUM][j], mc = sm[3 % NSUM][j], mhg = sm[4 % NSUM][j];
+        const f32x2 nr2 = f2_mul(f2_mul(rstd2[j], rstd2[j]), neg1);                         // -rstd^2
+        const f32x2 q = f2_fma(f2_fma(mh, mg, f2_mul(ma, mc)), neg1, mhg);                   // mhg - mh mg - ma mc
+        const f32x2 mamc = f2_mul(ma, mc);
+        cA[j % M4] = f2_mul(nr2, f2_fma(f2_add(mamc, mamc), neg1, q));
+        cB[j % M4] = f2_mul(nr2, mc);
+        cC[j % M4] = f2_mul(nr2, ma);
+        cD[j % M4] = f2_mul(f2_mul(nr2, neg1), f2_fma(mc, mh, f2_mul(ma, mg)));
+        c0v[j] = f2_mul(f2_mul(mh, rstd2[j]), neg1);                                         // E
+        c1v[j] = f2_mul(f2_mul(ma, rstd2[j]), neg1);                                         // F
+      }
+    }
+    int rslot = slot0;  // resident mode: walk this unit's boxes again
+    for (int k = 0; k < nst; ++k) {
+      const int cur = resident ? rslot : slot;
+      if (!resident) mbar_wait(&full[slot], par);
+      const uint8_t* st = ring + (size_t)cur * Cfg::STAGE_BYTES + off0;
+#pragma unroll(MODE == M_BWD2 ? 1 : 2)
+      for (int v = 0; v < CK_PIXB / 32; ++v) {
+        const long long pix = pix0 + prow + (long long)k * CK_PIXB + v * 32;
+        const uint4 zw = *reinterpret_cast<const uint4*>(st + v * 4096);
+        const uint4 gw = *reinterpret_cast<const uint4*>(st + CK_BOX_BYTES + v * 4096);
+        const uint32_t zq[4] = {zw.x, zw.y, zw.z, zw.w}, gq[4] = {gw.x, gw.y, gw.z, gw.w};
+        if (MODE == M_BWD) {
+          uint32_t o[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const f32x2 xh = f2_fma(f2_bf16x2(zq[j]), rstd2[j], shift2[j]);
+            const f32x2 gn = f2_mul(f2_bf16x2(gq[j]), f2_dact(xh, k0, k1));
+            o[j] = f2_to_bf16x2(f2_fma(gn, rstd2[j], f2_fma(xh, c1v[j], c0v[j])));
+          }
+          *reinterpret_cast<uint4*>(a.o0 + pix * a.ldo0 + c0) = make_uint4(o[0], o[1], o[2], o[3]);
+        } else {
+          const uint4 hw = *reinterpret_cast<const uint4*>(st + 2 * CK_BOX_BYTES + v * 4096);
+          const uint32_t hq[4] = {hw.x, hw.y, hw.z, hw.w};
+          uint32_t og[4], oz[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const f32x2 xh = f2_fma(f2_bf16x2(zq[j]), rstd2[j], shift2[j]);
+            const f32x2 da = f2_dact(xh, k0, k1);
+            const f32x2 gn = f2_mul(f2_bf16x2(gq[j]), da);
+            const f32x2 h = f2_bf16x2(hq[j]);
+            og[j] = f2_to_bf16x2(f2_mul(f2_fma(h, rstd2[j], f2_fma(xh, c1v[j], c0v[j])), da));
+            oz[j] = f2_to_bf16x2(f2_fma(xh, cA[j % M4], f2_fma(h, cB[j % M4], f2_fma(gn, cC[j % M4], cD[j % M4]))));
+          }
+          *reinterpret_cast<uint4*>(a.o0 + pix * a.ldo0 + c0) = make_uint4(og[0], og[1], og[2], og[3]);
+          *reinterpret_cast<uint4*>(a.o1 + pix * a.ldo1 + c0) = make_uint4(oz[0], oz[1], oz[2], oz[3]);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[cur]);  // streaming: this phase-2 box; resident: the unit's box, free for the next unit
+      if (resident) { if (++rslot == RS) rslot = 0; }
+      else if (++slot == RS) { slot = 0; par ^= 1; }
+    }
   }
-  if (CS > 1) cluster_wait();
+  if (CS > 1) { cluster_arrive(); cluster_wait(); }
 }
 
 // rank-2 map over an NHWC bf16 tensor seen as [N*HW pixel rows][C] with pixel stride ld; box = [CK_PIXB rows][64 channels].
@@ -789,8 +799,9 @@ static int try_cluster(const NormArgs& a, cudaStream_t st) {
   const long long npix = (long long)a.N * a.HW;
   if (ck_tmap(&tmZ, a.z, a.ldz, npix, a.C) || ck_tmap(&tmG, a.g, a.ldg, npix, a.C)) return -B2C_ERR_DRIVER;
   if (MODE == M_BWD2) { if (ck_tmap(&tmH, a.h, a.ldh, npix, a.C)) return -B2C_ERR_DRIVER; } else tmH = tmZ;
+  const int nunits = a.N * (a.C / 64);
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(CS, a.C / 64, a.N);
+  cfg.gridDim = dim3(CS * nunits);
   cfg.blockDim = dim3(CK_THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
@@ -798,7 +809,19 @@ static int try_cluster(const NormArgs& a, cudaStream_t st) {
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, plane_cluster_kernel<MODE>, tmZ, tmG, tmH, a, CS, nst, RS);
+  // persistent: as many clusters as can be co-resident (cached per configuration), each walks nunits / nclusters units
+  static int cache_key[8] = {0}, cache_val[8] = {0};
+  const int key = (CS << 20) | smem;
+  int ncl = 0;
+  for (int i = 0; i < 8; ++i) if (cache_key[i] == key) ncl = cache_val[i];
+  if (!ncl) {
+    if (cudaOccupancyMaxActiveClusters(&ncl, plane_cluster_kernel<MODE>, &cfg) != cudaSuccess || ncl <= 0) { cudaGetLastError(); ncl = 148 / CS; }
+    for (int i = 0; i < 8; ++i) if (!cache_key[i]) { cache_key[i] = key; cache_val[i] = ncl; break; }
+  }
+  static const int persist = env_int("B2C_NORM_PERSIST", 1);
+  if (!persist || ncl > nunits) ncl = nunits;
+  cfg.gridDim = dim3(CS * ncl);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, plane_cluster_kernel<MODE>, tmZ, tmG, tmH, a, CS, nst, RS, nunits);
   if (e != cudaSuccess) { b2c_set_error("plane_cluster launch: %s", cudaGetErrorString(e)); return -B2C_ERR_CUDA; }
   return 0;
 }

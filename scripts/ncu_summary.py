@@ -1,7 +1,8 @@
 """Summarise an `ncu --set full` capture (exported with `ncu -i rep --page raw --csv`) per launch and per kernel family.
 Usage: python scripts/ncu_summary.py raw.csv [traffic.json]
-Families follow the C-ABI entry points: convT = convt64_kernel + tapgemm_persistent_kernel<BN, 1> + tapgemm_kernel launched
-with 4 parities (grid.z = 4), conv = tapgemm_persistent_kernel<BN, 0> + the other tapgemm_kernel launches, wgrad = wgrad_kernel."""
+Families follow the C-ABI entry points: convT = convt64_kernel + tapgemm_{persistent,pair}_kernel<BN, 1> + tapgemm_kernel launched
+with 4 parities (grid.z = 4), conv = tapgemm_{persistent,pair}_kernel<BN, 0> + the other tapgemm_kernel launches, wgrad =
+wgrad_kernel; every other kernel is its own family (bandwidth kernels: read the dram% / dramMB columns)."""
 import collections
 import csv
 import json
@@ -42,7 +43,7 @@ def family(name, grid):
         return "b2c_wgrad4s2_bf16"
     if "tapgemm_kernel<(int)32" in name or "tapgemm_kernel<32" in name:
         return "b2c_first_dgrad"
-    m = re.search(r"tapgemm_persistent_kernel<\(?(?:int\))?\d+, \(?(?:int\))?(\d)>", name)
+    m = re.search(r"tapgemm_(?:persistent|pair)_kernel<\(?(?:int\))?\d+, \(?(?:int\))?(\d)>", name)
     if m:
         return "b2c_convt4s2_bf16" if m.group(1) == "1" else "b2c_conv4s2_bf16"
     if "tapgemm" in name:
