@@ -379,6 +379,462 @@ static int launch_first_wgrad(const FirstIn& in, const CUtensorMap& tmG, float* 
   return b2c_check_launch("first_wgrad");
 }
 
+// ================================================================================================ TMA-staged variants
+// Round-2 profile of the register-gather kernels above (profiles/r02_bw_step_ncu.txt, ncu_first): 1230 instructions per
+// output pixel, L1TEX the busiest unit (every input row is fetched by two output rows, plus predicated halo loads and
+// shuffles), 15 resident warps waiting on their own global loads -> 2.1 TB/s.  Here the caller's NCHW fp32 rows are
+// staged by TMA instead: a box of [3 channels][4 input rows][136 columns] (x = 2*ox0-4 .. 2*ox0+131: the innermost TMA
+// coordinate must be 16-byte aligned - x = 2*ox0-1 traps as an illegal instruction; rows / columns outside the image
+// are zero-filled by the TMA unit = the conv's padding) per 64 output pixels of one output row and source tensor, in a
+// ring of NS half-tile stages filled by a producer warp that runs ahead of the 128 packer threads.  A packer reads its
+// 4x4xCIN field with three shared-memory loads per (channel, ky) - l, (x0, x1), r - so the halo shuffles, the address
+// arithmetic and the load latency all leave the packers' path.
+// Needs Wo % 64 == 0 (patches >= 128) and 16-byte aligned inputs; smaller patches keep the kernels above.
+static constexpr int FS_BOXW = 136;
+static constexpr int FS_BOX_BYTES = 3 * 4 * FS_BOXW * 4;  // 6528 = 51 * 128
+static constexpr int FS_SLOT = FS_BOX_BYTES;
+static constexpr int FS_THREADS = 160;                    // warps 0-3: packers / epilogue, warp 4: TMA producer
+static constexpr int FS_GZ_BYTES = 64 * 128;              // wgrad: gz rows of one half tile
+
+struct FirstMaps {
+  CUtensorMap m[4];  // a0, a1, b0, b1 as (W, H, 3N) fp32
+};
+
+// One half tile (64 output pixels) -> 64 im2col rows of sA.  `st` = this half's stage; slot order: a-parts, then the
+// b-parts that are really interpolated (lerp_mask bit p).
+template <int CIN, bool INTERP>
+__device__ __forceinline__ void pack_from_stage(uint8_t* sA, int row, const uint8_t* st, int oxl, float al, int lerp_mask) {
+  uint8_t* base = sA + (row >> 3) * 1024 + (row & 7) * 128;
+  const float be = 1.f - al;
+  uint32_t p[4];
+  int bslot = CIN / 3;
+#pragma unroll
+  for (int part = 0; part < CIN / 3; ++part) {
+    const float* ra = reinterpret_cast<const float*>(st + part * FS_SLOT) + 2 * oxl;
+    const bool lerp = INTERP && ((lerp_mask >> part) & 1);
+    const float* rb = reinterpret_cast<const float*>(st + bslot * FS_SLOT) + 2 * oxl;
+    if (lerp) ++bslot;
+#pragma unroll
+    for (int r = 0; r < 12; ++r) {  // r = cc*4 + ky: the box's own row order
+      // staged column j <-> x = 2*ox0 - 4 + j: this pixel's taps x = 2*ox-1 .. 2*ox+2 are j = 2*oxl+3 .. 2*oxl+6
+      float l = ra[r * FS_BOXW + 3], rr = ra[r * FS_BOXW + 6];
+      float2 mid = *reinterpret_cast<const float2*>(ra + r * FS_BOXW + 4);
+      if (lerp) {
+        const float lb = rb[r * FS_BOXW + 3], rrb = rb[r * FS_BOXW + 6];
+        const float2 midb = *reinterpret_cast<const float2*>(rb + r * FS_BOXW + 4);
+        l = al * l + be * lb; rr = al * rr + be * rrb;
+        mid.x = al * mid.x + be * midb.x; mid.y = al * mid.y + be * midb.y;
+      }
+      const int g = part * 12 + r;
+      p[(g & 1) * 2] = pack_bf16(l, mid.x);
+      p[(g & 1) * 2 + 1] = pack_bf16(mid.y, rr);
+      if (g & 1) {
+        const int j = g >> 1;
+        *reinterpret_cast<uint4*>(base + (j >> 3) * 16384 + (((j & 7) ^ (row & 7)) << 4)) = make_uint4(p[0], p[1], p[2], p[3]);
+      }
+    }
+  }
+}
+
+// Producer: lane 0 of warp 4 walks this CTA's tiles, two half-tile stages per tile.
+template <int CIN, bool INTERP, bool WGRAD>
+__device__ __forceinline__ void first_producer(const FirstMaps& maps, const CUtensorMap* tmG, uint8_t* raw, uint8_t* gzs,
+                                               uint64_t* full, uint64_t* empty, int lerp_mask, int NS, int stage_bytes,
+                                               int ntiles, int Ho, int Wo) {
+  int nslots = CIN / 3;
+  if (INTERP) nslots += __popc(lerp_mask & ((1 << (CIN / 3)) - 1));
+  const uint32_t tx = (uint32_t)nslots * FS_BOX_BYTES + (WGRAD ? FS_GZ_BYTES : 0);
+  int s = 0, use = 0;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (int h = 0; h < 2; ++h) {
+      if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
+      const int p0 = tile * 128 + h * 64;
+      const int ox0 = p0 % Wo, q = p0 / Wo, oy = q % Ho, n = q / Ho;
+      mbar_expect_tx(&full[s], tx);
+      uint8_t* dst = raw + (size_t)s * stage_bytes;
+      int slot = 0;
+#pragma unroll
+      for (int part = 0; part < CIN / 3; ++part)
+        tma_load_3d(dst + (slot++) * FS_SLOT, &maps.m[part], &full[s], 2 * ox0 - 4, 2 * oy - 1, 3 * n);
+      if (INTERP) {
+#pragma unroll
+        for (int part = 0; part < CIN / 3; ++part)
+          if ((lerp_mask >> part) & 1) tma_load_3d(dst + (slot++) * FS_SLOT, &maps.m[2 + part], &full[s], 2 * ox0 - 4, 2 * oy - 1, 3 * n);
+      }
+      if (WGRAD) tma_load_2d(gzs + (size_t)s * FS_GZ_BYTES, tmG, &full[s], 0, p0);
+      if (++s == NS) { s = 0; ++use; }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ fprop (TMA-staged)
+// Per tile: pack(i) -> MMA(i) into TMEM[i&1] -> epilogue(i-1) from TMEM[(i-1)&1]: the MMAs and the producer's loads run
+// under the previous tile's epilogue; two CTAs per SM interleave the rest.
+template <int CIN, bool INTERP>
+__global__ void __launch_bounds__(FS_THREADS, 2) first_fprop_tma_kernel(const __grid_constant__ FirstMaps maps,
+                                                                      const float* __restrict__ alpha, int lerp_mask,
+                                                                      const float* __restrict__ w,
+                                                                      const float* __restrict__ inv_sigma,
+                                                                      const float* __restrict__ bias,
+                                                                      __nv_bfloat16* __restrict__ y, int N, int H, int W,
+                                                                      float slope, int NS, int stage_bytes) {
+  constexpr int KB = (16 * CIN + 63) / 64;  // k-blocks of 64
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;                   // [KB][128 rows][128 B]
+  uint8_t* sB = sA + KB * 16384;        // [KB][64 co][128 B]
+  uint8_t* raw = sB + KB * 8192;        // [NS][stage_bytes]
+  uint64_t* full = reinterpret_cast<uint64_t*>(raw + (size_t)NS * stage_bytes);
+  uint64_t* empty = full + 16;
+  uint64_t* mma_bar = empty + 16;       // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 2);
+  __shared__ float bias_s[64];
+
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int Ho = H / 2, Wo = W / 2;
+  const int ntiles = N * Ho * Wo / 128;
+
+  if (t == 0) {
+    for (int i = 0; i < CIN / 3; ++i) tma_prefetch_desc(&maps.m[i]);
+    for (int s = 0; s < NS; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 2);  // the two packer warps of a half
+    }
+    mbar_init(&mma_bar[0], 1);
+    mbar_init(&mma_bar[1], 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<128>(tmem_slot);
+  const float osc = inv_sigma ? __ldg(inv_sigma) : 1.f;
+  {
+    constexpr int NCH = 2 * CIN;
+    for (int i = t; i < 64 * NCH; i += FS_THREADS) {
+      const int co = i / NCH, j = i % NCH;
+      const float4 lo = __ldg(reinterpret_cast<const float4*>(w + (long long)co * (16 * CIN) + j * 8));
+      const float4 hi = __ldg(reinterpret_cast<const float4*>(w + (long long)co * (16 * CIN) + j * 8 + 4));
+      const uint4 u = make_uint4(pack_bf16(lo.x, lo.y), pack_bf16(lo.z, lo.w), pack_bf16(hi.x, hi.y), pack_bf16(hi.z, hi.w));
+      *reinterpret_cast<uint4*>(sB + (j >> 3) * 8192 + (co >> 3) * 1024 + (co & 7) * 128 + (((j & 7) ^ (co & 7)) << 4)) = u;
+    }
+    if (t < 64) bias_s[t] = bias ? __ldg(bias + t) : 0.f;
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 0);
+
+  if (warp == 4) {
+    if (lane == 0)
+      first_producer<CIN, INTERP, false>(maps, nullptr, raw, nullptr, full, empty, lerp_mask, NS, stage_bytes, ntiles, Ho, Wo);
+  } else {
+    const int half = t >> 6, oxl = t & 63;
+    int s = half, use = 0;  // NS >= 2
+    auto epilogue = [&](int tile, uint32_t buf) {
+      const long long pix = (long long)tile * 128 + t;
+#pragma unroll
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t v0[16], v1[16];
+        const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + buf * 64 + c0;
+        tmem_ld16(taddr, v0);
+        tmem_ld16(taddr + 16, v1);
+        tmem_ld_wait();
+        uint32_t o[16];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float a = fmaf(__uint_as_float(v0[2 * j]), osc, bias_s[c0 + 2 * j]), b = fmaf(__uint_as_float(v0[2 * j + 1]), osc, bias_s[c0 + 2 * j + 1]);
+          float c = fmaf(__uint_as_float(v1[2 * j]), osc, bias_s[c0 + 16 + 2 * j]), d = fmaf(__uint_as_float(v1[2 * j + 1]), osc, bias_s[c0 + 17 + 2 * j]);
+          a = a > 0.f ? a : a * slope; b = b > 0.f ? b : b * slope;
+          c = c > 0.f ? c : c * slope; d = d > 0.f ? d : d * slope;
+          o[j] = pack_bf16(a, b);
+          o[8 + j] = pack_bf16(c, d);
+        }
+        __nv_bfloat16* dst = y + pix * 64 + c0;
+        st_global_v8(dst, o);
+        st_global_v8(dst + 16, o + 8);
+      }
+    };
+    int it = 0, prev_tile = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      if (it > 0) mbar_wait(&mma_bar[(it - 1) & 1], ((it - 1) >> 1) & 1);  // MMA(it-1) done: sA free, TMEM[(it-1)&1] full
+      float al = 1.f;
+      if (INTERP) al = __ldg(alpha + (tile * 128 + half * 64) / (Ho * Wo));
+      mbar_wait(&full[s], use & 1);
+      pack_from_stage<CIN, INTERP>(sA, t, raw + (size_t)s * stage_bytes, oxl, al, lerp_mask);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+      s += 2;
+      if (s >= NS) { s -= NS; ++use; }
+      fence_proxy_async();
+      tc_fence_before();
+      named_bar_sync(1, 128);
+      if (t == 0) {
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+        const uint32_t d = tmem_base + (uint32_t)(it & 1) * 64;
+#pragma unroll
+        for (int k = 0; k < CIN; ++k)  // K = 16*CIN
+          umma_bf16(d, umma_desc_sw128(a0 + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
+                    umma_desc_sw128(b0 + (k >> 2) * 8192 + (k & 3) * 32, 16, 1024), idesc, (uint32_t)(k != 0));
+        umma_commit(&mma_bar[it & 1]);
+      }
+      __syncwarp();
+      if (it > 0) {
+        tc_fence_after();
+        epilogue(prev_tile, (uint32_t)((it - 1) & 1));
+      }
+      prev_tile = tile;
+    }
+    if (it > 0) {
+      mbar_wait(&mma_bar[(it - 1) & 1], ((it - 1) >> 1) & 1);
+      tc_fence_after();
+      epilogue(prev_tile, (uint32_t)((it - 1) & 1));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<128>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------ wgrad (TMA-staged)
+// The gz rows of a half tile travel in the same stage as its input boxes; a stage is released by the commit of the MMAs
+// that read its gz rows.  TMEM accumulates over all tiles of the CTA; one atomic flush per CTA, as above.
+template <int CIN, bool INTERP>
+__global__ void __launch_bounds__(FS_THREADS, 2) first_wgrad_tma_kernel(const __grid_constant__ FirstMaps maps,
+                                                                      const __grid_constant__ CUtensorMap tmG,
+                                                                      const float* __restrict__ alpha, int lerp_mask,
+                                                                      float* __restrict__ dw, float* __restrict__ db,
+                                                                      const float* __restrict__ scale,
+                                                                      const float* __restrict__ wdot, float* __restrict__ part,
+                                                                      int N, int H, int W, int NS, int stage_bytes) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;                              // [2][128 rows][128 B]
+  uint8_t* gzs = sA + FT_A_BYTES;                  // [NS][64 pix][128 B]
+  uint8_t* raw = gzs + (size_t)NS * FS_GZ_BYTES;   // [NS][stage_bytes]
+  uint64_t* full = reinterpret_cast<uint64_t*>(raw + (size_t)NS * stage_bytes);
+  uint64_t* empty = full + 16;
+  uint64_t* mma_bar = empty + 16;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 2);
+
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int Ho = H / 2, Wo = W / 2;
+  const int ntiles = N * Ho * Wo / 128;
+
+  if (t == 0) {
+    for (int i = 0; i < CIN / 3; ++i) tma_prefetch_desc(&maps.m[i]);
+    tma_prefetch_desc(&tmG);
+    for (int s = 0; s < NS; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);  // the commit of the MMAs that read the stage's gz rows
+    }
+    mbar_init(mma_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<64>(tmem_slot);
+  // k = 127 (last element of chunk 15) is the all-ones im2col column whose dW row is the bias gradient
+  if (t < 128)
+    *reinterpret_cast<uint4*>(sA + 16384 + (t >> 3) * 1024 + (t & 7) * 128 + ((7 ^ (t & 7)) << 4)) =
+        make_uint4(0u, 0u, 0u, pack_bf16(0.f, 1.f));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);
+
+  int it = 0;
+  if (warp == 4) {
+    if (lane == 0)
+      first_producer<CIN, INTERP, true>(maps, &tmG, raw, gzs, full, empty, lerp_mask, NS, stage_bytes, ntiles, Ho, Wo);
+  } else {
+    const int half = t >> 6, oxl = t & 63;
+    int s = half, use = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      if (it > 0) mbar_wait(mma_bar, (it - 1) & 1);  // the previous tile's MMAs are done reading sA
+      float al = 1.f;
+      if (INTERP) al = __ldg(alpha + (tile * 128 + half * 64) / (Ho * Wo));
+      mbar_wait(&full[s], use & 1);
+      pack_from_stage<CIN, INTERP>(sA, t, raw + (size_t)s * stage_bytes, oxl, al, lerp_mask);
+      fence_proxy_async();
+      tc_fence_before();
+      named_bar_sync(1, 128);
+      if (t == 0) {
+        // this thread packed half 0; half 1's stage is the next one in the ring
+        int s1 = s + 1, use1 = use;
+        if (s1 == NS) { s1 = 0; ++use1; }
+        mbar_wait(&full[s1], use1 & 1);
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(sA);
+        const uint32_t g0 = smem_u32(gzs + (size_t)s * FS_GZ_BYTES), g1 = smem_u32(gzs + (size_t)s1 * FS_GZ_BYTES);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)  // 16 pixels of the reduction per MMA
+          umma_bf16(tmem_base, umma_desc_sw128(a0 + k * 2048, 16384, 1024),
+                    umma_desc_sw128((k < 4 ? g0 : g1) + (k & 3) * 2048, 16384, 1024), idesc, (uint32_t)((it | k) != 0));
+        umma_commit(&empty[s]);
+        umma_commit(&empty[s1]);
+        umma_commit(mma_bar);
+      }
+      __syncwarp();
+      s += 2;
+      if (s >= NS) { s -= NS; ++use; }
+    }
+  }
+  float dot = 0.f;  // <this CTA's partial dW (unscaled), wdot>: deferred rank-1 term of the spectral-norm backward
+  if (warp < 4 && it > 0) {
+    const float sc = scale ? __ldg(scale) : 1.f;
+    mbar_wait(mma_bar, (it - 1) & 1);
+    tc_fence_after();
+    const int rot = (blockIdx.x * 16) & 63;
+#pragma unroll 1
+    for (int cc = 0; cc < 64; cc += 16) {
+      const int c0 = (cc + rot) & 63;
+      uint32_t v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + c0, v);
+      tmem_ld_wait();
+      if (t < 16 * CIN) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const long long idx = (long long)(c0 + j) * (16 * CIN) + t;
+          if (wdot) dot += __uint_as_float(v[j]) * __ldg(wdot + idx);
+          atomicAdd(dw + idx, __uint_as_float(v[j]) * sc);
+        }
+      } else if (t == 127 && db) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) atomicAdd(db + c0 + j, __uint_as_float(v[j]));
+      }
+    }
+  }
+  if (part) {
+    __shared__ float dsh[4];
+    dot = warp_sum(dot);
+    if (lane == 0 && warp < 4) dsh[warp] = dot;
+    __syncthreads();
+    if (t == 0) part[blockIdx.x] = (dsh[0] + dsh[1]) + (dsh[2] + dsh[3]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<64>(tmem_base);
+}
+
+// ---- host side of the TMA-staged variants
+static bool first_tma_ok(const float* a0, const float* a1, const float* b0, const float* b1, int N, int H, int W) {
+  static int enabled = -1;
+  if (enabled < 0) {
+    const char* e = getenv("B2C_FIRST_TMA");
+    enabled = (e && e[0] == '0') ? 0 : 1;
+  }
+  if (!enabled) return false;
+  const int Ho = H / 2, Wo = W / 2;
+  if (Wo % 64 != 0 || ((long long)Ho * Wo) % 128 != 0) return false;
+  if ((long long)N * 3 >= (1ll << 31)) return false;
+  const uintptr_t al = (uintptr_t)a0 | (uintptr_t)a1 | (uintptr_t)b0 | (uintptr_t)b1;
+  return (al & 15) == 0;
+}
+
+static int first_maps(FirstMaps* maps, const FirstIn& in, bool two, bool interp, int N, int H, int W, int* lerp_mask) {
+  uint64_t dims[3] = {(uint64_t)W, (uint64_t)H, (uint64_t)N * 3};
+  uint64_t str[2] = {(uint64_t)W * 4, (uint64_t)W * H * 4};
+  uint32_t box[3] = {(uint32_t)FS_BOXW, 4, 3};
+  *lerp_mask = 0;
+  const int nparts = two ? 2 : 1;
+  for (int p = 0; p < nparts; ++p) {
+    int rc = b2c_make_tmap_f32(&maps->m[p], in.a[p], 3, dims, str, box);
+    if (rc) return rc;
+    // x = alpha*a + (1-alpha)*a = a: a part whose two sources are the same tensor (the critic's `pred` channels under the
+    // gradient penalty, cgan/losses.py:203-204 with real = (pred, gt), fake = (pred, refined)) is staged once
+    if (interp && in.b[p] != in.a[p]) {
+      rc = b2c_make_tmap_f32(&maps->m[2 + p], in.b[p], 3, dims, str, box);
+      if (rc) return rc;
+      *lerp_mask |= 1 << p;
+    } else {
+      maps->m[2 + p] = maps->m[p];
+    }
+  }
+  for (int p = nparts; p < 2; ++p) maps->m[p] = maps->m[0], maps->m[2 + p] = maps->m[0];
+  return B2C_OK;
+}
+
+static int first_ns(int fixed_bytes, int stage_bytes_total) {
+  // two CTAs per SM: 227 KB of shared memory, 1 KB reserved per CTA
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("B2C_FIRST_NS");
+    forced = e ? atoi(e) : 0;
+  }
+  int ns = (113 * 1024 - fixed_bytes) / stage_bytes_total;
+  if (forced >= 2) ns = forced;
+  if (ns > 8) ns = 8;
+  if (ns < 2) ns = 2;
+  return ns;
+}
+
+template <int CIN, bool INTERP>
+static int launch_first_fprop_tma(const FirstIn& in, const float* w, const float* inv_sigma, const float* bias, void* y, int N,
+                                  int H, int W, float slope, cudaStream_t st) {
+  FirstMaps maps;
+  int lerp_mask = 0;
+  int rc = first_maps(&maps, in, CIN == 6, INTERP, N, H, W, &lerp_mask);
+  if (rc) return rc;
+  constexpr int KB = (16 * CIN + 63) / 64;
+  const int nslots = CIN / 3 + __builtin_popcount(lerp_mask);
+  const int stage_bytes = nslots * FS_SLOT;
+  const int fixed = KB * 16384 + KB * 8192 + 2048;
+  const int NS = first_ns(fixed, stage_bytes);
+  const int smem = fixed + NS * stage_bytes;
+  static int attr_smem = 0;
+  if (smem > attr_smem) {
+    cudaError_t e = cudaFuncSetAttribute(first_fprop_tma_kernel<CIN, INTERP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      b2c_set_error("cudaFuncSetAttribute(first_fprop_tma, %d): %s", smem, cudaGetErrorString(e));
+      return B2C_ERR_CUDA;
+    }
+    attr_smem = smem;
+  }
+  const long long ntiles = (long long)N * (H / 2) * (W / 2) / 128;
+  const unsigned blocks = (unsigned)(ntiles < 148 * 2 ? ntiles : 148 * 2);
+  first_fprop_tma_kernel<CIN, INTERP><<<blocks, FS_THREADS, smem, st>>>(maps, in.alpha, lerp_mask, w, inv_sigma, bias,
+                                                                     (__nv_bfloat16*)y, N, H, W, slope, NS, stage_bytes);
+  return b2c_check_launch("first_fprop_tma");
+}
+
+template <int CIN, bool INTERP>
+static int launch_first_wgrad_tma(const FirstIn& in, const void* gz, float* dw, float* db, const float* scale,
+                                  const float* wdot, float* part, int* nparts_host, int N, int H, int W, cudaStream_t st) {
+  FirstMaps maps;
+  int lerp_mask = 0;
+  int rc = first_maps(&maps, in, CIN == 6, INTERP, N, H, W, &lerp_mask);
+  if (rc) return rc;
+  const long long npix = (long long)N * (H / 2) * (W / 2);
+  CUtensorMap tmG;
+  {
+    uint64_t dims[2] = {64, (uint64_t)npix};
+    uint64_t str[1] = {128};
+    uint32_t box[2] = {64, 64};
+    rc = b2c_make_tmap_bf16(&tmG, gz, 2, dims, str, box);
+    if (rc) return rc;
+  }
+  const int nslots = CIN / 3 + __builtin_popcount(lerp_mask);
+  const int stage_bytes = nslots * FS_SLOT;
+  const int fixed = FT_A_BYTES + 2048;
+  const int NS = first_ns(fixed, stage_bytes + FS_GZ_BYTES);
+  const int smem = fixed + NS * (stage_bytes + FS_GZ_BYTES);
+  static int attr_smem = 0;
+  if (smem > attr_smem) {
+    cudaError_t e = cudaFuncSetAttribute(first_wgrad_tma_kernel<CIN, INTERP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      b2c_set_error("cudaFuncSetAttribute(first_wgrad_tma, %d): %s", smem, cudaGetErrorString(e));
+      return B2C_ERR_CUDA;
+    }
+    attr_smem = smem;
+  }
+  const long long ntiles = npix / 128;
+  const unsigned blocks = (unsigned)(ntiles < 148 * 2 ? ntiles : 148 * 2);
+  if (nparts_host) *nparts_host = (int)blocks;
+  first_wgrad_tma_kernel<CIN, INTERP><<<blocks, FS_THREADS, smem, st>>>(maps, tmG, in.alpha, lerp_mask, dw, db, scale, wdot,
+                                                                     part, N, H, W, NS, stage_bytes);
+  return b2c_check_launch("first_wgrad_tma");
+}
+
 // a0/a1: (N,3,H,W) fp32 NCHW halves (a1 null => Cin=3).  b0/b1/alpha: optional interpolation (all or none).
 extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                                const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
@@ -390,6 +846,14 @@ extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0
   long long blocks = (npix + 127) / 128;
   if (blocks > 148 * 4) blocks = 148 * 4;
   cudaStream_t st = (cudaStream_t)stream;
+  if (first_tma_ok(a0, a1, b0, b1, N, H, W)) {
+    if (a1) {
+      if (alpha) return launch_first_fprop_tma<6, true>(in, w, inv_sigma, bias, y, N, H, W, slope, st);
+      return launch_first_fprop_tma<6, false>(in, w, inv_sigma, bias, y, N, H, W, slope, st);
+    }
+    if (alpha) return launch_first_fprop_tma<3, true>(in, w, inv_sigma, bias, y, N, H, W, slope, st);
+    return launch_first_fprop_tma<3, false>(in, w, inv_sigma, bias, y, N, H, W, slope, st);
+  }
   if (a1) {
     if (alpha) return launch_first_fprop<6, true>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
     return launch_first_fprop<6, false>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
@@ -408,6 +872,15 @@ extern "C" int b2c_first_wgrad(const float* a0, const float* a1, const float* b0
   if (rc) return rc;
   B2C_REQUIRE((wdot == nullptr) == (part == nullptr), "first_wgrad: wdot and part go together");
   FirstIn in = make_in(a0, a1, b0, b1, alpha);
+  if (first_tma_ok(a0, a1, b0, b1, N, H, W)) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (a1) {
+      if (alpha) return launch_first_wgrad_tma<6, true>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st);
+      return launch_first_wgrad_tma<6, false>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st);
+    }
+    if (alpha) return launch_first_wgrad_tma<3, true>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st);
+    return launch_first_wgrad_tma<3, false>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st);
+  }
   const long long npix = (long long)N * (H / 2) * (W / 2);
   CUtensorMap tmG;
   {

@@ -74,3 +74,34 @@ int b2c_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint6
   }
   return B2C_OK;
 }
+
+int b2c_make_tmap_f32(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    b2c_set_error("cuTensorMapEncodeTiled driver entry point unavailable");
+    return B2C_ERR_DRIVER;
+  }
+  cuuint64_t gd[5], gs[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gd[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+    if (i > 0) gs[i - 1] = strides_bytes[i - 1];
+  }
+  if (((uintptr_t)base & 15) != 0) {
+    b2c_set_error("tensor map base not 16-byte aligned");
+    return B2C_ERR_ARG;
+  }
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    b2c_set_error("cuTensorMapEncodeTiled(f32) failed (%d): rank %d dims %llu %llu %llu box %u %u %u", (int)r, rank,
+                  (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
+                  (unsigned long long)(rank > 2 ? dims[2] : 0), box[0], rank > 1 ? box[1] : 0, rank > 2 ? box[2] : 0);
+    return B2C_ERR_DRIVER;
+  }
+  return B2C_OK;
+}

@@ -17,7 +17,10 @@ g0 = torch.empty_like(a0); g1 = torch.empty_like(a1)
 ws = torch.empty(32 * 576, dtype=torch.bfloat16, device=dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 nb_in, nb_map = 2 * a0.numel() * 4, y.numel() * 2
+b1 = torch.randn(B, 3, S, S, device=dev); alpha = torch.rand(B, device=dev)
 cases = {
+    "fprop_interp": (lambda: L.call("b2c_first_fprop", a0, a1, a0, b1, alpha, w, isg, bias, y, B, S, S, 0.2), nb_in + nb_map + nb_in // 2),
+    "wgrad_interp": (lambda: L.call("b2c_first_wgrad", a0, a1, a0, b1, alpha, gz, dw, db, None, None, None, None, B, S, S), nb_in + nb_map + nb_in // 2),
     "first_fprop": (lambda: L.call("b2c_first_fprop", a0, a1, None, None, None, w, isg, bias, y, B, S, S, 0.2), nb_in + nb_map),
     "first_wgrad": (lambda: L.call("b2c_first_wgrad", a0, a1, None, None, None, gz, dw, db, None, None, None, None, B, S, S), nb_in + nb_map),
     "first_dgrad": (lambda: L.call("b2c_first_dgrad", gz, w, isg, g0, g1, ws, B, S, S), nb_in + nb_map),

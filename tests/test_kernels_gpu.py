@@ -176,12 +176,17 @@ def test_wgrad4s2(L, N, Hs, Ws, Cs, Cl):
 
 
 @pytest.mark.parametrize("cin,N,S,interp", [(3, 3, 32, True), (6, 3, 32, True), (6, 2, 128, False), (3, 5, 64, False),
-                                             (6, 1, 256, True)])
+                                             (6, 1, 256, True), (3, 3, 128, True), (6, 5, 256, "same0"), (3, 5, 256, False),
+                                             (6, 3, 512, False)])
 def test_first_layer(L, cin, N, S, interp):
-    """First-layer kernels (tcgen05, bf16 operands, fp32 accumulate) against torch on bf16-rounded x and w."""
+    """First-layer kernels (tcgen05, bf16 operands, fp32 accumulate) against torch on bf16-rounded x and w.  S >= 128 takes
+    the TMA-staged kernels (5 x 256^2 = 640 tiles: several per CTA); "same0": the first three channels of both
+    interpolation sources are the same tensor (the critic's `pred` under the gradient penalty) and are staged once."""
     g = torch.Generator().manual_seed(5)
     x = torch.randn(N, cin, S, S, generator=g)
     xb = torch.randn(N, cin, S, S, generator=g)
+    if interp == "same0":
+        xb[:, :3] = x[:, :3]
     alpha = torch.rand(N, generator=g)
     w = torch.randn(64, cin, 4, 4, generator=g) * 0.1
     b = torch.randn(64, generator=g) * 0.1
@@ -189,6 +194,8 @@ def test_first_layer(L, cin, N, S, interp):
     parts = lambda t: [t[:, :3].contiguous().cuda(), t[:, 3:].contiguous().cuda() if cin == 6 else None]
     a0, a1 = parts(x)
     b0, b1 = parts(xb) if interp else (None, None)
+    if interp == "same0":
+        b0 = a0
     al_d = alpha.cuda() if interp else None
     y = torch.empty(N, S // 2, S // 2, 64, dtype=torch.bfloat16, device="cuda")
     L.call("b2c_first_fprop", a0, a1, b0, b1, al_d, w.cuda(), sig.cuda()[1:], b.cuda(), y, N, S, S, 0.2)
