@@ -385,49 +385,70 @@ static int launch_first_wgrad(const FirstIn& in, const CUtensorMap& tmG, float* 
 // shuffles), 15 resident warps waiting on their own global loads -> 2.1 TB/s.  Here the caller's NCHW fp32 rows are
 // staged by TMA instead: a box of [3 channels][4 input rows][136 columns] (x = 2*ox0-4 .. 2*ox0+131: the innermost TMA
 // coordinate must be 16-byte aligned - x = 2*ox0-1 traps as an illegal instruction; rows / columns outside the image
-// are zero-filled by the TMA unit = the conv's padding) per 64 output pixels of one output row and source tensor, in a
-// ring of NS half-tile stages filled by a producer warp that runs ahead of the 128 packer threads.  A packer reads its
-// 4x4xCIN field with three shared-memory loads per (channel, ky) - l, (x0, x1), r - so the halo shuffles, the address
-// arithmetic and the load latency all leave the packers' path.
-// Needs Wo % 64 == 0 (patches >= 128) and 16-byte aligned inputs; smaller patches keep the kernels above.
+// are zero-filled by the TMA unit = the conv's padding) per 64 output pixels of one output row and source tensor.
+//
+// ONE CTA per SM: a producer warp fills a ring of NS half-tile stages that takes all the shared memory the fixed
+// buffers leave (>= 100 KB in flight per SM: the first version, two CTAs with a private 2-3 stage ring each, spent a
+// third of its time waiting for data), and NG = 2 or 3 groups of 128 packer threads take tiles from it in turn, each with its
+// own im2col tile and TMEM accumulator, so one group's MMA / epilogue latency is covered by the other groups' packing
+// (with two groups the 8 warps' dependent instruction chains were the limit: IPC 1.2).  The fprop output staging tile
+// aliases the group's im2col tile, which is dead once the MMAs have completed.  Shared-memory wavefronts are the next limit (the first version ran L1TEX at 80 %), so
+// a lane pair (2m, 2m+1) shares one aligned LDS.128 - staged columns 4m+4..4m+7 hold three of the four taps of both
+// pixels - plus one LDS.32 for the fourth (4 wavefronts per (channel, ky) row instead of 6), the bias is read with
+// LDS.128, and the fprop output leaves through a swizzled staging tile and ONE TMA store per tile instead of 16 strided
+// STG.256 per warp.  Needs Wo % 64 == 0 (patches >= 128) and 16-byte aligned inputs; smaller patches keep the kernels above.
 static constexpr int FS_BOXW = 136;
 static constexpr int FS_BOX_BYTES = 3 * 4 * FS_BOXW * 4;  // 6528 = 51 * 128
 static constexpr int FS_SLOT = FS_BOX_BYTES;
-static constexpr int FS_THREADS = 160;                    // warps 0-3: packers / epilogue, warp 4: TMA producer
+// threads = NG * 128 + 32: warps 4g..4g+3 = packer group g (NG = 2 or 3), last warp = TMA producer
 static constexpr int FS_GZ_BYTES = 64 * 128;              // wgrad: gz rows of one half tile
 
 struct FirstMaps {
   CUtensorMap m[4];  // a0, a1, b0, b1 as (W, H, 3N) fp32
 };
 
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // One half tile (64 output pixels) -> 64 im2col rows of sA.  `st` = this half's stage; slot order: a-parts, then the
-// b-parts that are really interpolated (lerp_mask bit p).
+// b-parts that are really interpolated (lerp_mask bit p).  Staged column j <-> x = 2*ox0 - 4 + j, so pixel oxl needs
+// j = 2*oxl+3 .. 2*oxl+6: for the lane pair (2m, 2m+1) the aligned chunk B = j 4m+4..4m+7 holds (x0, x1, r) of the even
+// pixel and (l, x0, x1) of the odd one; the even lane's l (j = 4m+3) / the odd lane's r (j = 4m+8) come from one LDS.32.
 template <int CIN, bool INTERP>
 __device__ __forceinline__ void pack_from_stage(uint8_t* sA, int row, const uint8_t* st, int oxl, float al, int lerp_mask) {
   uint8_t* base = sA + (row >> 3) * 1024 + (row & 7) * 128;
   const float be = 1.f - al;
+  const bool odd = oxl & 1;
+  const int cb = (oxl >> 1) * 4 + 4, ce = odd ? cb + 4 : cb - 1;
   uint32_t p[4];
   int bslot = CIN / 3;
 #pragma unroll
   for (int part = 0; part < CIN / 3; ++part) {
-    const float* ra = reinterpret_cast<const float*>(st + part * FS_SLOT) + 2 * oxl;
+    const float* ra = reinterpret_cast<const float*>(st + part * FS_SLOT);
     const bool lerp = INTERP && ((lerp_mask >> part) & 1);
-    const float* rb = reinterpret_cast<const float*>(st + bslot * FS_SLOT) + 2 * oxl;
+    const float* rb = reinterpret_cast<const float*>(st + bslot * FS_SLOT);
     if (lerp) ++bslot;
 #pragma unroll
     for (int r = 0; r < 12; ++r) {  // r = cc*4 + ky: the box's own row order
-      // staged column j <-> x = 2*ox0 - 4 + j: this pixel's taps x = 2*ox-1 .. 2*ox+2 are j = 2*oxl+3 .. 2*oxl+6
-      float l = ra[r * FS_BOXW + 3], rr = ra[r * FS_BOXW + 6];
-      float2 mid = *reinterpret_cast<const float2*>(ra + r * FS_BOXW + 4);
+      float4 B = *reinterpret_cast<const float4*>(ra + r * FS_BOXW + cb);
+      float e = ra[r * FS_BOXW + ce];
       if (lerp) {
-        const float lb = rb[r * FS_BOXW + 3], rrb = rb[r * FS_BOXW + 6];
-        const float2 midb = *reinterpret_cast<const float2*>(rb + r * FS_BOXW + 4);
-        l = al * l + be * lb; rr = al * rr + be * rrb;
-        mid.x = al * mid.x + be * midb.x; mid.y = al * mid.y + be * midb.y;
+        const float4 Bb = *reinterpret_cast<const float4*>(rb + r * FS_BOXW + cb);
+        const float eb = rb[r * FS_BOXW + ce];
+        B.x = al * B.x + be * Bb.x; B.y = al * B.y + be * Bb.y;
+        B.z = al * B.z + be * Bb.z; B.w = al * B.w + be * Bb.w;
+        e = al * e + be * eb;
       }
+      const float l = odd ? B.y : e, x0 = odd ? B.z : B.x, x1 = odd ? B.w : B.y, rr = odd ? e : B.z;
       const int g = part * 12 + r;
-      p[(g & 1) * 2] = pack_bf16(l, mid.x);
-      p[(g & 1) * 2 + 1] = pack_bf16(mid.y, rr);
+      p[(g & 1) * 2] = pack_bf16(l, x0);
+      p[(g & 1) * 2 + 1] = pack_bf16(x1, rr);
       if (g & 1) {
         const int j = g >> 1;
         *reinterpret_cast<uint4*>(base + (j >> 3) * 16384 + (((j & 7) ^ (row & 7)) << 4)) = make_uint4(p[0], p[1], p[2], p[3]);
@@ -436,7 +457,7 @@ __device__ __forceinline__ void pack_from_stage(uint8_t* sA, int row, const uint
   }
 }
 
-// Producer: lane 0 of warp 4 walks this CTA's tiles, two half-tile stages per tile.
+// Producer: lane 0 of warp 8 walks this CTA's tiles, two half-tile stages per tile.
 template <int CIN, bool INTERP, bool WGRAD>
 __device__ __forceinline__ void first_producer(const FirstMaps& maps, const CUtensorMap* tmG, uint8_t* raw, uint8_t* gzs,
                                                uint64_t* full, uint64_t* empty, int lerp_mask, int NS, int stage_bytes,
@@ -467,28 +488,53 @@ __device__ __forceinline__ void first_producer(const FirstMaps& maps, const CUte
   }
 }
 
+// Ring position of packer group `grp`, half `half`, at the group's j-th tile: the CTA's i-th tile (i = NG*j + grp) uses
+// half-stage counts 2i and 2i+1.  The groups share one ring and skip each other's stages, so a group can reach a stage
+// whose PREVIOUS fill has not even landed yet, and a bare parity wait for "its" fill would then pass on the wrong phase.
+// wait_full() therefore first waits until the previous fill was consumed (=> it landed), which is well defined because
+// the host guarantees NS >= 2*NG: the previous occupant of the stage is then a half tile the in-order producer issued
+// before the tile this group has just finished.
+struct RingPos {
+  int s, use;
+  __device__ __forceinline__ RingPos(int grp, int half, int NS) {
+    const int cnt = 2 * grp + half;
+    s = cnt % NS;
+    use = cnt / NS;
+  }
+  __device__ __forceinline__ void next_tile(int NS, int NG) {
+    s += 2 * NG;
+    while (s >= NS) { s -= NS; ++use; }
+  }
+};
+__device__ __forceinline__ void wait_full(uint64_t* full, uint64_t* empty, int s, int use) {
+  if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
+  mbar_wait(&full[s], use & 1);
+}
+
 // ------------------------------------------------------------------------------------------------ fprop (TMA-staged)
-// Per tile: pack(i) -> MMA(i) into TMEM[i&1] -> epilogue(i-1) from TMEM[(i-1)&1]: the MMAs and the producer's loads run
-// under the previous tile's epilogue; two CTAs per SM interleave the rest.
-template <int CIN, bool INTERP>
-__global__ void __launch_bounds__(FS_THREADS, 2) first_fprop_tma_kernel(const __grid_constant__ FirstMaps maps,
+template <int CIN, bool INTERP, int NG>
+__global__ void __launch_bounds__(NG * 128 + 32, 1) first_fprop_tma_kernel(const __grid_constant__ FirstMaps maps,
+                                                                      const __grid_constant__ CUtensorMap tmY,
                                                                       const float* __restrict__ alpha, int lerp_mask,
                                                                       const float* __restrict__ w,
                                                                       const float* __restrict__ inv_sigma,
-                                                                      const float* __restrict__ bias,
-                                                                      __nv_bfloat16* __restrict__ y, int N, int H, int W,
+                                                                      const float* __restrict__ bias, int N, int H, int W,
                                                                       float slope, int NS, int stage_bytes) {
   constexpr int KB = (16 * CIN + 63) / 64;  // k-blocks of 64
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sA = smem;                   // [KB][128 rows][128 B]
-  uint8_t* sB = sA + KB * 16384;        // [KB][64 co][128 B]
-  uint8_t* raw = sB + KB * 8192;        // [NS][stage_bytes]
+  uint8_t* sA = smem;                            // [NG groups][KB][128 rows][128 B]; the first 16 KB double as output staging
+  uint8_t* sB = sA + NG * KB * 16384;         // [KB][64 co][128 B]
+  // output staging: with three groups it aliases the group's im2col tile (dead once the MMAs have completed; costs one more
+  // barrier per tile), with two there is room for a tile of its own
+  constexpr bool ALIAS_O = NG == 3;
+  uint8_t* sO = sB + KB * 8192;                  // [NG groups][128 rows][128 B] unless aliased
+  uint8_t* raw = sO + (ALIAS_O ? 0 : NG * 16384);  // [NS][stage_bytes]
   uint64_t* full = reinterpret_cast<uint64_t*>(raw + (size_t)NS * stage_bytes);
-  uint64_t* empty = full + 16;
-  uint64_t* mma_bar = empty + 16;       // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 2);
-  __shared__ float bias_s[64];
+  uint64_t* empty = full + 32;
+  uint64_t* mma_bar = empty + 32;                // [NG groups]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 4);
+  __shared__ __align__(16) float bias_s[64];
 
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
   const int Ho = H / 2, Wo = W / 2;
@@ -496,19 +542,19 @@ __global__ void __launch_bounds__(FS_THREADS, 2) first_fprop_tma_kernel(const __
 
   if (t == 0) {
     for (int i = 0; i < CIN / 3; ++i) tma_prefetch_desc(&maps.m[i]);
+    tma_prefetch_desc(&tmY);
     for (int s = 0; s < NS; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 2);  // the two packer warps of a half
     }
-    mbar_init(&mma_bar[0], 1);
-    mbar_init(&mma_bar[1], 1);
+    for (int g = 0; g < NG; ++g) mbar_init(&mma_bar[g], 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<128>(tmem_slot);
+  if (warp == 1) tmem_alloc<256>(tmem_slot);
   const float osc = inv_sigma ? __ldg(inv_sigma) : 1.f;
   {
     constexpr int NCH = 2 * CIN;
-    for (int i = t; i < 64 * NCH; i += FS_THREADS) {
+    for (int i = t; i < 64 * NCH; i += NG * 128 + 32) {
       const int co = i / NCH, j = i % NCH;
       const float4 lo = __ldg(reinterpret_cast<const float4*>(w + (long long)co * (16 * CIN) + j * 8));
       const float4 hi = __ldg(reinterpret_cast<const float4*>(w + (long long)co * (16 * CIN) + j * 8 + 4));
@@ -524,83 +570,93 @@ __global__ void __launch_bounds__(FS_THREADS, 2) first_fprop_tma_kernel(const __
   const uint32_t tmem_base = *tmem_slot;
   constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 0);
 
-  if (warp == 4) {
+  if (warp == 4 * NG) {
     if (lane == 0)
       first_producer<CIN, INTERP, false>(maps, nullptr, raw, nullptr, full, empty, lerp_mask, NS, stage_bytes, ntiles, Ho, Wo);
   } else {
-    const int half = t >> 6, oxl = t & 63;
-    int s = half, use = 0;  // NS >= 2
-    auto epilogue = [&](int tile, uint32_t buf) {
-      const long long pix = (long long)tile * 128 + t;
+    const int grp = warp >> 2, tg = t & 127, half = tg >> 6, oxl = tg & 63;
+    uint8_t* sAg = sA + grp * (KB * 16384);
+    uint8_t* sOg = ALIAS_O ? sAg : sO + grp * 16384;
+    const uint32_t tmem_g = tmem_base + (uint32_t)grp * 64;
+    RingPos rp(grp, half, NS);
+    int j = 0;
+    for (int tile = blockIdx.x + grp * gridDim.x; tile < ntiles; tile += NG * gridDim.x, ++j) {
+      if (ALIAS_O) {
+        if (tg == 0) tma_store_wait_read();  // the previous tile's store has read the staging tile = this im2col tile
+        named_bar_sync(1 + grp, 128);
+      }
+      float al = 1.f;
+      if (INTERP) al = __ldg(alpha + (tile * 128 + half * 64) / (Ho * Wo));
+      wait_full(full, empty, rp.s, rp.use);
+      pack_from_stage<CIN, INTERP>(sAg, tg, raw + (size_t)rp.s * stage_bytes, oxl, al, lerp_mask);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[rp.s]);
+      rp.next_tile(NS, NG);
+      if (!ALIAS_O && tg == 0) tma_store_wait_read();  // the previous tile's store has read the staging tile
+      fence_proxy_async();
+      tc_fence_before();
+      named_bar_sync(1 + grp, 128);
+      if (tg == 0) {
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(sAg), b0 = smem_u32(sB);
+#pragma unroll
+        for (int k = 0; k < CIN; ++k)  // K = 16*CIN
+          umma_bf16(tmem_g, umma_desc_sw128(a0 + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
+                    umma_desc_sw128(b0 + (k >> 2) * 8192 + (k & 3) * 32, 16, 1024), idesc, (uint32_t)(k != 0));
+        umma_commit(&mma_bar[grp]);
+      }
+      __syncwarp();
+      mbar_wait(&mma_bar[grp], j & 1);
+      tc_fence_after();
+      uint8_t* orow = sOg + (tg >> 3) * 1024 + (tg & 7) * 128;
 #pragma unroll
       for (int c0 = 0; c0 < 64; c0 += 32) {
         uint32_t v0[16], v1[16];
-        const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + buf * 64 + c0;
+        const uint32_t taddr = tmem_g + ((uint32_t)((warp & 3) * 32) << 16) + c0;
         tmem_ld16(taddr, v0);
         tmem_ld16(taddr + 16, v1);
         tmem_ld_wait();
         uint32_t o[16];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float a = fmaf(__uint_as_float(v0[2 * j]), osc, bias_s[c0 + 2 * j]), b = fmaf(__uint_as_float(v0[2 * j + 1]), osc, bias_s[c0 + 2 * j + 1]);
-          float c = fmaf(__uint_as_float(v1[2 * j]), osc, bias_s[c0 + 16 + 2 * j]), d = fmaf(__uint_as_float(v1[2 * j + 1]), osc, bias_s[c0 + 17 + 2 * j]);
-          a = a > 0.f ? a : a * slope; b = b > 0.f ? b : b * slope;
-          c = c > 0.f ? c : c * slope; d = d > 0.f ? d : d * slope;
-          o[j] = pack_bf16(a, b);
-          o[8 + j] = pack_bf16(c, d);
+        for (int q = 0; q < 4; ++q) {
+          const float4 b0v = *reinterpret_cast<const float4*>(bias_s + c0 + 4 * q);
+          const float4 b1v = *reinterpret_cast<const float4*>(bias_s + c0 + 16 + 4 * q);
+          float a = fmaf(__uint_as_float(v0[4 * q]), osc, b0v.x), b = fmaf(__uint_as_float(v0[4 * q + 1]), osc, b0v.y);
+          float c = fmaf(__uint_as_float(v0[4 * q + 2]), osc, b0v.z), d = fmaf(__uint_as_float(v0[4 * q + 3]), osc, b0v.w);
+          a = fmaxf(a, a * slope); b = fmaxf(b, b * slope);  // LeakyReLU for 0 <= slope <= 1 (host-checked)
+          c = fmaxf(c, c * slope); d = fmaxf(d, d * slope);
+          o[2 * q] = pack_bf16(a, b);
+          o[2 * q + 1] = pack_bf16(c, d);
+          a = fmaf(__uint_as_float(v1[4 * q]), osc, b1v.x); b = fmaf(__uint_as_float(v1[4 * q + 1]), osc, b1v.y);
+          c = fmaf(__uint_as_float(v1[4 * q + 2]), osc, b1v.z); d = fmaf(__uint_as_float(v1[4 * q + 3]), osc, b1v.w);
+          a = fmaxf(a, a * slope); b = fmaxf(b, b * slope);  // LeakyReLU for 0 <= slope <= 1 (host-checked)
+          c = fmaxf(c, c * slope); d = fmaxf(d, d * slope);
+          o[8 + 2 * q] = pack_bf16(a, b);
+          o[8 + 2 * q + 1] = pack_bf16(c, d);
         }
-        __nv_bfloat16* dst = y + pix * 64 + c0;
-        st_global_v8(dst, o);
-        st_global_v8(dst + 16, o + 8);
+        // channels c0 .. c0+31 = 16-byte chunks c0/8 .. c0/8+3 of this pixel's 128-byte row (128B-swizzled like a TMA tile)
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          *reinterpret_cast<uint4*>(orow + ((((c0 >> 3) + q) ^ (tg & 7)) << 4)) = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
       }
-    };
-    int it = 0, prev_tile = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      if (it > 0) mbar_wait(&mma_bar[(it - 1) & 1], ((it - 1) >> 1) & 1);  // MMA(it-1) done: sA free, TMEM[(it-1)&1] full
-      float al = 1.f;
-      if (INTERP) al = __ldg(alpha + (tile * 128 + half * 64) / (Ho * Wo));
-      mbar_wait(&full[s], use & 1);
-      pack_from_stage<CIN, INTERP>(sA, t, raw + (size_t)s * stage_bytes, oxl, al, lerp_mask);
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty[s]);
-      s += 2;
-      if (s >= NS) { s -= NS; ++use; }
       fence_proxy_async();
       tc_fence_before();
-      named_bar_sync(1, 128);
-      if (t == 0) {
-        tc_fence_after();
-        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
-        const uint32_t d = tmem_base + (uint32_t)(it & 1) * 64;
-#pragma unroll
-        for (int k = 0; k < CIN; ++k)  // K = 16*CIN
-          umma_bf16(d, umma_desc_sw128(a0 + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
-                    umma_desc_sw128(b0 + (k >> 2) * 8192 + (k & 3) * 32, 16, 1024), idesc, (uint32_t)(k != 0));
-        umma_commit(&mma_bar[it & 1]);
-      }
+      named_bar_sync(1 + grp, 128);
+      if (tg == 0) tma_store_2d(&tmY, sOg, 0, tile * 128);
       __syncwarp();
-      if (it > 0) {
-        tc_fence_after();
-        epilogue(prev_tile, (uint32_t)((it - 1) & 1));
-      }
-      prev_tile = tile;
     }
-    if (it > 0) {
-      mbar_wait(&mma_bar[(it - 1) & 1], ((it - 1) >> 1) & 1);
-      tc_fence_after();
-      epilogue(prev_tile, (uint32_t)((it - 1) & 1));
-    }
+    if (tg == 0) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<128>(tmem_base);
+  if (warp == 1) tmem_dealloc<256>(tmem_base);
 }
 
 // ------------------------------------------------------------------------------------------------ wgrad (TMA-staged)
 // The gz rows of a half tile travel in the same stage as its input boxes; a stage is released by the commit of the MMAs
-// that read its gz rows.  TMEM accumulates over all tiles of the CTA; one atomic flush per CTA, as above.
-template <int CIN, bool INTERP>
-__global__ void __launch_bounds__(FS_THREADS, 2) first_wgrad_tma_kernel(const __grid_constant__ FirstMaps maps,
+// that read its gz rows.  Each group accumulates its tiles in its own TMEM columns; one atomic flush per group.
+template <int CIN, bool INTERP, int NG>
+__global__ void __launch_bounds__(NG * 128 + 32, 1) first_wgrad_tma_kernel(const __grid_constant__ FirstMaps maps,
                                                                       const __grid_constant__ CUtensorMap tmG,
                                                                       const float* __restrict__ alpha, int lerp_mask,
                                                                       float* __restrict__ dw, float* __restrict__ db,
@@ -609,13 +665,14 @@ __global__ void __launch_bounds__(FS_THREADS, 2) first_wgrad_tma_kernel(const __
                                                                       int N, int H, int W, int NS, int stage_bytes) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sA = smem;                              // [2][128 rows][128 B]
-  uint8_t* gzs = sA + FT_A_BYTES;                  // [NS][64 pix][128 B]
+  uint8_t* sA = smem;                              // [NG groups][2][128 rows][128 B]
+  uint8_t* gzs = sA + NG * FT_A_BYTES;          // [NS][64 pix][128 B]
   uint8_t* raw = gzs + (size_t)NS * FS_GZ_BYTES;   // [NS][stage_bytes]
   uint64_t* full = reinterpret_cast<uint64_t*>(raw + (size_t)NS * stage_bytes);
-  uint64_t* empty = full + 16;
-  uint64_t* mma_bar = empty + 16;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 2);
+  uint64_t* empty = full + 32;
+  uint64_t* mma_bar = empty + 32;                  // [NG groups]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 4);
+  __shared__ float dsh[4 * NG];
 
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
   const int Ho = H / 2, Wo = W / 2;
@@ -628,92 +685,100 @@ __global__ void __launch_bounds__(FS_THREADS, 2) first_wgrad_tma_kernel(const __
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);  // the commit of the MMAs that read the stage's gz rows
     }
-    mbar_init(mma_bar, 1);
+    for (int g = 0; g < NG; ++g) mbar_init(&mma_bar[g], 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<64>(tmem_slot);
+  if (warp == 1) tmem_alloc<256>(tmem_slot);
   // k = 127 (last element of chunk 15) is the all-ones im2col column whose dW row is the bias gradient
-  if (t < 128)
-    *reinterpret_cast<uint4*>(sA + 16384 + (t >> 3) * 1024 + (t & 7) * 128 + ((7 ^ (t & 7)) << 4)) =
+  if (t < NG * 128) {
+    const int g = t >> 7, r = t & 127;
+    *reinterpret_cast<uint4*>(sA + g * FT_A_BYTES + 16384 + (r >> 3) * 1024 + (r & 7) * 128 + ((7 ^ (r & 7)) << 4)) =
         make_uint4(0u, 0u, 0u, pack_bf16(0.f, 1.f));
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);
 
-  int it = 0;
-  if (warp == 4) {
+  float dot = 0.f;  // <this group's partial dW (unscaled), wdot>: deferred rank-1 term of the spectral-norm backward
+  if (warp == 4 * NG) {
     if (lane == 0)
       first_producer<CIN, INTERP, true>(maps, &tmG, raw, gzs, full, empty, lerp_mask, NS, stage_bytes, ntiles, Ho, Wo);
   } else {
-    const int half = t >> 6, oxl = t & 63;
-    int s = half, use = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      if (it > 0) mbar_wait(mma_bar, (it - 1) & 1);  // the previous tile's MMAs are done reading sA
+    const int grp = warp >> 2, tg = t & 127, half = tg >> 6, oxl = tg & 63;
+    uint8_t* sAg = sA + grp * FT_A_BYTES;
+    const uint32_t tmem_g = tmem_base + (uint32_t)grp * 64;
+    RingPos rp(grp, half, NS);
+    int j = 0;
+    for (int tile = blockIdx.x + grp * gridDim.x; tile < ntiles; tile += NG * gridDim.x, ++j) {
+      if (j > 0) mbar_wait(&mma_bar[grp], (j - 1) & 1);  // the group's previous MMAs are done reading sAg
       float al = 1.f;
       if (INTERP) al = __ldg(alpha + (tile * 128 + half * 64) / (Ho * Wo));
-      mbar_wait(&full[s], use & 1);
-      pack_from_stage<CIN, INTERP>(sA, t, raw + (size_t)s * stage_bytes, oxl, al, lerp_mask);
+      wait_full(full, empty, rp.s, rp.use);
+      pack_from_stage<CIN, INTERP>(sAg, tg, raw + (size_t)rp.s * stage_bytes, oxl, al, lerp_mask);
       fence_proxy_async();
       tc_fence_before();
-      named_bar_sync(1, 128);
-      if (t == 0) {
+      named_bar_sync(1 + grp, 128);
+      if (tg == 0) {
         // this thread packed half 0; half 1's stage is the next one in the ring
-        int s1 = s + 1, use1 = use;
+        int s1 = rp.s + 1, use1 = rp.use;
         if (s1 == NS) { s1 = 0; ++use1; }
-        mbar_wait(&full[s1], use1 & 1);
+        wait_full(full, empty, s1, use1);
         tc_fence_after();
-        const uint32_t a0 = smem_u32(sA);
-        const uint32_t g0 = smem_u32(gzs + (size_t)s * FS_GZ_BYTES), g1 = smem_u32(gzs + (size_t)s1 * FS_GZ_BYTES);
+        const uint32_t a0 = smem_u32(sAg);
+        const uint32_t g0 = smem_u32(gzs + (size_t)rp.s * FS_GZ_BYTES), g1 = smem_u32(gzs + (size_t)s1 * FS_GZ_BYTES);
 #pragma unroll
         for (int k = 0; k < 8; ++k)  // 16 pixels of the reduction per MMA
-          umma_bf16(tmem_base, umma_desc_sw128(a0 + k * 2048, 16384, 1024),
-                    umma_desc_sw128((k < 4 ? g0 : g1) + (k & 3) * 2048, 16384, 1024), idesc, (uint32_t)((it | k) != 0));
-        umma_commit(&empty[s]);
+          umma_bf16(tmem_g, umma_desc_sw128(a0 + k * 2048, 16384, 1024),
+                    umma_desc_sw128((k < 4 ? g0 : g1) + (k & 3) * 2048, 16384, 1024), idesc, (uint32_t)((j | k) != 0));
+        umma_commit(&empty[rp.s]);
         umma_commit(&empty[s1]);
-        umma_commit(mma_bar);
+        umma_commit(&mma_bar[grp]);
       }
       __syncwarp();
-      s += 2;
-      if (s >= NS) { s -= NS; ++use; }
+      rp.next_tile(NS, NG);
     }
-  }
-  float dot = 0.f;  // <this CTA's partial dW (unscaled), wdot>: deferred rank-1 term of the spectral-norm backward
-  if (warp < 4 && it > 0) {
-    const float sc = scale ? __ldg(scale) : 1.f;
-    mbar_wait(mma_bar, (it - 1) & 1);
-    tc_fence_after();
-    const int rot = (blockIdx.x * 16) & 63;
+    if (j > 0) {
+      const float sc = scale ? __ldg(scale) : 1.f;
+      mbar_wait(&mma_bar[grp], (j - 1) & 1);
+      tc_fence_after();
+      // TMEM lane tg = im2col column k = (c*4 + ky)*4 + kx: dw[co][k] in the weight tensor's own layout.
+      // CTAs finish together: rotate the column order per CTA so concurrent flushes hit different addresses
+      const int rot = ((blockIdx.x * NG + grp) * 16) & 63;
 #pragma unroll 1
-    for (int cc = 0; cc < 64; cc += 16) {
-      const int c0 = (cc + rot) & 63;
-      uint32_t v[16];
-      tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + c0, v);
-      tmem_ld_wait();
-      if (t < 16 * CIN) {
+      for (int cc = 0; cc < 64; cc += 16) {
+        const int c0 = (cc + rot) & 63;
+        uint32_t v[16];
+        tmem_ld16(tmem_g + ((uint32_t)((warp & 3) * 32) << 16) + c0, v);
+        tmem_ld_wait();
+        if (tg < 16 * CIN) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const long long idx = (long long)(c0 + j) * (16 * CIN) + t;
-          if (wdot) dot += __uint_as_float(v[j]) * __ldg(wdot + idx);
-          atomicAdd(dw + idx, __uint_as_float(v[j]) * sc);
+          for (int q = 0; q < 16; ++q) {
+            const long long idx = (long long)(c0 + q) * (16 * CIN) + tg;
+            if (wdot) dot += __uint_as_float(v[q]) * __ldg(wdot + idx);
+            atomicAdd(dw + idx, __uint_as_float(v[q]) * sc);
+          }
+        } else if (tg == 127 && db) {
+#pragma unroll
+          for (int q = 0; q < 16; ++q) atomicAdd(db + c0 + q, __uint_as_float(v[q]));
         }
-      } else if (t == 127 && db) {
-#pragma unroll
-        for (int j = 0; j < 16; ++j) atomicAdd(db + c0 + j, __uint_as_float(v[j]));
       }
     }
   }
   if (part) {
-    __shared__ float dsh[4];
     dot = warp_sum(dot);
-    if (lane == 0 && warp < 4) dsh[warp] = dot;
+    if (lane == 0 && warp < 4 * NG) dsh[warp] = dot;
     __syncthreads();
-    if (t == 0) part[blockIdx.x] = (dsh[0] + dsh[1]) + (dsh[2] + dsh[3]);
+    if (t == 0) {
+      float d = 0.f;
+      for (int i = 0; i < 4 * NG; ++i) d += dsh[i];
+      part[blockIdx.x] = d;
+    }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<64>(tmem_base);
+  if (warp == 1) tmem_dealloc<256>(tmem_base);
 }
 
 // ---- host side of the TMA-staged variants
@@ -754,52 +819,93 @@ static int first_maps(FirstMaps* maps, const FirstIn& in, bool two, bool interp,
   return B2C_OK;
 }
 
-static int first_ns(int fixed_bytes, int stage_bytes_total) {
-  // two CTAs per SM: 227 KB of shared memory, 1 KB reserved per CTA
-  static int forced = -1;
-  if (forced < 0) {
-    const char* e = getenv("B2C_FIRST_NS");
-    forced = e ? atoi(e) : 0;
+// Packer groups and ring depth: three groups when the shared memory one CTA per SM has left (227 KB) still holds a ring of
+// NS >= 2*NG half-tile stages (the condition RingPos needs), else two; NG = 0: use the register-gather kernels.
+static void first_plan(int per_group_bytes, int shared_bytes, int stage_bytes_total, int max_ng, int* NG, int* NS) {
+  static int forced_ng = -1, forced_ns = -1;
+  if (forced_ng < 0) {
+    const char* e = getenv("B2C_FIRST_NG");
+    forced_ng = e ? atoi(e) : 0;
+    e = getenv("B2C_FIRST_NS");
+    forced_ns = e ? atoi(e) : 0;
   }
-  int ns = (113 * 1024 - fixed_bytes) / stage_bytes_total;
-  if (forced >= 2) ns = forced;
-  if (ns > 8) ns = 8;
-  if (ns < 2) ns = 2;
-  return ns;
+  *NG = 0;
+  for (int ng = max_ng; ng >= 2; --ng) {
+    if (forced_ng && ng != forced_ng) continue;
+    // two fprop groups carry an output staging tile of their own (per_group_bytes is the im2col tile: 16 KB per k-block)
+    const int extra = (max_ng == 3 && ng == 2) ? 2 * 16384 : 0;
+    int ns = (226 * 1024 - ng * per_group_bytes - extra - shared_bytes - 2048) / stage_bytes_total;
+    if (forced_ns && forced_ns < ns) ns = forced_ns;
+    if (ns > 16) ns = 16;
+    if (ns >= 2 * ng) {
+      *NG = ng;
+      *NS = ns;
+      return;
+    }
+  }
 }
 
+template <typename K>
+static int first_smem_attr(K kernel, int smem, int* have) {
+  if (smem > *have) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      b2c_set_error("cudaFuncSetAttribute(first layer, %d): %s", smem, cudaGetErrorString(e));
+      return B2C_ERR_CUDA;
+    }
+    *have = smem;
+  }
+  return B2C_OK;
+}
+
+// returns B2C_OK + *done = false when the shapes do not fit the TMA-staged kernels
 template <int CIN, bool INTERP>
 static int launch_first_fprop_tma(const FirstIn& in, const float* w, const float* inv_sigma, const float* bias, void* y, int N,
-                                  int H, int W, float slope, cudaStream_t st) {
+                                  int H, int W, float slope, cudaStream_t st, bool* done) {
+  *done = false;
   FirstMaps maps;
   int lerp_mask = 0;
   int rc = first_maps(&maps, in, CIN == 6, INTERP, N, H, W, &lerp_mask);
   if (rc) return rc;
+  const long long npix = (long long)N * (H / 2) * (W / 2);
+  CUtensorMap tmY;
+  {
+    uint64_t dims[2] = {64, (uint64_t)npix};
+    uint64_t str[1] = {128};
+    uint32_t box[2] = {64, 128};
+    rc = b2c_make_tmap_bf16(&tmY, y, 2, dims, str, box);
+    if (rc) return rc;
+  }
   constexpr int KB = (16 * CIN + 63) / 64;
   const int nslots = CIN / 3 + __builtin_popcount(lerp_mask);
   const int stage_bytes = nslots * FS_SLOT;
-  const int fixed = KB * 16384 + KB * 8192 + 2048;
-  const int NS = first_ns(fixed, stage_bytes);
-  const int smem = fixed + NS * stage_bytes;
-  static int attr_smem = 0;
-  if (smem > attr_smem) {
-    cudaError_t e = cudaFuncSetAttribute(first_fprop_tma_kernel<CIN, INTERP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) {
-      b2c_set_error("cudaFuncSetAttribute(first_fprop_tma, %d): %s", smem, cudaGetErrorString(e));
-      return B2C_ERR_CUDA;
-    }
-    attr_smem = smem;
+  int NG, NS;
+  first_plan(KB * 16384, KB * 8192, stage_bytes, 3, &NG, &NS);
+  if (!NG) return B2C_OK;
+  const int smem = NG * KB * 16384 + (NG == 2 ? 2 * 16384 : 0) + KB * 8192 + 2048 + NS * stage_bytes;
+  const long long ntiles = npix / 128;
+  const unsigned blocks = (unsigned)(ntiles < 148 ? ntiles : 148);
+  static int have2 = 0, have3 = 0;
+  if (NG == 3) {
+    rc = first_smem_attr(first_fprop_tma_kernel<CIN, INTERP, 3>, smem, &have3);
+    if (rc) return rc;
+    first_fprop_tma_kernel<CIN, INTERP, 3><<<blocks, 3 * 128 + 32, smem, st>>>(maps, tmY, in.alpha, lerp_mask, w, inv_sigma, bias,
+                                                                           N, H, W, slope, NS, stage_bytes);
+  } else {
+    rc = first_smem_attr(first_fprop_tma_kernel<CIN, INTERP, 2>, smem, &have2);
+    if (rc) return rc;
+    first_fprop_tma_kernel<CIN, INTERP, 2><<<blocks, 2 * 128 + 32, smem, st>>>(maps, tmY, in.alpha, lerp_mask, w, inv_sigma, bias,
+                                                                           N, H, W, slope, NS, stage_bytes);
   }
-  const long long ntiles = (long long)N * (H / 2) * (W / 2) / 128;
-  const unsigned blocks = (unsigned)(ntiles < 148 * 2 ? ntiles : 148 * 2);
-  first_fprop_tma_kernel<CIN, INTERP><<<blocks, FS_THREADS, smem, st>>>(maps, in.alpha, lerp_mask, w, inv_sigma, bias,
-                                                                     (__nv_bfloat16*)y, N, H, W, slope, NS, stage_bytes);
+  *done = true;
   return b2c_check_launch("first_fprop_tma");
 }
 
 template <int CIN, bool INTERP>
 static int launch_first_wgrad_tma(const FirstIn& in, const void* gz, float* dw, float* db, const float* scale,
-                                  const float* wdot, float* part, int* nparts_host, int N, int H, int W, cudaStream_t st) {
+                                  const float* wdot, float* part, int* nparts_host, int N, int H, int W, cudaStream_t st,
+                                  bool* done) {
+  *done = false;
   FirstMaps maps;
   int lerp_mask = 0;
   int rc = first_maps(&maps, in, CIN == 6, INTERP, N, H, W, &lerp_mask);
@@ -815,23 +921,26 @@ static int launch_first_wgrad_tma(const FirstIn& in, const void* gz, float* dw, 
   }
   const int nslots = CIN / 3 + __builtin_popcount(lerp_mask);
   const int stage_bytes = nslots * FS_SLOT;
-  const int fixed = FT_A_BYTES + 2048;
-  const int NS = first_ns(fixed, stage_bytes + FS_GZ_BYTES);
-  const int smem = fixed + NS * (stage_bytes + FS_GZ_BYTES);
-  static int attr_smem = 0;
-  if (smem > attr_smem) {
-    cudaError_t e = cudaFuncSetAttribute(first_wgrad_tma_kernel<CIN, INTERP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) {
-      b2c_set_error("cudaFuncSetAttribute(first_wgrad_tma, %d): %s", smem, cudaGetErrorString(e));
-      return B2C_ERR_CUDA;
-    }
-    attr_smem = smem;
-  }
+  int NG, NS;
+  first_plan(FT_A_BYTES, 0, stage_bytes + FS_GZ_BYTES, 2, &NG, &NS);  // wgrad has no epilogue to hide: two groups, deeper ring
+  if (!NG) return B2C_OK;
+  const int smem = NG * FT_A_BYTES + 2048 + NS * (stage_bytes + FS_GZ_BYTES);
   const long long ntiles = npix / 128;
-  const unsigned blocks = (unsigned)(ntiles < 148 * 2 ? ntiles : 148 * 2);
+  const unsigned blocks = (unsigned)(ntiles < 148 ? ntiles : 148);
   if (nparts_host) *nparts_host = (int)blocks;
-  first_wgrad_tma_kernel<CIN, INTERP><<<blocks, FS_THREADS, smem, st>>>(maps, tmG, in.alpha, lerp_mask, dw, db, scale, wdot,
-                                                                     part, N, H, W, NS, stage_bytes);
+  static int have2 = 0, have3 = 0;
+  if (NG == 3) {
+    rc = first_smem_attr(first_wgrad_tma_kernel<CIN, INTERP, 3>, smem, &have3);
+    if (rc) return rc;
+    first_wgrad_tma_kernel<CIN, INTERP, 3><<<blocks, 3 * 128 + 32, smem, st>>>(maps, tmG, in.alpha, lerp_mask, dw, db, scale, wdot,
+                                                                           part, N, H, W, NS, stage_bytes);
+  } else {
+    rc = first_smem_attr(first_wgrad_tma_kernel<CIN, INTERP, 2>, smem, &have2);
+    if (rc) return rc;
+    first_wgrad_tma_kernel<CIN, INTERP, 2><<<blocks, 2 * 128 + 32, smem, st>>>(maps, tmG, in.alpha, lerp_mask, dw, db, scale, wdot,
+                                                                           part, N, H, W, NS, stage_bytes);
+  }
+  *done = true;
   return b2c_check_launch("first_wgrad_tma");
 }
 
@@ -846,13 +955,16 @@ extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0
   long long blocks = (npix + 127) / 128;
   if (blocks > 148 * 4) blocks = 148 * 4;
   cudaStream_t st = (cudaStream_t)stream;
-  if (first_tma_ok(a0, a1, b0, b1, N, H, W)) {
+  if (slope >= 0.f && slope <= 1.f && first_tma_ok(a0, a1, b0, b1, N, H, W)) {
+    bool done = false;
     if (a1) {
-      if (alpha) return launch_first_fprop_tma<6, true>(in, w, inv_sigma, bias, y, N, H, W, slope, st);
-      return launch_first_fprop_tma<6, false>(in, w, inv_sigma, bias, y, N, H, W, slope, st);
+      rc = alpha ? launch_first_fprop_tma<6, true>(in, w, inv_sigma, bias, y, N, H, W, slope, st, &done)
+                 : launch_first_fprop_tma<6, false>(in, w, inv_sigma, bias, y, N, H, W, slope, st, &done);
+    } else {
+      rc = alpha ? launch_first_fprop_tma<3, true>(in, w, inv_sigma, bias, y, N, H, W, slope, st, &done)
+                 : launch_first_fprop_tma<3, false>(in, w, inv_sigma, bias, y, N, H, W, slope, st, &done);
     }
-    if (alpha) return launch_first_fprop_tma<3, true>(in, w, inv_sigma, bias, y, N, H, W, slope, st);
-    return launch_first_fprop_tma<3, false>(in, w, inv_sigma, bias, y, N, H, W, slope, st);
+    if (rc || done) return rc;
   }
   if (a1) {
     if (alpha) return launch_first_fprop<6, true>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
@@ -874,12 +986,15 @@ extern "C" int b2c_first_wgrad(const float* a0, const float* a1, const float* b0
   FirstIn in = make_in(a0, a1, b0, b1, alpha);
   if (first_tma_ok(a0, a1, b0, b1, N, H, W)) {
     cudaStream_t st = (cudaStream_t)stream;
+    bool done = false;
     if (a1) {
-      if (alpha) return launch_first_wgrad_tma<6, true>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st);
-      return launch_first_wgrad_tma<6, false>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st);
+      rc = alpha ? launch_first_wgrad_tma<6, true>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st, &done)
+                 : launch_first_wgrad_tma<6, false>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st, &done);
+    } else {
+      rc = alpha ? launch_first_wgrad_tma<3, true>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st, &done)
+                 : launch_first_wgrad_tma<3, false>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st, &done);
     }
-    if (alpha) return launch_first_wgrad_tma<3, true>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st);
-    return launch_first_wgrad_tma<3, false>(in, gz, dw, db, scale, wdot, part, nparts_host, N, H, W, st);
+    if (rc || done) return rc;
   }
   const long long npix = (long long)N * (H / 2) * (W / 2);
   CUtensorMap tmG;
