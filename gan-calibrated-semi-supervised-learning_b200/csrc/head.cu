@@ -185,8 +185,268 @@ __global__ void __launch_bounds__(256) head_wgrad_kernel(const __nv_bfloat16* __
   }
 }
 
+
+// ================================================================================================ round-2 rewrites
+// ncu on the kernels above at (64, 16, 512) (profiles/r02_head_ncu.txt): fprop 23.6 us - 10.2 M instructions for 4.2 M
+// FMAs, half its shared-memory wavefronts bank conflicts of the transposing weight staging; dgrad 29.5 us - 18.5 M
+// instructions, ALU-bound on per-tap index arithmetic and predicated single loads of gy; wgrad 25.6 us - seven dependent
+// load -> __syncthreads -> FMA rounds per block.  The rewrites keep the arithmetic (fp32 accumulation of bf16 activations
+// times fp32 weights) and remove the overhead:
+//   fprop : (experimental, B2C_HEAD_V2=2; not faster yet) the weights stay in the tensor's own [c][16 taps] order (a plain
+//           32 KB copy, 16-byte skew per channel quarter); four adjacent lanes own FP pixels x a quarter of the channels,
+//           and the 16 partial taps are transpose-reduced over the lane quad with 12 shuffles
+//   dgrad : a thread owns 4 channels - its 64 weights live in registers for the whole kernel - and DP adjacent pixels;
+//           the 4 x (DP+3) window of gy it needs is loaded up front (warp-uniform addresses), then 64*DP FMAs
+//   wgrad : one 1024-thread block per SM: four pixel sub-ranges x 256 channel pairs, all gathered gy taps of the block's
+//           range staged once, activation loads software-pipelined 8 pixels ahead, the four partial sums combined in
+//           shared memory, one vector-atomic flush per block (148 x 2048 instead of 296 x 2048)
+
+// A lane owns FP pixels x a quarter of the channels: every LDS.128 of four weights feeds 4*FP FMAs (a shared-memory load
+// returns 32 x 4 bytes per cycle however many lanes share an address, so with one pixel per lane the kernel ran at the
+// LDS rate: 28.8 us).
+constexpr int FP = 4;
+template <int C>
+__global__ void __launch_bounds__(128) head_fprop2_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ w,
+                                                          float* __restrict__ out, int N, int h) {
+  constexpr int CQ = C / 4;                      // channels per lane of a quad
+  __shared__ __align__(16) float w_s[C * 16 + 16];  // (c, t) at c*16 + t + (c / CQ)*4: the quad's four rows hit disjoint banks
+  for (int i = threadIdx.x; i < C * 4; i += blockDim.x) {
+    const int c = i >> 2, t0 = (i & 3) * 4;
+    *reinterpret_cast<float4*>(w_s + c * 16 + t0 + (c / CQ) * 4) = __ldg(reinterpret_cast<const float4*>(w) + i);
+  }
+  __syncthreads();
+  const int ho = h - 1;
+  const long long npix = (long long)N * h * h;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  const int sub = lane & 3;
+  const float* wq = w_s + sub * CQ * 16 + sub * 4;
+  for (long long p0 = ((long long)blockIdx.x * wpb + warp) * (8 * FP); p0 < npix; p0 += (long long)gridDim.x * wpb * (8 * FP)) {
+    const long long pixb = p0 + (lane >> 2) * FP;
+    const __nv_bfloat16* ap = a + sub * CQ;
+    float acc[FP][16];
+#pragma unroll
+    for (int q = 0; q < FP; ++q)
+#pragma unroll
+      for (int t = 0; t < 16; ++t) acc[q][t] = 0.f;
+#pragma unroll 1
+    for (int i0 = 0; i0 < CQ; i0 += 32) {
+      uint4 u[FP][4];
+#pragma unroll
+      for (int q = 0; q < FP; ++q)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          u[q][j] = pixb + q < npix ? __ldg(reinterpret_cast<const uint4*>(ap + (pixb + q) * C + i0 + j * 8)) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          float f[FP];
+#pragma unroll
+          for (int q = 0; q < FP; ++q) {
+            const uint32_t word = k < 2 ? u[q][j].x : k < 4 ? u[q][j].y : k < 6 ? u[q][j].z : u[q][j].w;
+            f[q] = (k & 1) ? __uint_as_float(word & 0xffff0000u) : __uint_as_float(word << 16);
+          }
+          const float* wp = wq + (i0 + j * 8 + k) * 16;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const float4 wv = *reinterpret_cast<const float4*>(wp + g * 4);
+#pragma unroll
+            for (int q = 0; q < FP; ++q) {
+              acc[q][4 * g] = fmaf(f[q], wv.x, acc[q][4 * g]);
+              acc[q][4 * g + 1] = fmaf(f[q], wv.y, acc[q][4 * g + 1]);
+              acc[q][4 * g + 2] = fmaf(f[q], wv.z, acc[q][4 * g + 2]);
+              acc[q][4 * g + 3] = fmaf(f[q], wv.w, acc[q][4 * g + 3]);
+            }
+          }
+        }
+      }
+    }
+    // transpose-reduce over the quad: after xor 1 a lane keeps 8 taps, after xor 2 four: taps of one ky
+    const bool up1 = sub & 1, up2 = sub & 2;
+    const int ky = (up1 ? 2 : 0) + (up2 ? 1 : 0);
+#pragma unroll
+    for (int q = 0; q < FP; ++q) {
+      float r8[8], r4[4];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float send = up1 ? acc[q][j] : acc[q][j + 8], keep = up1 ? acc[q][j + 8] : acc[q][j];
+        r8[j] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float send = up2 ? r8[j] : r8[j + 4], keep = up2 ? r8[j + 4] : r8[j];
+        r4[j] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+      }
+      const long long pix = pixb + q;
+      if (pix < npix) {
+        const int ix = (int)(pix % h), iy = (int)((pix / h) % h), n = (int)(pix / ((long long)h * h));
+        const int oy = iy - ky + 1;
+        if (oy >= 0 && oy < ho) {
+#pragma unroll
+          for (int kx = 0; kx < 4; ++kx) {
+            const int ox = ix - kx + 1;
+            if (ox >= 0 && ox < ho) atomicAdd(out + ((long long)n * ho + oy) * ho + ox, r4[kx]);
+          }
+        }
+      }
+    }
+  }
+}
+
+template <int DPX>
+__global__ void __launch_bounds__(256) head_dgrad2_kernel(const float* __restrict__ gy, const float* __restrict__ w,
+                                                          __nv_bfloat16* __restrict__ ga, int N, int h, int C) {
+  const int ho = h - 1;
+  const int cqs = C / 4;                       // 256 % cqs == 0 (host-checked): a thread keeps its channel quad
+  const int cq = threadIdx.x % cqs;
+  float wr[4][16];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(w + (long long)(cq * 4 + j) * 16 + g * 4));
+      wr[j][4 * g] = v.x; wr[j][4 * g + 1] = v.y; wr[j][4 * g + 2] = v.z; wr[j][4 * g + 3] = v.w;
+    }
+  const int gpr = h / DPX;                     // pixel groups per row
+  const long long ngroups = (long long)N * h * gpr;
+  const int gpb = blockDim.x / cqs;            // pixel groups per block and sweep
+  for (long long g0 = (long long)blockIdx.x * gpb + threadIdx.x / cqs; g0 < ngroups; g0 += (long long)gridDim.x * gpb) {
+    const int ix0 = (int)(g0 % gpr) * DPX, iy = (int)((g0 / gpr) % h), n = (int)(g0 / ((long long)gpr * h));
+    // window of gy: rows oy = iy+1-ky (ky = 0..3), columns ox = ix0-2 .. ix0+DPX
+    float G[4][DPX + 3];
+#pragma unroll
+    for (int ky = 0; ky < 4; ++ky) {
+      const int oy = iy + 1 - ky;
+      const bool rok = oy >= 0 && oy < ho;
+      const float* gr = gy + ((long long)n * ho + (rok ? oy : 0)) * ho;
+#pragma unroll
+      for (int cidx = 0; cidx < DPX + 3; ++cidx) {
+        const int ox = ix0 - 2 + cidx;
+        G[ky][cidx] = (rok && ox >= 0 && ox < ho) ? __ldg(gr + ox) : 0.f;
+      }
+    }
+    float acc[DPX][4];
+#pragma unroll
+    for (int q = 0; q < DPX; ++q)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[q][j] = 0.f;
+#pragma unroll
+    for (int ky = 0; ky < 4; ++ky)
+#pragma unroll
+      for (int kx = 0; kx < 4; ++kx)
+#pragma unroll
+        for (int q = 0; q < DPX; ++q) {
+          const float g = G[ky][q + 3 - kx];   // ox = ix0 + q + 1 - kx
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[q][j] = fmaf(g, wr[j][ky * 4 + kx], acc[q][j]);
+        }
+#pragma unroll
+    for (int q = 0; q < DPX; ++q) {
+      const long long pix = ((long long)n * h + iy) * h + ix0 + q;
+      *reinterpret_cast<uint2*>(ga + pix * C + cq * 4) = make_uint2(pack_bf16(acc[q][0], acc[q][1]), pack_bf16(acc[q][2], acc[q][3]));
+    }
+  }
+}
+
+// blockDim = 4 * (C/2): sub-range sr = tid / (C/2), channel pair cp = tid % (C/2).
+constexpr int HW_MAXPIX = 160;  // pixels per block (host sizes the grid accordingly)
+__global__ void __launch_bounds__(1024) head_wgrad2_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ gy,
+                                                           float* __restrict__ dw, int N, int h, int C) {
+  extern __shared__ __align__(16) float hw_smem[];
+  float* g_s = hw_smem;                 // [HW_MAXPIX][16] gathered taps of the block's pixel range
+  float* red = g_s + HW_MAXPIX * 16;    // [C][16] block sums
+  const int ho = h - 1;
+  const long long npix = (long long)N * h * h;
+  const long long p_begin = npix * blockIdx.x / gridDim.x, p_end = npix * (blockIdx.x + 1) / gridDim.x;
+  const int len = (int)(p_end - p_begin);
+  const int half_c = C / 2, sr = threadIdx.x / half_c, cp = threadIdx.x % half_c;
+  for (int i = threadIdx.x; i < len * 16; i += blockDim.x) {
+    const long long pix = p_begin + (i >> 4);
+    const int t = i & 15;
+    const int ix = (int)(pix % h), iy = (int)((pix / h) % h), n = (int)(pix / ((long long)h * h));
+    const int oy = iy - (t >> 2) + 1, ox = ix - (t & 3) + 1;
+    g_s[i] = (oy >= 0 && oy < ho && ox >= 0 && ox < ho) ? __ldg(gy + ((long long)n * ho + oy) * ho + ox) : 0.f;
+  }
+  __syncthreads();
+  const int per = (len + 3) / 4;
+  const int q0 = sr * per, q1 = min(len, q0 + per);
+  float acc0[16], acc1[16];
+#pragma unroll
+  for (int t = 0; t < 16; ++t) acc0[t] = acc1[t] = 0.f;
+  constexpr int PB = 8;
+  const __nv_bfloat16* ap = a + p_begin * C + cp * 2;
+  uint32_t u[PB], un[PB];
+#pragma unroll
+  for (int j = 0; j < PB; ++j) u[j] = (q0 + j < q1) ? __ldg(reinterpret_cast<const uint32_t*>(ap + (long long)(q0 + j) * C)) : 0u;
+  for (int q = q0; q < q1; q += PB) {
+#pragma unroll
+    for (int j = 0; j < PB; ++j)
+      un[j] = (q + PB + j < q1) ? __ldg(reinterpret_cast<const uint32_t*>(ap + (long long)(q + PB + j) * C)) : 0u;
+#pragma unroll
+    for (int j = 0; j < PB; ++j) {
+      if (q + j < q1) {
+        const float f0 = __uint_as_float(u[j] << 16), f1 = __uint_as_float(u[j] & 0xffff0000u);
+        const float4* gp = reinterpret_cast<const float4*>(g_s + (q + j) * 16);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const float4 gv = gp[g];
+          acc0[4 * g] = fmaf(gv.x, f0, acc0[4 * g]); acc1[4 * g] = fmaf(gv.x, f1, acc1[4 * g]);
+          acc0[4 * g + 1] = fmaf(gv.y, f0, acc0[4 * g + 1]); acc1[4 * g + 1] = fmaf(gv.y, f1, acc1[4 * g + 1]);
+          acc0[4 * g + 2] = fmaf(gv.z, f0, acc0[4 * g + 2]); acc1[4 * g + 2] = fmaf(gv.z, f1, acc1[4 * g + 2]);
+          acc0[4 * g + 3] = fmaf(gv.w, f0, acc0[4 * g + 3]); acc1[4 * g + 3] = fmaf(gv.w, f1, acc1[4 * g + 3]);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < PB; ++j) u[j] = un[j];
+  }
+  // combine the four sub-ranges in turn: (tap, channel) at red[t*C + ch], so a warp's float2 accesses are contiguous
+  for (int r = 0; r < 4; ++r) {
+    if (sr == r) {
+#pragma unroll
+      for (int t = 0; t < 16; ++t) {
+        float2* p2 = reinterpret_cast<float2*>(red + t * C + cp * 2);
+        float2 v = make_float2(acc0[t], acc1[t]);
+        if (r > 0) { const float2 o = *p2; v.x += o.x; v.y += o.y; }
+        *p2 = v;
+      }
+    }
+    __syncthreads();
+  }
+  float4* d4 = reinterpret_cast<float4*>(dw);
+  for (int i = threadIdx.x; i < C * 4; i += blockDim.x) {
+    const int ch = i >> 2, g = i & 3;
+    atomicAdd(d4 + i, make_float4(red[(4 * g) * C + ch], red[(4 * g + 1) * C + ch], red[(4 * g + 2) * C + ch], red[(4 * g + 3) * C + ch]));
+  }
+}
+
+static bool head_v2() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B2C_HEAD_V2");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+static bool head_v2_fprop() {
+  const char* e = getenv("B2C_HEAD_V2");
+  return e && e[0] == '2';
+}
+
 extern "C" int b2c_head_fprop(const void* a, const float* w, float* out, int N, int h, int C, void* stream) {
   B2C_REQUIRE(C % 256 == 0 && h >= 2, "head_fprop: C=%d must be a multiple of 256, h=%d >= 2", C, h);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(out, 0, sizeof(float) * (size_t)N * (h - 1) * (h - 1), st);
+  if (e != cudaSuccess) { b2c_set_error("head_fprop memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+  const long long npix = (long long)N * h * h;
+  // measured at (64, 16, 512): 31.7 us against 29.7 us for the warp-per-4-pixels kernel below - opt-in only (B2C_HEAD_V2=2)
+  if (head_v2_fprop() && C == 512 && ((uintptr_t)a & 15) == 0) {
+    long long blocks = (npix + 4 * 8 * FP - 1) / (4 * 8 * FP);  // 4 warps x 8 quads x FP pixels
+    if (blocks > 148) blocks = 148;
+    head_fprop2_kernel<512><<<(unsigned)blocks, 128, 0, st>>>((const __nv_bfloat16*)a, w, out, N, h);
+    return b2c_check_launch("head_fprop2");
+  }
   const size_t smem = (size_t)16 * C * sizeof(float);
   static bool attr_done = false;
   if (!attr_done) {
@@ -194,10 +454,6 @@ extern "C" int b2c_head_fprop(const void* a, const float* w, float* out, int N, 
     attr_done = true;
   }
   B2C_REQUIRE(smem <= 64 * 1024, "head_fprop: C=%d too large", C);
-  cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e = cudaMemsetAsync(out, 0, sizeof(float) * (size_t)N * (h - 1) * (h - 1), st);
-  if (e != cudaSuccess) { b2c_set_error("head_fprop memset: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
-  const long long npix = (long long)N * h * h;
   long long blocks = (npix + 8 * HP - 1) / (8 * HP);
   if (blocks > 148 * 2) blocks = 148 * 2;  // the 32 KB weight staging is paid per block
   head_fprop_kernel<<<(unsigned)blocks, 256, smem, st>>>((const __nv_bfloat16*)a, w, out, N, h, C);
@@ -207,6 +463,18 @@ extern "C" int b2c_head_fprop(const void* a, const float* w, float* out, int N, 
 extern "C" int b2c_head_dgrad(const float* gy, const float* w, void* ga, int N, int h, int C, void* stream) {
   B2C_REQUIRE(C % 128 == 0 && (size_t)16 * C * sizeof(float) <= 64 * 1024, "head_dgrad: C=%d must be a multiple of 128, <= 1024", C);
   B2C_REQUIRE(h % DP == 0, "head_dgrad: h=%d must be even", h);
+  if (head_v2() && 256 % (C / 4) == 0) {
+    const int dpx = h % 4 == 0 ? 4 : 2;
+    const long long ngroups = (long long)N * h * (h / dpx);
+    const int gpb = 256 / (C / 4);
+    long long blocks = (ngroups + gpb - 1) / gpb;
+    if (blocks > 148 * 2) blocks = 148 * 2;
+    if (dpx == 4)
+      head_dgrad2_kernel<4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(gy, w, (__nv_bfloat16*)ga, N, h, C);
+    else
+      head_dgrad2_kernel<2><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(gy, w, (__nv_bfloat16*)ga, N, h, C);
+    return b2c_check_launch("head_dgrad2");
+  }
   static bool attr_done = false;
   if (!attr_done) {
     cudaFuncSetAttribute(head_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
@@ -224,6 +492,19 @@ extern "C" int b2c_head_dgrad(const float* gy, const float* w, void* ga, int N, 
 extern "C" int b2c_head_wgrad(const void* a, const float* gy, float* dw, int N, int h, int C, void* stream) {
   B2C_REQUIRE(C == 256 || C == 512, "head_wgrad: C=%d must be 256 or 512", C);
   const long long npix = (long long)N * h * h;
+  if (head_v2()) {
+    long long blocks = (npix + HW_MAXPIX - 1) / HW_MAXPIX;  // at most HW_MAXPIX pixels per block ...
+    if (blocks < 148 && npix >= 148 * 8) blocks = 148;        // ... and every SM busy when there is enough work
+    if (blocks < 1) blocks = 1;
+    const size_t smem = sizeof(float) * ((size_t)HW_MAXPIX * 16 + (size_t)C * 16);
+    static bool attr_done = false;
+    if (!attr_done) {
+      cudaFuncSetAttribute(head_wgrad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+      attr_done = true;
+    }
+    head_wgrad2_kernel<<<(unsigned)blocks, 4 * (C / 2), smem, (cudaStream_t)stream>>>((const __nv_bfloat16*)a, gy, dw, N, h, C);
+    return b2c_check_launch("head_wgrad2");
+  }
   long long blocks = npix / 32;
   if (blocks > 148 * 2) blocks = 148 * 2;
   if (blocks < 1) blocks = 1;

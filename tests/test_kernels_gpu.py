@@ -226,9 +226,10 @@ def test_first_layer(L, cin, N, S, interp):
     assert abs(dot - float((refdw.double() * w.double()).sum())) <= 1e-4 * float(refdw.norm() * w.norm())
 
 
-def test_head(L):
+@pytest.mark.parametrize("N,h", [(3, 8), (5, 16), (2, 4), (3, 2), (64, 16)])
+def test_head(L, N, h):
     g = torch.Generator().manual_seed(6)
-    N, h, C = 3, 8, 512
+    C = 512
     a = q(torch.randn(N, C, h, h, generator=g))
     w = torch.randn(1, C, 4, 4, generator=g) * 0.05
     out = torch.empty(N, 1, h - 1, h - 1, device="cuda")
