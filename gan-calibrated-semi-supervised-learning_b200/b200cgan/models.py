@@ -282,10 +282,10 @@ class GeneratorSimpleRegressor(nn.Module):
     """The reference's alternative generator (cgan/models.py:147-216; generator_type: "simple", cgan/config.yaml:21):
     4 blocks of [Conv3x3 + InstanceNorm + ReLU] x 2 + MaxPool2d(2), then AvgPool -> Linear 512-256-64-4 -> Tanh -> * delta_scale.
     Same constructor, state-dict keys (features.{0,3,7,10,14,17,21,24}.{weight,bias}, regressor.{2,5,8}.{weight,bias};
-    4 833 412 parameters) and forward signature.  The forward pass runs on the B200 kernels in both modes (train mode draws
-    the two Dropout(0.5) masks of the head from b200cgan.rng); a backward pass through it is not built (SURVEY.md §8 f1 is
-    the generator-only / inference use of this model), so calling it with autograd enabled raises instead of silently
-    returning a tensor without a graph."""
+    4 833 412 parameters) and forward signature.  Forward and (first-order) backward run on the B200 kernels: the whole
+    network is one autograd Function (ops.SimpleRegressorFn: 9-tap tcgen05 convs for fprop / dgrad, the split-K tcgen05
+    weight-gradient kernel in its 3x3 mode, MaxPool / InstanceNorm+ReLU / head backward kernels); train mode draws the two
+    Dropout(0.5) masks of the head from b200cgan.rng.  It trains under CGANTrainer like the U-Net (generator_type: simple)."""
 
     CHANNELS = [(3, 64), (64, 64), (64, 128), (128, 128), (128, 256), (256, 256), (256, 512), (512, 512)]
 
@@ -311,10 +311,14 @@ class GeneratorSimpleRegressor(nn.Module):
     def dropout_numels(B, S):
         return [B * 256, B * 64]
 
+    def ordered_parameters(self):
+        convs = [m for m in self.features if isinstance(m, Conv2dK3S1)]
+        lins = [self.regressor[2], self.regressor[5], self.regressor[8]]
+        return [p for m in convs + lins for p in (m.weight, m.bias)]
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
-            raise NotImplementedError("GeneratorSimpleRegressor: only the forward pass is built (inference / no_grad); "
-                                      "train the U-Net generator, or wrap the call in torch.no_grad()")
+            return ops.SimpleRegressorFn.apply(self, x, *self.ordered_parameters())
         return ops.simple_regressor_forward(self, x)
 
 

@@ -864,15 +864,27 @@ def packed_k3(param):
     return e["k3"]
 
 
-@torch.no_grad()
-def simple_regressor_forward(net, x):
-    """GeneratorSimpleRegressor.forward (cgan/models.py:213-216) on the kernels: (B,3,S,S) fp32 -> (B,4)."""
+def packed_k3_flip(param):
+    """bf16 [Cin][9*Cout] data-gradient operand of a 3x3 conv weight (taps flipped, channels transposed), cached."""
+    e = _pack_entry(param)
+    if not e.get("k3f_ok") or e.get("k3f") is None:
+        co, ci = param.shape[:2]
+        if e.get("k3f") is None:
+            e["k3f"] = torch.empty(ci, 9 * co, dtype=BF16, device=param.device)
+        _lib.call("b2c_pack_w_k3", param.detach(), e["k3f"], co, ci, 1)
+        e["k3f_ok"] = True
+    return e["k3f"]
+
+
+def _simple_forward(net, x, save):
+    """GeneratorSimpleRegressor.forward (cgan/models.py:213-216) on the kernels: (B,3,S,S) fp32 -> (B,4).  save: keep what
+    the backward needs (per conv: its input, pre-norm output, statistics, post-activation map; head activations, masks)."""
     from . import rng
     x = x.detach().to(torch.float32).contiguous()
     N, _, H, W = x.shape
     dev = x.device
     convs = [m for m in net.features if m.__class__.__name__ == "Conv2dK3S1"]
-    a = None
+    a, saved = None, []
     for i, conv in enumerate(convs):
         cout = conv.out_channels
         z = cl_empty(N, cout, H, W, device=dev)
@@ -883,8 +895,11 @@ def simple_regressor_forward(net, x):
         else:
             _lib.call("b2c_conv3s1_bf16", a, conv.in_channels, packed_k3(conv.weight), None, conv.bias.detach(), z, cout, zs,
                       N, H, W, conv.in_channels, cout)
+        inp = a
         a = cl_empty(N, cout, H, W, device=dev)
         _lib.call("b2c_in_act_fwd", z, cout, zs, None, 0.0, a, cout, None, 0, N, H * W, cout)
+        if save:
+            saved.append((inp, z, zs, a, H, W))
         if i % 2 == 1:
             p = cl_empty(N, cout, H // 2, W // 2, device=dev)
             _lib.call("b2c_maxpool2_fwd", a, p, N, H, W, cout)
@@ -894,9 +909,85 @@ def simple_regressor_forward(net, x):
     if net.training:  # Dropout(0.5) after each hidden ReLU
         m1, m2 = rng.next_mask(N * 256, dev), rng.next_mask(N * 64, dev)
     delta = torch.empty(N, 4, dtype=torch.float32, device=dev)
+    acts = torch.empty(N, 836, dtype=torch.float32, device=dev) if save else None
     _lib.call("b2c_simple_head_fwd", a, H * W, l1.weight.detach(), l1.bias.detach(), l2.weight.detach(), l2.bias.detach(),
-              l3.weight.detach(), l3.bias.detach(), m1, m2, float(net.delta_scale), delta, None, N)
-    return delta
+              l3.weight.detach(), l3.bias.detach(), m1, m2, float(net.delta_scale), delta, acts, N)
+    return delta, (x, saved, acts, m1, m2, H * W)
+
+
+@torch.no_grad()
+def simple_regressor_forward(net, x):
+    return _simple_forward(net, x, False)[0]
+
+
+class SimpleRegressorFn(torch.autograd.Function):
+    """The whole GeneratorSimpleRegressor as ONE differentiable op (first order: the generator is never under the gradient
+    penalty).  Parameter order: the 8 conv (weight, bias) pairs, then the 3 Linear (weight, bias) pairs.  Conv biases feed an
+    InstanceNorm2d, which removes per-channel constants: their gradient is zero in exact arithmetic (the reference's autograd
+    returns rounding noise of the order 1e-9 there) and is returned as exact zeros."""
+
+    @staticmethod
+    def forward(ctx, net, x, *params):
+        delta, state = _simple_forward(net, x, True)
+        ctx.net, ctx.state = net, state
+        return delta
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, gdelta):
+        net = ctx.net
+        x, saved, acts, m1, m2, HWp = ctx.state
+        ctx.state = None
+        N, dev = x.shape[0], x.device
+        convs = [m for m in net.features if m.__class__.__name__ == "Conv2dK3S1"]
+        l1, l2, l3 = net.regressor[2], net.regressor[5], net.regressor[8]
+        sm = _lib.sm_count()
+
+        def target(p):  # (buffer the kernel writes, accumulate flag, value autograd should see)
+            sink = sink_of(p)
+            if sink is not None:
+                return sink, 1, None
+            buf = torch.empty_like(p, dtype=torch.float32)
+            return buf, 0, buf
+
+        lin = [target(q) for q in (l1.weight, l1.bias, l2.weight, l2.bias, l3.weight, l3.bias)]
+        gv = torch.empty(N, 836, dtype=torch.float32, device=dev)
+        hp = int(round(HWp ** 0.5))
+        g = cl_empty(N, 512, hp, hp, device=dev)
+        acc = lin[0][1]
+        assert all(t[1] == acc for t in lin), "GeneratorSimpleRegressor: all or none of the head parameters may have a gradient sink"
+        _lib.call("b2c_simple_head_bwd", gdelta.contiguous().float(), acts, l1.weight.detach(), l2.weight.detach(),
+                  l3.weight.detach(), m1, m2, float(net.delta_scale), HWp, gv, g, lin[0][0], lin[1][0], lin[2][0], lin[3][0],
+                  lin[4][0], lin[5][0], acc, N)
+        _sink_written(*[q for q, t in zip((l1.weight, l1.bias, l2.weight, l2.bias, l3.weight, l3.bias), lin) if t[2] is None])
+        conv_grads = [None] * 16
+        for i in reversed(range(8)):
+            conv = convs[i]
+            inp, z, zs, a, H, W = saved[i]
+            cout, cin = conv.out_channels, conv.in_channels
+            if i % 2 == 1:  # MaxPool2d(2, 2) follows this block
+                ga = cl_empty(N, cout, H, W, device=dev)
+                _lib.call("b2c_maxpool2_bwd", a, g, ga, N, H, W, cout)
+                g = ga
+            ws2 = torch.empty(N, cout, 2, dtype=torch.float32, device=dev)
+            gz = cl_empty(N, cout, H, W, device=dev)
+            _lib.call("b2c_in_act_bwd", g, cout, None, None, z, cout, zs, None, 0.0, ws2, gz, cout, N, H * W, cout)
+            wbuf, wacc, wret = target(conv.weight)
+            if i == 0:
+                if not wacc:
+                    wbuf.zero_()
+                _lib.call("b2c_conv3x3_first_wgrad", x, gz, wbuf, N, H, W)
+            else:
+                nws = 9 * cout * cin
+                ws = torch.empty(nws, dtype=torch.float32, device=dev)
+                _lib.call("b2c_wgrad3s1_bf16", gz, inp, ws, nws, wbuf, wacc, N, H, W, cout, cin, sm)
+                g = cl_empty(N, cin, H, W, device=dev)
+                _lib.call("b2c_conv3s1_bf16", gz, cout, packed_k3_flip(conv.weight), None, None, g, cin, None, N, H, W, cout, cin)
+            conv_grads[2 * i] = wret
+            bsink = sink_of(conv.bias)
+            conv_grads[2 * i + 1] = None if bsink is not None else torch.zeros_like(conv.bias)
+            _sink_written(conv.weight if wret is None else None, conv.bias if bsink is not None else None)
+        return (None, None, *conv_grads, *[t[2] for t in lin])
 
 
 def fill_(t, value):

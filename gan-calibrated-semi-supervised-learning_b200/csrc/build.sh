@@ -3,7 +3,7 @@
 set -e
 cd "$(dirname "$0")"
 OUT=../b200cgan/libb2c.so
-SRCS="host.cu tapgemm.cu convt64.cu wgrad.cu pack.cu first.cu head.cu norm.cu sn.cu loss.cu optim.cu refine.cu simple.cu"
+SRCS="host.cu tapgemm.cu convt64.cu wgrad.cu pack.cu first.cu head.cu norm.cu sn.cu loss.cu optim.cu refine.cu simple.cu dataset.cu"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -fvisibility=default"
 mkdir -p build

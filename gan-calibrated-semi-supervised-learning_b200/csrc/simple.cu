@@ -197,3 +197,147 @@ extern "C" int b2c_simple_head_fwd(const void* a, int HW, const float* W1, const
   simple_head_fwd_kernel<<<N, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)a, HW, W1, b1, W2, b2, W3, b3, m1, m2, scale, delta, acts);
   return b2c_check_launch("simple_head_fwd");
 }
+
+// ================================================================================================ backward (training)
+// First conv (nn.Conv2d(3, 64, 3, padding=1), cgan/models.py:163): dW[co][ci][ky][kx] = sum gz[n,y,x,co] x[n,ci,y+ky-1,x+kx-1].
+// K = 27 cannot feed a tensor-core tile; a thread owns 4 output channels x all 27 taps (108 fp32 accumulators kept over all the
+// image rows its persistent block walks), so every shared-memory x value it reads feeds 4 FMAs.  256 threads = 16 channel
+// quads x 16 column strips; one atomic flush per block.  gz: dense (N,H,W,64) bf16, x: (N,3,H,W) fp32.
+__global__ void __launch_bounds__(256) conv3x3_first_wgrad_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ gz,
+                                                                  float* __restrict__ dw, int N, int H, int W) {
+  extern __shared__ float xs[];  // [3 ci][3 rows][W + 2]
+  const int t = threadIdx.x, cq = t & 15, strip = t >> 4;
+  const int P = W + 2;
+  float acc[4][27];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int k = 0; k < 27; ++k) acc[j][k] = 0.f;
+  for (int row = blockIdx.x; row < N * H; row += gridDim.x) {
+    const int n = row / H, y = row % H;
+    __syncthreads();
+    for (int i = t; i < 9 * P; i += 256) {
+      const int ci = i / (3 * P), r = (i / P) % 3, xx = i % P - 1;
+      const int yy = y + r - 1;
+      xs[i] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(x + (((long long)n * 3 + ci) * H + yy) * W + xx) : 0.f;
+    }
+    __syncthreads();
+    const __nv_bfloat16* grow = gz + ((long long)row * W) * 64 + cq * 4;
+    for (int px = strip; px < W; px += 16) {
+      const uint2 u = __ldg(reinterpret_cast<const uint2*>(grow + (long long)px * 64));
+      const float2 g01 = unpack_bf16(u.x), g23 = unpack_bf16(u.y);
+      const float g[4] = {g01.x, g01.y, g23.x, g23.y};
+#pragma unroll
+      for (int k = 0; k < 27; ++k) {
+        const float xv = xs[(k / 9) * 3 * P + ((k / 3) % 3) * P + px + (k % 3)];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[j][k] = fmaf(g[j], xv, acc[j][k]);
+      }
+    }
+  }
+  // strips 2s / 2s+1 share a warp (lanes 0-15 / 16-31): pair them, then one atomic per (co, tap) and warp
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int k = 0; k < 27; ++k) {
+      const float v = acc[j][k] + __shfl_xor_sync(0xffffffffu, acc[j][k], 16);
+      if ((t & 16) == 0) atomicAdd(dw + (cq * 4 + j) * 27 + k, v);
+    }
+}
+// dw fp32 [64][3][3][3] is ACCUMULATED into (caller zeroes).
+extern "C" int b2c_conv3x3_first_wgrad(const float* x, const void* gz, float* dw, int N, int H, int W, void* stream) {
+  B2C_REQUIRE(W >= 16 && W <= 2048, "conv3x3_first_wgrad: W=%d out of range", W);
+  const size_t smem = sizeof(float) * 9 * (size_t)(W + 2);
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaFuncSetAttribute(conv3x3_first_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    attr_done = true;
+  }
+  long long blocks = (long long)N * H;
+  if (blocks > 148 * 2) blocks = 148 * 2;
+  conv3x3_first_wgrad_kernel<<<(unsigned)blocks, 256, smem, (cudaStream_t)stream>>>(x, (const __nv_bfloat16*)gz, dw, N, H, W);
+  return b2c_check_launch("conv3x3_first_wgrad");
+}
+
+// Regression head backward (cgan/models.py:199-211), one block per sample: from gdelta (N,4) and the activations the forward
+// saved (acts [N][836] = f, h1, h2, tanh) to the per-sample pre-activation gradients gv [N][836] = (gf 512, g1 256, g2 64, g3 4)
+// and the gradient of the pooled map, ga[n,p,c] = gf[c] / HW (bf16, dense (N,HW,512)).
+__global__ void __launch_bounds__(256) simple_head_bwd_kernel(const float* __restrict__ gdelta, const float* __restrict__ acts,
+                                                              const float* __restrict__ W1, const float* __restrict__ W2,
+                                                              const float* __restrict__ W3, const uint8_t* __restrict__ m1,
+                                                              const uint8_t* __restrict__ m2, float scale, int HW,
+                                                              float* __restrict__ gv, __nv_bfloat16* __restrict__ ga) {
+  __shared__ float g3[4], g2[64], g1[256], gf[512];
+  const int n = blockIdx.x, t = threadIdx.x;
+  const float* A = acts + (long long)n * 836;
+  if (t < 4) {
+    const float th = A[832 + t];
+    g3[t] = gdelta[n * 4 + t] * scale * (1.f - th * th);
+  }
+  __syncthreads();
+  if (t < 64) {
+    float s = 0.f;
+#pragma unroll
+    for (int o = 0; o < 4; ++o) s = fmaf(W3[o * 64 + t], g3[o], s);
+    const float keep = m2 ? (m2[n * 64 + t] ? 2.f : 0.f) : 1.f;
+    g2[t] = A[768 + t] > 0.f ? s * keep : 0.f;
+  }
+  __syncthreads();
+  {
+    float s = 0.f;
+    for (int o = 0; o < 64; ++o) s = fmaf(W2[o * 256 + t], g2[o], s);
+    const float keep = m1 ? (m1[n * 256 + t] ? 2.f : 0.f) : 1.f;
+    g1[t] = A[512 + t] > 0.f ? s * keep : 0.f;
+  }
+  __syncthreads();
+  for (int c = t; c < 512; c += 256) {
+    float s = 0.f;
+    for (int o = 0; o < 256; ++o) s = fmaf(W1[o * 512 + c], g1[o], s);
+    gf[c] = s;
+  }
+  __syncthreads();
+  float* G = gv + (long long)n * 836;
+  for (int c = t; c < 512; c += 256) G[c] = gf[c];
+  G[512 + t] = g1[t];
+  if (t < 64) G[768 + t] = g2[t];
+  if (t < 4) G[832 + t] = g3[t];
+  const float inv = 1.f / (float)HW;
+  for (int i = t; i < HW * 256; i += 256) {  // two channels per thread and store
+    const int p = i >> 8, c = (i & 255) * 2;
+    *reinterpret_cast<uint32_t*>(ga + ((long long)n * HW + p) * 512 + c) = pack_bf16(gf[c] * inv, gf[c + 1] * inv);
+  }
+}
+// Weight / bias gradients of the three Linear layers as fixed-order sums over the batch: dW[o][c] (+)= sum_n g[n][o] in[n][c].
+__global__ void __launch_bounds__(256) simple_head_wgrad_kernel(const float* __restrict__ acts, const float* __restrict__ gv,
+                                                                float* dW1, float* db1, float* dW2, float* db2, float* dW3,
+                                                                float* db3, int N, int accumulate) {
+  const int total = 256 * 512 + 256 + 64 * 256 + 64 + 4 * 64 + 4;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    int j = i, go, io, stride_o;
+    float* dst;
+    // (offset of the layer's g inside gv, offset of its input inside acts, -1: bias)
+    if (j < 256 * 512) { go = 512 + j / 512; io = j % 512; dst = dW1 + j; }
+    else if ((j -= 256 * 512) < 256) { go = 512 + j; io = -1; dst = db1 + j; }
+    else if ((j -= 256) < 64 * 256) { go = 768 + j / 256; io = 512 + j % 256; dst = dW2 + j; }
+    else if ((j -= 64 * 256) < 64) { go = 768 + j; io = -1; dst = db2 + j; }
+    else if ((j -= 64) < 4 * 64) { go = 832 + j / 64; io = 768 + j % 64; dst = dW3 + j; }
+    else { j -= 4 * 64; go = 832 + j; io = -1; dst = db3 + j; }
+    (void)stride_o;
+    float s = 0.f;
+    for (int n = 0; n < N; ++n) s = fmaf(gv[(long long)n * 836 + go], io >= 0 ? acts[(long long)n * 836 + io] : 1.f, s);
+    *dst = accumulate ? *dst + s : s;
+  }
+}
+// gdelta (N,4) fp32; acts / gv: [N][836] fp32 (gv is scratch + output of the per-sample gradients); ga: dense (N,HW,512) bf16;
+// dW1 [256][512], dW2 [64][256], dW3 [4][64] and biases: overwritten or (accumulate) added to.
+extern "C" int b2c_simple_head_bwd(const float* gdelta, const float* acts, const float* W1, const float* W2, const float* W3,
+                                   const uint8_t* m1, const uint8_t* m2, float scale, int HW, float* gv, void* ga, float* dW1,
+                                   float* db1, float* dW2, float* db2, float* dW3, float* db3, int accumulate, int N,
+                                   void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  simple_head_bwd_kernel<<<N, 256, 0, st>>>(gdelta, acts, W1, W2, W3, m1, m2, scale, HW, gv, (__nv_bfloat16*)ga);
+  int rc = b2c_check_launch("simple_head_bwd");
+  if (rc) return rc;
+  simple_head_wgrad_kernel<<<148 * 2, 256, 0, st>>>(acts, gv, dW1, db1, dW2, db2, dW3, db3, N, accumulate);
+  return b2c_check_launch("simple_head_wgrad");
+}

@@ -26,6 +26,8 @@ struct WgradParams {
   float* ws;               // [16][Cs][Cl] (atomic mode) or [splits][16][Cs][Cl] (deterministic mode)
   long long slab;          // 0: split-K partials are reduced with fp32 vector atomics into one slab (ws zeroed by the host);
                            // else: floats per slab, split s stores its partial tile into slab s (no atomics, no memset)
+  int k3;                  // 1: the k3/s1/p1 convs of GeneratorSimpleRegressor (cgan/models.py:163-196): 9 taps, `large` at the
+                           // resolution of `small` through a plain 4-D map, dW[a][b][ky][kx] = sum small[n,y,x,a] large[n,y+ky-1,x+kx-1,b]
 };
 
 template <int NB>
@@ -90,13 +92,24 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
           const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
           if (++tx == p.tiles_x) { tx = 0; if (++ty == p.tiles_y) { ty = 0; ++tn; } }
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_expect_tx(&full[stage], Cfg::A_BYTES + Cfg::B_BYTES);
+          const int live = p.k3 ? (9 - tap0 < TPC ? 9 - tap0 : TPC) : TPC;  // taps of this CTA that exist
+          mbar_expect_tx(&full[stage], Cfg::A_BYTES + live * Cfg::B_TAP_BYTES);
           uint8_t* dA = sA + stage * Cfg::A_BYTES;
           uint8_t* dB = sB + stage * Cfg::B_BYTES;
           tma_load_4d(dA, &tmS, &full[stage], a0, x0, y0, n0);
           tma_load_4d(dA + Cfg::BOX_BYTES, &tmS, &full[stage], a0 + 64, x0, y0, n0);
 #pragma unroll
           for (int tt = 0; tt < TPC; ++tt) {
+            if (p.k3) {
+              if (tt < live) {
+                const int ky = (tap0 + tt) / 3, kx = (tap0 + tt) % 3;
+#pragma unroll
+                for (int j = 0; j < NB / 64; ++j)
+                  tma_load_4d(dB + tt * Cfg::B_TAP_BYTES + j * Cfg::BOX_BYTES, &tmL, &full[stage], b0 + 64 * j, x0 + kx - 1,
+                              y0 + ky - 1, n0);
+              }
+              continue;
+            }
             const int ky = (tap0 + tt) >> 2, kx = (tap0 + tt) & 3;
             const int fy = (ky - 1) >> 1, di = (ky - 1) & 1, fx = (kx - 1) >> 1, dj = (kx - 1) & 1;
 #pragma unroll
@@ -137,6 +150,8 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
       tc_fence_after();
 #pragma unroll 1
       for (int tt = ((warp - 2) >> 2) * (TPC / 2); tt < (((warp - 2) >> 2) + 1) * (TPC / 2); ++tt) {  // 2 warps per lane quarter
+        if (p.k3 && tap0 + tt >= 9) continue;  // dead taps of the last group (their columns hold products of stale shared memory)
+        const bool row_ok = a < p.Cs;          // Cs = 64: rows 64..127 are the zero-filled half of the `small` box
         float* dst = p.ws + (long long)blockIdx.y * p.slab + ((long long)(tap0 + tt) * p.Cs + a) * p.Cl + b0;
 #pragma unroll 1
         for (int c0 = 0; c0 < NB; c0 += 16) {
@@ -147,6 +162,7 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
           for (int j = 0; j < 4; ++j) {
             float4 f = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
                                    __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+            if (!row_ok) continue;
             if (p.slab) *reinterpret_cast<float4*>(dst + c0 + 4 * j) = f;
             else atomicAdd(reinterpret_cast<float4*>(dst + c0 + 4 * j), f);
           }
@@ -280,7 +296,7 @@ extern "C" int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* l
   B2C_REQUIRE(ws_floats >= slab, "wgrad4s2: workspace of %lld floats < %lld", ws_floats, slab);
   const bool det = ws_floats >= slab * q.splits;
   WgradParams p;
-  p.N = N; p.Cs = Cs; p.Cl = Cl; p.ws = ws; p.slab = det ? slab : 0;
+  p.N = N; p.Cs = Cs; p.Cl = Cl; p.ws = ws; p.slab = det ? slab : 0; p.k3 = 0;
   p.BW = q.BW; p.BH = q.BH; p.BI = q.BI; p.tiles_x = q.tiles_x; p.tiles_y = q.tiles_y; p.nchunks = q.nchunks;
   const int NB = q.NB;
   p.mtiles = Cs / 128; p.ntiles = Cl / NB;
@@ -316,4 +332,86 @@ extern "C" int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* l
   if (nparts_host) *nparts_host = (int)blocks;
   wgrad_unpack_kernel<<<(unsigned)blocks, 256, 0, st>>>(ws, slab, det ? q.splits : 1, dw, Cs, Cl, accumulate, scale, wdot, part);
   return b2c_check_launch("wgrad_unpack_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------ k3 / s1 / p1
+// ws[split][9][a][b] -> dw[a][b][3][3], fixed-order sum over the slabs, optional accumulation.
+__global__ void __launch_bounds__(256) wgrad_unpack9_kernel(const float* __restrict__ ws, long long slab, int nslabs,
+                                                            float* __restrict__ dw, long long n, int accumulate) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    float v[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) v[t] = ws[(long long)t * n + i];
+    for (int sl = 1; sl < nslabs; ++sl) {
+      const float* w2 = ws + (long long)sl * slab;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) v[t] += w2[(long long)t * n + i];
+    }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) dw[i * 9 + t] = accumulate ? dw[i * 9 + t] + v[t] : v[t];
+  }
+}
+
+static WgradPlan wgrad3_plan(int N, int H, int W, int Cs, int Cl, int sm_count) {
+  WgradPlan q = wgrad_plan(N, H, W, Cs >= 128 ? Cs : 128, Cl, sm_count);  // box geometry and NB
+  const int tpc = 512 / q.NB;
+  q.tiles = ((9 + tpc - 1) / tpc) * ((Cs + 127) / 128) * (Cl / q.NB);
+  const int sms = sm_count > 0 ? sm_count : 148;
+  int splits = 1;
+  double best = 1e30;
+  for (int s = 1; s <= 2 * sms && s <= q.nchunks; ++s) {
+    const int waves = (q.tiles * s + sms - 1) / sms;
+    const double cost = waves * ((double)((q.nchunks + s - 1) / s) + 12.0);
+    if (cost < best - 1e-9) { best = cost; splits = s; }
+  }
+  q.splits = splits < 1 ? 1 : splits;
+  return q;
+}
+
+extern "C" long long b2c_wgrad3s1_ws_floats(int N, int H, int W, int Cs, int Cl, int sm_count) {
+  if (H <= 0 || W <= 0 || Cs <= 0 || Cl <= 0 || N <= 0) return 0;
+  return (long long)wgrad3_plan(N, H, W, Cs, Cl, sm_count).splits * 9 * Cs * Cl;
+}
+
+// Weight gradient of nn.Conv2d(Cl, Cs, 3, padding=1) (cgan/models.py:163-196): small = grad of the conv output (N,H,W,Cs),
+// large = the conv input (N,H,W,Cl), both dense NHWC bf16; dw fp32 [Cs][Cl][3][3] overwritten or (accumulate) added to.
+// ws: >= 9*Cs*Cl floats (atomic split-K) or b2c_wgrad3s1_ws_floats (deterministic).  Cs: 64 or a multiple of 128.
+extern "C" int b2c_wgrad3s1_bf16(const void* small, const void* large, float* ws, long long ws_floats, float* dw,
+                                 int accumulate, int N, int H, int W, int Cs, int Cl, int sm_count, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  B2C_REQUIRE((Cs == 64 || Cs % 128 == 0) && Cl % 64 == 0, "wgrad3s1: Cs=%d must be 64 or a multiple of 128, Cl=%d of 64", Cs, Cl);
+  B2C_REQUIRE(w_is_pow2(H) && w_is_pow2(W), "wgrad3s1: unsupported spatial size %dx%d", H, W);
+  const WgradPlan q = wgrad3_plan(N, H, W, Cs, Cl, sm_count);
+  const long long slab = (long long)9 * Cs * Cl;
+  B2C_REQUIRE(ws_floats >= slab, "wgrad3s1: workspace of %lld floats < %lld", ws_floats, slab);
+  const bool det = ws_floats >= slab * q.splits;
+  WgradParams p;
+  p.N = N; p.Cs = Cs; p.Cl = Cl; p.ws = ws; p.slab = det ? slab : 0; p.k3 = 1;
+  p.BW = q.BW; p.BH = q.BH; p.BI = q.BI; p.tiles_x = q.tiles_x; p.tiles_y = q.tiles_y; p.nchunks = q.nchunks;
+  const int NB = q.NB;
+  p.mtiles = (Cs + 127) / 128; p.ntiles = Cl / NB;
+  CUtensorMap tmS, tmL;
+  for (int which = 0; which < 2; ++which) {
+    const int C = which ? Cl : Cs;
+    uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint64_t str[3] = {(uint64_t)2 * C, (uint64_t)2 * W * C, (uint64_t)2 * H * W * C};
+    uint32_t box[4] = {64, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BI};
+    int rc = b2c_make_tmap_bf16(which ? &tmL : &tmS, which ? large : small, 4, dims, str, box);
+    if (rc) return rc;
+  }
+  if (!det) {
+    cudaError_t e = cudaMemsetAsync(ws, 0, sizeof(float) * (size_t)slab, st);
+    if (e != cudaSuccess) {
+      b2c_set_error("wgrad3s1 memset: %s", cudaGetErrorString(e));
+      return B2C_ERR_CUDA;
+    }
+  }
+  dim3 grid(q.tiles, q.splits);
+  int rc = NB == 128 ? launch_wgrad<128>(tmS, tmL, p, grid, st) : launch_wgrad<64>(tmS, tmL, p, grid, st);
+  if (rc) return rc;
+  const long long n = (long long)Cs * Cl;
+  long long blocks = (n + 255) / 256;
+  if (blocks > 1024) blocks = 1024;
+  wgrad_unpack9_kernel<<<(unsigned)blocks, 256, 0, st>>>(ws, slab, det ? q.splits : 1, dw, n, accumulate);
+  return b2c_check_launch("wgrad_unpack9_kernel");
 }

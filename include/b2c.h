@@ -66,6 +66,24 @@ int b2c_simple_head_fwd(const void* a, int HW, const float* W1, const float* b1,
                         const float* W3, const float* b3, const uint8_t* m1, const uint8_t* m2, float scale, float* delta,
                         float* acts, int N, void* stream);
 
+/* ---- GeneratorSimpleRegressor backward (training with generator_type: "simple", cgan/cgan_train_enhanced.py:26-31) ----
+ * wgrad3s1: weight gradient of nn.Conv2d(Cl, Cs, 3, padding=1): small = grad of the conv output (N,H,W,Cs), large = conv input
+ * (N,H,W,Cl), dense NHWC bf16; dw fp32 [Cs][Cl][3][3].  The input gradient is b2c_conv3s1_bf16 with b2c_pack_w_k3(flip = 1). */
+long long b2c_wgrad3s1_ws_floats(int N, int H, int W, int Cs, int Cl, int sm_count);
+int b2c_wgrad3s1_bf16(const void* small, const void* large, float* ws, long long ws_floats, float* dw, int accumulate, int N,
+                      int H, int W, int Cs, int Cl, int sm_count, void* stream);
+int b2c_conv3x3_first_wgrad(const float* x, const void* gz, float* dw, int N, int H, int W, void* stream);
+int b2c_simple_head_bwd(const float* gdelta, const float* acts, const float* W1, const float* W2, const float* W3,
+                        const uint8_t* m1, const uint8_t* m2, float scale, int HW, float* gv, void* ga, float* dW1, float* db1,
+                        float* dW2, float* db2, float* dW3, float* db3, int accumulate, int N, void* stream);
+
+/* ---- dataset indexing: CalibratorDataset._prepare_index / _hungarian_matching / _bbox_iou (cgan/dataset.py:57-70,128-205).
+ * pred (P,4), gt (G,4): normalised (cx,cy,w,h) fp32, 16-byte aligned; gt_begin / gt_end (P): the row range in `gt` of the image
+ * pred box i belongs to.  best_iou (P) <- max IoU over that range (the reference's fp32 arithmetic, bit-identical),
+ * best_idx (P) <- index of its FIRST maximum within the range (torch.max(dim=1)), -1 for an empty range. */
+int b2c_match_boxes(const float* pred, const float* gt, const int* gt_begin, const int* gt_end, float* best_iou,
+                    int* best_idx, int P, void* stream);
+
 /* ---- first layers, Cin = 3 / 6, NCHW fp32 in (cgan/models.py:103,245,257; interpolation cgan/losses.py:203-204) ---- */
 int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                     const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,

@@ -185,9 +185,10 @@ def g_forward(g, x, delta_scale: float = 0.3, train: bool = True,
 SIMPLE_CONVS = [0, 3, 7, 10, 14, 17, 21, 24]  # indices of the Conv2d entries of GeneratorSimpleRegressor.features
 
 
-def simple_forward(g, x, delta_scale: float = 0.3):
-    """GeneratorSimpleRegressor in eval mode (cgan/models.py:162-216): [conv3x3 + IN + ReLU] x 2 + maxpool, four times;
-    avg-pool -> Linear 512-256-64-4 (ReLU between, dropout off) -> tanh -> * delta_scale.  g: its state dict."""
+def simple_forward(g, x, delta_scale: float = 0.3, masks=None):
+    """GeneratorSimpleRegressor (cgan/models.py:162-216): [conv3x3 + IN + ReLU] x 2 + maxpool, four times; avg-pool ->
+    Linear 512-256-64-4 (ReLU + Dropout(0.5) between) -> tanh -> * delta_scale.  g: its state dict (differentiable when its
+    tensors require grad).  masks: None = eval mode, else the two keep-masks (B,256), (B,64) of the train-mode dropouts."""
     h = x
     for i, idx in enumerate(SIMPLE_CONVS):
         h = F.conv2d(_r(h), _r(g[f"features.{idx}.weight"]), g[f"features.{idx}.bias"], 1, 1)
@@ -196,7 +197,11 @@ def simple_forward(g, x, delta_scale: float = 0.3):
             h = F.max_pool2d(h, 2, 2)
     f = h.mean(dim=(2, 3))
     h1 = F.relu(F.linear(f, g["regressor.2.weight"], g["regressor.2.bias"]))
+    if masks is not None:
+        h1 = h1 * masks[0] * 2.0
     h2 = F.relu(F.linear(h1, g["regressor.5.weight"], g["regressor.5.bias"]))
+    if masks is not None:
+        h2 = h2 * masks[1] * 2.0
     return torch.tanh(F.linear(h2, g["regressor.8.weight"], g["regressor.8.bias"])) * delta_scale
 
 

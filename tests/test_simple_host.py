@@ -30,3 +30,20 @@ def test_simple_regressor_init_and_oracle_match_reference():
     with torch.no_grad():
         out = O.simple_forward({k: v.float() for k, v in sd.items()}, x, 0.3)
     assert torch.allclose(out, torch.tensor(GOLD["delta"]), rtol=1e-4, atol=1e-6)
+
+
+def test_simple_regressor_oracle_gradients_match_reference():
+    """loss = sum(delta * r) in eval mode: autograd through the oracle restatement reproduces the reference module's parameter
+    gradients (norm and a strided partial sum per tensor; conv biases feed an InstanceNorm: rounding noise, compared absolutely)."""
+    net = build_cpu()
+    sd = {k: v.float().clone().requires_grad_(True) for k, v in net.state_dict().items()}
+    x = torch.rand(*GOLD["shape"], generator=torch.Generator().manual_seed(GOLD["x_seed"])) * 2 - 1
+    (O.simple_forward(sd, x, 0.3) * torch.tensor(GOLD["r"])).sum().backward()
+    for k, (nrm, part) in GOLD["grad_stats"].items():
+        g = sd[k].grad.double()
+        if k.startswith("features") and k.endswith("bias"):
+            assert float(g.norm()) < 1e-6 and nrm < 1e-6, k
+            continue
+        assert abs(float(g.norm()) - nrm) <= 2e-3 * nrm + 1e-9, (k, float(g.norm()), nrm)
+        ps = float(g.flatten()[:: max(1, g.numel() // 7)][:7].sum())
+        assert abs(ps - part) <= 2e-3 * nrm + 1e-9, (k, ps, part)
