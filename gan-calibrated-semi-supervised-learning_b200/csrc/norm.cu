@@ -1065,3 +1065,73 @@ extern "C" int b2c_dropout_mask(uint8_t* mask, long long n, unsigned long long s
   dropout_mask_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(mask, n / 8, seed, offset / 8, offset_base);
   return b2c_check_launch("dropout_mask");
 }
+
+// ================================================================================================ fp32 CHECK MODE
+// BASELINE north_star: "per-layer outputs and gradients <= 1e-4 in an fp32 check mode".  The tensor-core kernels have
+// b2c_set_f32_output (unrounded fp32 accumulators); these two kernels are the InstanceNorm2d + (Leaky)ReLU pair on fp32
+// storage, so that a whole conv -> IN -> activation block can be held to 1e-4 against fp64 on bf16-exact inputs (and its
+// backward from the block's fp32 pre-activation).  Verification only - never on the training path: one block per (image, 32
+// channels), statistics accumulated in double.
+__global__ void __launch_bounds__(256) in_act_f32_kernel(const float* __restrict__ z, const float* __restrict__ g, float slope,
+                                                         float* __restrict__ out, int HW, int C) {
+  __shared__ double red[3][8][32];
+  __shared__ float st[4][32];
+  const int n = blockIdx.y, c = blockIdx.x * 32 + (threadIdx.x & 31), r = threadIdx.x >> 5;
+  const float* zp = z + (long long)n * HW * C + c;
+  double s = 0.0, ss = 0.0;
+  for (int p = r; p < HW; p += 8) { const double v = zp[(long long)p * C]; s += v; ss += v * v; }
+  red[0][r][threadIdx.x & 31] = s; red[1][r][threadIdx.x & 31] = ss;
+  __syncthreads();
+  if (r == 0) {
+    double a = 0.0, b = 0.0;
+    for (int k = 0; k < 8; ++k) { a += red[0][k][threadIdx.x]; b += red[1][k][threadIdx.x]; }
+    const double mean = a / HW, var = b / HW - mean * mean;
+    st[0][threadIdx.x] = (float)mean;
+    st[1][threadIdx.x] = (float)(1.0 / sqrt((var > 0.0 ? var : 0.0) + 1e-5));
+  }
+  __syncthreads();
+  const float mean = st[0][threadIdx.x & 31], rstd = st[1][threadIdx.x & 31];
+  float* op = out + (long long)n * HW * C + c;
+  if (!g) {  // forward: out = act((z - mean) * rstd)
+    for (int p = r; p < HW; p += 8) {
+      const float xh = (zp[(long long)p * C] - mean) * rstd;
+      op[(long long)p * C] = xh > 0.f ? xh : xh * slope;
+    }
+    return;
+  }
+  // backward: gz = rstd * (gx - mean(gx) - xh * mean(gx * xh)),  gx = g * act'(xh)
+  const float* gp = g + (long long)n * HW * C + c;
+  double m0 = 0.0, m1 = 0.0;
+  for (int p = r; p < HW; p += 8) {
+    const float xh = (zp[(long long)p * C] - mean) * rstd;
+    const float gx = gp[(long long)p * C] * (xh > 0.f ? 1.f : slope);
+    m0 += gx; m1 += (double)gx * xh;
+  }
+  __syncthreads();
+  red[0][r][threadIdx.x & 31] = m0; red[1][r][threadIdx.x & 31] = m1;
+  __syncthreads();
+  if (r == 0) {
+    double a = 0.0, b = 0.0;
+    for (int k = 0; k < 8; ++k) { a += red[0][k][threadIdx.x]; b += red[1][k][threadIdx.x]; }
+    st[2][threadIdx.x] = (float)(a / HW);
+    st[3][threadIdx.x] = (float)(b / HW);
+  }
+  __syncthreads();
+  const float a0 = st[2][threadIdx.x & 31], a1 = st[3][threadIdx.x & 31];
+  for (int p = r; p < HW; p += 8) {
+    const float xh = (zp[(long long)p * C] - mean) * rstd;
+    const float gx = gp[(long long)p * C] * (xh > 0.f ? 1.f : slope);
+    op[(long long)p * C] = rstd * (gx - a0 - xh * a1);
+  }
+}
+// z, out (and g): dense NHWC fp32.  fwd: out = act(IN(z)).  bwd: out = d/dz of act(IN(z)) applied to g.
+extern "C" int b2c_in_act_fwd_f32(const float* z, float slope, float* out, int N, int HW, int C, void* stream) {
+  B2C_REQUIRE(C % 32 == 0, "in_act_fwd_f32: C=%d must be a multiple of 32", C);
+  in_act_f32_kernel<<<dim3(C / 32, N), 256, 0, (cudaStream_t)stream>>>(z, nullptr, slope, out, HW, C);
+  return b2c_check_launch("in_act_fwd_f32");
+}
+extern "C" int b2c_in_act_bwd_f32(const float* g, const float* z, float slope, float* gz, int N, int HW, int C, void* stream) {
+  B2C_REQUIRE(C % 32 == 0 && g, "in_act_bwd_f32: C=%d must be a multiple of 32, g non-null", C);
+  in_act_f32_kernel<<<dim3(C / 32, N), 256, 0, (cudaStream_t)stream>>>(z, g, slope, gz, HW, C);
+  return b2c_check_launch("in_act_bwd_f32");
+}

@@ -112,6 +112,10 @@ int b2c_in_act_pool_fwd(const void* z, long long ldz, const long long* zs, float
 int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const long long* fwd_sums, const void* z, long long ldz,
                    const long long* zs, const uint8_t* mask, float slope, float* ws, void* gz, long long ldgz, int N, int HW,
                    int C, void* stream);
+/* fp32 CHECK MODE of the pair above (north_star: <= 1e-4 per layer in an fp32 check mode; with b2c_set_f32_output a whole
+ * conv -> InstanceNorm -> activation block runs on fp32 storage): z / g / out dense NHWC fp32.  Verification only. */
+int b2c_in_act_fwd_f32(const float* z, float slope, float* out, int N, int HW, int C, void* stream);
+int b2c_in_act_bwd_f32(const float* g, const float* z, float slope, float* gz, int N, int HW, int C, void* stream);
 int b2c_in_act_bwd2(const void* h, long long ldh, const void* g, long long ldg, const void* z, long long ldz,
                     const long long* zs, const uint8_t* mask, float slope, float* ws, void* gg, long long ldgg, void* gx,
                     long long ldgx, int N, int HW, int C, void* stream);

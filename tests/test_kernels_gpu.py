@@ -111,6 +111,65 @@ def test_fp32_check_mode(L, mode, N, H, W, Cin, Cout):
     assert rel(y.permute(0, 3, 1, 2), ref) < 1e-4
 
 
+@pytest.mark.parametrize("kind,N,H,W,Cin,Cout,slope", [("D", 3, 32, 32, 64, 128, 0.2), ("D", 2, 16, 16, 256, 512, 0.2),
+                                                       ("Gdown", 2, 32, 32, 128, 256, 0.2), ("Gup", 2, 8, 8, 512, 256, 0.0)])
+def test_fp32_check_mode_whole_block(L, kind, N, H, W, Cin, Cout, slope):
+    """North-star fp32 check on a whole block - D's SN-conv -> InstanceNorm -> LeakyReLU (cgan/models.py:236-242), UNetDown
+    (:57-62), UNetUp's ConvTranspose -> InstanceNorm -> ReLU (:72-77) - on fp32 storage: tensor-core conv with unrounded
+    fp32 stores, fp32 InstanceNorm + activation, against fp64 torch on the same bf16-exact input / weights: output <= 1e-4;
+    and the block's backward from that fp32 pre-activation: d/dz <= 1e-4, then data / weight gradients of the conv on the
+    bf16-rounded d/dz (the tensor cores' operand format) <= 1e-4 against fp64 on the same rounded tensor."""
+    g = torch.Generator().manual_seed(12)
+    x = q(torch.randn(N, Cin, H, W, generator=g))
+    up = kind == "Gup"
+    w = q(torch.randn(*((Cin, Cout) if up else (Cout, Cin)), 4, 4, generator=g) * 0.05)
+    Ho, Wo = (2 * H, 2 * W) if up else (H // 2, W // 2)
+    xd, wd = x.double().requires_grad_(True), w.double().requires_grad_(True)
+    zr = F.conv_transpose2d(xd, wd, None, 2, 1) if up else F.conv2d(xd, wd, None, 2, 1)
+    ar = F.leaky_relu(F.instance_norm(zr, eps=1e-5), slope)
+    L.call("b2c_set_f32_output", 1)
+    try:
+        z = torch.empty(N, Ho, Wo, Cout, dtype=torch.float32, device="cuda")
+        if up:
+            wp = torch.empty(4, Cout, 4 * Cin, dtype=torch.bfloat16, device="cuda")
+            L.call("b2c_pack_w_t", w.cuda(), None, wp, Cin, Cout)
+            L.call("b2c_convt4s2_bf16", nhwc(x), Cin, wp, None, None, z, Cout, None, None, 1.0, N, H, W, Cin, Cout)
+        else:
+            wp = torch.empty(Cout, 16 * Cin, dtype=torch.bfloat16, device="cuda")
+            L.call("b2c_pack_w_c", w.cuda(), None, wp, Cout, Cin)
+            L.call("b2c_conv4s2_bf16", nhwc(x), Cin, wp, None, None, z, Cout, None, N, H, W, Cin, Cout)
+        a = torch.empty_like(z)
+        L.call("b2c_in_act_fwd_f32", z, slope, a, N, Ho * Wo, Cout)
+        assert rel(a.permute(0, 3, 1, 2), ar) < 1e-4
+        # backward
+        gy = q(torch.randn(N, Cout, Ho, Wo, generator=g))
+        gzr, = torch.autograd.grad(ar, zr, gy.double(), retain_graph=True)
+        gz = torch.empty_like(z)
+        L.call("b2c_in_act_bwd_f32", gy.permute(0, 2, 3, 1).contiguous().cuda(), z, slope, gz, N, Ho * Wo, Cout)
+        assert rel(gz.permute(0, 3, 1, 2), gzr) < 1e-4
+        gzq = q(gz.permute(0, 3, 1, 2).cpu())                       # tensor-core operand format
+        dxr, dwr = torch.autograd.grad(zr, (xd, wd), gzq.double())
+        dx = torch.empty(N, H, W, Cin, dtype=torch.float32, device="cuda")
+        if up:   # dgrad of a transposed conv = conv with the same weights, repacked
+            wc = torch.empty(Cin, 16 * Cout, dtype=torch.bfloat16, device="cuda")
+            L.call("b2c_pack_w_c", w.cuda(), None, wc, Cin, Cout)
+            L.call("b2c_conv4s2_bf16", nhwc(gzq), Cout, wc, None, None, dx, Cin, None, N, Ho, Wo, Cout, Cin)
+        else:    # dgrad of a conv = transposed conv with the same weights
+            wt = torch.empty(4, Cin, 4 * Cout, dtype=torch.bfloat16, device="cuda")
+            L.call("b2c_pack_w_t", w.cuda(), None, wt, Cout, Cin)
+            L.call("b2c_convt4s2_bf16", nhwc(gzq), Cout, wt, None, None, dx, Cin, None, None, 1.0, N, Ho, Wo, Cout, Cin)
+        assert rel(dx.permute(0, 3, 1, 2), dxr) < 1e-4
+    finally:
+        L.call("b2c_set_f32_output", 0)
+    # weight gradient: fp32 accumulate and fp32 output in every mode
+    small, large, Cs, Cl, Hs, Ws = (x, gzq, Cin, Cout, H, W) if up else (gzq, x, Cout, Cin, Ho, Wo)
+    nws = 16 * Cs * Cl
+    ws = torch.empty(nws, dtype=torch.float32, device="cuda")
+    dw = torch.empty(Cs, Cl, 4, 4, device="cuda")
+    L.call("b2c_wgrad4s2_bf16", nhwc(small), Cs, nhwc(large), Cl, ws, nws, dw, 0, None, None, None, None, N, Hs, Ws, Cs, Cl, 148)
+    assert rel(dw, dwr) < 1e-4
+
+
 def test_convt64_fused_lrelu_backward(L):
     """convt4s2 with `act`: y = convT(x) * (act > 0 ? 1 : slope), the LeakyReLU backward fused into the dgrad epilogue."""
     g = torch.Generator().manual_seed(5)
