@@ -1135,3 +1135,54 @@ extern "C" int b2c_in_act_bwd_f32(const float* g, const float* z, float slope, f
   in_act_f32_kernel<<<dim3(C / 32, N), 256, 0, (cudaStream_t)stream>>>(z, g, slope, gz, HW, C);
   return b2c_check_launch("in_act_bwd_f32");
 }
+
+// ================================================================================================ allocation-free variant
+// b2c_in_act_bwd_static: b2c_in_act_bwd's two-pass path (plane sums -> apply) with its [N][C][2] fp32 scratch in a file-scope
+// device array instead of a caller-provided buffer, for callers that cannot allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The array lives in every GPU context that loads the library (1 MiB) until exit.  Its name is a host-side stand-in in host
+// code: the device address is resolved once per device with cudaGetSymbolAddress (with that device current) and passed to the
+// kernels.  All calls share the array: it is cleared at the start of each call (cudaMemsetAsync on the caller's stream), and
+// two calls that overlap on the GPU (different streams, or concurrent graphs) race on it.
+static constexpr int B2C_STATIC_PLANES = 131072;  // N * C <= 131072 (e.g. 256 images x 512 channels)
+static __device__ __align__(256) float g_in_act_bwd_scratch[2 * B2C_STATIC_PLANES];
+
+static int static_scratch_ptr(float** out) {
+  constexpr int MAX_DEV = 64;
+  static float* ptrs[MAX_DEV] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+    b2c_set_error("in_act_bwd_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return B2C_ERR_CUDA;
+  }
+  if (!ptrs[dev]) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_in_act_bwd_scratch);
+    if (e != cudaSuccess || !p) {
+      b2c_set_error("in_act_bwd_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return B2C_ERR_CUDA;
+    }
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return B2C_OK;
+}
+
+// Same arguments and result as b2c_in_act_bwd in its full-gradient mode (g given, no gvec / fwd_sums), minus `ws`.
+extern "C" int b2c_in_act_bwd_static(const void* g, long long ldg, const void* z, long long ldz, const long long* zs,
+                                     const uint8_t* mask, float slope, void* gz, long long ldgz, int N, int HW, int C,
+                                     void* stream) {
+  B2C_REQUIRE(g != nullptr, "in_act_bwd_static: g must be given");
+  B2C_REQUIRE(N > 0 && C > 0 && (long long)N * C <= B2C_STATIC_PLANES,
+              "in_act_bwd_static: N * C = %lld planes exceed the static scratch of %d planes; use b2c_in_act_bwd with a "
+              "caller-provided workspace", (long long)N * C, B2C_STATIC_PLANES);
+  float* scratch = nullptr;
+  if (int rc = static_scratch_ptr(&scratch)) return rc;
+  NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
+  a.g = (const __nv_bfloat16*)g; a.ldg = ldg; a.mask = mask; a.sums = scratch;
+  a.o0 = (__nv_bfloat16*)gz; a.ldo0 = ldgz;
+  if (int rc = norm_check(a, "in_act_bwd_static")) return rc;
+  if (int rc = launch_reduce<M_BWD>(a, (cudaStream_t)stream)) return rc;  // clears the scratch first
+  return launch_apply<M_BWD>(a, (cudaStream_t)stream);
+}

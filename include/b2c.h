@@ -116,6 +116,14 @@ int b2c_in_act_bwd(const void* g, long long ldg, const float* gvec, const long l
  * conv -> InstanceNorm -> activation block runs on fp32 storage): z / g / out dense NHWC fp32.  Verification only. */
 int b2c_in_act_fwd_f32(const float* z, float slope, float* out, int N, int HW, int C, void* stream);
 int b2c_in_act_bwd_f32(const float* g, const float* z, float slope, float* gz, int N, int HW, int C, void* stream);
+/* Allocation-free variant of b2c_in_act_bwd (full-gradient mode: g given; same result).  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that
+ * forbid cudaMalloc).  The [N][C][2] fp32 scratch is a file-scope device array inside the library (1 MiB per GPU that loads
+ * it, held until exit): N * C <= 131072 planes, larger calls are rejected with B2C_ERR_ARG.  The call allocates nothing (no
+ * cudaMalloc / cudaFree / torch).  All calls share the array; it is cleared at the start of every call on `stream`; calls that
+ * overlap on the GPU (other streams, concurrent graphs) race on it. */
+int b2c_in_act_bwd_static(const void* g, long long ldg, const void* z, long long ldz, const long long* zs, const uint8_t* mask,
+                          float slope, void* gz, long long ldgz, int N, int HW, int C, void* stream);
 int b2c_in_act_bwd2(const void* h, long long ldh, const void* g, long long ldg, const void* z, long long ldz,
                     const long long* zs, const uint8_t* mask, float slope, float* ws, void* gg, long long ldgg, void* gx,
                     long long ldgx, int N, int HW, int C, void* stream);
