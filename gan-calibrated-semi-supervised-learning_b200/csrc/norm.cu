@@ -826,6 +826,71 @@ static int try_cluster(const NormArgs& a, cudaStream_t st) {
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ flat forward apply
+// The forward apply is a pure map once the statistics are known (they come from the producing GEMM's epilogue).  The ring
+// kernel above keeps 3 blocks x 256 threads per SM with 2-4 pixels in flight per thread and, at the step's plane sizes, ran
+// 1.4 waves of short blocks: 18 / 25 / 33 us for 34 / 67 / 134 MB (1.8 - 4.1 TB/s).  Here the whole launch is ONE wave of
+// 4 x 256 threads per SM; a thread owns one channel vector (statistics in registers) and a strided set of pixels of one
+// image, and issues FU 16-byte loads back to back before it touches any of them (64 KB in flight per SM).  Same arithmetic
+// as plane_apply_kernel<M_FWD>, bit for bit.
+constexpr int FU = 4;
+template <bool MASK>
+__global__ void __launch_bounds__(256, 4) in_act_fwd_flat_kernel(NormArgs a, int chunk) {
+  const int n = blockIdx.y, cvecs = a.C / 8, rows = 256 / cvecs;
+  const int cv = threadIdx.x % cvecs, prow = threadIdx.x / cvecs, c0 = cv * 8;
+  float mean[8], rstd[8];
+  load_stats8(a.zs, n, a.C, c0, a.HW, mean, rstd);
+  const int p0 = blockIdx.x * chunk, p1 = min(a.HW, p0 + chunk);
+  const long long img = (long long)n * a.HW;
+  const float slope = a.slope;
+  for (int p = p0 + prow; p < p1; p += FU * rows) {
+    uint4 zv[FU];
+    uint2 mv[FU];
+#pragma unroll
+    for (int u = 0; u < FU; ++u) {
+      const int pp = p + u * rows;
+      if (pp < p1) {
+        zv[u] = __ldg(reinterpret_cast<const uint4*>(a.z + (img + pp) * a.ldz + c0));
+        if (MASK) mv[u] = __ldg(reinterpret_cast<const uint2*>(a.mask + (img + pp) * a.C + c0));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < FU; ++u) {
+      const int pp = p + u * rows;
+      if (pp >= p1) break;
+      float z[8], o[8];
+      cvt8(zv[u], z);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float xh = fmaf(z[e], rstd[e], mean[e]);  // mean = -mean * rstd (load_stats8)
+        o[e] = xh > 0.f ? xh : xh * slope;
+      }
+      if (MASK) {
+        float k[8];
+        cvt_mask8(mv[u], k);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] *= k[e] * 2.f;
+      }
+      store8(a.o0 + (img + pp) * a.ldo0 + c0, o);
+      if (a.o1) store8(a.o1 + (img + pp) * a.ldo1 + c0, o);
+    }
+  }
+}
+static int launch_fwd_flat(const NormArgs& a, cudaStream_t st) {
+  const int cvecs = a.C / 8, rows = 256 / cvecs;
+  // one wave: ~4 blocks per SM over all images; chunk = pixels per block, a multiple of FU * rows
+  int bpi = (148 * 4 + a.N - 1) / a.N;
+  if (bpi < 1) bpi = 1;
+  int chunk = (a.HW + bpi - 1) / bpi;
+  const int q = FU * rows;
+  chunk = (chunk + q - 1) / q * q;
+  bpi = (a.HW + chunk - 1) / chunk;
+  dim3 grid(bpi, a.N);
+  if (a.mask) in_act_fwd_flat_kernel<true><<<grid, 256, 0, st>>>(a, chunk);
+  else in_act_fwd_flat_kernel<false><<<grid, 256, 0, st>>>(a, chunk);
+  return b2c_check_launch("in_act_fwd_flat");
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 static int norm_check(const NormArgs& a, const char* who) {
   B2C_REQUIRE(a.C >= 64 && a.C <= 2048 && (a.C & (a.C - 1)) == 0, "%s: C=%d must be a power of two in [64,2048]", who, a.C);
@@ -887,6 +952,12 @@ extern "C" int b2c_in_act_fwd(const void* z, long long ldz, const long long* zs,
   NormArgs a = base_args(z, ldz, zs, N, HW, C, slope);
   a.mask = mask; a.o0 = (__nv_bfloat16*)o0; a.ldo0 = ldo0; a.o1 = (__nv_bfloat16*)o1; a.ldo1 = ldo1;
   if (int rc = norm_check(a, "in_act_fwd")) return rc;
+  static const int flat = env_int("B2C_NORM_FLAT", 1);
+  // measured (scripts/bench_norm.py): 16.4 / 20.5 us vs 18.4 / 24.5 us at 34 / 67 MB per tensor, equal at 134 MB, slower
+  // beyond (63.5 vs 55.3 us at 268 MB: the ring kernel's deeper per-thread pipeline wins on long streams)
+  if (flat && (long long)N * HW * C * 2 <= (100ll << 20) && ((reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(o0) | reinterpret_cast<uintptr_t>(o1)) & 15) == 0 &&
+      ldo0 % 8 == 0 && (!o1 || ldo1 % 8 == 0) && (!mask || (reinterpret_cast<uintptr_t>(mask) & 7) == 0))
+    return launch_fwd_flat(a, (cudaStream_t)stream);
   return launch_apply<M_FWD>(a, (cudaStream_t)stream);
 }
 // pooled_sums: planar [2][N][C] <- (sum over the plane of act(IN(z)), sum of act'(IN(z))): the global-average-pool numerator
