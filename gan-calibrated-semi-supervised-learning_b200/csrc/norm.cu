@@ -467,6 +467,11 @@ __device__ __forceinline__ f32x2 f2_pack(float lo, float hi) {
   asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(__float_as_uint(lo)), "r"(__float_as_uint(hi)));
   return r;
 }
+// Dropout keep-mask of channels 2j, 2j+1 of a vector (8 u8 flags in a uint2) as the multipliers (2 or 0) of Dropout(0.5)
+__device__ __forceinline__ f32x2 f2_keep(const uint2& m, int j) {
+  const uint32_t w = (j < 2 ? m.x : m.y) >> ((j & 1) * 16);
+  return f2_pack((w & 0xffu) ? 2.f : 0.f, (w & 0xff00u) ? 2.f : 0.f);
+}
 __device__ __forceinline__ void f2_split(f32x2 v, float& lo, float& hi) {
   uint32_t a, b;
   asm("mov.b64 {%0, %1}, %2;" : "=r"(a), "=r"(b) : "l"(v));
@@ -507,7 +512,7 @@ __device__ __forceinline__ uint32_t f2_to_bf16x2(f32x2 v) {
   return pack_bf16(lo, hi);
 }
 
-template <int MODE>
+template <int MODE, bool MASK>
 __global__ void __launch_bounds__(CK_THREADS, MODE == M_BWD2 ? 2 : 3) plane_cluster_kernel(const __grid_constant__ CUtensorMap tmZ,
                                                                    const __grid_constant__ CUtensorMap tmG,
                                                                    const __grid_constant__ CUtensorMap tmH, NormArgs a,
@@ -575,6 +580,7 @@ __global__ void __launch_bounds__(CK_THREADS, MODE == M_BWD2 ? 2 : 3) plane_clus
 
   // ---------------------------------------------------------------- consumers: 8 channel vectors x 32 pixel rows
   const int cv = t & 7, prow = t >> 3;
+  constexpr bool has_mask = MASK;  // Dropout(0.5) keep-mask on the forward output (first backward only; own instantiation)
   const int off0 = prow * 128 + ((cv ^ (prow & 7)) << 4);  // this thread's 16 bytes of row prow (row u*32 + prow: + u * 4096)
   const f32x2 k0 = f2_pack(a.slope, a.slope), k1 = f2_pack(1.f - a.slope, 1.f - a.slope);
   const f32x2 neg1 = f2_pack(-1.f, -1.f);
@@ -600,6 +606,12 @@ __global__ void __launch_bounds__(CK_THREADS, MODE == M_BWD2 ? 2 : 3) plane_clus
     const int slot0 = slot;  // where this unit's first box sits (resident mode re-reads from here)
     // ---- phase 1: plane sums
     for (int k = 0; k < nst; ++k) {
+      uint2 mk[CK_PIXB / 32];
+      if (MODE == M_BWD && has_mask) {  // plain loads, issued before the wait for the stage's boxes
+#pragma unroll
+        for (int v = 0; v < CK_PIXB / 32; ++v)
+          mk[v] = __ldg(reinterpret_cast<const uint2*>(a.mask + (pix0 + prow + (long long)k * CK_PIXB + v * 32) * a.C + c0));
+      }
       mbar_wait(&full[slot], par);
       const uint8_t* st = ring + (size_t)slot * Cfg::STAGE_BYTES + off0;
 #pragma unroll(MODE == M_BWD2 ? 1 : 2)
@@ -615,7 +627,8 @@ __global__ void __launch_bounds__(CK_THREADS, MODE == M_BWD2 ? 2 : 3) plane_clus
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const f32x2 xh = f2_fma(f2_bf16x2(zq[j]), rstd2[j], shift2[j]);
-          const f32x2 gn = f2_mul(f2_bf16x2(gq[j]), f2_dact(xh, k0, k1));
+          f32x2 gn = f2_mul(f2_bf16x2(gq[j]), f2_dact(xh, k0, k1));
+          if (MODE == M_BWD && has_mask) gn = f2_mul(gn, f2_keep(mk[v], j));
           if (MODE == M_BWD) {
             acc[0][j] = f2_add(acc[0][j], gn);
             acc[1][j] = f2_fma(gn, xh, acc[1][j]);
@@ -712,6 +725,12 @@ __global__ void __launch_bounds__(CK_THREADS, MODE == M_BWD2 ? 2 : 3) plane_clus
     int rslot = slot0;  // resident mode: walk this unit's boxes again
     for (int k = 0; k < nst; ++k) {
       const int cur = resident ? rslot : slot;
+      uint2 mk[CK_PIXB / 32];
+      if (MODE == M_BWD && has_mask) {
+#pragma unroll
+        for (int v = 0; v < CK_PIXB / 32; ++v)
+          mk[v] = __ldg(reinterpret_cast<const uint2*>(a.mask + (pix0 + prow + (long long)k * CK_PIXB + v * 32) * a.C + c0));
+      }
       if (!resident) mbar_wait(&full[slot], par);
       const uint8_t* st = ring + (size_t)cur * Cfg::STAGE_BYTES + off0;
 #pragma unroll(MODE == M_BWD2 ? 1 : 2)
@@ -725,7 +744,8 @@ __global__ void __launch_bounds__(CK_THREADS, MODE == M_BWD2 ? 2 : 3) plane_clus
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const f32x2 xh = f2_fma(f2_bf16x2(zq[j]), rstd2[j], shift2[j]);
-            const f32x2 gn = f2_mul(f2_bf16x2(gq[j]), f2_dact(xh, k0, k1));
+            f32x2 gn = f2_mul(f2_bf16x2(gq[j]), f2_dact(xh, k0, k1));
+            if (has_mask) gn = f2_mul(gn, f2_keep(mk[v], j));
             o[j] = f2_to_bf16x2(f2_fma(gn, rstd2[j], f2_fma(xh, c1v[j], c0v[j])));
           }
           *reinterpret_cast<uint4*>(a.o0 + pix * a.ldo0 + c0) = make_uint4(o[0], o[1], o[2], o[3]);
@@ -773,7 +793,8 @@ template <int MODE>
 static int try_cluster(const NormArgs& a, cudaStream_t st) {
   using Cfg = CkCfg<MODE>;
   static const int enable = env_int("B2C_NORM_CLUSTER", 1);
-  if (!enable || a.mask || !a.g || a.C % 64 != 0 || a.HW % CK_PIXB != 0) return 1;
+  if (!enable || !a.g || a.C % 64 != 0 || a.HW % CK_PIXB != 0) return 1;
+  if (a.mask && (MODE != M_BWD || (reinterpret_cast<uintptr_t>(a.mask) & 7))) return 1;
   if ((reinterpret_cast<uintptr_t>(a.z) | reinterpret_cast<uintptr_t>(a.g) | reinterpret_cast<uintptr_t>(a.h)) & 15) return 1;
   if (a.ldg % 8 || (MODE == M_BWD2 && a.ldh % 8)) return 1;
   // cluster size: slices of <= 512 pixels, at most 8 CTAs (portable cluster size); ring: resident whenever the slice is <= 4 boxes
@@ -789,11 +810,14 @@ static int try_cluster(const NormArgs& a, cudaStream_t st) {
   if (RS > 24) RS = 24;
   const int smem = Cfg::smem(RS);
   if (smem > 220 * 1024) return 1;
-  static int attr_smem = 0;
-  if (smem > attr_smem) {
-    cudaError_t e = cudaFuncSetAttribute(plane_cluster_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+  const bool masked = MODE == M_BWD && a.mask;
+  auto kern = plane_cluster_kernel<MODE, false>;
+  if (masked) kern = plane_cluster_kernel<MODE == M_BWD ? M_BWD : MODE, MODE == M_BWD>;
+  static bool attr_done[2] = {false, false};
+  if (!attr_done[masked]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
     if (e != cudaSuccess) { b2c_set_error("plane_cluster attr: %s", cudaGetErrorString(e)); return -B2C_ERR_CUDA; }
-    attr_smem = 220 * 1024;
+    attr_done[masked] = true;
   }
   CUtensorMap tmZ, tmG, tmH;
   const long long npix = (long long)a.N * a.HW;
@@ -811,17 +835,17 @@ static int try_cluster(const NormArgs& a, cudaStream_t st) {
   cfg.attrs = attr; cfg.numAttrs = 1;
   // persistent: as many clusters as can be co-resident (cached per configuration), each walks nunits / nclusters units
   static int cache_key[8] = {0}, cache_val[8] = {0};
-  const int key = (CS << 20) | smem;
+  const int key = (masked << 24) | (CS << 20) | smem;
   int ncl = 0;
   for (int i = 0; i < 8; ++i) if (cache_key[i] == key) ncl = cache_val[i];
   if (!ncl) {
-    if (cudaOccupancyMaxActiveClusters(&ncl, plane_cluster_kernel<MODE>, &cfg) != cudaSuccess || ncl <= 0) { cudaGetLastError(); ncl = 148 / CS; }
+    if (cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg) != cudaSuccess || ncl <= 0) { cudaGetLastError(); ncl = 148 / CS; }
     for (int i = 0; i < 8; ++i) if (!cache_key[i]) { cache_key[i] = key; cache_val[i] = ncl; break; }
   }
   static const int persist = env_int("B2C_NORM_PERSIST", 1);
   if (!persist || ncl > nunits) ncl = nunits;
   cfg.gridDim = dim3(CS * ncl);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, plane_cluster_kernel<MODE>, tmZ, tmG, tmH, a, CS, nst, RS, nunits);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmZ, tmG, tmH, a, CS, nst, RS, nunits);
   if (e != cudaSuccess) { b2c_set_error("plane_cluster launch: %s", cudaGetErrorString(e)); return -B2C_ERR_CUDA; }
   return 0;
 }
