@@ -175,6 +175,140 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
   if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
+// ------------------------------------------------------------------------------------------------ CTA pairs
+// The kernel above is L2 -> SM fill bound: per 32-pixel stage a CTA stages 8 KB of `small` and 32 KB of tap-shifted `large`
+// boxes.  For Cs >= 256 two CTAs of a cluster take adjacent 128-channel tiles of `small` and issue ONE M = 256
+// tcgen05.mma.cta_group::2 per tap pair: the N = 256 operand (two taps x 128 channels of `large`) is split between the two
+// CTAs' shared memories, so each CTA stages only HALF of the tap boxes (16 KB + its own 8 KB: 24 instead of 40 KB per stage,
+// and the ring deepens from 5 to 8 stages).  Protocol as in tapgemm_pair_kernel: both CTAs' TMA loads complete on the
+// LEADER's mbarrier (cta_group::2 TMA), the leader's elected thread issues the MMAs, its commits are multicast to both CTAs.
+struct WgradP2Cfg {
+  static constexpr int NB = 128, TPC = 4, STAGES = 8, PIX = 32;
+  static constexpr int BOX_BYTES = PIX * 128;
+  static constexpr int A_BYTES = 2 * BOX_BYTES;              // this CTA's 128 channels of `small`
+  static constexpr int B_TAP_BYTES = 2 * BOX_BYTES;          // 128 channels of `large` for one tap
+  static constexpr int B_BYTES = (TPC / 2) * B_TAP_BYTES;    // this CTA's half of the taps
+  static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;
+};
+
+__global__ void __launch_bounds__(320, 1) wgrad_pair_kernel(const __grid_constant__ CUtensorMap tmS,
+                                                            const __grid_constant__ CUtensorMap tmL, WgradParams p) {
+  using Cfg = WgradP2Cfg;
+  constexpr int STAGES = Cfg::STAGES, TPC = Cfg::TPC, NB = Cfg::NB;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * Cfg::A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * Cfg::B_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank_u32();
+  int t = blockIdx.x >> 1;                  // tile of the pair
+  const int nt = t % p.ntiles; t /= p.ntiles;
+  const int mt2 = t % (p.mtiles / 2); t /= (p.mtiles / 2);
+  const int tap0 = t * TPC;
+  const int a0 = (2 * mt2 + (int)rank) * 128, b0 = nt * NB;
+  const int splits = gridDim.y;
+  const int c_begin = (int)((long long)p.nchunks * blockIdx.y / splits);
+  const int c_end = (int)((long long)p.nchunks * (blockIdx.y + 1) / splits);
+  const int niters = c_end - c_begin;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmS);
+    tma_prefetch_desc(&tmL);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 2);   // (leader's) one arrive per producer of the pair + the transaction bytes of both
+      mbar_init(&empty[s], 1);  // multicast commit from the leader's MMA thread
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc2<512>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0, phase = 0;
+      int tx = c_begin % p.tiles_x, ty = (c_begin / p.tiles_x) % p.tiles_y, tn = c_begin / (p.tiles_x * p.tiles_y);
+      for (int c = c_begin; c < c_end; ++c) {
+        const int x0 = tx * p.BW, y0 = ty * p.BH, n0 = tn * p.BI;
+        if (++tx == p.tiles_x) { tx = 0; if (++ty == p.tiles_y) { ty = 0; ++tn; } }
+        mbar_wait(&empty[stage], phase ^ 1);
+        const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
+        if (rank == 0) mbar_expect_tx(&full[stage], 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
+        else mbar_arrive_cluster(lead_full);
+        uint8_t* dA = sA + stage * Cfg::A_BYTES;
+        uint8_t* dB = sB + stage * Cfg::B_BYTES;
+        tma2_load_4d(dA, &tmS, lead_full, a0, x0, y0, n0);
+        tma2_load_4d(dA + Cfg::BOX_BYTES, &tmS, lead_full, a0 + 64, x0, y0, n0);
+#pragma unroll
+        for (int g = 0; g < TPC / 2; ++g) {  // columns [256 g + 128 rank, +128) of the accumulators = tap tap0 + 2 g + rank
+          const int tap = tap0 + 2 * g + (int)rank;
+          const int ky = tap >> 2, kx = tap & 3;
+          const int fy = (ky - 1) >> 1, di = (ky - 1) & 1, fx = (kx - 1) >> 1, dj = (kx - 1) & 1;
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+            tma2_load_5d(dB + g * Cfg::B_TAP_BYTES + j * Cfg::BOX_BYTES, &tmL, lead_full, dj * p.Cl + b0 + 64 * j, x0 + fx, di,
+                         y0 + fy, n0);
+        }
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(256, 256, 1, 1);
+      int stage = 0, phase = 0;
+      for (int it = 0; it < niters; ++it) {
+        mbar_wait_cluster(&full[stage], phase);  // both CTAs' boxes have landed
+        tc_fence_after();
+        const uint32_t sa = smem_u32(sA + stage * Cfg::A_BYTES), sb = smem_u32(sB + stage * Cfg::B_BYTES);
+#pragma unroll
+        for (int g = 0; g < TPC / 2; ++g)
+#pragma unroll
+          for (int k = 0; k < 2; ++k)  // 16 pixels (= 2 swizzle atoms of 8 k-rows) per MMA
+            umma2_bf16(tmem_base + g * 256, umma_desc_sw128(sa + k * 2048, Cfg::BOX_BYTES, 1024),
+                       umma_desc_sw128(sb + g * Cfg::B_TAP_BYTES + k * 2048, Cfg::BOX_BYTES, 1024), idesc,
+                       (uint32_t)((it | k) != 0));
+        umma2_commit(&empty[stage]);  // frees the ring slot in BOTH CTAs
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma2_commit(tmem_full);
+    }
+  } else {
+    const int q = warp & 3;
+    const int a = a0 + q * 32 + lane;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int tt = ((warp - 2) >> 2) * (TPC / 2); tt < (((warp - 2) >> 2) + 1) * (TPC / 2); ++tt) {  // 2 warps per lane quarter
+      float* dst = p.ws + (long long)blockIdx.y * p.slab + ((long long)(tap0 + tt) * p.Cs + a) * p.Cl + b0;
+#pragma unroll 1
+      for (int c0 = 0; c0 < NB; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + tt * NB + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float4 f = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                 __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+          if (p.slab) *reinterpret_cast<float4*>(dst + c0 + 4 * j) = f;
+          else atomicAdd(reinterpret_cast<float4*>(dst + c0 + 4 * j), f);
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncwarp();
+  cluster_sync_all();  // the peer's shared memory and barriers stay alive until the leader's last MMA / commit has landed
+  if (warp == 1) tmem_dealloc2<512>(tmem_base);
+}
+
 // ws[split][tap][a][b] -> dw[a][b][ky][kx] (torch weight layout): fixed-order sum over the split-K slabs, optional
 // device-scalar scale (spectral norm: dW_orig gets dWe / sigma), optional accumulation into dw, and optionally the block
 // partials of <dWe, wdot> (unscaled; wdot in dw's layout) for the deferred rank-1 term of the spectral-norm backward
@@ -324,7 +458,30 @@ extern "C" int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* l
     }
   }
   dim3 grid(q.tiles, q.splits);
-  int rc = NB == 128 ? launch_wgrad<128>(tmS, tmL, p, grid, st) : launch_wgrad<64>(tmS, tmL, p, grid, st);
+  static const bool pair_ok = !(getenv("B2C_WGRAD_2CTA") && getenv("B2C_WGRAD_2CTA")[0] == '0');
+  int rc;
+  if (pair_ok && NB == 128 && Cs % 256 == 0) {
+    static bool attr_done = false;
+    if (!attr_done) {
+      cudaError_t e = cudaFuncSetAttribute(wgrad_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WgradP2Cfg::SMEM);
+      if (e != cudaSuccess) { b2c_set_error("cudaFuncSetAttribute(wgrad_pair): %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+      attr_done = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;  // x = 2 * (tap groups x channel-tile pairs x Cl tiles): CTAs 2i, 2i+1 form a cluster
+    cfg.blockDim = dim3(320);
+    cfg.dynamicSmemBytes = WgradP2Cfg::SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, wgrad_pair_kernel, tmS, tmL, p);
+    if (e != cudaSuccess) { b2c_set_error("wgrad_pair_kernel launch: %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+    rc = b2c_check_launch("wgrad_pair_kernel");
+  } else {
+    rc = NB == 128 ? launch_wgrad<128>(tmS, tmL, p, grid, st) : launch_wgrad<64>(tmS, tmL, p, grid, st);
+  }
   if (rc) return rc;
   const long long n = (long long)Cs * Cl;
   long long blocks = (n + 255) / 256;

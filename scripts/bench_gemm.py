@@ -23,7 +23,8 @@ def timeit(fn):
 
 CONV = [(128, 128, 64, 128), (64, 64, 128, 256), (32, 32, 256, 512), (256, 256, 64, 128), (128, 128, 64, 256), (64, 64, 128, 512)]
 CONVT = [(128, 128, 128, 64), (64, 64, 128, 64), (64, 64, 256, 64), (32, 32, 256, 128), (32, 32, 512, 128), (16, 16, 512, 256)]
-WGRAD = [(64, 64, 128, 64), (32, 32, 256, 128), (16, 16, 512, 256), (128, 128, 128, 64), (64, 64, 256, 64), (32, 32, 512, 128)]
+WGRAD = [(64, 64, 128, 64), (32, 32, 256, 128), (16, 16, 512, 256), (128, 128, 128, 64), (64, 64, 256, 64), (32, 32, 512, 128),
+         (16, 16, 512, 512), (32, 32, 1024, 256), (64, 64, 512, 128), (64, 64, 256, 128)]
 if which in ("conv", "all"):
     for H, W, Cin, Cout in CONV:
         x, w, y = bf(B, H, W, Cin), bf(Cout, 16 * Cin), bf(B, H // 2, W // 2, Cout)
