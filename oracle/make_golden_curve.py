@@ -1,7 +1,7 @@
 """200-step loss curves of the UNMODIFIED reference modules (build container only; needs /root/reference).
 Same driver as oracle/make_golden.py (reference nets + restated loop body with injected refined / dropout masks / GP alpha),
 B = 2 patches of 64x64 per step, inputs from cgan_oracle.make_batch(B, S, step).  Only the logged scalars are kept:
-tests/golden/curve_B2_S64_200.json.  TEST INFRASTRUCTURE; run:  PYTHONDONTWRITEBYTECODE=1 python oracle/make_golden_curve.py"""
+tests/golden/curve_B2_S{64,128}_200.json.  TEST INFRASTRUCTURE; run:  PYTHONDONTWRITEBYTECODE=1 python oracle/make_golden_curve.py [steps] [S]"""
 import json
 import sys
 from pathlib import Path
@@ -12,10 +12,11 @@ import make_golden as MG  # noqa: E402
 
 if __name__ == "__main__":
     steps = int(sys.argv[1]) if len(sys.argv) > 1 else 200
-    rec = MG.run(2, 64, steps)
+    S = int(sys.argv[2]) if len(sys.argv) > 2 else 64
+    rec = MG.run(2, S, steps)
     keys = ("d_loss", "gp", "wd", "loss_G", "loss_iou", "loss_wgan", "g_gradnorm", "d_gradnorm_0", "d_gradnorm_1")
-    out = {"B": 2, "S": 64, "n_critic": rec["n_critic"], "lambda_gp": rec["lambda_gp"], "steps": steps,
+    out = {"B": 2, "S": S, "n_critic": rec["n_critic"], "lambda_gp": rec["lambda_gp"], "steps": steps,
            "curves": {k: [round(s[k], 6) for s in rec["steps"]] for k in keys}}
-    dst = Path(__file__).resolve().parent.parent / "tests" / "golden" / f"curve_B2_S64_{steps}.json"
+    dst = Path(__file__).resolve().parent.parent / "tests" / "golden" / f"curve_B2_S{S}_{steps}.json"
     dst.write_text(json.dumps(out))
     print("wrote", dst)
