@@ -71,8 +71,13 @@ def test_200_step_loss_curves_vs_reference(gold_path):
     print("max windowed deviation / curve scale:", {k: round(v, 4) for k, v in dev.items()})
     for k in ("d_loss", "gp", "loss_iou"):
         assert dev[k] <= 0.02, (k, dev[k])
-    assert dev["wd"] <= 0.10, dev["wd"]  # measured 2-7 % from run to run (fp32 atomics reorder the bf16 roundings)
-    assert dev["loss_wgan"] <= 0.35 and dev["loss_G"] <= 0.35, dev  # critic offset: gauge direction, see the docstring
+    # wd, loss_wgan and loss_G are means of the critic's raw output.  At S = 128 those stay tiny over the first 200 steps
+    # (|wd| <= 0.05, |loss_wgan| <= 0.15, next to d_loss ~ 38), so besides the relative bound they get the absolute floor of
+    # bf16 storage noise in a mean critic output (0.03; 0.1 for the gauge direction); d_loss = -wd + gp holds both to 2 % anyway
+    scale = {k: float(windowed(gold["curves"][k]).abs().max()) for k in KEYS}
+    assert dev["wd"] * scale["wd"] <= max(0.10 * scale["wd"], 0.03), (dev["wd"], scale["wd"])  # measured 2-7 % at S = 64
+    for k in ("loss_wgan", "loss_G"):  # critic offset: gauge direction, see the docstring
+        assert dev[k] * scale[k] <= max(0.35 * scale[k], 0.10), (k, dev[k], scale[k])
     if gold["S"] != 64:
         return
     dev16 = deviations(got, json.loads(GOLD_BF16.read_text()))
