@@ -107,6 +107,8 @@ def useful_flops_per_patch(S, c=N_CRITIC, live_critic_g=False):
 
 
 GEMM_KERNELS = ("b2c_conv4s2_bf16", "b2c_convt4s2_bf16", "b2c_wgrad4s2_bf16")
+# entry points that are variants of a family above (same kernels, same trailing size arguments): timed and reported with it
+ALIASES = {"b2c_convt4s2_signbits_bf16": "b2c_convt4s2_bf16", "b2c_first_fprop_bits": "b2c_first_fprop"}
 BW_KERNELS = ("b2c_in_act_fwd", "b2c_in_act_bwd", "b2c_in_act_bwd2", "b2c_in_act_pool_fwd", "b2c_first_fprop",
               "b2c_first_wgrad", "b2c_first_dgrad", "b2c_multi_adam", "b2c_lrelu_bwd", "b2c_head_fprop", "b2c_head_dgrad",
               "b2c_head_wgrad")
@@ -129,9 +131,10 @@ def bw_bytes(name, a):
         return N * HW * C * 2 * 5
     if name == "b2c_lrelu_bwd":          # g, a, out, n, slope
         return a[3] * 2 * 3
-    if name == "b2c_first_fprop":        # a0, a1, b0, b1, alpha, w, inv_sigma, bias, y, N, H, W, slope
+    if name == "b2c_first_fprop":        # a0, a1, b0, b1, alpha, w, inv_sigma, bias, y, N, H, W, slope[, sign_bits]
         N, H, W = a[9:12]
-        return N * 3 * H * W * 4 * (2 if a[1] else 1) * (2 if a[2] else 1) + N * (H // 2) * (W // 2) * 64 * 2
+        bits = 8 if len(a) > 13 else 0   # b2c_first_fprop_bits: one 64-bit word per output pixel
+        return N * 3 * H * W * 4 * (2 if a[1] else 1) * (2 if a[2] else 1) + N * (H // 2) * (W // 2) * (64 * 2 + bits)
     if name == "b2c_first_wgrad":        # a0, a1, b0, b1, alpha, gz, dw, db, scale, wdot, part, nparts, N, H, W
         N, H, W = a[-3:]
         return N * 3 * H * W * 4 * (2 if a[1] else 1) * (2 if a[2] else 1) + N * (H // 2) * (W // 2) * 64 * 2
@@ -158,6 +161,8 @@ def gemm_flops(name, a):
 def kernel_families(timed, K, adam_bytes):
     """Aggregate the CUDA-event records of _lib.time_kernels over K steps -> (tensor-core families, bandwidth families)."""
     timed = dict(timed)
+    for alias, base in ALIASES.items():
+        timed[base] = list(timed.get(base, [])) + list(timed.pop(alias, []))
     bwfam = {}
     for name in BW_KERNELS:
         recs = timed.pop(name, [])
@@ -425,7 +430,7 @@ def run_b200(args):
     tr.disable_cuda_graph()
     tr.step(*[resident[0][k] for k in keys])
     barrier()
-    timed = _lib.time_kernels(GEMM_KERNELS + BW_KERNELS)
+    timed = _lib.time_kernels(GEMM_KERNELS + BW_KERNELS + tuple(ALIASES))
     g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     g0.record()
     for i in range(K):
@@ -523,7 +528,7 @@ def run_infer(args):
         f1.record()
         torch.cuda.synchronize()
         ms2 = f0.elapsed_time(f1)
-        timed = _lib.time_kernels(GEMM_KERNELS + BW_KERNELS)
+        timed = _lib.time_kernels(GEMM_KERNELS + BW_KERNELS + tuple(ALIASES))
         for i in range(K):
             G(dev[i % 2])
         torch.cuda.synchronize()

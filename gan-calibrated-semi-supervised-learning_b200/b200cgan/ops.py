@@ -231,11 +231,29 @@ def _conv_raw(x, wctx, bias, want_stats=False):
     return y
 
 
+# Sign bits of the LeakyReLU outputs of the first layers, keyed by the activation's data pointer: FirstConv(premasked=True)
+# leaves them (b2c_first_fprop_bits), the Cout = 64 data gradient of the conv above reads them instead of the activation tensor
+# (8 instead of 128 bytes per pixel in its epilogue).  Only FirstConv outputs are ever looked up, and each FirstConv forward
+# overwrites the entry of the pointer it returns, so a recycled pointer cannot carry stale bits.
+_SIGN_BITS = {}
+
+
+def _sign_bits_of(act):
+    e = _SIGN_BITS.get(act.data_ptr())
+    if e is not None and e.numel() * 64 == act.numel():
+        return e
+    return None
+
+
 def _convt_raw(x, wpack_t, Cout, wctx=None, act=None, slope=1.0, scale=None):
     x, ld = as_nhwc(x)
     N, Cin, H, W = x.shape
     y = cl_empty(N, Cout, 2 * H, 2 * W, device=x.device)
     zs = _stats_buf(N, Cout, x.device) if (wctx is not None and wctx.want_stats) else None
+    bits = _sign_bits_of(act) if (act is not None and Cout == 64 and zs is None) else None
+    if bits is not None:
+        _lib.call("b2c_convt4s2_signbits_bf16", x, ld, wpack_t, scale, y, Cout, bits, float(slope), N, H, W, Cin, Cout)
+        return y
     _lib.call("b2c_convt4s2_bf16", x, ld, wpack_t, scale, None, y, Cout, zs, act, float(slope), N, H, W, Cin, Cout)
     if zs is not None:
         wctx._stats = zs
@@ -399,13 +417,21 @@ class Interp:
         self.alpha = alpha.detach().to(torch.float32).reshape(-1).contiguous()
 
 
-def _first_fprop_raw(a0, a1, wctx, bias, slope, interp=None):
+def _first_fprop_raw(a0, a1, wctx, bias, slope, interp=None, want_bits=False):
     if interp is not None:
         a0, a1, b0, b1, al = interp.a0, interp.a1, interp.b0, interp.b1, interp.alpha
     else:
         a0, a1, b0, b1, al = _f32c(a0), _f32c(a1), None, None, None
     N, _, H, W = a0.shape
     y = cl_empty(N, 64, H // 2, W // 2, device=a0.device)
+    if want_bits:
+        bits = torch.empty(N * (H // 2) * (W // 2), dtype=torch.int64, device=a0.device)
+        _lib.call("b2c_first_fprop_bits", a0, a1, b0, b1, al, wctx.weight.detach(), wctx.inv_sigma, bias, y, N, H, W, slope, bits)
+        if len(_SIGN_BITS) > 64:
+            _SIGN_BITS.clear()
+        _SIGN_BITS[y.data_ptr()] = bits
+        return y
+    _SIGN_BITS.pop(y.data_ptr(), None)
     _lib.call("b2c_first_fprop", a0, a1, b0, b1, al, wctx.weight.detach(), wctx.inv_sigma, bias, y, N, H, W, slope)
     return y
 
@@ -456,7 +482,7 @@ class FirstConv(torch.autograd.Function):
         gradient already multiplied by LeakyReLU' - no separate activation-backward pass here.
         interp: the layer input is alpha * real + (1 - alpha) * fake, formed inside the gather; a0 / a1 are then only
         autograd PLACEHOLDERS of the interpolates (uninitialised, never read) that receive d out / d interpolate."""
-        y = _first_fprop_raw(a0, a1, wctx, bias, slope, interp)
+        y = _first_fprop_raw(a0, a1, wctx, bias, slope, interp, want_bits=premasked)
         ctx.premasked, ctx.interp = premasked, interp
         ctx.wctx, ctx.slope, ctx.has_a1, ctx.has_bias = wctx, slope, a1 is not None, bias is not None
         ctx.bias_param = bias if isinstance(bias, torch.nn.Parameter) else None

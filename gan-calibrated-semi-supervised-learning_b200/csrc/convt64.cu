@@ -31,6 +31,7 @@ struct ConvT64Params {
   float slope;               // backward of the LeakyReLU that produced this conv's input, fused into its data gradient
   int st256;                 // y and ldy allow 32-byte stores
   const float* scale;        // nullable device scalar multiplying the accumulators (spectral norm 1/sigma)
+  const unsigned long long* act_bits;  // alternative to act: one 64-bit word per output pixel, bit c = (a[c] > 0) (first_fprop)
 };
 
 namespace {
@@ -66,7 +67,8 @@ __device__ __forceinline__ int axis_pairs(int d, int (&par)[2], int (&tap)[2]) {
 // ACT = the fused LeakyReLU-backward variant (never combined with statistics): the 4 x 128-byte activation rows a thread
 // needs for its tile are fetched with 256-bit loads BEFORE it waits for the accumulator, so their latency hides behind the
 // MMAs instead of being paid once per 32-channel chunk.
-template <bool ACT, bool MERGE>
+// ACT: 0 = none, 1 = activation tensor `act`, 2 = its sign bits `act_bits` (8 bytes instead of 128 per output pixel).
+template <int ACT, bool MERGE>
 __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__ CUtensorMap tmA,
                                                          const __grid_constant__ CUtensorMap tmB, ConvT64Params p,
                                                          int ntiles) {
@@ -237,14 +239,22 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
       const bool valid = n < p.N;
       const int buf = lt & 1;
       const uint32_t acc = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
-      uint32_t am[ACT ? 4 : 1][ACT ? 32 : 1];
-      if (ACT && valid) {
+      uint32_t am[ACT == 1 ? 4 : 1][ACT == 1 ? 32 : 1];
+      uint2 ab[ACT == 2 ? 4 : 1];
+      if (ACT == 2 && valid) {
+#pragma unroll
+        for (int parity = 0; parity < 4; ++parity) {
+          const int oy = 2 * (y0 + bh) + (parity >> 1), ox = 2 * (x0 + bw) + (parity & 1);
+          ab[ACT == 2 ? parity : 0] = __ldg(reinterpret_cast<const uint2*>(p.act_bits + (((long long)n * Ho + oy) * Wo + ox)));
+        }
+      }
+      if (ACT == 1 && valid) {
 #pragma unroll
         for (int parity = 0; parity < 4; ++parity) {
           const int oy = 2 * (y0 + bh) + (parity >> 1), ox = 2 * (x0 + bw) + (parity & 1);
           const __nv_bfloat16* a = p.act + (((long long)n * Ho + oy) * Wo + ox) * 64;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) ld_global_nc_v8(a + 16 * j, &am[ACT ? parity : 0][ACT ? 8 * j : 0]);
+          for (int j = 0; j < 4; ++j) ld_global_nc_v8(a + 16 * j, &am[ACT == 1 ? parity : 0][ACT == 1 ? 8 * j : 0]);
         }
       }
       mbar_wait(&tmem_full[buf], (lt >> 1) & 1);
@@ -274,10 +284,18 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
               v1[i] = __float_as_uint(__uint_as_float(v1[i]) * osc);
             }
           }
-          if (ACT && valid) {  // fused LeakyReLU backward: scale by the slope where the forward activation was <= 0
+          if (ACT == 2 && valid) {  // the same from the sign bits: v0 = channels c0 .. c0+15, v1 = c0+16 .. c0+31
+            const uint32_t bits = c0 == 0 ? ab[ACT == 2 ? parity : 0].x : ab[ACT == 2 ? parity : 0].y;
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-              const float2 t = unpack_bf16(am[ACT ? parity : 0][ACT ? c0 / 2 + i : 0]);
+              if (!((bits >> i) & 1u)) v0[i] = __float_as_uint(__uint_as_float(v0[i]) * p.slope);
+              if (!((bits >> (16 + i)) & 1u)) v1[i] = __float_as_uint(__uint_as_float(v1[i]) * p.slope);
+            }
+          }
+          if (ACT == 1 && valid) {  // fused LeakyReLU backward: scale by the slope where the forward activation was <= 0
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float2 t = unpack_bf16(am[ACT == 1 ? parity : 0][ACT == 1 ? c0 / 2 + i : 0]);
               uint32_t* v = i < 8 ? v0 : v1;
               const int i0 = (2 * i) & 15;
               if (!(t.x > 0.f)) v[i0] = __float_as_uint(__uint_as_float(v[i0]) * p.slope);
@@ -347,12 +365,13 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
 extern "C" int b2c_in_stats(const void* z, long long ldz, long long* zs, int N, int HW, int C, void* stream);  // norm.cu
 
 int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const float* scale, void* y, long long ldy,
-                    long long* stats, const void* act, float slope, int N, int H, int W, int Cin, void* stream) {
+                    long long* stats, const void* act, const unsigned long long* act_bits, float slope, int N, int H, int W,
+                    int Cin, void* stream) {
   extern int g_f32_output;  // tapgemm.cu
   ConvT64Params p;
   p.stats = nullptr;
   p.f32out = g_f32_output;
-  p.act = (const __nv_bfloat16*)act; p.slope = slope; p.scale = scale;
+  p.act = (const __nv_bfloat16*)act; p.act_bits = act_bits; p.slope = slope; p.scale = scale;
   p.st256 = (((uintptr_t)y & 31) == 0 && ldy % 16 == 0) ? 1 : 0;
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.kchunks = Cin / 64; p.y = (__nv_bfloat16*)y; p.ldy = ldy;
   p.BW = W < 128 ? W : 128;
@@ -378,17 +397,21 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const flo
   }
   static bool attr_done = false;
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(convt64_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(convt64_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(convt64_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
     if (e != cudaSuccess) {
       b2c_set_error("cudaFuncSetAttribute(convt64): %s", cudaGetErrorString(e));
       return B2C_ERR_CUDA;
     }
     attr_done = true;
   }
-  B2C_REQUIRE(!(act && stats), "convt64: the fused LeakyReLU backward and the statistics epilogue are exclusive");
+  B2C_REQUIRE(!(act && act_bits), "convt64: act and act_bits are alternatives");
+  B2C_REQUIRE(!((act || act_bits) && stats), "convt64: the fused LeakyReLU backward and the statistics epilogue are exclusive");
+  B2C_REQUIRE(((uintptr_t)act_bits & 7) == 0, "convt64: act_bits must be 8-byte aligned");
   B2C_REQUIRE(!act || ((uintptr_t)act & 31) == 0, "convt64: act must be 32-byte aligned");
   const bool fuse_stats = stats && p.BI == 1;
   if (fuse_stats) {
@@ -407,11 +430,13 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const flo
   const int ctas = ntiles < sms ? ntiles : sms;
   const cudaStream_t st = (cudaStream_t)stream;
   if (merge) {
-    if (act) convt64_kernel<true, true><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
-    else convt64_kernel<false, true><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    if (act_bits) convt64_kernel<2, true><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    else if (act) convt64_kernel<1, true><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    else convt64_kernel<0, true><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
   } else {
-    if (act) convt64_kernel<true, false><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
-    else convt64_kernel<false, false><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    if (act_bits) convt64_kernel<2, false><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    else if (act) convt64_kernel<1, false><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    else convt64_kernel<0, false><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
   }
   int rc = b2c_check_launch("convt64_kernel");
   if (rc == 0 && stats && !fuse_stats) rc = b2c_in_stats(y, ldy, stats, N, 4 * H * W, 64, stream);

@@ -116,13 +116,24 @@ __device__ __forceinline__ void pack_store_field(uint8_t* sA, int row, int Wo, c
   }
 }
 
+// Sign bits of 32 consecutive channels from their 16 packed bf16 pairs (word j = channels 2j, 2j+1): bit c = (value > 0).
+__device__ __forceinline__ uint32_t sign_bits32(const uint32_t (&o)[16]) {
+  uint32_t bits = 0;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    bits |= (uint32_t)((int16_t)(o[j] & 0xffffu) > 0) << (2 * j);
+    bits |= (uint32_t)((int32_t)o[j] >= 0x10000) << (2 * j + 1);
+  }
+  return bits;
+}
+
 // ------------------------------------------------------------------------------------------------ fprop
 template <int CIN, bool INTERP>
 __global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_kernel(FirstIn in, const float* __restrict__ w,
                                                                     const float* __restrict__ inv_sigma,
                                                                     const float* __restrict__ bias,
                                                                     __nv_bfloat16* __restrict__ y, int N, int H, int W,
-                                                                    float slope) {
+                                                                    float slope, unsigned long long* __restrict__ sign) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
@@ -210,6 +221,7 @@ __global__ void __launch_bounds__(FT_THREADS, INTERP ? 2 : 4) first_fprop_tc_ker
         __nv_bfloat16* dst = y + (long long)pix * 64 + c0;
         st_global_v8(dst, o);
         st_global_v8(dst + 16, o + 8);
+        if (sign) reinterpret_cast<uint32_t*>(sign + pix)[c0 >> 5] = sign_bits32(o);
       }
     }
   }
@@ -354,7 +366,7 @@ static int first_check(const float* a0, const float* b0, const float* alpha, int
 
 template <int CIN, bool INTERP>
 static int launch_first_fprop(const FirstIn& in, const float* w, const float* inv_sigma, const float* bias, void* y,
-                              int N, int H, int W, float slope, unsigned blocks, cudaStream_t st) {
+                              int N, int H, int W, float slope, unsigned long long* sign, unsigned blocks, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
     int rc = first_attr(first_fprop_tc_kernel<CIN, INTERP>);
@@ -362,7 +374,7 @@ static int launch_first_fprop(const FirstIn& in, const float* w, const float* in
     attr_done = true;
   }
   first_fprop_tc_kernel<CIN, INTERP><<<blocks, FT_THREADS, FT_SMEM_FPROP, st>>>(in, w, inv_sigma, bias, (__nv_bfloat16*)y, N,
-                                                                          H, W, slope);
+                                                                          H, W, slope, sign);
   return b2c_check_launch("first_fprop");
 }
 
@@ -519,7 +531,8 @@ __global__ void __launch_bounds__(NG * 128 + 32, 1) first_fprop_tma_kernel(const
                                                                       const float* __restrict__ w,
                                                                       const float* __restrict__ inv_sigma,
                                                                       const float* __restrict__ bias, int N, int H, int W,
-                                                                      float slope, int NS, int stage_bytes) {
+                                                                      float slope, int NS, int stage_bytes,
+                                                                      unsigned long long* __restrict__ sign) {
   constexpr int KB = (16 * CIN + 63) / 64;  // k-blocks of 64
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -638,6 +651,7 @@ __global__ void __launch_bounds__(NG * 128 + 32, 1) first_fprop_tma_kernel(const
 #pragma unroll
         for (int q = 0; q < 4; ++q)
           *reinterpret_cast<uint4*>(orow + ((((c0 >> 3) + q) ^ (tg & 7)) << 4)) = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+        if (sign) reinterpret_cast<uint32_t*>(sign + ((long long)tile * 128 + tg))[c0 >> 5] = sign_bits32(o);
       }
       fence_proxy_async();
       tc_fence_before();
@@ -861,7 +875,7 @@ static int first_smem_attr(K kernel, int smem, int* have) {
 // returns B2C_OK + *done = false when the shapes do not fit the TMA-staged kernels
 template <int CIN, bool INTERP>
 static int launch_first_fprop_tma(const FirstIn& in, const float* w, const float* inv_sigma, const float* bias, void* y, int N,
-                                  int H, int W, float slope, cudaStream_t st, bool* done) {
+                                  int H, int W, float slope, unsigned long long* sign, cudaStream_t st, bool* done) {
   *done = false;
   FirstMaps maps;
   int lerp_mask = 0;
@@ -890,12 +904,12 @@ static int launch_first_fprop_tma(const FirstIn& in, const float* w, const float
     rc = first_smem_attr(first_fprop_tma_kernel<CIN, INTERP, 3>, smem, &have3);
     if (rc) return rc;
     first_fprop_tma_kernel<CIN, INTERP, 3><<<blocks, 3 * 128 + 32, smem, st>>>(maps, tmY, in.alpha, lerp_mask, w, inv_sigma, bias,
-                                                                           N, H, W, slope, NS, stage_bytes);
+                                                                           N, H, W, slope, NS, stage_bytes, sign);
   } else {
     rc = first_smem_attr(first_fprop_tma_kernel<CIN, INTERP, 2>, smem, &have2);
     if (rc) return rc;
     first_fprop_tma_kernel<CIN, INTERP, 2><<<blocks, 2 * 128 + 32, smem, st>>>(maps, tmY, in.alpha, lerp_mask, w, inv_sigma, bias,
-                                                                           N, H, W, slope, NS, stage_bytes);
+                                                                           N, H, W, slope, NS, stage_bytes, sign);
   }
   *done = true;
   return b2c_check_launch("first_fprop_tma");
@@ -945,9 +959,9 @@ static int launch_first_wgrad_tma(const FirstIn& in, const void* gz, float* dw, 
 }
 
 // a0/a1: (N,3,H,W) fp32 NCHW halves (a1 null => Cin=3).  b0/b1/alpha: optional interpolation (all or none).
-extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
-                               const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
-                               float slope, void* stream) {
+static int first_fprop_impl(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
+                            const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W, float slope,
+                            unsigned long long* sign, void* stream) {
   int rc = first_check(a0, b0, alpha, N, H, W);
   if (rc) return rc;
   FirstIn in = make_in(a0, a1, b0, b1, alpha);
@@ -958,20 +972,34 @@ extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0
   if (slope >= 0.f && slope <= 1.f && first_tma_ok(a0, a1, b0, b1, N, H, W)) {
     bool done = false;
     if (a1) {
-      rc = alpha ? launch_first_fprop_tma<6, true>(in, w, inv_sigma, bias, y, N, H, W, slope, st, &done)
-                 : launch_first_fprop_tma<6, false>(in, w, inv_sigma, bias, y, N, H, W, slope, st, &done);
+      rc = alpha ? launch_first_fprop_tma<6, true>(in, w, inv_sigma, bias, y, N, H, W, slope, sign, st, &done)
+                 : launch_first_fprop_tma<6, false>(in, w, inv_sigma, bias, y, N, H, W, slope, sign, st, &done);
     } else {
-      rc = alpha ? launch_first_fprop_tma<3, true>(in, w, inv_sigma, bias, y, N, H, W, slope, st, &done)
-                 : launch_first_fprop_tma<3, false>(in, w, inv_sigma, bias, y, N, H, W, slope, st, &done);
+      rc = alpha ? launch_first_fprop_tma<3, true>(in, w, inv_sigma, bias, y, N, H, W, slope, sign, st, &done)
+                 : launch_first_fprop_tma<3, false>(in, w, inv_sigma, bias, y, N, H, W, slope, sign, st, &done);
     }
     if (rc || done) return rc;
   }
   if (a1) {
-    if (alpha) return launch_first_fprop<6, true>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
-    return launch_first_fprop<6, false>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
+    if (alpha) return launch_first_fprop<6, true>(in, w, inv_sigma, bias, y, N, H, W, slope, sign, (unsigned)blocks, st);
+    return launch_first_fprop<6, false>(in, w, inv_sigma, bias, y, N, H, W, slope, sign, (unsigned)blocks, st);
   }
-  if (alpha) return launch_first_fprop<3, true>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
-  return launch_first_fprop<3, false>(in, w, inv_sigma, bias, y, N, H, W, slope, (unsigned)blocks, st);
+  if (alpha) return launch_first_fprop<3, true>(in, w, inv_sigma, bias, y, N, H, W, slope, sign, (unsigned)blocks, st);
+  return launch_first_fprop<3, false>(in, w, inv_sigma, bias, y, N, H, W, slope, sign, (unsigned)blocks, st);
+}
+
+extern "C" int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
+                               const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
+                               float slope, void* stream) {
+  return first_fprop_impl(a0, a1, b0, b1, alpha, w, inv_sigma, bias, y, N, H, W, slope, nullptr, stream);
+}
+// The same, and sign_bits[pixel] (one 64-bit word per output pixel, N*(H/2)*(W/2) of them) <- bit c = (y[pixel][c] > 0): what
+// the LeakyReLU backward of this layer needs, 1/16 of the activation's bytes (b2c_convt4s2_signbits_bf16 consumes it).
+extern "C" int b2c_first_fprop_bits(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
+                                    const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
+                                    float slope, unsigned long long* sign_bits, void* stream) {
+  B2C_REQUIRE(sign_bits != nullptr && ((uintptr_t)sign_bits & 7) == 0, "first_fprop_bits: sign_bits must be given, 8-byte aligned");
+  return first_fprop_impl(a0, a1, b0, b1, alpha, w, inv_sigma, bias, y, N, H, W, slope, sign_bits, stream);
 }
 
 // dw: fp32 [64][Cin][4][4], db: fp32 [64] or null; both are ACCUMULATED into (caller zeroes).  gz: dense NHWC bf16.

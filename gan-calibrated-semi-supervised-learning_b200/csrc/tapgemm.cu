@@ -909,8 +909,8 @@ extern "C" int b2c_conv4s2_bf16(const void* x, long long ldx, const void* wpack_
 }
 
 int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const float* scale, void* y, long long ldy,
-                    long long* stats, const void* act, float slope, int N, int H, int W, int Cin, void* stream);  // convt64.cu
-
+                    long long* stats, const void* act, const unsigned long long* act_bits, float slope, int N, int H, int W,
+                    int Cin, void* stream);
 extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack_t, const float* scale, const float* bias,
                                  void* y, long long ldy, long long* stats, const void* act, float slope, int N, int H, int W,
                                  int Cin, int Cout, void* stream) {
@@ -918,7 +918,19 @@ extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack
   if (g_f32_output) B2C_REQUIRE(stats == nullptr, "fp32 check mode: fused statistics are not available");
   if (Cout == 64 && bias == nullptr && merge && Cin % 64 == 0 && ldx % 8 == 0 && ldy % 8 == 0 &&
       ((uintptr_t)y & 15) == 0 && is_pow2(H) && is_pow2(W))
-    return b2c_run_convt64(x, ldx, wpack_t, scale, y, ldy, stats, act, slope, N, H, W, Cin, stream);
+    return b2c_run_convt64(x, ldx, wpack_t, scale, y, ldy, stats, act, nullptr, slope, N, H, W, Cin, stream);
   B2C_REQUIRE(act == nullptr, "convt4s2: the fused LeakyReLU backward needs the Cout = 64 kernel (Cout=%d, bias=%p)", Cout, (const void*)bias);
   return run_tapgemm(1, x, ldx, wpack_t, scale, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
+}
+
+// b2c_convt4s2_bf16 for Cout = 64 with the fused LeakyReLU backward driven by SIGN BITS of the activation (one 64-bit word per
+// output pixel, bit c = (a[c] > 0), written by b2c_first_fprop_bits) instead of the activation tensor: 8 bytes instead of 128
+// per output pixel in the epilogue.  y = convT(x) * scale * (bit ? 1 : slope).
+extern "C" int b2c_convt4s2_signbits_bf16(const void* x, long long ldx, const void* wpack_t, const float* scale, void* y,
+                                          long long ldy, const unsigned long long* act_bits, float slope, int N, int H, int W,
+                                          int Cin, int Cout, void* stream) {
+  B2C_REQUIRE(act_bits != nullptr, "convt4s2_signbits: act_bits must be given");
+  B2C_REQUIRE(Cout == 64 && Cin % 64 == 0 && ldx % 8 == 0 && ldy % 8 == 0 && ((uintptr_t)y & 15) == 0 && is_pow2(H) && is_pow2(W),
+              "convt4s2_signbits: needs Cout = 64 (got %d), Cin %% 64 == 0, 16-byte aligned y, power-of-two %dx%d", Cout, H, W);
+  return b2c_run_convt64(x, ldx, wpack_t, scale, y, ldy, nullptr, nullptr, act_bits, slope, N, H, W, Cin, stream);
 }

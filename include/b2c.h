@@ -88,6 +88,15 @@ int b2c_match_boxes(const float* pred, const float* gt, const int* gt_begin, con
 int b2c_first_fprop(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
                     const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
                     float slope, void* stream);
+/* first_fprop that also leaves the SIGN BITS of its output (one 64-bit word per output pixel, bit c = (y[c] > 0)), and the
+ * Cout = 64 transposed conv / conv data gradient whose fused LeakyReLU backward (cgan/models.py:60,241 under autograd) reads those
+ * bits instead of the activation tensor (8 instead of 128 bytes per output pixel in the epilogue). */
+int b2c_first_fprop_bits(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,
+                         const float* w, const float* inv_sigma, const float* bias, void* y, int N, int H, int W,
+                         float slope, unsigned long long* sign_bits, void* stream);
+int b2c_convt4s2_signbits_bf16(const void* x, long long ldx, const void* wpack_t, const float* scale, void* y, long long ldy,
+                               const unsigned long long* act_bits, float slope, int N, int H, int W, int Cin, int Cout,
+                               void* stream);
 int b2c_first_dgrad(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1, void* ws, int N,
                     int H, int W, void* stream); /* ws: >= 36864 bytes of scratch for the packed tap weights */
 int b2c_first_wgrad(const float* a0, const float* a1, const float* b0, const float* b1, const float* alpha,

@@ -184,6 +184,14 @@ def test_convt64_fused_lrelu_backward(L):
     torch.cuda.synchronize()
     ref = F.conv_transpose2d(x, q(w), None, 2, 1) * torch.where(act > 0, 1.0, 0.2)
     assert rel(nchw(y), ref) < 1e-2
+    # the same from the activation's SIGN BITS (one 64-bit word per output pixel): bit-identical output
+    pos = (act.permute(0, 2, 3, 1) > 0).to(torch.int64)  # (N, 2H, 2W, 64)
+    sh = torch.arange(64, dtype=torch.int64)
+    bits = (pos << sh).sum(-1)  # bit 63 wraps into the sign bit of int64: the same 64-bit pattern
+    y2 = torch.empty_like(y)
+    L.call("b2c_convt4s2_signbits_bf16", nhwc(x), Cin, wp, None, y2, Cout, bits.contiguous().cuda(), 0.2, N, H, W, Cin, Cout)
+    torch.cuda.synchronize()
+    assert torch.equal(y2, y)
 
 
 def test_conv_dgrad_is_convt(L):
@@ -262,6 +270,13 @@ def test_first_layer(L, cin, N, S, interp):
     xi = q(al * x + (1 - al) * xb) if interp else q(x)
     ref = F.leaky_relu(F.conv2d(xi, q(w * 0.5), b, 2, 1), 0.2)
     assert rel(nchw(y), ref) < 5e-3
+    # the variant that also leaves the sign bits of its output (input of the fused LeakyReLU backward one layer up)
+    y2 = torch.empty_like(y)
+    bits = torch.zeros(N * (S // 2) * (S // 2), dtype=torch.int64, device="cuda")
+    L.call("b2c_first_fprop_bits", a0, a1, b0, b1, al_d, w.cuda(), sig.cuda()[1:], b.cuda(), y2, N, S, S, 0.2, bits)
+    assert torch.equal(y2, y)
+    want = ((y.float().reshape(-1, 64) > 0).to(torch.int64) << torch.arange(64, dtype=torch.int64, device="cuda")).sum(-1)
+    assert torch.equal(bits, want)
     gz = q(torch.randn(N, 64, S // 2, S // 2, generator=g))
     gx0 = torch.empty(N, 3, S, S, device="cuda")
     gx1 = torch.empty(N, 3, S, S, device="cuda") if cin == 6 else None
