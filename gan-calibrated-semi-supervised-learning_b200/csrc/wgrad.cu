@@ -148,13 +148,18 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
       const int a = a0 + q * 32 + lane;
       mbar_wait(tmem_full, 0);
       tc_fence_after();
+      // The split-K CTAs of a tile finish together and flush to the SAME addresses: each starts its sweep over (tap, 16-column
+      // chunk) at a different position, so concurrent atomics spread over the L2 instead of queueing on one line after another
+      constexpr int CHUNKS = (TPC / 2) * (NB / 16);
+      const int rot = p.slab ? 0 : (int)((blockIdx.y * 5u) % CHUNKS);
 #pragma unroll 1
-      for (int tt = ((warp - 2) >> 2) * (TPC / 2); tt < (((warp - 2) >> 2) + 1) * (TPC / 2); ++tt) {  // 2 warps per lane quarter
+      for (int ci = 0; ci < CHUNKS; ++ci) {
+        const int cr = (ci + rot) % CHUNKS;
+        const int tt = ((warp - 2) >> 2) * (TPC / 2) + cr / (NB / 16), c0 = (cr % (NB / 16)) * 16;  // 2 warps per lane quarter
         if (p.k3 && tap0 + tt >= 9) continue;  // dead taps of the last group (their columns hold products of stale shared memory)
         const bool row_ok = a < p.Cs;          // Cs = 64: rows 64..127 are the zero-filled half of the `small` box
         float* dst = p.ws + (long long)blockIdx.y * p.slab + ((long long)(tap0 + tt) * p.Cs + a) * p.Cl + b0;
-#pragma unroll 1
-        for (int c0 = 0; c0 < NB; c0 += 16) {
+        {
           uint32_t v[16];
           tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + tt * NB + c0, v);
           tmem_ld_wait();
@@ -285,11 +290,14 @@ __global__ void __launch_bounds__(320, 1) wgrad_pair_kernel(const __grid_constan
     const int a = a0 + q * 32 + lane;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
+    constexpr int CHUNKS = (TPC / 2) * (NB / 16);
+    const int rot = p.slab ? 0 : (int)((blockIdx.y * 5u) % CHUNKS);  // see wgrad_kernel
 #pragma unroll 1
-    for (int tt = ((warp - 2) >> 2) * (TPC / 2); tt < (((warp - 2) >> 2) + 1) * (TPC / 2); ++tt) {  // 2 warps per lane quarter
+    for (int ci = 0; ci < CHUNKS; ++ci) {
+      const int cr = (ci + rot) % CHUNKS;
+      const int tt = ((warp - 2) >> 2) * (TPC / 2) + cr / (NB / 16), c0 = (cr % (NB / 16)) * 16;  // 2 warps per lane quarter
       float* dst = p.ws + (long long)blockIdx.y * p.slab + ((long long)(tap0 + tt) * p.Cs + a) * p.Cl + b0;
-#pragma unroll 1
-      for (int c0 = 0; c0 < NB; c0 += 16) {
+      {
         uint32_t v[16];
         tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + tt * NB + c0, v);
         tmem_ld_wait();
