@@ -201,7 +201,7 @@ def roofline_blocks(fam, bwfam, ms_step):
         total_ms = sum(f["ms_per_step"] for f in fam.values())
         total_tf = sum(f["tflops"] * f["ms_per_step"] for f in fam.values()) / total_ms if total_ms else 0.0
         traffic = None  # ncu dram__bytes_read+write per launch of the dominant family (one --set full capture of a step)
-        for tfn in ("r02_traffic.json", "r01_traffic.json"):
+        for tfn in ("r02f_traffic.json", "r02_traffic.json", "r01_traffic.json"):
             tf = ROOT / "profiles" / tfn
             if tf.exists():
                 traffic = json.loads(tf.read_text()).get(dom, {}).get("dram_bytes_per_launch")

@@ -39,7 +39,7 @@ def val(row, key):
 def family(name, grid):
     if "convt64" in name:
         return "b2c_convt4s2_bf16"
-    if "wgrad_kernel" in name:
+    if "wgrad_kernel" in name or "wgrad_pair_kernel" in name:
         return "b2c_wgrad4s2_bf16"
     if "tapgemm_kernel<(int)32" in name or "tapgemm_kernel<32" in name:
         return "b2c_first_dgrad"
