@@ -1044,3 +1044,225 @@ extern "C" int b2c_first_wgrad(const float* a0, const float* a1, const float* b0
   if (alpha) return launch_first_wgrad<3, true>(in, tmG, dw, db, scale, wdot, part, N, H, W, (unsigned)blocks, st);
   return launch_first_wgrad<3, false>(in, tmG, dw, db, scale, wdot, part, N, H, W, (unsigned)blocks, st);
 }
+
+// ================================================================================================ first-layer DATA gradient
+// gx[n,c,Y,X] = sum_{co,ky,kx : 2oy+ky-1 = Y, 2ox+kx-1 = X} gz[n,oy,ox,co] * w[co][c][ky][kx]   (needed only under the gradient
+// penalty: d D(x_hat) / d x_hat, cgan/losses.py:213-220).  tapgemm.cu mode D1 computes it as four parity GEMMs over NINE
+// tap-shifted boxes of gz: 1.2 GB through the L2 for 134 MB of input (142 us, 25 % of HBM).  Here the shifts move to the
+// OUTPUT side: one GEMM  P[pixel][(c,ky,kx)] = gz[pixel][co] . Wd[co][(c,ky,kx)]  (M = pixels, N = 16*Cin, K = 64) over a
+// tile of 8 x 16 gz pixels plus a one-pixel halo (ONE TMA box of 10 x 18 pixels, zero-filled outside the image), P parked in
+// shared memory as fp32, and every output pixel of the tile's 16 x 32 block is the sum of its four (pixel, tap) entries,
+// written as coalesced fp32 rows of the caller's NCHW tensors.  gz crosses the L2 1.4 times instead of 9.
+namespace fd2 {
+constexpr int TH = 8, TW = 16, HR = TH + 2, HC = TW + 2, NPIX = HR * HC;  // 180 halo pixels, rows 180..255 of A are never read
+constexpr int A_BYTES = 256 * 128;       // two M = 128 tiles of [pixel][64 co] bf16
+constexpr int PSTR = 100;                // floats per pixel row of P (96 used; 100 keeps float4 stores conflict-free)
+constexpr int P_FLOATS = NPIX * PSTR;    // P is double-buffered: the output pass of tile i overlaps the TMEM pass of tile i + 1
+constexpr int THREADS = 448;             // warp 0: TMA producer, 1: MMA, 2-5: TMEM -> P (one per lane quarter), 6-13: P -> output rows
+constexpr int SMEM = 2 * A_BYTES + 96 * 128 + 2 * P_FLOATS * 4 + 256 + 1024;
+// Measured at (64, 256, 256): 86 us (tapgemm mode D1: 142 us).  What did not help: 8 instead of 4 TMEM-pass warps, two TMEM
+// accumulator sets, a 6-stage ring of 4 x 16 tiles (100 us: the per-tile hand-offs TMA -> MMA -> P -> rows cost more than the
+// larger halo saves).
+}  // namespace fd2
+
+template <int CIN>
+__global__ void __launch_bounds__(fd2::THREADS, 1) first_dgrad2_kernel(const __grid_constant__ CUtensorMap tmG,
+                                                                     const float* __restrict__ w, const float* __restrict__ inv_sigma,
+                                                                     float* __restrict__ gx0, float* __restrict__ gx1, int N, int Ho,
+                                                                     int Wo, int ntiles) {
+  using namespace fd2;
+  constexpr int NCOL = 16 * CIN;  // 48 / 96
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;                                        // [2 stages][256 rows][128 B], 128B-swizzled by TMA
+  uint8_t* sB = sA + 2 * A_BYTES;                            // [NCOL rows (c,ky,kx)][64 co] bf16, K-major, 128B-swizzled
+  float* Pbuf = reinterpret_cast<float*>(sB + 96 * 128);     // [2][NPIX][PSTR]
+  uint64_t* full = reinterpret_cast<uint64_t*>(Pbuf + 2 * P_FLOATS);
+  uint64_t* empty = full + 2;
+  uint64_t* tmem_full = empty + 2;
+  uint64_t* tmem_empty = tmem_full + 1;
+  uint64_t* p_full = tmem_empty + 1;   // [2]
+  uint64_t* p_empty = p_full + 2;      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_empty + 2);
+
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int tiles_x = Wo / TW, tiles_y = Ho / TH;
+
+  if (t == 0) {
+    tma_prefetch_desc(&tmG);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    mbar_init(tmem_empty, 4);  // one arrival per TMEM-pass warp
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&p_full[b], 4);
+      mbar_init(&p_empty[b], 8);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<256>(tmem_slot);
+  // Wd[j = (c*4 + ky)*4 + kx][co] = bf16(w[co][c][ky][kx]): one 16-byte chunk (8 co) per thread and step
+  for (int i = t; i < NCOL * 8; i += THREADS) {
+    const int j = i >> 3, kc = i & 7;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = __ldg(w + (long long)(kc * 8 + e) * NCOL + j);
+    *reinterpret_cast<uint4*>(sB + (j >> 3) * 1024 + (j & 7) * 128 + ((kc ^ (j & 7)) << 4)) =
+        make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0, use = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int tx = tile % tiles_x, ty = (tile / tiles_x) % tiles_y, n = tile / (tiles_x * tiles_y);
+        if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
+        mbar_expect_tx(&full[s], NPIX * 128);
+        tma_load_4d(sA + s * A_BYTES, &tmG, &full[s], 0, tx * TW - 1, ty * TH - 1, n);
+        if (++s == 2) { s = 0; ++use; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, NCOL, 0, 0);
+      constexpr uint32_t DHI = umma_desc_hi_sw128(1024);
+      const uint32_t a_lo0 = umma_desc_lo(smem_u32(sA), 16), b_lo = umma_desc_lo(smem_u32(sB), 16);
+      int s = 0, ph = 0, it = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        if (it > 0) mbar_wait(tmem_empty, (it - 1) & 1);  // the previous P has been moved out of TMEM
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t alo = a_lo0 + s * (A_BYTES >> 4);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(tmem_base + mt * 128, umma_desc_join(DHI, alo + mt * (16384 >> 4) + 2 * k), umma_desc_join(DHI, b_lo + 2 * k),
+                      idesc, (uint32_t)(k != 0));
+        umma_commit(&empty[s]);
+        umma_commit(tmem_full);
+        if (++s == 2) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp < 6) {
+    // ---- pass 1 warps: P (both M tiles of this warp's TMEM lane quarter) from TMEM to shared memory
+    const int q = warp & 3;
+    const float sc = inv_sigma ? __ldg(inv_sigma) : 1.f;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      float* P = Pbuf + (it & 1) * P_FLOATS;
+      if (it >= 2) mbar_wait(&p_empty[it & 1], ((it >> 1) - 1) & 1);  // the output pass of tile it - 2 has read this buffer
+      mbar_wait(tmem_full, it & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        const int r = mt * 128 + q * 32 + lane;  // halo pixel
+#pragma unroll
+        for (int c0 = 0; c0 < NCOL; c0 += 48) {
+          uint32_t v[3][16];
+#pragma unroll
+          for (int u = 0; u < 3; ++u) tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + mt * 128 + c0 + 16 * u, v[u]);
+          tmem_ld_wait();
+          if (r < NPIX) {
+#pragma unroll
+            for (int u = 0; u < 3; ++u) {
+              float4* d = reinterpret_cast<float4*>(P + r * PSTR + c0 + 16 * u);
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj)
+                d[jj] = make_float4(__uint_as_float(v[u][4 * jj]) * sc, __uint_as_float(v[u][4 * jj + 1]) * sc,
+                                    __uint_as_float(v[u][4 * jj + 2]) * sc, __uint_as_float(v[u][4 * jj + 3]) * sc);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(tmem_empty);
+        mbar_arrive(&p_full[it & 1]);
+      }
+    }
+  } else {
+    // ---- pass 2 warps: output rows.  Lane = output column X of the tile's 32; warp ew owns rows yl = ew and ew + 8 of every
+    // channel.  Y + 1 = 2 oy + ky has the two solutions (oy1 = (Y+1) >> 1, ky1 = (Y+1) & 1) and (oy1 - 1, ky1 + 2); same along X.
+    const int ew = warp - 6;
+    const int H = 2 * Ho, W = 2 * Wo;
+    const int hc1 = ((lane + 1) >> 1) + 1, kx1 = (lane + 1) & 1;  // halo column / tap of the first solution
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const int tx = tile % tiles_x, ty = (tile / tiles_x) % tiles_y, n = tile / (tiles_x * tiles_y);
+      const float* pl = Pbuf + (it & 1) * P_FLOATS + hc1 * PSTR + kx1;
+      mbar_wait(&p_full[it & 1], (it >> 1) & 1);
+#pragma unroll
+      for (int cg = 0; cg < CIN; cg += 3) {  // all loads of a group of 3 channels are issued before the sums
+        float a[6][4];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+          const int c = cg + (i >> 1), yl = ew + 8 * (i & 1);
+          const int hr1 = ((yl + 1) >> 1) + 1, ky1 = (yl + 1) & 1;
+          const float* p11 = pl + hr1 * HC * PSTR + c * 16 + ky1 * 4;
+          a[i][0] = p11[0]; a[i][1] = p11[-PSTR + 2]; a[i][2] = p11[-HC * PSTR + 8]; a[i][3] = p11[-HC * PSTR - PSTR + 10];
+        }
+        if (cg + 3 >= CIN) {  // last reads of this buffer
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&p_empty[it & 1]);
+        }
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+          const int c = cg + (i >> 1), yl = ew + 8 * (i & 1);
+          float* plane = (c < 3 ? gx0 : gx1) + ((long long)n * 3 + (c % 3)) * H * W;
+          plane[(long long)(2 * ty * TH + yl) * W + 2 * tx * TW + lane] = (a[i][0] + a[i][1]) + (a[i][2] + a[i][3]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<256>(tmem_base);
+}
+
+static int launch_first_dgrad2(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1, int N, int Ho, int Wo,
+                               cudaStream_t st) {
+  CUtensorMap tmG;
+  {
+    uint64_t dims[4] = {64, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)N};
+    uint64_t str[3] = {128, (uint64_t)128 * Wo, (uint64_t)128 * Wo * Ho};
+    uint32_t box[4] = {64, (uint32_t)fd2::HC, (uint32_t)fd2::HR, 1};
+    if (int rc = b2c_make_tmap_bf16(&tmG, gz, 4, dims, str, box)) return rc;
+  }
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(first_dgrad2_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, fd2::SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(first_dgrad2_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, fd2::SMEM);
+    if (e != cudaSuccess) { b2c_set_error("cudaFuncSetAttribute(first_dgrad2): %s", cudaGetErrorString(e)); return B2C_ERR_CUDA; }
+    attr_done = true;
+  }
+  const long long ntiles = (long long)N * (Ho / fd2::TH) * (Wo / fd2::TW);
+  const unsigned blocks = (unsigned)(ntiles < 148 ? ntiles : 148);
+  if (gx1) first_dgrad2_kernel<6><<<blocks, fd2::THREADS, fd2::SMEM, st>>>(tmG, w, inv_sigma, gx0, gx1, N, Ho, Wo, (int)ntiles);
+  else first_dgrad2_kernel<3><<<blocks, fd2::THREADS, fd2::SMEM, st>>>(tmG, w, inv_sigma, gx0, gx1, N, Ho, Wo, (int)ntiles);
+  return b2c_check_launch("first_dgrad2");
+}
+
+// Called by b2c_first_dgrad (tapgemm.cu).  Returns B2C_OK with *done = false when the shape does not fit this kernel.
+int b2c_first_dgrad2(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1, int N, int H, int W,
+                     void* stream, bool* done) {
+  static int enabled = -1;
+  if (enabled < 0) {
+    const char* e = getenv("B2C_FIRST_DGRAD2");
+    enabled = (e && e[0] == '0') ? 0 : 1;
+  }
+  *done = false;
+  const int Ho = H / 2, Wo = W / 2;
+  if (!enabled || Ho % fd2::TH || Wo % fd2::TW || ((uintptr_t)gz & 15) || (long long)N * (Ho / fd2::TH) * (Wo / fd2::TW) >= (1ll << 31))
+    return B2C_OK;
+  *done = true;
+  return launch_first_dgrad2(gz, w, inv_sigma, gx0, gx1, N, Ho, Wo, (cudaStream_t)stream);
+}

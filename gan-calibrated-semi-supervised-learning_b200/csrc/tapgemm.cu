@@ -864,12 +864,19 @@ __global__ void pack_w_d1_kernel(const float* __restrict__ w, const float* __res
   out[i] = __float2bfloat16(v);
 }
 
+int b2c_first_dgrad2(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1, int N, int H, int W,
+                     void* stream, bool* done);  // first.cu
 // gz: dense (N,H/2,W/2,64) bf16; gx0/gx1: fp32 (N,3,H,W) (gx1 null => Cin = 3); ws: >= 36864 bytes, 16-byte aligned.
 extern "C" int b2c_first_dgrad(const void* gz, const float* w, const float* inv_sigma, float* gx0, float* gx1,
                                void* ws, int N, int H, int W, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   B2C_REQUIRE(H % 2 == 0 && W % 2 == 0, "first_dgrad: odd size %dx%d", H, W);
   B2C_REQUIRE(ws && ((uintptr_t)ws & 15) == 0, "first_dgrad: workspace missing or unaligned");
+  {
+    bool done = false;  // first.cu: one GEMM over a halo tile, taps resolved on the output side (patches >= 32 x 64)
+    const int rc2 = b2c_first_dgrad2(gz, w, inv_sigma, gx0, gx1, N, H, W, stream, &done);
+    if (rc2 || done) return rc2;
+  }
   TapGemmParams p;
   p.mode = 2; p.N = N; p.Cin = 64; p.Cout = 32; p.kchunks = 1;
   p.y = nullptr; p.ldy = 0; p.bias = nullptr; p.scale = inv_sigma; p.gx0 = gx0; p.gx1 = gx1; p.stats = nullptr; p.f32out = 0; p.st256 = 0;
