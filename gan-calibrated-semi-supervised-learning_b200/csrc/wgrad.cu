@@ -43,7 +43,7 @@ struct WgradCfg {
 };
 
 template <int NB>
-__global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUtensorMap tmS,
+__global__ void __launch_bounds__(352) wgrad_kernel(const __grid_constant__ CUtensorMap tmS,
                                                     const __grid_constant__ CUtensorMap tmL, WgradParams p) {
   using Cfg = WgradCfg<NB>;
   constexpr int STAGES = Cfg::STAGES, TPC = Cfg::TPC;
@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
     tma_prefetch_desc(&tmS);
     tma_prefetch_desc(&tmL);
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&full[s], 1);
+      mbar_init(&full[s], 2);  // two producer threads (warps 0 and 10) split the stage's TMA loads
       mbar_init(&empty[s], 1);
     }
     mbar_init(tmem_full, 1);
@@ -84,7 +84,10 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
   const uint32_t tmem_base = *tmem_slot;
 
   if (niters > 0) {
-    if (warp == 0) {
+    if (warp == 0 || warp == 10) {
+      // A stage is 2 + TPC small boxes (4-8 KB each): one issuing thread needs about as long per stage as the MMAs take, so
+      // two threads share it - warp 0: the `small` boxes and the first half of the taps, warp 10: the second half.
+      const int half = warp == 10;
       if (elect_one()) {
         int stage = 0, phase = 0;
         int tx = c_begin % p.tiles_x, ty = (c_begin / p.tiles_x) % p.tiles_y, tn = c_begin / (p.tiles_x * p.tiles_y);
@@ -93,13 +96,18 @@ __global__ void __launch_bounds__(320) wgrad_kernel(const __grid_constant__ CUte
           if (++tx == p.tiles_x) { tx = 0; if (++ty == p.tiles_y) { ty = 0; ++tn; } }
           mbar_wait(&empty[stage], phase ^ 1);
           const int live = p.k3 ? (9 - tap0 < TPC ? 9 - tap0 : TPC) : TPC;  // taps of this CTA that exist
-          mbar_expect_tx(&full[stage], Cfg::A_BYTES + live * Cfg::B_TAP_BYTES);
+          const int t_lo = half ? TPC / 2 : 0, t_hi = half ? TPC : TPC / 2;
+          const int mine = (live < t_hi ? live : t_hi) - t_lo;  // live taps in this thread's half (may be <= 0)
+          mbar_expect_tx(&full[stage], (half ? 0 : Cfg::A_BYTES) + (mine > 0 ? mine : 0) * Cfg::B_TAP_BYTES);
           uint8_t* dA = sA + stage * Cfg::A_BYTES;
           uint8_t* dB = sB + stage * Cfg::B_BYTES;
-          tma_load_4d(dA, &tmS, &full[stage], a0, x0, y0, n0);
-          tma_load_4d(dA + Cfg::BOX_BYTES, &tmS, &full[stage], a0 + 64, x0, y0, n0);
+          if (!half) {
+            tma_load_4d(dA, &tmS, &full[stage], a0, x0, y0, n0);
+            tma_load_4d(dA + Cfg::BOX_BYTES, &tmS, &full[stage], a0 + 64, x0, y0, n0);
+          }
 #pragma unroll
           for (int tt = 0; tt < TPC; ++tt) {
+            if (tt < t_lo || tt >= t_hi) continue;
             if (p.k3) {
               if (tt < live) {
                 const int ky = (tap0 + tt) / 3, kx = (tap0 + tt) % 3;
@@ -378,7 +386,7 @@ static int launch_wgrad(const CUtensorMap& tmS, const CUtensorMap& tmL, const Wg
     }
     attr_done = true;
   }
-  wgrad_kernel<NB><<<grid, 320, WgradCfg<NB>::SMEM, st>>>(tmS, tmL, p);
+  wgrad_kernel<NB><<<grid, 352, WgradCfg<NB>::SMEM, st>>>(tmS, tmL, p);
   return b2c_check_launch("wgrad_kernel");
 }
 
