@@ -69,7 +69,7 @@ __device__ __forceinline__ int axis_pairs(int d, int (&par)[2], int (&tap)[2]) {
 // MMAs instead of being paid once per 32-channel chunk.
 // ACT: 0 = none, 1 = activation tensor `act`, 2 = its sign bits `act_bits` (8 bytes instead of 128 per output pixel).
 template <int ACT, bool MERGE>
-__global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__ CUtensorMap tmA,
+__global__ void __launch_bounds__(352, 1) convt64_kernel(const __grid_constant__ CUtensorMap tmA,
                                                          const __grid_constant__ CUtensorMap tmB, ConvT64Params p,
                                                          int ntiles) {
   extern __shared__ uint8_t smem_raw[];
@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 4);  // one arrival per epilogue warp
+      mbar_init(&tmem_empty[s], 8);  // one arrival per epilogue warp
     }
     fence_barrier_init();
   }
@@ -226,7 +226,11 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
       }
     }
   } else {
+    // EIGHT epilogue warps (2-5 and 7-10), two per TMEM lane quarter: with four, one warp per scheduler had ~1600 (2100 with the
+    // fused LeakyReLU backward) dependent instructions per tile against ~4100 cycles of MMAs - the epilogue, not the tensor pipe,
+    // set the pace (38 % tensor-pipe active with the sign-bit variant).  The two warps of a quarter take 32 channels each.
     const int q = warp & 3;  // TMEM lane quarter this warp may read
+    const int c0 = warp >= 7 ? 32 : 0;
     const int r = q * 32 + lane;
     const int bw = r % p.BW, bh = (r / p.BW) % p.BH, bi = r / (p.BW * p.BH);
     const int Ho = 2 * p.H, Wo = 2 * p.W;
@@ -239,7 +243,7 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
       const bool valid = n < p.N;
       const int buf = lt & 1;
       const uint32_t acc = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
-      uint32_t am[ACT == 1 ? 4 : 1][ACT == 1 ? 32 : 1];
+      uint32_t am[ACT == 1 ? 4 : 1][ACT == 1 ? 16 : 1];  // this warp's 32 channels of the 4 parity pixels
       uint2 ab[ACT == 2 ? 4 : 1];
       if (ACT == 2 && valid) {
 #pragma unroll
@@ -254,13 +258,12 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
           const int oy = 2 * (y0 + bh) + (parity >> 1), ox = 2 * (x0 + bw) + (parity & 1);
           const __nv_bfloat16* a = p.act + (((long long)n * Ho + oy) * Wo + ox) * 64;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) ld_global_nc_v8(a + 16 * j, &am[ACT == 1 ? parity : 0][ACT == 1 ? 8 * j : 0]);
+          for (int j = 0; j < 2; ++j) ld_global_nc_v8(a + c0 + 16 * j, &am[ACT == 1 ? parity : 0][ACT == 1 ? 8 * j : 0]);
         }
       }
       mbar_wait(&tmem_full[buf], (lt >> 1) & 1);
       tc_fence_after();
-#pragma unroll(ACT ? 2 : 1)
-      for (int c0 = 0; c0 < 64; c0 += 32) {
+      {
         float f[32], sq[32];  // per-channel partial statistics of this pixel over the 4 parities
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = sq[j] = 0.f;
@@ -272,7 +275,7 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
           tmem_ld16(acc + parity * 64 + c0, v0);
           tmem_ld16(acc + parity * 64 + c0 + 16, v1);
           tmem_ld_wait();
-          if (c0 == 32 && parity == 3) {  // last read of this accumulator set: hand it back to the MMA warp
+          if (parity == 3) {  // this warp's last read of the accumulator set: hand it back to the MMA warp
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty[buf]);
@@ -295,7 +298,7 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
           if (ACT == 1 && valid) {  // fused LeakyReLU backward: scale by the slope where the forward activation was <= 0
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-              const float2 t = unpack_bf16(am[ACT == 1 ? parity : 0][ACT == 1 ? c0 / 2 + i : 0]);
+              const float2 t = unpack_bf16(am[ACT == 1 ? parity : 0][ACT == 1 ? i : 0]);
               uint32_t* v = i < 8 ? v0 : v1;
               const int i0 = (2 * i) & 15;
               if (!(t.x > 0.f)) v[i0] = __float_as_uint(__uint_as_float(v[i0]) * p.slope);
@@ -344,14 +347,14 @@ __global__ void __launch_bounds__(224, 1) convt64_kernel(const __grid_constant__
         }
       }
       if (!ACT && p.stats) {  // combine the 4 epilogue warps, then one atomic per (channel, statistic) and tile
-        named_bar_sync(1, 128);
-        if (r < 64) {
+        named_bar_sync(1, 256);
+        if (warp < 7 && r < 64) {
           const float2 a = red[r], b = red[64 + r], c = red[128 + r], d = red[192 + r];
           long long* st = p.stats + ((long long)n0 * 64 + r) * 2;
           stat_add(st, (a.x + b.x) + (c.x + d.x));
           stat_add(st + 1, (a.y + b.y) + (c.y + d.y));
         }
-        named_bar_sync(1, 128);  // scratch may be overwritten by the next tile
+        named_bar_sync(1, 256);  // scratch may be overwritten by the next tile
       }
     }
   }
@@ -430,13 +433,13 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const flo
   const int ctas = ntiles < sms ? ntiles : sms;
   const cudaStream_t st = (cudaStream_t)stream;
   if (merge) {
-    if (act_bits) convt64_kernel<2, true><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
-    else if (act) convt64_kernel<1, true><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
-    else convt64_kernel<0, true><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    if (act_bits) convt64_kernel<2, true><<<ctas, 352, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    else if (act) convt64_kernel<1, true><<<ctas, 352, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    else convt64_kernel<0, true><<<ctas, 352, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
   } else {
-    if (act_bits) convt64_kernel<2, false><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
-    else if (act) convt64_kernel<1, false><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
-    else convt64_kernel<0, false><<<ctas, 224, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    if (act_bits) convt64_kernel<2, false><<<ctas, 352, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    else if (act) convt64_kernel<1, false><<<ctas, 352, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
+    else convt64_kernel<0, false><<<ctas, 352, CT_SMEM, st>>>(tmA, tmB, p, ntiles);
   }
   int rc = b2c_check_launch("convt64_kernel");
   if (rc == 0 && stats && !fuse_stats) rc = b2c_in_stats(y, ldy, stats, N, 4 * H * W, 64, stream);
