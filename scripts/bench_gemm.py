@@ -37,6 +37,13 @@ if which in ("convt", "all"):
         t = timeit(lambda: L.call("b2c_convt4s2_bf16", x, Cin, w, None, None, y, Cout, None, None, 1.0, B, H, W, Cin, Cout))
         fl = 2.0 * B * H * W * Cout * 16 * Cin
         print(f"convt4s2 ({B},{H},{W},{Cin},{Cout}): {t*1e3:8.1f} us {fl/t/1e9:7.0f} TFLOP/s")
+        if Cout == 64:  # the fused LeakyReLU backward: from the activation tensor / from its sign bits
+            act = bf(B, 2 * H, 2 * W, Cout)
+            bits = torch.randint(-2**62, 2**62, (B * 4 * H * W,), dtype=torch.int64, device="cuda")
+            t = timeit(lambda: L.call("b2c_convt4s2_bf16", x, Cin, w, None, None, y, Cout, None, act, 0.2, B, H, W, Cin, Cout))
+            print(f"  + act tensor                   : {t*1e3:8.1f} us {fl/t/1e9:7.0f} TFLOP/s")
+            t = timeit(lambda: L.call("b2c_convt4s2_signbits_bf16", x, Cin, w, None, y, Cout, bits, 0.2, B, H, W, Cin, Cout))
+            print(f"  + sign bits                    : {t*1e3:8.1f} us {fl/t/1e9:7.0f} TFLOP/s")
 if which in ("wgrad", "all"):
     for Hs, Ws, Cs, Cl in WGRAD:
         sm, lg = bf(B, Hs, Ws, Cs), bf(B, 2 * Hs, 2 * Ws, Cl)

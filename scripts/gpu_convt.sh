@@ -1,5 +1,5 @@
 #!/bin/bash
 mkdir -p gpurun_out
 export PYTHONUNBUFFERED=1
-timeout 600 python -m pytest tests/test_kernels_gpu.py -x -q -k "convt or conv4s2 or fp32_check or fused_lrelu" > gpurun_out/t_convt.log 2>&1; echo "rc=$?"; tail -3 gpurun_out/t_convt.log
-timeout 300 python scripts/bench_gemm.py convt 5 > gpurun_out/convt.txt 2>&1; cat gpurun_out/convt.txt
+{ echo "== 8 epilogue warps"; timeout 300 python scripts/bench_gemm.py convt 5
+  echo "== 4 epilogue warps (previous build)"; cp gan-calibrated-semi-supervised-learning_b200/b200cgan/libb2c.so /tmp/new.so; cp scripts/probe/libb2c_old4w.so gan-calibrated-semi-supervised-learning_b200/b200cgan/libb2c.so; timeout 300 python scripts/bench_gemm.py convt 5; cp /tmp/new.so gan-calibrated-semi-supervised-learning_b200/b200cgan/libb2c.so; } > gpurun_out/convt.txt 2>&1; cat gpurun_out/convt.txt
