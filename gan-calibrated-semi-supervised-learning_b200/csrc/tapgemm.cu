@@ -468,7 +468,7 @@ template <int BN>
 struct TapGemmP2Cfg {
   static constexpr int A_BYTES = 128 * 128;
   static constexpr int B_BYTES = (BN / 2) * 128;     // this CTA's half of the weight slice
-  static constexpr int STAGES = (192 * 1024) / (A_BYTES + B_BYTES);
+  static constexpr int STAGES = (216 * 1024) / (A_BYTES + B_BYTES);  // 9 (BN = 128) / 6 (BN = 256): all the shared memory there is
   static constexpr int RED_BYTES = 4 * BN * 8;
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + RED_BYTES + 1024 + 1024;
 };
