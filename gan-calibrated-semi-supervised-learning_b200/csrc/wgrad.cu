@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(352) wgrad_kernel(const __grid_constant__ CUte
 // and the ring deepens from 5 to 8 stages).  Protocol as in tapgemm_pair_kernel: both CTAs' TMA loads complete on the
 // LEADER's mbarrier (cta_group::2 TMA), the leader's elected thread issues the MMAs, its commits are multicast to both CTAs.
 struct WgradP2Cfg {
-  static constexpr int NB = 128, TPC = 4, STAGES = 8, PIX = 32;
+  static constexpr int NB = 128, TPC = 4, STAGES = 9, PIX = 32;
   static constexpr int BOX_BYTES = PIX * 128;
   static constexpr int A_BYTES = 2 * BOX_BYTES;              // this CTA's 128 channels of `small`
   static constexpr int B_TAP_BYTES = 2 * BOX_BYTES;          // 128 channels of `large` for one tap
