@@ -377,9 +377,10 @@ int b2c_run_convt64(const void* x, long long ldx, const void* wpack_t, const flo
   p.act = (const __nv_bfloat16*)act; p.act_bits = act_bits; p.slope = slope; p.scale = scale;
   p.st256 = (((uintptr_t)y & 31) == 0 && ldy % 16 == 0) ? 1 : 0;
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.kchunks = Cin / 64; p.y = (__nv_bfloat16*)y; p.ldy = ldy;
-  p.BW = W < 128 ? W : 128;
+  const int lw = W & -W, lh = H & -H;  // largest powers of two dividing the extents (tapgemm.cu pick_box)
+  p.BW = lw < 128 ? lw : 128;
   int rem = 128 / p.BW;
-  p.BH = H < rem ? H : rem;
+  p.BH = lh < rem ? lh : rem;
   p.BI = rem / p.BH;
   B2C_REQUIRE(p.BW * p.BH * p.BI == 128 && p.BI <= 256, "convt64: unsupported spatial size %dx%d", H, W);
   p.tiles_x = W / p.BW; p.tiles_y = H / p.BH;

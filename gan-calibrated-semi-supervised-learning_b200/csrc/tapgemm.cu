@@ -666,14 +666,16 @@ __global__ void __launch_bounds__(192, 1) tapgemm_pair_kernel(const __grid_const
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-static bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
-// Pixel box for a 128-row tile over a (TH x TW) tile space: widest row run first, then rows, then images.
+// Pixel box for a 128-row tile over a (TH x TW) tile space: widest row run first, then rows, then images.  The box sides are
+// the largest powers of two that DIVIDE the extents, so any size works (the reference CLI takes any --img_size that is a
+// multiple of 16, cgan/cgan_train_enhanced.py:147): 96 -> 48 x 48 maps -> 16 x 8 boxes, 3 x 3 maps -> 1 x 1 x 128 images.
 static int pick_box(int TH, int TW, int rows, int* BW, int* BH, int* BI) {
-  if (!is_pow2(TH) || !is_pow2(TW)) return 0;
-  *BW = TW < rows ? TW : rows;
+  if (TH <= 0 || TW <= 0) return 0;
+  const int lw = TW & -TW, lh = TH & -TH;
+  *BW = lw < rows ? lw : rows;
   int rem = rows / *BW;
-  *BH = TH < rem ? TH : rem;
+  *BH = lh < rem ? lh : rem;
   *BI = rem / *BH;
   return (*BW) * (*BH) * (*BI) == rows && *BI <= 256;
 }
@@ -734,7 +736,7 @@ static int run_tapgemm(int mode, const void* x, long long ldx, const void* wpack
   static const bool allow_mt2 = getenv("B2C_TAPGEMM_MT2") && getenv("B2C_TAPGEMM_MT2")[0] == '1';
   int MT = 1;
   if (allow_mt2 && BN == 256 && (long long)N * TH * TW >= 256LL * 64) MT = 2;  // measured: no gain at BN = 128
-  B2C_REQUIRE(pick_box(TH, TW, 128 * MT, &p.BW, &p.BH, &p.BI), "tapgemm: unsupported spatial size %dx%d (need powers of two)", TH, TW);
+  B2C_REQUIRE(pick_box(TH, TW, 128 * MT, &p.BW, &p.BH, &p.BI), "tapgemm: unsupported spatial size %dx%d", TH, TW);
   p.tiles_x = TW / p.BW; p.tiles_y = TH / p.BH;
   const int tiles_n = (N + p.BI - 1) / p.BI;
   int rc;
@@ -924,7 +926,7 @@ extern "C" int b2c_convt4s2_bf16(const void* x, long long ldx, const void* wpack
   static const bool merge = !(getenv("B2C_CONVT_MERGE") && getenv("B2C_CONVT_MERGE")[0] == '0');  // A/B switch for profiling
   if (g_f32_output) B2C_REQUIRE(stats == nullptr, "fp32 check mode: fused statistics are not available");
   if (Cout == 64 && bias == nullptr && merge && Cin % 64 == 0 && ldx % 8 == 0 && ldy % 8 == 0 &&
-      ((uintptr_t)y & 15) == 0 && is_pow2(H) && is_pow2(W))
+      ((uintptr_t)y & 15) == 0)
     return b2c_run_convt64(x, ldx, wpack_t, scale, y, ldy, stats, act, nullptr, slope, N, H, W, Cin, stream);
   B2C_REQUIRE(act == nullptr, "convt4s2: the fused LeakyReLU backward needs the Cout = 64 kernel (Cout=%d, bias=%p)", Cout, (const void*)bias);
   return run_tapgemm(1, x, ldx, wpack_t, scale, bias, y, ldy, stats, N, H, W, Cin, Cout, stream);
@@ -937,7 +939,7 @@ extern "C" int b2c_convt4s2_signbits_bf16(const void* x, long long ldx, const vo
                                           long long ldy, const unsigned long long* act_bits, float slope, int N, int H, int W,
                                           int Cin, int Cout, void* stream) {
   B2C_REQUIRE(act_bits != nullptr, "convt4s2_signbits: act_bits must be given");
-  B2C_REQUIRE(Cout == 64 && Cin % 64 == 0 && ldx % 8 == 0 && ldy % 8 == 0 && ((uintptr_t)y & 15) == 0 && is_pow2(H) && is_pow2(W),
-              "convt4s2_signbits: needs Cout = 64 (got %d), Cin %% 64 == 0, 16-byte aligned y, power-of-two %dx%d", Cout, H, W);
+  B2C_REQUIRE(Cout == 64 && Cin % 64 == 0 && ldx % 8 == 0 && ldy % 8 == 0 && ((uintptr_t)y & 15) == 0,
+              "convt4s2_signbits: needs Cout = 64 (got %d), Cin %% 64 == 0, 16-byte aligned y (%dx%d)", Cout, H, W);
   return b2c_run_convt64(x, ldx, wpack_t, scale, y, ldy, nullptr, nullptr, act_bits, slope, N, H, W, Cin, stream);
 }

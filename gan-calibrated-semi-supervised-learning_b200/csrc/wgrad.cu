@@ -373,7 +373,6 @@ __global__ void __launch_bounds__(256) wgrad_unpack_kernel(const float* __restri
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-static bool w_is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
 template <int NB>
 static int launch_wgrad(const CUtensorMap& tmS, const CUtensorMap& tmL, const WgradParams& p, dim3 grid, cudaStream_t st) {
@@ -393,9 +392,10 @@ static int launch_wgrad(const CUtensorMap& tmS, const CUtensorMap& tmL, const Wg
 struct WgradPlan { int BW, BH, BI, tiles_x, tiles_y, nchunks, NB, tiles, splits; };
 static WgradPlan wgrad_plan(int N, int Hs, int Ws, int Cs, int Cl, int sm_count) {
   WgradPlan q;
-  q.BW = Ws < 32 ? Ws : 32;
+  const int lw = Ws & -Ws, lh = Hs & -Hs;  // largest powers of two dividing the extents: any spatial size works
+  q.BW = lw < 32 ? lw : 32;
   int rem = 32 / q.BW;
-  q.BH = Hs < rem ? Hs : rem;
+  q.BH = lh < rem ? lh : rem;
   q.BI = rem / q.BH;
   q.tiles_x = Ws / q.BW; q.tiles_y = Hs / q.BH;
   const int tiles_n = (N + q.BI - 1) / q.BI;
@@ -439,7 +439,7 @@ extern "C" int b2c_wgrad4s2_bf16(const void* small, long long lds, const void* l
   B2C_REQUIRE(Cs % 128 == 0 && Cl % 64 == 0, "wgrad4s2: Cs=%d must be a multiple of 128, Cl=%d of 64", Cs, Cl);
   B2C_REQUIRE(ldl == Cl, "wgrad4s2: large operand must be dense NHWC (ldl=%lld, Cl=%d)", ldl, Cl);
   B2C_REQUIRE(lds % 8 == 0, "wgrad4s2: lds=%lld must be a multiple of 8", lds);
-  B2C_REQUIRE(w_is_pow2(Hs) && w_is_pow2(Ws), "wgrad4s2: unsupported spatial size %dx%d", Hs, Ws);
+  B2C_REQUIRE(Hs > 0 && Ws > 0, "wgrad4s2: unsupported spatial size %dx%d", Hs, Ws);
   B2C_REQUIRE((wdot == nullptr) == (part == nullptr), "wgrad4s2: wdot and part go together");
   const WgradPlan q = wgrad_plan(N, Hs, Ws, Cs, Cl, sm_count);
   const long long slab = (long long)16 * Cs * Cl;
@@ -553,7 +553,7 @@ extern "C" int b2c_wgrad3s1_bf16(const void* small, const void* large, float* ws
                                  int accumulate, int N, int H, int W, int Cs, int Cl, int sm_count, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   B2C_REQUIRE((Cs == 64 || Cs % 128 == 0) && Cl % 64 == 0, "wgrad3s1: Cs=%d must be 64 or a multiple of 128, Cl=%d of 64", Cs, Cl);
-  B2C_REQUIRE(w_is_pow2(H) && w_is_pow2(W), "wgrad3s1: unsupported spatial size %dx%d", H, W);
+  B2C_REQUIRE(H > 0 && W > 0, "wgrad3s1: unsupported spatial size %dx%d", H, W);
   const WgradPlan q = wgrad3_plan(N, H, W, Cs, Cl, sm_count);
   const long long slab = (long long)9 * Cs * Cl;
   B2C_REQUIRE(ws_floats >= slab, "wgrad3s1: workspace of %lld floats < %lld", ws_floats, slab);

@@ -34,7 +34,8 @@ def L():
 
 CONV_CASES = [(2, 16, 16, 64, 128), (3, 32, 32, 64, 64), (2, 8, 8, 256, 512), (1, 128, 128, 64, 128), (5, 4, 4, 128, 256),
               (2, 256, 256, 64, 64),
-              (4, 128, 128, 64, 128), (17, 64, 64, 64, 256), (65, 32, 32, 128, 128)]  # two pixel tiles per CTA (MT = 2)
+              (4, 128, 128, 64, 128), (17, 64, 64, 64, 256), (65, 32, 32, 128, 128),  # two pixel tiles per CTA (MT = 2)
+              (2, 48, 48, 64, 128), (3, 24, 24, 128, 256), (2, 12, 12, 256, 512), (5, 6, 6, 512, 512), (2, 80, 40, 64, 64)]  # not powers of two
 
 
 @pytest.mark.parametrize("N,H,W,Cin,Cout", CONV_CASES)
@@ -61,7 +62,10 @@ def test_conv4s2(L, N, H, W, Cin, Cout):
 @pytest.mark.parametrize("N,H,W,Cin,Cout", [(2, 8, 8, 128, 64), (3, 16, 16, 64, 128), (2, 4, 4, 512, 256),
                                             (1, 64, 64, 128, 64), (2, 128, 128, 128, 64), (5, 2, 2, 64, 64),
                                             (3, 32, 32, 256, 64), (130, 1, 1, 64, 64),
-                                            (16, 32, 32, 128, 128), (65, 16, 16, 64, 256)])  # MT = 2
+                                            (16, 32, 32, 128, 128), (65, 16, 16, 64, 256),  # MT = 2
+                                            # sizes that are not powers of two (img_size 96 / 160 / 192: any multiple of 16)
+                                            (2, 24, 24, 128, 64), (3, 12, 12, 256, 128), (2, 6, 6, 512, 256), (5, 3, 3, 512, 512),
+                                            (2, 40, 40, 128, 64), (1, 48, 24, 64, 64)])
 def test_convt4s2(L, N, H, W, Cin, Cout):
     g = torch.Generator().manual_seed(2)
     x = q(torch.randn(N, Cin, H, W, generator=g))
@@ -210,7 +214,9 @@ def test_conv_dgrad_is_convt(L):
 
 
 @pytest.mark.parametrize("N,Hs,Ws,Cs,Cl", [(2, 8, 8, 128, 64), (3, 16, 16, 128, 128), (2, 4, 4, 512, 256),
-                                           (1, 64, 64, 128, 64), (5, 2, 2, 256, 128), (4, 32, 32, 256, 128)])
+                                           (1, 64, 64, 128, 64), (5, 2, 2, 256, 128), (4, 32, 32, 256, 128),
+                                           (2, 24, 24, 128, 64), (3, 12, 12, 256, 128), (2, 6, 6, 512, 256), (5, 3, 3, 512, 512),
+                                           (2, 40, 20, 128, 64)])  # not powers of two
 def test_wgrad4s2(L, N, Hs, Ws, Cs, Cl):
     g = torch.Generator().manual_seed(4)
     small = q(torch.randn(N, Cs, Hs, Ws, generator=g))

@@ -1,6 +1,7 @@
 """The train step at the other BASELINE patch sizes / batch shapes, one step each against the CPU oracle on the same
 weights, inputs, dropout masks and GP alpha: configs[3] (512x512 patches, activation-heavy), the reference's own
-default img_size 128 with an odd batch, and batch 1 (every per-sample statistic degenerates to one image)."""
+default img_size 128 with an odd batch, batch 1 (every per-sample statistic degenerates to one image), and patch sizes
+that are not powers of two (96, 160, 192: the reference CLI takes any multiple of 16, cgan_train_enhanced.py:147)."""
 import pytest
 import torch
 
@@ -9,7 +10,7 @@ import cgan_oracle as O
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("B,S", [(2, 512), (5, 128), (1, 256)])
+@pytest.mark.parametrize("B,S", [(2, 512), (5, 128), (1, 256), (2, 96), (3, 160), (2, 192)])
 def test_one_step_vs_oracle(B, S):
     from b200cgan.models import Discriminator, GeneratorUNet
     from b200cgan.train_step import CGANTrainer
