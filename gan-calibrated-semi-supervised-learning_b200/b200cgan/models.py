@@ -7,7 +7,7 @@ behaviour as /root/reference/cgan/models.py:37-141,222-258:
 Constructing G then D under the same torch seed draws the same initial parameters as the reference (same tensor
 shapes initialised in the same order).  The nn.InstanceNorm2d / LeakyReLU / ReLU / Dropout entries of each
 nn.Sequential are kept as parameter-less markers (indices and printing match); the arithmetic runs fused in ops.py.
-Inputs are NCHW fp32 CUDA patches whose size is a multiple of 32; activations are channels_last bf16.
+Inputs are NCHW fp32 CUDA patches whose size is a multiple of 16; activations are channels_last bf16.
 """
 from __future__ import annotations
 

@@ -462,19 +462,21 @@ extern "C" int b2c_head_fprop(const void* a, const float* w, float* out, int N, 
 
 extern "C" int b2c_head_dgrad(const float* gy, const float* w, void* ga, int N, int h, int C, void* stream) {
   B2C_REQUIRE(C % 128 == 0 && (size_t)16 * C * sizeof(float) <= 64 * 1024, "head_dgrad: C=%d must be a multiple of 128, <= 1024", C);
-  B2C_REQUIRE(h % DP == 0, "head_dgrad: h=%d must be even", h);
   if (head_v2() && 256 % (C / 4) == 0) {
-    const int dpx = h % 4 == 0 ? 4 : 2;
+    const int dpx = h % 4 == 0 ? 4 : (h % 2 == 0 ? 2 : 1);  // odd maps (img_size = 16 * odd): one pixel per thread
     const long long ngroups = (long long)N * h * (h / dpx);
     const int gpb = 256 / (C / 4);
     long long blocks = (ngroups + gpb - 1) / gpb;
     if (blocks > 148 * 2) blocks = 148 * 2;
     if (dpx == 4)
       head_dgrad2_kernel<4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(gy, w, (__nv_bfloat16*)ga, N, h, C);
-    else
+    else if (dpx == 2)
       head_dgrad2_kernel<2><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(gy, w, (__nv_bfloat16*)ga, N, h, C);
+    else
+      head_dgrad2_kernel<1><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(gy, w, (__nv_bfloat16*)ga, N, h, C);
     return b2c_check_launch("head_dgrad2");
   }
+  B2C_REQUIRE(h % DP == 0, "head_dgrad: h=%d must be even", h);
   static bool attr_done = false;
   if (!attr_done) {
     cudaFuncSetAttribute(head_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);

@@ -306,7 +306,7 @@ def test_first_layer(L, cin, N, S, interp):
     assert abs(dot - float((refdw.double() * w.double()).sum())) <= 1e-4 * float(refdw.norm() * w.norm())
 
 
-@pytest.mark.parametrize("N,h", [(3, 8), (5, 16), (2, 4), (3, 2), (64, 16)])
+@pytest.mark.parametrize("N,h", [(3, 8), (5, 16), (2, 4), (3, 2), (64, 16), (3, 3), (2, 5), (2, 6)])
 def test_head(L, N, h):
     g = torch.Generator().manual_seed(6)
     C = 512

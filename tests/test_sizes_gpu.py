@@ -10,7 +10,7 @@ import cgan_oracle as O
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("B,S", [(2, 512), (5, 128), (1, 256), (2, 96), (3, 160), (2, 192)])
+@pytest.mark.parametrize("B,S", [(2, 512), (5, 128), (1, 256), (2, 96), (3, 160), (2, 192), (2, 48), (2, 80)])
 def test_one_step_vs_oracle(B, S):
     from b200cgan.models import Discriminator, GeneratorUNet
     from b200cgan.train_step import CGANTrainer
