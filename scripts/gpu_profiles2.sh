@@ -10,4 +10,5 @@ M=gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__pipe_ten
 timeout 1500 ncu --metrics $M --clock-control none --profile-from-start off --csv --page raw --log-file $P/step_raw.csv python scripts/one_step.py > $P/step.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:"tapgemm_pair_kernel" -c 1 -f -o $P/top_conv python scripts/one_step.py > $P/top_conv.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:"wgrad_pair_kernel" -c 1 -f -o $P/top_wgrad python scripts/one_step.py > $P/top_wgrad.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:"convt64_kernel" -c 1 -f -o $P/top_convt64 python scripts/one_step.py > $P/top_convt64.log 2>&1
 ls -la $P
