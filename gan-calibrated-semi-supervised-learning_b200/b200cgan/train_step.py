@@ -88,7 +88,11 @@ class GradBuckets:
     (after that slice's spectral-norm rank-1 terms were flushed), while backward keeps running on the main stream.  finish()
     reduces whatever is left and joins the streams.  The 1/world factor is applied inside the Adam kernel."""
 
-    def __init__(self, opt, group, min_bytes=4 << 20):
+    def __init__(self, opt, group, min_bytes=None):
+        import os
+        if min_bytes is None:
+            min_bytes = int(os.environ.get("B2C_DP_BUCKET_MB", "4")) << 20
+        self.overlap = os.environ.get("B2C_DP_OVERLAP", "1") != "0"
         self.opt, self.group = opt, group
         self.index = {id(p): i for i, p in enumerate(opt.params)}
         self.expected = None            # writes per parameter and backward (learned)
@@ -115,7 +119,7 @@ class GradBuckets:
         if i is None:
             return
         self.counts[i] += 1
-        if self.expected is None:
+        if self.expected is None or not self.overlap:
             return
         for k, (lo, hi, idxs) in enumerate(self.slices):
             if self.done[k]:
@@ -138,6 +142,11 @@ class GradBuckets:
     def finish(self):
         if self.expected is None:
             self.expected = list(self.counts)  # learned: from the next backward on, slices go out as they complete
+        if not self.overlap:  # B2C_DP_OVERLAP=0: one all-reduce of the whole bucket after backward, on the main stream
+            import torch.distributed as dist
+            ops.flush_sn_pending(list(self.opt.params))
+            dist.all_reduce(self.opt.flat_g, op=dist.ReduceOp.SUM, group=self.group)
+            return
         for k in range(len(self.slices)):
             if not self.done[k]:
                 self._reduce(k)
