@@ -420,6 +420,272 @@ __global__ void __launch_bounds__(1024) head_wgrad2_kernel(const __nv_bfloat16* 
   }
 }
 
+// ------------------------------------------------------------------------------------------------ fprop on mma.sync
+// The per-tap dot products of head_fprop_kernel are a GEMM with N = 16: P[pixel][tap] = a[pixel][:] . w[:][tap].  On the
+// CUDA cores it is FFMA- and LDS-bound (22 us for 17 MB at (64, 16, 512)); here a warp owns 16 pixels x 16 taps as two
+// m16n8k16 bf16 MMAs per 16 channels, so what is left is the activation stream.  The contraction index may be permuted
+// freely as long as A and B agree, which lets every thread feed its A fragments from ONE 16-byte load per pixel row (8
+// consecutive channels: 4 k-pairs = two MMAs) and its B fragments from one LDS.128 of the [tap][channel] weight rows.
+// The fp32 weights enter as hi + lo bf16 pairs (two MMAs, 16 mantissa bits): results agree with the fp32-weight kernel to
+// ~1e-5.  The channel range is split over KS warps per pixel tile (the taps are scattered with atomics anyway).
+constexpr int H3_U = 4;        // 16-byte loads in flight per pixel row and thread
+constexpr int H3_THREADS = 512;
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                               uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__global__ void __launch_bounds__(H3_THREADS) head_fprop3_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ w,
+                                                                 float* __restrict__ out, int N, int h, int C, int KS) {
+  extern __shared__ __align__(16) uint8_t h3_smem[];
+  __nv_bfloat16* ws = reinterpret_cast<__nv_bfloat16*>(h3_smem);  // [hi, lo][16 taps][C + 32]: rows 64 B apart mod 128 B
+  const int ldw = C + 32;
+  for (int i = threadIdx.x; i < 4 * C; i += blockDim.x) {  // one float4 = 4 consecutive taps of a channel
+    const int c = i >> 2, t0 = (i & 3) * 4;
+    const float4 v = __ldg(reinterpret_cast<const float4*>(w) + i);
+    const float f[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __nv_bfloat16 hi = __float2bfloat16_rn(f[j]);
+      ws[(t0 + j) * ldw + c] = hi;
+      ws[(16 + t0 + j) * ldw + c] = __float2bfloat16_rn(f[j] - __bfloat162float(hi));
+    }
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int ho = h - 1, CK = C / KS;
+  const long long npix = (long long)N * h * h;
+  const long long items = ((npix + 15) / 16) * KS;
+  for (long long item = (long long)blockIdx.x * (H3_THREADS / 32) + warp; item < items; item += (long long)gridDim.x * (H3_THREADS / 32)) {
+    const long long p0 = (item / KS) * 16;
+    const int cbase = (int)(item % KS) * CK + 8 * t;
+    const long long r0 = p0 + g, r1 = p0 + g + 8;
+    const bool v0 = r0 < npix, v1 = r1 < npix;
+    const uint4* pa = reinterpret_cast<const uint4*>(a + (v0 ? r0 : 0) * C + cbase);
+    const uint4* pb = reinterpret_cast<const uint4*>(a + (v1 ? r1 : 0) * C + cbase);
+    float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+    for (int c = 0; c < CK; c += 32 * H3_U) {
+      uint4 ra[H3_U], rb[H3_U];
+#pragma unroll
+      for (int u = 0; u < H3_U; ++u) {
+        ra[u] = v0 ? __ldg(pa + (c + 32 * u) / 8) : make_uint4(0, 0, 0, 0);
+        rb[u] = v1 ? __ldg(pb + (c + 32 * u) / 8) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < H3_U; ++u) {
+        const int cc = cbase + c + 32 * u;
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          const uint4 bh = *reinterpret_cast<const uint4*>(ws + (nt * 8 + g) * ldw + cc);
+          const uint4 bl = *reinterpret_cast<const uint4*>(ws + (16 + nt * 8 + g) * ldw + cc);
+          mma_bf16_16816(acc[nt], ra[u].x, rb[u].x, ra[u].y, rb[u].y, bh.x, bh.y);
+          mma_bf16_16816(acc[nt], ra[u].z, rb[u].z, ra[u].w, rb[u].w, bh.z, bh.w);
+          mma_bf16_16816(acc[nt], ra[u].x, rb[u].x, ra[u].y, rb[u].y, bl.x, bl.y);
+          mma_bf16_16816(acc[nt], ra[u].z, rb[u].z, ra[u].w, rb[u].w, bl.z, bl.w);
+        }
+      }
+    }
+    // C fragment: acc[nt][j] = P[row g + 8 (j >> 1)][tap nt * 8 + 2 t + (j & 1)]
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const long long pix = half ? r1 : r0;
+      if (pix >= npix) continue;
+      const int ix = (int)(pix % h), iy = (int)((pix / h) % h);
+      float* on = out + (pix / ((long long)h * h)) * ho * ho;
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int tap = nt * 8 + 2 * t + j;
+          const int oy = iy - (tap >> 2) + 1, ox = ix - (tap & 3) + 1;
+          if (oy >= 0 && oy < ho && ox >= 0 && ox < ho) atomicAdd(on + oy * ho + ox, acc[nt][half * 2 + j]);
+        }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ dgrad on mma.sync
+// ga[pixel][c] = sum_tap G[pixel][tap] w[c][tap] with G[pixel][tap] = gy[n, iy - ky + 1, ix - kx + 1] (0 outside): a GEMM with
+// K = 16 taps = ONE k16 step.  A warp owns 16 pixels: it gathers its A fragments (G, split hi + lo) once and then walks the
+// channels in groups of 4 n-tiles whose columns are PERMUTED so that a thread's 8 accumulators of a pixel row are 8
+// consecutive channels (logical column 2t'+e of n-tile j = channel base + 8t' + 2j + e): one 16-byte store per row and group.
+// Weights: bf16x2 tap pairs, hi and lo, as [pair][C + 2] words in shared memory (conflict-free for the B fragment reads);
+// three MMAs per n-tile (hi*hi + lo*hi + hi*lo) keep 16 mantissa bits of both operands.
+__device__ __forceinline__ void split_bf16x2(float x, float y, uint32_t& hi, uint32_t& lo) {
+  const __nv_bfloat16 xh = __float2bfloat16_rn(x), yh = __float2bfloat16_rn(y);
+  hi = (uint32_t)__bfloat16_as_ushort(xh) | ((uint32_t)__bfloat16_as_ushort(yh) << 16);
+  lo = pack_bf16(x - __bfloat162float(xh), y - __bfloat162float(yh));
+}
+
+__global__ void __launch_bounds__(H3_THREADS) head_dgrad3_kernel(const float* __restrict__ gy, const float* __restrict__ w,
+                                                                 __nv_bfloat16* __restrict__ ga, int N, int h, int C, int NS) {
+  extern __shared__ __align__(16) uint8_t h3_smem[];
+  uint32_t* wsd = reinterpret_cast<uint32_t*>(h3_smem);  // [hi, lo][8 tap pairs][C + 2]
+  const int ldw = C + 2;
+  for (int i = threadIdx.x; i < 8 * C; i += blockDim.x) {
+    const int c = i >> 3, tp = i & 7;
+    const float2 v = __ldg(reinterpret_cast<const float2*>(w) + i);
+    uint32_t hi, lo;
+    split_bf16x2(v.x, v.y, hi, lo);
+    wsd[tp * ldw + c] = hi;
+    wsd[(8 + tp) * ldw + c] = lo;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int ho = h - 1, CN = C / NS;
+  const long long npix = (long long)N * h * h;
+  const long long items = ((npix + 15) / 16) * NS;
+  for (long long item = (long long)blockIdx.x * (H3_THREADS / 32) + warp; item < items; item += (long long)gridDim.x * (H3_THREADS / 32)) {
+    const long long p0 = (item / NS) * 16;
+    const int cbeg = (int)(item % NS) * CN;
+    uint32_t ah[4], al[4];  // a0: row g, taps 2t,2t+1; a1: row g+8, same taps; a2 / a3: taps 2t+8, 2t+9
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const long long pix = p0 + g + 8 * half;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (pix < npix) {
+        const int ix = (int)(pix % h), iy = (int)((pix / h) % h);
+        const float* gn = gy + (pix / ((long long)h * h)) * ho * ho;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int tap = 2 * t + (q & 1) + 8 * (q >> 1);
+          const int oy = iy - (tap >> 2) + 1, ox = ix - (tap & 3) + 1;
+          if (oy >= 0 && oy < ho && ox >= 0 && ox < ho) v[q] = __ldg(gn + oy * ho + ox);
+        }
+      }
+      split_bf16x2(v[0], v[1], ah[half], al[half]);
+      split_bf16x2(v[2], v[3], ah[2 + half], al[2 + half]);
+    }
+    const long long pr0 = p0 + g, pr1 = p0 + g + 8;
+    for (int base = cbeg; base < cbeg + CN; base += 32) {
+      float acc[4][4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+        const int ch = base + 8 * (g >> 1) + 2 * j + (g & 1);
+        const uint32_t b0h = wsd[t * ldw + ch], b1h = wsd[(t + 4) * ldw + ch];
+        const uint32_t b0l = wsd[(8 + t) * ldw + ch], b1l = wsd[(12 + t) * ldw + ch];
+        mma_bf16_16816(acc[j], ah[0], ah[1], ah[2], ah[3], b0h, b1h);
+        mma_bf16_16816(acc[j], al[0], al[1], al[2], al[3], b0h, b1h);
+        mma_bf16_16816(acc[j], ah[0], ah[1], ah[2], ah[3], b0l, b1l);
+      }
+      if (pr0 < npix)
+        *reinterpret_cast<uint4*>(ga + pr0 * C + base + 8 * t) =
+            make_uint4(pack_bf16(acc[0][0], acc[0][1]), pack_bf16(acc[1][0], acc[1][1]), pack_bf16(acc[2][0], acc[2][1]),
+                       pack_bf16(acc[3][0], acc[3][1]));
+      if (pr1 < npix)
+        *reinterpret_cast<uint4*>(ga + pr1 * C + base + 8 * t) =
+            make_uint4(pack_bf16(acc[0][2], acc[0][3]), pack_bf16(acc[1][2], acc[1][3]), pack_bf16(acc[2][2], acc[2][3]),
+                       pack_bf16(acc[3][2], acc[3][3]));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ wgrad on mma.sync
+// dw[c][tap] += sum_pixel a[pixel][c] G[pixel][tap]: D[16 taps][8 channels] += A[16 taps][16 pixels] B[16 pixels][8 channels].
+// B wants pixel PAIRS of one channel per register, memory has channel pairs of one pixel: a thread loads 8 consecutive
+// channels of pixel row g (one 16-byte load = the row-major fragments of four 8x8 tiles under the channel permutation of
+// the dgrad kernel above) and `movmatrix.trans` turns each into the B fragment.  A warp owns a 128-channel slice (64
+// accumulators) and a quarter of the CTA's pixel tiles; the CTA's warps meet in a shared [16][C + 1] array, then one global
+// atomic per element and CTA (dw is accumulated into, as before).  G is split hi + lo (two MMAs), the activations are exact.
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t x) {
+  uint32_t y;
+  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(y) : "r"(x));
+  return y;
+}
+
+constexpr int W3_CW = 128;  // channels per warp
+__global__ void __launch_bounds__(H3_THREADS) head_wgrad3_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ gy,
+                                                                 float* __restrict__ dw, int N, int h, int C) {
+  extern __shared__ __align__(16) uint8_t h3_smem[];
+  float* sacc = reinterpret_cast<float*>(h3_smem);  // [16 taps][C + 1]
+  const int lds = C + 1;
+  for (int i = threadIdx.x; i < 16 * lds; i += blockDim.x) sacc[i] = 0.f;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int nslices = C / W3_CW, PG = (H3_THREADS / 32) / nslices;  // pixel groups per CTA
+  const int slice = warp % nslices, pg = warp / nslices;
+  const int ho = h - 1, cbeg = slice * W3_CW;
+  const long long npix = (long long)N * h * h, ntiles = (npix + 15) / 16;
+  float acc[W3_CW / 32][4][4];
+#pragma unroll
+  for (int q = 0; q < W3_CW / 32; ++q)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[q][j][0] = acc[q][j][1] = acc[q][j][2] = acc[q][j][3] = 0.f;
+  if (pg < PG)
+    for (long long tile = (long long)blockIdx.x * PG + pg; tile < ntiles; tile += (long long)gridDim.x * PG) {
+      const long long p0 = tile * 16;
+      const long long r0 = p0 + g, r1 = p0 + g + 8;
+      const bool v0 = r0 < npix, v1 = r1 < npix;
+      const uint4* pa = reinterpret_cast<const uint4*>(a + (v0 ? r0 : 0) * C + cbeg + 8 * t);
+      const uint4* pb = reinterpret_cast<const uint4*>(a + (v1 ? r1 : 0) * C + cbeg + 8 * t);
+      uint4 ra[W3_CW / 32], rb[W3_CW / 32];
+#pragma unroll
+      for (int q = 0; q < W3_CW / 32; ++q) {
+        ra[q] = v0 ? __ldg(pa + 4 * q) : make_uint4(0, 0, 0, 0);
+        rb[q] = v1 ? __ldg(pb + 4 * q) : make_uint4(0, 0, 0, 0);
+      }
+      // A fragments: G[pixel][tap] for pixels 2t, 2t+1 (a0, a1) and 2t+8, 2t+9 (a2, a3), taps g (a0, a2) and g+8 (a1, a3)
+      uint32_t ah[4], al[4];
+#pragma unroll
+      for (int kh = 0; kh < 2; ++kh) {
+        float v[2][2] = {{0.f, 0.f}, {0.f, 0.f}};  // [tap half][pixel of the pair]
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const long long pix = p0 + 2 * t + e + 8 * kh;
+          if (pix < npix) {
+            const int ix = (int)(pix % h), iy = (int)((pix / h) % h);
+            const float* gn = gy + (pix / ((long long)h * h)) * ho * ho;
+#pragma unroll
+            for (int th = 0; th < 2; ++th) {
+              const int tap = g + 8 * th;
+              const int oy = iy - (tap >> 2) + 1, ox = ix - (tap & 3) + 1;
+              if (oy >= 0 && oy < ho && ox >= 0 && ox < ho) v[th][e] = __ldg(gn + oy * ho + ox);
+            }
+          }
+        }
+        split_bf16x2(v[0][0], v[0][1], ah[2 * kh], al[2 * kh]);
+        split_bf16x2(v[1][0], v[1][1], ah[2 * kh + 1], al[2 * kh + 1]);
+      }
+#pragma unroll
+      for (int q = 0; q < W3_CW / 32; ++q) {
+        const uint32_t x0[4] = {ra[q].x, ra[q].y, ra[q].z, ra[q].w}, x1[4] = {rb[q].x, rb[q].y, rb[q].z, rb[q].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t b0 = movmatrix_trans(x0[j]), b1 = movmatrix_trans(x1[j]);
+          mma_bf16_16816(acc[q][j], ah[0], ah[1], ah[2], ah[3], b0, b1);
+          mma_bf16_16816(acc[q][j], al[0], al[1], al[2], al[3], b0, b1);
+        }
+      }
+    }
+  // acc[q][j][e] = D[tap g][channel cbeg + 32 q + 8 t + 2 j + e], acc[q][j][2 + e]: tap g + 8
+  if (pg < PG) {
+#pragma unroll
+    for (int q = 0; q < W3_CW / 32; ++q)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int c = cbeg + 32 * q + 8 * t + 2 * j + e;
+          atomicAdd(sacc + g * lds + c, acc[q][j][e]);
+          atomicAdd(sacc + (g + 8) * lds + c, acc[q][j][2 + e]);
+        }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 16 * C; i += blockDim.x) atomicAdd(dw + i, sacc[(i & 15) * lds + (i >> 4)]);
+}
+
+static bool head_mma() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B2C_HEAD_MMA");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 static bool head_v2() {
   static int v = -1;
   if (v < 0) {
@@ -447,6 +713,20 @@ extern "C" int b2c_head_fprop(const void* a, const float* w, float* out, int N, 
     head_fprop2_kernel<512><<<(unsigned)blocks, 128, 0, st>>>((const __nv_bfloat16*)a, w, out, N, h);
     return b2c_check_launch("head_fprop2");
   }
+  if (head_mma() && C % (32 * H3_U) == 0 && C <= 1024 && ((uintptr_t)a & 15) == 0) {
+    const int KS = C % (64 * H3_U) == 0 ? 2 : 1;
+    const size_t smem3 = (size_t)32 * (C + 32) * sizeof(__nv_bfloat16);
+    static bool attr3 = false;
+    if (!attr3) {
+      cudaFuncSetAttribute(head_fprop3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
+      attr3 = true;
+    }
+    const long long items = ((npix + 15) / 16) * KS, wpb = H3_THREADS / 32;
+    long long blocks = (items + wpb - 1) / wpb;
+    if (blocks > 148) blocks = 148;  // one CTA per SM: the weight staging is paid per CTA
+    head_fprop3_kernel<<<(unsigned)blocks, H3_THREADS, smem3, st>>>((const __nv_bfloat16*)a, w, out, N, h, C, KS);
+    return b2c_check_launch("head_fprop3");
+  }
   const size_t smem = (size_t)16 * C * sizeof(float);
   static bool attr_done = false;
   if (!attr_done) {
@@ -462,6 +742,21 @@ extern "C" int b2c_head_fprop(const void* a, const float* w, float* out, int N, 
 
 extern "C" int b2c_head_dgrad(const float* gy, const float* w, void* ga, int N, int h, int C, void* stream) {
   B2C_REQUIRE(C % 128 == 0 && (size_t)16 * C * sizeof(float) <= 64 * 1024, "head_dgrad: C=%d must be a multiple of 128, <= 1024", C);
+  if (head_mma() && C % 64 == 0 && ((uintptr_t)ga & 15) == 0) {
+    const int NS = 2;
+    const size_t smem3 = (size_t)16 * (C + 2) * sizeof(uint32_t);
+    static bool attr3 = false;
+    if (!attr3) {
+      cudaFuncSetAttribute(head_dgrad3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
+      attr3 = true;
+    }
+    const long long npix = (long long)N * h * h;
+    const long long items = ((npix + 15) / 16) * NS, wpb = H3_THREADS / 32;
+    long long blocks = (items + wpb - 1) / wpb;
+    if (blocks > 148) blocks = 148;
+    head_dgrad3_kernel<<<(unsigned)blocks, H3_THREADS, smem3, (cudaStream_t)stream>>>(gy, w, (__nv_bfloat16*)ga, N, h, C, NS);
+    return b2c_check_launch("head_dgrad3");
+  }
   if (head_v2() && 256 % (C / 4) == 0) {
     const int dpx = h % 4 == 0 ? 4 : (h % 2 == 0 ? 2 : 1);  // odd maps (img_size = 16 * odd): one pixel per thread
     const long long ngroups = (long long)N * h * (h / dpx);
@@ -494,6 +789,20 @@ extern "C" int b2c_head_dgrad(const float* gy, const float* w, void* ga, int N, 
 extern "C" int b2c_head_wgrad(const void* a, const float* gy, float* dw, int N, int h, int C, void* stream) {
   B2C_REQUIRE(C == 256 || C == 512, "head_wgrad: C=%d must be 256 or 512", C);
   const long long npix = (long long)N * h * h;
+  if (head_mma() && ((uintptr_t)a & 15) == 0) {
+    const size_t smem3 = (size_t)16 * (C + 1) * sizeof(float);
+    static bool attr3 = false;
+    if (!attr3) {
+      cudaFuncSetAttribute(head_wgrad3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
+      attr3 = true;
+    }
+    const int PG = (H3_THREADS / 32) / (C / W3_CW);
+    long long blocks = ((npix + 15) / 16 + PG - 1) / PG;
+    if (blocks > 148) blocks = 148;  // fewer CTAs are slower (96: +3, 74: +5 us at (64, 16, 512)): the stream, not the atomics, is the cost
+    if (blocks < 1) blocks = 1;
+    head_wgrad3_kernel<<<(unsigned)blocks, H3_THREADS, smem3, (cudaStream_t)stream>>>((const __nv_bfloat16*)a, gy, dw, N, h, C);
+    return b2c_check_launch("head_wgrad3");
+  }
   if (head_v2()) {
     long long blocks = (npix + HW_MAXPIX - 1) / HW_MAXPIX;  // at most HW_MAXPIX pixels per block ...
     if (blocks < 148 && npix >= 148 * 8) blocks = 148;        // ... and every SM busy when there is enough work
