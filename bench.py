@@ -379,10 +379,11 @@ def run_b200(args):
         return float(t)
 
     # ---- device-resident leg: `value`.  With CUDA-graph mode the first two steps run eagerly, the third is captured.
+    tr.step(*[resident[0][k] for k in keys])  # first step: allocates the weight-pack buffers (lazy per-weight packs)
     l0 = _lib.launch_count()
-    tr.step(*[resident[0][k] for k in keys])
-    launches_per_step = _lib.launch_count() - l0  # libb2c entry-point calls of one (eager) step
-    for i in range(1, max(W, 3)):
+    tr.step(*[resident[1][k] for k in keys])
+    launches_per_step = _lib.launch_count() - l0  # libb2c entry-point calls of one steady-state (eager) step
+    for i in range(2, max(W, 3)):
         tr.step(*[resident[i % 2][k] for k in keys])
     barrier()
     clocks = ClockSampler(local)

@@ -124,6 +124,29 @@ def invalidate_packs():
         e["c_ok"] = e["t_ok"] = e["k3_ok"] = False
 
 
+def pack_all(params):
+    """Re-pack, in ONE launch, every stale bf16 pack of these parameters whose buffer already exists (i.e. that has been
+    used in that layout before).  FusedClipAdam calls it right after its update: the 26 lazy per-weight pack launches of a
+    step become 3, and a captured step starts with current packs."""
+    jobs = []
+    for p in params:
+        e = _PACKS.get(id(p))
+        if e is None or e["ref"] is not p or (e["c"] is None and e["t"] is None):
+            continue
+        e = _pack_entry(p)
+        d0, d1 = p.shape[:2]
+        for kind, name in ((0, "c"), (1, "t")):
+            if e[name] is not None and not e[name + "_ok"]:
+                jobs.append((p.data_ptr(), e[name].data_ptr(), d0, d1, kind))
+                e[name + "_ok"] = True
+    if not jobs:
+        return
+    n = len(jobs)
+    P, I = ctypes.c_void_p, ctypes.c_int
+    _lib.call("b2c_pack_w_multi", (P * n)(*[j[0] for j in jobs]), (P * n)(*[j[1] for j in jobs]), (I * n)(*[j[2] for j in jobs]),
+              (I * n)(*[j[3] for j in jobs]), (I * n)(*[j[4] for j in jobs]), n)
+
+
 def packed_c(param):
     """bf16 [D0][16*D1] K-major operand of the UN-SCALED master weight; re-packed only after the weight changed
     (torch version counter, or FusedClipAdam's epoch stamp) - once per optimizer step instead of once per forward."""
@@ -1110,4 +1133,5 @@ class FusedClipAdam:
                   self.step_base)
         for p in self.params:
             p._b2c_epoch = getattr(p, "_b2c_epoch", 0) + 1  # cached bf16 packs of this weight are stale now
+        pack_all(self.params)
         return self.gnorm_sq

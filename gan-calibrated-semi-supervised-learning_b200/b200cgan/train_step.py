@@ -386,7 +386,10 @@ class CGANTrainer:
         rng.set_device_base(self._ctr[0:1])
         self.optD.step_base, self.optG.step_base = self._ctr[1:2], self._ctr[2:3]
         self.optD.step_count = self.optG.step_count = 0
-        ops.invalidate_packs()  # the capture must contain every weight pack the replays need
+        # every optimizer step re-packs its network's weights itself (ops.pack_all): the capture then contains exactly the
+        # packs the replays need, provided the packs are current when it starts
+        ops.pack_all(self.optD.params)
+        ops.pack_all(self.optG.params)
         torch.cuda.synchronize()
         self._graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._graph):

@@ -22,6 +22,10 @@ int b2c_zero(void* p, long long bytes, void* stream); /* cudaMemsetAsync: gradie
  * optimizer step and applies 1/sigma as the `scale` of the GEMM epilogues instead ---- */
 int b2c_pack_w_c(const float* w, const float* inv_sigma, void* out_bf16, int D0, int D1, void* stream);
 int b2c_pack_w_t(const float* w, const float* inv_sigma, void* out_bf16, int D0, int D1, void* stream);
+/* all stale packs of a network in one launch (after its optimizer step): HOST arrays of njobs entries, kind 0 = C-form,
+ * 1 = T-form, un-scaled (inv_sigma = NULL above) */
+int b2c_pack_w_multi(const void* const* w, void* const* out_bf16, const int* D0, const int* D1, const int* kind, int njobs,
+                     void* stream);
 
 /* ---- tcgen05 implicit-GEMM convolutions ----
  * conv4s2 : nn.Conv2d(k4,s2,p1) fprop (cgan/models.py:57,236) and ConvTranspose2d dgrad.   x dense (N,H,W,Cin).

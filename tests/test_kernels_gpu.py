@@ -322,3 +322,25 @@ def test_head(L, N, h):
     dw = torch.zeros(1, C, 4, 4, device="cuda")
     L.call("b2c_head_wgrad", nhwc(a), gy.cuda(), dw, N, h, C)
     assert rel(dw, torch.nn.grad.conv2d_weight(a, (1, C, 4, 4), gy, 1, 1)) < 1e-4
+
+
+def test_pack_w_multi_equals_single_packs(L):
+    """b2c_pack_w_multi (all stale packs of a network in one launch) writes exactly what b2c_pack_w_c / _t write."""
+    g = torch.Generator().manual_seed(11)
+    shapes = [(128, 64), (256, 128), (512, 512), (64, 128), (512, 1024)]
+    ws = [torch.randn(d0, d1, 4, 4, generator=g).cuda() for d0, d1 in shapes]
+    ref, jobs = [], []
+    for w, (d0, d1) in zip(ws, shapes):
+        for kind, name, shape in ((0, "b2c_pack_w_c", (d0, 16 * d1)), (1, "b2c_pack_w_t", (4, d1, 4 * d0))):
+            r = torch.empty(shape, dtype=torch.bfloat16, device="cuda")
+            L.call(name, w, None, r, d0, d1)
+            o = torch.full(shape, float("nan"), dtype=torch.bfloat16, device="cuda")
+            ref.append(r)
+            jobs.append((w, o, d0, d1, kind))
+    n = len(jobs)
+    P, I = ctypes.c_void_p, ctypes.c_int
+    L.call("b2c_pack_w_multi", (P * n)(*[j[0].data_ptr() for j in jobs]), (P * n)(*[j[1].data_ptr() for j in jobs]),
+           (I * n)(*[j[2] for j in jobs]), (I * n)(*[j[3] for j in jobs]), (I * n)(*[j[4] for j in jobs]), n)
+    torch.cuda.synchronize()
+    for r, j in zip(ref, jobs):
+        assert torch.equal(r.view(torch.int16), j[1].view(torch.int16))
