@@ -43,3 +43,20 @@ def test_drop_in_surface_names_and_state_dict_keys():
     assert float(D.model[0].bias.abs().max()) == 0.0 and abs(float(D.model[2].weight_orig.std()) - 0.02) < 2e-3
     for name in ("EIoULoss", "HybridLoss", "smooth_clamp", "apply_delta_to_bbox", "iou_metric", "compute_gradient_penalty"):
         assert hasattr(losses, name)
+
+
+def test_environment_switches_are_documented():
+    """Every B2C_* variable the library or the package reads appears in DESIGN.md's switches table, and vice versa."""
+    import re
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    pkg = root / "gan-calibrated-semi-supervised-learning_b200"
+    read = set()
+    for f in list((pkg / "csrc").glob("*.cu")) + list((pkg / "csrc").glob("*.cuh")) + list((pkg / "b200cgan").glob("*.py")):
+        text = f.read_text()
+        read |= set(re.findall(r'(?:getenv|env_int|environ\.get)\(\s*"(B2C_[A-Z0-9_]+)"', text))
+    design = (root / "DESIGN.md").read_text()
+    table = design[design.index("### Switches"):design.index("## 4. Oracle and parity")]
+    documented = set(re.findall(r"`(B2C_[A-Z0-9_]+)", table))
+    assert read - documented == set(), sorted(read - documented)
+    assert documented - read == set(), sorted(documented - read)
