@@ -331,6 +331,10 @@ class CGANTrainer:
             if a is not None and s.data_ptr() != a.data_ptr():
                 s.copy_(a, non_blocking=True)
         self._load_injected()
+        # weights changed through torch since the last step (load_state_dict, manual edits): the captured step only re-packs
+        # after its own optimizer updates, so refresh the stale bf16 packs here (no launch when nothing changed)
+        ops.pack_all(self.optD.params)
+        ops.pack_all(self.optG.params)
         self._graph.replay()
         self._ctr.add_(self._ctr_inc)  # dropout stream position, D / G Adam step counts
         self.optD.host_steps += self.n_critic

@@ -9,7 +9,7 @@ import cgan_oracle as O
 pytestmark = pytest.mark.gpu
 
 
-def run(use_graph, steps, B=2, S=64):
+def run(use_graph, steps, B=2, S=64, reload_at=None):
     from b200cgan import rng
     from b200cgan.models import Discriminator, GeneratorUNet
     from b200cgan.train_step import CGANTrainer
@@ -23,6 +23,8 @@ def run(use_graph, steps, B=2, S=64):
     tr = CGANTrainer(G, D, n_critic=2, lambda_gp=1.0, use_cuda_graph=use_graph)
     logs = []
     for i in range(steps):
+        if i == reload_at:  # weights replaced through torch between two steps (a checkpoint restored mid-run)
+            G.load_state_dict(st["G"]); D.load_state_dict(st["D"])
         batch, _, _ = O.make_batch(B, S, i)
         out = tr.step(*[batch[k].cuda() for k in ("pred", "gt", "refined", "pred_box", "delta_true")])
         logs.append(out.to_host())
@@ -53,3 +55,18 @@ def test_graph_replay_matches_eager():
         if we[k].numel() > 1000:
             rel = float((we[k] - wg[k]).norm() / (we[k].norm() + 1e-30))
             assert rel < 2e-2, (k, rel)
+
+
+def test_graph_replay_sees_weights_loaded_between_steps():
+    """load_state_dict between two replays: the captured step re-packs the bf16 weight operands only after its own optimizer
+    updates, so the trainer must refresh them before the replay.  Reloading the INITIAL weights before step 4 makes that
+    step's generator output a function of the initial weights and its batch alone: graph and eager runs agree on it tightly
+    (a replay on stale packs would still carry three steps of updates)."""
+    le, we, _ = run(False, 5, reload_at=4)
+    lg, wg, _ = run(True, 5, reload_at=4)
+    for k in ("loss_iou", "loss_G", "wd", "gp", "d_loss"):
+        assert abs(le[4][k] - lg[4][k]) <= 3e-2 * abs(le[4][k]) + 5e-3, (k, le[4][k], lg[4][k])
+    for k in we:
+        if we[k].numel() > 1000:
+            rel = float((we[k] - wg[k]).norm() / (we[k].norm() + 1e-30))
+            assert rel < 1e-2, (k, rel)  # one optimizer step away from identical weights
